@@ -1,0 +1,197 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes binding of oracle/liborb_oracle.so (the CPU restatement).
+
+May be imported only by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs. The product package never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+KNN_DTYPE = np.dtype([("d1", "<i4"), ("d2", "<i4"), ("i1", "<i8"), ("i2", "<i8")])
+
+UPSTREAM_PYRAMID, LEGACY_BLUR, LIBM_TRIG = 1, 2, 4
+
+
+def build(force: bool = False) -> str:
+    so = os.path.join(_HERE, "liborb_oracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "cv_primitives.cpp", "orb_oracle.h", "cv_primitives.h")]
+    if force or not os.path.exists(so) or any(os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liborb_oracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build())
+        u8p, i32p, f32p, vp = C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_float), C.c_void_p
+        L.orb_oracle_create.restype = vp
+        L.orb_oracle_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.orb_oracle_destroy.argtypes = [vp]
+        L.orb_oracle_get_table.argtypes = [vp, C.c_int, vp]
+        L.orb_oracle_get_quota.argtypes = [vp, vp]
+        L.orb_oracle_get_umax.argtypes = [vp, vp]
+        L.orb_oracle_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, C.c_int, vp]
+        L.orb_oracle_level_dims.argtypes = [vp, C.c_int, i32p, i32p]
+        L.orb_oracle_level_ptr.restype = vp
+        L.orb_oracle_level_ptr.argtypes = [vp, C.c_int]
+        L.orb_oracle_blurred_ptr.restype = vp
+        L.orb_oracle_blurred_ptr.argtypes = [vp, C.c_int]
+        L.orb_oracle_raw_count.argtypes = [vp, C.c_int]
+        L.orb_oracle_raw_keypoints.argtypes = [vp, C.c_int, vp, C.c_int]
+        L.orb_oracle_resize.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int]
+        L.orb_oracle_border101.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int]
+        L.orb_oracle_blur.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int]
+        L.orb_oracle_fast.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orb_oracle_fast_score_map.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp]
+        L.orb_oracle_fast_atan2.restype = C.c_float
+        L.orb_oracle_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orb_oracle_sincos.argtypes = [C.c_float, C.c_int, f32p, f32p]
+        L.orb_oracle_distribute.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
+        L.orb_oracle_descriptor_distance.argtypes = [vp, vp]
+        L.orb_oracle_hamming_knn.argtypes = [vp, C.c_int, vp, C.c_int64, C.c_int64, C.c_int, vp, C.c_int]
+        L.orb_oracle_extract_many.restype = C.c_int64
+        L.orb_oracle_extract_many.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int,
+                                              C.c_int, C.c_int, C.c_int]
+        _LIB = L
+    return _LIB
+
+
+def _p(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class OracleExtractor:
+    """Mirror of ORB_SLAM2::ORBextractor (include/ORBextractor.h:104-185) over the CPU oracle."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, flags=0):
+        self.L = lib()
+        self.h = self.L.orb_oracle_create(nfeatures, scale_factor, nlevels, ini_th, min_th, flags)
+        if not self.h:
+            raise ValueError("bad ORB parameters")
+        self.nlevels, self.nfeatures = nlevels, nfeatures
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orb_oracle_destroy(self.h)
+            self.h = None
+
+    def table(self, what: int) -> np.ndarray:
+        out = np.zeros(self.nlevels, np.float32)
+        self.L.orb_oracle_get_table(self.h, what, _p(out))
+        return out
+
+    def quota(self) -> np.ndarray:
+        out = np.zeros(self.nlevels, np.int32)
+        self.L.orb_oracle_get_quota(self.h, _p(out))
+        return out
+
+    def umax(self) -> np.ndarray:
+        out = np.zeros(16, np.int32)
+        self.L.orb_oracle_get_umax(self.h, _p(out))
+        return out
+
+    def __call__(self, img: np.ndarray):
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        cap = self.nfeatures + 64 * self.nlevels + 1024
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        lc = np.zeros(self.nlevels, np.int32)
+        n = self.L.orb_oracle_extract(self.h, _p(img), img.strides[0], img.shape[1], img.shape[0], _p(kps), _p(desc),
+                                      cap, _p(lc))
+        if n < 0:
+            raise RuntimeError("oracle extract failed")
+        return kps[:n].copy(), desc[:n].copy(), lc
+
+    def level(self, l: int, blurred: bool = False):
+        c, r = C.c_int32(), C.c_int32()
+        self.L.orb_oracle_level_dims(self.h, l, C.byref(c), C.byref(r))
+        ptr = (self.L.orb_oracle_blurred_ptr if blurred else self.L.orb_oracle_level_ptr)(self.h, l)
+        if not ptr:
+            return None
+        buf = (C.c_uint8 * (c.value * r.value)).from_address(ptr)
+        return np.frombuffer(buf, np.uint8).reshape(r.value, c.value).copy()
+
+    def raw_keypoints(self, l: int) -> np.ndarray:
+        n = self.L.orb_oracle_raw_count(self.h, l)
+        out = np.zeros(max(n, 1), KP_DTYPE)
+        self.L.orb_oracle_raw_keypoints(self.h, l, _p(out), max(n, 1))
+        return out[:n]
+
+
+def resize(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orb_oracle_resize(_p(src), src.strides[0], src.shape[1], src.shape[0], _p(dst), dw, dw, dh)
+    return dst
+
+
+def border101(src: np.ndarray, b: int = 19) -> np.ndarray:
+    dst = np.zeros((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib().orb_oracle_border101(_p(src), src.strides[0], src.shape[1], src.shape[0], _p(dst), dst.shape[1], b)
+    return dst
+
+
+def blur(src: np.ndarray, legacy: bool = False) -> np.ndarray:
+    dst = np.zeros_like(src, order="C")
+    lib().orb_oracle_blur(_p(src), src.strides[0], src.shape[1], src.shape[0], _p(dst), dst.shape[1], int(legacy))
+    return dst
+
+
+def fast(img: np.ndarray, threshold: int) -> np.ndarray:
+    cap = img.size
+    out = np.zeros(max(cap, 1), KP_DTYPE)
+    n = lib().orb_oracle_fast(_p(img), img.strides[0], img.shape[1], img.shape[0], threshold, _p(out), cap)
+    return out[:n].copy()
+
+
+def fast_score_map(img: np.ndarray) -> np.ndarray:
+    out = np.zeros(img.shape, np.uint8)
+    lib().orb_oracle_fast_score_map(_p(img), img.strides[0], img.shape[1], img.shape[0], _p(out))
+    return out
+
+
+def fast_atan2(y: float, x: float) -> float:
+    return lib().orb_oracle_fast_atan2(y, x)
+
+
+def sincos(angle: float, libm: bool = False):
+    s, c = C.c_float(), C.c_float()
+    lib().orb_oracle_sincos(angle, int(libm), C.byref(s), C.byref(c))
+    return s.value, c.value
+
+
+def distribute(kps: np.ndarray, minx, maxx, miny, maxy, nfeat) -> np.ndarray:
+    kps = np.ascontiguousarray(kps)
+    out = np.zeros(len(kps) + 8, KP_DTYPE)
+    n = lib().orb_oracle_distribute(_p(kps), len(kps), minx, maxx, miny, maxy, nfeat, _p(out), len(out))
+    return out[:n].copy()
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().orb_oracle_descriptor_distance(_p(a), _p(b))
+
+
+def hamming_knn(q: np.ndarray, db: np.ndarray, index_base: int = 0, sentinel: int = 256, nthreads: int = 1) -> np.ndarray:
+    q = np.ascontiguousarray(q, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    out = np.zeros(len(q), KNN_DTYPE)
+    lib().orb_oracle_hamming_knn(_p(q), len(q), _p(db), len(db), index_base, sentinel, _p(out), nthreads)
+    return out
+
+
+def extract_many(frames: np.ndarray, nfeatures, nthreads, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, flags=0) -> int:
+    frames = np.ascontiguousarray(frames, np.uint8)
+    n, h, w = frames.shape
+    return lib().orb_oracle_extract_many(nfeatures, scale_factor, nlevels, ini_th, min_th, flags, _p(frames), w, h, n,
+                                         nthreads)

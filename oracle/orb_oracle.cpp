@@ -1,0 +1,525 @@
+// TEST INFRASTRUCTURE ONLY — see orb_oracle.h. Compile with -ffp-contract=off (canonical: no FMA).
+#include "orb_oracle.h"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstring>
+#include <list>
+#include <thread>
+#include <utility>
+#include <vector>
+
+#include "cv_primitives.h"
+
+namespace orb_oracle {
+
+static const int kPatch = 31, kHalfPatch = 15, kEdge = 19;  // src/ORBextractor.cc:80-82
+static const int8_t kPattern[256 * 4] = {
+#include "../include/orb_pattern_31.inc"
+};
+
+// Canonical sin/cos: fdlibm-style reduction + kernels in double, plain * + - only, one rounding
+// to float. Replaces libm cosf/sinf of src/ORBextractor.cc:184-186 (see header).
+static void sincos_canonical(float angle, float* s, float* c) {
+  const double x = (double)angle;
+  const double invpio2 = 6.36619772367581382433e-01, pio2_1 = 1.57079632673412561417e+00,
+               pio2_1t = 6.07710050650619224932e-11;
+  const double kf = std::floor(x * invpio2 + 0.5);
+  const int k = (int)kf;
+  const double r = (x - kf * pio2_1) - kf * pio2_1t;
+  const double z = r * r;
+  const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03, S3 = -1.98412698298579493134e-04,
+               S4 = 2.75573137070700676789e-06, S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
+  const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03, C3 = 2.48015872894767294178e-05,
+               C4 = -2.75573143513906633035e-07, C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+  const double ps = S2 + z * (S3 + z * (S4 + z * (S5 + z * S6)));
+  const double sn = r + (z * r) * (S1 + z * ps);
+  const double pc = z * (C1 + z * (C2 + z * (C3 + z * (C4 + z * (C5 + z * C6)))));
+  const double cs = 1.0 - (0.5 * z - z * pc);
+  switch (k & 3) {
+    case 0: *s = (float)sn; *c = (float)cs; break;
+    case 1: *s = (float)cs; *c = (float)(-sn); break;
+    case 2: *s = (float)(-sn); *c = (float)(-cs); break;
+    default: *s = (float)(-cs); *c = (float)sn; break;
+  }
+}
+
+struct Plane {
+  std::vector<uint8_t> buf;
+  int cols = 0, rows = 0;
+  void alloc(int c, int r) { cols = c; rows = r; buf.assign((size_t)c * r, 0); }
+  Img view() { return Img{buf.data(), cols, rows, cols}; }
+  Img view() const { return Img{const_cast<uint8_t*>(buf.data()), cols, rows, cols}; }
+};
+
+class Extractor {
+ public:
+  Extractor(int nf, float sf, int nl, int ini, int mn, int flags);
+  int run(const Img& image, std::vector<KeyPoint>& kps, std::vector<uint8_t>& desc);
+
+  int nfeatures, nlevels, iniTh, minTh, flags;
+  double scaleFactor;  // the reference member is double (include/ORBextractor.h:234)
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> quota, umax;
+  std::vector<Plane> pyr, blurred;
+  std::vector<char> has_blur;
+  std::vector<std::vector<KeyPoint>> raw;  // vToDistributeKeys per level
+  std::vector<int> levelCounts;
+
+ private:
+  void computePyramid(const Img& image);
+  void computeKeyPoints(std::vector<std::vector<KeyPoint>>& all);
+};
+
+std::vector<KeyPoint> distribute(const std::vector<KeyPoint>& in, int minX, int maxX, int minY, int maxY, int N,
+                                 int reserveHint);
+
+// src/ORBextractor.cc:776-925
+Extractor::Extractor(int nf, float sf, int nl, int ini, int mn, int fl)
+    : nfeatures(nf), nlevels(nl), iniTh(ini), minTh(mn), flags(fl), scaleFactor(sf) {
+  scale.resize(nl); invScale.resize(nl); sigma2.resize(nl); invSigma2.resize(nl);
+  scale[0] = 1.f; sigma2[0] = 1.f;
+  for (int i = 1; i < nl; ++i) {
+    scale[i] = (float)(scale[i - 1] * scaleFactor);  // float * double -> double, stored as float
+    sigma2[i] = scale[i] * scale[i];
+  }
+  for (int i = 0; i < nl; ++i) { invScale[i] = 1.f / scale[i]; invSigma2[i] = 1.f / sigma2[i]; }
+  quota.resize(nl);
+  const float factor = (float)(1.0f / scaleFactor);
+  float perScale = (float)(nf * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl)));
+  int sum = 0;
+  for (int l = 0; l < nl - 1; ++l) {
+    quota[l] = cv_round(perScale);
+    sum += quota[l];
+    perScale *= factor;
+  }
+  quota[nl - 1] = std::max(nf - sum, 0);
+  // umax: quarter-circle row half-widths, made symmetric (:866-910)
+  umax.assign(kHalfPatch + 1, 0);
+  const int vmax = (int)std::floor(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+  const int vmin = (int)std::ceil(kHalfPatch * std::sqrt(2.f) / 2);
+  const double hp2 = kHalfPatch * kHalfPatch;
+  for (int v = 0; v <= vmax; ++v) umax[v] = cv_round(std::sqrt(hp2 - v * v));
+  for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+    while (umax[v0] == umax[v0 + 1]) ++v0;
+    umax[v] = v0;
+    ++v0;
+  }
+  pyr.resize(nl); blurred.resize(nl); has_blur.assign(nl, 0); raw.resize(nl); levelCounts.assign(nl, 0);
+}
+
+// src/ORBextractor.cc:2093-2168. Default = this fork: level l is resized from the PADDED level l-1
+// and mvImagePyramid[l] is the padded image (line 2166). Upstream flag: ROI semantics.
+void Extractor::computePyramid(const Img& image) {
+  const bool upstream = flags & ORB_ORACLE_UPSTREAM_PYRAMID;
+  for (int l = 0; l < nlevels; ++l) {
+    const float s = invScale[l];
+    const int w = cv_round((float)image.cols * s), h = cv_round((float)image.rows * s);
+    pyr[l].alloc(w + 2 * kEdge, h + 2 * kEdge);
+    Img whole = pyr[l].view();
+    Img inner = whole.roi(kEdge, kEdge, w, h);
+    if (l == 0) {
+      copy_make_border_reflect101(image, whole, kEdge);
+    } else {
+      Img prev = pyr[l - 1].view();
+      if (upstream) prev = prev.roi(kEdge, kEdge, prev.cols - 2 * kEdge, prev.rows - 2 * kEdge);
+      resize_linear_u8(prev, inner);
+      copy_make_border_reflect101(inner, whole, kEdge);
+    }
+  }
+}
+
+// src/ORBextractor.cc:1424-1601
+void Extractor::computeKeyPoints(std::vector<std::vector<KeyPoint>>& all) {
+  all.assign(nlevels, {});
+  const bool upstream = flags & ORB_ORACLE_UPSTREAM_PYRAMID;
+  const float W = 30;
+  std::vector<KeyPoint> cellKps;
+  for (int level = 0; level < nlevels; ++level) {
+    // Image FAST runs on: the padded level (this fork, F1) or its interior ROI (upstream flag).
+    Img base = pyr[level].view();
+    int ox = 0, oy = 0, cols = base.cols, rows = base.rows;
+    if (upstream) { ox = oy = kEdge; cols -= 2 * kEdge; rows -= 2 * kEdge; }
+    const int minBX = kEdge - 3, minBY = minBX;
+    const int maxBX = cols - kEdge + 3, maxBY = rows - kEdge + 3;
+    std::vector<KeyPoint>& toDist = raw[level];
+    toDist.clear();
+    toDist.reserve((size_t)nfeatures * 10);
+    const float width = (float)(maxBX - minBX), height = (float)(maxBY - minBY);
+    const int nCols = (int)(width / W), nRows = (int)(height / W);
+    const int wCell = (int)std::ceil(width / nCols), hCell = (int)std::ceil(height / nRows);
+    for (int i = 0; i < nRows; ++i) {
+      const float iniY = (float)(minBY + i * hCell);
+      float maxY = iniY + hCell + 6;
+      if (iniY >= maxBY - 3) continue;
+      if (maxY > maxBY) maxY = (float)maxBY;
+      for (int j = 0; j < nCols; ++j) {
+        const float iniX = (float)(minBX + j * wCell);
+        float maxX = iniX + wCell + 6;
+        if (iniX >= maxBX - 6) continue;
+        if (maxX > maxBX) maxX = (float)maxBX;
+        const Img cell = base.roi(ox + (int)iniX, oy + (int)iniY, (int)maxX - (int)iniX, (int)maxY - (int)iniY);
+        fast_detect(cell, iniTh, true, cellKps);
+        if (cellKps.empty()) fast_detect(cell, minTh, true, cellKps);
+        for (KeyPoint& k : cellKps) {
+          k.x += j * wCell;
+          k.y += i * hCell;
+          toDist.push_back(k);
+        }
+      }
+    }
+    std::vector<KeyPoint>& kps = all[level];
+    kps = distribute(toDist, minBX, maxBX, minBY, maxBY, quota[level], nfeatures);
+    const int scaledPatch = (int)(kPatch * scale[level]);
+    for (KeyPoint& k : kps) {
+      k.x += minBX;
+      k.y += minBY;
+      k.octave = level;
+      k.size = (float)scaledPatch;
+    }
+  }
+  // orientation, src/ORBextractor.cc:104-161 + 933-952, on the un-blurred level
+  for (int level = 0; level < nlevels; ++level) {
+    Img base = pyr[level].view();
+    const int off = upstream ? kEdge : 0;
+    for (KeyPoint& k : all[level]) {
+      const uint8_t* center = base.ptr(cv_round(k.y) + off) + cv_round(k.x) + off;
+      const int step = base.step;
+      int m01 = 0, m10 = 0;
+      for (int u = -kHalfPatch; u <= kHalfPatch; ++u) m10 += u * center[u];
+      for (int v = 1; v <= kHalfPatch; ++v) {
+        int vsum = 0;
+        const int d = umax[v];
+        for (int u = -d; u <= d; ++u) {
+          const int p = center[u + v * step], m = center[u - v * step];
+          vsum += p - m;
+          m10 += u * (p + m);
+        }
+        m01 += v * vsum;
+      }
+      k.angle = fast_atan2((float)m01, (float)m10);
+    }
+  }
+}
+
+// ---- DistributeOctTree, src/ORBextractor.cc:1050-1417 (+ DivideNode :963-1035) -------------------
+// Node list = std::list with push_front / erase like the reference; keys held as indices into `in`
+// (in-node order preserved: it decides the "first max response" winner, :1394-1409).
+struct Node {
+  int ulx, uly, brx, bry;  // UL.x, UL.y, BR.x, BR.y (UR = (brx, uly), BL = (ulx, bry))
+  std::vector<int> keys;
+  bool noMore = false;
+  std::list<Node>::iterator self;
+};
+
+static void divide(const Node& n, const std::vector<KeyPoint>& in, Node out[4]) {
+  const int halfX = (int)std::ceil((float)(n.brx - n.ulx) / 2);
+  const int halfY = (int)std::ceil((float)(n.bry - n.uly) / 2);
+  const int mx = n.ulx + halfX, my = n.uly + halfY;
+  out[0].ulx = n.ulx; out[0].uly = n.uly; out[0].brx = mx;    out[0].bry = my;
+  out[1].ulx = mx;    out[1].uly = n.uly; out[1].brx = n.brx; out[1].bry = my;
+  out[2].ulx = n.ulx; out[2].uly = my;    out[2].brx = mx;    out[2].bry = n.bry;
+  out[3].ulx = mx;    out[3].uly = my;    out[3].brx = n.brx; out[3].bry = n.bry;
+  for (int c = 0; c < 4; ++c) { out[c].keys.clear(); out[c].keys.reserve(n.keys.size()); out[c].noMore = false; }
+  for (int idx : n.keys) {
+    const KeyPoint& kp = in[idx];
+    const int c = (kp.x < (float)mx ? 0 : 1) + (kp.y < (float)my ? 0 : 2);
+    out[c].keys.push_back(idx);
+  }
+  for (int c = 0; c < 4; ++c)
+    if (out[c].keys.size() == 1) out[c].noMore = true;
+}
+
+std::vector<KeyPoint> distribute(const std::vector<KeyPoint>& in, int minX, int maxX, int minY, int maxY, int N,
+                                 int reserveHint) {
+  std::vector<KeyPoint> result;
+  const int nIni = (int)std::round((float)(maxX - minX) / (maxY - minY));
+  if (nIni <= 0) return result;  // the reference divides by zero here (portrait aspect < 0.5); rejected upstream
+  const float hX = (float)(maxX - minX) / nIni;
+  std::list<Node> nodes;
+  std::vector<Node*> ini(nIni);
+  for (int i = 0; i < nIni; ++i) {
+    Node n;
+    n.ulx = (int)(hX * (float)i); n.uly = 0;
+    n.brx = (int)(hX * (float)(i + 1)); n.bry = maxY - minY;
+    nodes.push_back(n);
+    ini[i] = &nodes.back();
+  }
+  for (size_t i = 0; i < in.size(); ++i) {
+    const int slot = (int)(in[i].x / hX);
+    if (slot >= 0 && slot < nIni) ini[slot]->keys.push_back((int)i);  // always true for in-domain FAST points
+  }
+  for (auto it = nodes.begin(); it != nodes.end();) {
+    if (it->keys.size() == 1) { it->noMore = true; ++it; }
+    else if (it->keys.empty()) it = nodes.erase(it);
+    else ++it;
+  }
+  // (size, seq, node): seq = creation order -> canonical replacement of the pointer tie-break (F2)
+  struct Cand { int size; int seq; Node* node; };
+  std::vector<Cand> cands;
+  int seq = 0;
+  Node kids[4];
+  auto push_children = [&](bool countExpand, int& nToExpand) {
+    for (int c = 0; c < 4; ++c) {
+      if (kids[c].keys.empty()) continue;
+      nodes.push_front(kids[c]);
+      if (kids[c].keys.size() > 1) {
+        if (countExpand) ++nToExpand;
+        cands.push_back(Cand{(int)kids[c].keys.size(), seq++, &nodes.front()});
+        nodes.front().self = nodes.begin();
+      }
+    }
+  };
+  bool finish = false;
+  while (!finish) {
+    int prevSize = (int)nodes.size();
+    int nToExpand = 0;
+    cands.clear();
+    for (auto it = nodes.begin(); it != nodes.end();) {
+      if (it->noMore) { ++it; continue; }
+      divide(*it, in, kids);
+      push_children(true, nToExpand);
+      it = nodes.erase(it);
+    }
+    if ((int)nodes.size() >= N || (int)nodes.size() == prevSize) {
+      finish = true;
+    } else if ((int)nodes.size() + nToExpand * 3 > N) {
+      while (!finish) {
+        prevSize = (int)nodes.size();
+        std::vector<Cand> prev = cands;
+        cands.clear();
+        std::sort(prev.begin(), prev.end(), [](const Cand& a, const Cand& b) {
+          return a.size != b.size ? a.size < b.size : a.seq < b.seq;
+        });
+        for (int j = (int)prev.size() - 1; j >= 0; --j) {
+          divide(*prev[j].node, in, kids);
+          int dummy = 0;
+          push_children(false, dummy);
+          nodes.erase(prev[j].node->self);
+          if ((int)nodes.size() >= N) break;
+        }
+        if ((int)nodes.size() >= N || (int)nodes.size() == prevSize) finish = true;
+      }
+    }
+  }
+  result.reserve(reserveHint);
+  for (const Node& n : nodes) {
+    int best = n.keys[0];
+    float maxResp = in[best].response;
+    for (size_t k = 1; k < n.keys.size(); ++k)
+      if (in[n.keys[k]].response > maxResp) { best = n.keys[k]; maxResp = in[best].response; }
+    result.push_back(in[best]);
+  }
+  return result;
+}
+
+// src/ORBextractor.cc:1961-2084 (+ computeOrbDescriptor :177-254)
+int Extractor::run(const Img& image, std::vector<KeyPoint>& out, std::vector<uint8_t>& desc) {
+  computePyramid(image);
+  std::vector<std::vector<KeyPoint>> all;
+  computeKeyPoints(all);
+  int total = 0;
+  for (int l = 0; l < nlevels; ++l) { levelCounts[l] = (int)all[l].size(); total += levelCounts[l]; }
+  out.clear(); out.reserve(total);
+  desc.assign((size_t)total * 32, 0);
+  const bool upstream = flags & ORB_ORACLE_UPSTREAM_PYRAMID;
+  const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+  int offset = 0;
+  for (int l = 0; l < nlevels; ++l) {
+    has_blur[l] = 0;
+    std::vector<KeyPoint>& kps = all[l];
+    if (kps.empty()) continue;
+    // workingMat = clone of mvImagePyramid[l]; blur reflects at ITS border (padded image in this fork)
+    Img srcv = pyr[l].view();
+    if (upstream) srcv = srcv.roi(kEdge, kEdge, srcv.cols - 2 * kEdge, srcv.rows - 2 * kEdge);
+    blurred[l].alloc(srcv.cols, srcv.rows);
+    Img bl = blurred[l].view();
+    gaussian_blur_7x7_s2(srcv, bl, flags & ORB_ORACLE_LEGACY_BLUR);
+    has_blur[l] = 1;
+    for (size_t i = 0; i < kps.size(); ++i) {
+      const KeyPoint& k = kps[i];
+      const float angle = k.angle * factorPI;
+      float a, b;
+      if (flags & ORB_ORACLE_LIBM_TRIG) { a = cosf(angle); b = sinf(angle); }
+      else sincos_canonical(angle, &b, &a);
+      const uint8_t* center = bl.ptr(cv_round(k.y)) + cv_round(k.x);
+      const int step = bl.step;
+      uint8_t* d = &desc[(size_t)(offset + i) * 32];
+      for (int byte = 0; byte < 32; ++byte) {
+        int val = 0;
+        for (int bit = 0; bit < 8; ++bit) {
+          const int8_t* p = &kPattern[(byte * 8 + bit) * 4];
+          const float x0 = (float)p[0], y0 = (float)p[1], x1 = (float)p[2], y1 = (float)p[3];
+          const int t0 = center[cv_round(x0 * b + y0 * a) * step + cv_round(x0 * a - y0 * b)];
+          const int t1 = center[cv_round(x1 * b + y1 * a) * step + cv_round(x1 * a - y1 * b)];
+          val |= (t0 < t1) << bit;
+        }
+        d[byte] = (uint8_t)val;
+      }
+    }
+    offset += (int)kps.size();
+    if (l != 0) {
+      const float s = scale[l];
+      for (KeyPoint& k : kps) { k.x *= s; k.y *= s; }
+    }
+    out.insert(out.end(), kps.begin(), kps.end());
+  }
+  return total;
+}
+
+}  // namespace orb_oracle
+
+// ---------------------------------------------------------------------------------------------
+// C API
+// ---------------------------------------------------------------------------------------------
+using namespace orb_oracle;
+
+struct orb_oracle_extractor {
+  Extractor ex;
+  std::vector<KeyPoint> kps;
+  std::vector<uint8_t> desc;
+  orb_oracle_extractor(int nf, float sf, int nl, int ini, int mn, int fl) : ex(nf, sf, nl, ini, mn, fl) {}
+};
+
+static_assert(sizeof(orb_oracle_kp) == sizeof(KeyPoint), "kp layout");
+
+extern "C" {
+
+orb_oracle_extractor* orb_oracle_create(int nf, float sf, int nl, int ini, int mn, int flags) {
+  if (nf < 0 || nl < 1 || nl > 32 || !(sf > 1.f)) return nullptr;
+  return new orb_oracle_extractor(nf, sf, nl, ini, mn, flags);
+}
+void orb_oracle_destroy(orb_oracle_extractor* e) { delete e; }
+
+void orb_oracle_get_table(const orb_oracle_extractor* e, int what, float* out) {
+  const std::vector<float>& t = what == 0 ? e->ex.scale : what == 1 ? e->ex.invScale : what == 2 ? e->ex.sigma2 : e->ex.invSigma2;
+  std::copy(t.begin(), t.end(), out);
+}
+void orb_oracle_get_quota(const orb_oracle_extractor* e, int32_t* out) { std::copy(e->ex.quota.begin(), e->ex.quota.end(), out); }
+void orb_oracle_get_umax(const orb_oracle_extractor* e, int32_t* out) { std::copy(e->ex.umax.begin(), e->ex.umax.end(), out); }
+
+int orb_oracle_extract(orb_oracle_extractor* e, const uint8_t* img, int step, int width, int height, orb_oracle_kp* kps,
+                       uint8_t* desc, int cap, int32_t* level_counts) {
+  if (!e || !img || width <= 0 || height <= 0) return -1;
+  Img im{const_cast<uint8_t*>(img), width, height, step};
+  const int n = e->ex.run(im, e->kps, e->desc);
+  if (level_counts) std::copy(e->ex.levelCounts.begin(), e->ex.levelCounts.end(), level_counts);
+  if (n > cap) return -1;
+  if (kps && n) std::memcpy(kps, e->kps.data(), (size_t)n * sizeof(KeyPoint));
+  if (desc && n) std::memcpy(desc, e->desc.data(), (size_t)n * 32);
+  return n;
+}
+
+int orb_oracle_level_dims(const orb_oracle_extractor* e, int l, int* cols, int* rows) {
+  if (l < 0 || l >= e->ex.nlevels) return -1;
+  *cols = e->ex.pyr[l].cols; *rows = e->ex.pyr[l].rows;
+  return 0;
+}
+const uint8_t* orb_oracle_level_ptr(const orb_oracle_extractor* e, int l) { return e->ex.pyr[l].buf.data(); }
+const uint8_t* orb_oracle_blurred_ptr(const orb_oracle_extractor* e, int l) {
+  return e->ex.has_blur[l] ? e->ex.blurred[l].buf.data() : nullptr;
+}
+int orb_oracle_raw_count(const orb_oracle_extractor* e, int l) { return (int)e->ex.raw[l].size(); }
+int orb_oracle_raw_keypoints(const orb_oracle_extractor* e, int l, orb_oracle_kp* out, int cap) {
+  const int n = (int)e->ex.raw[l].size();
+  if (n > cap) return -1;
+  if (n) std::memcpy(out, e->ex.raw[l].data(), (size_t)n * sizeof(KeyPoint));
+  return n;
+}
+
+void orb_oracle_resize(const uint8_t* src, int sstep, int sw, int sh, uint8_t* dst, int dstep, int dw, int dh) {
+  resize_linear_u8(Img{const_cast<uint8_t*>(src), sw, sh, sstep}, Img{dst, dw, dh, dstep});
+}
+void orb_oracle_border101(const uint8_t* src, int sstep, int sw, int sh, uint8_t* dst, int dstep, int b) {
+  copy_make_border_reflect101(Img{const_cast<uint8_t*>(src), sw, sh, sstep}, Img{dst, sw + 2 * b, sh + 2 * b, dstep}, b);
+}
+void orb_oracle_blur(const uint8_t* src, int sstep, int w, int h, uint8_t* dst, int dstep, int legacy) {
+  gaussian_blur_7x7_s2(Img{const_cast<uint8_t*>(src), w, h, sstep}, Img{dst, w, h, dstep}, legacy != 0);
+}
+int orb_oracle_fast(const uint8_t* img, int step, int w, int h, int threshold, orb_oracle_kp* out, int cap) {
+  std::vector<KeyPoint> k;
+  fast_detect(Img{const_cast<uint8_t*>(img), w, h, step}, threshold, true, k);
+  if ((int)k.size() > cap) return -1;
+  if (!k.empty()) std::memcpy(out, k.data(), k.size() * sizeof(KeyPoint));
+  return (int)k.size();
+}
+void orb_oracle_fast_score_map(const uint8_t* img, int step, int w, int h, uint8_t* out) {
+  std::memset(out, 0, (size_t)w * h);
+  for (int y = 3; y < h - 3; ++y)
+    for (int x = 3; x < w - 3; ++x) out[(size_t)y * w + x] = (uint8_t)fast_corner_score(img + (size_t)y * step + x, step);
+}
+float orb_oracle_fast_atan2(float y, float x) { return fast_atan2(y, x); }
+void orb_oracle_sincos(float a, int libm, float* s, float* c) {
+  if (libm) { *s = sinf(a); *c = cosf(a); }
+  else sincos_canonical(a, s, c);
+}
+int orb_oracle_distribute(const orb_oracle_kp* in, int n, int minx, int maxx, int miny, int maxy, int nfeat,
+                          orb_oracle_kp* out, int cap) {
+  std::vector<KeyPoint> v(n);
+  if (n) std::memcpy(v.data(), in, (size_t)n * sizeof(KeyPoint));
+  std::vector<KeyPoint> r = distribute(v, minx, maxx, miny, maxy, nfeat, nfeat);
+  if ((int)r.size() > cap) return -1;
+  if (!r.empty()) std::memcpy(out, r.data(), r.size() * sizeof(KeyPoint));
+  return (int)r.size();
+}
+
+// src/ORBmatcher.cc:2073-2093: 8 x 32-bit words, SWAR popcount.
+int orb_oracle_descriptor_distance(const uint8_t* a, const uint8_t* b) {
+  int dist = 0;
+  for (int i = 0; i < 8; ++i) {
+    uint32_t x, y;
+    std::memcpy(&x, a + 4 * i, 4);
+    std::memcpy(&y, b + 4 * i, 4);
+    uint32_t v = x ^ y;
+    v = v - ((v >> 1) & 0x55555555u);
+    v = (v & 0x33333333u) + ((v >> 2) & 0x33333333u);
+    dist += (int)((((v + (v >> 4)) & 0xF0F0F0Fu) * 0x1010101u) >> 24);
+  }
+  return dist;
+}
+
+void orb_oracle_hamming_knn(const uint8_t* q, int Q, const uint8_t* db, int64_t D, int64_t base, int sentinel,
+                            orb_oracle_knn2* out, int nthreads) {
+  auto work = [&](int lo, int hi) {
+    for (int qi = lo; qi < hi; ++qi) {
+      int best = sentinel, second = sentinel;
+      int64_t i1 = -1, i2 = -1;
+      const uint8_t* qd = q + (size_t)qi * 32;
+      for (int64_t j = 0; j < D; ++j) {
+        const int d = orb_oracle_descriptor_distance(qd, db + (size_t)j * 32);
+        if (d < best) { second = best; i2 = i1; best = d; i1 = base + j; }
+        else if (d < second) { second = d; i2 = base + j; }
+      }
+      out[qi] = orb_oracle_knn2{best, second, i1, i2};
+    }
+  };
+  nthreads = std::max(1, std::min(nthreads, Q));
+  if (nthreads == 1) { work(0, Q); return; }
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; ++t) th.emplace_back(work, (int)((int64_t)Q * t / nthreads), (int)((int64_t)Q * (t + 1) / nthreads));
+  for (auto& t : th) t.join();
+}
+
+int64_t orb_oracle_extract_many(int nf, float sf, int nl, int ini, int mn, int flags, const uint8_t* frames, int width,
+                                int height, int n, int nthreads) {
+  nthreads = std::max(1, std::min(nthreads, n));
+  std::vector<int64_t> totals(nthreads, 0);
+  auto work = [&](int t) {
+    Extractor ex(nf, sf, nl, ini, mn, flags);
+    std::vector<KeyPoint> k;
+    std::vector<uint8_t> d;
+    for (int f = t; f < n; f += nthreads) {
+      Img im{const_cast<uint8_t*>(frames) + (size_t)f * width * height, width, height, width};
+      totals[t] += ex.run(im, k, d);
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+  for (auto& t : th) t.join();
+  int64_t s = 0;
+  for (int64_t v : totals) s += v;
+  return s;
+}
+
+}  // extern "C"

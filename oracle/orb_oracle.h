@@ -1,0 +1,97 @@
+/* TEST INFRASTRUCTURE ONLY — CPU oracle for the ORB front-end hot path.
+ *
+ * A CPU restatement of /root/reference src/ORBextractor.cc (ORBextractor ctor :776-925,
+ * operator() :1961-2084, ComputePyramid :2093-2168, ComputeKeyPointsOctTree :1424-1601,
+ * DistributeOctTree :1050-1417, DivideNode :963-1035, IC_Angle :104-161,
+ * computeOrbDescriptor :177-254) and src/ORBmatcher.cc (DescriptorDistance :2073-2093 and the
+ * best/second-best idiom :304-342), on top of the OpenCV primitives restated in cv_primitives.*.
+ *
+ * The reference itself cannot be compiled in the build container (needs OpenCV C++ headers;
+ * include/ORBextractor.h:26) and ships no tests or golden vectors, so parity is pinned by
+ * (1) the primitives checked bit-exact against the real OpenCV (cv2 4.13) and (2) a whole-pipeline
+ * composition of real cv2 calls (tests/golden/make_golden.py) whose outputs are committed under
+ * tests/golden/ and compared with this oracle.
+ *
+ * Two documented canonicalisations (DESIGN.md "Determinism contract"):
+ *  - quadtree "biggest first" tie-break: (size, creation sequence) instead of (size, heap pointer),
+ *    src/ORBextractor.cc:1295-1308;
+ *  - cos/sin of the keypoint angle: a fixed double-precision polynomial rounded once to float
+ *    instead of the platform libm cosf/sinf (src/ORBextractor.cc:184-186); flag
+ *    ORB_ORACLE_LIBM_TRIG selects libm for a bit-agreement diagnostic.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may use
+ * this library. The product (orb_slam2_detailed_comments_b200/) never links or loads it.
+ */
+#ifndef ORB_ORACLE_H_
+#define ORB_ORACLE_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  ORB_ORACLE_UPSTREAM_PYRAMID = 1, /* raulmur/ORB_SLAM2 behaviour: mvImagePyramid = unpadded ROI (not this fork) */
+  ORB_ORACLE_LEGACY_BLUR = 2,      /* OpenCV <= 3.4.0 taps [18,34,49,55,49,34,18] */
+  ORB_ORACLE_LIBM_TRIG = 4         /* glibc cosf/sinf instead of the canonical polynomial */
+};
+
+typedef struct orb_oracle_kp { /* == cv::KeyPoint, 28 bytes */
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} orb_oracle_kp;
+
+typedef struct orb_oracle_extractor orb_oracle_extractor;
+
+orb_oracle_extractor* orb_oracle_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast,
+                                        int min_th_fast, int flags);
+void orb_oracle_destroy(orb_oracle_extractor* e);
+
+/* Table accessors (what = 0 mvScaleFactor, 1 mvInvScaleFactor, 2 mvLevelSigma2, 3 mvInvLevelSigma2). */
+void orb_oracle_get_table(const orb_oracle_extractor* e, int what, float* out);
+void orb_oracle_get_quota(const orb_oracle_extractor* e, int32_t* out); /* mnFeaturesPerLevel */
+void orb_oracle_get_umax(const orb_oracle_extractor* e, int32_t* out);  /* 16 ints */
+
+/* operator(): returns N (>=0) or -1 if cap is too small / bad args. level_counts may be NULL. */
+int orb_oracle_extract(orb_oracle_extractor* e, const uint8_t* img, int step, int width, int height,
+                       orb_oracle_kp* kps, uint8_t* desc, int cap, int32_t* level_counts);
+
+/* Stage dumps of the last orb_oracle_extract call. */
+int orb_oracle_level_dims(const orb_oracle_extractor* e, int level, int* cols, int* rows);
+const uint8_t* orb_oracle_level_ptr(const orb_oracle_extractor* e, int level);   /* mvImagePyramid[level], step = cols */
+const uint8_t* orb_oracle_blurred_ptr(const orb_oracle_extractor* e, int level); /* NULL if the level had no keypoints */
+int orb_oracle_raw_count(const orb_oracle_extractor* e, int level);
+int orb_oracle_raw_keypoints(const orb_oracle_extractor* e, int level, orb_oracle_kp* out, int cap); /* vToDistributeKeys */
+
+/* Primitives (for tests vs cv2). */
+void orb_oracle_resize(const uint8_t* src, int sstep, int sw, int sh, uint8_t* dst, int dstep, int dw, int dh);
+void orb_oracle_border101(const uint8_t* src, int sstep, int sw, int sh, uint8_t* dst, int dstep, int b);
+void orb_oracle_blur(const uint8_t* src, int sstep, int w, int h, uint8_t* dst, int dstep, int legacy);
+int orb_oracle_fast(const uint8_t* img, int step, int w, int h, int threshold, orb_oracle_kp* out, int cap);
+void orb_oracle_fast_score_map(const uint8_t* img, int step, int w, int h, uint8_t* out /* w*h */);
+float orb_oracle_fast_atan2(float y, float x);
+void orb_oracle_sincos(float angle_rad, int libm, float* s, float* c);
+int orb_oracle_distribute(const orb_oracle_kp* in, int n, int minx, int maxx, int miny, int maxy, int nfeat,
+                          orb_oracle_kp* out, int cap);
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2073-2093). */
+int orb_oracle_descriptor_distance(const uint8_t* a, const uint8_t* b);
+/* Brute-force k=2 with the reference's strict-< update rule (src/ORBmatcher.cc:304-335); sentinel
+ * is the initial best/second (256 normally, INT_MAX at :611-612). Index base added to i1/i2.
+ * out: per query {int32 d1, int32 d2, int64 i1, int64 i2}; i = -1 where unset. nthreads over queries. */
+typedef struct orb_oracle_knn2 {
+  int32_t d1, d2;
+  int64_t i1, i2;
+} orb_oracle_knn2;
+void orb_oracle_hamming_knn(const uint8_t* q, int Q, const uint8_t* db, int64_t D, int64_t index_base,
+                            int sentinel, orb_oracle_knn2* out, int nthreads);
+
+/* Multi-threaded extraction over frames, one extractor per thread (bench cpu baseline).
+ * Returns total keypoints. frames: n contiguous w*h images. */
+int64_t orb_oracle_extract_many(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int flags,
+                                const uint8_t* frames, int width, int height, int n, int nthreads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,84 @@
+"""Deterministic synthetic frames and descriptor sets.
+
+The reference ships no data (its examples read TUM/KITTI/EuRoC from disk, Examples/Monocular/mono_tum.cc:70),
+so every test and benchmark uses these seeded generators at the dataset shapes.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+CONFIGS = {
+    # name: (width, height, nFeatures)  -- 8 levels, scale 1.2, FAST 20/7 everywhere
+    "tum": (640, 480, 1000),       # Examples/Monocular/TUM1.yaml:30-43
+    "kitti": (1241, 376, 2000),    # Examples/Stereo/KITTI00-02.yaml:38-51
+    "euroc": (752, 480, 1200),     # Examples/Stereo/EuRoC.yaml:93-106
+    "4k": (3840, 2160, 8000),
+}
+
+
+def synth_frame(width: int, height: int, seed: int) -> np.ndarray:
+    """One u8 frame: smooth background + W*H/1500 filled rotated rectangles, soft-blurred, + noise."""
+    rng = np.random.RandomState(seed)
+    yy, xx = np.mgrid[0:height, 0:width].astype(np.float32)
+    img = 96.0 + 48.0 * np.sin(xx / 97.0) + 32.0 * np.cos(yy / 61.0)
+    nrect = (width * height) // 1500
+    cx = rng.uniform(0, width, nrect)
+    cy = rng.uniform(0, height, nrect)
+    sw = rng.uniform(6, 80, nrect)
+    sh = rng.uniform(6, 80, nrect)
+    ang = np.deg2rad(rng.uniform(0, 180, nrect))
+    grey = rng.randint(0, 256, nrect)
+    for i in range(nrect):
+        r = 0.5 * np.hypot(sw[i], sh[i]) + 1
+        x0, x1 = max(int(cx[i] - r), 0), min(int(cx[i] + r) + 1, width)
+        y0, y1 = max(int(cy[i] - r), 0), min(int(cy[i] + r) + 1, height)
+        if x0 >= x1 or y0 >= y1:
+            continue
+        dx = xx[y0:y1, x0:x1] - cx[i]
+        dy = yy[y0:y1, x0:x1] - cy[i]
+        c, s = np.cos(ang[i]), np.sin(ang[i])
+        u = dx * c + dy * s
+        v = -dx * s + dy * c
+        m = (np.abs(u) <= 0.5 * sw[i]) & (np.abs(v) <= 0.5 * sh[i])
+        img[y0:y1, x0:x1][m] = grey[i]
+    # separable Gaussian sigma 0.8 (radius 3), reflect border
+    t = np.arange(-3, 4, dtype=np.float32)
+    k = np.exp(-t * t / (2 * 0.8 * 0.8))
+    k /= k.sum()
+    p = np.pad(img, 3, mode="reflect")
+    tmp = sum(k[i] * p[:, i:i + width] for i in range(7))
+    img = sum(k[i] * tmp[i:i + height, :] for i in range(7))
+    img = img + rng.uniform(-3, 3, img.shape).astype(np.float32)
+    return np.clip(np.rint(img), 0, 255).astype(np.uint8)
+
+
+def synth_batch(width: int, height: int, n: int, seed0: int = 1234, distinct: int | None = None) -> np.ndarray:
+    """n frames (n, H, W) u8; seeds seed0+i. `distinct` < n generates that many and tiles them with a
+    per-copy circular shift so every frame still differs (used by large throughput batches)."""
+    d = n if distinct is None else min(distinct, n)
+    base = [synth_frame(width, height, seed0 + i) for i in range(d)]
+    out = np.empty((n, height, width), np.uint8)
+    for i in range(n):
+        f = base[i % d]
+        rep = i // d
+        out[i] = f if rep == 0 else np.roll(f, (7 * rep, 13 * rep), axis=(0, 1))
+    return out
+
+
+def synth_descriptors(n_query: int, n_db: int, seed: int = 7, planted_frac: float = 0.1):
+    """Random 256-bit descriptors; planted_frac of the queries are database rows with 0..40 bit flips
+    so the ratio test has accepts (config C4)."""
+    rng = np.random.RandomState(seed)
+    db = rng.randint(0, 256, (n_db, 32), dtype=np.uint8) if n_db else np.zeros((0, 32), np.uint8)
+    q = rng.randint(0, 256, (n_query, 32), dtype=np.uint8)
+    if n_db:
+        npl = int(n_query * planted_frac)
+        rows = rng.randint(0, n_db, npl)
+        for i in range(npl):
+            d = db[rows[i]].copy()
+            nflip = rng.randint(0, 41)
+            bits = rng.choice(256, nflip, replace=False)
+            for b in bits:
+                d[b >> 3] ^= np.uint8(1 << (b & 7))
+            q[i] = d
+    return q, db
