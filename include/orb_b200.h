@@ -1,0 +1,139 @@
+/* orb_b200.h — C ABI of the B200-native ORB front-end (liborb_b200.so).
+ *
+ * Drop-in boundary for the hot path of cheukwaylee/ORB_SLAM2_detailed_comments. Every entry point
+ * names the reference interface it replaces (paths relative to the reference root):
+ *
+ *   orb_extractor_create      <- ORBextractor::ORBextractor(int,float,int,int,int)   include/ORBextractor.h:104, src/ORBextractor.cc:776-925
+ *   orb_extractor_get_*       <- GetLevels/GetScaleFactor(s)/GetInverseScaleFactors/GetScaleSigmaSquares/
+ *                                GetInverseScaleSigmaSquares                          include/ORBextractor.h:134-182
+ *   orb_extract_batch         <- ORBextractor::operator()(image, mask, keypoints, descriptors)
+ *                                                                                     include/ORBextractor.h:122-126, src/ORBextractor.cc:1961-2084
+ *                                (batched: the stereo Frame ctor runs two of them concurrently, src/Frame.cc:158-168)
+ *   orb_extractor_pyramid_*   <- public member mvImagePyramid                         include/ORBextractor.h:185 (read by src/Frame.cc:910,1040)
+ *   orb_hamming_knn           <- ORBmatcher::DescriptorDistance in the best/second-best scan
+ *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
+ *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
+ *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
+ *
+ * Plain C: pointers and sizes only, no C++/torch types, no exceptions cross the boundary. All
+ * buffers are caller-owned. Functions are thread-safe per handle (one handle = one CUDA stream +
+ * private workspaces, like one ORBextractor instance, which is not re-entrant either).
+ * There is no CPU fallback: without a CUDA device every compute call returns ORB_E_CUDA.
+ */
+#ifndef ORB_B200_H_
+#define ORB_B200_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORB_B200_ABI_VERSION 1
+
+enum orb_status {
+  ORB_OK = 0,
+  ORB_E_BADARG = -1,   /* null pointer, non-positive size, unsupported parameter */
+  ORB_E_CAPACITY = -2, /* an internal or caller buffer was too small (raw keypoints / kps cap); outputs invalid */
+  ORB_E_CUDA = -3,     /* CUDA runtime error or no device; see orb_last_error() */
+  ORB_E_SHAPE = -4     /* image too small for the pyramid, or aspect < 0.5 (the reference divides by nIni == 0, src/ORBextractor.cc:1059-1063) */
+};
+
+enum orb_mem { ORB_MEM_HOST = 0, ORB_MEM_DEVICE = 1 };
+
+enum orb_flags {
+  ORB_FLAG_UPSTREAM_PYRAMID = 1, /* reserved: raulmur/ORB_SLAM2 ROI pyramid; NOT implemented on device (create fails) */
+  ORB_FLAG_LEGACY_BLUR = 2       /* OpenCV <= 3.4.0 Gaussian taps [18,34,49,55,49,34,18] instead of [18,34,48,56,48,34,18] */
+};
+
+typedef struct orb_params {
+  int32_t nfeatures;   /* ORBextractor.nFeatures  (src/Tracking.cc:160) */
+  float scale_factor;  /* ORBextractor.scaleFactor */
+  int32_t nlevels;     /* ORBextractor.nLevels    (1..16) */
+  int32_t ini_th_fast; /* ORBextractor.iniThFAST */
+  int32_t min_th_fast; /* ORBextractor.minThFAST */
+  int32_t flags;       /* orb_flags */
+} orb_params;
+
+/* Same memory layout as cv::KeyPoint (28 bytes): a std::vector<cv::KeyPoint> can be filled by memcpy. */
+typedef struct orb_keypoint {
+  float x, y;     /* pt, in level-0 padded coordinates of this fork (src/ORBextractor.cc:2066-2076) */
+  float size;     /* (int)(31 * mvScaleFactor[octave]) */
+  float angle;    /* IC_Angle, degrees [0,360) */
+  float response; /* FAST score */
+  int32_t octave;
+  int32_t class_id; /* -1 */
+} orb_keypoint;
+
+typedef struct orb_knn2 {
+  int32_t d1, d2; /* best / second-best Hamming distance; == sentinel where unset */
+  int64_t i1, i2; /* global database row of best / second best; -1 where unset */
+} orb_knn2;
+
+typedef struct orb_extractor orb_extractor;
+
+const char* orb_last_error(void); /* thread-local message of the last failing call */
+int orb_abi_version(void);
+int orb_device_count(void);
+
+/* ---- extractor ------------------------------------------------------------------------------- */
+int orb_extractor_create(const orb_params* p, int device, orb_extractor** out);
+void orb_extractor_destroy(orb_extractor* e);
+
+int orb_extractor_get_levels(const orb_extractor* e);
+float orb_extractor_get_scale_factor(const orb_extractor* e);
+/* what: 0 mvScaleFactor, 1 mvInvScaleFactor, 2 mvLevelSigma2, 3 mvInvLevelSigma2; out[nlevels] */
+int orb_extractor_get_table(const orb_extractor* e, int what, float* out);
+int orb_extractor_get_features_per_level(const orb_extractor* e, int32_t* out); /* mnFeaturesPerLevel */
+/* Upper bound on keypoints per image for buffer sizing: nfeatures + 3*nlevels (a split can overshoot the quota by 3). */
+int orb_extractor_max_keypoints(const orb_extractor* e);
+
+/* operator() over a batch of equally sized CV_8UC1 images.
+ *  images      : `batch` pointers (host array) to image rows; all host (ORB_MEM_HOST) or all device memory
+ *  step        : row pitch in bytes (same for all images)
+ *  kps, desc   : [batch][cap] orb_keypoint and [batch][cap][32] bytes, in `out_mem` memory; cap >= orb_extractor_max_keypoints
+ *  counts      : [batch] keypoints per image (always HOST memory); level_counts [batch][nlevels] optional (HOST)
+ * Order of keypoints == the reference's: levels ascending, quadtree list order within a level.
+ * Blocks until the results are complete (the reference call is synchronous too). */
+int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height,
+                      int batch, orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts,
+                      int32_t* level_counts);
+
+/* Device-resident fast path used by the benchmark: `images` is ONE device buffer [batch][height][step];
+ * outputs stay in device memory (kps/desc as above, counts_dev [batch] int32 device). Asynchronous on the
+ * extractor's stream unless `sync` != 0. */
+int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, int width, int height, int batch,
+                             orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts_dev, int sync);
+
+/* mvImagePyramid of image `index` of the last batch: padded level (cols x rows), copied to `dst` (host, pitch dst_step).
+ * blurred != 0 returns the Gaussian-blurred working copy instead (test hook). */
+int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int* rows);
+int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurred, uint8_t* dst, int dst_step);
+/* Test hook: vToDistributeKeys of (image index, level) of the last batch: x, y (cell-shifted, border-relative) and response. */
+int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keypoint* out, int cap);
+/* CUDA stream of the handle (cudaStream_t) for callers that enqueue dependent work, and the number of kernels
+ * launched by this handle so far. */
+void* orb_extractor_stream(orb_extractor* e);
+int64_t orb_extractor_launch_count(const orb_extractor* e);
+
+/* ---- matcher ------------------------------------------------------------------------------- */
+/* Brute-force k=2 over 256-bit descriptors with the reference update rule (strict <: earliest index wins,
+ * a duplicate of the minimum becomes `second`). sentinel = initial best/second (256; INT_MAX at src/ORBmatcher.cc:611).
+ * query [Q][32], db [D][32] in q_mem / db_mem memory; out [Q] in out_mem memory. index_base is added to i1/i2
+ * (database shard offset). stream: cudaStream_t or NULL (default stream); the call synchronises before returning
+ * when any buffer is host memory. */
+int orb_hamming_knn(const uint8_t* query, int q_mem, int Q, const uint8_t* db, int db_mem, int64_t D,
+                    int64_t index_base, int sentinel, orb_knn2* out, int out_mem, void* stream);
+/* Merge `nshards` per-shard results (shard-major [nshards][Q], device memory, shards in ascending index order)
+ * into out[Q] (device): equals one sequential scan over the concatenated database. */
+int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentinel, orb_knn2* out, void* stream);
+/* DescriptorDistance for n row pairs: out[i] = popcount(a[i] ^ b[i]); all device memory. */
+int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream);
+int64_t orb_matcher_launch_count(void);
+
+/* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
+double orb_measure_popc_peak(int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORB_B200_H_ */

@@ -1,0 +1,97 @@
+"""Loader for liborb_b200.so (the C ABI declared in include/orb_b200.h).
+
+There is no CPU fallback: if the shared library is missing or fails to load, import of the compute
+classes raises. The library is built in-tree by `__graft_entry__.build()` / csrc/Makefile.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "liborb_b200.so")
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+KNN_DTYPE = np.dtype([("d1", "<i4"), ("d2", "<i4"), ("i1", "<i8"), ("i2", "<i8")])
+assert KP_DTYPE.itemsize == 28 and KNN_DTYPE.itemsize == 24
+
+ORB_OK, ORB_E_BADARG, ORB_E_CAPACITY, ORB_E_CUDA, ORB_E_SHAPE = 0, -1, -2, -3, -4
+MEM_HOST, MEM_DEVICE = 0, 1
+FLAG_UPSTREAM_PYRAMID, FLAG_LEGACY_BLUR = 1, 2
+
+# every symbol include/orb_b200.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "orb_last_error", "orb_abi_version", "orb_device_count", "orb_extractor_create", "orb_extractor_destroy",
+    "orb_extractor_get_levels", "orb_extractor_get_scale_factor", "orb_extractor_get_table",
+    "orb_extractor_get_features_per_level", "orb_extractor_max_keypoints", "orb_extract_batch",
+    "orb_extract_batch_device", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
+    "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count", "orb_hamming_knn",
+    "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_matcher_launch_count", "orb_measure_popc_peak",
+]
+
+
+class OrbParams(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("flags", C.c_int32)]
+
+
+class OrbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"orb_b200 error {code}: {msg}")
+        self.code = code
+
+
+def build(verbose: bool = False) -> str:
+    """Compile csrc/*.cu for sm_100a into liborb_b200.so (nvcc cross-compiles without a GPU)."""
+    subprocess.check_call(["make", "-C", os.path.join(_PKG, "csrc"), "-j8"],
+                          stdout=None if verbose else subprocess.DEVNULL)
+    return LIB_PATH
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
+    L.orb_last_error.restype = C.c_char_p
+    L.orb_extractor_create.argtypes = [C.POINTER(OrbParams), i32, C.POINTER(vp)]
+    L.orb_extractor_destroy.argtypes = [vp]
+    L.orb_extractor_destroy.restype = None
+    L.orb_extractor_get_levels.argtypes = [vp]
+    L.orb_extractor_get_scale_factor.argtypes = [vp]
+    L.orb_extractor_get_scale_factor.restype = f32
+    L.orb_extractor_get_table.argtypes = [vp, i32, vp]
+    L.orb_extractor_get_features_per_level.argtypes = [vp, vp]
+    L.orb_extractor_max_keypoints.argtypes = [vp]
+    L.orb_extract_batch.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, i32, vp, vp]
+    L.orb_extract_batch_device.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp, i32]
+    L.orb_extractor_pyramid_dims.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
+    L.orb_extractor_pyramid_read.argtypes = [vp, i32, i32, i32, vp, i32]
+    L.orb_extractor_raw_keypoints.argtypes = [vp, i32, i32, vp, i32]
+    L.orb_extractor_stream.argtypes = [vp]
+    L.orb_extractor_stream.restype = vp
+    L.orb_extractor_launch_count.argtypes = [vp]
+    L.orb_extractor_launch_count.restype = i64
+    L.orb_hamming_knn.argtypes = [vp, i32, i32, vp, i32, i64, i64, i32, vp, i32, vp]
+    L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
+    L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
+    L.orb_matcher_launch_count.restype = i64
+    L.orb_measure_popc_peak.argtypes = [i32]
+    L.orb_measure_popc_peak.restype = C.c_double
+    _LIB = L
+    return L
+
+
+def check(rc: int) -> int:
+    if rc < 0:
+        raise OrbError(rc, lib().orb_last_error().decode("utf-8", "replace"))
+    return rc

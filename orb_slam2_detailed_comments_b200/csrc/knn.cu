@@ -1,0 +1,206 @@
+// Brute-force 256-bit Hamming k=2: ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2073-2093) inside the
+// best/second-best scan of src/ORBmatcher.cc:304-335.
+//
+// The reference's sequential rule (strict <, earliest index wins, a duplicate of the minimum becomes `second`)
+// returns exactly the two lexicographically smallest (distance, index) pairs with distance < sentinel, so the
+// scan is order-independent: every thread keeps the two smallest packed keys (d << 22 | local row) of its own
+// queries with three integer min/max per pair, database chunks are scanned by different CTAs, and a merge takes
+// the two smallest of all partial keys. INT pipe (popc) bound; the database streams through shared memory as
+// uint4 pairs read by broadcast, queries live in registers.
+#include <cuda_pipeline.h>
+
+#include "orb_common.cuh"
+
+#define KNN_THREADS 128
+#define KNN_QPT 2
+#define KNN_TILE 256   // database rows per smem stage (8 KB)
+
+struct OrbKnn2 {   // == orb_knn2
+  int d1, d2;
+  long long i1, i2;
+};
+
+__device__ __forceinline__ unsigned knn_dist(const uint4& qa, const uint4& qb, const uint4& a, const uint4& b) {
+  return __popc(qa.x ^ a.x) + __popc(qa.y ^ a.y) + __popc(qa.z ^ a.z) + __popc(qa.w ^ a.w) + __popc(qb.x ^ b.x) +
+         __popc(qb.y ^ b.y) + __popc(qb.z ^ b.z) + __popc(qb.w ^ b.w);
+}
+
+__global__ void __launch_bounds__(KNN_THREADS)
+orb_knn_kernel(const uint4* __restrict__ query, int Q, const uint4* __restrict__ db, long long D, long long rows_per_chunk,
+               long long index_base, unsigned long long* __restrict__ partial /*[nchunks][Q][2]*/) {
+  __shared__ uint4 s_db[2][KNN_TILE * 2];
+  const int tid = threadIdx.x;
+  uint4 qa[KNN_QPT], qb[KNN_QPT];
+  unsigned k1[KNN_QPT], k2[KNN_QPT];
+#pragma unroll
+  for (int i = 0; i < KNN_QPT; ++i) {
+    const int qi = blockIdx.x * (KNN_THREADS * KNN_QPT) + i * KNN_THREADS + tid;
+    qa[i] = qi < Q ? query[2 * qi] : make_uint4(0, 0, 0, 0);
+    qb[i] = qi < Q ? query[2 * qi + 1] : make_uint4(0, 0, 0, 0);
+    k1[i] = 0xffffffffu;
+    k2[i] = 0xffffffffu;
+  }
+  const long long c0 = (long long)blockIdx.y * rows_per_chunk;
+  const long long c1 = min(c0 + rows_per_chunk, D);
+  const int ntiles = c1 > c0 ? (int)((c1 - c0 + KNN_TILE - 1) / KNN_TILE) : 0;
+  auto stage = [&](int t, int buf) {
+    const long long r0 = c0 + (long long)t * KNN_TILE;
+    const int rows = (int)min((long long)KNN_TILE, c1 - r0);
+    const uint4* src = db + 2 * r0;
+    for (int i = tid; i < rows * 2; i += KNN_THREADS) __pipeline_memcpy_async(&s_db[buf][i], src + i, 16);
+    __pipeline_commit();
+  };
+  if (ntiles > 0) stage(0, 0);
+  for (int t = 0; t < ntiles; ++t) {
+    const int buf = t & 1;
+    if (t + 1 < ntiles) { stage(t + 1, buf ^ 1); __pipeline_wait_prior(1); }
+    else __pipeline_wait_prior(0);
+    __syncthreads();
+    const int rows = (int)min((long long)KNN_TILE, c1 - (c0 + (long long)t * KNN_TILE));
+    const unsigned jbase = (unsigned)(t * KNN_TILE);
+#pragma unroll 4
+    for (int r = 0; r < rows; ++r) {
+      const uint4 a = s_db[buf][2 * r], b = s_db[buf][2 * r + 1];
+#pragma unroll
+      for (int i = 0; i < KNN_QPT; ++i) {
+        const unsigned key = (knn_dist(qa[i], qb[i], a, b) << 22) | (jbase + r);
+        k2[i] = min(k2[i], max(k1[i], key));
+        k1[i] = min(k1[i], key);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < KNN_QPT; ++i) {
+    const int qi = blockIdx.x * (KNN_THREADS * KNN_QPT) + i * KNN_THREADS + tid;
+    if (qi < Q) {
+      unsigned long long* out = partial + ((long long)blockIdx.y * Q + qi) * 2;
+      out[0] = k1[i] == 0xffffffffu ? ~0ull : (((unsigned long long)(k1[i] >> 22) << 40) | (unsigned long long)(index_base + c0 + (k1[i] & 0x3fffffu)));
+      out[1] = k2[i] == 0xffffffffu ? ~0ull : (((unsigned long long)(k2[i] >> 22) << 40) | (unsigned long long)(index_base + c0 + (k2[i] & 0x3fffffu)));
+    }
+  }
+}
+
+__device__ __forceinline__ void knn_emit(unsigned long long a, unsigned long long b, int sentinel, OrbKnn2* o) {
+  OrbKnn2 r;
+  const long long da = a == ~0ull ? (long long)sentinel : (long long)(a >> 40);
+  const long long dbb = b == ~0ull ? (long long)sentinel : (long long)(b >> 40);
+  // a distance that is not < sentinel is never recorded by the reference loop
+  if (da < sentinel) { r.d1 = (int)da; r.i1 = (long long)(a & 0xffffffffffull); } else { r.d1 = sentinel; r.i1 = -1; }
+  if (da < sentinel && dbb < sentinel) { r.d2 = (int)dbb; r.i2 = (long long)(b & 0xffffffffffull); } else { r.d2 = sentinel; r.i2 = -1; }
+  *o = r;
+}
+
+__global__ void orb_knn_merge_partial_kernel(const unsigned long long* __restrict__ partial, int nchunks, int Q, int sentinel,
+                                             OrbKnn2* __restrict__ out) {
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= Q) return;
+  unsigned long long a = ~0ull, b = ~0ull;
+  for (int c = 0; c < nchunks; ++c) {
+    const unsigned long long* p = partial + ((long long)c * Q + qi) * 2;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const unsigned long long k = p[j];
+      b = min(b, max(a, k));
+      a = min(a, k);
+    }
+  }
+  knn_emit(a, b, sentinel, out + qi);
+}
+
+// Merge per-shard orb_knn2 results (e.g. all-gathered over NCCL): two lexicographically smallest (d, i).
+__global__ void orb_knn_merge_shards_kernel(const OrbKnn2* __restrict__ shards, int nshards, int Q, int sentinel,
+                                            OrbKnn2* __restrict__ out) {
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= Q) return;
+  unsigned long long a = ~0ull, b = ~0ull;
+  for (int s = 0; s < nshards; ++s) {
+    const OrbKnn2 e = shards[(long long)s * Q + qi];
+    const unsigned long long ka = (e.i1 < 0 || e.d1 >= sentinel) ? ~0ull : (((unsigned long long)e.d1 << 40) | (unsigned long long)e.i1);
+    const unsigned long long kb = (e.i2 < 0 || e.d2 >= sentinel) ? ~0ull : (((unsigned long long)e.d2 << 40) | (unsigned long long)e.i2);
+    b = min(b, max(a, ka)); a = min(a, ka);
+    b = min(b, max(a, kb)); a = min(a, kb);
+  }
+  knn_emit(a, b, sentinel, out + qi);
+}
+
+__global__ void orb_distance_batch_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, long long n, int* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = (int)knn_dist(a[2 * i], a[2 * i + 1], b[2 * i], b[2 * i + 1]);
+}
+
+// Register-resident xor+popc+add loop: 8 independent chains per thread.
+__global__ void orb_popc_peak_kernel(unsigned* out, int iters, unsigned seed) {
+  unsigned x[8], acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { x[i] = seed * (threadIdx.x + 1) + i * 0x9e3779b9u; acc[i] = 0; }
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { acc[i] += __popc(x[i] ^ acc[i]); }
+  }
+  unsigned s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += acc[i];
+  if (s == 0xdeadbeefu) out[0] = s;
+}
+
+static long long g_knn_launches = 0;
+long long orb_knn_launches() { return g_knn_launches; }
+
+int orb_knn_num_chunks(int Q, long long D, int num_sms) {
+  const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+  // ~4 CTAs per SM across the grid, chunks of >= 1 tile and < 2^22 rows
+  long long want = (4LL * num_sms + qtiles - 1) / qtiles;
+  const long long max_chunks = (D + KNN_TILE - 1) / KNN_TILE;
+  if (want > max_chunks) want = max_chunks;
+  const long long min_chunks = (D + (1LL << 22) - 1) >> 22;
+  if (want < min_chunks) want = min_chunks;
+  if (want < 1) want = 1;
+  return (int)want;
+}
+
+void orb_launch_knn(const uint8_t* q, int Q, const uint8_t* db, long long D, long long index_base, int sentinel,
+                    unsigned long long* partial, int nchunks, OrbKnn2* out, cudaStream_t st) {
+  const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+  long long rows = (D + nchunks - 1) / nchunks;
+  rows = (rows + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+  orb_knn_kernel<<<dim3(qtiles, nchunks), KNN_THREADS, 0, st>>>((const uint4*)q, Q, (const uint4*)db, D, rows, index_base, partial);
+  orb_knn_merge_partial_kernel<<<(Q + 127) / 128, 128, 0, st>>>(partial, nchunks, Q, sentinel, out);
+  g_knn_launches += 2;
+}
+
+void orb_launch_knn_merge_shards(const OrbKnn2* shards, int nshards, int Q, int sentinel, OrbKnn2* out, cudaStream_t st) {
+  orb_knn_merge_shards_kernel<<<(Q + 127) / 128, 128, 0, st>>>(shards, nshards, Q, sentinel, out);
+  ++g_knn_launches;
+}
+
+void orb_launch_distance_batch(const uint8_t* a, const uint8_t* b, long long n, int* out, cudaStream_t st) {
+  orb_distance_batch_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint4*)a, (const uint4*)b, n, out);
+  ++g_knn_launches;
+}
+
+double orb_popc_peak(int num_sms) {
+  unsigned* d;
+  if (cudaMalloc(&d, 4) != cudaSuccess) return 0.0;
+  const int iters = 1 << 16, threads = 512, blocks = num_sms * 4;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  orb_popc_peak_kernel<<<blocks, threads>>>(d, 1024, 1u);
+  double best = 0.0;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(e0);
+    orb_popc_peak_kernel<<<blocks, threads>>>(d, iters, 12345u + rep);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double ops = (double)blocks * threads * (double)iters * 8.0;
+    if (ms > 0.f) best = fmax(best, ops / (ms * 1e-3));
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  return best;
+}

@@ -1,0 +1,527 @@
+// C ABI (include/orb_b200.h) over the sm_100a kernels. Host logic only: parameter tables exactly as the
+// reference constructor computes them (src/ORBextractor.cc:776-925), per-shape geometry, workspaces, launches.
+// No CPU fallback: every compute entry point needs a CUDA device.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../../include/orb_b200.h"
+#include "orb_common.cuh"
+
+// ---- kernel launchers (other translation units) -------------------------------------------------------------
+struct OrbKnn2;
+void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_fast(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t*, int*, int*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_describe(const uint8_t*, const uint8_t*, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
+                         const OrbGeom&, int, cudaStream_t, long long*);
+int orb_knn_num_chunks(int Q, long long D, int num_sms);
+void orb_launch_knn(const uint8_t*, int, const uint8_t*, long long, long long, int, unsigned long long*, int, OrbKnn2*, cudaStream_t);
+void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaStream_t);
+void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
+long long orb_knn_launches();
+double orb_popc_peak(int num_sms);
+
+static_assert(sizeof(orb_keypoint) == 28 && sizeof(OrbKeypoint) == 28, "cv::KeyPoint layout");
+static_assert(sizeof(orb_knn2) == 24, "orb_knn2 layout");
+
+// ---- errors ------------------------------------------------------------------------------------------
+static thread_local char t_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_err, sizeof(t_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CU(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) return fail(ORB_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+static inline int cv_round_f(float v) { return (int)lrintf(v); }
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int ensure(size_t need) {
+    if (need <= bytes) return ORB_OK;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e != cudaSuccess) return fail(ORB_E_CUDA, "cudaMalloc(%zu): %s", need, cudaGetErrorString(e));
+    bytes = need;
+    return ORB_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct orb_extractor {
+  orb_params prm;
+  int device = 0, num_sms = 148;
+  cudaStream_t stream = nullptr;
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> quota;
+  OrbGeom geom;            // valid when geom.width > 0
+  int chunk = 0;           // frames per internal pass (workspace capacity)
+  int last_batch = 0;      // frames of the last pass still resident in the workspace
+  int cap_ws = 0;
+  long long launches = 0;
+  DevBuf tabs, pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, err, stage_in, out_kps, out_desc, out_cnt;
+  DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
+  int* h_err = nullptr;    // pinned
+  int* h_cnt = nullptr;    // pinned [chunk * (1 + nlevels)]
+  std::mutex mu;
+};
+
+// src/ORBextractor.cc:776-845 with the reference's types: scaleFactor member is double, tables are float.
+static void build_tables(orb_extractor* e) {
+  const int nl = e->prm.nlevels;
+  const double sf = (double)e->prm.scale_factor;
+  e->scale.assign(nl, 1.f); e->sigma2.assign(nl, 1.f); e->invScale.assign(nl, 1.f); e->invSigma2.assign(nl, 1.f);
+  for (int i = 1; i < nl; ++i) {
+    e->scale[i] = (float)(e->scale[i - 1] * sf);
+    e->sigma2[i] = e->scale[i] * e->scale[i];
+  }
+  for (int i = 0; i < nl; ++i) { e->invScale[i] = 1.0f / e->scale[i]; e->invSigma2[i] = 1.0f / e->sigma2[i]; }
+  e->quota.assign(nl, 0);
+  const float factor = (float)(1.0f / sf);
+  float per = e->prm.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+  int sum = 0;
+  for (int l = 0; l < nl - 1; ++l) {
+    e->quota[l] = cv_round_f(per);
+    sum += e->quota[l];
+    per *= factor;
+  }
+  e->quota[nl - 1] = std::max(e->prm.nfeatures - sum, 0);
+}
+
+// cv::resize INTER_LINEAR coefficient table for one axis (ssz -> dsz), 11-bit fixed point.
+static void resize_table(int ssz, int dsz, ResizeTab* out) {
+  const double scale = 1.0 / ((double)dsz / ssz);
+  for (int d = 0; d < dsz; ++d) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= s;
+    if (s < 0) { s = 0; f = 0.f; }
+    if (s >= ssz - 1) { s = ssz - 1; f = 0.f; }
+    out[d].ofs = (short)s;
+    out[d].c0 = (short)cv_round_f((1.f - f) * 2048.f);
+    out[d].c1 = (short)cv_round_f(f * 2048.f);
+    out[d].pad = 0;
+  }
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Per-shape geometry: level sizes (:2099-2102), FAST cell grid (:1443-1462), quadtree roots (:1059-1063).
+static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>& tabs) {
+  OrbGeom g;
+  memset(&g, 0, sizeof(g));
+  const int nl = e->prm.nlevels;
+  g.nlevels = nl; g.width = W; g.height = H;
+  g.ini_th = e->prm.ini_th_fast; g.min_th = e->prm.min_th_fast;
+  static const int taps_new[7] = {18, 34, 48, 56, 48, 34, 18}, taps_old[7] = {18, 34, 49, 55, 49, 34, 18};
+  memcpy(g.blur_taps, (e->prm.flags & ORB_FLAG_LEGACY_BLUR) ? taps_old : taps_new, sizeof(g.blur_taps));
+  size_t plane = 0;
+  int cells = 0, raw = 0, nodes = 0, tab = 0;
+  tabs.clear();
+  for (int l = 0; l < nl; ++l) {
+    OrbLevel& L = g.lv[l];
+    L.iw = cv_round_f((float)W * e->invScale[l]);
+    L.ih = cv_round_f((float)H * e->invScale[l]);
+    if (L.iw < 2 * ORB_EDGE + 2 || L.ih < 2 * ORB_EDGE + 2)
+      return fail(ORB_E_SHAPE, "level %d is %dx%d: too small for the 19-px reflect border", l, L.iw, L.ih);
+    L.cols = L.iw + 2 * ORB_EDGE; L.rows = L.ih + 2 * ORB_EDGE;
+    L.pitch = (int)align_up(L.cols, 64);
+    L.plane_off = plane;
+    plane += align_up((size_t)L.pitch * L.rows, 256);
+    L.maxBX = L.cols - ORB_EDGE + 3; L.maxBY = L.rows - ORB_EDGE + 3;
+    const float width = (float)(L.maxBX - ORB_MIN_BORDER), height = (float)(L.maxBY - ORB_MIN_BORDER);
+    L.nCols = (int)(width / 30.f); L.nRows = (int)(height / 30.f);
+    if (L.nCols < 1 || L.nRows < 1) return fail(ORB_E_SHAPE, "level %d has no 30-px cell", l);
+    L.wCell = (int)ceilf(width / L.nCols); L.hCell = (int)ceilf(height / L.nRows);
+    if (L.maxBX - ORB_MIN_BORDER > 4095 || L.maxBY - ORB_MIN_BORDER > 4095)
+      return fail(ORB_E_SHAPE, "level %d exceeds the 4095-px packed coordinate range", l);
+    L.cell_base = cells;
+    cells += L.nCols * L.nRows;
+    L.nIni = (int)roundf((float)(L.maxBX - ORB_MIN_BORDER) / (L.maxBY - ORB_MIN_BORDER));
+    if (L.nIni < 1) return fail(ORB_E_SHAPE, "aspect ratio < 0.5: the reference divides by nIni == 0 (src/ORBextractor.cc:1059)");
+    L.hX = (float)(L.maxBX - ORB_MIN_BORDER) / L.nIni;
+    L.quota = e->quota[l];
+    const long long by_cells = (long long)L.nCols * L.nRows * ORB_CELL_CAP;
+    L.raw_cap = (int)std::min<long long>(by_cells, std::max(32LL * L.quota, 8192LL));
+    L.raw_off = raw; raw += (int)align_up(L.raw_cap, 32);
+    L.node_cap = std::max(L.quota + 3, 4 * L.nIni) + L.nIni + 8;
+    L.node_off = nodes; nodes += (int)align_up(L.node_cap, 32);
+    L.kept_off = L.node_off;
+    L.scale = e->scale[l];
+    L.patch_size = (float)(int)(31 * e->scale[l]);
+    L.tab_off = tab;
+    if (l > 0) {
+      const OrbLevel& P = g.lv[l - 1];
+      tabs.resize(tab + L.iw + L.ih);
+      resize_table(P.cols, L.iw, tabs.data() + tab);          // source = PADDED level l-1 (this fork, :2119)
+      resize_table(P.rows, L.ih, tabs.data() + tab + L.iw);
+      tab += L.iw + L.ih;
+    }
+  }
+  g.ncells_total = cells; g.raw_total = raw; g.node_total = nodes;
+  g.frame_stride = plane;
+  e->geom = g;
+  return ORB_OK;
+}
+
+// ---- workspace -------------------------------------------------------------------------------------------
+static int default_chunk(const OrbGeom& g) {
+  // Frames per internal pass: keep pyramid + blurred copy of a pass inside the 126 MB L2 where possible.
+  const char* env = getenv("ORB_B200_CHUNK");
+  if (env && atoi(env) > 0) return atoi(env);
+  const double per_frame = 2.0 * (double)g.frame_stride;
+  int c = (int)(96.0 * 1024 * 1024 / per_frame);
+  return std::max(1, std::min(c, 64));
+}
+
+static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
+  int rc;
+  if (e->geom.width != W || e->geom.height != H) {
+    std::vector<ResizeTab> tabs;
+    if ((rc = build_geometry(e, W, H, tabs)) != ORB_OK) return rc;
+    if ((rc = e->tabs.ensure(std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTab))) != ORB_OK) return rc;
+    if (!tabs.empty()) CU(cudaMemcpyAsync(e->tabs.p, tabs.data(), tabs.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    e->chunk = 0;
+  }
+  const OrbGeom& g = e->geom;
+  const int want = std::min(batch, default_chunk(g));
+  if (want > e->chunk || cap > e->cap_ws) {
+    const size_t B = (size_t)std::max(want, e->chunk);
+    const int capw = std::max(cap, e->cap_ws);
+    const int nl = g.nlevels;
+#define ENS(buf, bytes) if ((rc = e->buf.ensure(bytes)) != ORB_OK) return rc
+    ENS(pyr, B * g.frame_stride);
+    ENS(blr, B * g.frame_stride);
+    ENS(cell_cnt, B * g.ncells_total * sizeof(int));
+    ENS(cell_kp, B * g.ncells_total * ORB_CELL_CAP * sizeof(uint32_t));
+    ENS(kept, B * g.node_total * sizeof(uint32_t));
+    ENS(kept_cnt, B * nl * sizeof(int));
+    ENS(err, sizeof(int));
+    ENS(out_kps, B * capw * sizeof(OrbKeypoint));
+    ENS(out_desc, B * capw * 32);
+    ENS(out_cnt, B * sizeof(int));
+    ENS(q_key, B * g.raw_total * sizeof(uint32_t));
+    ENS(q_knode, B * g.raw_total * sizeof(int));
+    ENS(q_kchild, B * g.raw_total);
+    ENS(q_bbox, B * g.node_total * sizeof(int4));
+    ENS(q_ncount, B * g.node_total * sizeof(int));
+    ENS(q_pidx, B * g.node_total * sizeof(int));
+    ENS(q_best, B * g.node_total * sizeof(unsigned));
+    ENS(q_ordA, B * g.node_total * sizeof(int));
+    ENS(q_ordB, B * g.node_total * sizeof(int));
+    ENS(q_par, B * g.node_total * sizeof(int));
+    ENS(q_cand, B * g.node_total * 2 * sizeof(unsigned long long));
+    ENS(q_ccnt, B * g.node_total * 4 * sizeof(int));
+    ENS(q_cslot, B * g.node_total * 4 * sizeof(int));
+    ENS(q_scan, B * g.node_total * sizeof(unsigned long long));
+    ENS(q_rawn, B * nl * sizeof(int));
+#undef ENS
+    if (e->h_cnt) cudaFreeHost(e->h_cnt);
+    e->h_cnt = nullptr;
+    CU(cudaMallocHost(&e->h_cnt, B * (1 + nl) * sizeof(int)));
+    CU(cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream));
+    e->chunk = (int)B;
+    e->cap_ws = capw;
+    e->last_batch = 0;
+  }
+  return ORB_OK;
+}
+
+// One internal pass over `n` (<= chunk) device-resident frames; outputs to device pointers.
+static void run_pass(orb_extractor* e, const uint8_t* images, int step, long long image_stride, int n, OrbKeypoint* kps,
+                     uint8_t* desc, int cap, int* counts_dev) {
+  const OrbGeom& g = e->geom;
+  cudaStream_t st = e->stream;
+  QtScratch S;
+  S.key = e->q_key.as<uint32_t>(); S.knode = e->q_knode.as<int>(); S.kchild = e->q_kchild.as<uint8_t>();
+  S.bbox = e->q_bbox.as<int4>(); S.ncount = e->q_ncount.as<int>(); S.pidx = e->q_pidx.as<int>();
+  S.best = e->q_best.as<unsigned>(); S.ordA = e->q_ordA.as<int>(); S.ordB = e->q_ordB.as<int>(); S.par = e->q_par.as<int>();
+  S.cand = e->q_cand.as<unsigned long long>(); S.ccnt = e->q_ccnt.as<int>(); S.cslot = e->q_cslot.as<int>();
+  S.scan = e->q_scan.as<unsigned long long>(); S.raw_n = e->q_rawn.as<int>();
+  orb_launch_pyramid(images, step, image_stride, e->pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches);
+  orb_launch_fast(e->pyr.as<uint8_t>(), e->cell_cnt.as<int>(), e->cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
+  orb_launch_blur(e->pyr.as<uint8_t>(), e->blr.as<uint8_t>(), g, n, st, &e->launches);
+  orb_launch_quadtree(e->cell_cnt.as<int>(), e->cell_kp.as<uint32_t>(), S, e->kept.as<uint32_t>(), e->kept_cnt.as<int>(),
+                      e->err.as<int>(), g, n, st, &e->launches);
+  orb_launch_describe(e->pyr.as<uint8_t>(), e->blr.as<uint8_t>(), e->kept.as<uint32_t>(), e->kept_cnt.as<int>(), kps, desc, cap,
+                      counts_dev, e->err.as<int>(), g, n, st, &e->launches);
+  e->last_batch = n;
+}
+
+static int check_err_flag(orb_extractor* e) {
+  int flag = 0;
+  CU(cudaMemcpyAsync(&flag, e->err.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  CU(cudaGetLastError());
+  if (flag) {
+    cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream);
+    return fail(ORB_E_CAPACITY, "capacity overflow (flags %d: 1 cell cap, 2 raw keypoints, 4 nodes, 8 output cap)", flag);
+  }
+  return ORB_OK;
+}
+
+extern "C" {
+
+const char* orb_last_error(void) { return t_err; }
+int orb_abi_version(void) { return ORB_B200_ABI_VERSION; }
+int orb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
+  if (!p || !out) return fail(ORB_E_BADARG, "null argument");
+  *out = nullptr;
+  if (p->nfeatures < 1 || p->nlevels < 1 || p->nlevels > ORB_MAX_LEVELS || !(p->scale_factor > 1.0f) || p->min_th_fast < 1 ||
+      p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 254)
+    return fail(ORB_E_BADARG, "unsupported ORB parameters (nfeatures>=1, 1<=nlevels<=%d, scale>1, 1<=minTh<=iniTh<=254)", ORB_MAX_LEVELS);
+  if (p->flags & ORB_FLAG_UPSTREAM_PYRAMID) return fail(ORB_E_BADARG, "ORB_FLAG_UPSTREAM_PYRAMID is not implemented on device");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  if (device < 0 || device >= ndev) return fail(ORB_E_BADARG, "device %d out of range (%d devices)", device, ndev);
+  CU(cudaSetDevice(device));
+  orb_extractor* e = new orb_extractor();
+  e->prm = *p;
+  e->device = device;
+  memset(&e->geom, 0, sizeof(e->geom));
+  build_tables(e);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
+  cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+  if (ce != cudaSuccess) { delete e; return fail(ORB_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce)); }
+  *out = e;
+  return ORB_OK;
+}
+
+void orb_extractor_destroy(orb_extractor* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+  DevBuf* bufs[] = {&e->tabs, &e->pyr, &e->blr, &e->cell_cnt, &e->cell_kp, &e->kept, &e->kept_cnt, &e->err, &e->stage_in, &e->out_kps,
+                    &e->out_desc, &e->out_cnt, &e->q_key, &e->q_knode, &e->q_kchild, &e->q_bbox, &e->q_ncount, &e->q_pidx, &e->q_best,
+                    &e->q_ordA, &e->q_ordB, &e->q_par, &e->q_cand, &e->q_ccnt, &e->q_cslot, &e->q_scan, &e->q_rawn};
+  for (DevBuf* b : bufs) b->release();
+  if (e->h_cnt) cudaFreeHost(e->h_cnt);
+  delete e;
+}
+
+int orb_extractor_get_levels(const orb_extractor* e) { return e ? e->prm.nlevels : 0; }
+float orb_extractor_get_scale_factor(const orb_extractor* e) { return e ? (float)(double)e->prm.scale_factor : 0.f; }
+int orb_extractor_get_table(const orb_extractor* e, int what, float* out) {
+  if (!e || !out || what < 0 || what > 3) return fail(ORB_E_BADARG, "bad argument");
+  const std::vector<float>& t = what == 0 ? e->scale : what == 1 ? e->invScale : what == 2 ? e->sigma2 : e->invSigma2;
+  std::copy(t.begin(), t.end(), out);
+  return ORB_OK;
+}
+int orb_extractor_get_features_per_level(const orb_extractor* e, int32_t* out) {
+  if (!e || !out) return fail(ORB_E_BADARG, "bad argument");
+  std::copy(e->quota.begin(), e->quota.end(), out);
+  return ORB_OK;
+}
+int orb_extractor_max_keypoints(const orb_extractor* e) {
+  if (!e) return 0;
+  // per level the list can end at max(quota + 3, 4 * nIni); nIni <= 4 for aspect <= 4.5 -> generous fixed slack
+  return e->prm.nfeatures + 16 * e->prm.nlevels;
+}
+void* orb_extractor_stream(orb_extractor* e) { return e ? (void*)e->stream : nullptr; }
+int64_t orb_extractor_launch_count(const orb_extractor* e) { return e ? e->launches : 0; }
+
+int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, int width, int height, int batch,
+                             orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts_dev, int sync) {
+  if (!e || !images || !kps || !desc || !counts_dev) return fail(ORB_E_BADARG, "null argument");
+  if (width <= 0 || height <= 0 || step < width || batch <= 0 || cap <= 0) return fail(ORB_E_BADARG, "bad size");
+  std::lock_guard<std::mutex> lk(e->mu);
+  CU(cudaSetDevice(e->device));
+  int rc = ensure_shape(e, width, height, batch, cap);
+  if (rc != ORB_OK) return rc;
+  const long long istride = (long long)step * height;
+  for (int f0 = 0; f0 < batch; f0 += e->chunk) {
+    const int n = std::min(e->chunk, batch - f0);
+    run_pass(e, images + (long long)f0 * istride, step, istride, n, reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap,
+             desc + (long long)f0 * cap * 32, cap, counts_dev + f0);
+  }
+  CU(cudaGetLastError());
+  if (sync) return check_err_flag(e);
+  return ORB_OK;
+}
+
+int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height, int batch,
+                      orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts, int32_t* level_counts) {
+  if (!e || !images || !kps || !desc || !counts) return fail(ORB_E_BADARG, "null argument");
+  if (width <= 0 || height <= 0 || step < width || batch <= 0 || cap <= 0) return fail(ORB_E_BADARG, "bad size");
+  for (int i = 0; i < batch; ++i)
+    if (!images[i]) return fail(ORB_E_BADARG, "null image %d", i);   // the reference returns silently on an empty image (:1966)
+  std::lock_guard<std::mutex> lk(e->mu);
+  CU(cudaSetDevice(e->device));
+  int rc = ensure_shape(e, width, height, batch, cap);
+  if (rc != ORB_OK) return rc;
+  const OrbGeom& g = e->geom;
+  const int nl = g.nlevels;
+  const int spitch = (width + 63) & ~63;
+  if ((rc = e->stage_in.ensure((size_t)e->chunk * spitch * height)) != ORB_OK) return rc;
+  for (int f0 = 0; f0 < batch; f0 += e->chunk) {
+    const int n = std::min(e->chunk, batch - f0);
+    for (int i = 0; i < n; ++i)
+      CU(cudaMemcpy2DAsync(e->stage_in.as<uint8_t>() + (size_t)i * spitch * height, spitch, images[f0 + i], step, width, height,
+                           in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, e->stream));
+    OrbKeypoint* dk = out_mem == ORB_MEM_DEVICE ? reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap : e->out_kps.as<OrbKeypoint>();
+    uint8_t* dd = out_mem == ORB_MEM_DEVICE ? desc + (long long)f0 * cap * 32 : e->out_desc.as<uint8_t>();
+    run_pass(e, e->stage_in.as<uint8_t>(), spitch, (long long)spitch * height, n, dk, dd, cap, e->out_cnt.as<int>());
+    CU(cudaMemcpyAsync(e->h_cnt, e->out_cnt.p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(e->h_cnt + e->chunk, e->kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    if (out_mem != ORB_MEM_DEVICE) {
+      CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->stream));
+      CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->stream));
+    }
+    if ((rc = check_err_flag(e)) != ORB_OK) return rc;
+    memcpy(counts + f0, e->h_cnt, n * sizeof(int));
+    if (level_counts) memcpy(level_counts + (size_t)f0 * nl, e->h_cnt + e->chunk, (size_t)n * nl * sizeof(int));
+  }
+  return ORB_OK;
+}
+
+int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int* rows) {
+  if (!e || !cols || !rows || e->geom.width == 0 || level < 0 || level >= e->geom.nlevels) return fail(ORB_E_BADARG, "bad argument / no image processed yet");
+  *cols = e->geom.lv[level].cols;
+  *rows = e->geom.lv[level].rows;
+  return ORB_OK;
+}
+
+int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurred, uint8_t* dst, int dst_step) {
+  if (!e || !dst || e->geom.width == 0 || level < 0 || level >= e->geom.nlevels) return fail(ORB_E_BADARG, "bad argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (index < 0 || index >= e->last_batch) return fail(ORB_E_BADARG, "image %d is not resident (last pass held %d frames)", index, e->last_batch);
+  const OrbLevel& L = e->geom.lv[level];
+  if (dst_step < L.cols) return fail(ORB_E_BADARG, "dst_step too small");
+  CU(cudaSetDevice(e->device));
+  const uint8_t* src = (blurred ? e->blr.as<uint8_t>() : e->pyr.as<uint8_t>()) + (size_t)index * e->geom.frame_stride + L.plane_off;
+  CU(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, L.cols, L.rows, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return ORB_OK;
+}
+
+int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keypoint* out, int cap) {
+  if (!e || !out || e->geom.width == 0 || level < 0 || level >= e->geom.nlevels) return fail(ORB_E_BADARG, "bad argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (index < 0 || index >= e->last_batch) return fail(ORB_E_BADARG, "image %d is not resident", index);
+  CU(cudaSetDevice(e->device));
+  const OrbGeom& g = e->geom;
+  const OrbLevel& L = g.lv[level];
+  int n = 0;
+  CU(cudaMemcpyAsync(&n, e->q_rawn.as<int>() + (size_t)index * g.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  n = std::min(n, L.raw_cap);
+  if (n > cap) return fail(ORB_E_CAPACITY, "need room for %d raw keypoints", n);
+  std::vector<uint32_t> keys(std::max(n, 1));
+  CU(cudaMemcpyAsync(keys.data(), e->q_key.as<uint32_t>() + (size_t)index * g.raw_total + L.raw_off, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  for (int i = 0; i < n; ++i) {
+    out[i].x = (float)(keys[i] & 0xfffu); out[i].y = (float)((keys[i] >> 12) & 0xfffu);
+    out[i].size = 7.f; out[i].angle = -1.f; out[i].response = (float)(keys[i] >> 24);
+    out[i].octave = 0; out[i].class_id = -1;
+  }
+  return n;
+}
+
+// ---- matcher ------------------------------------------------------------------------------------------------
+struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mutex (calls on one device serialise their setup)
+  std::mutex mu;
+  DevBuf partial, q, db, out;
+  int num_sms = 0;
+};
+static KnnWorkspace g_knn_ws[16];
+
+static int current_device_ws(KnnWorkspace** ws) {
+  int dev = 0;
+  CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 16) return fail(ORB_E_BADARG, "device index %d unsupported", dev);
+  *ws = &g_knn_ws[dev];
+  if ((*ws)->num_sms == 0) {
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    (*ws)->num_sms = prop.multiProcessorCount;
+  }
+  return ORB_OK;
+}
+
+int orb_hamming_knn(const uint8_t* query, int q_mem, int Q, const uint8_t* db, int db_mem, int64_t D, int64_t index_base,
+                    int sentinel, orb_knn2* out, int out_mem, void* stream) {
+  if (!query || !out || Q <= 0 || D < 0 || (D > 0 && !db) || sentinel < 1) return fail(ORB_E_BADARG, "bad argument");
+  if (index_base < 0 || index_base + D >= (1LL << 40)) return fail(ORB_E_BADARG, "index range exceeds 2^40");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const uint8_t* dq = query;
+  const uint8_t* ddb = db;
+  orb_knn2* dout = out;
+  const bool any_host = q_mem != ORB_MEM_DEVICE || db_mem != ORB_MEM_DEVICE || out_mem != ORB_MEM_DEVICE;
+  if (q_mem != ORB_MEM_DEVICE || ((uintptr_t)query & 15)) {
+    if ((rc = ws->q.ensure((size_t)Q * 32)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->q.p, query, (size_t)Q * 32, q_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    dq = ws->q.as<uint8_t>();
+  }
+  if (D > 0 && (db_mem != ORB_MEM_DEVICE || ((uintptr_t)db & 15))) {
+    if ((rc = ws->db.ensure((size_t)D * 32)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->db.p, db, (size_t)D * 32, db_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    ddb = ws->db.as<uint8_t>();
+  }
+  if (out_mem != ORB_MEM_DEVICE) {
+    if ((rc = ws->out.ensure((size_t)Q * sizeof(orb_knn2))) != ORB_OK) return rc;
+    dout = ws->out.as<orb_knn2>();
+  }
+  const int nchunks = orb_knn_num_chunks(Q, D, ws->num_sms);
+  if ((rc = ws->partial.ensure((size_t)nchunks * Q * 2 * sizeof(unsigned long long))) != ORB_OK) return rc;
+  orb_launch_knn(dq, Q, ddb, D, index_base, sentinel, ws->partial.as<unsigned long long>(), nchunks, (OrbKnn2*)dout, st);
+  CU(cudaGetLastError());
+  if (out_mem != ORB_MEM_DEVICE) CU(cudaMemcpyAsync(out, dout, (size_t)Q * sizeof(orb_knn2), cudaMemcpyDeviceToHost, st));
+  if (any_host) CU(cudaStreamSynchronize(st));
+  return ORB_OK;
+}
+
+int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentinel, orb_knn2* out, void* stream) {
+  if (!shards || !out || nshards < 1 || Q <= 0) return fail(ORB_E_BADARG, "bad argument");
+  orb_launch_knn_merge_shards((const OrbKnn2*)shards, nshards, Q, sentinel, (OrbKnn2*)out, (cudaStream_t)stream);
+  CU(cudaGetLastError());
+  return ORB_OK;
+}
+
+int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream) {
+  if (!a || !b || !out || n < 0) return fail(ORB_E_BADARG, "bad argument");
+  if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return fail(ORB_E_BADARG, "descriptor arrays must be 16-byte aligned");
+  if (n == 0) return ORB_OK;
+  orb_launch_distance_batch(a, b, n, out, (cudaStream_t)stream);
+  CU(cudaGetLastError());
+  return ORB_OK;
+}
+
+int64_t orb_matcher_launch_count(void) { return orb_knn_launches(); }
+
+double orb_measure_popc_peak(int device) {
+  if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return 0.0; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0.0;
+  return orb_popc_peak(prop.multiProcessorCount);
+}
+
+}  // extern "C"

@@ -1,0 +1,76 @@
+// Shared device/host definitions for the B200 (sm_100a) ORB front-end kernels.
+// Data layout in HBM (per extractor handle, batch capacity B frames):
+//   pyramid  : [B] frames, each a block of nlevels padded u8 planes (rows_l x pitch_l, pitch 64-byte aligned)
+//   blurred  : same layout
+//   cell_cnt : [B][ncells_total] int32, cell_kp : [B][ncells_total][CELL_CAP] packed u32 (x:12 | y:12 | score:8)
+//   quadtree scratch + kept keypoints per (frame, level)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define ORB_MAX_LEVELS 16
+#define ORB_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:82
+#define ORB_HALF_PATCH 15    // HALF_PATCH_SIZE, :81
+#define ORB_MIN_BORDER 16    // EDGE_THRESHOLD - 3, :1443
+#define ORB_CELL_CAP 128     // NMS survivors kept per 30-px cell (overflow -> ORB_E_CAPACITY)
+
+struct OrbLevel {
+  int cols, rows, pitch;     // padded level (mvImagePyramid[l] of this fork)
+  int iw, ih;                // interior size cvRound(W * invScale)
+  unsigned long long plane_off;  // byte offset of the plane inside one frame's pyramid block
+  int maxBX, maxBY;          // cols-16, rows-16
+  int nCols, nRows, wCell, hCell;
+  int cell_base;             // first cell of this level in the per-frame cell arrays
+  int nIni;                  // quadtree roots
+  float hX;
+  int quota;                 // mnFeaturesPerLevel[l]
+  int raw_cap, raw_off;      // raw keypoint capacity / offset in per-frame raw arrays
+  int node_cap, node_off;    // node arrays
+  int kept_off;              // offset into per-frame kept arrays (capacity node_cap)
+  float scale;               // mvScaleFactor[l]
+  float patch_size;          // (int)(31*scale)
+  int tab_off;               // offset into resize tables (x table then y table), level >= 1
+};
+
+struct OrbGeom {
+  int nlevels, width, height;
+  int ncells_total;
+  int raw_total, node_total;
+  unsigned long long frame_stride;   // bytes per frame in pyramid / blurred
+  int ini_th, min_th;
+  int blur_taps[7];
+  OrbLevel lv[ORB_MAX_LEVELS];
+};
+
+struct ResizeTab {   // per destination index of cv::resize INTER_LINEAR (11-bit coefficients)
+  short ofs, c0, c1, pad;
+};
+
+struct OrbKeypoint {  // == cv::KeyPoint / orb_keypoint
+  float x, y, size, angle, response;
+  int octave, class_id;
+};
+
+struct QtScratch {          // per-frame strides are the *_total fields of OrbGeom
+  uint32_t* key;            // [B][raw_total]   packed x | y<<12 | score<<24
+  int* knode;               // [B][raw_total]
+  uint8_t* kchild;          // [B][raw_total]
+  int4* bbox;               // [B][node_total]  ulx, uly, brx, bry
+  int* ncount;              // [B][node_total]
+  int* pidx;                // [B][node_total]  index in P this round, or -1
+  unsigned* best;           // [B][node_total]
+  int* ordA;                // [B][node_total]
+  int* ordB;                // [B][node_total]
+  int* par;                 // [B][node_total]
+  unsigned long long* cand; // [B][node_total*2] (size<<40 | seq<<20 | node), second half = sort padding
+  int* ccnt;                // [B][node_total*4] child key counts per parent index
+  int* cslot;               // [B][node_total*4] child slots per parent index
+  unsigned long long* scan; // [B][node_total]   packed scan: low = nonempty children, high = multi-key children
+  int* raw_n;               // [B][nlevels]      raw keypoint count (test hook / diagnostics)
+};
+
+__host__ __device__ __forceinline__ int orb_reflect101(int p, int n) {
+  // BORDER_REFLECT_101 for |overshoot| < n (border 19 / 3 << level sizes, checked on the host)
+  p = p < 0 ? -p : p;
+  return p >= n ? 2 * (n - 1) - p : p;
+}

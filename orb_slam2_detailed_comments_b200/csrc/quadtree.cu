@@ -1,0 +1,334 @@
+// ORBextractor::DistributeOctTree (src/ORBextractor.cc:1050-1417) + ExtractorNode::DivideNode (:963-1035)
+// as a data-parallel round algorithm, one CTA per (frame, level).
+//
+// What the reference's std::list manipulation computes, restated:
+//  * A key never changes relative order inside a node (push_back in scan order), so the per-node winner
+//    "first key with the maximum response" (:1394-1409) is max(response), ties -> lowest raw index.
+//    Keys therefore only carry a node id; no per-node vectors are materialised.
+//  * One "round" splits an ordered parent sequence P. Children are push_front'ed in order n1..n4 and the
+//    parent erased, so new_list = reverse(concat_r nonempty_children(P[r])) ++ (old_list minus split parents).
+//  * Phase 1 (:1166-1268): P = every node with > 1 keys in list order (= reverse creation order of the
+//    previous round); stop if size >= N or nothing grew; enter phase 2 when size + 3*nToExpand > N.
+//  * Phase 2 (:1284-1374): P = previous round's multi-key children sorted by (size, creation seq) descending
+//    (canonical replacement of the reference's (size, heap pointer) order), cut at the first
+//    parent after which size >= N. The cut is a prefix-sum over P of (nonempty children - 1).
+// Child slots: the first non-empty child reuses its parent's slot, so live slots == list size <= max(N+3, 4*nIni).
+#include "orb_common.cuh"
+
+#define QT_THREADS 256
+#define QT_SORT_SMEM 2048
+
+template <typename T>
+__device__ T qt_block_scan_excl(T* a, int n, T* s_warp) {
+  // in-place exclusive scan over a[0..n); every thread of the block calls it. Returns the total.
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  T carry = 0;
+  for (int base = 0; base < n; base += QT_THREADS) {
+    const int i = base + threadIdx.x;
+    const T v = i < n ? a[i] : (T)0;
+    T x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const T y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      T w = lane < QT_THREADS / 32 ? s_warp[lane] : (T)0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const T y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      s_warp[lane] = w;
+    }
+    __syncthreads();
+    const T wo = warp ? s_warp[warp - 1] : (T)0;
+    if (i < n) a[i] = carry + wo + x - v;
+    carry += s_warp[QT_THREADS / 32 - 1];
+    __syncthreads();
+  }
+  return carry;
+}
+
+// bitonic sort, descending, n2 = power of two >= n (padding zeros sort last)
+__device__ void qt_sort_desc(unsigned long long* a, int n2) {
+  for (int k = 2; k <= n2; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < n2; i += QT_THREADS) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long x = a[i], y = a[ixj];
+          const bool desc = (i & k) == 0;
+          if (desc ? (x < y) : (x > y)) { a[i] = y; a[ixj] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(QT_THREADS)
+orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_kp, QtScratch S,
+                    uint32_t* __restrict__ kept /*[B][node_total] packed key*/, int* __restrict__ kept_cnt /*[B][nlevels]*/,
+                    int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
+  __shared__ unsigned long long s_warp64[32];
+  __shared__ int s_warp32[32];
+  __shared__ unsigned long long s_sort[QT_SORT_SMEM];
+  __shared__ int s_nalloc, s_cut, s_ncand;
+
+  const int frame = blockIdx.x / g.nlevels, level = blockIdx.x - frame * g.nlevels;
+  const OrbLevel& L = g.lv[level];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int N = L.quota;
+
+  const long long ro = (long long)frame * g.raw_total + L.raw_off;
+  const long long no = (long long)frame * g.node_total + L.node_off;
+  uint32_t* key = S.key + ro;
+  int* knode = S.knode + ro;
+  uint8_t* kchild = S.kchild + ro;
+  int4* bbox = S.bbox + no;
+  int* ncount = S.ncount + no;
+  int* pidx = S.pidx + no;
+  unsigned* best = S.best + no;
+  int* ordOld = S.ordA + no;
+  int* ordNew = S.ordB + no;
+  int* par = S.par + no;
+  unsigned long long* cand = S.cand + 2 * no;
+  int* ccnt = S.ccnt + 4 * no;
+  int* cslot = S.cslot + 4 * no;
+  unsigned long long* scan = S.scan + no;
+  uint32_t* kept_out = kept + no;
+
+  // ---- gather this level's raw keypoints in (cell row, cell col, row-major in cell) order: vToDistributeKeys
+  const int ncell = L.nRows * L.nCols;
+  const int* ccount = cell_cnt + (long long)frame * g.ncells_total + L.cell_base;
+  const uint32_t* ckp = cell_kp + ((long long)frame * g.ncells_total + L.cell_base) * ORB_CELL_CAP;
+  // scan cell counts in chunks, reusing `scan` storage is too small for 4K levels, so do a running carry
+  int n = 0;
+  for (int base = 0; base < ncell; base += QT_THREADS) {
+    const int c = base + tid;
+    const int v = c < ncell ? ccount[c] : 0;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_warp32[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int w = lane < QT_THREADS / 32 ? s_warp32[lane] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      s_warp32[lane] = w;
+    }
+    __syncthreads();
+    const int off = n + (warp ? s_warp32[warp - 1] : 0) + x - v;
+    // each thread copies its own cell's entries (<= CELL_CAP, typically a handful)
+    if (c < ncell) {
+      const uint32_t* src = ckp + (long long)c * ORB_CELL_CAP;
+      for (int e = 0; e < v; ++e)
+        if (off + e < L.raw_cap) key[off + e] = src[e];
+    }
+    n += s_warp32[QT_THREADS / 32 - 1];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    S.raw_n[frame * g.nlevels + level] = n;
+    if (n > L.raw_cap) atomicOr(err_flag, 2);
+  }
+  n = min(n, L.raw_cap);
+  if (n == 0) {
+    if (tid == 0) kept_cnt[frame * g.nlevels + level] = 0;
+    return;
+  }
+
+  // ---- roots (:1060-1129)
+  const int nIni = L.nIni;
+  const float hX = L.hX;
+  for (int i = tid; i < L.node_cap; i += QT_THREADS) { ncount[i] = 0; pidx[i] = -1; }
+  __syncthreads();
+  for (int i = tid; i < nIni; i += QT_THREADS)
+    bbox[i] = make_int4((int)__fmul_rn(hX, (float)i), 0, (int)__fmul_rn(hX, (float)(i + 1)), L.maxBY - ORB_MIN_BORDER);
+  for (int i = tid; i < n; i += QT_THREADS) {
+    const int r = (int)__fdiv_rn((float)(key[i] & 0xfffu), hX);
+    knode[i] = r;
+    atomicAdd(&ncount[r], 1);
+  }
+  if (tid == 0) s_nalloc = nIni;
+  __syncthreads();
+  int m = 0, k = 0;   // list size, parents this round (uniform across the block)
+  if (tid == 0) {     // nIni is 1..4: serial
+    int mm = 0, kk = 0;
+    for (int i = 0; i < nIni; ++i) {
+      if (ncount[i] > 0) ordOld[mm++] = i;
+      if (ncount[i] > 1) par[kk++] = i;
+    }
+    s_cut = mm;
+    s_ncand = kk;
+  }
+  __syncthreads();
+  m = s_cut;
+  k = s_ncand;
+  __syncthreads();
+
+  bool phase2 = false;
+  while (k > 0) {
+    // A: register parents
+    for (int r = tid; r < k; r += QT_THREADS) {
+      pidx[par[r]] = r;
+      ccnt[4 * r] = 0; ccnt[4 * r + 1] = 0; ccnt[4 * r + 2] = 0; ccnt[4 * r + 3] = 0;
+    }
+    if (tid == 0) { s_cut = k; s_ncand = 0; }
+    __syncthreads();
+    // B: classify keys of parents (DivideNode :968-1022)
+    for (int i = tid; i < n; i += QT_THREADS) {
+      const int nd = knode[i];
+      const int r = pidx[nd];
+      if (r >= 0) {
+        const int4 b = bbox[nd];
+        const int hx = (b.z - b.x + 1) >> 1, hy = (b.w - b.y + 1) >> 1;   // ceil(w / 2.f), w >= 0
+        const uint32_t q = key[i];
+        const int x = q & 0xfffu, y = (q >> 12) & 0xfffu;
+        const int c = (x < b.x + hx ? 0 : 1) + (y < b.y + hy ? 0 : 2);
+        kchild[i] = (uint8_t)c;
+        atomicAdd(&ccnt[4 * r + c], 1);
+      }
+    }
+    __syncthreads();
+    // C/D: scan nonempty / multi-key child counts over P, find the phase-2 cut
+    for (int r = tid; r < k; r += QT_THREADS) {
+      unsigned ne = 0, nc = 0;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { const int v = ccnt[4 * r + c]; ne += v > 0; nc += v > 1; }
+      scan[r] = (unsigned long long)ne | ((unsigned long long)nc << 32);
+    }
+    __syncthreads();
+    const unsigned long long tot = qt_block_scan_excl<unsigned long long>(scan, k, s_warp64);
+    int kc = k;
+    if (phase2) {
+      for (int r = tid; r < k; r += QT_THREADS) {
+        unsigned ne = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) ne += ccnt[4 * r + c] > 0;
+        const int after = m + (int)(unsigned)(scan[r] & 0xffffffffu) + (int)ne - (r + 1);   // list size after splitting P[0..r]
+        if (after >= N) atomicMin(&s_cut, r + 1);
+      }
+      __syncthreads();
+      kc = s_cut;
+    }
+    // totals over the committed prefix
+    int T, ncand;
+    if (kc == k) { T = (int)(unsigned)(tot & 0xffffffffu); ncand = (int)(tot >> 32); }
+    else { const unsigned long long e = scan[kc]; T = (int)(unsigned)(e & 0xffffffffu); ncand = (int)(e >> 32); }
+    // E: create children
+    for (int r = tid; r < kc; r += QT_THREADS) {
+      const int p = par[r];
+      const int4 b = bbox[p];
+      const int hx = (b.z - b.x + 1) >> 1, hy = (b.w - b.y + 1) >> 1;
+      const int mx = b.x + hx, my = b.y + hy;
+      const unsigned long long e = scan[r];
+      int o = (int)(unsigned)(e & 0xffffffffu), q = (int)(e >> 32);
+      bool first = true;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int cnt = ccnt[4 * r + c];
+        if (cnt == 0) continue;
+        int slot;
+        if (first) { slot = p; first = false; }
+        else slot = atomicAdd(&s_nalloc, 1);
+        if (slot < L.node_cap) {
+          bbox[slot] = make_int4((c & 1) ? mx : b.x, (c & 2) ? my : b.y, (c & 1) ? b.z : mx, (c & 2) ? b.w : my);
+          ncount[slot] = cnt;
+          ordNew[T - 1 - o] = slot;
+          if (cnt > 1) cand[q++] = ((unsigned long long)cnt << 40) | ((unsigned long long)o << 20) | (unsigned)slot;
+        }
+        cslot[4 * r + c] = slot;
+        ++o;
+      }
+    }
+    __syncthreads();
+    if (s_nalloc > L.node_cap) {   // cannot happen by the size bound; guard against corrupt state
+      if (tid == 0) { atomicOr(err_flag, 4); kept_cnt[frame * g.nlevels + level] = 0; }
+      return;
+    }
+    // F: move keys to their child nodes
+    for (int i = tid; i < n; i += QT_THREADS) {
+      const int nd = knode[i];
+      const int r = pidx[nd];
+      if (r >= 0 && r < kc) knode[i] = cslot[4 * r + kchild[i]];
+    }
+    // G: survivors keep their relative order behind the new children
+    unsigned long long* sflag = scan;   // reuse (E is done with it after the barrier below)
+    __syncthreads();
+    for (int q = tid; q < m; q += QT_THREADS) {
+      const int r = pidx[ordOld[q]];
+      sflag[q] = (r >= 0 && r < kc) ? 0ull : 1ull;
+    }
+    __syncthreads();
+    {
+      // survivor flags need the pre-scan value after the scan: keep it in a register per element
+      // (each element is touched by the same thread before and after: index q = base + tid)
+    }
+    // scan in place; recover flag as (next - cur) is not possible for the last one, so re-derive from pidx
+    qt_block_scan_excl<unsigned long long>(sflag, m, s_warp64);
+    for (int q = tid; q < m; q += QT_THREADS) {
+      const int nd = ordOld[q];
+      const int r = pidx[nd];
+      if (!(r >= 0 && r < kc)) ordNew[T + (int)sflag[q]] = nd;
+    }
+    __syncthreads();
+    // H: unregister parents
+    for (int r = tid; r < k; r += QT_THREADS) pidx[par[r]] = -1;
+    const int m_new = T + (m - kc);
+    __syncthreads();
+    { int* t = ordOld; ordOld = ordNew; ordNew = t; }
+    const int m_prev = m;
+    m = m_new;
+    // ---- loop control (:1260-1268, :1360-1370)
+    if (m >= N || m == m_prev) break;
+    if (phase2 && kc < k) break;   // unreachable (cut implies m >= N), kept for safety
+    if (!phase2 && m + 3 * ncand > N) phase2 = true;
+    k = ncand;
+    if (k == 0) break;
+    if (phase2) {
+      int n2 = 1;
+      while (n2 < k) n2 <<= 1;
+      unsigned long long* buf = n2 <= QT_SORT_SMEM ? s_sort : cand;
+      if (buf == s_sort) {
+        for (int i = tid; i < n2; i += QT_THREADS) s_sort[i] = i < k ? cand[i] : 0ull;
+      } else {
+        for (int i = k + tid; i < n2; i += QT_THREADS) cand[i] = 0ull;
+      }
+      __syncthreads();
+      qt_sort_desc(buf, n2);
+      for (int r = tid; r < k; r += QT_THREADS) par[r] = (int)(buf[r] & 0xfffffu);
+    } else {
+      for (int r = tid; r < k; r += QT_THREADS) par[r] = (int)(cand[k - 1 - r] & 0xfffffu);   // list order = reverse creation
+    }
+    __syncthreads();
+  }
+
+  // ---- per node keep the best key (:1387-1413), output in list order
+  for (int q = tid; q < m; q += QT_THREADS) best[ordOld[q]] = 0u;
+  __syncthreads();
+  for (int i = tid; i < n; i += QT_THREADS)
+    atomicMax(&best[knode[i]], ((key[i] >> 24) << 24) | (0xffffffu - (unsigned)i));
+  __syncthreads();
+  for (int q = tid; q < m; q += QT_THREADS) {
+    const unsigned b = best[ordOld[q]];
+    kept_out[q] = key[0xffffffu - (b & 0xffffffu)];
+  }
+  if (tid == 0) kept_cnt[frame * g.nlevels + level] = m;
+}
+
+void orb_launch_quadtree(const int* cell_cnt, const uint32_t* cell_kp, const QtScratch& S, uint32_t* kept, int* kept_cnt,
+                         int* err_flag, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
+  orb_quadtree_kernel<<<batch * g.nlevels, QT_THREADS, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
+  ++*launches;
+}
