@@ -1,0 +1,134 @@
+"""Host-side mirror of ORB_SLAM2::ORBmatcher's distance semantics (reference include/ORBmatcher.h:40-230)
+over the C ABI: DescriptorDistance (src/ORBmatcher.cc:2073-2093) and the best/second-best + ratio idiom
+(src/ORBmatcher.cc:304-342) as a brute-force k=2 scan on the GPU. No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import KNN_DTYPE, MEM_DEVICE, MEM_HOST, check
+
+
+def _vp(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def hamming_knn(query: np.ndarray, db: np.ndarray, index_base: int = 0, sentinel: int = 256) -> np.ndarray:
+    """query [Q,32] u8, db [D,32] u8 host arrays -> KNN_DTYPE[Q] (d1, d2, i1, i2); i = -1 / d = sentinel where
+    the reference loop would have left best/second at their initial value."""
+    query = np.ascontiguousarray(query, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    if query.ndim != 2 or query.shape[1] != 32 or db.ndim != 2 or db.shape[1] != 32:
+        raise TypeError("descriptors must be [N,32] uint8 (256-bit ORB)")
+    out = np.zeros(len(query), KNN_DTYPE)
+    if len(query) == 0:
+        return out
+    check(_lib.lib().orb_hamming_knn(_vp(query), MEM_HOST, len(query), _vp(db) if len(db) else None, MEM_HOST, len(db),
+                                     index_base, sentinel, _vp(out), MEM_HOST, None))
+    return out
+
+
+def hamming_knn_device(query, db, out=None, index_base: int = 0, sentinel: int = 256, stream=None):
+    """torch CUDA tensors: query [Q,32] u8, db [D,32] u8 -> out [Q,3] int64 viewable as orb_knn2 (24 B records).
+    Asynchronous on `stream` (torch.cuda.Stream) or the current stream."""
+    import torch
+    assert query.is_cuda and db.is_cuda and query.dtype == torch.uint8 and db.dtype == torch.uint8
+    assert query.is_contiguous() and db.is_contiguous()
+    Q, D = query.shape[0], db.shape[0]
+    if out is None:
+        out = torch.empty((Q, 3), dtype=torch.int64, device=query.device)
+    st = (stream or torch.cuda.current_stream(query.device)).cuda_stream
+    check(_lib.lib().orb_hamming_knn(query.data_ptr(), MEM_DEVICE, Q, db.data_ptr(), MEM_DEVICE, D, index_base, sentinel,
+                                     out.data_ptr(), MEM_DEVICE, C.c_void_p(st)))
+    return out
+
+
+def knn_merge_device(shards, nshards: int, Q: int, out=None, sentinel: int = 256, stream=None):
+    """shards: torch int64 CUDA tensor [nshards, Q, 3] of orb_knn2 records in ascending shard order."""
+    import torch
+    if out is None:
+        out = torch.empty((Q, 3), dtype=torch.int64, device=shards.device)
+    st = (stream or torch.cuda.current_stream(shards.device)).cuda_stream
+    check(_lib.lib().orb_hamming_knn_merge(shards.data_ptr(), nshards, Q, sentinel, out.data_ptr(), C.c_void_p(st)))
+    return out
+
+
+def knn_records(t) -> np.ndarray:
+    """torch [Q,3] int64 (device or host) -> KNN_DTYPE[Q] numpy records."""
+    return t.detach().cpu().numpy().view(KNN_DTYPE).reshape(-1)
+
+
+def hamming_knn_sharded(query, db_shard, shard_base: int, group=None, sentinel: int = 256):
+    """Database sharded contiguously over the ranks of `group` (ascending rank = ascending rows):
+    local k=2 on this rank's shard, ONE all_gather of the per-query records, local top-2 merge.
+    Equals one sequential scan over the concatenated database (earliest global index wins ties).
+    query / db_shard: torch uint8 tensors on this rank's device (CUDA -> NCCL; the merge of CPU tensors
+    used by the gloo tests goes through `merge_records_host`)."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    if query.is_cuda:
+        local = hamming_knn_device(query, db_shard, index_base=shard_base, sentinel=sentinel)
+        gathered = torch.empty((world,) + tuple(local.shape), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(gathered, local, group=group)
+        return knn_merge_device(gathered, world, query.shape[0], sentinel=sentinel)
+    raise RuntimeError("hamming_knn_sharded needs CUDA tensors (there is no CPU fallback)")
+
+
+def merge_records_host(parts: list, sentinel: int = 256) -> np.ndarray:
+    """Host-side statement of the shard merge rule (the two lexicographically smallest (d, i) with d < sentinel)
+    for the gloo tests of the exchange logic; the product path merges on the device (orb_hamming_knn_merge)."""
+    Q = len(parts[0])
+    d = np.stack([np.stack([p["d1"], p["d2"]], 1) for p in parts], 1).reshape(Q, -1).astype(np.int64)
+    i = np.stack([np.stack([p["i1"], p["i2"]], 1) for p in parts], 1).reshape(Q, -1).astype(np.int64)
+    key = np.where((i < 0) | (d >= sentinel), np.iinfo(np.int64).max, (d << 40) | np.maximum(i, 0))
+    key.sort(axis=1)
+    out = np.zeros(Q, KNN_DTYPE)
+    big = np.iinfo(np.int64).max
+    a, b = key[:, 0], key[:, 1]
+    out["d1"] = np.where(a == big, sentinel, a >> 40)
+    out["i1"] = np.where(a == big, -1, a & ((1 << 40) - 1))
+    ok2 = (a != big) & (b != big)
+    out["d2"] = np.where(ok2, b >> 40, sentinel)
+    out["i2"] = np.where(ok2, b & ((1 << 40) - 1), -1)
+    return out
+
+
+class ORBmatcher:
+    """include/ORBmatcher.h: constructor (nnratio=0.6, checkOri=true) :54, TH_LOW/TH_HIGH/HISTO_LENGTH :223-225."""
+    TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30
+
+    def __init__(self, nnratio: float = 0.6, checkOri: bool = True):
+        self.mfNNratio = np.float32(nnratio)
+        self.mbCheckOrientation = checkOri
+
+    @staticmethod
+    def DescriptorDistance(a: np.ndarray, b: np.ndarray) -> int:
+        """src/ORBmatcher.cc:2073-2093 for one pair of 32-byte rows (computed on the GPU)."""
+        import torch
+        ta = torch.from_numpy(np.ascontiguousarray(a, np.uint8).reshape(1, 32)).cuda()
+        tb = torch.from_numpy(np.ascontiguousarray(b, np.uint8).reshape(1, 32)).cuda()
+        return int(ORBmatcher.DescriptorDistanceBatch(ta, tb)[0])
+
+    @staticmethod
+    def DescriptorDistanceBatch(a, b):
+        """n row pairs on the device: torch uint8 [n,32] x2 -> int32 [n]."""
+        import torch
+        assert a.is_cuda and b.is_cuda and a.shape == b.shape and a.is_contiguous() and b.is_contiguous()
+        out = torch.empty((a.shape[0],), dtype=torch.int32, device=a.device)
+        st = torch.cuda.current_stream(a.device).cuda_stream
+        check(_lib.lib().orb_descriptor_distance_batch(a.data_ptr(), b.data_ptr(), a.shape[0], out.data_ptr(), C.c_void_p(st)))
+        return out
+
+    def accept(self, knn: np.ndarray, th: int | None = None) -> np.ndarray:
+        """The accept test of src/ORBmatcher.cc:339-342: best <= TH_LOW and (float)best < mfNNratio*(float)second."""
+        th = self.TH_LOW if th is None else th
+        return (knn["d1"] <= th) & (knn["d1"].astype(np.float32) < self.mfNNratio * knn["d2"].astype(np.float32))
+
+    def match(self, query: np.ndarray, db: np.ndarray, th: int | None = None):
+        """Brute-force k=2 + ratio test. Returns (knn records, accept mask)."""
+        knn = hamming_knn(query, db)
+        return knn, self.accept(knn, th)

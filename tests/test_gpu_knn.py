@@ -1,0 +1,106 @@
+"""GPU parity of the matcher path: orb_hamming_knn / merge / distance batch vs the scalar oracle."""
+import numpy as np
+import pytest
+
+from orb_slam2_detailed_comments_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _eq(a, b):
+    for f in ("d1", "d2", "i1", "i2"):
+        assert np.array_equal(a[f], b[f]), f
+    
+
+@pytest.mark.parametrize("Q,D", [(1, 1), (7, 2), (300, 1000), (2000, 50000), (257, 255), (513, 70001)])
+def test_knn_matches_oracle(oracle, Q, D):
+    from orb_slam2_detailed_comments_b200 import hamming_knn
+    q, db = synth.synth_descriptors(Q, D, seed=Q + D)
+    _eq(hamming_knn(q, db), oracle.hamming_knn(q, db))
+
+
+def test_knn_edge_cases(oracle):
+    from orb_slam2_detailed_comments_b200 import hamming_knn
+    q, db = synth.synth_descriptors(50, 400, seed=5)
+    # empty database: everything stays at the sentinel
+    r = hamming_knn(q, db[:0])
+    assert (r["d1"] == 256).all() and (r["i1"] == -1).all() and (r["i2"] == -1).all()
+    # duplicates of the minimum: earliest index is best, duplicate becomes second
+    db2 = np.concatenate([db, db[:10], db[:10]])
+    _eq(hamming_knn(q, db2), oracle.hamming_knn(q, db2))
+    qq = db2[:20].copy()
+    r = hamming_knn(qq, db2)
+    assert (r["d1"][:10] == 0).all() and (r["d2"][:10] == 0).all()
+    assert np.array_equal(r["i1"][:10], np.arange(10)) and np.array_equal(r["i2"][:10], 400 + np.arange(10))
+    # all-ones vs all-zeros: distance 256 is never < 256 -> unset
+    r = hamming_knn(np.full((3, 32), 255, np.uint8), np.zeros((5, 32), np.uint8))
+    assert (r["d1"] == 256).all() and (r["i1"] == -1).all()
+    _eq(r, oracle.hamming_knn(np.full((3, 32), 255, np.uint8), np.zeros((5, 32), np.uint8)))
+    # INT_MAX sentinel (src/ORBmatcher.cc:611-612)
+    big = 2**31 - 1
+    _eq(hamming_knn(q, db, sentinel=big), oracle.hamming_knn(q, db, sentinel=big))
+    _eq(hamming_knn(np.full((3, 32), 255, np.uint8), np.zeros((5, 32), np.uint8), sentinel=big),
+        oracle.hamming_knn(np.full((3, 32), 255, np.uint8), np.zeros((5, 32), np.uint8), sentinel=big))
+    # index base (database shard offset)
+    _eq(hamming_knn(q, db, index_base=123456789), oracle.hamming_knn(q, db, index_base=123456789))
+
+
+def test_shard_merge_equals_single_scan(oracle):
+    import torch
+    from orb_slam2_detailed_comments_b200 import matcher
+    q, db = synth.synth_descriptors(700, 40000, seed=11)
+    db[30000:30050] = db[100:150]     # ties across shards
+    tq, tdb = torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda()
+    bounds = [0, 9000, 9000, 25001, 40000]   # includes an empty shard
+    parts = [matcher.hamming_knn_device(tq, tdb[a:b].contiguous() if b > a else tdb[:0], index_base=a)
+             for a, b in zip(bounds[:-1], bounds[1:])]
+    merged = matcher.knn_records(matcher.knn_merge_device(torch.stack(parts), len(parts), len(q)))
+    want = oracle.hamming_knn(q, db)
+    _eq(merged, want)
+    _eq(matcher.merge_records_host([matcher.knn_records(p) for p in parts]), want)
+
+
+def test_full_size_properties():
+    """C4 at full size (2000 x 1M): planted rows are found at the planted distance; best <= second;
+    results are identical across two different shardings (size-independent properties)."""
+    import torch
+    from orb_slam2_detailed_comments_b200 import matcher
+    rng = np.random.RandomState(1)
+    D, Q = 1_000_000, 2000
+    db = rng.randint(0, 256, (D, 32), dtype=np.uint8)
+    rows = rng.randint(0, D, Q)
+    q = db[rows].copy()
+    flips = rng.randint(0, 30, Q)
+    for i in range(Q):
+        for b in rng.choice(256, flips[i], replace=False):
+            q[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    tq, tdb = torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda()
+    full = matcher.knn_records(matcher.hamming_knn_device(tq, tdb))
+    assert np.array_equal(full["d1"], flips) and np.array_equal(full["i1"], rows)
+    assert (full["d1"] <= full["d2"]).all() and (full["i1"] != full["i2"]).all()
+    parts = [matcher.hamming_knn_device(tq, tdb[a:a + 125000], index_base=a) for a in range(0, D, 125000)]
+    merged = matcher.knn_records(matcher.knn_merge_device(torch.stack(parts), 8, Q))
+    _eq(merged, full)
+
+
+def test_descriptor_distance(oracle):
+    import torch
+    from orb_slam2_detailed_comments_b200 import ORBmatcher
+    rng = np.random.RandomState(2)
+    a = rng.randint(0, 256, (1000, 32), dtype=np.uint8)
+    b = rng.randint(0, 256, (1000, 32), dtype=np.uint8)
+    got = ORBmatcher.DescriptorDistanceBatch(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()).cpu().numpy()
+    want = np.array([oracle.descriptor_distance(a[i], b[i]) for i in range(1000)])
+    assert np.array_equal(got, want)
+    assert ORBmatcher.DescriptorDistance(a[0], a[0]) == 0
+    assert ORBmatcher.DescriptorDistance(np.zeros(32, np.uint8), np.full(32, 255, np.uint8)) == 256
+
+
+def test_ratio_accept(oracle):
+    from orb_slam2_detailed_comments_b200 import ORBmatcher
+    q, db = synth.synth_descriptors(500, 20000, seed=21)
+    m = ORBmatcher(0.6)
+    knn, acc = m.match(q, db)
+    ref = oracle.hamming_knn(q, db)
+    want = (ref["d1"] <= 50) & (ref["d1"].astype(np.float32) < np.float32(0.6) * ref["d2"].astype(np.float32))
+    assert np.array_equal(acc, want) and acc.sum() > 10
