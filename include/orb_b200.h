@@ -114,6 +114,13 @@ int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keyp
  * launched by this handle so far. */
 void* orb_extractor_stream(orb_extractor* e);
 int64_t orb_extractor_launch_count(const orb_extractor* e);
+/* Per-stage device timing: CUDA events recorded on the handle's stream around each stage of every internal pass and
+ * resolved lazily by stage_times (no synchronisation inside the pass). Off by default. Stages: 0 pyramid, 1 FAST cells, 2 blur, 3 quadtree,
+ * 4 orientation+descriptor+output. set_profiling resets the accumulators; stage_times returns the stage count,
+ * fills ms[ORB_NUM_STAGES] (sum over passes) and *passes (internal passes = kernel launches per stage). */
+#define ORB_NUM_STAGES 5
+int orb_extractor_set_profiling(orb_extractor* e, int on);
+int orb_extractor_stage_times(orb_extractor* e, double* ms, int64_t* passes);
 
 /* ---- matcher ------------------------------------------------------------------------------- */
 /* Brute-force k=2 over 256-bit descriptors with the reference update rule (strict <: earliest index wins,

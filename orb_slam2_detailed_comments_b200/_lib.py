@@ -30,7 +30,8 @@ SYMBOLS = [
     "orb_extractor_get_levels", "orb_extractor_get_scale_factor", "orb_extractor_get_table",
     "orb_extractor_get_features_per_level", "orb_extractor_max_keypoints", "orb_extract_batch",
     "orb_extract_batch_device", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
-    "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count", "orb_hamming_knn",
+    "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
+    "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_matcher_launch_count", "orb_measure_popc_peak",
 ]
 
@@ -81,6 +82,8 @@ def lib():
     L.orb_extractor_stream.restype = vp
     L.orb_extractor_launch_count.argtypes = [vp]
     L.orb_extractor_launch_count.restype = i64
+    L.orb_extractor_set_profiling.argtypes = [vp, i32]
+    L.orb_extractor_stage_times.argtypes = [vp, vp, vp]
     L.orb_hamming_knn.argtypes = [vp, i32, i32, vp, i32, i64, i64, i32, vp, i32, vp]
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]

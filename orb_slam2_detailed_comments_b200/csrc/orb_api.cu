@@ -78,6 +78,11 @@ struct orb_extractor {
   DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
   int* h_err = nullptr;    // pinned
   int* h_cnt = nullptr;    // pinned [chunk * (1 + nlevels)]
+  bool profile = false;    // per-stage CUDA-event timing (orb_extractor_set_profiling)
+  std::vector<cudaEvent_t> ev;   // (ORB_NUM_STAGES + 1) events per profiled pass, resolved lazily (no sync in the pass)
+  size_t ev_used = 0;
+  double stage_ms[ORB_NUM_STAGES] = {};
+  long long stage_passes = 0;
   std::mutex mu;
 };
 
@@ -254,14 +259,44 @@ static void run_pass(orb_extractor* e, const uint8_t* images, int step, long lon
   S.best = e->q_best.as<unsigned>(); S.ordA = e->q_ordA.as<int>(); S.ordB = e->q_ordB.as<int>(); S.par = e->q_par.as<int>();
   S.cand = e->q_cand.as<unsigned long long>(); S.ccnt = e->q_ccnt.as<int>(); S.cslot = e->q_cslot.as<int>();
   S.scan = e->q_scan.as<unsigned long long>(); S.raw_n = e->q_rawn.as<int>();
+  bool prof = e->profile;
+  cudaEvent_t* ev = nullptr;
+  if (prof) {
+    if (e->ev_used + ORB_NUM_STAGES + 1 > e->ev.size()) {
+      const size_t old = e->ev.size();
+      e->ev.resize(old + 64 * (ORB_NUM_STAGES + 1), nullptr);
+      for (size_t i = old; i < e->ev.size(); ++i)
+        if (cudaEventCreate(&e->ev[i]) != cudaSuccess) { e->ev.resize(old); prof = false; break; }
+    }
+    if (prof) { ev = e->ev.data() + e->ev_used; e->ev_used += ORB_NUM_STAGES + 1; }
+  }
+  if (prof) cudaEventRecord(ev[0], st);
   orb_launch_pyramid(images, step, image_stride, e->pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches);
+  if (prof) cudaEventRecord(ev[1], st);
   orb_launch_fast(e->pyr.as<uint8_t>(), e->cell_cnt.as<int>(), e->cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
+  if (prof) cudaEventRecord(ev[2], st);
   orb_launch_blur(e->pyr.as<uint8_t>(), e->blr.as<uint8_t>(), g, n, st, &e->launches);
+  if (prof) cudaEventRecord(ev[3], st);
   orb_launch_quadtree(e->cell_cnt.as<int>(), e->cell_kp.as<uint32_t>(), S, e->kept.as<uint32_t>(), e->kept_cnt.as<int>(),
                       e->err.as<int>(), g, n, st, &e->launches);
+  if (prof) cudaEventRecord(ev[4], st);
   orb_launch_describe(e->pyr.as<uint8_t>(), e->blr.as<uint8_t>(), e->kept.as<uint32_t>(), e->kept_cnt.as<int>(), kps, desc, cap,
                       counts_dev, e->err.as<int>(), g, n, st, &e->launches);
+  if (prof) cudaEventRecord(ev[5], st);
   e->last_batch = n;
+}
+
+static void resolve_stage_events(orb_extractor* e) {
+  if (e->ev_used == 0) return;
+  cudaStreamSynchronize(e->stream);
+  for (size_t b = 0; b + ORB_NUM_STAGES < e->ev_used; b += ORB_NUM_STAGES + 1) {
+    for (int i = 0; i < ORB_NUM_STAGES; ++i) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, e->ev[b + i], e->ev[b + i + 1]) == cudaSuccess) e->stage_ms[i] += ms;
+    }
+    ++e->stage_passes;
+  }
+  e->ev_used = 0;
 }
 
 static int check_err_flag(orb_extractor* e) {
@@ -319,6 +354,8 @@ void orb_extractor_destroy(orb_extractor* e) {
                     &e->q_ordA, &e->q_ordB, &e->q_par, &e->q_cand, &e->q_ccnt, &e->q_cslot, &e->q_scan, &e->q_rawn};
   for (DevBuf* b : bufs) b->release();
   if (e->h_cnt) cudaFreeHost(e->h_cnt);
+  for (cudaEvent_t ev : e->ev)
+    if (ev) cudaEventDestroy(ev);
   delete e;
 }
 
@@ -341,6 +378,27 @@ int orb_extractor_max_keypoints(const orb_extractor* e) {
   return e->prm.nfeatures + 16 * e->prm.nlevels;
 }
 void* orb_extractor_stream(orb_extractor* e) { return e ? (void*)e->stream : nullptr; }
+
+int orb_extractor_set_profiling(orb_extractor* e, int on) {
+  if (!e) return fail(ORB_E_BADARG, "null argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  CU(cudaSetDevice(e->device));
+  resolve_stage_events(e);
+  e->profile = on != 0;
+  for (int i = 0; i < ORB_NUM_STAGES; ++i) e->stage_ms[i] = 0.0;
+  e->stage_passes = 0;
+  return ORB_OK;
+}
+
+int orb_extractor_stage_times(orb_extractor* e, double* ms, int64_t* passes) {
+  if (!e || !ms) return fail(ORB_E_BADARG, "null argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  CU(cudaSetDevice(e->device));
+  resolve_stage_events(e);
+  for (int i = 0; i < ORB_NUM_STAGES; ++i) ms[i] = e->stage_ms[i];
+  if (passes) *passes = e->stage_passes;
+  return ORB_NUM_STAGES;
+}
 int64_t orb_extractor_launch_count(const orb_extractor* e) { return e ? e->launches : 0; }
 
 int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, int width, int height, int batch,
@@ -378,9 +436,16 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
   if ((rc = e->stage_in.ensure((size_t)e->chunk * spitch * height)) != ORB_OK) return rc;
   for (int f0 = 0; f0 < batch; f0 += e->chunk) {
     const int n = std::min(e->chunk, batch - f0);
-    for (int i = 0; i < n; ++i)
-      CU(cudaMemcpy2DAsync(e->stage_in.as<uint8_t>() + (size_t)i * spitch * height, spitch, images[f0 + i], step, width, height,
-                           in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, e->stream));
+    const cudaMemcpyKind kin = in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    bool contiguous = true;   // frames back to back with the same pitch -> one 2-D copy for the whole pass
+    for (int i = 1; i < n && contiguous; ++i) contiguous = images[f0 + i] == images[f0] + (size_t)i * step * height;
+    if (contiguous) {
+      CU(cudaMemcpy2DAsync(e->stage_in.p, spitch, images[f0], step, width, (size_t)height * n, kin, e->stream));
+    } else {
+      for (int i = 0; i < n; ++i)
+        CU(cudaMemcpy2DAsync(e->stage_in.as<uint8_t>() + (size_t)i * spitch * height, spitch, images[f0 + i], step, width, height, kin,
+                             e->stream));
+    }
     OrbKeypoint* dk = out_mem == ORB_MEM_DEVICE ? reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap : e->out_kps.as<OrbKeypoint>();
     uint8_t* dd = out_mem == ORB_MEM_DEVICE ? desc + (long long)f0 * cap * 32 : e->out_desc.as<uint8_t>();
     run_pass(e, e->stage_in.as<uint8_t>(), spitch, (long long)spitch * height, n, dk, dd, cap, e->out_cnt.as<int>());

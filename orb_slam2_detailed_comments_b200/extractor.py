@@ -69,6 +69,18 @@ class ORBextractor:
     def launch_count(self) -> int:
         return self._L.orb_extractor_launch_count(self._h)
 
+    STAGES = ("pyramid", "fast_cells", "blur", "quadtree", "describe")
+
+    def set_profiling(self, on: bool):
+        check(self._L.orb_extractor_set_profiling(self._h, int(on)))
+
+    def stage_times(self):
+        """({stage: summed ms}, internal passes) since set_profiling(True)."""
+        ms = (C.c_double * 8)()
+        passes = C.c_int64()
+        n = check(self._L.orb_extractor_stage_times(self._h, ms, C.byref(passes)))
+        return {self.STAGES[i]: ms[i] for i in range(n)}, passes.value
+
     # ---- operator(), include/ORBextractor.h:122-126 ----
     def __call__(self, image: np.ndarray, mask=None):
         """Returns (keypoints[N] structured cv::KeyPoint records, descriptors[N,32] u8). `mask` is ignored
