@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""Benchmark of the ORB front-end hot path on B200 (contract: see the task statement / DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload kitti|tum|euroc|4k]
+
+One "step" = ORBextractor::operator() over one batch of synthetic frames (default: BASELINE.json configs[1],
+KITTI-shaped 1241x376 stereo pairs, nFeatures 2000, left+right images batched on the GPU). Metric = images
+(frames) per second, whole job. `value` is measured with the frames resident in HBM; `e2e` goes through the
+reference-facing host API (orb_extract_batch) with pinned HOST buffers, H2D and D2H inside the timed region.
+A secondary object `knn` reports the ORBmatcher path (config C4: 2000 queries x 1M database rows, k=2).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from orb_slam2_detailed_comments_b200 import geometry, synth  # noqa: E402
+
+METRIC = "ORB frames/sec (extract+describe)"
+UNIT = "images/s"
+WORKLOADS = {
+    # name: (config label, width, height, nFeatures, images per step per GPU)
+    "kitti": ("KITTI-shaped 1241x376 stereo pairs, nFeatures=2000, 8 levels, scale 1.2, FAST 20/7, L+R batched", 1241, 376, 2000, 512),
+    "tum": ("TUM-shaped 640x480 mono, nFeatures=1000, 8 levels, scale 1.2, FAST 20/7", 640, 480, 1000, 1024),
+    "euroc": ("EuRoC-shaped 752x480 stereo, nFeatures=1200, 256 frame pairs per GPU", 752, 480, 1200, 512),
+    "4k": ("4K 3840x2160, nFeatures=8000, 8 levels", 3840, 2160, 8000, 16),
+}
+KNN_Q, KNN_D = 2000, 1_000_000
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self) -> dict:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ---- CPU legs (the only place bench.py executes oracle/: cpu_baseline and --impl reference) ------------------
+def _host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_extract_rate(width, height, nf, n_images, threads, seed0=4321):
+    """Oracle (CPU restatement of the reference, kind "port") over `n_images` frames, one extractor per thread."""
+    from oracle import oracle_py
+    frames = synth.synth_batch(width, height, n_images, seed0=seed0, distinct=min(8, n_images))
+    oracle_py.extract_many(frames[:min(threads, n_images)], nf, threads)   # warm: page in, spawn
+    t0 = time.perf_counter()
+    total = oracle_py.extract_many(frames, nf, threads)
+    dt = time.perf_counter() - t0
+    return n_images / dt, dt, int(total)
+
+
+def cpu_knn_rate(threads, q_n=256, d_n=200_000):
+    from oracle import oracle_py
+    q, db = synth.synth_descriptors(q_n, d_n, seed=7)
+    t0 = time.perf_counter()
+    oracle_py.hamming_knn(q, db, nthreads=threads)
+    dt = time.perf_counter() - t0
+    return q_n * d_n / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference itself cannot be compiled here)
+    on all host cores, same config/metric/unit. Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    label, W, H, nf, _ = WORKLOADS[args.workload]
+    cores = _host_cores()
+    from oracle import oracle_py
+    n = max(2 * cores, 16)   # images per step: a bounded sample of the workload
+    frames = synth.synth_batch(W, H, n, seed0=4321, distinct=min(8, n))
+    for _ in range(args.warmup):
+        oracle_py.extract_many(frames, nf, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle_py.extract_many(frames, nf, cores)
+    dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": label, "images_per_step": n, "timing": "host wall clock"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{n} images per step x {args.steps} steps, one oracle extractor per thread"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- GPU arm ---------------------------------------------------------------------------------------------
+def _dist_setup(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def _barrier(world):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_over_ranks(x: float, world: int) -> float:
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def bench_extract_resident(ex, frames_dev, steps, warmup, world):
+    """`value`: frames already in HBM, outputs left in HBM; timed with CUDA events on the extractor's stream."""
+    import torch
+    st = torch.cuda.ExternalStream(ex._L.orb_extractor_stream(ex._h))
+    kps, desc, counts = ex.extract_batch_device(frames_dev, sync=True)
+    for _ in range(warmup):
+        ex.extract_batch_device(frames_dev, kps, desc, counts, sync=False)
+    torch.cuda.synchronize()
+    ex.set_profiling(True)
+    l0 = ex.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world)
+    e0.record(st)
+    for _ in range(steps):
+        ex.extract_batch_device(frames_dev, kps, desc, counts, sync=False)
+    e1.record(st)
+    e1.synchronize()
+    _barrier(world)
+    ms = _max_over_ranks(e0.elapsed_time(e1), world)
+    launches = ex.launch_count - l0
+    stage_ms, passes = ex.stage_times()
+    ex.set_profiling(False)
+    return ms, launches, stage_ms, passes, int(counts.sum().item())
+
+
+def bench_extract_e2e(ex, frames_host, steps, warmup, world):
+    """`e2e`: orb_extract_batch with pinned HOST frames in, HOST keypoints/descriptors out (copies inside the call)."""
+    import torch
+    B, H, W = frames_host.shape
+    cap = ex.max_keypoints()
+    pin_in = torch.from_numpy(frames_host).pin_memory()
+    pin_k = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    pin_d = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    from orb_slam2_detailed_comments_b200 import KP_DTYPE
+    k_np = pin_k.numpy().view(KP_DTYPE).reshape(B, cap)
+    out = (k_np, pin_d.numpy())
+    src = pin_in.numpy()
+    for _ in range(max(warmup, 1)):
+        ex.extract_batch(src, out=out)
+    _barrier(world)
+    t0 = time.perf_counter()
+    nk = 0
+    for _ in range(steps):
+        _, _, counts, _ = ex.extract_batch(src, out=out)
+        nk += int(counts.sum())
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    _barrier(world)
+    ms = _max_over_ranks(dt * 1e3, world)
+    h2d = B * H * W
+    d2h = B * cap * 60 + B * 4 * (1 + ex.nlevels)
+    return ms, h2d, d2h, nk
+
+
+def bench_knn(rank, world, steps, warmup):
+    """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks, one all_gather
+    of the per-query records + device merge when world > 1. pairs/s = Q*D / time (max over ranks)."""
+    import torch
+    from orb_slam2_detailed_comments_b200 import _lib, matcher
+    rng = np.random.RandomState(7)
+    per = KNN_D // world
+    base = rank * per
+    q = torch.from_numpy(rng.randint(0, 256, (KNN_Q, 32), dtype=np.uint8)).cuda()
+    gdb = torch.Generator(device="cuda").manual_seed(100 + rank)
+    db = torch.randint(0, 256, (per, 32), dtype=torch.uint8, device="cuda", generator=gdb)
+    out = torch.empty((KNN_Q, 3), dtype=torch.int64, device="cuda")
+    gathered = torch.empty((world, KNN_Q, 3), dtype=torch.int64, device="cuda") if world > 1 else None
+
+    def step():
+        matcher.hamming_knn_device(q, db, out=out, index_base=base)
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(gathered, out)
+            matcher.knn_merge_device(gathered, world, KNN_Q, out=out)
+
+    for _ in range(max(warmup, 3)):
+        step()
+    l0 = _lib.lib().orb_matcher_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    e1.synchronize()
+    _barrier(world)
+    ms = _max_over_ranks(e0.elapsed_time(e1), world)
+    launches = _lib.lib().orb_matcher_launch_count() - l0
+    pairs = KNN_Q * per * world * steps
+    return pairs / (ms * 1e-3), ms / steps, launches
+
+
+def run_b200(args):
+    import torch
+    import orb_slam2_detailed_comments_b200 as pkg
+    if not torch.cuda.is_available() or pkg.lib().orb_device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    rank, world, local = _dist_setup(args)
+    label, W, H, nf, B = WORKLOADS[args.workload]
+    if args.batch:
+        B = args.batch
+    frames = synth.synth_batch(W, H, B, seed0=1234 + 100000 * rank, distinct=8)
+    ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, device=local)
+    frames_dev = torch.from_numpy(frames).cuda()
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, launches, stage_ms, passes, nkp = bench_extract_resident(ex, frames_dev, args.steps, args.warmup, world)
+    clocks = sampler.stop() if sampler else {}
+    value = B * world * args.steps / (ms * 1e-3)
+
+    e_steps = max(1, min(args.steps, 5))
+    e_ms, h2d, d2h, _ = bench_extract_e2e(ex, frames, e_steps, args.warmup, world)
+    e2e_value = B * world * e_steps / (e_ms * 1e-3)
+
+    knn_rate, knn_ms, knn_launches = bench_knn(rank, world, max(args.steps, 5), args.warmup)
+    popc_peak = pkg.lib().orb_measure_popc_peak(local) if rank == 0 else 0.0
+
+    if rank != 0:
+        return
+    peak, peak_src = _peaks()
+    A = geometry.algorithmic_bytes(W, H, nf)
+    sb = geometry.stage_bytes(W, H, nf)
+    per_rank_rate = value / world
+    total_stage = sum(stage_ms.values()) or 1.0
+    dom = max(stage_ms, key=stage_ms.get)
+    n_launch_dom = passes * (8 if dom == "pyramid" else 1)
+    frames_per_launch = B * args.steps / max(passes, 1)
+    dom_ms = stage_ms[dom] / max(passes, 1)                       # per internal pass (pyramid: its 8 launches together)
+    dom_bytes = sb[dom] * frames_per_launch
+    dom_achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    roofline = {
+        "bound": "hbm", "kernel": dom, "achieved": dom_achieved, "peak": peak, "unit": "GB/s",
+        "frac": dom_achieved / peak, "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": dom_bytes, "avg_launch_ms": dom_ms, "launches": n_launch_dom,
+        "share_of_step": stage_ms[dom] / total_stage,
+        "pipeline": {"algorithmic_bytes_per_image": A, "achieved": per_rank_rate * A / 1e9, "frac": per_rank_rate * A / 1e9 / peak},
+        "stages_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
+    }
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": label, "images_per_step_per_gpu": B, "width": W, "height": H, "nfeatures": nf,
+                   "l2": "inputs larger than L2 (%.0f MB of frames per step, +pyramid workspaces)" % (B * W * H / 1e6),
+                   "keypoints_per_image": nkp / B, "parallelism": f"frames sharded over {world} GPU(s), no collective"},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e_steps, "ms_per_step": e_ms / e_steps, "api": "orb_extract_batch (pinned host in/out)"},
+        "gpu_launches": int(launches),
+        "roofline": roofline,
+        "knn": {"metric": "Hamming matches/sec (k=2 brute force)", "value": knn_rate, "unit": "pairs/s",
+                "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
+                          + (", NCCL all_gather + device top-2 merge" if world > 1 else ""),
+                "ms_per_step": knn_ms, "gpu_launches": int(knn_launches),
+                "roofline": {"bound": "popc", "achieved": knn_rate * 8 / world, "peak": popc_peak, "unit": "popc.b32/s",
+                             "frac": (knn_rate * 8 / world / popc_peak) if popc_peak else None}},
+    }
+    if world == 1 and not args.no_cpu:
+        cores = _host_cores()
+        n = int(min(max(4 * cores, 64), 512))
+        v, dt, _ = cpu_extract_rate(W, H, nf, n, cores)
+        kv, kdt = cpu_knn_rate(cores)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{n} images of the same workload, one oracle extractor per thread, {dt:.1f} s wall",
+                                "knn_pairs_per_s": kv}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="kitti", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="images per step per GPU (default: per workload)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
