@@ -7,15 +7,18 @@ __constant__ int8_t c_pattern[256 * 4] = {
 };
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};  // :866-910
 
-// ---- 7x7 sigma-2 Gaussian, OpenCV 8-bit fixed-point path: taps 8.8, row pass -> u16, column pass -> u32,
-// out = (c + 32768) >> 16, BORDER_REFLECT_101 at the border of the PADDED level (this fork blurs the padded image).
-#define BL_TW 64
+// ---- 7x7 sigma-2 Gaussian, OpenCV 8-bit fixed-point path (taps 8.8): out = (sum_ij k_i k_j p_ij + 32768) >> 16,
+// BORDER_REFLECT_101 at the border of the PADDED level (this fork blurs the padded image). All intermediate sums are exact
+// integers (row sums <= 257*255 fit 16 bits), so the order of the two passes is free. CTA tile = 128 x 32 output pixels:
+//   H pass: one thread = 4 adjacent pixels of one of the 38 input rows, read straight from global (3 words), bytes widened
+//           to 16-bit lane pairs [p(a), p(a+2)] so that one 32-bit IMAD does two taps -> u16 row sums in shared memory;
+//   V pass: one thread = 4 pixels x 4 output rows from 10 staged rows, 32-bit accumulators, one 32-bit store per row.
+#define BL_TW 128
 #define BL_TH 32
+template <bool CLAMP>   // CLAMP: tap sum > 256 (legacy taps sum to 257): saturate like OpenCV's ufixedpoint -> u8 cast
 __global__ void __launch_bounds__(256) orb_blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
                                                        const __grid_constant__ OrbGeom g) {
-  __shared__ uint8_t s_in[BL_TH + 6][BL_TW + 8];
-  __shared__ uint16_t s_row[BL_TH + 6][BL_TW];
-  // blockIdx.y = tile index over all levels (table walk), blockIdx.z = frame
+  __shared__ uint2 s_h[BL_TH + 6][BL_TW / 4];   // per pixel quad: .x = [h0, h2], .y = [h1, h3] (16-bit lanes)
   int level = 0, t = blockIdx.x;
   for (; level < g.nlevels; ++level) {
     const int tx = (g.lv[level].cols + BL_TW - 1) / BL_TW, ty = (g.lv[level].rows + BL_TH - 1) / BL_TH;
@@ -25,30 +28,68 @@ __global__ void __launch_bounds__(256) orb_blur_kernel(const uint8_t* __restrict
   if (level >= g.nlevels) return;
   const OrbLevel& L = g.lv[level];
   const int tiles_x = (L.cols + BL_TW - 1) / BL_TW;
-  const int x0 = (t % tiles_x) * BL_TW, y0 = (t / tiles_x) * BL_TH;
-  const unsigned long long off = (unsigned long long)blockIdx.z * g.frame_stride + L.plane_off;
+  const int ty_ = t / tiles_x;
+  const int x0 = (t - ty_ * tiles_x) * BL_TW, y0 = ty_ * BL_TH;
+  const unsigned long long off = (unsigned long long)blockIdx.y * g.frame_stride + L.plane_off;
   const uint8_t* src = pyr + off;
-  for (int i = threadIdx.x; i < (BL_TH + 6) * (BL_TW + 6); i += 256) {
-    const int ly = i / (BL_TW + 6), lx = i - ly * (BL_TW + 6);
-    const int sx = orb_reflect101(min(x0 + lx - 3, L.cols + 2), L.cols), sy = orb_reflect101(min(y0 + ly - 3, L.rows + 2), L.rows);
-    s_in[ly][lx] = src[(long long)sy * L.pitch + sx];
+  const unsigned k0 = g.blur_taps[0], k1 = g.blur_taps[1], k2 = g.blur_taps[2], k3 = g.blur_taps[3];
+  for (int i = threadIdx.x; i < (BL_TH + 6) * (BL_TW / 4); i += 256) {
+    const int ly = i >> 5, q = i & 31;
+    const int x = x0 + 4 * q;
+    const int sy = orb_reflect101(min(y0 + ly - 3, L.rows + 2), L.rows);
+    const uint8_t* row = src + (long long)sy * L.pitch;
+    unsigned c0, c1, c2;
+    if (x >= 4 && x + 8 <= L.cols) {
+      c0 = *reinterpret_cast<const unsigned*>(row + x - 4);
+      c1 = *reinterpret_cast<const unsigned*>(row + x);
+      c2 = *reinterpret_cast<const unsigned*>(row + x + 4);
+    } else {
+      c0 = c1 = c2 = 0;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        c0 |= (unsigned)row[orb_reflect101(min(x - 4 + b, L.cols + 2), L.cols)] << (8 * b);
+        c1 |= (unsigned)row[orb_reflect101(min(x + b, L.cols + 2), L.cols)] << (8 * b);
+        c2 |= (unsigned)row[orb_reflect101(min(x + 4 + b, L.cols + 2), L.cols)] << (8 * b);
+      }
+    }
+    // W(a) = bytes B[a..a+3] of the 12 loaded bytes B[0..11] = pixels x-4 .. x+7
+    const unsigned w1 = __byte_perm(c0, c1, 0x4321), w3 = __byte_perm(c0, c1, 0x6543), w5 = __byte_perm(c1, c2, 0x4321),
+                   w7 = __byte_perm(c1, c2, 0x6543);
+    // P(a) = [B[a], B[a+2]] as 16-bit lanes
+    const unsigned p1 = __byte_perm(w1, 0, 0x4240), p2 = __byte_perm(w1, 0, 0x4341), p3 = __byte_perm(w3, 0, 0x4240),
+                   p4 = __byte_perm(w3, 0, 0x4341), p5 = __byte_perm(w5, 0, 0x4240), p6 = __byte_perm(w5, 0, 0x4341),
+                   p7 = __byte_perm(w7, 0, 0x4240), p8 = __byte_perm(w7, 0, 0x4341);
+    uint2 h;
+    h.x = k0 * (p1 + p7) + k1 * (p2 + p6) + k2 * (p3 + p5) + k3 * p4;   // [h(x), h(x+2)]
+    h.y = k0 * (p2 + p8) + k1 * (p3 + p7) + k2 * (p4 + p6) + k3 * p5;   // [h(x+1), h(x+3)]
+    s_h[ly][q] = h;
   }
   __syncthreads();
-  const int k0 = g.blur_taps[0], k1 = g.blur_taps[1], k2 = g.blur_taps[2], k3 = g.blur_taps[3];
-  for (int i = threadIdx.x; i < (BL_TH + 6) * BL_TW; i += 256) {
-    const int ly = i / BL_TW, lx = i - ly * BL_TW;
-    const uint8_t* p = &s_in[ly][lx];
-    s_row[ly][lx] = (uint16_t)(k0 * (p[0] + p[6]) + k1 * (p[1] + p[5]) + k2 * (p[2] + p[4]) + k3 * p[3]);
+  const int q = threadIdx.x & 31, seg = threadIdx.x >> 5;
+  const int x = x0 + 4 * q;
+  if (x >= L.cols) return;
+  unsigned v[10][4];
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint2 h = s_h[4 * seg + r][q];
+    v[r][0] = h.x & 0xffffu; v[r][2] = h.x >> 16; v[r][1] = h.y & 0xffffu; v[r][3] = h.y >> 16;
   }
-  __syncthreads();
   uint8_t* dst = blr + off;
-  for (int i = threadIdx.x; i < BL_TH * BL_TW; i += 256) {
-    const int ly = i / BL_TW, lx = i - ly * BL_TW;
-    const int x = x0 + lx, y = y0 + ly;
-    if (x < L.cols && y < L.rows) {
-      const uint32_t c = k0 * ((uint32_t)s_row[ly][lx] + s_row[ly + 6][lx]) + k1 * ((uint32_t)s_row[ly + 1][lx] + s_row[ly + 5][lx]) +
-                         k2 * ((uint32_t)s_row[ly + 2][lx] + s_row[ly + 4][lx]) + k3 * (uint32_t)s_row[ly + 3][lx];
-      dst[(long long)y * L.pitch + x] = (uint8_t)min((c + 32768u) >> 16, 255u);
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int y = y0 + 4 * seg + r;
+    if (y < L.rows) {
+      unsigned c[4];
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+        c[p] = k0 * (v[r][p] + v[r + 6][p]) + k1 * (v[r + 1][p] + v[r + 5][p]) + k2 * (v[r + 2][p] + v[r + 4][p]) + k3 * v[r + 3][p] + 32768u;
+      if (CLAMP) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) c[p] = min(c[p], 0xffffffu);
+      }
+      // byte 2 of each accumulator is the output pixel
+      const unsigned lo = __byte_perm(c[0], c[1], 0x0062), hi = __byte_perm(c[2], c[3], 0x0062);
+      *reinterpret_cast<unsigned*>(dst + (long long)y * L.pitch + x) = __byte_perm(lo, hi, 0x5410);
     }
   }
 }
@@ -188,7 +229,10 @@ void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const OrbGeom& g, int bat
   int tiles = 0;
   for (int l = 0; l < g.nlevels; ++l)
     tiles += ((g.lv[l].cols + BL_TW - 1) / BL_TW) * ((g.lv[l].rows + BL_TH - 1) / BL_TH);
-  orb_blur_kernel<<<dim3(tiles, 1, batch), 256, 0, st>>>(pyr, blr, g);
+  int sum = g.blur_taps[3];
+  for (int i = 0; i < 3; ++i) sum += 2 * g.blur_taps[i];
+  if (sum > 256) orb_blur_kernel<true><<<dim3(tiles, batch), 256, 0, st>>>(pyr, blr, g);
+  else orb_blur_kernel<false><<<dim3(tiles, batch), 256, 0, st>>>(pyr, blr, g);
   ++*launches;
 }
 

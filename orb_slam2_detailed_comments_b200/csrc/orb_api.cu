@@ -108,19 +108,20 @@ static void build_tables(orb_extractor* e) {
   e->quota[nl - 1] = std::max(e->prm.nfeatures - sum, 0);
 }
 
-// cv::resize INTER_LINEAR coefficient table for one axis (ssz -> dsz), 11-bit fixed point.
-static void resize_table(int ssz, int dsz, ResizeTab* out) {
+// cv::resize INTER_LINEAR coefficient table for one axis (ssz -> dsz interior pixels), 11-bit fixed point, laid out in
+// PADDED destination coordinates: entry p describes interior pixel reflect101(p - 19) (the in-place copyMakeBorder of
+// src/ORBextractor.cc:2138 is an index remap of the interior). `len` >= dsz + 38 entries are written.
+static void resize_table(int ssz, int dsz, int len, ResizeTab* out) {
   const double scale = 1.0 / ((double)dsz / ssz);
-  for (int d = 0; d < dsz; ++d) {
+  for (int p = 0; p < len; ++p) {
+    const int d = orb_reflect101(std::min(p, dsz + 2 * ORB_EDGE - 1) - ORB_EDGE, dsz);
     float f = (float)((d + 0.5) * scale - 0.5);
     int s = (int)floorf(f);
     f -= s;
     if (s < 0) { s = 0; f = 0.f; }
     if (s >= ssz - 1) { s = ssz - 1; f = 0.f; }
-    out[d].ofs = (short)s;
-    out[d].c0 = (short)cv_round_f((1.f - f) * 2048.f);
-    out[d].c1 = (short)cv_round_f(f * 2048.f);
-    out[d].pad = 0;
+    out[p].ofs = s;
+    out[p].coef = (unsigned)cv_round_f((1.f - f) * 2048.f) | ((unsigned)cv_round_f(f * 2048.f) << 16);
   }
 }
 
@@ -136,7 +137,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
   static const int taps_new[7] = {18, 34, 48, 56, 48, 34, 18}, taps_old[7] = {18, 34, 49, 55, 49, 34, 18};
   memcpy(g.blur_taps, (e->prm.flags & ORB_FLAG_LEGACY_BLUR) ? taps_old : taps_new, sizeof(g.blur_taps));
   size_t plane = 0;
-  int cells = 0, raw = 0, nodes = 0, tab = 0;
+  int cells = 0, raw = 0, nodes = 0, tab = 0, ftiles = 0;
   tabs.clear();
   for (int l = 0; l < nl; ++l) {
     OrbLevel& L = g.lv[l];
@@ -157,6 +158,10 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
       return fail(ORB_E_SHAPE, "level %d exceeds the 4095-px packed coordinate range", l);
     L.cell_base = cells;
     cells += L.nCols * L.nRows;
+    L.fast_G = std::max(1, ORB_FAST_TILE_W / L.wCell);
+    L.fast_nseg = (L.nCols + L.fast_G - 1) / L.fast_G;
+    L.fast_tile_base = ftiles;
+    ftiles += L.fast_nseg * L.nRows;
     L.nIni = (int)roundf((float)(L.maxBX - ORB_MIN_BORDER) / (L.maxBY - ORB_MIN_BORDER));
     if (L.nIni < 1) return fail(ORB_E_SHAPE, "aspect ratio < 0.5: the reference divides by nIni == 0 (src/ORBextractor.cc:1059)");
     L.hX = (float)(L.maxBX - ORB_MIN_BORDER) / L.nIni;
@@ -172,13 +177,23 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.tab_off = tab;
     if (l > 0) {
       const OrbLevel& P = g.lv[l - 1];
-      tabs.resize(tab + L.iw + L.ih);
-      resize_table(P.cols, L.iw, tabs.data() + tab);          // source = PADDED level l-1 (this fork, :2119)
-      resize_table(P.rows, L.ih, tabs.data() + tab + L.iw);
-      tab += L.iw + L.ih;
+      L.xtab_len = (L.cols + 3) & ~3;
+      const int ytab_len = (L.rows + 3) & ~3;   // keeps every table 16-byte aligned
+      tabs.resize(tab + L.xtab_len + ytab_len);
+      resize_table(P.cols, L.iw, L.xtab_len, tabs.data() + tab);          // source = PADDED level l-1 (this fork, :2119)
+      resize_table(P.rows, L.ih, L.rows, tabs.data() + tab + L.xtab_len);
+      // the 4-pixel kernel reads an 8-byte source window per thread: needs ofs(x+3) + 1 - ofs(x) <= 7
+      L.pyr_fast = 1;
+      for (int x = 0; x + 3 < L.xtab_len && L.pyr_fast; x += 4) {
+        int lo = tabs[tab + x].ofs, hi = lo;
+        for (int k = 1; k < 4; ++k) { lo = std::min(lo, tabs[tab + x + k].ofs); hi = std::max(hi, tabs[tab + x + k].ofs); }
+        if (hi + 1 - lo > 7) L.pyr_fast = 0;
+      }
+      if (getenv("ORB_B200_PYR_GENERIC")) L.pyr_fast = 0;
+      tab += L.xtab_len + ytab_len;
     }
   }
-  g.ncells_total = cells; g.raw_total = raw; g.node_total = nodes;
+  g.ncells_total = cells; g.raw_total = raw; g.node_total = nodes; g.fast_tiles_total = ftiles;
   g.frame_stride = plane;
   e->geom = g;
   return ORB_OK;
@@ -211,8 +226,8 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     const int capw = std::max(cap, e->cap_ws);
     const int nl = g.nlevels;
 #define ENS(buf, bytes) if ((rc = e->buf.ensure(bytes)) != ORB_OK) return rc
-    ENS(pyr, B * g.frame_stride);
-    ENS(blr, B * g.frame_stride);
+    ENS(pyr, B * g.frame_stride + 256);   // +256: the resize window loads may run 12 bytes past a row end
+    ENS(blr, B * g.frame_stride + 256);
     ENS(cell_cnt, B * g.ncells_total * sizeof(int));
     ENS(cell_kp, B * g.ncells_total * ORB_CELL_CAP * sizeof(uint32_t));
     ENS(kept, B * g.node_total * sizeof(uint32_t));

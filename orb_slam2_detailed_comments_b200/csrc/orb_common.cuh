@@ -12,6 +12,7 @@
 #define ORB_EDGE 19          // EDGE_THRESHOLD, src/ORBextractor.cc:82
 #define ORB_HALF_PATCH 15    // HALF_PATCH_SIZE, :81
 #define ORB_MIN_BORDER 16    // EDGE_THRESHOLD - 3, :1443
+#define ORB_FAST_TILE_W 248  // max detection-domain width of one FAST tile (<= 64 aligned pixel quads)
 #define ORB_CELL_CAP 128     // NMS survivors kept per 30-px cell (overflow -> ORB_E_CAPACITY)
 
 struct OrbLevel {
@@ -29,21 +30,27 @@ struct OrbLevel {
   int kept_off;              // offset into per-frame kept arrays (capacity node_cap)
   float scale;               // mvScaleFactor[l]
   float patch_size;          // (int)(31*scale)
-  int tab_off;               // offset into resize tables (x table then y table), level >= 1
+  int tab_off;               // level >= 1: resize tables in padded destination coordinates: x table [xtab_len], then y table [rows]
+  int xtab_len;              // cols rounded up to a multiple of 4
+  int pyr_fast;              // 1: 4-pixel window kernel applies (horizontal ratio <= 2)
+  int fast_G, fast_nseg;     // FAST tile = one cell row x fast_G cells; segments per cell row
+  int fast_tile_base;        // first FAST tile of this level
 };
 
 struct OrbGeom {
   int nlevels, width, height;
   int ncells_total;
   int raw_total, node_total;
+  int fast_tiles_total;      // FAST tiles per frame (all levels)
   unsigned long long frame_stride;   // bytes per frame in pyramid / blurred
   int ini_th, min_th;
   int blur_taps[7];
   OrbLevel lv[ORB_MAX_LEVELS];
 };
 
-struct ResizeTab {   // per destination index of cv::resize INTER_LINEAR (11-bit coefficients)
-  short ofs, c0, c1, pad;
+struct ResizeTab {   // per PADDED destination index of cv::resize INTER_LINEAR: source offset + 11-bit coefficients
+  int ofs;           // first source pixel (second = ofs + 1; its coefficient is 0 where that would leave the image)
+  unsigned coef;     // c0 | c1 << 16   (c0 + c1 == 2048)
 };
 
 struct OrbKeypoint {  // == cv::KeyPoint / orb_keypoint
