@@ -9,63 +9,67 @@
 //
 // One CTA = one cell row x up to fast_G cells (a band of <= 248 x hCell detection pixels):
 //   1. the band window (+3 px halo) is staged in shared memory with 16-byte loads;
-//   2. quick reject, 4 pixels per thread with byte-SIMD (VABSDIFF4): a 9-arc always holds one of {up, down}
-//      and one of {left, right}, so min(max|d_ud|, max|d_lr|) > minTh is necessary for S >= minTh;
-//   3. surviving candidates are compacted per warp (ballot) and scored 32 at a time with full lanes;
-//   4. per cell (one warp each): NMS on the shared score plane, ballot/popc emission in row-major order.
+//   2. quick reject, 4 pixels per thread with byte-SIMD (VABSDIFF4 + carry-free byte compares): a 9-arc always
+//      holds one of {up, down} and one of {left, right}, so min(max|d_ud|, max|d_lr|) > minTh is necessary for
+//      S >= minTh; survivors are compacted into a per-warp candidate list (ballot);
+//   3. candidates are scored 32 at a time with full lanes. The dark and the bright arc tests share one instruction
+//      stream: ring pixel r_k becomes the 16-bit lane pair [256 + v - r_k, 256 - v + r_k] (one IMAD) and
+//      max_arcs(min_9) of both lanes is 16 + 16 VIMNMX3.U16x2 + an 8-op max tree. Corners (S >= minTh) are
+//      compacted in place to the front of the warp's list;
+//   4. each corner does the 3x3 NMS on the shared score plane (cell-window masked) and sets its bit in the
+//      min / ini survivor bit planes;
+//   5. per cell (one warp each, lane = row): 64-bit row masks from the bit planes, popc + warp scan give every
+//      survivor its row-major rank; ini/min selection by the cell's ini count.
 #include "orb_common.cuh"
 
 #define FAST_THREADS 256
 #define FAST_WARPS 8
 #define FAST_WP 288      // window row pitch in smem: 16 B front pad + <= 272 B
 #define FAST_SP 272      // score plane row pitch
-#define FAST_LIST 160    // per-warp candidate list capacity (< 32 + 128)
+#define FAST_BP 11       // survivor bit plane row pitch in words (window columns < 288 -> 9 words, +2 for the 64-bit extract)
 
-__device__ __forceinline__ int fast_score(const uint8_t* __restrict__ p, int wp, int min_th) {
+// cornerScore (OpenCV fast_score.cpp, 16-pixel ring, K = 8): S = max(max_arcs min_9(v - r), max_arcs min_9(r - v)) - 1,
+// clamped at 0. Lanes of every 32-bit value: lo = 256 + (v - r), hi = 256 + (r - v), both in [1, 511].
+__device__ __forceinline__ int fast_score(const uint8_t* __restrict__ p) {
+  constexpr int wp = FAST_WP;
+  const unsigned v = p[0];
+  const unsigned base = (256u + v) | ((256u - v) << 16);
+  unsigned e[16];
   // ring offsets (dx,dy), k = 0..15: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
-  const int v = p[0];
-  int d[16];
-  d[0] = v - p[3 * wp];      d[8] = v - p[-3 * wp];
-  d[4] = v - p[3];           d[12] = v - p[-3];
-  d[2] = v - p[2 * wp + 2];  d[10] = v - p[-2 * wp - 2];
-  d[6] = v - p[-2 * wp + 2]; d[14] = v - p[2 * wp - 2];
-  // every 9-arc holds one pixel of each opposite pair: sign-consistent reject on the four even pairs
-  {
-    const bool dark = (max(d[0], d[8]) > min_th) && (max(d[4], d[12]) > min_th) && (max(d[2], d[10]) > min_th) &&
-                      (max(d[6], d[14]) > min_th);
-    const bool bright = (min(d[0], d[8]) < -min_th) && (min(d[4], d[12]) < -min_th) && (min(d[2], d[10]) < -min_th) &&
-                        (min(d[6], d[14]) < -min_th);
-    if (!dark && !bright) return 0;
-  }
-  d[1] = v - p[3 * wp + 1];  d[3] = v - p[wp + 3];
-  d[5] = v - p[-wp + 3];     d[7] = v - p[-3 * wp + 1];
-  d[9] = v - p[-3 * wp - 1]; d[11] = v - p[-wp - 3];
-  d[13] = v - p[wp - 3];     d[15] = v - p[3 * wp - 1];
-  int lo2[16], hi2[16], lo4[16], hi4[16];
+  e[0] = p[3 * wp];       e[1] = p[3 * wp + 1];   e[2] = p[2 * wp + 2];   e[3] = p[wp + 3];
+  e[4] = p[3];            e[5] = p[-wp + 3];      e[6] = p[-2 * wp + 2];  e[7] = p[-3 * wp + 1];
+  e[8] = p[-3 * wp];      e[9] = p[-3 * wp - 1];  e[10] = p[-2 * wp - 2]; e[11] = p[-wp - 3];
+  e[12] = p[-3];          e[13] = p[wp - 3];      e[14] = p[2 * wp - 2];  e[15] = p[3 * wp - 1];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) { lo2[k] = min(d[k], d[(k + 1) & 15]); hi2[k] = max(d[k], d[(k + 1) & 15]); }
+  for (int k = 0; k < 16; ++k) e[k] = base + e[k] * 0xffffu;   // (r << 16) - r: no borrow, lo >= 1
+  unsigned m3[16], m9[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) { lo4[k] = min(lo2[k], lo2[(k + 2) & 15]); hi4[k] = max(hi2[k], hi2[(k + 2) & 15]); }
-  int A = -256, Bn = 256;  // A = max_k min(arc_k), Bn = min_k max(arc_k)  (B = -Bn)
+  for (int k = 0; k < 16; ++k) m3[k] = __vimin3_u16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const int lo9 = min(min(lo4[k], lo4[(k + 4) & 15]), d[(k + 8) & 15]);
-    const int hi9 = max(max(hi4[k], hi4[(k + 4) & 15]), d[(k + 8) & 15]);
-    A = max(A, lo9);
-    Bn = min(Bn, hi9);
-  }
-  const int s = max(A, -Bn) - 1;
-  return s < 0 ? 0 : s;
+  for (int k = 0; k < 16; ++k) m9[k] = __vimin3_u16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+  const unsigned a0 = __vimax3_u16x2(m9[0], m9[1], m9[2]), a1 = __vimax3_u16x2(m9[3], m9[4], m9[5]),
+                 a2 = __vimax3_u16x2(m9[6], m9[7], m9[8]), a3 = __vimax3_u16x2(m9[9], m9[10], m9[11]),
+                 a4 = __vimax3_u16x2(m9[12], m9[13], m9[14]);
+  const unsigned b = __vimax3_u16x2(__vimax3_u16x2(a0, a1, a2), __vimax3_u16x2(a3, a4, m9[15]), 0u);
+  const int s = (int)max(b & 0xffffu, b >> 16) - 257;
+  return max(s, 0);
 }
 
+// per-byte a > t (bit 7 of each result byte), t <= 126: ((a & 0x7f) | 0x80) - (t + 1) never borrows across bytes
+__device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned t1) {
+  return (((a & 0x7f7f7f7fu) | 0x80808080u) - t1) | a;
+}
+
+template <bool SMALL_TH>   // SMALL_TH: minTh <= 126 (carry-free byte compare); otherwise the generic video intrinsic
 __global__ void __launch_bounds__(FAST_THREADS)
 orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ cell_kp,
-                     int* __restrict__ err_flag, int win_rows, int sc_rows, const __grid_constant__ OrbGeom g) {
+                     int* __restrict__ err_flag, int win_rows, int sc_rows, int list_cap, const __grid_constant__ OrbGeom g) {
   extern __shared__ __align__(16) uint8_t smem[];
   uint8_t* win = smem;                                    // [win_rows][FAST_WP], pixel x at column 16 + x
   uint8_t* sc = win + win_rows * FAST_WP;                 // [sc_rows][FAST_SP], score of domain row y at row y + 1
-  uint16_t* lists = reinterpret_cast<uint16_t*>(sc + sc_rows * FAST_SP);        // [FAST_WARPS][FAST_LIST]
-  uint32_t* ballots = reinterpret_cast<uint32_t*>(lists + FAST_WARPS * FAST_LIST);  // [FAST_WARPS][4 * (sc_rows - 2)]
+  uint32_t* pl_min = reinterpret_cast<uint32_t*>(sc + sc_rows * FAST_SP);   // [sc_rows - 2][FAST_BP] NMS survivors, S >= minTh
+  uint32_t* pl_ini = pl_min + (sc_rows - 2) * FAST_BP;                       //                         S >= iniTh
+  uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + (sc_rows - 2) * FAST_BP);   // [FAST_WARPS][list_cap]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
   int level = 0;
@@ -76,13 +80,14 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   const int t = blockIdx.x - L.fast_tile_base;
   const int ci = t / L.fast_nseg, sg = t - ci * L.fast_nseg;
   const int j0 = sg * L.fast_G, j1 = min(j0 + L.fast_G, L.nCols);
+  const int wCell = L.wCell;
   int* cnt_row = cell_cnt + (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
   uint32_t* kp_row = cell_kp + ((long long)frame * g.ncells_total + L.cell_base + ci * L.nCols) * ORB_CELL_CAP;
 
   const int iniY = ORB_MIN_BORDER + ci * L.hCell;
   const int wh = min(iniY + L.hCell + 6, L.maxBY) - iniY, dh = wh - 6;   // window rows, detection rows
-  const int X0 = ORB_MIN_BORDER + j0 * L.wCell;                          // window [X0, X1)
-  const int X1 = min(ORB_MIN_BORDER + j1 * L.wCell + 6, L.maxBX);
+  const int X0 = ORB_MIN_BORDER + j0 * wCell;                            // window [X0, X1)
+  const int X1 = min(ORB_MIN_BORDER + j1 * wCell + 6, L.maxBX);
   if (iniY >= L.maxBY - 3 || dh <= 0 || X1 - X0 <= 6) {                  // :1479-1503 skip rules / empty domain
     for (int j = j0 + tid; j < j1; j += FAST_THREADS) cnt_row[j] = 0;
     return;
@@ -90,131 +95,159 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   const int xa = X0 & ~15;                         // 16-byte aligned global column of window column 0
   const int nvec = (X1 - xa + 15) >> 4;
   const uint8_t* src = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)iniY * L.pitch + xa;
-  // 1. stage the window
+  // 1. stage the window; clear the score plane and the survivor bit planes
   for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
     const int y = i / nvec, v = i - y * nvec;
     *reinterpret_cast<uint4*>(win + y * FAST_WP + 16 + 16 * v) = *reinterpret_cast<const uint4*>(src + (long long)y * L.pitch + 16 * v);
   }
   for (int i = tid; i < (dh + 2) * (FAST_SP / 16); i += FAST_THREADS) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 2 * (sc_rows - 2) * FAST_BP; i += FAST_THREADS) pl_min[i] = 0u;
   __syncthreads();
 
-  // 2 + 3. quick reject by pixel quads, per-warp compaction, full score of candidates
+  // 2. quick reject by pixel quads, per-warp compaction (warp w owns detection rows w, w + 8, ...)
   const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
   const int qbase = dx0 & ~3;
   const int nq = (dx1 - qbase + 3) >> 2;                 // <= 64
-  const unsigned th4 = (unsigned)g.min_th * 0x01010101u;
-  uint16_t* list = lists + warp * FAST_LIST;
+  const unsigned th4 = (unsigned)g.min_th * 0x01010101u, t1 = th4 + 0x01010101u;
+  uint16_t* list = lists + warp * list_cap;
   const uint32_t lt = (1u << lane) - 1u;
   int cnt = 0;
-  for (int y = warp; y < dh; y += FAST_WARPS) {
-    const uint8_t* row = win + (y + 3) * FAST_WP + 16;
-    for (int h = 0; h < nq; h += 32) {
-      const int q = h + lane;
-      const int x = qbase + 4 * q;
-      unsigned pass = 0;
-      if (q < nq) {
-        const unsigned c0 = *reinterpret_cast<const unsigned*>(row + x - 4), c1 = *reinterpret_cast<const unsigned*>(row + x),
-                       c2 = *reinterpret_cast<const unsigned*>(row + x + 4);
-        const unsigned up = *reinterpret_cast<const unsigned*>(row + x - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + x + 3 * FAST_WP);
-        const unsigned lf = __byte_perm(c0, c1, 0x4321), rt = __byte_perm(c1, c2, 0x6543);
-        const unsigned a = __vminu4(__vmaxu4(__vabsdiffu4(c1, up), __vabsdiffu4(c1, dn)),
-                                    __vmaxu4(__vabsdiffu4(c1, lf), __vabsdiffu4(c1, rt)));
-        pass = __vcmpgtu4(a, th4);
-        if (pass) {
+  for (int h = 0; h < nq; h += 32) {
+    const int q = h + lane;
+    const int x = qbase + 4 * q;
+    unsigned colmask = 0;                                // bit 7 of byte k: column x + k is a detection column
+    if (q < nq) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (x + k < dx0 || x + k >= dx1) pass &= ~(0xffu << (8 * k));
-        }
+      for (int k = 0; k < 4; ++k)
+        if (x + k >= dx0 && x + k < dx1) colmask |= 0x80u << (8 * k);
+    }
+    for (int y = warp; y < dh; y += FAST_WARPS) {
+      const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
+      unsigned pass = 0;
+      if (colmask) {
+        const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c1 = *reinterpret_cast<const unsigned*>(row),
+                       c2 = *reinterpret_cast<const unsigned*>(row + 4);
+        const unsigned up = *reinterpret_cast<const unsigned*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + 3 * FAST_WP);
+        const unsigned lf = __byte_perm(c0, c1, 0x4321), rt = __byte_perm(c1, c2, 0x6543);
+        const unsigned au = __vabsdiffu4(c1, up), ad = __vabsdiffu4(c1, dn), al = __vabsdiffu4(c1, lf), ar = __vabsdiffu4(c1, rt);
+        if (SMALL_TH) pass = (fast_gt4(au, t1) | fast_gt4(ad, t1)) & (fast_gt4(al, t1) | fast_gt4(ar, t1)) & colmask;
+        else pass = (__vcmpgtu4(au, th4) | __vcmpgtu4(ad, th4)) & (__vcmpgtu4(al, th4) | __vcmpgtu4(ar, th4)) & colmask;
       }
       if (__any_sync(0xffffffffu, pass != 0)) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const bool f = (pass >> (8 * k)) & 1u;
+          const bool f = (pass >> (8 * k + 7)) & 1u;
           const uint32_t b = __ballot_sync(0xffffffffu, f);
           if (f) list[cnt + __popc(b & lt)] = (uint16_t)((y << 9) | (x + k));
           cnt += __popc(b);
         }
-        __syncwarp();
-        while (cnt >= 32) {
-          cnt -= 32;
-          const int e = list[cnt + lane];
-          const int ey = e >> 9, ex = e & 511;
-          const int s = fast_score(win + (ey + 3) * FAST_WP + 16 + ex, FAST_WP, g.min_th);
-          if (s) sc[(ey + 1) * FAST_SP + ex] = (uint8_t)s;
-          __syncwarp();
-        }
       }
     }
   }
-  if (lane < cnt) {
-    const int e = list[lane];
-    const int ey = e >> 9, ex = e & 511;
-    const int s = fast_score(win + (ey + 3) * FAST_WP + 16 + ex, FAST_WP, g.min_th);
-    if (s) sc[(ey + 1) * FAST_SP + ex] = (uint8_t)s;
+  __syncwarp();
+
+  // 3. score the candidates, 32 per step; corners (S >= minTh) are compacted in place to the front of the list
+  int ncorner = 0;
+  for (int c0 = 0; c0 < cnt; c0 += 32) {
+    const int i = c0 + lane;
+    int e = 0, s = 0;
+    if (i < cnt) {
+      e = list[i];
+      s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
+    }
+    const bool corner = s >= g.min_th;
+    __syncwarp();                                            // the reads of this chunk precede the in-place writes below
+    const uint32_t b = __ballot_sync(0xffffffffu, corner);
+    if (corner) {
+      sc[((e >> 9) + 1) * FAST_SP + (e & 511)] = (uint8_t)s;
+      list[ncorner + __popc(b & lt)] = (uint16_t)e;
+    }
+    ncorner += __popc(b);
   }
   __syncthreads();
 
-  // 4. per cell: NMS inside the cell's detection window, ini/min selection, ordered emission
-  uint32_t* bal = ballots + warp * 4 * (sc_rows - 2);   // [row][chunk][min, ini]
+  // 4. 3x3 NMS of every corner against its neighbours inside the same cell's detection window
+  {
+    const unsigned inv = (1u << 20) / (unsigned)wCell + 1u;      // p / wCell == (p * inv) >> 20 for p < 4096, wCell < 256
+    const int xlim = L.maxBX - 3 - xa;                           // detection columns end here (last cell may be clipped)
+    for (int i = lane; i < ncorner; i += 32) {
+      const int e = list[i];
+      const int y = e >> 9, x = e & 511;
+      const uint8_t* q = sc + (y + 1) * FAST_SP + x;
+      const int s = q[0];
+      const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);
+      const unsigned r = p - ((p * inv) >> 20) * (unsigned)wCell;   // column inside the cell's detection window
+      bool ok = s > q[-FAST_SP] && s > q[FAST_SP];
+      if (r > 0) ok = ok && s > q[-1] && s > q[-FAST_SP - 1] && s > q[FAST_SP - 1];
+      if ((int)r < wCell - 1 && x + 1 < xlim) ok = ok && s > q[1] && s > q[-FAST_SP + 1] && s > q[FAST_SP + 1];
+      if (ok) {
+        atomicOr(&pl_min[y * FAST_BP + (x >> 5)], 1u << (x & 31));
+        if (s >= g.ini_th) atomicOr(&pl_ini[y * FAST_BP + (x >> 5)], 1u << (x & 31));
+      }
+    }
+  }
+  __syncthreads();
+
+  // 5. per cell: row-major ranks from the survivor bit planes, ini/min selection, emission. Lane = detection row
+  //    (two row slots cover dh <= 64); a cell's detection window is < 64 columns wide.
   for (int cj = j0 + warp; cj < j1; cj += FAST_WARPS) {
-    const int cx0 = ORB_MIN_BORDER + cj * L.wCell + 3 - xa;
-    const int cx1 = min(ORB_MIN_BORDER + (cj + 1) * L.wCell + 3, L.maxBX - 3) - xa;
+    const int cx0 = ORB_MIN_BORDER + cj * wCell + 3 - xa;
+    const int cx1 = min(ORB_MIN_BORDER + (cj + 1) * wCell + 3, L.maxBX - 3) - xa;
     const int dw = cx1 - cx0;
     if (dw <= 0) {
       if (lane == 0) cnt_row[cj] = 0;
       continue;
     }
-    const int nch = (dw + 31) >> 5;   // 1 or 2
-    int n_ini = 0, n_min = 0;
-    for (int y = 0; y < dh; ++y) {
-      for (int c = 0; c < nch; ++c) {
-        const int x = cx0 + (c << 5) + lane;
-        bool f_min = false, f_ini = false;
-        if (x < cx1) {
-          const uint8_t* q = sc + (y + 1) * FAST_SP + x;
-          const int s = q[0];
-          if (s >= g.min_th) {
-            const bool hl = x > cx0, hr = x + 1 < cx1;
-            bool ok = s > q[-FAST_SP] && s > q[FAST_SP];
-            if (hl) ok = ok && s > q[-1] && s > q[-FAST_SP - 1] && s > q[FAST_SP - 1];
-            if (hr) ok = ok && s > q[1] && s > q[-FAST_SP + 1] && s > q[FAST_SP + 1];
-            f_min = ok;
-            f_ini = ok && s >= g.ini_th;
-          }
-        }
-        const uint32_t bm = __ballot_sync(0xffffffffu, f_min), bi = __ballot_sync(0xffffffffu, f_ini);
-        if (lane == 0) { bal[(y * 2 + c) * 2] = bm; bal[(y * 2 + c) * 2 + 1] = bi; }
-        n_min += __popc(bm);
-        n_ini += __popc(bi);
+    const unsigned long long wmask = dw >= 64 ? ~0ull : ((1ull << dw) - 1ull);
+    const int w0 = cx0 >> 5, sh = cx0 & 31;
+    unsigned long long m_min[2], m_ini[2];
+    int n_ini = 0;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int y = lane + 32 * r;
+      m_min[r] = 0ull; m_ini[r] = 0ull;
+      if (y < dh) {
+        const uint32_t* a = pl_min + y * FAST_BP + w0;
+        const uint32_t* b = pl_ini + y * FAST_BP + w0;
+        m_min[r] = (((unsigned long long)__funnelshift_r(a[1], a[2], sh) << 32) | __funnelshift_r(a[0], a[1], sh)) & wmask;
+        m_ini[r] = (((unsigned long long)__funnelshift_r(b[1], b[2], sh) << 32) | __funnelshift_r(b[0], b[1], sh)) & wmask;
+        n_ini += __popcll(m_ini[r]);
       }
     }
-    __syncwarp();
-    const int sel = n_ini > 0 ? 1 : 0;
-    const int total = n_ini > 0 ? n_ini : n_min;
+    n_ini = __reduce_add_sync(0xffffffffu, n_ini);
+    const unsigned long long m0 = n_ini > 0 ? m_ini[0] : m_min[0], m1 = n_ini > 0 ? m_ini[1] : m_min[1];
+    const int c0 = __popcll(m0), c1 = __popcll(m1);
+    // exclusive scan over rows 0..63 (slot 0 of all lanes, then slot 1)
+    int x0 = c0, x1 = c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y0 = __shfl_up_sync(0xffffffffu, x0, o), y1 = __shfl_up_sync(0xffffffffu, x1, o);
+      if (lane >= o) { x0 += y0; x1 += y1; }
+    }
+    const int tot0 = __shfl_sync(0xffffffffu, x0, 31), tot1 = __shfl_sync(0xffffffffu, x1, 31);
+    const int total = tot0 + tot1;
     uint32_t* kp_out = kp_row + (long long)cj * ORB_CELL_CAP;
-    int base = 0;
-    if (total > 0) {
-      for (int y = 0; y < dh; ++y) {
-        for (int c = 0; c < nch; ++c) {
-          const uint32_t m = bal[(y * 2 + c) * 2 + sel];
-          if ((m >> lane) & 1u) {
-            const int r = base + __popc(m & lt);
-            if (r < ORB_CELL_CAP) {
-              const int x = cx0 + (c << 5) + lane;
-              const uint32_t s = sc[(y + 1) * FAST_SP + x];
-              // cell-local FAST coordinates shifted by (j*wCell, i*hCell) (:1540-1541) == level pixel - 16
-              kp_out[r] = (uint32_t)(x + xa - ORB_MIN_BORDER) | ((uint32_t)(y + 3 + ci * L.hCell) << 12) | (s << 24);
-            }
-          }
-          base += __popc(m);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      unsigned long long m = r ? m1 : m0;
+      int rank = r ? tot0 + x1 - c1 : x0 - c0;
+      const int y = lane + 32 * r;
+      while (m) {
+        const int bx = __ffsll((long long)m) - 1;
+        m &= m - 1;
+        const int x = cx0 + bx;
+        if (rank < ORB_CELL_CAP) {
+          const uint32_t s = sc[(y + 1) * FAST_SP + x];
+          // cell-local FAST coordinates shifted by (j*wCell, i*hCell) (:1540-1541) == level pixel - 16
+          kp_out[rank] = (uint32_t)(x + xa - ORB_MIN_BORDER) | ((uint32_t)(y + 3 + ci * L.hCell) << 12) | (s << 24);
         }
+        ++rank;
       }
     }
     if (lane == 0) {
       cnt_row[cj] = min(total, ORB_CELL_CAP);
       if (total > ORB_CELL_CAP) atomicOr(err_flag, 1);
     }
-    __syncwarp();
   }
 }
 
@@ -223,14 +256,18 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
   int max_h = 0;
   for (int l = 0; l < g.nlevels; ++l) max_h = max(max_h, g.lv[l].hCell);
   const int win_rows = max_h + 6, sc_rows = max_h + 2;
-  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + FAST_WARPS * FAST_LIST * 2 +
-                      (size_t)FAST_WARPS * 4 * max_h * 4;
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    cudaFuncSetAttribute(orb_fast_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
+  const int list_cap = ((max_h + FAST_WARPS - 1) / FAST_WARPS) * 256;   // a warp's rows x <= 256 detection columns
+  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)max_h * FAST_BP * 4 +
+                      (size_t)FAST_WARPS * list_cap * 2;
+  static size_t configured[2] = {0, 0};
+  const int small = g.min_th <= 126;
+  if (smem > 48 * 1024 && smem > configured[small]) {
+    if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured[small] = smem;
   }
-  orb_fast_band_kernel<<<dim3(g.fast_tiles_total, batch), FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows,
-                                                                                   sc_rows, g);
+  const dim3 grid(g.fast_tiles_total, batch);
+  if (small) orb_fast_band_kernel<true><<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, list_cap, g);
+  else orb_fast_band_kernel<false><<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, list_cap, g);
   ++*launches;
 }

@@ -74,10 +74,15 @@ struct orb_extractor {
   int last_batch = 0;      // frames of the last pass still resident in the workspace
   int cap_ws = 0;
   long long launches = 0;
-  DevBuf tabs, pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, err, stage_in, out_kps, out_desc, out_cnt;
+  DevBuf tabs, pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, err, out_cnt;
+  // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  DevBuf stage_in[2], out_kps[2], out_desc[2], out_cnt2[2];
+  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {};
+  size_t h_cnt_cap = 0;    // ints in h_cnt
   DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
   int* h_err = nullptr;    // pinned
-  int* h_cnt = nullptr;    // pinned [chunk * (1 + nlevels)]
+  int* h_cnt = nullptr;    // pinned [batch * (1 + nlevels)]: counts, then per-level counts
   bool profile = false;    // per-stage CUDA-event timing (orb_extractor_set_profiling)
   std::vector<cudaEvent_t> ev;   // (ORB_NUM_STAGES + 1) events per profiled pass, resolved lazily (no sync in the pass)
   size_t ev_used = 0;
@@ -233,8 +238,6 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     ENS(kept, B * g.node_total * sizeof(uint32_t));
     ENS(kept_cnt, B * nl * sizeof(int));
     ENS(err, sizeof(int));
-    ENS(out_kps, B * capw * sizeof(OrbKeypoint));
-    ENS(out_desc, B * capw * 32);
     ENS(out_cnt, B * sizeof(int));
     ENS(q_key, B * g.raw_total * sizeof(uint32_t));
     ENS(q_knode, B * g.raw_total * sizeof(int));
@@ -252,9 +255,6 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     ENS(q_scan, B * g.node_total * sizeof(unsigned long long));
     ENS(q_rawn, B * nl * sizeof(int));
 #undef ENS
-    if (e->h_cnt) cudaFreeHost(e->h_cnt);
-    e->h_cnt = nullptr;
-    CU(cudaMallocHost(&e->h_cnt, B * (1 + nl) * sizeof(int)));
     CU(cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream));
     e->chunk = (int)B;
     e->cap_ws = capw;
@@ -364,11 +364,18 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
-  DevBuf* bufs[] = {&e->tabs, &e->pyr, &e->blr, &e->cell_cnt, &e->cell_kp, &e->kept, &e->kept_cnt, &e->err, &e->stage_in, &e->out_kps,
-                    &e->out_desc, &e->out_cnt, &e->q_key, &e->q_knode, &e->q_kchild, &e->q_bbox, &e->q_ncount, &e->q_pidx, &e->q_best,
+  DevBuf* bufs[] = {&e->tabs, &e->pyr, &e->blr, &e->cell_cnt, &e->cell_kp, &e->kept, &e->kept_cnt, &e->err, &e->stage_in[0], &e->stage_in[1],
+                    &e->out_kps[0], &e->out_kps[1], &e->out_desc[0], &e->out_desc[1], &e->out_cnt2[0], &e->out_cnt2[1], &e->out_cnt, &e->q_key, &e->q_knode, &e->q_kchild, &e->q_bbox, &e->q_ncount, &e->q_pidx, &e->q_best,
                     &e->q_ordA, &e->q_ordB, &e->q_par, &e->q_cand, &e->q_ccnt, &e->q_cslot, &e->q_scan, &e->q_rawn};
   for (DevBuf* b : bufs) b->release();
   if (e->h_cnt) cudaFreeHost(e->h_cnt);
+  if (e->s_in) cudaStreamDestroy(e->s_in);
+  if (e->s_out) cudaStreamDestroy(e->s_out);
+  for (int b = 0; b < 2; ++b) {
+    if (e->ev_in[b]) cudaEventDestroy(e->ev_in[b]);
+    if (e->ev_done[b]) cudaEventDestroy(e->ev_done[b]);
+    if (e->ev_out[b]) cudaEventDestroy(e->ev_out[b]);
+  }
   for (cudaEvent_t ev : e->ev)
     if (ev) cudaEventDestroy(ev);
   delete e;
@@ -447,33 +454,72 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
   if (rc != ORB_OK) return rc;
   const OrbGeom& g = e->geom;
   const int nl = g.nlevels;
-  const int spitch = (width + 63) & ~63;
-  if ((rc = e->stage_in.ensure((size_t)e->chunk * spitch * height)) != ORB_OK) return rc;
-  for (int f0 = 0; f0 < batch; f0 += e->chunk) {
+  const bool host_out = out_mem != ORB_MEM_DEVICE;
+  // Three streams, two buffer sets: the H2D copy of pass p+1 and the D2H copy of pass p-1 overlap the kernels of pass p.
+  if (!e->s_in) {
+    CU(cudaStreamCreateWithFlags(&e->s_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      CU(cudaEventCreateWithFlags(&e->ev_in[b], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&e->ev_done[b], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&e->ev_out[b], cudaEventDisableTiming));
+    }
+  }
+  const size_t fbytes = (size_t)step * height;   // frames are staged with the caller's pitch (level 0 reads any pitch)
+  const int nbuf = batch > e->chunk ? 2 : 1;
+  for (int b = 0; b < nbuf; ++b) {
+    if ((rc = e->stage_in[b].ensure((size_t)e->chunk * fbytes)) != ORB_OK) return rc;
+    if ((rc = e->out_cnt2[b].ensure((size_t)e->chunk * sizeof(int))) != ORB_OK) return rc;
+    if (host_out) {
+      if ((rc = e->out_kps[b].ensure((size_t)e->chunk * cap * sizeof(OrbKeypoint))) != ORB_OK) return rc;
+      if ((rc = e->out_desc[b].ensure((size_t)e->chunk * cap * 32)) != ORB_OK) return rc;
+    }
+  }
+  if (e->h_cnt_cap < (size_t)batch * (1 + nl)) {
+    if (e->h_cnt) cudaFreeHost(e->h_cnt);
+    e->h_cnt = nullptr; e->h_cnt_cap = 0;
+    CU(cudaMallocHost(&e->h_cnt, (size_t)batch * (1 + nl) * sizeof(int)));
+    e->h_cnt_cap = (size_t)batch * (1 + nl);
+  }
+  int* h_counts = e->h_cnt;
+  int* h_levels = e->h_cnt + batch;
+  const cudaMemcpyKind kin = in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  int pass = 0;
+  for (int f0 = 0; f0 < batch; f0 += e->chunk, ++pass) {
     const int n = std::min(e->chunk, batch - f0);
-    const cudaMemcpyKind kin = in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    bool contiguous = true;   // frames back to back with the same pitch -> one 2-D copy for the whole pass
-    for (int i = 1; i < n && contiguous; ++i) contiguous = images[f0 + i] == images[f0] + (size_t)i * step * height;
+    const int b = pass & 1;
+    // ---- copy-in stream: stage_in[b] is free once pass-2 finished computing
+    if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_done[b], 0));
+    bool contiguous = true;   // frames back to back with the same pitch -> one linear copy for the whole pass
+    for (int i = 1; i < n && contiguous; ++i) contiguous = images[f0 + i] == images[f0] + (size_t)i * fbytes;
     if (contiguous) {
-      CU(cudaMemcpy2DAsync(e->stage_in.p, spitch, images[f0], step, width, (size_t)height * n, kin, e->stream));
+      CU(cudaMemcpyAsync(e->stage_in[b].p, images[f0], (size_t)n * fbytes - (step - width), kin, e->s_in));
     } else {
       for (int i = 0; i < n; ++i)
-        CU(cudaMemcpy2DAsync(e->stage_in.as<uint8_t>() + (size_t)i * spitch * height, spitch, images[f0 + i], step, width, height, kin,
-                             e->stream));
+        CU(cudaMemcpyAsync(e->stage_in[b].as<uint8_t>() + (size_t)i * fbytes, images[f0 + i], fbytes - (step - width), kin, e->s_in));
     }
-    OrbKeypoint* dk = out_mem == ORB_MEM_DEVICE ? reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap : e->out_kps.as<OrbKeypoint>();
-    uint8_t* dd = out_mem == ORB_MEM_DEVICE ? desc + (long long)f0 * cap * 32 : e->out_desc.as<uint8_t>();
-    run_pass(e, e->stage_in.as<uint8_t>(), spitch, (long long)spitch * height, n, dk, dd, cap, e->out_cnt.as<int>());
-    CU(cudaMemcpyAsync(e->h_cnt, e->out_cnt.p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    CU(cudaMemcpyAsync(e->h_cnt + e->chunk, e->kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    if (out_mem != ORB_MEM_DEVICE) {
-      CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->stream));
-      CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaEventRecord(e->ev_in[b], e->s_in));
+    // ---- compute stream
+    CU(cudaStreamWaitEvent(e->stream, e->ev_in[b], 0));
+    if (host_out && pass >= 2) CU(cudaStreamWaitEvent(e->stream, e->ev_out[b], 0));   // out buffers [b] drained
+    OrbKeypoint* dk = host_out ? e->out_kps[b].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
+    uint8_t* dd = host_out ? e->out_desc[b].as<uint8_t>() : desc + (long long)f0 * cap * 32;
+    run_pass(e, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, e->out_cnt2[b].as<int>());
+    CU(cudaMemcpyAsync(h_counts + f0, e->out_cnt2[b].p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(h_levels + (size_t)f0 * nl, e->kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaEventRecord(e->ev_done[b], e->stream));
+    // ---- copy-out stream
+    if (host_out) {
+      CU(cudaStreamWaitEvent(e->s_out, e->ev_done[b], 0));
+      CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->s_out));
+      CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->s_out));
+      CU(cudaEventRecord(e->ev_out[b], e->s_out));
     }
-    if ((rc = check_err_flag(e)) != ORB_OK) return rc;
-    memcpy(counts + f0, e->h_cnt, n * sizeof(int));
-    if (level_counts) memcpy(level_counts + (size_t)f0 * nl, e->h_cnt + e->chunk, (size_t)n * nl * sizeof(int));
   }
+  if (host_out) CU(cudaStreamSynchronize(e->s_out));
+  if ((rc = check_err_flag(e)) != ORB_OK) return rc;   // synchronises the compute stream (counts are on the host after it)
+  memcpy(counts, h_counts, (size_t)batch * sizeof(int));
+  if (level_counts) memcpy(level_counts, h_levels, (size_t)batch * nl * sizeof(int));
   return ORB_OK;
 }
 
