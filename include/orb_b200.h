@@ -104,7 +104,8 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
 int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, int width, int height, int batch,
                              orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts_dev, int sync);
 
-/* mvImagePyramid of image `index` of the last batch: padded level (cols x rows), copied to `dst` (host, pitch dst_step).
+/* mvImagePyramid of image `index` of the last internal pass (index -1 = the last image of the last call, which is what the
+ * reference's member holds): padded level (cols x rows), copied to `dst` (host, pitch dst_step).
  * blurred != 0 returns the Gaussian-blurred working copy instead (test hook). */
 int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int* rows);
 int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurred, uint8_t* dst, int dst_step);

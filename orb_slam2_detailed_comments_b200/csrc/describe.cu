@@ -2,28 +2,32 @@
 // output assembly of ORBextractor::operator() (:2020-2081).
 #include "orb_common.cuh"
 
-__constant__ int8_t c_pattern[256 * 4] = {
+__device__ const int8_t d_pattern[256 * 4] = {
 #include "../../include/orb_pattern_31.inc"
 };
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};  // :866-910
 
 // ---- 7x7 sigma-2 Gaussian, OpenCV 8-bit fixed-point path (taps 8.8): out = (sum_ij k_i k_j p_ij + 32768) >> 16,
-// BORDER_REFLECT_101 at the border of the PADDED level (this fork blurs the padded image). All intermediate sums are exact
-// integers (row sums <= 257*255 fit 16 bits), so the order of the two passes is free. CTA tile = 128 x 32 output pixels:
-//   H pass: one thread = 4 adjacent pixels of one of the 38 input rows, read straight from global (3 words), bytes widened
-//           to 16-bit lane pairs [p(a), p(a+2)] so that one 32-bit IMAD does two taps -> u16 row sums in shared memory;
-//   V pass: one thread = 4 pixels x 4 output rows from 10 staged rows, 32-bit accumulators, one 32-bit store per row.
+// BORDER_REFLECT_101 at the border of the PADDED level (this fork blurs the padded image; the pyramid kernels have already
+// written that reflection into the plane's apron, so no index is remapped here). All intermediate sums are exact integers
+// (row sums <= 257*255 fit 16 bits), so the order of the two passes is free. CTA tile = 128 x 32 output pixels, 320 threads:
+//   H pass: one thread = 4 adjacent pixels of two adjacent rows: three 32-bit loads per row, the seven taps of a pixel are
+//           two DP4A on byte windows (PRMT); the two rows' sums are stored as vertical 16-bit pairs [h(r), h(r+1)], r even;
+//   V pass: one thread = 4 pixels x 4 output rows from 6 staged row pairs; the seven taps are four DP2A on the pairs
+//           (tap pairs differ for even and odd output rows), accumulator preloaded with the rounding constant.
 #define BL_TW 128
 #define BL_TH 32
+#define BL_THREADS 320
 template <bool CLAMP>   // CLAMP: tap sum > 256 (legacy taps sum to 257): saturate like OpenCV's ufixedpoint -> u8 cast
-__global__ void __launch_bounds__(256) orb_blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
-                                                       const __grid_constant__ OrbGeom g) {
-  __shared__ uint2 s_h[BL_TH + 6][BL_TW / 4];   // per pixel quad: .x = [h0, h2], .y = [h1, h3] (16-bit lanes)
+__global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
+                                                              const __grid_constant__ OrbGeom g) {
+  __shared__ uint4 s_p[(BL_TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
   int level = 0, t = blockIdx.x;
+#pragma unroll 1
   for (; level < g.nlevels; ++level) {
-    const int tx = (g.lv[level].cols + BL_TW - 1) / BL_TW, ty = (g.lv[level].rows + BL_TH - 1) / BL_TH;
-    if (t < tx * ty) break;
-    t -= tx * ty;
+    const int n = ((g.lv[level].cols + BL_TW - 1) / BL_TW) * ((g.lv[level].rows + BL_TH - 1) / BL_TH);
+    if (t < n) break;
+    t -= n;
   }
   if (level >= g.nlevels) return;
   const OrbLevel& L = g.lv[level];
@@ -33,63 +37,65 @@ __global__ void __launch_bounds__(256) orb_blur_kernel(const uint8_t* __restrict
   const unsigned long long off = (unsigned long long)blockIdx.y * g.frame_stride + L.plane_off;
   const uint8_t* src = pyr + off;
   const unsigned k0 = g.blur_taps[0], k1 = g.blur_taps[1], k2 = g.blur_taps[2], k3 = g.blur_taps[3];
-  for (int i = threadIdx.x; i < (BL_TH + 6) * (BL_TW / 4); i += 256) {
-    const int ly = i >> 5, q = i & 31;
-    const int x = x0 + 4 * q;
-    const int sy = orb_reflect101(min(y0 + ly - 3, L.rows + 2), L.rows);
-    const uint8_t* row = src + (long long)sy * L.pitch;
-    unsigned c0, c1, c2;
-    if (x >= 4 && x + 8 <= L.cols) {
-      c0 = *reinterpret_cast<const unsigned*>(row + x - 4);
-      c1 = *reinterpret_cast<const unsigned*>(row + x);
-      c2 = *reinterpret_cast<const unsigned*>(row + x + 4);
-    } else {
-      c0 = c1 = c2 = 0;
+  const unsigned tapA = k0 | (k1 << 8) | (k2 << 16) | (k3 << 24), tapB = k2 | (k1 << 8) | (k0 << 16);
+  const int pitch = L.pitch;
+  // local row r <-> plane row y0 - 4 + r (row -4 and rows past rows + 3 only ever meet a zero tap)
 #pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        c0 |= (unsigned)row[orb_reflect101(min(x - 4 + b, L.cols + 2), L.cols)] << (8 * b);
-        c1 |= (unsigned)row[orb_reflect101(min(x + b, L.cols + 2), L.cols)] << (8 * b);
-        c2 |= (unsigned)row[orb_reflect101(min(x + 4 + b, L.cols + 2), L.cols)] << (8 * b);
+  for (int it = 0; it < 2; ++it) {
+    const int i = threadIdx.x + it * BL_THREADS;   // 20 row pairs x 32 quads = 640 items
+    const int k = i >> 5, q = i & 31;
+    const int x = x0 + 4 * q;
+    if (x < L.cols) {
+      unsigned h[2][4];
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        const int ry = min(y0 - 4 + 2 * k + rr, L.rows + 3);
+        const unsigned* row = reinterpret_cast<const unsigned*>(src + (long long)ry * pitch + x);
+        const unsigned c0 = row[-1], c1 = row[0], c2 = row[1];
+        // W(a) = bytes B[a..a+3] of the 12 loaded bytes B[0..11] = pixels x-4 .. x+7; pixel j: W(j+1).tapA + W(j+5).tapB
+        const unsigned w1 = __byte_perm(c0, c1, 0x4321), w2 = __byte_perm(c0, c1, 0x5432), w3 = __byte_perm(c0, c1, 0x6543),
+                       w5 = __byte_perm(c1, c2, 0x4321), w6 = __byte_perm(c1, c2, 0x5432), w7 = __byte_perm(c1, c2, 0x6543);
+        h[rr][0] = __dp4a(w1, tapA, __dp4a(w5, tapB, 0u));
+        h[rr][1] = __dp4a(w2, tapA, __dp4a(w6, tapB, 0u));
+        h[rr][2] = __dp4a(w3, tapA, __dp4a(w7, tapB, 0u));
+        h[rr][3] = __dp4a(c1, tapA, __dp4a(c2, tapB, 0u));
       }
+      s_p[k][q] = make_uint4(__byte_perm(h[0][0], h[1][0], 0x5410), __byte_perm(h[0][1], h[1][1], 0x5410),
+                             __byte_perm(h[0][2], h[1][2], 0x5410), __byte_perm(h[0][3], h[1][3], 0x5410));
     }
-    // W(a) = bytes B[a..a+3] of the 12 loaded bytes B[0..11] = pixels x-4 .. x+7
-    const unsigned w1 = __byte_perm(c0, c1, 0x4321), w3 = __byte_perm(c0, c1, 0x6543), w5 = __byte_perm(c1, c2, 0x4321),
-                   w7 = __byte_perm(c1, c2, 0x6543);
-    // P(a) = [B[a], B[a+2]] as 16-bit lanes
-    const unsigned p1 = __byte_perm(w1, 0, 0x4240), p2 = __byte_perm(w1, 0, 0x4341), p3 = __byte_perm(w3, 0, 0x4240),
-                   p4 = __byte_perm(w3, 0, 0x4341), p5 = __byte_perm(w5, 0, 0x4240), p6 = __byte_perm(w5, 0, 0x4341),
-                   p7 = __byte_perm(w7, 0, 0x4240), p8 = __byte_perm(w7, 0, 0x4341);
-    uint2 h;
-    h.x = k0 * (p1 + p7) + k1 * (p2 + p6) + k2 * (p3 + p5) + k3 * p4;   // [h(x), h(x+2)]
-    h.y = k0 * (p2 + p8) + k1 * (p3 + p7) + k2 * (p4 + p6) + k3 * p5;   // [h(x+1), h(x+3)]
-    s_h[ly][q] = h;
   }
   __syncthreads();
-  const int q = threadIdx.x & 31, seg = threadIdx.x >> 5;
+  if (threadIdx.x >= 256) return;
+  const int q = threadIdx.x & 31, seg = threadIdx.x >> 5;   // output rows y0 + 4*seg .. + 3 = local rows 4*seg + 4 .. + 7
   const int x = x0 + 4 * q;
   if (x >= L.cols) return;
-  unsigned v[10][4];
+  uint4 P[6];                                                // pairs 2*seg .. 2*seg + 5 = local rows 4*seg .. 4*seg + 11
 #pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    const uint2 h = s_h[4 * seg + r][q];
-    v[r][0] = h.x & 0xffffu; v[r][2] = h.x >> 16; v[r][1] = h.y & 0xffffu; v[r][3] = h.y >> 16;
-  }
+  for (int i = 0; i < 6; ++i) P[i] = s_p[2 * seg + i][q];
+  // even local row t = 2m: [0,k0].P(m-2) + [k1,k2].P(m-1) + [k3,k2].P(m) + [k1,k0].P(m+1)
+  // odd  local row t = 2m+1: [k0,k1].P(m-1) + [k2,k3].P(m) + [k2,k1].P(m+1) + [k0,0].P(m+2)
+  const unsigned e0 = k0 << 8, e1 = k1 | (k2 << 8), e2 = k3 | (k2 << 8), e3 = k1 | (k0 << 8);
+  const unsigned o0 = k0 | (k1 << 8), o1 = k2 | (k3 << 8), o2 = k2 | (k1 << 8), o3 = k0;
   uint8_t* dst = blr + off;
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     const int y = y0 + 4 * seg + r;
     if (y < L.rows) {
+      const int m = 2 + (r >> 1);                           // pair index (relative to P[0]) holding local row t
       unsigned c[4];
 #pragma unroll
-      for (int p = 0; p < 4; ++p)
-        c[p] = k0 * (v[r][p] + v[r + 6][p]) + k1 * (v[r + 1][p] + v[r + 5][p]) + k2 * (v[r + 2][p] + v[r + 4][p]) + k3 * v[r + 3][p] + 32768u;
-      if (CLAMP) {
-#pragma unroll
-        for (int p = 0; p < 4; ++p) c[p] = min(c[p], 0xffffffu);
+      for (int p = 0; p < 4; ++p) {
+#define PW(i) (p == 0 ? P[i].x : p == 1 ? P[i].y : p == 2 ? P[i].z : P[i].w)
+        if ((r & 1) == 0)
+          c[p] = __dp2a_lo(PW(m - 2), e0, __dp2a_lo(PW(m - 1), e1, __dp2a_lo(PW(m), e2, __dp2a_lo(PW(m + 1), e3, 32768u))));
+        else
+          c[p] = __dp2a_lo(PW(m - 1), o0, __dp2a_lo(PW(m), o1, __dp2a_lo(PW(m + 1), o2, __dp2a_lo(PW(m + 2), o3, 32768u))));
+#undef PW
+        if (CLAMP) c[p] = min(c[p], 0xffffffu);
       }
       // byte 2 of each accumulator is the output pixel
       const unsigned lo = __byte_perm(c[0], c[1], 0x0062), hi = __byte_perm(c[2], c[3], 0x0062);
-      *reinterpret_cast<unsigned*>(dst + (long long)y * L.pitch + x) = __byte_perm(lo, hi, 0x5410);
+      *reinterpret_cast<unsigned*>(dst + (long long)y * pitch + x) = __byte_perm(lo, hi, 0x5410);
     }
   }
 }
@@ -143,85 +149,121 @@ __device__ __forceinline__ void orb_sincos(float angle, float* s, float* c) {
   }
 }
 
-// One warp per kept keypoint: orientation on the un-blurred level, descriptor on the blurred level,
-// then the final cv::KeyPoint (pt *= scale for level != 0) at the frame's output offset.
+// Orientation (un-blurred level), descriptor (blurred level) and the final cv::KeyPoint (pt *= scale for level != 0).
+// One warp handles DESC_KPW keypoints of one frame back to back, so the per-lane tables stay in registers:
+//   * IC_Angle: lane = patch row v (31 rows). The row's 32 bytes u = -16..15 are 9 aligned 32-bit loads funnel-shifted
+//     into 8 words; m10 += dp4a(word, [u masked by the disc]), rowsum += dp4a(word, [disc mask]); m01 = v * rowsum;
+//     two REDUX adds finish the moments (exact int32).
+//   * rBRIEF: lane = descriptor byte; its 8 test pairs are 32 float registers (x0, y0, x1, y1).
 #define DESC_WARPS 8
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+#define DESC_KPW 8
+__device__ __forceinline__ int dp4a_u8_s8(unsigned a, unsigned b, int c) {   // a: unsigned bytes, b: signed bytes
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__global__ void __launch_bounds__(DESC_WARPS * 32, 3)
 orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr, const uint32_t* __restrict__ kept,
                     const int* __restrict__ kept_cnt, OrbKeypoint* __restrict__ kps, uint8_t* __restrict__ desc, int cap,
                     int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
-  __shared__ int8_t s_pat[1024];
-  for (int i = threadIdx.x; i < 1024; i += DESC_WARPS * 32) s_pat[i] = c_pattern[i];
-  __syncthreads();
   const int frame = blockIdx.y;
-  const int lane = threadIdx.x & 31;
-  const int w = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);   // keypoint slot of this frame in output order
-  const int* kc = kept_cnt + frame * g.nlevels;
-  int level = -1, base = 0, total = 0;
-  for (int l = 0; l < g.nlevels; ++l) {
-    const int c = kc[l];
-    if (level < 0 && w < total + c) { level = l; base = total; }
-    total += c;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // cumulative kept counts: lane l holds the inclusive prefix of level l
+  int cinc = lane < g.nlevels ? kept_cnt[frame * g.nlevels + lane] : 0;
+  const int cown = cinc;
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, cinc, o);
+    if (lane >= o) cinc += y;
   }
-  if (w == 0 && lane == 0) {
+  const int total = __shfl_sync(0xffffffffu, cinc, g.nlevels - 1);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
     counts[frame] = min(total, cap);
     if (total > cap) atomicOr(err_flag, 8);
   }
-  if (level < 0 || w >= cap) return;
-  const OrbLevel& L = g.lv[level];
-  const uint32_t q = kept[(long long)frame * g.node_total + L.node_off + (w - base)];
-  const int x = (int)(q & 0xfffu) + ORB_MIN_BORDER, y = (int)((q >> 12) & 0xfffu) + ORB_MIN_BORDER;   // :1573-1589
-  const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off;
-  // IC_Angle: lane u = lane-15 sums column u of the disc; m10 = sum u*I, m01 = sum v*I (exact int32)
-  const uint8_t* center = pyr + off + (long long)y * L.pitch + x;
-  int m10 = 0, m01 = 0;
+  const int w_first = (blockIdx.x * DESC_WARPS + warp) * DESC_KPW;
+  const int w_end = min(min(w_first + DESC_KPW, total), cap);
+  if (w_first >= w_end) return;
+
+  // per-lane constants
+  const int v = lane - ORB_HALF_PATCH;                   // patch row of this lane (lane 31: none)
+  unsigned cu[8], cm[8];
   {
-    const int u = lane - ORB_HALF_PATCH;
-    if (lane < 31) {
+    const int hw = lane < 31 ? c_umax[v < 0 ? -v : v] : -1;   // half width of the disc in this row (:866-910, symmetric)
 #pragma unroll
-      for (int v = -ORB_HALF_PATCH; v <= ORB_HALF_PATCH; ++v) {
-        if (abs(u) <= c_umax[v < 0 ? -v : v]) {
-          const int val = center[v * L.pitch + u];
-          m10 += u * val;
-          m01 += v * val;
-        }
+    for (int i = 0; i < 8; ++i) {
+      cu[i] = 0u; cm[i] = 0u;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int u = -16 + 4 * i + j;
+        if ((u < 0 ? -u : u) <= hw) { cu[i] |= ((unsigned)u & 0xffu) << (8 * j); cm[i] |= 1u << (8 * j); }
       }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
   }
-  const float angle = orb_fast_atan2((float)m01, (float)m10);
-  const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
-  float a, b;
-  orb_sincos(__fmul_rn(angle, factorPI), &b, &a);
-  const uint8_t* bc = blr + off + (long long)y * L.pitch + x;
-  int val = 0;
+  float px0[8], py0[8], px1[8], py1[8];
 #pragma unroll
   for (int bit = 0; bit < 8; ++bit) {
-    const int8_t* p = &s_pat[(lane * 8 + bit) * 4];
-    const float x0 = (float)p[0], y0 = (float)p[1], x1 = (float)p[2], y1 = (float)p[3];
-    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-    const int t0 = bc[r0 * L.pitch + c0], t1 = bc[r1 * L.pitch + c1];
-    val |= (t0 < t1) << bit;
+    const char4 p = reinterpret_cast<const char4*>(d_pattern)[lane * 8 + bit];
+    px0[bit] = (float)p.x; py0[bit] = (float)p.y; px1[bit] = (float)p.z; py1[bit] = (float)p.w;
   }
-  const long long o = (long long)frame * cap + w;
-  desc[o * 32 + lane] = (uint8_t)val;
-  if (lane == 0) {
-    OrbKeypoint k;
-    k.x = level ? __fmul_rn((float)x, L.scale) : (float)x;
-    k.y = level ? __fmul_rn((float)y, L.scale) : (float)y;
-    k.size = L.patch_size;
-    k.angle = angle;
-    k.response = (float)(q >> 24);
-    k.octave = level;
-    k.class_id = -1;
-    kps[o] = k;
+
+  for (int w = w_first; w < w_end; ++w) {
+    const int level = __popc(__ballot_sync(0xffffffffu, lane < g.nlevels && cinc <= w));
+    const int base = __shfl_sync(0xffffffffu, cinc - cown, level);
+    const OrbLevel& L = g.lv[level];
+    const int pitch = L.pitch;
+    const uint32_t q = kept[(long long)frame * g.node_total + L.node_off + (w - base)];
+    const int x = (int)(q & 0xfffu) + ORB_MIN_BORDER, y = (int)((q >> 12) & 0xfffu) + ORB_MIN_BORDER;   // :1573-1589
+    const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)y * pitch + x;
+    // IC_Angle (:104-161)
+    int m10 = 0, rs = 0;
+    if (lane < 31) {
+      const uint8_t* rp = pyr + off + (long long)v * pitch - 16;
+      const unsigned sh = 8u * (unsigned)((uintptr_t)rp & 3);
+      const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)rp & ~(uintptr_t)3);
+      unsigned a[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) a[i] = __ldg(ap + i);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const unsigned wv = __funnelshift_r(a[i], a[i + 1], sh);
+        m10 = dp4a_u8_s8(wv, cu[i], m10);
+        rs = (int)__dp4a(wv, cm[i], (unsigned)rs);
+      }
+    }
+    m10 = __reduce_add_sync(0xffffffffu, m10);
+    const int m01 = __reduce_add_sync(0xffffffffu, v * rs);
+    const float angle = orb_fast_atan2((float)m01, (float)m10);
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+    float a, b;
+    orb_sincos(__fmul_rn(angle, factorPI), &b, &a);
+    // computeOrbDescriptor (:177-254)
+    const uint8_t* bc = blr + off;
+    int val = 0;
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(px0[bit], b), __fmul_rn(py0[bit], a)));
+      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(px0[bit], a), __fmul_rn(py0[bit], b)));
+      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(px1[bit], b), __fmul_rn(py1[bit], a)));
+      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(px1[bit], a), __fmul_rn(py1[bit], b)));
+      const int t0 = __ldg(bc + r0 * pitch + c0), t1 = __ldg(bc + r1 * pitch + c1);
+      val |= (t0 < t1) << bit;
+    }
+    const long long o = (long long)frame * cap + w;
+    desc[o * 32 + lane] = (uint8_t)val;
+    if (lane < 7) {   // the 28-byte cv::KeyPoint as seven coalesced 32-bit stores
+      float f;
+      switch (lane) {
+        case 0: f = level ? __fmul_rn((float)x, L.scale) : (float)x; break;
+        case 1: f = level ? __fmul_rn((float)y, L.scale) : (float)y; break;
+        case 2: f = L.patch_size; break;
+        case 3: f = angle; break;
+        case 4: f = (float)(q >> 24); break;
+        case 5: f = __int_as_float(level); break;
+        default: f = __int_as_float(-1); break;
+      }
+      reinterpret_cast<float*>(kps + o)[lane] = f;
+    }
   }
 }
 
@@ -231,15 +273,16 @@ void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const OrbGeom& g, int bat
     tiles += ((g.lv[l].cols + BL_TW - 1) / BL_TW) * ((g.lv[l].rows + BL_TH - 1) / BL_TH);
   int sum = g.blur_taps[3];
   for (int i = 0; i < 3; ++i) sum += 2 * g.blur_taps[i];
-  if (sum > 256) orb_blur_kernel<true><<<dim3(tiles, batch), 256, 0, st>>>(pyr, blr, g);
-  else orb_blur_kernel<false><<<dim3(tiles, batch), 256, 0, st>>>(pyr, blr, g);
+  if (sum > 256) orb_blur_kernel<true><<<dim3(tiles, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
+  else orb_blur_kernel<false><<<dim3(tiles, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
   ++*launches;
 }
 
 void orb_launch_describe(const uint8_t* pyr, const uint8_t* blr, const uint32_t* kept, const int* kept_cnt, OrbKeypoint* kps,
                          uint8_t* desc, int cap, int* counts, int* err_flag, const OrbGeom& g, int batch, cudaStream_t st,
                          long long* launches) {
-  orb_describe_kernel<<<dim3((cap + DESC_WARPS - 1) / DESC_WARPS, batch), DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps,
+  const int per_cta = DESC_WARPS * DESC_KPW;
+  orb_describe_kernel<<<dim3((cap + per_cta - 1) / per_cta, batch), DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps,
                                                                                                   desc, cap, counts, err_flag, g);
   ++*launches;
 }

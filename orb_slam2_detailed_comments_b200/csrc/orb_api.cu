@@ -114,19 +114,23 @@ static void build_tables(orb_extractor* e) {
 }
 
 // cv::resize INTER_LINEAR coefficient table for one axis (ssz -> dsz interior pixels), 11-bit fixed point, laid out in
-// PADDED destination coordinates: entry p describes interior pixel reflect101(p - 19) (the in-place copyMakeBorder of
-// src/ORBextractor.cc:2138 is an index remap of the interior). `len` >= dsz + 38 entries are written.
-static void resize_table(int ssz, int dsz, int len, ResizeTab* out) {
+// APRON coordinates of the padded destination: entry t describes padded index p = t - lead, i.e. interior pixel
+// reflect101(reflect101(p, dsz + 38) - 19, dsz). The in-place copyMakeBorder of src/ORBextractor.cc:2138 is an index remap
+// of the interior, and the apron (p < 0, p >= dsz + 38) is the BORDER_REFLECT_101 extension of the padded image that the
+// 7x7 blur reads (:2042). `len` entries are written; entries past the apron repeat the last valid one.
+static void resize_table(int ssz, int dsz, int lead, int len, ResizeTab* out) {
   const double scale = 1.0 / ((double)dsz / ssz);
-  for (int p = 0; p < len; ++p) {
-    const int d = orb_reflect101(std::min(p, dsz + 2 * ORB_EDGE - 1) - ORB_EDGE, dsz);
+  const int padded = dsz + 2 * ORB_EDGE;
+  for (int t = 0; t < len; ++t) {
+    const int p = std::min(t - lead, padded + ORB_APRON - 1);
+    const int d = orb_reflect101(orb_reflect101(p, padded) - ORB_EDGE, dsz);
     float f = (float)((d + 0.5) * scale - 0.5);
     int s = (int)floorf(f);
     f -= s;
     if (s < 0) { s = 0; f = 0.f; }
     if (s >= ssz - 1) { s = ssz - 1; f = 0.f; }
-    out[p].ofs = s;
-    out[p].coef = (unsigned)cv_round_f((1.f - f) * 2048.f) | ((unsigned)cv_round_f(f * 2048.f) << 16);
+    out[t].ofs = s;
+    out[t].coef = (unsigned)cv_round_f((1.f - f) * 2048.f) | ((unsigned)cv_round_f(f * 2048.f) << 16);
   }
 }
 
@@ -151,9 +155,11 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     if (L.iw < 2 * ORB_EDGE + 2 || L.ih < 2 * ORB_EDGE + 2)
       return fail(ORB_E_SHAPE, "level %d is %dx%d: too small for the 19-px reflect border", l, L.iw, L.ih);
     L.cols = L.iw + 2 * ORB_EDGE; L.rows = L.ih + 2 * ORB_EDGE;
-    L.pitch = (int)align_up(L.cols, 64);
-    L.plane_off = plane;
-    plane += align_up((size_t)L.pitch * L.rows, 256);
+    // plane = [4 apron rows][rows][4 apron rows], row = [16 B lead][cols][>= 8 B]: the pyramid kernels also write the
+    // reflect-101 extension of the padded image (4 columns / 3 rows each side) so the blur never remaps indices
+    L.pitch = (int)align_up(16 + L.cols + 8, 64);
+    L.plane_off = plane + (size_t)ORB_APRON_ROWS * L.pitch + 16;
+    plane += align_up((size_t)L.pitch * (L.rows + 2 * ORB_APRON_ROWS), 256);
     L.maxBX = L.cols - ORB_EDGE + 3; L.maxBY = L.rows - ORB_EDGE + 3;
     const float width = (float)(L.maxBX - ORB_MIN_BORDER), height = (float)(L.maxBY - ORB_MIN_BORDER);
     L.nCols = (int)(width / 30.f); L.nRows = (int)(height / 30.f);
@@ -182,11 +188,12 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.tab_off = tab;
     if (l > 0) {
       const OrbLevel& P = g.lv[l - 1];
-      L.xtab_len = (L.cols + 3) & ~3;
-      const int ytab_len = (L.rows + 3) & ~3;   // keeps every table 16-byte aligned
+      L.xtab_len = (L.cols + 2 * ORB_APRON + 3) & ~3;                   // columns -4 .. cols + 4
+      const int yrows = L.rows + 2 * (ORB_APRON - 1);                   // rows -3 .. rows + 3
+      const int ytab_len = (yrows + 3) & ~3;   // keeps every table 16-byte aligned
       tabs.resize(tab + L.xtab_len + ytab_len);
-      resize_table(P.cols, L.iw, L.xtab_len, tabs.data() + tab);          // source = PADDED level l-1 (this fork, :2119)
-      resize_table(P.rows, L.ih, L.rows, tabs.data() + tab + L.xtab_len);
+      resize_table(P.cols, L.iw, ORB_APRON, L.xtab_len, tabs.data() + tab);          // source = PADDED level l-1 (this fork, :2119)
+      resize_table(P.rows, L.ih, ORB_APRON - 1, ytab_len, tabs.data() + tab + L.xtab_len);
       // the 4-pixel kernel reads an 8-byte source window per thread: needs ofs(x+3) + 1 - ofs(x) <= 7
       L.pyr_fast = 1;
       for (int x = 0; x + 3 < L.xtab_len && L.pyr_fast; x += 4) {
@@ -533,6 +540,7 @@ int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int
 int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurred, uint8_t* dst, int dst_step) {
   if (!e || !dst || e->geom.width == 0 || level < 0 || level >= e->geom.nlevels) return fail(ORB_E_BADARG, "bad argument");
   std::lock_guard<std::mutex> lk(e->mu);
+  if (index == -1) index = e->last_batch - 1;   // the last image of the last call
   if (index < 0 || index >= e->last_batch) return fail(ORB_E_BADARG, "image %d is not resident (last pass held %d frames)", index, e->last_batch);
   const OrbLevel& L = e->geom.lv[level];
   if (dst_step < L.cols) return fail(ORB_E_BADARG, "dst_step too small");

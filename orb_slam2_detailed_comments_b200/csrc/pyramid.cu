@@ -6,25 +6,38 @@
 // directly from level l-1 (no second pass over the plane).
 #include "orb_common.cuh"
 
-// One thread = 4 horizontally adjacent padded output pixels (one 32-bit store).
+// Every plane is written together with its apron: columns [-4, cols + 4) and rows [-3, rows + 3) hold the
+// BORDER_REFLECT_101 extension of the PADDED image (what cv::GaussianBlur reads beyond it), so the blur kernel is branch-free.
+// Kernel x index t <-> padded column t - ORB_APRON, y index t <-> padded row t - (ORB_APRON - 1).
+
+// Level 0 = copyMakeBorder(image, 19, REFLECT_101). One thread = 4 adjacent output pixels (one 32-bit store); interior quads
+// read the (arbitrarily aligned) source row as two aligned words + a funnel shift, border quads as 4 remapped bytes.
 __global__ void __launch_bounds__(256) orb_pyr_level0_kernel(const uint8_t* __restrict__ images, int step,
                                                              long long image_stride, uint8_t* __restrict__ pyr,
                                                              const __grid_constant__ OrbGeom g) {
   const OrbLevel& L = g.lv[0];
   const int frame = blockIdx.z;
-  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (y >= L.rows || x4 >= L.pitch) return;
+  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4 - ORB_APRON;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y - (ORB_APRON - 1);
+  if (y >= L.rows + ORB_APRON - 1 || x4 >= L.cols + ORB_APRON) return;
   const uint8_t* src = images + (long long)frame * image_stride;
-  const int sy = orb_reflect101(y - ORB_EDGE, g.height);
+  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - ORB_EDGE, g.height);
   const uint8_t* srow = src + (long long)sy * step;
   uint32_t out = 0;
+  const int sx = x4 - ORB_EDGE;
+  if (sx >= 4 && sx + 8 <= g.width) {   // both aligned words lie inside this source row
+    const uint8_t* p = srow + sx;
+    const unsigned sh = 8u * (unsigned)((uintptr_t)p & 3);
+    const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)p & ~(uintptr_t)3);
+    const unsigned lo = __ldg(ap);
+    const unsigned hi = __ldg(ap + 1);
+    out = __funnelshift_r(lo, hi, sh);
+  } else {
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int x = x4 + k;
-    uint32_t v = 0;
-    if (x < L.cols) v = __ldg(srow + orb_reflect101(x - ORB_EDGE, g.width));
-    out |= v << (8 * k);
+    for (int k = 0; k < 4; ++k) {
+      const int x = min(x4 + k, L.cols + ORB_APRON - 1);
+      out |= (uint32_t)__ldg(srow + orb_reflect101(orb_reflect101(x, L.cols) - ORB_EDGE, g.width)) << (8 * k);
+    }
   }
   uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off;
   *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x4) = out;
@@ -36,9 +49,9 @@ __global__ void __launch_bounds__(256) orb_pyr_resize_kernel(uint8_t* __restrict
   const OrbLevel& D = g.lv[level];
   const OrbLevel& S = g.lv[level - 1];
   const int frame = blockIdx.z;
-  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  if (y >= D.rows || x4 >= D.xtab_len) return;
+  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;   // table index; padded column x4 - ORB_APRON
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;           // table index; padded row y - (ORB_APRON - 1)
+  if (y >= D.rows + 2 * (ORB_APRON - 1) || x4 >= D.xtab_len) return;
   uint8_t* base = pyr + (unsigned long long)frame * g.frame_stride;
   const uint8_t* src = base + S.plane_off;
   const ResizeTab* xt = tabs + D.tab_off;
@@ -57,7 +70,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize_kernel(uint8_t* __restrict
     const uint32_t v = (uint32_t)((((cy0 * (t0 >> 4)) >> 16) + ((cy1 * (t1 >> 4)) >> 16) + 2) >> 2);  // VResizeLinear
     out |= (v & 0xffu) << (8 * k);
   }
-  *reinterpret_cast<uint32_t*>(base + D.plane_off + (long long)y * D.pitch + x4) = out;
+  *reinterpret_cast<uint32_t*>(base + D.plane_off + (long long)(y - (ORB_APRON - 1)) * D.pitch + x4 - ORB_APRON) = out;
 }
 
 // Fast path (horizontal ratio <= 2, checked on the host): one thread = 4 adjacent padded output pixels x 4 rows.
@@ -86,7 +99,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     const int y = blockIdx.y * 32 + threadIdx.y + 8 * r;
-    if (y >= D.rows) break;
+    if (y >= D.rows + 2 * (ORB_APRON - 1)) break;
     const ResizeTab ty = yt[y];
     const unsigned cy0 = ty.coef & 0xffffu, cy1 = ty.coef >> 16;
     const unsigned* r0 = reinterpret_cast<const unsigned*>(src + (long long)ty.ofs * S.pitch + wbase);
@@ -103,7 +116,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
     }
     ORB_PX(0, s0, e01.y) ORB_PX(1, s1, e01.w) ORB_PX(2, s2, e23.y) ORB_PX(3, s3, e23.w)
 #undef ORB_PX
-    *reinterpret_cast<unsigned*>(dst + (long long)y * D.pitch + x4) =
+    *reinterpret_cast<unsigned*>(dst + (long long)(y - (ORB_APRON - 1)) * D.pitch + x4 - ORB_APRON) =
         __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
   }
 }
@@ -113,17 +126,17 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
   dim3 blk(32, 8);
   {
     const OrbLevel& L = g.lv[0];
-    dim3 grd((L.pitch / 4 + 31) / 32, (L.rows + 7) / 8, batch);
+    dim3 grd(((L.cols + 2 * ORB_APRON + 3) / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 7) / 8, batch);
     orb_pyr_level0_kernel<<<grd, blk, 0, st>>>(images, step, image_stride, pyr, g);
     ++*launches;
   }
   for (int l = 1; l < g.nlevels; ++l) {
     const OrbLevel& L = g.lv[l];
     if (L.pyr_fast) {
-      dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 31) / 32, batch);
+      dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 31) / 32, batch);
       orb_pyr_resize4_kernel<<<grd, blk, 0, st>>>(pyr, tabs, l, g);
     } else {
-      dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 7) / 8, batch);
+      dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 7) / 8, batch);
       orb_pyr_resize_kernel<<<grd, blk, 0, st>>>(pyr, tabs, l, g);
     }
     ++*launches;
