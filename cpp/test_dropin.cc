@@ -1,0 +1,136 @@
+// C++ parity test of the drop-in classes (built against cv_shim.h): ORB_SLAM2::ORBextractor / ORBmatcher on the GPU versus
+// the CPU oracle (oracle/orb_oracle.h, test infrastructure). Run by tests/test_cpp_dropin.py on a B200; exit code 0 = pass.
+//   usage: test_dropin <frame.raw> <width> <height> <nfeatures> [<frame2.raw>]
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../oracle/orb_oracle.h"
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+
+#define REQUIRE(cond, ...)                      \
+  do {                                          \
+    if (!(cond)) {                              \
+      std::fprintf(stderr, "FAIL %s:%d: ", __FILE__, __LINE__); \
+      std::fprintf(stderr, __VA_ARGS__);        \
+      std::fprintf(stderr, "\n");               \
+      return 1;                                 \
+    }                                           \
+  } while (0)
+
+static bool read_raw(const char* path, std::vector<unsigned char>& buf, size_t n) {
+  buf.resize(n);
+  FILE* f = std::fopen(path, "rb");
+  if (!f) return false;
+  const size_t got = std::fread(buf.data(), 1, n, f);
+  std::fclose(f);
+  return got == n;
+}
+
+static int compare_with_oracle(orb_oracle_extractor* oe, const cv::Mat& img, const std::vector<cv::KeyPoint>& kps, const cv::Mat& desc,
+                               ORB_SLAM2::ORBextractor& ex, bool check_pyramid) {
+  const int cap = 1 << 16;
+  std::vector<orb_oracle_kp> okp(cap);
+  std::vector<uint8_t> odesc((size_t)cap * 32);
+  const int n = orb_oracle_extract(oe, img.data, (int)img.step, img.cols, img.rows, okp.data(), odesc.data(), cap, nullptr);
+  REQUIRE(n == (int)kps.size(), "keypoint count %zu vs oracle %d", kps.size(), n);
+  REQUIRE(n > 100, "too few keypoints (%d) for a meaningful test", n);
+  REQUIRE(desc.rows == n && desc.cols == 32, "descriptor shape %dx%d", desc.rows, desc.cols);
+  REQUIRE(std::memcmp(kps.data(), okp.data(), (size_t)n * 28) == 0, "cv::KeyPoint records differ from the oracle");
+  for (int r = 0; r < n; ++r) REQUIRE(std::memcmp(desc.ptr<unsigned char>(r), &odesc[(size_t)r * 32], 32) == 0, "descriptor row %d differs", r);
+  if (check_pyramid) {
+    for (int l = 0; l < ex.GetLevels(); ++l) {
+      int c = 0, r = 0;
+      orb_oracle_level_dims(oe, l, &c, &r);
+      const cv::Mat& m = ex.mvImagePyramid[l];
+      REQUIRE(m.cols == c && m.rows == r, "mvImagePyramid[%d] is %dx%d, oracle %dx%d", l, m.cols, m.rows, c, r);
+      const uint8_t* op = orb_oracle_level_ptr(oe, l);
+      for (int y = 0; y < r; ++y) REQUIRE(std::memcmp(m.ptr<unsigned char>(y), op + (size_t)y * c, c) == 0, "mvImagePyramid[%d] row %d differs", l, y);
+    }
+  }
+  return 0;
+}
+
+int main(int argc, char** argv) {
+  if (argc < 5) {
+    std::fprintf(stderr, "usage: %s frame.raw width height nfeatures [frame2.raw]\n", argv[0]);
+    return 2;
+  }
+  const int W = std::atoi(argv[2]), H = std::atoi(argv[3]), nf = std::atoi(argv[4]);
+  std::vector<unsigned char> f0, f1;
+  REQUIRE(read_raw(argv[1], f0, (size_t)W * H), "cannot read %s", argv[1]);
+  const bool two = argc > 5;
+  if (two) REQUIRE(read_raw(argv[5], f1, (size_t)W * H), "cannot read %s", argv[5]);
+
+  // ---- constructor tables and getters (include/ORBextractor.h:134-182)
+  ORB_SLAM2::ORBextractor ex(nf, 1.2f, 8, 20, 7);
+  orb_oracle_extractor* oe = orb_oracle_create(nf, 1.2f, 8, 20, 7, 0);
+  REQUIRE(ex.GetLevels() == 8, "GetLevels");
+  REQUIRE(ex.GetScaleFactor() == 1.2f, "GetScaleFactor");
+  for (int what = 0; what < 4; ++what) {
+    float t[8];
+    orb_oracle_get_table(oe, what, t);
+    const std::vector<float> got = what == 0 ? ex.GetScaleFactors() : what == 1 ? ex.GetInverseScaleFactors()
+                                   : what == 2 ? ex.GetScaleSigmaSquares() : ex.GetInverseScaleSigmaSquares();
+    REQUIRE(got.size() == 8 && std::memcmp(got.data(), t, sizeof(t)) == 0, "table %d differs from the oracle", what);
+  }
+
+  // ---- operator(): strided input (ROI of a wider buffer), empty mask, like Frame::ExtractORB (src/Frame.cc:468-481)
+  std::vector<unsigned char> wide((size_t)(W + 13) * H, 0);
+  for (int y = 0; y < H; ++y) std::memcpy(&wide[(size_t)y * (W + 13)], &f0[(size_t)y * W], W);
+  cv::Mat img(H, W, CV_8UC1, wide.data(), (size_t)W + 13);
+  std::vector<cv::KeyPoint> kps;
+  cv::Mat desc;
+  ex(img, cv::Mat(), kps, desc);
+  cv::Mat contiguous(H, W, CV_8UC1, f0.data());
+  if (compare_with_oracle(oe, contiguous, kps, desc, ex, true)) return 1;
+  std::printf("operator(): %zu keypoints, descriptors and mvImagePyramid bit-exact vs oracle\n", kps.size());
+
+  // empty image: outputs untouched (src/ORBextractor.cc:1966-1967)
+  const size_t before = kps.size();
+  ex(cv::Mat(), cv::Mat(), kps, desc);
+  REQUIRE(kps.size() == before && desc.rows == (int)before, "empty image must leave the outputs untouched");
+
+  // ---- batched stereo pair + brute-force matching left -> right
+  if (two) {
+    cv::Mat right(H, W, CV_8UC1, f1.data());
+    std::vector<cv::Mat> pair{contiguous, right};
+    std::vector<std::vector<cv::KeyPoint>> bk;
+    std::vector<cv::Mat> bd;
+    ex.ExtractBatch(pair, bk, bd);
+    if (compare_with_oracle(oe, right, bk[1], bd[1], ex, true)) return 1;   // oracle state now = right image
+    if (compare_with_oracle(oe, contiguous, bk[0], bd[0], ex, false)) return 1;
+    std::printf("ExtractBatch: %zu + %zu keypoints bit-exact vs oracle\n", bk[0].size(), bk[1].size());
+
+    std::vector<ORB_SLAM2::ORBmatcher::Knn2> knn;
+    ORB_SLAM2::ORBmatcher::BruteForceKnn2(bd[0], bd[1], knn);
+    std::vector<orb_oracle_knn2> want(bd[0].rows);
+    orb_oracle_hamming_knn(bd[0].ptr<unsigned char>(0), bd[0].rows, bd[1].ptr<unsigned char>(0), bd[1].rows, 0, 256, want.data(), 4);
+    for (int i = 0; i < bd[0].rows; ++i)
+      REQUIRE(knn[i].bestDist == want[i].d1 && knn[i].bestDist2 == want[i].d2 && knn[i].bestIdx == want[i].i1 && knn[i].bestIdx2 == want[i].i2,
+              "kNN row %d: (%d,%d,%lld,%lld) vs oracle (%d,%d,%lld,%lld)", i, knn[i].bestDist, knn[i].bestDist2, (long long)knn[i].bestIdx,
+              (long long)knn[i].bestIdx2, want[i].d1, want[i].d2, (long long)want[i].i1, (long long)want[i].i2);
+    ORB_SLAM2::ORBmatcher matcher(0.6f, true);
+    std::vector<int64_t> matches;
+    const int nacc = matcher.MatchBruteForce(bd[0], bd[1], matches);
+    int want_acc = 0;
+    for (int i = 0; i < bd[0].rows; ++i)
+      want_acc += want[i].d1 <= ORB_SLAM2::ORBmatcher::TH_LOW && (float)want[i].d1 < 0.6f * (float)want[i].d2;
+    REQUIRE(nacc == want_acc, "accepted matches %d vs oracle %d", nacc, want_acc);
+    // DescriptorDistance: scalar form, batch form and oracle agree on the matched pairs
+    std::vector<int> dist;
+    const int m = bd[0].rows < bd[1].rows ? bd[0].rows : bd[1].rows;
+    cv::Mat a(m, 32, CV_8U, bd[0].ptr<unsigned char>(0)), b(m, 32, CV_8U, bd[1].ptr<unsigned char>(0));
+    ORB_SLAM2::ORBmatcher::DescriptorDistanceBatch(a, b, dist);
+    for (int i = 0; i < m; ++i) {
+      const int o = orb_oracle_descriptor_distance(a.ptr<unsigned char>(i), b.ptr<unsigned char>(i));
+      REQUIRE(dist[i] == o && ORB_SLAM2::ORBmatcher::DescriptorDistance(a.row(i), b.row(i)) == o, "DescriptorDistance row %d", i);
+    }
+    std::printf("ORBmatcher: kNN over %d x %d bit-exact, %d ratio-test accepts, DescriptorDistance x %d exact\n", bd[0].rows, bd[1].rows, nacc, m);
+  }
+  orb_oracle_destroy(oe);
+  std::printf("PASS\n");
+  return 0;
+}

@@ -136,6 +136,8 @@ int orb_hamming_knn(const uint8_t* query, int q_mem, int Q, const uint8_t* db, i
 int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentinel, orb_knn2* out, void* stream);
 /* DescriptorDistance for n row pairs: out[i] = popcount(a[i] ^ b[i]); all device memory. */
 int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream);
+/* Same with HOST buffers (copies inside the call, default stream, synchronous). */
+int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out);
 int64_t orb_matcher_launch_count(void);
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */

@@ -32,7 +32,7 @@ SYMBOLS = [
     "orb_extract_batch_device", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
-    "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_matcher_launch_count", "orb_measure_popc_peak",
+    "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
 ]
 
 

@@ -649,6 +649,27 @@ int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n,
   return ORB_OK;
 }
 
+int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out) {
+  if (!a || !b || !out || n < 0) return fail(ORB_E_BADARG, "bad argument");
+  if (n == 0) return ORB_OK;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  if ((rc = ws->q.ensure((size_t)n * 32)) != ORB_OK) return rc;
+  if ((rc = ws->db.ensure((size_t)n * 32)) != ORB_OK) return rc;
+  if ((rc = ws->out.ensure((size_t)n * sizeof(int))) != ORB_OK) return rc;
+  CU(cudaMemcpyAsync(ws->q.p, a, (size_t)n * 32, cudaMemcpyHostToDevice, 0));
+  CU(cudaMemcpyAsync(ws->db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice, 0));
+  orb_launch_distance_batch(ws->q.as<uint8_t>(), ws->db.as<uint8_t>(), n, ws->out.as<int>(), 0);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out, ws->out.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, 0));
+  CU(cudaStreamSynchronize(0));
+  return ORB_OK;
+}
+
 int64_t orb_matcher_launch_count(void) { return orb_knn_launches(); }
 
 double orb_measure_popc_peak(int device) {

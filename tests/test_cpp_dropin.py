@@ -1,0 +1,50 @@
+"""The C++ drop-in layer (cpp/): ORB_SLAM2::ORBextractor / ORBmatcher with the reference's header surface
+(include/ORBextractor.h:80-250, include/ORBmatcher.h:54-62, 223-225) over the C ABI.
+
+CPU part: the layer builds, exports the reference's symbols and needs nothing but liborb_b200.so.
+GPU part: cpp/test_dropin runs operator(), ExtractBatch, mvImagePyramid and the matcher against the oracle, bit-exact."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPP = os.path.join(ROOT, "cpp")
+
+
+def _build():
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "orb_slam2_detailed_comments_b200", "csrc")], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", CPP], stdout=subprocess.DEVNULL)
+
+
+def test_dropin_builds_and_exports_reference_symbols():
+    _build()
+    out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(CPP, "liborb_slam2_frontend.so")], text=True)
+    for sym in ("ORB_SLAM2::ORBextractor::ORBextractor(int, float, int, int, int, int)",
+                "ORB_SLAM2::ORBextractor::operator()(cv::Mat const&, cv::Mat const&, std::vector<cv::KeyPoint",
+                "ORB_SLAM2::ORBmatcher::DescriptorDistance(cv::Mat const&, cv::Mat const&)",
+                "ORB_SLAM2::ORBmatcher::TH_LOW", "ORB_SLAM2::ORBmatcher::TH_HIGH", "ORB_SLAM2::ORBmatcher::HISTO_LENGTH"):
+        assert sym in out, sym
+    # the product layer must not link the oracle
+    needed = subprocess.check_output(["readelf", "-d", os.path.join(CPP, "liborb_slam2_frontend.so")], text=True)
+    assert "liborb_b200.so" in needed and "oracle" not in needed
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(640, 480, 1000), (1241, 376, 2000)])
+def test_dropin_matches_oracle_on_gpu(tmp_path, shape):
+    from orb_slam2_detailed_comments_b200 import synth
+    exe = os.path.join(CPP, "test_dropin")
+    if not os.path.exists(exe):
+        _build()
+    W, H, nf = shape
+    left = synth.synth_frame(W, H, 1234)
+    right = np.roll(left, -7, axis=1).copy()   # a shifted view as the right image: plenty of true matches
+    (tmp_path / "l.raw").write_bytes(left.tobytes())
+    (tmp_path / "r.raw").write_bytes(right.tobytes())
+    r = subprocess.run([exe, str(tmp_path / "l.raw"), str(W), str(H), str(nf), str(tmp_path / "r.raw")],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "PASS" in r.stdout
