@@ -191,7 +191,6 @@ def bench_extract_resident(ex, frames_dev, steps, warmup, world):
     for _ in range(warmup):
         ex.extract_batch_device(frames_dev, kps, desc, counts, sync=False)
     torch.cuda.synchronize()
-    ex.set_profiling(True)
     l0 = ex.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     _barrier(world)
@@ -203,6 +202,12 @@ def bench_extract_resident(ex, frames_dev, steps, warmup, world):
     _barrier(world)
     ms = _max_over_ranks(e0.elapsed_time(e1), world)
     launches = ex.launch_count - l0
+    # stage breakdown: a second, untimed run of the same steps with per-stage CUDA events; profiling serialises the passes
+    # on one stream (the timed run above overlaps consecutive passes on two streams), so the stage sum exceeds ms
+    ex.set_profiling(True)
+    for _ in range(steps):
+        ex.extract_batch_device(frames_dev, kps, desc, counts, sync=False)
+    torch.cuda.synchronize()
     stage_ms, passes = ex.stage_times()
     ex.set_profiling(False)
     return ms, launches, stage_ms, passes, int(counts.sum().item())
@@ -342,7 +347,7 @@ def run_b200(args):
     }
     if world == 1 and not args.no_cpu:
         cores = _host_cores()
-        n = int(min(max(4 * cores, 64), 512))
+        n = 512   # ~20-30 core-seconds of CPU work
         v, dt, _ = cpu_extract_rate(W, H, nf, n, cores)
         kv, kdt = cpu_knn_rate(cores)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",

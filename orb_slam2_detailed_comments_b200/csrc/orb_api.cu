@@ -71,16 +71,28 @@ struct orb_extractor {
   std::vector<int> quota;
   OrbGeom geom;            // valid when geom.width > 0
   int chunk = 0;           // frames per internal pass (workspace capacity)
-  int last_batch = 0;      // frames of the last pass still resident in the workspace
   int cap_ws = 0;
   long long launches = 0;
-  DevBuf tabs, pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, err, out_cnt;
+  DevBuf tabs, err;
+  // Two pass workspaces on two compute streams: consecutive internal passes alternate between them, so the latency-bound
+  // tail of pass p (quadtree, descriptors) overlaps the bandwidth/issue-bound head of pass p+1 (pyramid, FAST, blur).
+  // ws[0].st is the handle's public stream.
+  struct PassWs {
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev_join = nullptr;
+    int frames = 0;          // frames of the last pass run here
+    DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
+    DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
+    DevBuf* all[22] = {&pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
+                       &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
+  } ws[2];
+  int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
+  cudaEvent_t ev_fork = nullptr;
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  DevBuf stage_in[2], out_kps[2], out_desc[2], out_cnt2[2];
+  DevBuf stage_in[2], out_kps[2], out_desc[2];
   cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {};
   size_t h_cnt_cap = 0;    // ints in h_cnt
-  DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
   int* h_err = nullptr;    // pinned
   int* h_cnt = nullptr;    // pinned [batch * (1 + nlevels)]: counts, then per-level counts
   bool profile = false;    // per-stage CUDA-event timing (orb_extractor_set_profiling)
@@ -213,11 +225,15 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
 
 // ---- workspace -------------------------------------------------------------------------------------------
 static int default_chunk(const OrbGeom& g) {
-  // Frames per internal pass: keep pyramid + blurred copy of a pass inside the 126 MB L2 where possible.
+  // Frames per internal pass. Every stage is issue/latency bound rather than DRAM bound (profiles/), so L2 residency of a
+  // pass buys nothing and large passes win: they fill the 148 SMs for the small pyramid levels and the one-CTA-per-
+  // (frame, level) quadtree. Bounded by ~1.5 GB of workspace per pass (two workspaces exist) and 64 frames, which keeps
+  // >= 8 passes in a 512-frame call for the copy/compute pipeline of orb_extract_batch.
   const char* env = getenv("ORB_B200_CHUNK");
   if (env && atoi(env) > 0) return atoi(env);
-  const double per_frame = 2.0 * (double)g.frame_stride;
-  int c = (int)(96.0 * 1024 * 1024 / per_frame);
+  const double per_frame = 2.0 * (double)g.frame_stride + (double)g.ncells_total * (ORB_CELL_CAP + 1) * 4 +
+                           (double)g.raw_total * 9 + (double)g.node_total * 100;
+  int c = (int)(1.5e9 / per_frame);
   return std::max(1, std::min(c, 64));
 }
 
@@ -233,18 +249,22 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
   }
   const OrbGeom& g = e->geom;
   const int want = std::min(batch, default_chunk(g));
-  if (want > e->chunk || cap > e->cap_ws) {
+  if (want > e->chunk || cap > e->cap_ws || (batch > e->chunk && e->ws[1].pyr.p == nullptr)) {
+    for (int w = 0; w < 2; ++w) CU(cudaStreamSynchronize(e->ws[w].st));
     const size_t B = (size_t)std::max(want, e->chunk);
     const int capw = std::max(cap, e->cap_ws);
     const int nl = g.nlevels;
-#define ENS(buf, bytes) if ((rc = e->buf.ensure(bytes)) != ORB_OK) return rc
+    if ((rc = e->err.ensure(sizeof(int))) != ORB_OK) return rc;
+    const int nws = (batch > (int)B) ? 2 : 1;   // the second workspace only exists once a call needs more than one pass
+    for (int w = 0; w < nws; ++w) {
+      orb_extractor::PassWs& P = e->ws[w];
+#define ENS(buf, bytes) if ((rc = P.buf.ensure(bytes)) != ORB_OK) return rc
     ENS(pyr, B * g.frame_stride + 256);   // +256: the resize window loads may run 12 bytes past a row end
     ENS(blr, B * g.frame_stride + 256);
     ENS(cell_cnt, B * g.ncells_total * sizeof(int));
     ENS(cell_kp, B * g.ncells_total * ORB_CELL_CAP * sizeof(uint32_t));
     ENS(kept, B * g.node_total * sizeof(uint32_t));
     ENS(kept_cnt, B * nl * sizeof(int));
-    ENS(err, sizeof(int));
     ENS(out_cnt, B * sizeof(int));
     ENS(q_key, B * g.raw_total * sizeof(uint32_t));
     ENS(q_knode, B * g.raw_total * sizeof(int));
@@ -261,26 +281,28 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     ENS(q_cslot, B * g.node_total * 4 * sizeof(int));
     ENS(q_scan, B * g.node_total * sizeof(unsigned long long));
     ENS(q_rawn, B * nl * sizeof(int));
+      P.frames = 0;
+    }
 #undef ENS
     CU(cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream));
     e->chunk = (int)B;
     e->cap_ws = capw;
-    e->last_batch = 0;
   }
   return ORB_OK;
 }
 
 // One internal pass over `n` (<= chunk) device-resident frames; outputs to device pointers.
-static void run_pass(orb_extractor* e, const uint8_t* images, int step, long long image_stride, int n, OrbKeypoint* kps,
+static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, long long image_stride, int n, OrbKeypoint* kps,
                      uint8_t* desc, int cap, int* counts_dev) {
   const OrbGeom& g = e->geom;
-  cudaStream_t st = e->stream;
+  orb_extractor::PassWs& P = e->ws[w];
+  cudaStream_t st = P.st;
   QtScratch S;
-  S.key = e->q_key.as<uint32_t>(); S.knode = e->q_knode.as<int>(); S.kchild = e->q_kchild.as<uint8_t>();
-  S.bbox = e->q_bbox.as<int4>(); S.ncount = e->q_ncount.as<int>(); S.pidx = e->q_pidx.as<int>();
-  S.best = e->q_best.as<unsigned>(); S.ordA = e->q_ordA.as<int>(); S.ordB = e->q_ordB.as<int>(); S.par = e->q_par.as<int>();
-  S.cand = e->q_cand.as<unsigned long long>(); S.ccnt = e->q_ccnt.as<int>(); S.cslot = e->q_cslot.as<int>();
-  S.scan = e->q_scan.as<unsigned long long>(); S.raw_n = e->q_rawn.as<int>();
+  S.key = P.q_key.as<uint32_t>(); S.knode = P.q_knode.as<int>(); S.kchild = P.q_kchild.as<uint8_t>();
+  S.bbox = P.q_bbox.as<int4>(); S.ncount = P.q_ncount.as<int>(); S.pidx = P.q_pidx.as<int>();
+  S.best = P.q_best.as<unsigned>(); S.ordA = P.q_ordA.as<int>(); S.ordB = P.q_ordB.as<int>(); S.par = P.q_par.as<int>();
+  S.cand = P.q_cand.as<unsigned long long>(); S.ccnt = P.q_ccnt.as<int>(); S.cslot = P.q_cslot.as<int>();
+  S.scan = P.q_scan.as<unsigned long long>(); S.raw_n = P.q_rawn.as<int>();
   bool prof = e->profile;
   cudaEvent_t* ev = nullptr;
   if (prof) {
@@ -293,24 +315,26 @@ static void run_pass(orb_extractor* e, const uint8_t* images, int step, long lon
     if (prof) { ev = e->ev.data() + e->ev_used; e->ev_used += ORB_NUM_STAGES + 1; }
   }
   if (prof) cudaEventRecord(ev[0], st);
-  orb_launch_pyramid(images, step, image_stride, e->pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches);
+  orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[1], st);
-  orb_launch_fast(e->pyr.as<uint8_t>(), e->cell_cnt.as<int>(), e->cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
+  orb_launch_fast(P.pyr.as<uint8_t>(), P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[2], st);
-  orb_launch_blur(e->pyr.as<uint8_t>(), e->blr.as<uint8_t>(), g, n, st, &e->launches);
+  orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[3], st);
-  orb_launch_quadtree(e->cell_cnt.as<int>(), e->cell_kp.as<uint32_t>(), S, e->kept.as<uint32_t>(), e->kept_cnt.as<int>(),
+  orb_launch_quadtree(P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), S, P.kept.as<uint32_t>(), P.kept_cnt.as<int>(),
                       e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[4], st);
-  orb_launch_describe(e->pyr.as<uint8_t>(), e->blr.as<uint8_t>(), e->kept.as<uint32_t>(), e->kept_cnt.as<int>(), kps, desc, cap,
+  orb_launch_describe(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.kept.as<uint32_t>(), P.kept_cnt.as<int>(), kps, desc, cap,
                       counts_dev, e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[5], st);
-  e->last_batch = n;
+  P.frames = n;
+  e->last_ws = w;
 }
 
 static void resolve_stage_events(orb_extractor* e) {
   if (e->ev_used == 0) return;
   cudaStreamSynchronize(e->stream);
+  cudaStreamSynchronize(e->ws[1].st);
   for (size_t b = 0; b + ORB_NUM_STAGES < e->ev_used; b += ORB_NUM_STAGES + 1) {
     for (int i = 0; i < ORB_NUM_STAGES; ++i) {
       float ms = 0.f;
@@ -323,6 +347,7 @@ static void resolve_stage_events(orb_extractor* e) {
 
 static int check_err_flag(orb_extractor* e) {
   int flag = 0;
+  CU(cudaStreamSynchronize(e->ws[1].st));
   CU(cudaMemcpyAsync(&flag, e->err.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   CU(cudaGetLastError());
@@ -362,7 +387,11 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
   cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->ws[1].st, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[1].ev_join, cudaEventDisableTiming);
+  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
   if (ce != cudaSuccess) { delete e; return fail(ORB_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce)); }
+  e->ws[0].st = e->stream;
   *out = e;
   return ORB_OK;
 }
@@ -371,9 +400,12 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
-  DevBuf* bufs[] = {&e->tabs, &e->pyr, &e->blr, &e->cell_cnt, &e->cell_kp, &e->kept, &e->kept_cnt, &e->err, &e->stage_in[0], &e->stage_in[1],
-                    &e->out_kps[0], &e->out_kps[1], &e->out_desc[0], &e->out_desc[1], &e->out_cnt2[0], &e->out_cnt2[1], &e->out_cnt, &e->q_key, &e->q_knode, &e->q_kchild, &e->q_bbox, &e->q_ncount, &e->q_pidx, &e->q_best,
-                    &e->q_ordA, &e->q_ordB, &e->q_par, &e->q_cand, &e->q_ccnt, &e->q_cslot, &e->q_scan, &e->q_rawn};
+  if (e->ws[1].st) { cudaStreamSynchronize(e->ws[1].st); cudaStreamDestroy(e->ws[1].st); }
+  if (e->ws[1].ev_join) cudaEventDestroy(e->ws[1].ev_join);
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  for (int w = 0; w < 2; ++w)
+    for (DevBuf* b : e->ws[w].all) b->release();
+  DevBuf* bufs[] = {&e->tabs, &e->err, &e->stage_in[0], &e->stage_in[1], &e->out_kps[0], &e->out_kps[1], &e->out_desc[0], &e->out_desc[1]};
   for (DevBuf* b : bufs) b->release();
   if (e->h_cnt) cudaFreeHost(e->h_cnt);
   if (e->s_in) cudaStreamDestroy(e->s_in);
@@ -439,10 +471,21 @@ int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, 
   int rc = ensure_shape(e, width, height, batch, cap);
   if (rc != ORB_OK) return rc;
   const long long istride = (long long)step * height;
-  for (int f0 = 0; f0 < batch; f0 += e->chunk) {
+  // passes alternate between the two workspaces / streams; stage profiling keeps everything on the public stream
+  const bool two = batch > e->chunk && !e->profile;
+  if (two) {
+    CU(cudaEventRecord(e->ev_fork, e->stream));
+    CU(cudaStreamWaitEvent(e->ws[1].st, e->ev_fork, 0));
+  }
+  int pass = 0;
+  for (int f0 = 0; f0 < batch; f0 += e->chunk, ++pass) {
     const int n = std::min(e->chunk, batch - f0);
-    run_pass(e, images + (long long)f0 * istride, step, istride, n, reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap,
-             desc + (long long)f0 * cap * 32, cap, counts_dev + f0);
+    run_pass(e, two ? (pass & 1) : 0, images + (long long)f0 * istride, step, istride, n,
+             reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap, desc + (long long)f0 * cap * 32, cap, counts_dev + f0);
+  }
+  if (two) {
+    CU(cudaEventRecord(e->ws[1].ev_join, e->ws[1].st));
+    CU(cudaStreamWaitEvent(e->stream, e->ws[1].ev_join, 0));
   }
   CU(cudaGetLastError());
   if (sync) return check_err_flag(e);
@@ -476,7 +519,6 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
   const int nbuf = batch > e->chunk ? 2 : 1;
   for (int b = 0; b < nbuf; ++b) {
     if ((rc = e->stage_in[b].ensure((size_t)e->chunk * fbytes)) != ORB_OK) return rc;
-    if ((rc = e->out_cnt2[b].ensure((size_t)e->chunk * sizeof(int))) != ORB_OK) return rc;
     if (host_out) {
       if ((rc = e->out_kps[b].ensure((size_t)e->chunk * cap * sizeof(OrbKeypoint))) != ORB_OK) return rc;
       if ((rc = e->out_desc[b].ensure((size_t)e->chunk * cap * 32)) != ORB_OK) return rc;
@@ -506,15 +548,17 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
         CU(cudaMemcpyAsync(e->stage_in[b].as<uint8_t>() + (size_t)i * fbytes, images[f0 + i], fbytes - (step - width), kin, e->s_in));
     }
     CU(cudaEventRecord(e->ev_in[b], e->s_in));
-    // ---- compute stream
-    CU(cudaStreamWaitEvent(e->stream, e->ev_in[b], 0));
-    if (host_out && pass >= 2) CU(cudaStreamWaitEvent(e->stream, e->ev_out[b], 0));   // out buffers [b] drained
+    // ---- compute stream of workspace w (= b unless stage profiling serialises everything on the public stream)
+    const int w = e->profile ? 0 : b;
+    orb_extractor::PassWs& P = e->ws[w];
+    CU(cudaStreamWaitEvent(P.st, e->ev_in[b], 0));
+    if (host_out && pass >= 2) CU(cudaStreamWaitEvent(P.st, e->ev_out[b], 0));   // out buffers [b] drained
     OrbKeypoint* dk = host_out ? e->out_kps[b].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
     uint8_t* dd = host_out ? e->out_desc[b].as<uint8_t>() : desc + (long long)f0 * cap * 32;
-    run_pass(e, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, e->out_cnt2[b].as<int>());
-    CU(cudaMemcpyAsync(h_counts + f0, e->out_cnt2[b].p, n * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    CU(cudaMemcpyAsync(h_levels + (size_t)f0 * nl, e->kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-    CU(cudaEventRecord(e->ev_done[b], e->stream));
+    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, P.out_cnt.as<int>());
+    CU(cudaMemcpyAsync(h_counts + f0, P.out_cnt.p, n * sizeof(int), cudaMemcpyDeviceToHost, P.st));
+    CU(cudaMemcpyAsync(h_levels + (size_t)f0 * nl, P.kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, P.st));
+    CU(cudaEventRecord(e->ev_done[b], P.st));
     // ---- copy-out stream
     if (host_out) {
       CU(cudaStreamWaitEvent(e->s_out, e->ev_done[b], 0));
@@ -540,32 +584,34 @@ int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int
 int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurred, uint8_t* dst, int dst_step) {
   if (!e || !dst || e->geom.width == 0 || level < 0 || level >= e->geom.nlevels) return fail(ORB_E_BADARG, "bad argument");
   std::lock_guard<std::mutex> lk(e->mu);
-  if (index == -1) index = e->last_batch - 1;   // the last image of the last call
-  if (index < 0 || index >= e->last_batch) return fail(ORB_E_BADARG, "image %d is not resident (last pass held %d frames)", index, e->last_batch);
+  orb_extractor::PassWs& P = e->ws[e->last_ws];
+  if (index == -1) index = P.frames - 1;   // the last image of the last call
+  if (index < 0 || index >= P.frames) return fail(ORB_E_BADARG, "image %d is not resident (last pass held %d frames)", index, P.frames);
   const OrbLevel& L = e->geom.lv[level];
   if (dst_step < L.cols) return fail(ORB_E_BADARG, "dst_step too small");
   CU(cudaSetDevice(e->device));
-  const uint8_t* src = (blurred ? e->blr.as<uint8_t>() : e->pyr.as<uint8_t>()) + (size_t)index * e->geom.frame_stride + L.plane_off;
-  CU(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, L.cols, L.rows, cudaMemcpyDeviceToHost, e->stream));
-  CU(cudaStreamSynchronize(e->stream));
+  const uint8_t* src = (blurred ? P.blr.as<uint8_t>() : P.pyr.as<uint8_t>()) + (size_t)index * e->geom.frame_stride + L.plane_off;
+  CU(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, L.cols, L.rows, cudaMemcpyDeviceToHost, P.st));
+  CU(cudaStreamSynchronize(P.st));
   return ORB_OK;
 }
 
 int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keypoint* out, int cap) {
   if (!e || !out || e->geom.width == 0 || level < 0 || level >= e->geom.nlevels) return fail(ORB_E_BADARG, "bad argument");
   std::lock_guard<std::mutex> lk(e->mu);
-  if (index < 0 || index >= e->last_batch) return fail(ORB_E_BADARG, "image %d is not resident", index);
+  orb_extractor::PassWs& P = e->ws[e->last_ws];
+  if (index < 0 || index >= P.frames) return fail(ORB_E_BADARG, "image %d is not resident", index);
   CU(cudaSetDevice(e->device));
   const OrbGeom& g = e->geom;
   const OrbLevel& L = g.lv[level];
   int n = 0;
-  CU(cudaMemcpyAsync(&n, e->q_rawn.as<int>() + (size_t)index * g.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
-  CU(cudaStreamSynchronize(e->stream));
+  CU(cudaMemcpyAsync(&n, P.q_rawn.as<int>() + (size_t)index * g.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, P.st));
+  CU(cudaStreamSynchronize(P.st));
   n = std::min(n, L.raw_cap);
   if (n > cap) return fail(ORB_E_CAPACITY, "need room for %d raw keypoints", n);
   std::vector<uint32_t> keys(std::max(n, 1));
-  CU(cudaMemcpyAsync(keys.data(), e->q_key.as<uint32_t>() + (size_t)index * g.raw_total + L.raw_off, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
-  CU(cudaStreamSynchronize(e->stream));
+  CU(cudaMemcpyAsync(keys.data(), P.q_key.as<uint32_t>() + (size_t)index * g.raw_total + L.raw_off, (size_t)n * 4, cudaMemcpyDeviceToHost, P.st));
+  CU(cudaStreamSynchronize(P.st));
   for (int i = 0; i < n; ++i) {
     out[i].x = (float)(keys[i] & 0xfffu); out[i].y = (float)((keys[i] >> 12) & 0xfffu);
     out[i].size = 7.f; out[i].angle = -1.f; out[i].response = (float)(keys[i] >> 24);
