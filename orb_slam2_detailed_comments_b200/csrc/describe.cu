@@ -151,10 +151,11 @@ __device__ __forceinline__ void orb_sincos(float angle, float* s, float* c) {
 
 // Orientation (un-blurred level), descriptor (blurred level) and the final cv::KeyPoint (pt *= scale for level != 0).
 // One warp handles DESC_KPW keypoints of one frame back to back, so the per-lane tables stay in registers:
-//   * IC_Angle: lane = patch row v (31 rows). The row's 32 bytes u = -16..15 are 9 aligned 32-bit loads funnel-shifted
-//     into 8 words; m10 += dp4a(word, [u masked by the disc]), rowsum += dp4a(word, [disc mask]); m01 = v * rowsum;
+//   * IC_Angle: lane = patch row v (31 rows). The row's 32 bytes u = -16..15 are 9 aligned words (staged through shared
+//     memory by coalesced loads) funnel-shifted into 8 words; m10 += dp4a(word, [u masked by the disc]), rowsum += dp4a(word, [disc mask]); m01 = v * rowsum;
 //     two REDUX adds finish the moments (exact int32).
-//   * rBRIEF: lane = descriptor byte; its 8 test pairs are 32 float registers (x0, y0, x1, y1).
+//   * rBRIEF: lane = descriptor byte; its 8 test pairs (x0, y0, x1, y1 as floats) come from shared memory, one LDS.128 each;
+//     the 512 pixel gathers hit the staged 37 x 40-byte patch in shared memory.
 #define DESC_WARPS 8
 #define DESC_KPW 8
 __device__ __forceinline__ int dp4a_u8_s8(unsigned a, unsigned b, int c) {   // a: unsigned bytes, b: signed bytes
@@ -183,29 +184,37 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
   }
   const int w_first = (blockIdx.x * DESC_WARPS + warp) * DESC_KPW;
   const int w_end = min(min(w_first + DESC_KPW, total), cap);
+  // rBRIEF pattern as floats, [test bit][lane] so that one LDS.128 per test is conflict-free (256 threads = 256 test pairs)
+  __shared__ float4 s_pat[8 * 32];
+  {
+    const char4 p = reinterpret_cast<const char4*>(d_pattern)[lane * 8 + warp];
+    s_pat[warp * 32 + lane] = make_float4((float)p.x, (float)p.y, (float)p.z, (float)p.w);
+  }
+  __syncthreads();
   if (w_first >= w_end) return;
 
   // per-lane constants
   const int v = lane - ORB_HALF_PATCH;                   // patch row of this lane (lane 31: none)
-  unsigned cu[8], cm[8];
+  unsigned dm[8];                                        // byte mask of the disc in this lane's row, words u = -16 + 4i .. + 3
   {
     const int hw = lane < 31 ? c_umax[v < 0 ? -v : v] : -1;   // half width of the disc in this row (:866-910, symmetric)
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      cu[i] = 0u; cm[i] = 0u;
+      dm[i] = 0u;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int u = -16 + 4 * i + j;
-        if ((u < 0 ? -u : u) <= hw) { cu[i] |= ((unsigned)u & 0xffu) << (8 * j); cm[i] |= 1u << (8 * j); }
+        if ((u < 0 ? -u : u) <= hw) dm[i] |= 0xffu << (8 * j);
       }
     }
   }
-  float px0[8], py0[8], px1[8], py1[8];
-#pragma unroll
-  for (int bit = 0; bit < 8; ++bit) {
-    const char4 p = reinterpret_cast<const char4*>(d_pattern)[lane * 8 + bit];
-    px0[bit] = (float)p.x; py0[bit] = (float)p.y; px1[bit] = (float)p.z; py1[bit] = (float)p.w;
-  }
+  // per-warp staging: the 31 x 36-byte IC_Angle window of the un-blurred level and the 37 x 40-byte descriptor patch of the
+  // blurred level are fetched with coalesced 32-bit loads (row-major over the lanes) and then gathered from shared memory
+  __shared__ unsigned s_ic[DESC_WARPS][31 * 9 + 1];
+  __shared__ unsigned s_pt[DESC_WARPS][37 * 10 + 2];
+  unsigned* ic = s_ic[warp];
+  unsigned* pt = s_pt[warp];
+  const uint8_t* ptb = reinterpret_cast<const uint8_t*>(pt);
 
   for (int w = w_first; w < w_end; ++w) {
     const int level = __popc(__ballot_sync(0xffffffffu, lane < g.nlevels && cinc <= w));
@@ -214,21 +223,43 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     const int pitch = L.pitch;
     const uint32_t q = kept[(long long)frame * g.node_total + L.node_off + (w - base)];
     const int x = (int)(q & 0xfffu) + ORB_MIN_BORDER, y = (int)((q >> 12) & 0xfffu) + ORB_MIN_BORDER;   // :1573-1589
-    const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)y * pitch + x;
-    // IC_Angle (:104-161)
+    const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off;
+    // all global loads of this keypoint are issued up front
+    const int xi = (x - 16) & ~3, xp = (x - 18) & ~3;          // planes are 16-byte aligned: column alignment == address alignment
+    const unsigned* icg = reinterpret_cast<const unsigned*>(pyr + off + (long long)(y - 15) * pitch + xi);
+    const unsigned* ptg = reinterpret_cast<const unsigned*>(blr + off + (long long)(y - 18) * pitch + xp);
+    const int pw = pitch >> 2;
+    unsigned ra[9], rp[12];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+      const int idx = lane + 32 * i;
+      ra[i] = idx < 31 * 9 ? __ldg(icg + (idx / 9) * pw + (idx % 9)) : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < 12; ++i) {
+      const int idx = lane + 32 * i;
+      rp[i] = idx < 37 * 10 ? __ldg(ptg + (idx / 10) * pw + (idx % 10)) : 0u;
+    }
+    __syncwarp();                                              // the previous keypoint's gathers are done
+#pragma unroll
+    for (int i = 0; i < 9; ++i)
+      if (lane + 32 * i < 31 * 9) ic[lane + 32 * i] = ra[i];
+    __syncwarp();
+    // IC_Angle (:104-161): lane = row v
     int m10 = 0, rs = 0;
     if (lane < 31) {
-      const uint8_t* rp = pyr + off + (long long)v * pitch - 16;
-      const unsigned sh = 8u * (unsigned)((uintptr_t)rp & 3);
-      const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)rp & ~(uintptr_t)3);
+      const unsigned sh = 8u * (unsigned)((x - 16) & 3);
       unsigned a[9];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) a[i] = __ldg(ap + i);
+      for (int i = 0; i < 9; ++i) a[i] = ic[lane * 9 + i];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const unsigned wv = __funnelshift_r(a[i], a[i + 1], sh);
-        m10 = dp4a_u8_s8(wv, cu[i], m10);
-        rs = (int)__dp4a(wv, cm[i], (unsigned)rs);
+        const unsigned wv = __funnelshift_r(a[i], a[i + 1], sh) & dm[i];
+        const int u0 = -16 + 4 * i;                       // signed byte coefficients u0 .. u0 + 3 (compile-time constant)
+        const unsigned cu = ((unsigned)u0 & 0xffu) | (((unsigned)(u0 + 1) & 0xffu) << 8) | (((unsigned)(u0 + 2) & 0xffu) << 16) |
+                            (((unsigned)(u0 + 3) & 0xffu) << 24);
+        m10 = dp4a_u8_s8(wv, cu, m10);
+        rs = (int)__dp4a(wv, 0x01010101u, (unsigned)rs);
       }
     }
     m10 = __reduce_add_sync(0xffffffffu, m10);
@@ -237,16 +268,21 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
     float a, b;
     orb_sincos(__fmul_rn(angle, factorPI), &b, &a);
-    // computeOrbDescriptor (:177-254)
-    const uint8_t* bc = blr + off;
+    // computeOrbDescriptor (:177-254) on the staged patch: byte (r, c) of the patch is pt[(r + 18) * 40 + c + x - xp]
+#pragma unroll
+    for (int i = 0; i < 12; ++i)
+      if (lane + 32 * i < 37 * 10) pt[lane + 32 * i] = rp[i];
+    __syncwarp();
+    const uint8_t* bc = ptb + 18 * 40 + (x - xp);
     int val = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; ++bit) {
-      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(px0[bit], b), __fmul_rn(py0[bit], a)));
-      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(px0[bit], a), __fmul_rn(py0[bit], b)));
-      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(px1[bit], b), __fmul_rn(py1[bit], a)));
-      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(px1[bit], a), __fmul_rn(py1[bit], b)));
-      const int t0 = __ldg(bc + r0 * pitch + c0), t1 = __ldg(bc + r1 * pitch + c1);
+      const float4 p = s_pat[bit * 32 + lane];   // x0, y0, x1, y1
+      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)));
+      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)));
+      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)));
+      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)));
+      const int t0 = bc[r0 * 40 + c0], t1 = bc[r1 * 40 + c1];
       val |= (t0 < t1) << bit;
     }
     const long long o = (long long)frame * cap + w;

@@ -11,7 +11,7 @@
 //   1. the band window (+3 px halo) is staged in shared memory with 16-byte loads;
 //   2. quick reject, 4 pixels per thread with byte-SIMD (VABSDIFF4 + carry-free byte compares): a 9-arc always
 //      holds one of {up, down} and one of {left, right}, so min(max|d_ud|, max|d_lr|) > minTh is necessary for
-//      S >= minTh; survivors are compacted into a per-warp candidate list (ballot);
+//      S >= minTh; a thread keeps its survivors as bit masks and one warp scan compacts them into the warp's candidate list;
 //   3. candidates are scored 32 at a time with full lanes. The dark and the bright arc tests share one instruction
 //      stream: ring pixel r_k becomes the 16-bit lane pair [256 + v - r_k, 256 - v + r_k] (one IMAD) and
 //      max_arcs(min_9) of both lanes is 16 + 16 VIMNMX3.U16x2 + an 8-op max tree. Corners (S >= minTh) are
@@ -24,7 +24,7 @@
 
 #define FAST_THREADS 256
 #define FAST_WARPS 8
-#define FAST_WP 288      // window row pitch in smem: 16 B front pad + <= 272 B
+#define FAST_WP 304      // window row pitch in smem: 16 B front pad + <= 272 B; 76 words: 8 consecutive rows start in 8 different banks
 #define FAST_SP 272      // score plane row pitch
 #define FAST_BP 11       // survivor bit plane row pitch in words (window columns < 288 -> 9 words, +2 for the 64-bit extract)
 
@@ -96,24 +96,30 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   const int nvec = (X1 - xa + 15) >> 4;
   const uint8_t* src = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)iniY * L.pitch + xa;
   // 1. stage the window; clear the score plane and the survivor bit planes
+  const unsigned inv_nvec = 65536u / (unsigned)nvec + 1u;   // i / nvec == (i * inv) >> 16 for i < 65 * 18
   for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
-    const int y = i / nvec, v = i - y * nvec;
+    const int y = (int)(((unsigned)i * inv_nvec) >> 16), v = i - y * nvec;
     *reinterpret_cast<uint4*>(win + y * FAST_WP + 16 + 16 * v) = *reinterpret_cast<const uint4*>(src + (long long)y * L.pitch + 16 * v);
   }
   for (int i = tid; i < (dh + 2) * (FAST_SP / 16); i += FAST_THREADS) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < 2 * (sc_rows - 2) * FAST_BP; i += FAST_THREADS) pl_min[i] = 0u;
   __syncthreads();
 
-  // 2. quick reject by pixel quads, per-warp compaction (warp w owns detection rows w, w + 8, ...)
+  // 2. quick reject by pixel quads, per-warp compaction
   const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
   const int qbase = dx0 & ~3;
   const int nq = (dx1 - qbase + 3) >> 2;                 // <= 64
   const unsigned th4 = (unsigned)g.min_th * 0x01010101u, t1 = th4 + 0x01010101u;
   uint16_t* list = lists + warp * list_cap;
   const uint32_t lt = (1u << lane) - 1u;
-  int cnt = 0;
-  for (int h = 0; h < nq; h += 32) {
-    const int q = h + lane;
+  // warp w owns the detection rows [w * R, (w + 1) * R), R = ceil(dh / 8) <= 8
+  const int rpw = (dh + FAST_WARPS - 1) / FAST_WARPS;
+  const int row0 = warp * rpw, row1 = min(row0 + rpw, dh);
+  // candidate bits of this thread: nibble ri of cand[hi] = pixels x..x+3 of quad (32*hi + lane) in row row0 + ri
+  unsigned cand[2] = {0u, 0u};
+#pragma unroll
+  for (int hi = 0; hi < 2; ++hi) {
+    const int q = 32 * hi + lane;
     const int x = qbase + 4 * q;
     unsigned colmask = 0;                                // bit 7 of byte k: column x + k is a detection column
     if (q < nq) {
@@ -121,26 +127,42 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
       for (int k = 0; k < 4; ++k)
         if (x + k >= dx0 && x + k < dx1) colmask |= 0x80u << (8 * k);
     }
-    for (int y = warp; y < dh; y += FAST_WARPS) {
-      const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
-      unsigned pass = 0;
-      if (colmask) {
+    if (colmask) {
+      int sh = 0;
+      for (int y = row0; y < row1; ++y, sh += 4) {
+        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
         const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c1 = *reinterpret_cast<const unsigned*>(row),
                        c2 = *reinterpret_cast<const unsigned*>(row + 4);
         const unsigned up = *reinterpret_cast<const unsigned*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + 3 * FAST_WP);
         const unsigned lf = __byte_perm(c0, c1, 0x4321), rt = __byte_perm(c1, c2, 0x6543);
         const unsigned au = __vabsdiffu4(c1, up), ad = __vabsdiffu4(c1, dn), al = __vabsdiffu4(c1, lf), ar = __vabsdiffu4(c1, rt);
+        unsigned pass;
         if (SMALL_TH) pass = (fast_gt4(au, t1) | fast_gt4(ad, t1)) & (fast_gt4(al, t1) | fast_gt4(ar, t1)) & colmask;
         else pass = (__vcmpgtu4(au, th4) | __vcmpgtu4(ad, th4)) & (__vcmpgtu4(al, th4) | __vcmpgtu4(ar, th4)) & colmask;
+        cand[hi] |= ((pass * 0x204081u) >> 28) << sh;    // bits 7, 15, 23, 31 -> one nibble (no carries between the partial products)
       }
-      if (__any_sync(0xffffffffu, pass != 0)) {
+    }
+  }
+  // one warp scan places every thread's candidates in the warp's list (order is irrelevant)
+  int cnt;
+  {
+    const int c = __popc(cand[0]) + __popc(cand[1]);
+    int incl = c;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const bool f = (pass >> (8 * k + 7)) & 1u;
-          const uint32_t b = __ballot_sync(0xffffffffu, f);
-          if (f) list[cnt + __popc(b & lt)] = (uint16_t)((y << 9) | (x + k));
-          cnt += __popc(b);
-        }
+    for (int o = 1; o < 32; o <<= 1) {
+      const int yv = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += yv;
+    }
+    cnt = __shfl_sync(0xffffffffu, incl, 31);
+    int pos = incl - c;
+#pragma unroll
+    for (int hi = 0; hi < 2; ++hi) {
+      unsigned m = cand[hi];
+      const int xb = qbase + 4 * (32 * hi + lane);
+      while (m) {
+        const int j = __ffs(m) - 1;
+        m &= m - 1;
+        list[pos++] = (uint16_t)(((row0 + (j >> 2)) << 9) | (xb + (j & 3)));
       }
     }
   }
