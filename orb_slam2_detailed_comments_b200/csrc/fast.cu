@@ -115,22 +115,23 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   // warp w owns the detection rows [w * R, (w + 1) * R), R = ceil(dh / 8) <= 8
   const int rpw = (dh + FAST_WARPS - 1) / FAST_WARPS;
   const int row0 = warp * rpw, row1 = min(row0 + rpw, dh);
-  // candidate bits of this thread: nibble ri of cand[hi] = pixels x..x+3 of quad (32*hi + lane) in row row0 + ri
+  // candidate bits of this thread: nibble ri of cand[hi] = the 4 pixels of quad ((lane + 5*ri) & 31) + 32*hi in row row0 + ri.
+  // The per-row rotation spreads a textured blob (candidates cluster in 2-D) over many lanes, which bounds the longest
+  // per-lane list and with it the trip count of the divergent emission loop below.
   unsigned cand[2] = {0u, 0u};
+  const unsigned mfirst = 0x80808080u << (8 * (dx0 - qbase));                        // quad 0: columns >= dx0
+  const unsigned mlast = 0x80808080u >> (8 * (4 - (dx1 - (qbase + 4 * (nq - 1)))));   // quad nq-1: columns < dx1
+  for (int ri = 0; row0 + ri < row1; ++ri) {
+    const int y = row0 + ri;
+    const int rot = (lane + 5 * ri) & 31;
 #pragma unroll
-  for (int hi = 0; hi < 2; ++hi) {
-    const int q = 32 * hi + lane;
-    const int x = qbase + 4 * q;
-    unsigned colmask = 0;                                // bit 7 of byte k: column x + k is a detection column
-    if (q < nq) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (x + k >= dx0 && x + k < dx1) colmask |= 0x80u << (8 * k);
-    }
-    if (colmask) {
-      int sh = 0;
-      for (int y = row0; y < row1; ++y, sh += 4) {
-        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
+    for (int hi = 0; hi < 2; ++hi) {
+      const int q = rot + 32 * hi;
+      if (q < nq) {
+        unsigned colmask = 0x80808080u;                  // bit 7 of byte k: column x + k is a detection column
+        if (q == 0) colmask &= mfirst;
+        if (q == nq - 1) colmask &= mlast;
+        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + qbase + 4 * q;
         const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c1 = *reinterpret_cast<const unsigned*>(row),
                        c2 = *reinterpret_cast<const unsigned*>(row + 4);
         const unsigned up = *reinterpret_cast<const unsigned*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + 3 * FAST_WP);
@@ -139,11 +140,12 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
         unsigned pass;
         if (SMALL_TH) pass = (fast_gt4(au, t1) | fast_gt4(ad, t1)) & (fast_gt4(al, t1) | fast_gt4(ar, t1)) & colmask;
         else pass = (__vcmpgtu4(au, th4) | __vcmpgtu4(ad, th4)) & (__vcmpgtu4(al, th4) | __vcmpgtu4(ar, th4)) & colmask;
-        cand[hi] |= ((pass * 0x204081u) >> 28) << sh;    // bits 7, 15, 23, 31 -> one nibble (no carries between the partial products)
+        cand[hi] |= ((pass * 0x204081u) >> 28) << (4 * ri);   // bits 7, 15, 23, 31 -> one nibble (the partial products never carry)
       }
     }
   }
-  // one warp scan places every thread's candidates in the warp's list (order is irrelevant)
+  // one warp scan places every thread's candidates in the warp's list (order is irrelevant). Entry = hi:1 | lane:5 | ri:3 | k:2,
+  // decoded by full warps in the scoring loop
   int cnt;
   {
     const int c = __popc(cand[0]) + __popc(cand[1]);
@@ -154,27 +156,29 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
       if (lane >= o) incl += yv;
     }
     cnt = __shfl_sync(0xffffffffu, incl, 31);
-    int pos = incl - c;
+    uint16_t* out = list + (incl - c);
 #pragma unroll
     for (int hi = 0; hi < 2; ++hi) {
       unsigned m = cand[hi];
-      const int xb = qbase + 4 * (32 * hi + lane);
+      const unsigned code = (unsigned)((hi << 10) | (lane << 5));
       while (m) {
-        const int j = __ffs(m) - 1;
+        *out++ = (uint16_t)(code | (unsigned)(__ffs(m) - 1));
         m &= m - 1;
-        list[pos++] = (uint16_t)(((row0 + (j >> 2)) << 9) | (xb + (j & 3)));
       }
     }
   }
   __syncwarp();
 
-  // 3. score the candidates, 32 per step; corners (S >= minTh) are compacted in place to the front of the list
+  // 3. score the candidates, 32 per step; corners (S >= minTh) are compacted in place to the front of the list as (y << 9) | x
   int ncorner = 0;
   for (int c0 = 0; c0 < cnt; c0 += 32) {
     const int i = c0 + lane;
     int e = 0, s = 0;
     if (i < cnt) {
-      e = list[i];
+      const int code = list[i];
+      const int ri = (code >> 2) & 7;
+      const int q = (((code >> 5) + 5 * ri) & 31) + ((code >> 10) << 5);
+      e = ((row0 + ri) << 9) | (qbase + 4 * q + (code & 3));
       s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
     }
     const bool corner = s >= g.min_th;
