@@ -318,9 +318,18 @@ def run_b200(args):
     dom_ms = stage_ms[dom] / max(passes, 1)                       # per internal pass (pyramid: its 8 launches together)
     dom_bytes = sb[dom] * frames_per_launch
     dom_achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    traffic = None   # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu --set full capture
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tj = json.load(f)
+        if args.workload == "kitti":
+            t = tj["dram_bytes_per_launch"][dom]
+            traffic = (t["read"] + t["write"]) / tj["frames_per_launch"] * frames_per_launch
+    except Exception:
+        traffic = None
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": dom_achieved, "peak": peak, "unit": "GB/s",
-        "frac": dom_achieved / peak, "traffic": None, "peak_source": peak_src,
+        "frac": dom_achieved / peak, "traffic": traffic, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": dom_bytes, "avg_launch_ms": dom_ms, "launches": n_launch_dom,
         "share_of_step": stage_ms[dom] / total_stage,
         "pipeline": {"algorithmic_bytes_per_image": A, "achieved": per_rank_rate * A / 1e9, "frac": per_rank_rate * A / 1e9 / peak},

@@ -22,36 +22,44 @@ template <bool CLAMP>   // CLAMP: tap sum > 256 (legacy taps sum to 257): satura
 __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
                                                               const __grid_constant__ OrbGeom g) {
   __shared__ uint4 s_p[(BL_TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
-  int level = 0, t = blockIdx.x;
+  int level = 0;
 #pragma unroll 1
-  for (; level < g.nlevels; ++level) {
-    const int n = ((g.lv[level].cols + BL_TW - 1) / BL_TW) * ((g.lv[level].rows + BL_TH - 1) / BL_TH);
-    if (t < n) break;
-    t -= n;
-  }
-  if (level >= g.nlevels) return;
+  for (int l = 1; l < g.nlevels; ++l)
+    if ((int)blockIdx.x >= g.lv[l].blur_tile_base) level = l;
   const OrbLevel& L = g.lv[level];
-  const int tiles_x = (L.cols + BL_TW - 1) / BL_TW;
-  const int ty_ = t / tiles_x;
-  const int x0 = (t - ty_ * tiles_x) * BL_TW, y0 = ty_ * BL_TH;
+  const unsigned t = blockIdx.x - L.blur_tile_base;
+  const unsigned ty_ = (t * L.blur_inv_tx) >> 20;            // t / blur_tiles_x (host-checked range)
+  const int x0 = (int)(t - ty_ * L.blur_tiles_x) * BL_TW, y0 = (int)ty_ * BL_TH;
   const unsigned long long off = (unsigned long long)blockIdx.y * g.frame_stride + L.plane_off;
   const uint8_t* src = pyr + off;
-  const unsigned k0 = g.blur_taps[0], k1 = g.blur_taps[1], k2 = g.blur_taps[2], k3 = g.blur_taps[3];
-  const unsigned tapA = k0 | (k1 << 8) | (k2 << 16) | (k3 << 24), tapB = k2 | (k1 << 8) | (k0 << 16);
+  const unsigned tapA = g.blur_k[0], tapB = g.blur_k[1];
   const int pitch = L.pitch;
   // local row r <-> plane row y0 - 4 + r (row -4 and rows past rows + 3 only ever meet a zero tap)
+  // all 12 loads of this thread's two H-pass items (item = 4 pixels x 2 rows) are issued before any arithmetic
+  unsigned cw[2][2][3];
+  bool act[2];
 #pragma unroll
   for (int it = 0; it < 2; ++it) {
     const int i = threadIdx.x + it * BL_THREADS;   // 20 row pairs x 32 quads = 640 items
     const int k = i >> 5, q = i & 31;
     const int x = x0 + 4 * q;
-    if (x < L.cols) {
+    act[it] = x < L.cols;
+#pragma unroll
+    for (int rr = 0; rr < 2; ++rr) {
+      const int ry = min(y0 - 4 + 2 * k + rr, L.rows + 3);
+      const unsigned* row = reinterpret_cast<const unsigned*>(src + (long long)ry * pitch + x);
+      if (act[it]) { cw[it][rr][0] = __ldg(row - 1); cw[it][rr][1] = __ldg(row); cw[it][rr][2] = __ldg(row + 1); }
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int i = threadIdx.x + it * BL_THREADS;
+    const int k = i >> 5, q = i & 31;
+    if (act[it]) {
       unsigned h[2][4];
 #pragma unroll
       for (int rr = 0; rr < 2; ++rr) {
-        const int ry = min(y0 - 4 + 2 * k + rr, L.rows + 3);
-        const unsigned* row = reinterpret_cast<const unsigned*>(src + (long long)ry * pitch + x);
-        const unsigned c0 = row[-1], c1 = row[0], c2 = row[1];
+        const unsigned c0 = cw[it][rr][0], c1 = cw[it][rr][1], c2 = cw[it][rr][2];
         // W(a) = bytes B[a..a+3] of the 12 loaded bytes B[0..11] = pixels x-4 .. x+7; pixel j: W(j+1).tapA + W(j+5).tapB
         const unsigned w1 = __byte_perm(c0, c1, 0x4321), w2 = __byte_perm(c0, c1, 0x5432), w3 = __byte_perm(c0, c1, 0x6543),
                        w5 = __byte_perm(c1, c2, 0x4321), w6 = __byte_perm(c1, c2, 0x5432), w7 = __byte_perm(c1, c2, 0x6543);
@@ -74,9 +82,9 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __r
   for (int i = 0; i < 6; ++i) P[i] = s_p[2 * seg + i][q];
   // even local row t = 2m: [0,k0].P(m-2) + [k1,k2].P(m-1) + [k3,k2].P(m) + [k1,k0].P(m+1)
   // odd  local row t = 2m+1: [k0,k1].P(m-1) + [k2,k3].P(m) + [k2,k1].P(m+1) + [k0,0].P(m+2)
-  const unsigned e0 = k0 << 8, e1 = k1 | (k2 << 8), e2 = k3 | (k2 << 8), e3 = k1 | (k0 << 8);
-  const unsigned o0 = k0 | (k1 << 8), o1 = k2 | (k3 << 8), o2 = k2 | (k1 << 8), o3 = k0;
-  uint8_t* dst = blr + off;
+  const unsigned e0 = g.blur_k[2], e1 = g.blur_k[3], e2 = g.blur_k[4], e3 = g.blur_k[5];
+  const unsigned o0 = g.blur_k[6], o1 = g.blur_k[7], o2 = g.blur_k[8], o3 = g.blur_k[9];
+  uint8_t* dst = blr + off + (long long)(y0 + 4 * seg) * pitch + x;
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     const int y = y0 + 4 * seg + r;
@@ -95,7 +103,7 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __r
       }
       // byte 2 of each accumulator is the output pixel
       const unsigned lo = __byte_perm(c[0], c[1], 0x0062), hi = __byte_perm(c[2], c[3], 0x0062);
-      *reinterpret_cast<unsigned*>(dst + (long long)y * pitch + x) = __byte_perm(lo, hi, 0x5410);
+      *reinterpret_cast<unsigned*>(dst + r * pitch) = __byte_perm(lo, hi, 0x5410);
     }
   }
 }
@@ -304,13 +312,10 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
 }
 
 void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
-  int tiles = 0;
-  for (int l = 0; l < g.nlevels; ++l)
-    tiles += ((g.lv[l].cols + BL_TW - 1) / BL_TW) * ((g.lv[l].rows + BL_TH - 1) / BL_TH);
   int sum = g.blur_taps[3];
   for (int i = 0; i < 3; ++i) sum += 2 * g.blur_taps[i];
-  if (sum > 256) orb_blur_kernel<true><<<dim3(tiles, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
-  else orb_blur_kernel<false><<<dim3(tiles, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
+  if (sum > 256) orb_blur_kernel<true><<<dim3(g.blur_tiles_total, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
+  else orb_blur_kernel<false><<<dim3(g.blur_tiles_total, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
   ++*launches;
 }
 

@@ -157,6 +157,14 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
   g.ini_th = e->prm.ini_th_fast; g.min_th = e->prm.min_th_fast;
   static const int taps_new[7] = {18, 34, 48, 56, 48, 34, 18}, taps_old[7] = {18, 34, 49, 55, 49, 34, 18};
   memcpy(g.blur_taps, (e->prm.flags & ORB_FLAG_LEGACY_BLUR) ? taps_old : taps_new, sizeof(g.blur_taps));
+  {
+    const unsigned k0 = g.blur_taps[0], k1 = g.blur_taps[1], k2 = g.blur_taps[2], k3 = g.blur_taps[3];
+    const unsigned kk[10] = {k0 | (k1 << 8) | (k2 << 16) | (k3 << 24), k2 | (k1 << 8) | (k0 << 16),        // H pass, DP4A
+                             k0 << 8, k1 | (k2 << 8), k3 | (k2 << 8), k1 | (k0 << 8),                     // V pass, even rows
+                             k0 | (k1 << 8), k2 | (k3 << 8), k2 | (k1 << 8), k0};                         // V pass, odd rows
+    memcpy(g.blur_k, kk, sizeof(kk));
+  }
+  int btiles = 0;
   size_t plane = 0;
   int cells = 0, raw = 0, nodes = 0, tab = 0, ftiles = 0;
   tabs.clear();
@@ -185,6 +193,10 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.fast_nseg = (L.nCols + L.fast_G - 1) / L.fast_G;
     L.fast_tile_base = ftiles;
     ftiles += L.fast_nseg * L.nRows;
+    L.blur_tiles_x = (L.cols + 127) / 128;
+    L.blur_tile_base = btiles;
+    L.blur_inv_tx = (1u << 20) / (unsigned)L.blur_tiles_x + 1u;
+    btiles += L.blur_tiles_x * ((L.rows + 31) / 32);
     L.nIni = (int)roundf((float)(L.maxBX - ORB_MIN_BORDER) / (L.maxBY - ORB_MIN_BORDER));
     if (L.nIni < 1) return fail(ORB_E_SHAPE, "aspect ratio < 0.5: the reference divides by nIni == 0 (src/ORBextractor.cc:1059)");
     L.hX = (float)(L.maxBX - ORB_MIN_BORDER) / L.nIni;
@@ -217,6 +229,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
       tab += L.xtab_len + ytab_len;
     }
   }
+  g.blur_tiles_total = btiles;
   g.ncells_total = cells; g.raw_total = raw; g.node_total = nodes; g.fast_tiles_total = ftiles;
   g.frame_stride = plane;
   e->geom = g;
@@ -534,8 +547,11 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
   int* h_levels = e->h_cnt + batch;
   const cudaMemcpyKind kin = in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   int pass = 0;
-  for (int f0 = 0; f0 < batch; f0 += e->chunk, ++pass) {
-    const int n = std::min(e->chunk, batch - f0);
+  for (int f0 = 0, n = 0; f0 < batch; f0 += n, ++pass) {
+    // ramp-up: the first passes are short so that the first kernels start after a short copy (pipeline fill)
+    const int full = e->chunk;
+    const int want = (batch > 2 * full && pass < 2) ? std::max(full >> (2 - pass), 1) : full;
+    n = std::min(want, batch - f0);
     const int b = pass & 1;
     // ---- copy-in stream: stage_in[b] is free once pass-2 finished computing
     if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_done[b], 0));

@@ -37,6 +37,8 @@ struct OrbLevel {
   int pyr_fast;              // 1: 4-pixel window kernel applies (horizontal ratio <= 2)
   int fast_G, fast_nseg;     // FAST tile = one cell row x fast_G cells; segments per cell row
   int fast_tile_base;        // first FAST tile of this level
+  int blur_tile_base, blur_tiles_x;   // 128 x 32 blur tiles: first tile of this level, tiles per row
+  unsigned blur_inv_tx;      // t / blur_tiles_x == (t * blur_inv_tx) >> 20
 };
 
 struct OrbGeom {
@@ -47,6 +49,8 @@ struct OrbGeom {
   unsigned long long frame_stride;   // bytes per frame in pyramid / blurred
   int ini_th, min_th;
   int blur_taps[7];
+  unsigned blur_k[10];       // packed tap words of the blur kernel: tapA, tapB (DP4A), e0..e3, o0..o3 (DP2A)
+  int blur_tiles_total;
   OrbLevel lv[ORB_MAX_LEVELS];
 };
 
