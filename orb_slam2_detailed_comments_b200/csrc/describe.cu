@@ -206,15 +206,10 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
   unsigned dm[8];                                        // byte mask of the disc in this lane's row, words u = -16 + 4i .. + 3
   {
     const int hw = lane < 31 ? c_umax[v < 0 ? -v : v] : -1;   // half width of the disc in this row (:866-910, symmetric)
+    // one bit per byte u = -16..15: bits [16 - hw, 16 + hw]; each nibble is then widened to a byte mask
+    const unsigned bits = hw >= 0 ? ((2u << (2 * hw)) - 1u) << (16 - hw) : 0u;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      dm[i] = 0u;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int u = -16 + 4 * i + j;
-        if ((u < 0 ? -u : u) <= hw) dm[i] |= 0xffu << (8 * j);
-      }
-    }
+    for (int i = 0; i < 8; ++i) dm[i] = ((((bits >> (4 * i)) & 15u) * 0x00204081u) & 0x01010101u) * 0xffu;
   }
   // per-warp staging: the 31 x 36-byte IC_Angle window of the un-blurred level and the 37 x 40-byte descriptor patch of the
   // blurred level are fetched with coalesced 32-bit loads (row-major over the lanes) and then gathered from shared memory

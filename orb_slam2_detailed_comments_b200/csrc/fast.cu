@@ -60,7 +60,124 @@ __device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned t1) {
   return (((a & 0x7f7f7f7fu) | 0x80808080u) - t1) | a;
 }
 
-template <bool SMALL_TH>   // SMALL_TH: minTh <= 126 (carry-free byte compare); otherwise the generic video intrinsic
+// Quick reject + compaction + scoring for the rows [row0, row1) of one warp.
+//   SECOND == false: candidates = pixels passing the compass test at iniTh (superset of all S >= iniTh);
+//   SECOND == true : candidates = pixels passing at minTh but not at iniTh (not scored yet), in the columns marked in `need`.
+// Candidate codes go to list[start ..], corners (S >= minTh) are compacted in place to list[start ..] as (y << 9) | x and
+// their score is written to the score plane. Returns the number of corners appended.
+template <bool SMALL_TH, bool SECOND>
+__device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint8_t* __restrict__ sc, const uint8_t* __restrict__ need,
+                                           uint16_t* __restrict__ list, int start, int row0, int row1, int qbase, int nq, int lane,
+                                           int ini_th, int min_th) {
+  const unsigned thi4 = (unsigned)ini_th * 0x01010101u, ti1 = thi4 + 0x01010101u;
+  const unsigned thm4 = (unsigned)min_th * 0x01010101u, tm1 = thm4 + 0x01010101u;
+  const uint32_t lt = (1u << lane) - 1u;
+  // candidate bits of this thread: nibble ri of cand[hi] = the 4 pixels of quad ((lane + 5*ri) & 31) + 32*hi in row row0 + ri.
+  // The per-row rotation spreads a textured blob (candidates cluster in 2-D) over many lanes.
+  unsigned cand[2] = {0u, 0u};
+  for (int ri = 0; row0 + ri < row1; ++ri) {
+    const int y = row0 + ri;
+    const int rot = (lane + 5 * ri) & 31;
+#pragma unroll
+    for (int hi = 0; hi < 2; ++hi) {
+      const int q = rot + 32 * hi;
+      if (q < nq) {
+        const int x = qbase + 4 * q;
+        const unsigned colmask = *reinterpret_cast<const unsigned*>(need + x);   // bit 7 of byte k: column x + k takes part
+        if (colmask) {
+          const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
+          const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c1 = *reinterpret_cast<const unsigned*>(row),
+                         c2 = *reinterpret_cast<const unsigned*>(row + 4);
+          const unsigned up = *reinterpret_cast<const unsigned*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + 3 * FAST_WP);
+          const unsigned lf = __byte_perm(c0, c1, 0x4321), rt = __byte_perm(c1, c2, 0x6543);
+          const unsigned au = __vabsdiffu4(c1, up), ad = __vabsdiffu4(c1, dn), al = __vabsdiffu4(c1, lf), ar = __vabsdiffu4(c1, rt);
+          unsigned pass;
+          if (SMALL_TH) {
+            pass = (fast_gt4(au, SECOND ? tm1 : ti1) | fast_gt4(ad, SECOND ? tm1 : ti1)) &
+                   (fast_gt4(al, SECOND ? tm1 : ti1) | fast_gt4(ar, SECOND ? tm1 : ti1));
+            if (SECOND) pass &= ~((fast_gt4(au, ti1) | fast_gt4(ad, ti1)) & (fast_gt4(al, ti1) | fast_gt4(ar, ti1)));
+          } else {
+            pass = (__vcmpgtu4(au, SECOND ? thm4 : thi4) | __vcmpgtu4(ad, SECOND ? thm4 : thi4)) &
+                   (__vcmpgtu4(al, SECOND ? thm4 : thi4) | __vcmpgtu4(ar, SECOND ? thm4 : thi4));
+            if (SECOND) pass &= ~((__vcmpgtu4(au, thi4) | __vcmpgtu4(ad, thi4)) & (__vcmpgtu4(al, thi4) | __vcmpgtu4(ar, thi4)));
+          }
+          pass &= colmask;
+          cand[hi] |= ((pass * 0x204081u) >> 28) << (4 * ri);   // bits 7, 15, 23, 31 -> one nibble (the partial products never carry)
+        }
+      }
+    }
+  }
+  // one warp scan places every thread's candidates in the warp's list (order is irrelevant). Entry = hi:1 | lane:5 | ri:3 | k:2,
+  // decoded by full warps in the scoring loop
+  int cnt;
+  {
+    const int c = __popc(cand[0]) + __popc(cand[1]);
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int yv = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += yv;
+    }
+    cnt = __shfl_sync(0xffffffffu, incl, 31);
+    uint16_t* out = list + start + (incl - c);
+#pragma unroll
+    for (int hi = 0; hi < 2; ++hi) {
+      unsigned m = cand[hi];
+      const unsigned code = (unsigned)((hi << 10) | (lane << 5));
+      while (m) {
+        *out++ = (uint16_t)(code | (unsigned)(__ffs(m) - 1));
+        m &= m - 1;
+      }
+    }
+  }
+  __syncwarp();
+  // score the candidates, 32 per step
+  int ncorner = 0;
+  for (int c0 = 0; c0 < cnt; c0 += 32) {
+    const int i = c0 + lane;
+    int e = 0, s = 0;
+    if (i < cnt) {
+      const int code = list[start + i];
+      const int ri = (code >> 2) & 7;
+      const int q = (((code >> 5) + 5 * ri) & 31) + ((code >> 10) << 5);
+      e = ((row0 + ri) << 9) | (qbase + 4 * q + (code & 3));
+      s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
+    }
+    const bool corner = s >= min_th;
+    __syncwarp();                                            // the reads of this chunk precede the in-place writes below
+    const uint32_t b = __ballot_sync(0xffffffffu, corner);
+    if (corner) {
+      sc[((e >> 9) + 1) * FAST_SP + (e & 511)] = (uint8_t)s;
+      list[start + ncorner + __popc(b & lt)] = (uint16_t)e;
+    }
+    ncorner += __popc(b);
+  }
+  return ncorner;
+}
+
+// 3x3 NMS of the corners list[0 .. n) against their neighbours inside the same cell's detection window.
+//   SECOND == false: corners with S >= iniTh -> plane `pl` (ini survivors);
+//   SECOND == true : corners in the columns marked in `need` (cells that found no ini survivor) -> plane `pl` (min survivors).
+template <bool SECOND>
+__device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const uint8_t* __restrict__ need, const uint16_t* __restrict__ list,
+                                         int n, int lane, uint32_t* __restrict__ pl, int wCell, int xa, int xlim, int ini_th) {
+  const unsigned inv = (1u << 20) / (unsigned)wCell + 1u;      // p / wCell == (p * inv) >> 20 for p < 4096, wCell < 256
+  for (int i = lane; i < n; i += 32) {
+    const int e = list[i];
+    const int y = e >> 9, x = e & 511;
+    const uint8_t* q = sc + (y + 1) * FAST_SP + x;
+    const int s = q[0];
+    if (SECOND ? (need[x] == 0) : (s < ini_th)) continue;
+    const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);
+    const unsigned r = p - ((p * inv) >> 20) * (unsigned)wCell;   // column inside the cell's detection window
+    bool ok = s > q[-FAST_SP] && s > q[FAST_SP];
+    if (r > 0) ok = ok && s > q[-1] && s > q[-FAST_SP - 1] && s > q[FAST_SP - 1];
+    if ((int)r < wCell - 1 && x + 1 < xlim) ok = ok && s > q[1] && s > q[-FAST_SP + 1] && s > q[FAST_SP + 1];
+    if (ok) atomicOr(&pl[y * FAST_BP + (x >> 5)], 1u << (x & 31));
+  }
+}
+
+template <bool SMALL_TH>   // SMALL_TH: iniTh <= 126 (carry-free byte compares); otherwise the generic video intrinsic
 __global__ void __launch_bounds__(FAST_THREADS)
 orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ cell_kp,
                      int* __restrict__ err_flag, int win_rows, int sc_rows, int list_cap, const __grid_constant__ OrbGeom g) {
@@ -70,6 +187,8 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   uint32_t* pl_min = reinterpret_cast<uint32_t*>(sc + sc_rows * FAST_SP);   // [sc_rows - 2][FAST_BP] NMS survivors, S >= minTh
   uint32_t* pl_ini = pl_min + (sc_rows - 2) * FAST_BP;                       //                         S >= iniTh
   uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + (sc_rows - 2) * FAST_BP);   // [FAST_WARPS][list_cap]
+  uint8_t* need = reinterpret_cast<uint8_t*>(lists + FAST_WARPS * list_cap);          // [FAST_WP] 0x80 = column takes part in the pass
+  __shared__ int s_retry;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
   int level = 0;
@@ -103,116 +222,60 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   }
   for (int i = tid; i < (dh + 2) * (FAST_SP / 16); i += FAST_THREADS) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < 2 * (sc_rows - 2) * FAST_BP; i += FAST_THREADS) pl_min[i] = 0u;
+  const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
+  for (int i = tid; i < FAST_WP; i += FAST_THREADS) need[i] = (i >= dx0 && i < dx1) ? 0x80 : 0;   // pass 1: every detection column
+  if (tid == 0) s_retry = 0;
   __syncthreads();
 
-  // 2. quick reject by pixel quads, per-warp compaction
-  const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
+  // 2. first detection at iniTh (the reference's first cv::FAST call per cell, :1510)
   const int qbase = dx0 & ~3;
   const int nq = (dx1 - qbase + 3) >> 2;                 // <= 64
-  const unsigned th4 = (unsigned)g.min_th * 0x01010101u, t1 = th4 + 0x01010101u;
   uint16_t* list = lists + warp * list_cap;
-  const uint32_t lt = (1u << lane) - 1u;
   // warp w owns the detection rows [w * R, (w + 1) * R), R = ceil(dh / 8) <= 8
   const int rpw = (dh + FAST_WARPS - 1) / FAST_WARPS;
   const int row0 = warp * rpw, row1 = min(row0 + rpw, dh);
-  // candidate bits of this thread: nibble ri of cand[hi] = the 4 pixels of quad ((lane + 5*ri) & 31) + 32*hi in row row0 + ri.
-  // The per-row rotation spreads a textured blob (candidates cluster in 2-D) over many lanes, which bounds the longest
-  // per-lane list and with it the trip count of the divergent emission loop below.
-  unsigned cand[2] = {0u, 0u};
-  const unsigned mfirst = 0x80808080u << (8 * (dx0 - qbase));                        // quad 0: columns >= dx0
-  const unsigned mlast = 0x80808080u >> (8 * (4 - (dx1 - (qbase + 4 * (nq - 1)))));   // quad nq-1: columns < dx1
-  for (int ri = 0; row0 + ri < row1; ++ri) {
-    const int y = row0 + ri;
-    const int rot = (lane + 5 * ri) & 31;
-#pragma unroll
-    for (int hi = 0; hi < 2; ++hi) {
-      const int q = rot + 32 * hi;
-      if (q < nq) {
-        unsigned colmask = 0x80808080u;                  // bit 7 of byte k: column x + k is a detection column
-        if (q == 0) colmask &= mfirst;
-        if (q == nq - 1) colmask &= mlast;
-        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + qbase + 4 * q;
-        const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c1 = *reinterpret_cast<const unsigned*>(row),
-                       c2 = *reinterpret_cast<const unsigned*>(row + 4);
-        const unsigned up = *reinterpret_cast<const unsigned*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + 3 * FAST_WP);
-        const unsigned lf = __byte_perm(c0, c1, 0x4321), rt = __byte_perm(c1, c2, 0x6543);
-        const unsigned au = __vabsdiffu4(c1, up), ad = __vabsdiffu4(c1, dn), al = __vabsdiffu4(c1, lf), ar = __vabsdiffu4(c1, rt);
-        unsigned pass;
-        if (SMALL_TH) pass = (fast_gt4(au, t1) | fast_gt4(ad, t1)) & (fast_gt4(al, t1) | fast_gt4(ar, t1)) & colmask;
-        else pass = (__vcmpgtu4(au, th4) | __vcmpgtu4(ad, th4)) & (__vcmpgtu4(al, th4) | __vcmpgtu4(ar, th4)) & colmask;
-        cand[hi] |= ((pass * 0x204081u) >> 28) << (4 * ri);   // bits 7, 15, 23, 31 -> one nibble (the partial products never carry)
-      }
-    }
-  }
-  // one warp scan places every thread's candidates in the warp's list (order is irrelevant). Entry = hi:1 | lane:5 | ri:3 | k:2,
-  // decoded by full warps in the scoring loop
-  int cnt;
-  {
-    const int c = __popc(cand[0]) + __popc(cand[1]);
-    int incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int yv = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += yv;
-    }
-    cnt = __shfl_sync(0xffffffffu, incl, 31);
-    uint16_t* out = list + (incl - c);
-#pragma unroll
-    for (int hi = 0; hi < 2; ++hi) {
-      unsigned m = cand[hi];
-      const unsigned code = (unsigned)((hi << 10) | (lane << 5));
-      while (m) {
-        *out++ = (uint16_t)(code | (unsigned)(__ffs(m) - 1));
-        m &= m - 1;
-      }
-    }
-  }
-  __syncwarp();
-
-  // 3. score the candidates, 32 per step; corners (S >= minTh) are compacted in place to the front of the list as (y << 9) | x
-  int ncorner = 0;
-  for (int c0 = 0; c0 < cnt; c0 += 32) {
-    const int i = c0 + lane;
-    int e = 0, s = 0;
-    if (i < cnt) {
-      const int code = list[i];
-      const int ri = (code >> 2) & 7;
-      const int q = (((code >> 5) + 5 * ri) & 31) + ((code >> 10) << 5);
-      e = ((row0 + ri) << 9) | (qbase + 4 * q + (code & 3));
-      s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
-    }
-    const bool corner = s >= g.min_th;
-    __syncwarp();                                            // the reads of this chunk precede the in-place writes below
-    const uint32_t b = __ballot_sync(0xffffffffu, corner);
-    if (corner) {
-      sc[((e >> 9) + 1) * FAST_SP + (e & 511)] = (uint8_t)s;
-      list[ncorner + __popc(b & lt)] = (uint16_t)e;
-    }
-    ncorner += __popc(b);
-  }
+  const int xlim = L.maxBX - 3 - xa;                     // detection columns end here (last cell may be clipped)
+  int ncorner = fast_detect<SMALL_TH, false>(win, sc, need, list, 0, row0, row1, qbase, nq, lane, g.ini_th, g.min_th);
   __syncthreads();
-
-  // 4. 3x3 NMS of every corner against its neighbours inside the same cell's detection window
-  {
-    const unsigned inv = (1u << 20) / (unsigned)wCell + 1u;      // p / wCell == (p * inv) >> 20 for p < 4096, wCell < 256
-    const int xlim = L.maxBX - 3 - xa;                           // detection columns end here (last cell may be clipped)
-    for (int i = lane; i < ncorner; i += 32) {
-      const int e = list[i];
-      const int y = e >> 9, x = e & 511;
-      const uint8_t* q = sc + (y + 1) * FAST_SP + x;
-      const int s = q[0];
-      const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);
-      const unsigned r = p - ((p * inv) >> 20) * (unsigned)wCell;   // column inside the cell's detection window
-      bool ok = s > q[-FAST_SP] && s > q[FAST_SP];
-      if (r > 0) ok = ok && s > q[-1] && s > q[-FAST_SP - 1] && s > q[FAST_SP - 1];
-      if ((int)r < wCell - 1 && x + 1 < xlim) ok = ok && s > q[1] && s > q[-FAST_SP + 1] && s > q[FAST_SP + 1];
-      if (ok) {
-        atomicOr(&pl_min[y * FAST_BP + (x >> 5)], 1u << (x & 31));
-        if (s >= g.ini_th) atomicOr(&pl_ini[y * FAST_BP + (x >> 5)], 1u << (x & 31));
+  // 3. NMS of the corners with S >= iniTh -> ini survivor plane. A suppressor of such a corner has S >= iniTh itself, so it was
+  //    scored above. `need` is re-initialised meanwhile (nobody reads it until the next barrier).
+  fast_nms<false>(sc, need, list, ncorner, lane, pl_ini, wCell, xa, xlim, g.ini_th);
+  for (int i = tid; i < FAST_WP / 4; i += FAST_THREADS) reinterpret_cast<unsigned*>(need)[i] = 0u;
+  __syncthreads();
+  // 4. cells without an ini survivor retry at minTh (:1521): mark their detection columns
+  for (int cj = j0 + warp; cj < j1; cj += FAST_WARPS) {
+    const int cx0 = ORB_MIN_BORDER + cj * wCell + 3 - xa;
+    const int cx1 = min(ORB_MIN_BORDER + (cj + 1) * wCell + 3, L.maxBX - 3) - xa;
+    const int dw = cx1 - cx0;
+    if (dw <= 0) continue;
+    const unsigned long long wmask = dw >= 64 ? ~0ull : ((1ull << dw) - 1ull);
+    const int w0 = cx0 >> 5, sh = cx0 & 31;
+    bool any = false;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int y = lane + 32 * r;
+      if (y < dh) {
+        const uint32_t* b = pl_ini + y * FAST_BP + w0;
+        const unsigned long long m = (((unsigned long long)__funnelshift_r(b[1], b[2], sh) << 32) | __funnelshift_r(b[0], b[1], sh)) & wmask;
+        any = any || m != 0ull;
       }
+    }
+    if (!__any_sync(0xffffffffu, any)) {
+      if (lane < dw) need[cx0 + lane] = 0x80;
+      if (lane + 32 < dw) need[cx0 + lane + 32] = 0x80;
+      if (lane == 0) s_retry = 1;
     }
   }
   __syncthreads();
+  if (s_retry) {   // uniform over the CTA
+    // 4a. the pixels that pass the compass test at minTh but not at iniTh, in the retry cells only
+    const int n2 = fast_detect<SMALL_TH, true>(win, sc, need, list, ncorner, row0, row1, qbase, nq, lane, g.ini_th, g.min_th);
+    ncorner += n2;
+    __syncthreads();
+    // 4b. NMS of every corner (S >= minTh) of the retry cells -> min survivor plane
+    fast_nms<true>(sc, need, list, ncorner, lane, pl_min, wCell, xa, xlim, g.ini_th);
+    __syncthreads();
+  }
 
   // 5. per cell: row-major ranks from the survivor bit planes, ini/min selection, emission. Lane = detection row
   //    (two row slots cover dh <= 64); a cell's detection window is < 64 columns wide.
@@ -284,9 +347,9 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
   const int win_rows = max_h + 6, sc_rows = max_h + 2;
   const int list_cap = ((max_h + FAST_WARPS - 1) / FAST_WARPS) * 256;   // a warp's rows x <= 256 detection columns
   const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)max_h * FAST_BP * 4 +
-                      (size_t)FAST_WARPS * list_cap * 2;
+                      (size_t)FAST_WARPS * list_cap * 2 + FAST_WP;
   static size_t configured[2] = {0, 0};
-  const int small = g.min_th <= 126;
+  const int small = g.ini_th <= 126;   // both thresholds (min <= ini) in the carry-free byte-compare range
   if (smem > 48 * 1024 && smem > configured[small]) {
     if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -4,40 +4,56 @@
 // Integer-only restatement of OpenCV's 8-bit fixed-point resize -> bit-exact by construction.
 // Border pixels are pure index remaps of interior pixels, so every padded output pixel is computed
 // directly from level l-1 (no second pass over the plane).
+#include <algorithm>
+
 #include "orb_common.cuh"
 
 // Every plane is written together with its apron: columns [-4, cols + 4) and rows [-3, rows + 3) hold the
 // BORDER_REFLECT_101 extension of the PADDED image (what cv::GaussianBlur reads beyond it), so the blur kernel is branch-free.
 // Kernel x index t <-> padded column t - ORB_APRON, y index t <-> padded row t - (ORB_APRON - 1).
 
-// Level 0 = copyMakeBorder(image, 19, REFLECT_101). One thread = 4 adjacent output pixels (one 32-bit store); interior quads
-// read the (arbitrarily aligned) source row as two aligned words + a funnel shift, border quads as 4 remapped bytes.
-__global__ void __launch_bounds__(256) orb_pyr_level0_kernel(const uint8_t* __restrict__ images, int step,
-                                                             long long image_stride, uint8_t* __restrict__ pyr,
-                                                             const __grid_constant__ OrbGeom g) {
+// Level 0 = copyMakeBorder(image, 19, REFLECT_101) + apron, in 16-byte chunks of the destination row (chunk c = columns
+// [-16 + 16c, 16c)). Interior chunks (every source byte and the aligned words around it inside the source row) are one thread
+// each: five aligned 32-bit loads from the arbitrarily aligned source row, four funnel shifts, one 16-byte store. The few
+// border chunks per row go through a separate small launch of the byte-remapping kernel, so no warp mixes the two paths.
+__global__ void __launch_bounds__(256) orb_pyr_level0_interior_kernel(const uint8_t* __restrict__ images, int step, long long image_stride,
+                                                                      uint8_t* __restrict__ pyr, int c_lo, int c_hi,
+                                                                      const __grid_constant__ OrbGeom g) {
   const OrbLevel& L = g.lv[0];
   const int frame = blockIdx.z;
-  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4 - ORB_APRON;
+  const int c = c_lo + blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y - (ORB_APRON - 1);
-  if (y >= L.rows + ORB_APRON - 1 || x4 >= L.cols + ORB_APRON) return;
-  const uint8_t* src = images + (long long)frame * image_stride;
+  if (y >= L.rows + ORB_APRON - 1 || c > c_hi) return;
   const int sy = orb_reflect101(orb_reflect101(y, L.rows) - ORB_EDGE, g.height);
-  const uint8_t* srow = src + (long long)sy * step;
+  const int x0 = 16 * c - 16;
+  const uint8_t* p = images + (long long)frame * image_stride + (long long)sy * step + (x0 - ORB_EDGE);
+  const unsigned sh = 8u * (unsigned)((uintptr_t)p & 3);
+  const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)p & ~(uintptr_t)3);
+  const unsigned w0 = __ldg(ap), w1 = __ldg(ap + 1), w2 = __ldg(ap + 2), w3 = __ldg(ap + 3), w4 = __ldg(ap + 4);
+  uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)y * L.pitch + x0;
+  *reinterpret_cast<uint4*>(dst) = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
+                                              __funnelshift_r(w3, w4, sh));
+}
+
+// Border chunks: thread = (row, border chunk e, word k of the chunk); chunk index = e < n_left ? e : c_hi + 1 + (e - n_left).
+__global__ void __launch_bounds__(256) orb_pyr_level0_border_kernel(const uint8_t* __restrict__ images, int step, long long image_stride,
+                                                                    uint8_t* __restrict__ pyr, int n_left, int c_hi, int n_edge,
+                                                                    const __grid_constant__ OrbGeom g) {
+  const OrbLevel& L = g.lv[0];
+  const int frame = blockIdx.z;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nrows = L.rows + 2 * (ORB_APRON - 1);
+  if (i >= nrows * n_edge * 4) return;
+  const int k = i & 3, e = (i >> 2) % n_edge, y = (i >> 2) / n_edge - (ORB_APRON - 1);
+  const int c = e < n_left ? e : c_hi + 1 + (e - n_left);
+  const int x4 = 16 * c - 16 + 4 * k;
+  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - ORB_EDGE, g.height);
+  const uint8_t* srow = images + (long long)frame * image_stride + (long long)sy * step;
   uint32_t out = 0;
-  const int sx = x4 - ORB_EDGE;
-  if (sx >= 4 && sx + 8 <= g.width) {   // both aligned words lie inside this source row
-    const uint8_t* p = srow + sx;
-    const unsigned sh = 8u * (unsigned)((uintptr_t)p & 3);
-    const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)p & ~(uintptr_t)3);
-    const unsigned lo = __ldg(ap);
-    const unsigned hi = __ldg(ap + 1);
-    out = __funnelshift_r(lo, hi, sh);
-  } else {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int x = min(x4 + k, L.cols + ORB_APRON - 1);
-      out |= (uint32_t)__ldg(srow + orb_reflect101(orb_reflect101(x, L.cols) - ORB_EDGE, g.width)) << (8 * k);
-    }
+  for (int b = 0; b < 4; ++b) {
+    const int x = max(min(x4 + b, L.cols + ORB_APRON - 1), -ORB_APRON);   // columns outside the apron are never read
+    out |= (uint32_t)__ldg(srow + orb_reflect101(orb_reflect101(x, L.cols) - ORB_EDGE, g.width)) << (8 * b);
   }
   uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off;
   *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x4) = out;
@@ -101,7 +117,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
     const int y = blockIdx.y * 32 + threadIdx.y + 8 * r;
     if (y >= D.rows + 2 * (ORB_APRON - 1)) break;
     const ResizeTab ty = yt[y];
-    const unsigned cy0 = ty.coef & 0xffffu, cy1 = ty.coef >> 16;
+    const unsigned cy0 = (ty.coef & 0xffffu) << 16, cy1 = ty.coef & 0xffff0000u;   // pre-shifted: (cy * t) >> 16 == umulhi(cy << 16, t)
     const unsigned* r0 = reinterpret_cast<const unsigned*>(src + (long long)ty.ofs * S.pitch + wbase);
     const unsigned* r1 = reinterpret_cast<const unsigned*>(src + (long long)min(ty.ofs + 1, S.rows - 1) * S.pitch + wbase);
     const unsigned a0 = r0[0], a1 = r0[1], a2 = r0[2], b0 = r1[0], b1 = r1[1], b2 = r1[2];
@@ -112,7 +128,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
     {                                                                                            \
       const unsigned t0 = __dp2a_lo(coef, __byte_perm(al, ah, sel), 0u);                         \
       const unsigned t1 = __dp2a_lo(coef, __byte_perm(bl, bh, sel), 0u);                         \
-      v[k] = (((cy0 * (t0 >> 4)) >> 16) + ((cy1 * (t1 >> 4)) >> 16) + 2u) >> 2;                  \
+      v[k] = (__umulhi(cy0, t0 >> 4) + __umulhi(cy1, t1 >> 4) + 2u) >> 2;                         \
     }
     ORB_PX(0, s0, e01.y) ORB_PX(1, s1, e01.w) ORB_PX(2, s2, e23.y) ORB_PX(3, s3, e23.w)
 #undef ORB_PX
@@ -126,8 +142,21 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
   dim3 blk(32, 8);
   {
     const OrbLevel& L = g.lv[0];
-    dim3 grd(((L.cols + 2 * ORB_APRON + 3) / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 7) / 8, batch);
-    orb_pyr_level0_kernel<<<grd, blk, 0, st>>>(images, step, image_stride, pyr, g);
+    const int nrows = L.rows + 2 * (ORB_APRON - 1);
+    const int c_last = (L.cols + ORB_APRON - 1 + 16) / 16;              // chunk holding the last apron column
+    // interior chunk: source columns 16c - 35 .. 16c - 20 and the aligned words around them lie inside the source row
+    const int c_lo = 3;
+    const int c_hi = std::min(c_last, (g.width - 20 + 35) / 16);         // 16c - 35 <= W - 20
+    const int n_int = std::max(c_hi - c_lo + 1, 0);
+    const int hi_eff = n_int > 0 ? c_hi : c_lo - 1;
+    const int n_left = std::min(c_lo, c_last + 1), n_edge = n_left + (c_last - hi_eff);
+    if (n_int > 0) {
+      dim3 grd((n_int + 31) / 32, (nrows + 7) / 8, batch);
+      orb_pyr_level0_interior_kernel<<<grd, blk, 0, st>>>(images, step, image_stride, pyr, c_lo, c_hi, g);
+      ++*launches;
+    }
+    dim3 grd((nrows * n_edge * 4 + 255) / 256, 1, batch);
+    orb_pyr_level0_border_kernel<<<grd, 256, 0, st>>>(images, step, image_stride, pyr, n_left, hi_eff, n_edge, g);
     ++*launches;
   }
   for (int l = 1; l < g.nlevels; ++l) {

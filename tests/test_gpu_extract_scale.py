@@ -1,0 +1,120 @@
+"""GPU extraction at scale: multi-pass batches (the two-workspace / two-stream schedule and the copy pipeline of
+orb_extract_batch), ragged batch sizes, thresholds beyond the carry-free byte-compare range, the 4K stress shape, and
+size-independent properties at BASELINE.json's full batch sizes (the oracle cannot run those in seconds):
+batch == concatenation of single-frame results, idempotence, host path == device path."""
+import os
+
+import numpy as np
+import pytest
+
+from orb_slam2_detailed_comments_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _ex(nf, ini=20, mn=7, **kw):
+    from orb_slam2_detailed_comments_b200 import ORBextractor
+    return ORBextractor(nf, 1.2, 8, ini, mn, **kw)
+
+
+def _tiled(w, h, n, seed0, distinct):
+    """n frames cycling through `distinct` images (exact copies, unlike synth_batch's shifted copies)."""
+    base = synth.synth_batch(w, h, min(distinct, n), seed0=seed0)
+    return np.ascontiguousarray(base[np.arange(n) % len(base)])
+
+
+def _check_frame(oe, frame, kps, desc, n):
+    ok, od, _ = oe(frame)
+    assert n == len(ok)
+    assert np.array_equal(kps[:n].view(np.uint8), ok.view(np.uint8))
+    assert np.array_equal(desc[:n], od)
+
+
+@pytest.mark.parametrize("B", [1, 17, 70, 131, 200])
+def test_ragged_multipass_batches_match_oracle(oracle, B, monkeypatch):
+    """Pass size forced to 16 frames: B = 131 runs ramp-up passes of 4 and 8 frames, seven full passes and a ragged tail,
+    alternating between the two workspaces; every frame must equal the oracle."""
+    monkeypatch.setenv("ORB_B200_CHUNK", "16")
+    frames = _tiled(400, 300, B, 4000, 6)
+    ex = _ex(500)
+    kps, desc, counts, lc = ex.extract_batch(frames)
+    oe = oracle.OracleExtractor(500)
+    ref = {}
+    for i in range(B):
+        key = i % min(B, 6)
+        if key not in ref:
+            ref[key] = oe(frames[i])
+        ok, od, olc = ref[key]
+        n = int(counts[i])
+        assert n == len(ok), f"frame {i}"
+        assert np.array_equal(lc[i], olc)
+        assert np.array_equal(kps[i, :n].view(np.uint8), ok.view(np.uint8)), f"frame {i}"
+        assert np.array_equal(desc[i, :n], od), f"frame {i}"
+    # mvImagePyramid of the last image of the call
+    oe(frames[B - 1])
+    for l in (0, 3, 7):
+        assert np.array_equal(ex.pyramid_level(l, -1), oe.level(l))
+
+
+def test_device_path_equals_host_path_multipass(monkeypatch):
+    import torch
+    monkeypatch.setenv("ORB_B200_CHUNK", "8")
+    frames = synth.synth_batch(640, 480, 37, seed0=77, distinct=5)
+    ex = _ex(1000)
+    kps, desc, counts, _ = ex.extract_batch(frames)
+    dk, dd, dc = ex.extract_batch_device(torch.from_numpy(frames).cuda())
+    dk, dd, dc = dk.cpu().numpy(), dd.cpu().numpy(), dc.cpu().numpy()
+    assert np.array_equal(dc, counts)
+    for i in range(len(frames)):
+        n = int(counts[i])
+        assert np.array_equal(dk[i, :n].view(np.uint8).reshape(-1), kps[i, :n].view(np.uint8).reshape(-1))
+        assert np.array_equal(dd[i, :n], desc[i, :n])
+
+
+@pytest.mark.parametrize("ini,mn", [(200, 130), (254, 127), (127, 126), (20, 20), (40, 1)])
+def test_threshold_ranges(oracle, ini, mn):
+    """minTh/iniTh above 126 take the generic byte-compare path; equal thresholds make the retry a no-op."""
+    rng = np.random.RandomState(5)
+    img = synth.synth_frame(360, 300, 31)
+    img = np.where(rng.rand(*img.shape) < 0.02, rng.randint(0, 256, img.shape), img).astype(np.uint8)   # salt: very high scores
+    ex = _ex(400, ini, mn)
+    oe = oracle.OracleExtractor(400, 1.2, 8, ini, mn)
+    kps, desc, counts, _ = ex.extract_batch(img[None])
+    _check_frame(oe, img, kps[0], desc[0], int(counts[0]))
+
+
+def test_4k_frame_matches_oracle(oracle):
+    img = synth.synth_frame(3840, 2160, 8)
+    ex = _ex(8000)
+    oe = oracle.OracleExtractor(8000)
+    kps, desc, counts, _ = ex.extract_batch(img[None])
+    n = int(counts[0])
+    assert n >= 7900
+    _check_frame(oe, img, kps[0], desc[0], n)
+    for l in (0, 7):
+        assert np.array_equal(ex.pyramid_level(l), oe.level(l))
+
+
+@pytest.mark.parametrize("name,w,h,nf,B", [("kitti", 1241, 376, 2000, 512), ("euroc", 752, 480, 1200, 512), ("tum", 640, 480, 1000, 1024)])
+def test_full_size_batch_properties(oracle, name, w, h, nf, B):
+    """BASELINE.json batch sizes. Frames cycle through 8 distinct images, so (a) every occurrence of an image must give the
+    identical result wherever it sits in the batch / whichever pass and workspace processed it, (b) each distinct result
+    equals the oracle, (c) a second call reproduces the first bit for bit."""
+    import torch
+    frames = _tiled(w, h, B, 1234, 8)
+    ex = _ex(nf)
+    t = torch.from_numpy(frames).cuda()
+    k1, d1, c1 = ex.extract_batch_device(t)
+    k1, d1, c1 = k1.cpu().numpy(), d1.cpu().numpy(), c1.cpu().numpy()
+    k2, d2, c2 = ex.extract_batch_device(t)
+    assert np.array_equal(c1, c2.cpu().numpy()) and np.array_equal(d1, d2.cpu().numpy())
+    oe = oracle.OracleExtractor(nf)
+    for j in range(8):
+        n = int(c1[j])
+        ok, od, _ = oe(frames[j])
+        assert n == len(ok)
+        assert np.array_equal(k1[j, :n].view(np.uint8).reshape(-1), ok.view(np.uint8).reshape(-1))
+        assert np.array_equal(d1[j, :n], od)
+        for i in range(j + 8, B, 8):
+            assert c1[i] == n
+            assert np.array_equal(k1[i, :n].view(np.uint8), k1[j, :n].view(np.uint8)) and np.array_equal(d1[i, :n], d1[j, :n]), f"{name}: frame {i} != frame {j}"
