@@ -218,6 +218,9 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
   unsigned* ic = s_ic[warp];
   unsigned* pt = s_pt[warp];
   const uint8_t* ptb = reinterpret_cast<const uint8_t*>(pt);
+  const int ic_sub = lane / 9, ic_w = lane - 9 * ic_sub, ic_idx = 9 * ic_sub + ic_w;      // lanes 27..31 idle
+  const int pt_sub = lane / 10, pt_w = lane - 10 * pt_sub, pt_idx = 10 * pt_sub + pt_w;   // lanes 30, 31 idle
+  const bool ic_act = lane < 27, pt_act = lane < 30;
 
   for (int w = w_first; w < w_end; ++w) {
     const int level = __popc(__ballot_sync(0xffffffffu, lane < g.nlevels && cinc <= w));
@@ -232,21 +235,18 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     const unsigned* icg = reinterpret_cast<const unsigned*>(pyr + off + (long long)(y - 15) * pitch + xi);
     const unsigned* ptg = reinterpret_cast<const unsigned*>(blr + off + (long long)(y - 18) * pitch + xp);
     const int pw = pitch >> 2;
-    unsigned ra[9], rp[12];
+    // three window rows per load instruction: lane = (row % 3, word); the per-lane offsets need one IMAD per keypoint
+    const unsigned* icl = icg + ic_sub * pw + ic_w;
+    const unsigned* ptl = ptg + pt_sub * pw + pt_w;
+    unsigned ra[11], rp[13];
 #pragma unroll
-    for (int i = 0; i < 9; ++i) {
-      const int idx = lane + 32 * i;
-      ra[i] = idx < 31 * 9 ? __ldg(icg + (idx / 9) * pw + (idx % 9)) : 0u;
-    }
+    for (int i = 0; i < 11; ++i) ra[i] = (ic_act && 3 * i + ic_sub < 31) ? __ldg(icl + 3 * i * pw) : 0u;
 #pragma unroll
-    for (int i = 0; i < 12; ++i) {
-      const int idx = lane + 32 * i;
-      rp[i] = idx < 37 * 10 ? __ldg(ptg + (idx / 10) * pw + (idx % 10)) : 0u;
-    }
+    for (int i = 0; i < 13; ++i) rp[i] = (pt_act && 3 * i + pt_sub < 37) ? __ldg(ptl + 3 * i * pw) : 0u;
     __syncwarp();                                              // the previous keypoint's gathers are done
 #pragma unroll
-    for (int i = 0; i < 9; ++i)
-      if (lane + 32 * i < 31 * 9) ic[lane + 32 * i] = ra[i];
+    for (int i = 0; i < 11; ++i)
+      if (ic_act && 3 * i + ic_sub < 31) ic[27 * i + ic_idx] = ra[i];
     __syncwarp();
     // IC_Angle (:104-161): lane = row v
     int m10 = 0, rs = 0;
@@ -273,8 +273,8 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     orb_sincos(__fmul_rn(angle, factorPI), &b, &a);
     // computeOrbDescriptor (:177-254) on the staged patch: byte (r, c) of the patch is pt[(r + 18) * 40 + c + x - xp]
 #pragma unroll
-    for (int i = 0; i < 12; ++i)
-      if (lane + 32 * i < 37 * 10) pt[lane + 32 * i] = rp[i];
+    for (int i = 0; i < 13; ++i)
+      if (pt_act && 3 * i + pt_sub < 37) pt[30 * i + pt_idx] = rp[i];
     __syncwarp();
     const uint8_t* bc = ptb + 18 * 40 + (x - xp);
     int val = 0;
