@@ -14,7 +14,7 @@
 
 // ---- kernel launchers (other translation units) -------------------------------------------------------------
 struct OrbKnn2;
-void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const OrbGeom&, int, cudaStream_t, long long*, cudaEvent_t);
 void orb_launch_fast(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t*, int*, int*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
@@ -91,7 +91,7 @@ struct orb_extractor {
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
   cudaStream_t s_in = nullptr, s_out = nullptr;
   DevBuf stage_in[2], out_kps[2], out_desc[2];
-  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {};
+  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {}, ev_staged[2] = {};   // ev_staged: level 0 has consumed stage_in[b]
   size_t h_cnt_cap = 0;    // ints in h_cnt
   int* h_err = nullptr;    // pinned
   int* h_cnt = nullptr;    // pinned [batch * (1 + nlevels)]: counts, then per-level counts
@@ -306,7 +306,7 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
 
 // One internal pass over `n` (<= chunk) device-resident frames; outputs to device pointers.
 static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, long long image_stride, int n, OrbKeypoint* kps,
-                     uint8_t* desc, int cap, int* counts_dev) {
+                     uint8_t* desc, int cap, int* counts_dev, cudaEvent_t ev_input_consumed = nullptr) {
   const OrbGeom& g = e->geom;
   orb_extractor::PassWs& P = e->ws[w];
   cudaStream_t st = P.st;
@@ -328,7 +328,7 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
     if (prof) { ev = e->ev.data() + e->ev_used; e->ev_used += ORB_NUM_STAGES + 1; }
   }
   if (prof) cudaEventRecord(ev[0], st);
-  orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches);
+  orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches, ev_input_consumed);
   if (prof) cudaEventRecord(ev[1], st);
   orb_launch_fast(P.pyr.as<uint8_t>(), P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[2], st);
@@ -427,6 +427,7 @@ void orb_extractor_destroy(orb_extractor* e) {
     if (e->ev_in[b]) cudaEventDestroy(e->ev_in[b]);
     if (e->ev_done[b]) cudaEventDestroy(e->ev_done[b]);
     if (e->ev_out[b]) cudaEventDestroy(e->ev_out[b]);
+    if (e->ev_staged[b]) cudaEventDestroy(e->ev_staged[b]);
   }
   for (cudaEvent_t ev : e->ev)
     if (ev) cudaEventDestroy(ev);
@@ -526,6 +527,7 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
       CU(cudaEventCreateWithFlags(&e->ev_in[b], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&e->ev_done[b], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&e->ev_out[b], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&e->ev_staged[b], cudaEventDisableTiming));
     }
   }
   const size_t fbytes = (size_t)step * height;   // frames are staged with the caller's pitch (level 0 reads any pitch)
@@ -553,8 +555,8 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
     const int want = (batch > 2 * full && pass < 2) ? std::max(full >> (2 - pass), 1) : full;
     n = std::min(want, batch - f0);
     const int b = pass & 1;
-    // ---- copy-in stream: stage_in[b] is free once pass-2 finished computing
-    if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_done[b], 0));
+    // ---- copy-in stream: stage_in[b] is free once level 0 of pass-2 has read it (the rest of that pass works on the pyramid)
+    if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_staged[b], 0));
     bool contiguous = true;   // frames back to back with the same pitch -> one linear copy for the whole pass
     for (int i = 1; i < n && contiguous; ++i) contiguous = images[f0 + i] == images[f0] + (size_t)i * fbytes;
     if (contiguous) {
@@ -568,22 +570,24 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
     const int w = e->profile ? 0 : b;
     orb_extractor::PassWs& P = e->ws[w];
     CU(cudaStreamWaitEvent(P.st, e->ev_in[b], 0));
-    if (host_out && pass >= 2) CU(cudaStreamWaitEvent(P.st, e->ev_out[b], 0));   // out buffers [b] drained
+    if (pass >= 2) CU(cudaStreamWaitEvent(P.st, e->ev_out[b], 0));   // out buffers / count arrays of workspace [b] drained
+    if (e->profile && pass >= 1) CU(cudaStreamWaitEvent(P.st, e->ev_out[b ^ 1], 0));   // single workspace: also the previous pass's counts
     OrbKeypoint* dk = host_out ? e->out_kps[b].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
     uint8_t* dd = host_out ? e->out_desc[b].as<uint8_t>() : desc + (long long)f0 * cap * 32;
-    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, P.out_cnt.as<int>());
-    CU(cudaMemcpyAsync(h_counts + f0, P.out_cnt.p, n * sizeof(int), cudaMemcpyDeviceToHost, P.st));
-    CU(cudaMemcpyAsync(h_levels + (size_t)f0 * nl, P.kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, P.st));
+    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, P.out_cnt.as<int>(), e->ev_staged[b]);
     CU(cudaEventRecord(e->ev_done[b], P.st));
-    // ---- copy-out stream
+    // ---- copy-out stream (also the small count copies: a D2H queued on the compute stream would wait for the copy engine
+    //      behind the previous pass's output copy and hold back the next kernels of that stream)
+    CU(cudaStreamWaitEvent(e->s_out, e->ev_done[b], 0));
+    CU(cudaMemcpyAsync(h_counts + f0, P.out_cnt.p, n * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
+    CU(cudaMemcpyAsync(h_levels + (size_t)f0 * nl, P.kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
     if (host_out) {
-      CU(cudaStreamWaitEvent(e->s_out, e->ev_done[b], 0));
       CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->s_out));
       CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->s_out));
-      CU(cudaEventRecord(e->ev_out[b], e->s_out));
     }
+    CU(cudaEventRecord(e->ev_out[b], e->s_out));
   }
-  if (host_out) CU(cudaStreamSynchronize(e->s_out));
+  CU(cudaStreamSynchronize(e->s_out));
   if ((rc = check_err_flag(e)) != ORB_OK) return rc;   // synchronises the compute stream (counts are on the host after it)
   memcpy(counts, h_counts, (size_t)batch * sizeof(int));
   if (level_counts) memcpy(level_counts, h_levels, (size_t)batch * nl * sizeof(int));

@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
 }
 
 void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride, uint8_t* pyr, const ResizeTab* tabs,
-                        const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
+                        const OrbGeom& g, int batch, cudaStream_t st, long long* launches, cudaEvent_t ev_input_consumed) {
   dim3 blk(32, 8);
   {
     const OrbLevel& L = g.lv[0];
@@ -158,6 +158,7 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
     dim3 grd((nrows * n_edge * 4 + 255) / 256, 1, batch);
     orb_pyr_level0_border_kernel<<<grd, 256, 0, st>>>(images, step, image_stride, pyr, n_left, hi_eff, n_edge, g);
     ++*launches;
+    if (ev_input_consumed) cudaEventRecord(ev_input_consumed, st);   // only level 0 reads the input frames
   }
   for (int l = 1; l < g.nlevels; ++l) {
     const OrbLevel& L = g.lv[l];
