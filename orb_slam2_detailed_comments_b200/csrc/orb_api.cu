@@ -202,7 +202,9 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.hX = (float)(L.maxBX - ORB_MIN_BORDER) / L.nIni;
     L.quota = e->quota[l];
     const long long by_cells = (long long)L.nCols * L.nRows * ORB_CELL_CAP;
-    L.raw_cap = (int)std::min<long long>(by_cells, std::max(32LL * L.quota, 8192LL));
+    // a level can never hold more raw keypoints than its cells can (cell overflow is flagged separately); dense 4K frames
+    // exceed any quota-based bound (the reference's vector simply grows, src/ORBextractor.cc:1451)
+    L.raw_cap = (int)by_cells;
     L.raw_off = raw; raw += (int)align_up(L.raw_cap, 32);
     L.node_cap = std::max(L.quota + 3, 4 * L.nIni) + L.nIni + 8;
     L.node_off = nodes; nodes += (int)align_up(L.node_cap, 32);
