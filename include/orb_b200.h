@@ -10,6 +10,8 @@
  *                                                                                     include/ORBextractor.h:122-126, src/ORBextractor.cc:1961-2084
  *                                (batched: the stereo Frame ctor runs two of them concurrently, src/Frame.cc:158-168)
  *   orb_extractor_pyramid_*   <- public member mvImagePyramid                         include/ORBextractor.h:185 (read by src/Frame.cc:910,1040)
+ *   orb_extract_stereo_batch  <- the two operator() calls of the stereo Frame ctor + Frame::ComputeStereoMatches
+ *                                                                                     src/Frame.cc:158-168, 880-1176
  *   orb_hamming_knn           <- ORBmatcher::DescriptorDistance in the best/second-best scan
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
@@ -97,6 +99,19 @@ int orb_extractor_max_keypoints(const orb_extractor* e);
 int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height,
                       int batch, orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts,
                       int32_t* level_counts);
+
+/* operator() for both images of `pairs` rectified stereo pairs PLUS Frame::ComputeStereoMatches (src/Frame.cc:880-1176) on the
+ * device, so neither pyramid has to be copied back for it (the reference reads both extractors' mvImagePyramid, src/Frame.cc:910,
+ * 1040). images = 2*pairs pointers, left and right interleaved (L0, R0, L1, R1, ...); kps / desc / counts / level_counts as in
+ * orb_extract_batch for the 2*pairs images. bf = mbf (baseline * fx), b = mb (baseline); both extractors of the reference share one
+ * parameter set (src/Tracking.cc:171-176), so one handle serves both images.
+ *  uright, depth : [pairs][cap] float32 in `out_mem` memory: mvuRight / mvDepth of the LEFT keypoints (-1 = no match)
+ *  matched       : [pairs] matches kept after the median filter (HOST, optional)
+ * Requires cap <= 65535. Rows outside the level-0 image hold no candidates and an empty match list skips the median filter
+ * (the reference is undefined there). */
+int orb_extract_stereo_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height,
+                             int pairs, orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts,
+                             int32_t* level_counts, float bf, float b, float* uright, float* depth, int32_t* matched);
 
 /* Device-resident fast path used by the benchmark: `images` is ONE device buffer [batch][height][step];
  * outputs stay in device memory (kps/desc as above, counts_dev [batch] int32 device). Asynchronous on the

@@ -59,6 +59,7 @@ def lib():
         L.orb_oracle_distribute.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
         L.orb_oracle_descriptor_distance.argtypes = [vp, vp]
         L.orb_oracle_hamming_knn.argtypes = [vp, C.c_int, vp, C.c_int64, C.c_int64, C.c_int, vp, C.c_int]
+        L.orb_oracle_stereo_match.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp]
         L.orb_oracle_extract_many.restype = C.c_int64
         L.orb_oracle_extract_many.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int,
                                               C.c_int, C.c_int, C.c_int]
@@ -195,3 +196,14 @@ def extract_many(frames: np.ndarray, nfeatures, nthreads, scale_factor=1.2, nlev
     n, h, w = frames.shape
     return lib().orb_oracle_extract_many(nfeatures, scale_factor, nlevels, ini_th, min_th, flags, _p(frames), w, h, n,
                                          nthreads)
+
+
+def stereo_match(left: "OracleExtractor", right: "OracleExtractor", kl, dl, kr, dr, bf: float, b: float):
+    """Frame::ComputeStereoMatches (src/Frame.cc:880-1176) on the outputs and pyramids of the LAST call of `left` / `right`.
+    Returns (uright[nL], depth[nL], kept)."""
+    kl, dl = np.ascontiguousarray(kl), np.ascontiguousarray(dl)
+    kr, dr = np.ascontiguousarray(kr), np.ascontiguousarray(dr)
+    ur = np.empty(len(kl), np.float32)
+    dp = np.empty(len(kl), np.float32)
+    kept = lib().orb_oracle_stereo_match(left.h, right.h, _p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), bf, b, _p(ur), _p(dp))
+    return ur, dp, kept

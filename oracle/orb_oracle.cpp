@@ -501,6 +501,114 @@ void orb_oracle_hamming_knn(const uint8_t* q, int Q, const uint8_t* db, int64_t 
   for (auto& t : th) t.join();
 }
 
+// Frame::ComputeStereoMatches (src/Frame.cc:880-1176) for one rectified pair, on the keypoints / descriptors / pyramids the two
+// extractors produced. bf = mbf, b = mb. uright / depth have nL entries (-1 = no match).
+// Canonicalisations: rows outside [0, nRows) are ignored when the right keypoints are binned (the reference indexes
+// vRowIndices with them, which is out of bounds for this fork's padded coordinates at high octaves); an empty match list skips the
+// median filter (the reference reads vDistIdx[0] of an empty vector); float expressions are not contracted.
+int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_extractor* right, const orb_oracle_kp* kl,
+                            const uint8_t* dl, int nL, const orb_oracle_kp* kr, const uint8_t* dr, int nR, float bf, float b,
+                            float* uright, float* depth) {
+  const int TH_HIGH = 100, TH_LOW = 50;
+  const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+  const Extractor& EL = left->ex;
+  const Extractor& ER = right->ex;
+  const int nRows = EL.pyr[0].rows;
+  for (int i = 0; i < nL; ++i) { uright[i] = -1.0f; depth[i] = -1.0f; }
+  std::vector<std::vector<int>> rowIdx(nRows);
+  for (int iR = 0; iR < nR; ++iR) {
+    const float kpY = kr[iR].y;
+    const float r = 2.0f * ER.scale[kr[iR].octave];
+    const int maxr = (int)std::ceil(kpY + r);
+    const int minr = (int)std::floor(kpY - r);
+    for (int yi = minr; yi <= maxr; ++yi)
+      if (yi >= 0 && yi < nRows) rowIdx[yi].push_back(iR);
+  }
+  const float minZ = b;
+  const float minD = 0;
+  const float maxD = bf / minZ;
+  std::vector<std::pair<int, int>> distIdx;
+  for (int iL = 0; iL < nL; ++iL) {
+    const orb_oracle_kp& kpL = kl[iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int row = (int)vL;
+    if (row < 0 || row >= nRows) continue;
+    const std::vector<int>& cand = rowIdx[row];
+    if (cand.empty()) continue;
+    const float minU = uL - maxD;
+    const float maxU = uL - minD;
+    if (maxU < 0) continue;
+    int bestDist = TH_HIGH;
+    int bestIdxR = 0;
+    for (int iR : cand) {
+      const orb_oracle_kp& kpR = kr[iR];
+      if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+      const float uR = kpR.x;
+      if (uR >= minU && uR <= maxU) {
+        const int dist = orb_oracle_descriptor_distance(dl + (size_t)iL * 32, dr + (size_t)iR * 32);
+        if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+      }
+    }
+    if (bestDist >= thOrbDist) continue;
+    const float uR0 = kr[bestIdxR].x;
+    const float sf = EL.invScale[kpL.octave];
+    const float scaleduL = std::round(kpL.x * sf);
+    const float scaledvL = std::round(kpL.y * sf);
+    const float scaleduR0 = std::round(uR0 * sf);
+    const int w = 5, L = 5;
+    const Plane& PL = EL.pyr[kpL.octave];
+    const Plane& PR = ER.pyr[kpL.octave];
+    const int cy = (int)scaledvL, cxl = (int)scaleduL, cxr = (int)scaleduR0;
+    const float iniu = scaleduR0 - L - w;
+    const float endu = scaleduR0 + L + w + 1;
+    if (iniu < 0 || endu >= PR.cols) continue;
+    int bestSad = INT_MAX, bestinc = 0;
+    float vd[2 * 5 + 1];
+    const float cl = (float)PL.buf[(size_t)cy * PL.cols + cxl];
+    for (int inc = -L; inc <= L; ++inc) {
+      const float cr = (float)PR.buf[(size_t)cy * PR.cols + cxr + inc];
+      double acc = 0.0;   // cv::norm(NORM_L1) of two CV_32F patches accumulates in double; every term is an integer
+      for (int dy = -w; dy <= w; ++dy)
+        for (int dx = -w; dx <= w; ++dx) {
+          const float a = (float)PL.buf[(size_t)(cy + dy) * PL.cols + cxl + dx] - cl;
+          const float c = (float)PR.buf[(size_t)(cy + dy) * PR.cols + cxr + inc + dx] - cr;
+          acc += std::fabs((double)(a - c));
+        }
+      const float dist = (float)acc;
+      if (dist < (float)bestSad) { bestSad = (int)dist; bestinc = inc; }
+      vd[L + inc] = dist;
+    }
+    if (bestinc == -L || bestinc == L) continue;
+    const float d1 = vd[L + bestinc - 1], d2 = vd[L + bestinc], d3 = vd[L + bestinc + 1];
+    const float deltaR = (d1 - d3) / (2.0f * (d1 + d3 - 2.0f * d2));
+    if (deltaR < -1 || deltaR > 1) continue;
+    float bestuR = EL.scale[kpL.octave] * ((float)scaleduR0 + (float)bestinc + deltaR);
+    float disparity = uL - bestuR;
+    if (disparity >= minD && disparity < maxD) {
+      if (disparity <= 0) {
+        disparity = 0.01;
+        bestuR = uL - 0.01;
+      }
+      depth[iL] = bf / disparity;
+      uright[iL] = bestuR;
+      distIdx.push_back(std::make_pair(bestSad, iL));
+    }
+  }
+  if (distIdx.empty()) return 0;
+  std::sort(distIdx.begin(), distIdx.end());
+  const float median = distIdx[distIdx.size() / 2].first;
+  const float thDist = 1.5f * 1.4f * median;
+  int kept = (int)distIdx.size();
+  for (int i = (int)distIdx.size() - 1; i >= 0; --i) {
+    if (distIdx[i].first < thDist) break;
+    uright[distIdx[i].second] = -1;
+    depth[distIdx[i].second] = -1;
+    --kept;
+  }
+  return kept;
+}
+
 int64_t orb_oracle_extract_many(int nf, float sf, int nl, int ini, int mn, int flags, const uint8_t* frames, int width,
                                 int height, int n, int nthreads) {
   nthreads = std::max(1, std::min(nthreads, n));

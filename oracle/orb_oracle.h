@@ -86,6 +86,12 @@ typedef struct orb_oracle_knn2 {
 void orb_oracle_hamming_knn(const uint8_t* q, int Q, const uint8_t* db, int64_t D, int64_t index_base,
                             int sentinel, orb_oracle_knn2* out, int nthreads);
 
+/* Frame::ComputeStereoMatches (src/Frame.cc:880-1176) on the outputs and pyramids of the last orb_oracle_extract call of `left` and
+ * `right`. bf = mbf, b = mb. uright / depth [nL], -1 = no match. Returns the number of matches kept. */
+int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_extractor* right, const orb_oracle_kp* kl,
+                            const uint8_t* dl, int nL, const orb_oracle_kp* kr, const uint8_t* dr, int nR, float bf, float b,
+                            float* uright, float* depth);
+
 /* Multi-threaded extraction over frames, one extractor per thread (bench cpu baseline).
  * Returns total keypoints. frames: n contiguous w*h images. */
 int64_t orb_oracle_extract_many(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int flags,

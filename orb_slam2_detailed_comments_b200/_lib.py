@@ -29,7 +29,7 @@ SYMBOLS = [
     "orb_last_error", "orb_abi_version", "orb_device_count", "orb_extractor_create", "orb_extractor_destroy",
     "orb_extractor_get_levels", "orb_extractor_get_scale_factor", "orb_extractor_get_table",
     "orb_extractor_get_features_per_level", "orb_extractor_max_keypoints", "orb_extract_batch",
-    "orb_extract_batch_device", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
+    "orb_extract_batch_device", "orb_extract_stereo_batch", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
@@ -74,6 +74,8 @@ def lib():
     L.orb_extractor_get_features_per_level.argtypes = [vp, vp]
     L.orb_extractor_max_keypoints.argtypes = [vp]
     L.orb_extract_batch.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, i32, vp, vp]
+    L.orb_extract_stereo_batch.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, i32, vp, vp, f32, f32, vp, vp, vp]
+    L.orb_descriptor_distance_host.argtypes = [vp, vp, i64, vp]
     L.orb_extract_batch_device.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp, i32]
     L.orb_extractor_pyramid_dims.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
     L.orb_extractor_pyramid_read.argtypes = [vp, i32, i32, i32, vp, i32]

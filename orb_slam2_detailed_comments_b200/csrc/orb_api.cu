@@ -20,6 +20,8 @@ void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t
 void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_describe(const uint8_t*, const uint8_t*, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
                          const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, int, float, float, float*, float*, int*, int*,
+                       const OrbGeom&, int, cudaStream_t, long long*);
 int orb_knn_num_chunks(int Q, long long D, int num_sms);
 void orb_launch_knn(const uint8_t*, int, const uint8_t*, long long, long long, int, unsigned long long*, int, OrbKnn2*, cudaStream_t);
 void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaStream_t);
@@ -82,15 +84,16 @@ struct orb_extractor {
     cudaEvent_t ev_join = nullptr;
     int frames = 0;          // frames of the last pass run here
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
+    DevBuf st_sad, st_matched;   // stereo: SAD of every kept match [chunk/2][cap], matches per pair [chunk/2]
     DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
-    DevBuf* all[22] = {&pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
+    DevBuf* all[24] = {&st_sad, &st_matched, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
                        &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
   } ws[2];
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
   cudaEvent_t ev_fork = nullptr;
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  DevBuf stage_in[2], out_kps[2], out_desc[2];
+  DevBuf stage_in[2], out_kps[2], out_desc[2], out_ur[2], out_dp[2];
   cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {}, ev_staged[2] = {};   // ev_staged: level 0 has consumed stage_in[b]
   size_t h_cnt_cap = 0;    // ints in h_cnt
   int* h_err = nullptr;    // pinned
@@ -210,6 +213,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.node_off = nodes; nodes += (int)align_up(L.node_cap, 32);
     L.kept_off = L.node_off;
     L.scale = e->scale[l];
+    L.inv_scale = e->invScale[l];
     L.patch_size = (float)(int)(31 * e->scale[l]);
     L.tab_off = tab;
     if (l > 0) {
@@ -420,7 +424,8 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   for (int w = 0; w < 2; ++w)
     for (DevBuf* b : e->ws[w].all) b->release();
-  DevBuf* bufs[] = {&e->tabs, &e->err, &e->stage_in[0], &e->stage_in[1], &e->out_kps[0], &e->out_kps[1], &e->out_desc[0], &e->out_desc[1]};
+  DevBuf* bufs[] = {&e->tabs, &e->err, &e->stage_in[0], &e->stage_in[1], &e->out_kps[0], &e->out_kps[1], &e->out_desc[0], &e->out_desc[1],
+                    &e->out_ur[0], &e->out_ur[1], &e->out_dp[0], &e->out_dp[1]};
   for (DevBuf* b : bufs) b->release();
   if (e->h_cnt) cudaFreeHost(e->h_cnt);
   if (e->s_in) cudaStreamDestroy(e->s_in);
@@ -508,9 +513,21 @@ int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, 
   return ORB_OK;
 }
 
-int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height, int batch,
-                      orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts, int32_t* level_counts) {
+}  // extern "C"
+
+struct StereoReq {   // Frame::ComputeStereoMatches for the pairs (2p, 2p+1) of the batch
+  float bf, b;
+  float* uright;     // [batch / 2][cap], out_mem memory
+  float* depth;
+  int32_t* matched;  // [batch / 2] host, optional
+};
+
+static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height, int batch,
+                              orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts, int32_t* level_counts,
+                              const StereoReq* sr) {
   if (!e || !images || !kps || !desc || !counts) return fail(ORB_E_BADARG, "null argument");
+  if (sr && ((batch & 1) || !sr->uright || !sr->depth || !(sr->b > 0.f) || !(sr->bf > 0.f) || cap > 65535))
+    return fail(ORB_E_BADARG, "stereo: even batch (L,R interleaved), uright/depth buffers, bf > 0, b > 0 and cap <= 65535 required");
   if (width <= 0 || height <= 0 || step < width || batch <= 0 || cap <= 0) return fail(ORB_E_BADARG, "bad size");
   for (int i = 0; i < batch; ++i)
     if (!images[i]) return fail(ORB_E_BADARG, "null image %d", i);   // the reference returns silently on an empty image (:1966)
@@ -521,6 +538,7 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
   const OrbGeom& g = e->geom;
   const int nl = g.nlevels;
   const bool host_out = out_mem != ORB_MEM_DEVICE;
+  if (sr && e->chunk < 2) return fail(ORB_E_BADARG, "stereo needs passes of at least 2 frames (ORB_B200_CHUNK)");
   // Three streams, two buffer sets: the H2D copy of pass p+1 and the D2H copy of pass p-1 overlap the kernels of pass p.
   if (!e->s_in) {
     CU(cudaStreamCreateWithFlags(&e->s_in, cudaStreamNonBlocking));
@@ -539,16 +557,23 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
     if (host_out) {
       if ((rc = e->out_kps[b].ensure((size_t)e->chunk * cap * sizeof(OrbKeypoint))) != ORB_OK) return rc;
       if ((rc = e->out_desc[b].ensure((size_t)e->chunk * cap * 32)) != ORB_OK) return rc;
+      if (sr && (rc = e->out_ur[b].ensure((size_t)e->chunk / 2 * cap * sizeof(float) + 16)) != ORB_OK) return rc;
+      if (sr && (rc = e->out_dp[b].ensure((size_t)e->chunk / 2 * cap * sizeof(float) + 16)) != ORB_OK) return rc;
+    }
+    if (sr) {
+      if ((rc = e->ws[b].st_sad.ensure((size_t)e->chunk / 2 * cap * sizeof(int) + 16)) != ORB_OK) return rc;
+      if ((rc = e->ws[b].st_matched.ensure((size_t)e->chunk / 2 * sizeof(int) + 16)) != ORB_OK) return rc;
     }
   }
-  if (e->h_cnt_cap < (size_t)batch * (1 + nl)) {
+  if (e->h_cnt_cap < (size_t)batch * (2 + nl)) {
     if (e->h_cnt) cudaFreeHost(e->h_cnt);
     e->h_cnt = nullptr; e->h_cnt_cap = 0;
-    CU(cudaMallocHost(&e->h_cnt, (size_t)batch * (1 + nl) * sizeof(int)));
-    e->h_cnt_cap = (size_t)batch * (1 + nl);
+    CU(cudaMallocHost(&e->h_cnt, (size_t)batch * (2 + nl) * sizeof(int)));
+    e->h_cnt_cap = (size_t)batch * (2 + nl);
   }
   int* h_counts = e->h_cnt;
   int* h_levels = e->h_cnt + batch;
+  int* h_matched = e->h_cnt + (size_t)batch * (1 + nl);
   const cudaMemcpyKind kin = in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   int pass = 0;
   for (int f0 = 0, n = 0; f0 < batch; f0 += n, ++pass) {
@@ -556,6 +581,7 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
     const int full = e->chunk;
     const int want = (batch > 2 * full && pass < 2) ? std::max(full >> (2 - pass), 1) : full;
     n = std::min(want, batch - f0);
+    if (sr && (n & 1)) n = n > 1 ? n - 1 : 2;   // a pair never straddles two passes (batch and chunk parity checked below)
     const int b = pass & 1;
     // ---- copy-in stream: stage_in[b] is free once level 0 of pass-2 has read it (the rest of that pass works on the pyramid)
     if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_staged[b], 0));
@@ -577,6 +603,14 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
     OrbKeypoint* dk = host_out ? e->out_kps[b].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
     uint8_t* dd = host_out ? e->out_desc[b].as<uint8_t>() : desc + (long long)f0 * cap * 32;
     run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, P.out_cnt.as<int>(), e->ev_staged[b]);
+    float* dur = nullptr;
+    float* ddp = nullptr;
+    if (sr) {
+      dur = host_out ? e->out_ur[b].as<float>() : sr->uright + (long long)(f0 / 2) * cap;
+      ddp = host_out ? e->out_dp[b].as<float>() : sr->depth + (long long)(f0 / 2) * cap;
+      orb_launch_stereo(P.pyr.as<uint8_t>(), dk, dd, P.out_cnt.as<int>(), cap, sr->bf, sr->b, dur, ddp, P.st_sad.as<int>(),
+                        P.st_matched.as<int>(), g, n / 2, P.st, &e->launches);
+    }
     CU(cudaEventRecord(e->ev_done[b], P.st));
     // ---- copy-out stream (also the small count copies: a D2H queued on the compute stream would wait for the copy engine
     //      behind the previous pass's output copy and hold back the next kernels of that stream)
@@ -587,13 +621,36 @@ int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem
       CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->s_out));
       CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->s_out));
     }
+    if (sr) {
+      CU(cudaMemcpyAsync(h_matched + f0 / 2, P.st_matched.p, (size_t)(n / 2) * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
+      if (host_out) {
+        CU(cudaMemcpyAsync(sr->uright + (long long)(f0 / 2) * cap, dur, (size_t)(n / 2) * cap * sizeof(float), cudaMemcpyDeviceToHost, e->s_out));
+        CU(cudaMemcpyAsync(sr->depth + (long long)(f0 / 2) * cap, ddp, (size_t)(n / 2) * cap * sizeof(float), cudaMemcpyDeviceToHost, e->s_out));
+      }
+    }
     CU(cudaEventRecord(e->ev_out[b], e->s_out));
   }
   CU(cudaStreamSynchronize(e->s_out));
   if ((rc = check_err_flag(e)) != ORB_OK) return rc;   // synchronises the compute stream (counts are on the host after it)
   memcpy(counts, h_counts, (size_t)batch * sizeof(int));
   if (level_counts) memcpy(level_counts, h_levels, (size_t)batch * nl * sizeof(int));
+  if (sr && sr->matched) memcpy(sr->matched, h_matched, (size_t)(batch / 2) * sizeof(int));
   return ORB_OK;
+}
+
+extern "C" {
+
+int orb_extract_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height, int batch,
+                      orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts, int32_t* level_counts) {
+  return extract_batch_impl(e, images, in_mem, step, width, height, batch, kps, desc, out_mem, cap, counts, level_counts, nullptr);
+}
+
+int orb_extract_stereo_batch(orb_extractor* e, const uint8_t* const* images, int in_mem, int step, int width, int height, int pairs,
+                             orb_keypoint* kps, uint8_t* desc, int out_mem, int cap, int32_t* counts, int32_t* level_counts, float bf,
+                             float b, float* uright, float* depth, int32_t* matched) {
+  const StereoReq sr{bf, b, uright, depth, matched};
+  if (pairs <= 0) return fail(ORB_E_BADARG, "bad size");
+  return extract_batch_impl(e, images, in_mem, step, width, height, 2 * pairs, kps, desc, out_mem, cap, counts, level_counts, &sr);
 }
 
 int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int* rows) {

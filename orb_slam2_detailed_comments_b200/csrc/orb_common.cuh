@@ -31,6 +31,7 @@ struct OrbLevel {
   int node_cap, node_off;    // node arrays
   int kept_off;              // offset into per-frame kept arrays (capacity node_cap)
   float scale;               // mvScaleFactor[l]
+  float inv_scale;           // mvInvScaleFactor[l]
   float patch_size;          // (int)(31*scale)
   int tab_off;               // level >= 1: resize tables in padded destination coordinates: x table [xtab_len], then y table [rows]
   int xtab_len;              // cols rounded up to a multiple of 4

@@ -115,6 +115,29 @@ class ORBextractor:
         self._last_n = B
         return kps, desc, counts, lcounts
 
+    def extract_stereo_batch(self, left: np.ndarray, right: np.ndarray, bf: float, b: float):
+        """Stereo Frame constructor on the device: operator() for left[i] and right[i] (src/Frame.cc:158-168) followed by
+        Frame::ComputeStereoMatches (src/Frame.cc:880-1176). left/right [P,H,W] u8. Returns (kps[2P,cap], desc[2P,cap,32],
+        counts[2P] — images interleaved L0, R0, L1, ... — uright[P,cap], depth[P,cap], matched[P])."""
+        if left.shape != right.shape or left.dtype != np.uint8 or right.dtype != np.uint8 or left.ndim != 3:
+            raise TypeError("left/right must be uint8 [P,H,W] of one shape")
+        P, H, W = left.shape
+        inter = np.empty((2 * P, H, W), np.uint8)
+        inter[0::2], inter[1::2] = left, right
+        cap = self.max_keypoints()
+        kps = np.empty((2 * P, cap), KP_DTYPE)
+        desc = np.empty((2 * P, cap, 32), np.uint8)
+        counts = np.zeros(2 * P, np.int32)
+        ur = np.empty((P, cap), np.float32)
+        dp = np.empty((P, cap), np.float32)
+        matched = np.zeros(P, np.int32)
+        ptrs = (C.c_void_p * (2 * P))(*[inter.ctypes.data + i * inter.strides[0] for i in range(2 * P)])
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        check(self._L.orb_extract_stereo_batch(self._h, ptrs, MEM_HOST, W, W, H, P, vp(kps), vp(desc), MEM_HOST, cap, vp(counts), None,
+                                               bf, b, vp(ur), vp(dp), vp(matched)))
+        self._last_n = 2 * P
+        return kps, desc, counts, ur, dp, matched
+
     def extract_batch_device(self, images, kps=None, desc=None, counts=None, sync: bool = True):
         """Device-resident path: `images` is a torch.uint8 CUDA tensor [B,H,W] (last dim contiguous, uniform strides).
         Returns torch tensors (kps [B,cap,7] float32 view of cv::KeyPoint records, desc [B,cap,32] u8, counts [B] i32)."""
