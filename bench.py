@@ -242,6 +242,34 @@ def bench_extract_e2e(ex, frames_host, steps, warmup, world):
     return ms, h2d, d2h, nk
 
 
+def bench_stereo_e2e(ex, frames_host, steps, warmup, world, bf=386.1448, b=0.5372):
+    """Secondary: the stereo Frame constructor (two operator() calls + Frame::ComputeStereoMatches, src/Frame.cc:158-168,
+    880-1176) through orb_extract_stereo_batch with pinned host buffers; frames (2p, 2p+1) are treated as left / right."""
+    import torch
+    from orb_slam2_detailed_comments_b200 import KP_DTYPE
+    B, H, W = frames_host.shape
+    cap = ex.max_keypoints()
+    pin_in = torch.from_numpy(frames_host).pin_memory()
+    pin_k = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    pin_d = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    pin_u = torch.empty((B // 2, cap), dtype=torch.float32).pin_memory()
+    pin_z = torch.empty((B // 2, cap), dtype=torch.float32).pin_memory()
+    out = (pin_k.numpy().view(KP_DTYPE).reshape(B, cap), pin_d.numpy(), pin_u.numpy(), pin_z.numpy())
+    src = pin_in.numpy()
+    for _ in range(max(warmup, 1)):
+        ex.extract_stereo_interleaved(src, bf, b, out=out)
+    _barrier(world)
+    t0 = time.perf_counter()
+    nm = 0
+    for _ in range(steps):
+        r = ex.extract_stereo_interleaved(src, bf, b, out=out)
+        nm += int(r[5].sum())
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    _barrier(world)
+    return _max_over_ranks(dt * 1e3, world), nm / steps
+
+
 def bench_knn(rank, world, steps, warmup):
     """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks, one all_gather
     of the per-query records + device merge when world > 1. pairs/s = Q*D / time (max over ranks)."""
@@ -302,6 +330,7 @@ def run_b200(args):
     e_ms, h2d, d2h, _ = bench_extract_e2e(ex, frames, e_steps, args.warmup, world)
     e2e_value = B * world * e_steps / (e_ms * 1e-3)
 
+    st_ms, st_matches = bench_stereo_e2e(ex, frames, e_steps, args.warmup, world)
     knn_rate, knn_ms, knn_launches = bench_knn(rank, world, max(args.steps, 5), args.warmup)
     popc_peak = pkg.lib().orb_measure_popc_peak(local) if rank == 0 else 0.0
 
@@ -347,6 +376,9 @@ def run_b200(args):
                 "steps": e_steps, "ms_per_step": e_ms / e_steps, "api": "orb_extract_batch (pinned host in/out)"},
         "gpu_launches": int(launches),
         "roofline": roofline,
+        "stereo": {"metric": "stereo frame pairs/sec (extract L+R + Frame::ComputeStereoMatches on device, host to host)",
+                   "value": (B // 2) * world * e_steps / (st_ms * 1e-3), "unit": "pairs/s", "ms_per_step": st_ms / e_steps,
+                   "stereo_matches_per_pair": st_matches / (B // 2), "api": "orb_extract_stereo_batch (pinned host in/out)"},
         "knn": {"metric": "Hamming matches/sec (k=2 brute force)", "value": knn_rate, "unit": "pairs/s",
                 "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
                           + (", NCCL all_gather + device top-2 merge" if world > 1 else ""),

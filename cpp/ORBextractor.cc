@@ -88,6 +88,48 @@ void ORBextractor::ExtractBatch(const std::vector<cv::Mat>& images, std::vector<
   }
 }
 
+void ORBextractor::ExtractStereo(const cv::Mat& left, const cv::Mat& right, float mbf, float mb, std::vector<cv::KeyPoint>& keysLeft,
+                                 cv::Mat& descLeft, std::vector<cv::KeyPoint>& keysRight, cv::Mat& descRight,
+                                 std::vector<float>& uRight, std::vector<float>& depth) {
+  if (left.empty() || right.empty() || left.type() != CV_8UC1 || right.type() != CV_8UC1 || left.cols != right.cols || left.rows != right.rows)
+    throw std::runtime_error("ORBextractor::ExtractStereo: two non-empty CV_8UC1 images of one size required");
+  const int W = left.cols, H = left.rows;
+  mStage.resize((size_t)2 * W * H);
+  for (int r = 0; r < H; ++r) {
+    std::memcpy(&mStage[(size_t)r * W], left.ptr<unsigned char>(r), W);
+    std::memcpy(&mStage[((size_t)H + r) * W], right.ptr<unsigned char>(r), W);
+  }
+  const uint8_t* ptrs[2] = {mStage.data(), mStage.data() + (size_t)W * H};
+  const int cap = orb_extractor_max_keypoints(mpHandle);
+  std::vector<orb_keypoint> kps((size_t)2 * cap);
+  std::vector<uint8_t> desc((size_t)2 * cap * 32);
+  std::vector<float> ur(cap), dp(cap);
+  int32_t counts[2] = {0, 0};
+  check(orb_extract_stereo_batch(mpHandle, ptrs, ORB_MEM_HOST, W, W, H, 1, kps.data(), desc.data(), ORB_MEM_HOST, cap, counts, nullptr, mbf, mb,
+                                 ur.data(), dp.data(), nullptr),
+        "orb_extract_stereo_batch");
+  std::vector<cv::KeyPoint>* keys[2] = {&keysLeft, &keysRight};
+  cv::Mat* descs[2] = {&descLeft, &descRight};
+  for (int i = 0; i < 2; ++i) {
+    const int n = counts[i];
+    keys[i]->resize(n);
+    if (n == 0) { descs[i]->release(); continue; }
+    std::memcpy((void*)keys[i]->data(), &kps[(size_t)i * cap], (size_t)n * sizeof(orb_keypoint));
+    descs[i]->create(n, 32, CV_8U);
+    for (int r = 0; r < n; ++r) std::memcpy(descs[i]->ptr<unsigned char>(r), &desc[((size_t)i * cap + r) * 32], 32);
+  }
+  uRight.assign(ur.begin(), ur.begin() + counts[0]);
+  depth.assign(dp.begin(), dp.begin() + counts[0]);
+  if (mbDownloadPyramid) {
+    for (int l = 0; l < nlevels; ++l) {
+      int cc = 0, rr = 0;
+      check(orb_extractor_pyramid_dims(mpHandle, l, &cc, &rr), "pyramid_dims");
+      mvImagePyramid[l].create(rr, cc, CV_8UC1);
+      check(orb_extractor_pyramid_read(mpHandle, -1, l, 0, mvImagePyramid[l].ptr<unsigned char>(0), (int)mvImagePyramid[l].step), "pyramid_read");
+    }
+  }
+}
+
 void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint>& _keypoints,
                               cv::OutputArray _descriptors) {
 #ifdef ORB_B200_USE_OPENCV

@@ -42,6 +42,13 @@ class ORBextractor {
   void ExtractBatch(const std::vector<cv::Mat>& images, std::vector<std::vector<cv::KeyPoint>>& keypoints,
                     std::vector<cv::Mat>& descriptors);
 
+  // Stereo Frame constructor in one call (src/Frame.cc:158-168 + Frame::ComputeStereoMatches, src/Frame.cc:880-1176): extracts both
+  // images and fills mvuRight / mvDepth of the left keypoints on the device. mbf = baseline * fx, mb = baseline.
+  // mvImagePyramid afterwards holds the RIGHT image's levels (the last image of the call).
+  void ExtractStereo(const cv::Mat& left, const cv::Mat& right, float mbf, float mb, std::vector<cv::KeyPoint>& keysLeft,
+                     cv::Mat& descLeft, std::vector<cv::KeyPoint>& keysRight, cv::Mat& descRight, std::vector<float>& uRight,
+                     std::vector<float>& depth);
+
   int inline GetLevels() { return nlevels; }
   float inline GetScaleFactor() { return scaleFactor; }
   std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }

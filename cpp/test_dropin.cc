@@ -128,6 +128,29 @@ int main(int argc, char** argv) {
       const int o = orb_oracle_descriptor_distance(a.ptr<unsigned char>(i), b.ptr<unsigned char>(i));
       REQUIRE(dist[i] == o && ORB_SLAM2::ORBmatcher::DescriptorDistance(a.row(i), b.row(i)) == o, "DescriptorDistance row %d", i);
     }
+    // stereo Frame constructor in one call: keypoints as above, mvuRight / mvDepth equal to the oracle's ComputeStereoMatches
+    {
+      std::vector<cv::KeyPoint> kl, kr;
+      cv::Mat dl, dr;
+      std::vector<float> ur, dp;
+      const float bf = 386.1448f, mb = 0.5372f;
+      ex.ExtractStereo(contiguous, right, bf, mb, kl, dl, kr, dr, ur, dp);
+      orb_oracle_extractor* oR = orb_oracle_create(nf, 1.2f, 8, 20, 7, 0);
+      const int capo = 1 << 16;
+      std::vector<orb_oracle_kp> okl(capo), okr(capo);
+      std::vector<uint8_t> odl((size_t)capo * 32), odr((size_t)capo * 32);
+      const int nl = orb_oracle_extract(oe, contiguous.data, (int)contiguous.step, W, H, okl.data(), odl.data(), capo, nullptr);
+      const int nr = orb_oracle_extract(oR, right.data, (int)right.step, W, H, okr.data(), odr.data(), capo, nullptr);
+      REQUIRE(nl == (int)kl.size() && nr == (int)kr.size() && (int)ur.size() == nl && (int)dp.size() == nl, "ExtractStereo sizes");
+      REQUIRE(std::memcmp(kl.data(), okl.data(), (size_t)nl * 28) == 0 && std::memcmp(kr.data(), okr.data(), (size_t)nr * 28) == 0, "ExtractStereo keypoints");
+      std::vector<float> our(nl), odp(nl);
+      const int kept = orb_oracle_stereo_match(oe, oR, okl.data(), odl.data(), nl, okr.data(), odr.data(), nr, bf, mb, our.data(), odp.data());
+      REQUIRE(std::memcmp(ur.data(), our.data(), (size_t)nl * 4) == 0, "mvuRight differs from the oracle");
+      REQUIRE(std::memcmp(dp.data(), odp.data(), (size_t)nl * 4) == 0, "mvDepth differs from the oracle");
+      REQUIRE(kept > 50, "too few stereo matches (%d)", kept);
+      orb_oracle_destroy(oR);
+      std::printf("ExtractStereo: %d stereo matches, mvuRight / mvDepth bit-exact vs oracle\n", kept);
+    }
     std::printf("ORBmatcher: kNN over %d x %d bit-exact, %d ratio-test accepts, DescriptorDistance x %d exact\n", bd[0].rows, bd[1].rows, nacc, m);
   }
   orb_oracle_destroy(oe);

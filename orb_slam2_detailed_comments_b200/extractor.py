@@ -124,18 +124,28 @@ class ORBextractor:
         P, H, W = left.shape
         inter = np.empty((2 * P, H, W), np.uint8)
         inter[0::2], inter[1::2] = left, right
+        return self.extract_stereo_interleaved(inter, bf, b)
+
+    def extract_stereo_interleaved(self, images: np.ndarray, bf: float, b: float, out=None):
+        """Same with the images already interleaved [2P,H,W] (L0, R0, L1, R1, ...). `out` may pass preallocated
+        (kps[2P,cap], desc[2P,cap,32], uright[P,cap], depth[P,cap]) e.g. pinned buffers."""
+        if images.dtype != np.uint8 or images.ndim != 3 or images.shape[0] % 2 or not images.flags.c_contiguous:
+            raise TypeError("images must be a C-contiguous uint8 [2P,H,W] array")
+        B, H, W = images.shape
+        P = B // 2
         cap = self.max_keypoints()
-        kps = np.empty((2 * P, cap), KP_DTYPE)
-        desc = np.empty((2 * P, cap, 32), np.uint8)
-        counts = np.zeros(2 * P, np.int32)
-        ur = np.empty((P, cap), np.float32)
-        dp = np.empty((P, cap), np.float32)
+        if out is None:
+            kps, desc = np.empty((B, cap), KP_DTYPE), np.empty((B, cap, 32), np.uint8)
+            ur, dp = np.empty((P, cap), np.float32), np.empty((P, cap), np.float32)
+        else:
+            kps, desc, ur, dp = out
+        counts = np.zeros(B, np.int32)
         matched = np.zeros(P, np.int32)
-        ptrs = (C.c_void_p * (2 * P))(*[inter.ctypes.data + i * inter.strides[0] for i in range(2 * P)])
+        ptrs = (C.c_void_p * B)(*[images.ctypes.data + i * images.strides[0] for i in range(B)])
         vp = lambda a: a.ctypes.data_as(C.c_void_p)
         check(self._L.orb_extract_stereo_batch(self._h, ptrs, MEM_HOST, W, W, H, P, vp(kps), vp(desc), MEM_HOST, cap, vp(counts), None,
                                                bf, b, vp(ur), vp(dp), vp(matched)))
-        self._last_n = 2 * P
+        self._last_n = B
         return kps, desc, counts, ur, dp, matched
 
     def extract_batch_device(self, images, kps=None, desc=None, counts=None, sync: bool = True):

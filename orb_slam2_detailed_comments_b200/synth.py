@@ -65,6 +65,14 @@ def synth_batch(width: int, height: int, n: int, seed0: int = 1234, distinct: in
     return out
 
 
+def synth_stereo_pair(width: int, height: int, seed: int, shift: int):
+    """Rectified pair: right = left shifted by `shift` px (constant disparity) plus +-2 grey levels of independent noise."""
+    left = synth_frame(width, height, seed)
+    rng = np.random.RandomState(seed + 99)
+    right = np.roll(left, -shift, axis=1).astype(np.int16) + rng.randint(-2, 3, left.shape)
+    return left, np.clip(right, 0, 255).astype(np.uint8)
+
+
 def synth_descriptors(n_query: int, n_db: int, seed: int = 7, planted_frac: float = 0.1):
     """Random 256-bit descriptors; planted_frac of the queries are database rows with 0..40 bit flips
     so the ratio test has accepts (config C4)."""

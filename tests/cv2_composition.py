@@ -256,3 +256,96 @@ def extract(cv2, image, P: Params, pattern=None, return_stages=False):
     if return_stages:
         return kps, desc, levels, blurred, raw_all
     return kps, desc
+
+
+def stereo_matches(cv2, kL, dL, levelsL, kR, dR, levelsR, P: Params, bf, b):
+    """Frame::ComputeStereoMatches (src/Frame.cc:880-1176) with the reference's control flow and float32 arithmetic; the
+    patch arithmetic (convertTo CV_32F, centre subtraction, cv::norm NORM_L1) and the Hamming distance (cv2.norm NORM_HAMMING)
+    are executed by the real OpenCV. kL / kR: rows (x, y, size, angle, response, octave). Returns (mvuRight, mvDepth) float32.
+    Canonical choices as in the oracle: rows outside the level-0 image hold no candidates; an empty match list skips the filter."""
+    f32 = np.float32
+    N, Nr = len(kL), len(kR)
+    uright = np.full(N, -1.0, f32)
+    depth = np.full(N, -1.0, f32)
+    TH_HIGH, TH_LOW = 100, 50
+    thOrbDist = (TH_HIGH + TH_LOW) // 2
+    nRows = levelsL[0].shape[0]
+    rows = [[] for _ in range(nRows)]
+    for iR in range(Nr):
+        kpY = f32(kR[iR][1])
+        r = f32(2.0) * P.scale[int(kR[iR][5])]
+        maxr = int(math.ceil(float(f32(kpY + r))))
+        minr = int(math.floor(float(f32(kpY - r))))
+        for yi in range(minr, maxr + 1):
+            if 0 <= yi < nRows:
+                rows[yi].append(iR)
+    bf, b = f32(bf), f32(b)
+    minD, maxD = f32(0), f32(bf / b)
+    dist_idx = []
+    for iL in range(N):
+        uL, vL, levelL = f32(kL[iL][0]), f32(kL[iL][1]), int(kL[iL][5])
+        row = int(vL)
+        if not (0 <= row < nRows) or not rows[row]:
+            continue
+        minU, maxU = f32(uL - maxD), f32(uL - minD)
+        if maxU < 0:
+            continue
+        best, bestR = TH_HIGH, 0
+        for iR in rows[row]:
+            octR = int(kR[iR][5])
+            if octR < levelL - 1 or octR > levelL + 1:
+                continue
+            uR = f32(kR[iR][0])
+            if minU <= uR <= maxU:
+                d = int(cv2.norm(dL[iL:iL + 1], dR[iR:iR + 1], cv2.NORM_HAMMING))
+                if d < best:
+                    best, bestR = d, iR
+        if best >= thOrbDist:
+            continue
+        uR0 = f32(kR[bestR][0])
+        sf = P.inv_scale[levelL]
+        rnd = lambda v: f32(math.floor(float(v) + 0.5)) if v >= 0 else f32(-math.floor(-float(v) + 0.5))   # std::round
+        suL, svL, suR0 = rnd(f32(uL * sf)), rnd(f32(vL * sf)), rnd(f32(uR0 * sf))
+        w, L = 5, 5
+        imL, imR = levelsL[levelL], levelsR[levelL]
+        cy, cxl, cxr = int(svL), int(suL), int(suR0)
+        IL = imL[cy - w:cy + w + 1, cxl - w:cxl + w + 1].astype(f32)
+        IL = IL - IL[w, w] * np.ones(IL.shape, f32)
+        iniu = f32(f32(suR0 - f32(L)) - f32(w))
+        endu = f32(f32(f32(suR0 + f32(L)) + f32(w)) + f32(1))
+        if iniu < 0 or endu >= imR.shape[1]:
+            continue
+        best_sad, best_inc, vd = 2 ** 31 - 1, 0, [f32(0)] * (2 * L + 1)
+        for inc in range(-L, L + 1):
+            IR = imR[cy - w:cy + w + 1, cxr + inc - w:cxr + inc + w + 1].astype(f32)
+            IR = IR - IR[w, w] * np.ones(IR.shape, f32)
+            dist = f32(cv2.norm(IL, IR, cv2.NORM_L1))
+            if dist < f32(best_sad):
+                best_sad, best_inc = int(dist), inc
+            vd[L + inc] = dist
+        if best_inc == -L or best_inc == L:
+            continue
+        d1, d2, d3 = vd[L + best_inc - 1], vd[L + best_inc], vd[L + best_inc + 1]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            delta = f32(f32(d1 - d3) / f32(f32(2.0) * f32(f32(d1 + d3) - f32(f32(2.0) * d2))))
+        if delta < -1 or delta > 1:
+            continue
+        best_uR = f32(P.scale[levelL] * f32(f32(suR0 + f32(best_inc)) + delta))
+        disparity = f32(uL - best_uR)
+        if disparity >= minD and disparity < maxD:
+            if disparity <= 0:
+                disparity = f32(0.01)
+                best_uR = f32(float(uL) - 0.01)
+            depth[iL] = f32(bf / disparity)
+            uright[iL] = best_uR
+            dist_idx.append((best_sad, iL))
+    if dist_idx:
+        dist_idx.sort()
+        median = f32(dist_idx[len(dist_idx) // 2][0])
+        th = f32(f32(f32(1.5) * f32(1.4)) * median)
+        for d, i in reversed(dist_idx):
+            if f32(d) < th:
+                break
+            uright[i] = -1
+            depth[i] = -1
+    return uright, depth

@@ -9,10 +9,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _pair(w, h, seed, shift):
-    left = synth.synth_frame(w, h, seed)
-    rng = np.random.RandomState(seed + 99)
-    right = np.roll(left, -shift, axis=1).astype(np.int16) + rng.randint(-2, 3, left.shape)   # disparity + sensor noise
-    return left, np.clip(right, 0, 255).astype(np.uint8)
+    return synth.synth_stereo_pair(w, h, seed, shift)
 
 
 def _oracle_pair(oracle, nf, left, right, bf, b):

@@ -15,7 +15,8 @@ from orb_slam2_detailed_comments_b200 import synth
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 PIPELINES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                   if os.path.basename(p) not in ("fast_atan2.npz", "primitives_333x257.npz"))
+                   if os.path.basename(p) not in ("fast_atan2.npz", "primitives_333x257.npz") and not os.path.basename(p).startswith("stereo_"))
+STEREO = sorted(glob.glob(os.path.join(GOLDEN, "stereo_*.npz")))   # tests/golden/make_golden_stereo.py
 
 
 def sha(a: np.ndarray) -> str:
@@ -142,3 +143,20 @@ def test_oracle_is_deterministic_and_reentrant(oracle):
     assert np.array_equal(a[0].view(np.uint8), b[0].view(np.uint8)) and np.array_equal(a[1], b[1])
     frames = np.stack([img, img[::-1].copy()])
     assert oracle.extract_many(frames, 500, 2) == oracle.extract_many(frames, 500, 1) > 0
+
+
+@pytest.mark.parametrize("path", STEREO, ids=[os.path.basename(p)[:-4] for p in STEREO])
+def test_stereo_matches_cv2_composition(oracle, path):
+    """orb_oracle_stereo_match (restatement of src/Frame.cc:880-1176) == the real-OpenCV composition: mvuRight and mvDepth
+    bit for bit, on the oracle's own extraction of both images."""
+    g = np.load(path)
+    w, h, nf, seed, shift = (int(v) for v in g["params"])
+    left, right = synth.synth_stereo_pair(w, h, seed, shift)
+    oL, oR = oracle.OracleExtractor(nf), oracle.OracleExtractor(nf)
+    kl, dl, _ = oL(left)
+    kr, dr, _ = oR(right)
+    assert len(kl) == int(g["n_left"]) and len(kr) == int(g["n_right"])
+    ur, dp, kept = oracle.stereo_match(oL, oR, kl, dl, kr, dr, float(g["bf"]), float(g["b"]))
+    assert np.array_equal(ur.view(np.uint32), g["uright"].view(np.uint32))
+    assert np.array_equal(dp.view(np.uint32), g["depth"].view(np.uint32))
+    assert kept == int((g["uright"] >= 0).sum()) and kept > 200
