@@ -20,8 +20,8 @@ void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t
 void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_describe(const uint8_t*, const uint8_t*, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
                          const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, int, float, float, float*, float*, int*, int*,
-                       const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, int, float, float, float*, float*, int*, int*, int*,
+                       unsigned short*, const OrbGeom&, int, cudaStream_t, long long*);
 int orb_knn_num_chunks(int Q, long long D, int num_sms);
 void orb_launch_knn(const uint8_t*, int, const uint8_t*, long long, long long, int, unsigned long long*, int, OrbKnn2*, cudaStream_t);
 void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaStream_t);
@@ -85,8 +85,9 @@ struct orb_extractor {
     int frames = 0;          // frames of the last pass run here
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
     DevBuf st_sad, st_matched;   // stereo: SAD of every kept match [chunk/2][cap], matches per pair [chunk/2]
+    DevBuf st_rows, st_sorted;   // stereo: right keypoints sorted by image row: starts [chunk/2][rows0 + 1], indices [chunk/2][cap]
     DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
-    DevBuf* all[24] = {&st_sad, &st_matched, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
+    DevBuf* all[26] = {&st_rows, &st_sorted, &st_sad, &st_matched, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
                        &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
   } ws[2];
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
@@ -563,6 +564,8 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
     if (sr) {
       if ((rc = e->ws[b].st_sad.ensure((size_t)e->chunk / 2 * cap * sizeof(int) + 16)) != ORB_OK) return rc;
       if ((rc = e->ws[b].st_matched.ensure((size_t)e->chunk / 2 * sizeof(int) + 16)) != ORB_OK) return rc;
+      if ((rc = e->ws[b].st_rows.ensure((size_t)e->chunk / 2 * (g.lv[0].rows + 1) * sizeof(int) + 16)) != ORB_OK) return rc;
+      if ((rc = e->ws[b].st_sorted.ensure((size_t)e->chunk / 2 * cap * sizeof(unsigned short) + 16)) != ORB_OK) return rc;
     }
   }
   if (e->h_cnt_cap < (size_t)batch * (2 + nl)) {
@@ -609,7 +612,7 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
       dur = host_out ? e->out_ur[b].as<float>() : sr->uright + (long long)(f0 / 2) * cap;
       ddp = host_out ? e->out_dp[b].as<float>() : sr->depth + (long long)(f0 / 2) * cap;
       orb_launch_stereo(P.pyr.as<uint8_t>(), dk, dd, P.out_cnt.as<int>(), cap, sr->bf, sr->b, dur, ddp, P.st_sad.as<int>(),
-                        P.st_matched.as<int>(), g, n / 2, P.st, &e->launches);
+                        P.st_matched.as<int>(), P.st_rows.as<int>(), P.st_sorted.as<unsigned short>(), g, n / 2, P.st, &e->launches);
     }
     CU(cudaEventRecord(e->ev_done[b], P.st));
     // ---- copy-out stream (also the small count copies: a D2H queued on the compute stream would wait for the copy engine

@@ -19,15 +19,51 @@
 #define ST_TH_HIGH 100
 #define ST_TH_ORB 75   // (TH_HIGH + TH_LOW) / 2
 
+// Counting sort of the right keypoints of every pair by image row (int)y (clamped to the image): row_start[pair][nRows + 1] and
+// sorted[pair][cap]. The matcher then only visits the rows within the largest search radius of (int)vL; the order inside a row
+// is irrelevant because the winner is the minimum of (dist << 16 | iR).
+__global__ void __launch_bounds__(256)
+orb_stereo_bin_kernel(const OrbKeypoint* __restrict__ kps, const int* __restrict__ counts, int cap, int nRows,
+                      int* __restrict__ row_start, unsigned short* __restrict__ sorted) {
+  extern __shared__ int s_hist[];   // [nRows + 1] counts -> starts -> cursors
+  __shared__ int s_part[256];
+  const int pair = blockIdx.x;
+  const int nR = min(counts[2 * pair + 1], cap);
+  const OrbKeypoint* kr = kps + (long long)(2 * pair + 1) * cap;
+  for (int i = threadIdx.x; i <= nRows; i += 256) s_hist[i] = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < nR; i += 256) atomicAdd(&s_hist[min(max((int)kr[i].y, 0), nRows - 1)], 1);
+  __syncthreads();
+  // exclusive scan: every thread owns a contiguous slice
+  const int per = (nRows + 256) / 256;
+  const int lo = threadIdx.x * per, hi = min(lo + per, nRows + 1);
+  int sum = 0;
+  for (int i = lo; i < hi; ++i) sum += s_hist[i];
+  s_part[threadIdx.x] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int t = 0; t < 256; ++t) { const int v = s_part[t]; s_part[t] = acc; acc += v; }
+  }
+  __syncthreads();
+  int acc = s_part[threadIdx.x];
+  int* rs = row_start + (long long)pair * (nRows + 1);
+  for (int i = lo; i < hi; ++i) { const int v = s_hist[i]; s_hist[i] = acc; rs[i] = acc; acc += v; }
+  __syncthreads();
+  unsigned short* so = sorted + (long long)pair * cap;
+  for (int i = threadIdx.x; i < nR; i += 256) so[atomicAdd(&s_hist[min(max((int)kr[i].y, 0), nRows - 1)], 1)] = (unsigned short)i;
+}
+
 __global__ void __launch_bounds__(ST_WARPS * 32)
 orb_stereo_match_kernel(const uint8_t* __restrict__ pyr, const OrbKeypoint* __restrict__ kps, const uint8_t* __restrict__ desc,
-                        const int* __restrict__ counts, int cap, float bf, float b, float* __restrict__ uright,
+                        const int* __restrict__ counts, int cap, float bf, float b, const int* __restrict__ row_start,
+                        const unsigned short* __restrict__ sorted, int margin, float* __restrict__ uright,
                         float* __restrict__ depth, int* __restrict__ sad_out, const __grid_constant__ OrbGeom g) {
   const int pair = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int iL = blockIdx.x * ST_WARPS + (threadIdx.x >> 5);
   const int fL = 2 * pair, fR = 2 * pair + 1;
-  const int nL = min(counts[fL], cap), nR = min(counts[fR], cap);
+  const int nL = min(counts[fL], cap);
   if (iL >= cap) return;
   const long long o = (long long)pair * cap + iL;
   if (iL >= nL) {
@@ -46,7 +82,11 @@ orb_stereo_match_kernel(const uint8_t* __restrict__ pyr, const OrbKeypoint* __re
   if (row >= 0 && row < nRows && !(maxU < 0.f)) {
     const uint4* dl4 = reinterpret_cast<const uint4*>(desc + ((long long)fL * cap + iL) * 32);
     const uint4 a0 = __ldg(dl4), a1 = __ldg(dl4 + 1);
-    for (int iR = lane; iR < nR; iR += 32) {
+    const int* rs = row_start + (long long)pair * (nRows + 1);
+    const unsigned short* so = sorted + (long long)pair * cap;
+    const int j0 = rs[max(row - margin, 0)], j1 = rs[min(row + margin + 1, nRows)];
+    for (int j = j0 + lane; j < j1; j += 32) {
+      const int iR = so[j];
       const OrbKeypoint k = kr[iR];
       const float r = __fmul_rn(2.0f, g.lv[k.octave].scale);
       const int maxr = (int)ceilf(__fadd_rn(k.y, r));
@@ -59,7 +99,7 @@ orb_stereo_match_kernel(const uint8_t* __restrict__ pyr, const OrbKeypoint* __re
       const int dist = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
                        __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
       const unsigned key = ((unsigned)dist << 16) | (unsigned)iR;
-      best = min(best, key);   // iR ascends per lane: an equal distance never replaces an earlier index
+      best = min(best, key);   // smallest distance, then earliest index: the winner of the reference's ascending strict-< scan
     }
   }
   best = __reduce_min_sync(0xffffffffu, best);
@@ -182,9 +222,16 @@ orb_stereo_filter_kernel(const int* __restrict__ counts, int cap, float* __restr
 }
 
 void orb_launch_stereo(const uint8_t* pyr, const OrbKeypoint* kps, const uint8_t* desc, const int* counts, int cap, float bf, float b,
-                       float* uright, float* depth, int* sad, int* matched, const OrbGeom& g, int pairs, cudaStream_t st, long long* launches) {
-  orb_stereo_match_kernel<<<dim3((cap + ST_WARPS - 1) / ST_WARPS, pairs), ST_WARPS * 32, 0, st>>>(pyr, kps, desc, counts, cap, bf, b, uright,
-                                                                                                 depth, sad, g);
+                       float* uright, float* depth, int* sad, int* matched, int* row_start, unsigned short* sorted, const OrbGeom& g,
+                       int pairs, cudaStream_t st, long long* launches) {
+  const int nRows = g.lv[0].rows;
+  float smax = 1.f;
+  for (int l = 0; l < g.nlevels; ++l) smax = fmaxf(smax, g.lv[l].scale);
+  const int margin = (int)ceilf(2.f * smax) + 2;   // rows a right keypoint can be binned away from (int)y: ceil(y + r) - (int)y <= ceil(r) + 1
+  const size_t smem = (size_t)(nRows + 1) * sizeof(int);
+  orb_stereo_bin_kernel<<<pairs, 256, smem, st>>>(kps, counts, cap, nRows, row_start, sorted);
+  orb_stereo_match_kernel<<<dim3((cap + ST_WARPS - 1) / ST_WARPS, pairs), ST_WARPS * 32, 0, st>>>(pyr, kps, desc, counts, cap, bf, b, row_start,
+                                                                                                 sorted, margin, uright, depth, sad, g);
   orb_stereo_filter_kernel<<<pairs, 256, 0, st>>>(counts, cap, uright, depth, sad, matched);
-  *launches += 2;
+  *launches += 3;
 }
