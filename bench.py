@@ -152,12 +152,41 @@ def run_reference(args):
 
 
 # ---- GPU arm ---------------------------------------------------------------------------------------------
+_NUMA = None
+
+
+def _bind_to_gpu_numa_node(local):
+    """Pin this rank to the CPUs of its GPU's NUMA node before any pinned buffer is allocated (first touch puts the
+    pages on that node), so that N ranks do not pull their frames across the socket interconnect. Best effort: a box
+    without the sysfs entries stays unbound."""
+    global _NUMA
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local)
+        bus = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            _NUMA = {"node": node, "cpus": len(cpus)}
+    except Exception:
+        pass
+
+
 def _dist_setup(args):
     import torch
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    if world > 1:
+        _bind_to_gpu_numa_node(local)
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -386,6 +415,8 @@ def run_b200(args):
                 "roofline": {"bound": "popc", "achieved": knn_rate * 8 / world, "peak": popc_peak, "unit": "popc.b32/s",
                              "frac": (knn_rate * 8 / world / popc_peak) if popc_peak else None}},
     }
+    if _NUMA:
+        line["e2e"]["numa"] = _NUMA   # this rank's binding (rank 0); every rank binds to its own GPU's node
     if world == 1 and not args.no_cpu:
         cores = _host_cores()
         n = 512   # ~20-30 core-seconds of CPU work

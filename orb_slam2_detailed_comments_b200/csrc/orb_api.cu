@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <chrono>
 #include <vector>
 
 #include "../../include/orb_b200.h"
@@ -84,18 +85,20 @@ struct orb_extractor {
     cudaEvent_t ev_join = nullptr;
     int frames = 0;          // frames of the last pass run here
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
-    DevBuf st_sad, st_matched;   // stereo: SAD of every kept match [chunk/2][cap], matches per pair [chunk/2]
+    DevBuf st_sad;   // stereo: SAD of every kept match [chunk/2][cap]
     DevBuf st_rows, st_sorted;   // stereo: right keypoints sorted by image row: starts [chunk/2][rows0 + 1], indices [chunk/2][cap]
     DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
-    DevBuf* all[26] = {&st_rows, &st_sorted, &st_sad, &st_matched, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
+    DevBuf* all[25] = {&st_rows, &st_sorted, &st_sad, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
                        &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
   } ws[2];
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
   cudaEvent_t ev_fork = nullptr;
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  DevBuf stage_in[2], out_kps[2], out_desc[2], out_ur[2], out_dp[2];
-  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {}, ev_staged[2] = {};   // ev_staged: level 0 has consumed stage_in[b]
+  // Output staging is triple-buffered: pass p+2 runs on the workspace of pass p and must not wait for pass p's D2H copy.
+  DevBuf stage_in[2], out_kps[3], out_desc[3], out_ur[3], out_dp[3];
+  DevBuf cnt_all;   // per call: counts [batch], level counts [batch][nlevels], stereo matches [batch/2]; one D2H at the end
+  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[3] = {}, ev_staged[2] = {};   // ev_staged: level 0 has consumed stage_in[b]
   size_t h_cnt_cap = 0;    // ints in h_cnt
   int* h_err = nullptr;    // pinned
   int* h_cnt = nullptr;    // pinned [batch * (1 + nlevels)]: counts, then per-level counts
@@ -313,10 +316,11 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
 
 // One internal pass over `n` (<= chunk) device-resident frames; outputs to device pointers.
 static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, long long image_stride, int n, OrbKeypoint* kps,
-                     uint8_t* desc, int cap, int* counts_dev, cudaEvent_t ev_input_consumed = nullptr) {
+                     uint8_t* desc, int cap, int* counts_dev, cudaEvent_t ev_input_consumed = nullptr, int* level_counts_dev = nullptr) {
   const OrbGeom& g = e->geom;
   orb_extractor::PassWs& P = e->ws[w];
   cudaStream_t st = P.st;
+  int* kept_cnt = level_counts_dev ? level_counts_dev : P.kept_cnt.as<int>();
   QtScratch S;
   S.key = P.q_key.as<uint32_t>(); S.knode = P.q_knode.as<int>(); S.kchild = P.q_kchild.as<uint8_t>();
   S.bbox = P.q_bbox.as<int4>(); S.ncount = P.q_ncount.as<int>(); S.pidx = P.q_pidx.as<int>();
@@ -341,10 +345,10 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
   if (prof) cudaEventRecord(ev[2], st);
   orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[3], st);
-  orb_launch_quadtree(P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), S, P.kept.as<uint32_t>(), P.kept_cnt.as<int>(),
+  orb_launch_quadtree(P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), S, P.kept.as<uint32_t>(), kept_cnt,
                       e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[4], st);
-  orb_launch_describe(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.kept.as<uint32_t>(), P.kept_cnt.as<int>(), kps, desc, cap,
+  orb_launch_describe(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.kept.as<uint32_t>(), kept_cnt, kps, desc, cap,
                       counts_dev, e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[5], st);
   P.frames = n;
@@ -425,18 +429,19 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   for (int w = 0; w < 2; ++w)
     for (DevBuf* b : e->ws[w].all) b->release();
-  DevBuf* bufs[] = {&e->tabs, &e->err, &e->stage_in[0], &e->stage_in[1], &e->out_kps[0], &e->out_kps[1], &e->out_desc[0], &e->out_desc[1],
-                    &e->out_ur[0], &e->out_ur[1], &e->out_dp[0], &e->out_dp[1]};
+  DevBuf* bufs[] = {&e->tabs, &e->err, &e->cnt_all, &e->stage_in[0], &e->stage_in[1]};
   for (DevBuf* b : bufs) b->release();
+  for (int b = 0; b < 3; ++b) { e->out_kps[b].release(); e->out_desc[b].release(); e->out_ur[b].release(); e->out_dp[b].release(); }
   if (e->h_cnt) cudaFreeHost(e->h_cnt);
   if (e->s_in) cudaStreamDestroy(e->s_in);
   if (e->s_out) cudaStreamDestroy(e->s_out);
   for (int b = 0; b < 2; ++b) {
     if (e->ev_in[b]) cudaEventDestroy(e->ev_in[b]);
     if (e->ev_done[b]) cudaEventDestroy(e->ev_done[b]);
-    if (e->ev_out[b]) cudaEventDestroy(e->ev_out[b]);
     if (e->ev_staged[b]) cudaEventDestroy(e->ev_staged[b]);
   }
+  for (int b = 0; b < 3; ++b)
+    if (e->ev_out[b]) cudaEventDestroy(e->ev_out[b]);
   for (cudaEvent_t ev : e->ev)
     if (ev) cudaEventDestroy(ev);
   delete e;
@@ -547,23 +552,24 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
     for (int b = 0; b < 2; ++b) {
       CU(cudaEventCreateWithFlags(&e->ev_in[b], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&e->ev_done[b], cudaEventDisableTiming));
-      CU(cudaEventCreateWithFlags(&e->ev_out[b], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&e->ev_staged[b], cudaEventDisableTiming));
     }
+    for (int b = 0; b < 3; ++b) CU(cudaEventCreateWithFlags(&e->ev_out[b], cudaEventDisableTiming));
   }
   const size_t fbytes = (size_t)step * height;   // frames are staged with the caller's pitch (level 0 reads any pitch)
   const int nbuf = batch > e->chunk ? 2 : 1;
-  for (int b = 0; b < nbuf; ++b) {
-    if ((rc = e->stage_in[b].ensure((size_t)e->chunk * fbytes)) != ORB_OK) return rc;
+  const int nout = batch > 2 * e->chunk ? 3 : nbuf;
+  if ((rc = e->cnt_all.ensure((size_t)batch * (2 + nl) * sizeof(int))) != ORB_OK) return rc;
+  for (int b = 0; b < nout; ++b) {
+    if (b < nbuf && (rc = e->stage_in[b].ensure((size_t)e->chunk * fbytes)) != ORB_OK) return rc;
     if (host_out) {
       if ((rc = e->out_kps[b].ensure((size_t)e->chunk * cap * sizeof(OrbKeypoint))) != ORB_OK) return rc;
       if ((rc = e->out_desc[b].ensure((size_t)e->chunk * cap * 32)) != ORB_OK) return rc;
       if (sr && (rc = e->out_ur[b].ensure((size_t)e->chunk / 2 * cap * sizeof(float) + 16)) != ORB_OK) return rc;
       if (sr && (rc = e->out_dp[b].ensure((size_t)e->chunk / 2 * cap * sizeof(float) + 16)) != ORB_OK) return rc;
     }
-    if (sr) {
+    if (sr && b < nbuf) {
       if ((rc = e->ws[b].st_sad.ensure((size_t)e->chunk / 2 * cap * sizeof(int) + 16)) != ORB_OK) return rc;
-      if ((rc = e->ws[b].st_matched.ensure((size_t)e->chunk / 2 * sizeof(int) + 16)) != ORB_OK) return rc;
       if ((rc = e->ws[b].st_rows.ensure((size_t)e->chunk / 2 * (g.lv[0].rows + 1) * sizeof(int) + 16)) != ORB_OK) return rc;
       if ((rc = e->ws[b].st_sorted.ensure((size_t)e->chunk / 2 * cap * sizeof(unsigned short) + 16)) != ORB_OK) return rc;
     }
@@ -577,17 +583,41 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
   int* h_counts = e->h_cnt;
   int* h_levels = e->h_cnt + batch;
   int* h_matched = e->h_cnt + (size_t)batch * (1 + nl);
+  int* d_counts = e->cnt_all.as<int>();
+  int* d_levels = d_counts + batch;
+  int* d_matched = d_counts + (size_t)batch * (1 + nl);
   const cudaMemcpyKind kin = in_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  // ORB_B200_TRACE=1: per-pass timeline of the three pipelines on stderr (development aid; adds timing events only)
+  const bool trace = getenv("ORB_B200_TRACE") != nullptr;
+  std::vector<cudaEvent_t> tev;
+  std::vector<int> tn;
+  std::vector<double> thost;   // host clock when each pass had been issued
+  const auto t_entry = std::chrono::steady_clock::now();
+  auto host_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_entry).count(); };
+  auto tmark = [&](cudaStream_t st) {
+    if (!trace) return;
+    cudaEvent_t ev;
+    cudaEventCreate(&ev);
+    cudaEventRecord(ev, st);
+    tev.push_back(ev);
+  };
   int pass = 0;
   for (int f0 = 0, n = 0; f0 < batch; f0 += n, ++pass) {
-    // ramp-up: the first passes are short so that the first kernels start after a short copy (pipeline fill)
+    // ramp-up: the first passes are short so that the first kernels start after a short copy (pipeline fill); the rest of
+    // the batch is split evenly so that no short pass is left over at the end (its latency would be exposed)
     const int full = e->chunk;
-    const int want = (batch > 2 * full && pass < 2) ? std::max(full >> (2 - pass), 1) : full;
-    n = std::min(want, batch - f0);
-    if (sr && (n & 1)) n = n > 1 ? n - 1 : 2;   // a pair never straddles two passes (batch and chunk parity checked below)
-    const int b = pass & 1;
+    if (batch > 2 * full && pass < 2) {
+      n = std::max(full >> (2 - pass), 1);
+    } else {
+      const int left = batch - f0, passes = (left + full - 1) / full;
+      n = (left + passes - 1) / passes;
+    }
+    if (sr && (n & 1)) n = n < full ? n + 1 : n - 1;   // a pair never straddles two passes (batch is even, chunk >= 2)
+    n = std::min(n, batch - f0);
+    const int b = pass & 1, ob = pass % 3;
     // ---- copy-in stream: stage_in[b] is free once level 0 of pass-2 has read it (the rest of that pass works on the pyramid)
     if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_staged[b], 0));
+    tmark(e->s_in);
     bool contiguous = true;   // frames back to back with the same pitch -> one linear copy for the whole pass
     for (int i = 1; i < n && contiguous; ++i) contiguous = images[f0 + i] == images[f0] + (size_t)i * fbytes;
     if (contiguous) {
@@ -597,43 +627,59 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
         CU(cudaMemcpyAsync(e->stage_in[b].as<uint8_t>() + (size_t)i * fbytes, images[f0 + i], fbytes - (step - width), kin, e->s_in));
     }
     CU(cudaEventRecord(e->ev_in[b], e->s_in));
+    tmark(e->s_in);
     // ---- compute stream of workspace w (= b unless stage profiling serialises everything on the public stream)
     const int w = e->profile ? 0 : b;
     orb_extractor::PassWs& P = e->ws[w];
     CU(cudaStreamWaitEvent(P.st, e->ev_in[b], 0));
-    if (pass >= 2) CU(cudaStreamWaitEvent(P.st, e->ev_out[b], 0));   // out buffers / count arrays of workspace [b] drained
-    if (e->profile && pass >= 1) CU(cudaStreamWaitEvent(P.st, e->ev_out[b ^ 1], 0));   // single workspace: also the previous pass's counts
-    OrbKeypoint* dk = host_out ? e->out_kps[b].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
-    uint8_t* dd = host_out ? e->out_desc[b].as<uint8_t>() : desc + (long long)f0 * cap * 32;
-    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, P.out_cnt.as<int>(), e->ev_staged[b]);
+    if (pass >= 3) CU(cudaStreamWaitEvent(P.st, e->ev_out[ob], 0));   // output staging [ob] drained (pass - 3)
+    tmark(P.st);
+    OrbKeypoint* dk = host_out ? e->out_kps[ob].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
+    uint8_t* dd = host_out ? e->out_desc[ob].as<uint8_t>() : desc + (long long)f0 * cap * 32;
+    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, d_counts + f0, e->ev_staged[b], d_levels + (size_t)f0 * nl);
     float* dur = nullptr;
     float* ddp = nullptr;
     if (sr) {
-      dur = host_out ? e->out_ur[b].as<float>() : sr->uright + (long long)(f0 / 2) * cap;
-      ddp = host_out ? e->out_dp[b].as<float>() : sr->depth + (long long)(f0 / 2) * cap;
-      orb_launch_stereo(P.pyr.as<uint8_t>(), dk, dd, P.out_cnt.as<int>(), cap, sr->bf, sr->b, dur, ddp, P.st_sad.as<int>(),
-                        P.st_matched.as<int>(), P.st_rows.as<int>(), P.st_sorted.as<unsigned short>(), g, n / 2, P.st, &e->launches);
+      dur = host_out ? e->out_ur[ob].as<float>() : sr->uright + (long long)(f0 / 2) * cap;
+      ddp = host_out ? e->out_dp[ob].as<float>() : sr->depth + (long long)(f0 / 2) * cap;
+      orb_launch_stereo(P.pyr.as<uint8_t>(), dk, dd, d_counts + f0, cap, sr->bf, sr->b, dur, ddp, P.st_sad.as<int>(),
+                        d_matched + f0 / 2, P.st_rows.as<int>(), P.st_sorted.as<unsigned short>(), g, n / 2, P.st, &e->launches);
     }
     CU(cudaEventRecord(e->ev_done[b], P.st));
-    // ---- copy-out stream (also the small count copies: a D2H queued on the compute stream would wait for the copy engine
-    //      behind the previous pass's output copy and hold back the next kernels of that stream)
+    tmark(P.st);
+    // ---- copy-out stream; the count arrays of all passes are fetched once, after the last pass
     CU(cudaStreamWaitEvent(e->s_out, e->ev_done[b], 0));
-    CU(cudaMemcpyAsync(h_counts + f0, P.out_cnt.p, n * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
-    CU(cudaMemcpyAsync(h_levels + (size_t)f0 * nl, P.kept_cnt.p, (size_t)n * nl * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
     if (host_out) {
       CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->s_out));
       CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->s_out));
     }
     if (sr) {
-      CU(cudaMemcpyAsync(h_matched + f0 / 2, P.st_matched.p, (size_t)(n / 2) * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
       if (host_out) {
         CU(cudaMemcpyAsync(sr->uright + (long long)(f0 / 2) * cap, dur, (size_t)(n / 2) * cap * sizeof(float), cudaMemcpyDeviceToHost, e->s_out));
         CU(cudaMemcpyAsync(sr->depth + (long long)(f0 / 2) * cap, ddp, (size_t)(n / 2) * cap * sizeof(float), cudaMemcpyDeviceToHost, e->s_out));
       }
     }
-    CU(cudaEventRecord(e->ev_out[b], e->s_out));
+    CU(cudaEventRecord(e->ev_out[ob], e->s_out));
+    tmark(e->s_out);
+    tn.push_back(n);
+    if (trace) thost.push_back(host_ms());
   }
+  // s_out has waited for the last pass of either compute stream (ev_done of the last two passes), so all counts are final
+  CU(cudaMemcpyAsync(h_counts, d_counts, (size_t)batch * (2 + nl) * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
   CU(cudaStreamSynchronize(e->s_out));
+  if (trace) {
+    fprintf(stderr, "host: all passes issued at %.3f ms, outputs on the host at %.3f ms after entry; pass issue times:", thost.back(), host_ms());
+    for (double t : thost) fprintf(stderr, " %.3f", t);
+    fprintf(stderr, "\n");
+    for (int w = 0; w < 2; ++w) cudaStreamSynchronize(e->ws[w].st);
+    fprintf(stderr, "pass frames | h2d start..end | compute start..end | d2h end   (ms since the first copy was issued)\n");
+    for (size_t p = 0; p * 5 + 4 < tev.size(); ++p) {
+      float t[5];
+      for (int k = 0; k < 5; ++k) cudaEventElapsedTime(&t[k], tev[0], tev[p * 5 + k]);
+      fprintf(stderr, "%4zu %4d | %7.3f %7.3f | %7.3f %7.3f | %7.3f\n", p, tn[p], t[0], t[1], t[2], t[3], t[4]);
+    }
+    for (cudaEvent_t ev : tev) cudaEventDestroy(ev);
+  }
   if ((rc = check_err_flag(e)) != ORB_OK) return rc;   // synchronises the compute stream (counts are on the host after it)
   memcpy(counts, h_counts, (size_t)batch * sizeof(int));
   if (level_counts) memcpy(level_counts, h_levels, (size_t)batch * nl * sizeof(int));

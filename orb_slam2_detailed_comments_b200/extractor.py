@@ -91,12 +91,18 @@ class ORBextractor:
         n = int(counts[0])
         return kps[0, :n].copy(), desc[0, :n].copy()
 
+    @staticmethod
+    def _frame_pointers(images: np.ndarray) -> np.ndarray:
+        """uint64 array of the B frame addresses (the `images` argument of the C ABI), built without a Python loop."""
+        base = images.__array_interface__["data"][0]
+        return np.uint64(base) + np.arange(images.shape[0], dtype=np.uint64) * np.uint64(images.strides[0])
+
     def extract_batch(self, images: np.ndarray, out=None):
         """images [B,H,W] u8 host array (rows may be strided). Returns (kps[B,cap], desc[B,cap,32], counts[B],
         level_counts[B,nlevels]) host arrays. `out` may pass preallocated (kps, desc) e.g. pinned buffers."""
         if images.dtype != np.uint8 or images.ndim != 3:
             raise TypeError("images must be uint8 [B,H,W] (CV_8UC1, src/ORBextractor.cc:1972)")
-        if images.strides[2] != 1:
+        if images.strides[2] != 1 or images.strides[0] < 0 or images.strides[1] < images.shape[2]:
             images = np.ascontiguousarray(images)
         B, H, W = images.shape
         step = images.strides[1]
@@ -108,8 +114,8 @@ class ORBextractor:
             kps, desc = out
         counts = np.zeros(B, np.int32)
         lcounts = np.zeros((B, self.nlevels), np.int32)
-        ptrs = (C.c_void_p * B)(*[images.ctypes.data + i * images.strides[0] for i in range(B)])
-        check(self._L.orb_extract_batch(self._h, ptrs, MEM_HOST, step, W, H, B, kps.ctypes.data_as(C.c_void_p),
+        ptrs = self._frame_pointers(images)
+        check(self._L.orb_extract_batch(self._h, ptrs.ctypes.data_as(C.c_void_p), MEM_HOST, step, W, H, B, kps.ctypes.data_as(C.c_void_p),
                                         desc.ctypes.data_as(C.c_void_p), MEM_HOST, cap, counts.ctypes.data_as(C.c_void_p),
                                         lcounts.ctypes.data_as(C.c_void_p)))
         self._last_n = B
@@ -141,9 +147,9 @@ class ORBextractor:
             kps, desc, ur, dp = out
         counts = np.zeros(B, np.int32)
         matched = np.zeros(P, np.int32)
-        ptrs = (C.c_void_p * B)(*[images.ctypes.data + i * images.strides[0] for i in range(B)])
+        ptrs = self._frame_pointers(images)
         vp = lambda a: a.ctypes.data_as(C.c_void_p)
-        check(self._L.orb_extract_stereo_batch(self._h, ptrs, MEM_HOST, W, W, H, P, vp(kps), vp(desc), MEM_HOST, cap, vp(counts), None,
+        check(self._L.orb_extract_stereo_batch(self._h, vp(ptrs), MEM_HOST, W, W, H, P, vp(kps), vp(desc), MEM_HOST, cap, vp(counts), None,
                                                bf, b, vp(ur), vp(dp), vp(matched)))
         self._last_n = B
         return kps, desc, counts, ur, dp, matched
