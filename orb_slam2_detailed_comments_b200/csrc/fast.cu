@@ -20,6 +20,7 @@
 //      min / ini survivor bit planes;
 //   5. per cell (one warp each, lane = row): 64-bit row masks from the bit planes, popc + warp scan give every
 //      survivor its row-major rank; ini/min selection by the cell's ini count.
+#include <atomic>
 #include "orb_common.cuh"
 
 #define FAST_THREADS 256
@@ -348,15 +349,17 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
   const int list_cap = ((max_h + FAST_WARPS - 1) / FAST_WARPS) * 256;   // a warp's rows x <= 256 detection columns
   const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)max_h * FAST_BP * 4 +
                       (size_t)FAST_WARPS * list_cap * 2 + FAST_WP;
-  static size_t configured[64][2] = {};   // per device: the opt-in shared memory size is a per-context function attribute
+  // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
+  // (227 KB), so that concurrent callers with different level sizes never lower each other's limit.
+  static std::atomic<bool> configured[64][2];
   const int small = g.ini_th <= 126;      // both thresholds (min <= ini) in the carry-free byte-compare range
   int dev = 0;
   cudaGetDevice(&dev);
   dev &= 63;
-  if (smem > 48 * 1024 && smem > configured[dev][small]) {
-    if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured[dev][small] = smem;
+  if (!configured[dev][small].load(std::memory_order_acquire)) {
+    if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    configured[dev][small].store(true, std::memory_order_release);
   }
   const dim3 grid(g.fast_tiles_total, batch);
   if (small) orb_fast_band_kernel<true><<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, list_cap, g);

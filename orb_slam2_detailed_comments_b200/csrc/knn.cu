@@ -7,6 +7,7 @@
 // queries with three integer min/max per pair, database chunks are scanned by different CTAs, and a merge takes
 // the two smallest of all partial keys. INT pipe (popc) bound; the database streams through shared memory as
 // uint4 pairs read by broadcast, queries live in registers.
+#include <atomic>
 #include <cuda_pipeline.h>
 
 #include "orb_common.cuh"
@@ -145,8 +146,8 @@ __global__ void orb_popc_peak_kernel(unsigned* out, int iters, unsigned seed) {
   if (s == 0xdeadbeefu) out[0] = s;
 }
 
-static long long g_knn_launches = 0;
-long long orb_knn_launches() { return g_knn_launches; }
+static std::atomic<long long> g_knn_launches{0};   // the kNN entry points are callable from any thread
+long long orb_knn_launches() { return g_knn_launches.load(std::memory_order_relaxed); }
 
 int orb_knn_num_chunks(int Q, long long D, int num_sms) {
   const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
