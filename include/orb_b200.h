@@ -16,6 +16,11 @@
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
+ *   orb_search_by_projection  <- the guided matchers' core: Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
+ *                                (src/Frame.cc:432-460, 729-745, 633-717), the candidate scan with sequential claims of
+ *                                ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) (src/ORBmatcher.cc:69-184) and
+ *                                SearchByProjection(Frame&, Frame&, th, bMono) (src/ORBmatcher.cc:1702-1866), and
+ *                                ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2026-2068)
  *
  * Plain C: pointers and sizes only, no C++/torch types, no exceptions cross the boundary. All
  * buffers are caller-owned. Functions are thread-safe per handle (one handle = one CUDA stream +
@@ -154,6 +159,52 @@ int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n,
 /* Same with HOST buffers (copies inside the call, default stream, synchronous). */
 int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out);
 int64_t orb_matcher_launch_count(void);
+
+/* ---- guided matching ----------------------------------------------------------------------
+ * One projected map point = one query. The host computes the projection (pose, camera model, PredictScale stay in the
+ * reference's Tracking / MapPoint code); everything from GetFeaturesInArea on runs on the device, for `frames`
+ * independent (query set, target frame) pairs per call. */
+enum orb_query_flags {
+  ORB_QUERY_SKIP = 1,   /* not searched: !mbTrackInView, isBad(), outlier, invzc < 0, projection outside the image bounds */
+  ORB_QUERY_CLAIMS = 2  /* pMP->Observations() > 0: once matched, the keypoint is skipped by all later queries (src/ORBmatcher.cc:127-130, 1798-1801) */
+};
+
+typedef struct orb_proj_query {   /* 32 bytes */
+  float u, v;           /* x, y of GetFeaturesInArea: mTrackProjX/Y (src/ORBmatcher.cc:101) or the projection (:1755-1756) */
+  float radius;         /* r of GetFeaturesInArea = r*mvScaleFactors[level] (:102) / th*mvScaleFactors[octave] (:1769); also the stereo tolerance (:134-141, :1804-1811) */
+  float ur;             /* predicted right-image column: mTrackProjXR (:137) / u - mbf*invzc (:1806); read only where uright[i] > 0 */
+  float angle;          /* angle of the query's own keypoint (rotation histogram, :1828-1839); unused without check_orientation */
+  int16_t min_level;    /* GetFeaturesInArea(minLevel, maxLevel) (src/Frame.cc:673-703): levels are checked iff */
+  int16_t max_level;    /*   min_level > 0 || max_level >= 0; max_level < 0 = no upper bound */
+  int32_t flags;        /* orb_query_flags */
+  int32_t reserved;
+} orb_proj_query;
+
+typedef struct orb_search_params {
+  float min_x, min_y, max_x, max_y; /* Frame::mnMinX, mnMinY, mnMaxX, mnMaxY (src/Frame.cc:849-868, 186-202): grid of 64 x 48 cells over this box */
+  int32_t th_dist;           /* accept iff bestDist <= th_dist: TH_HIGH (:170, :1824), or TH_LOW / ORBdist of the other variants */
+  float nn_ratio;            /* > 0: reject when bestLevel == bestLevel2 && bestDist > nn_ratio * bestDist2 (:174); <= 0: best only (:1813-1821) */
+  int32_t check_orientation; /* != 0: rotation histogram of HISTO_LENGTH = 30 bins, keep the three maxima (:1828-1863, 2026-2068) */
+  int32_t reserved;
+} orb_search_params;
+
+/* For every frame f < frames, with N = n_kps[f] target keypoints and M = n_queries[f] queries processed in index order
+ * (the reference's loop order; the claims make the result order-dependent):
+ *   candidates of a query = GetFeaturesInArea(u, v, radius, min_level, max_level) in the reference's scan order (cell
+ *   column ix, cell row iy, insertion order), minus keypoints with claimed[i] != 0 or claimed by an earlier query, minus
+ *   keypoints with uright[i] > 0 && |ur - uright[i]| > radius; best / second best by DescriptorDistance with strict <;
+ *   accept rule per orb_search_params; on accept assigned[f][best] = query index (later accepts overwrite, as
+ *   F.mvpMapPoints[bestIdx] = pMP does) and nmatches[f]++; with check_orientation the accepts outside the three
+ *   dominant rotation bins are undone (assigned = -1, nmatches--).
+ * kps_un [frames][cap] (pt, octave, angle are read), desc [frames][cap][32], uright [frames][cap] or NULL (monocular: all -1),
+ * claimed [frames][cap] bytes or NULL, queries [frames][qcap], qdesc [frames][qcap][32], n_kps / n_queries / nmatches [frames],
+ * assigned [frames][cap] (-1 = untouched), query_match [frames][qcap] or NULL (keypoint accepted for the query and still
+ * standing after the orientation filter, else -1). `mem` = ORB_MEM_HOST or ORB_MEM_DEVICE for ALL array arguments
+ * (prm is always host). n_kps[f] <= cap < 2^18; descriptor arrays 16-byte aligned in device memory. stream as in orb_hamming_knn; host memory makes the call synchronous. */
+int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
+                             const int32_t* n_kps, int cap, const orb_proj_query* queries, const uint8_t* qdesc,
+                             const int32_t* n_queries, int qcap, int frames, const orb_search_params* prm, int32_t* assigned,
+                             int32_t* query_match, int32_t* nmatches, void* stream);
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
 double orb_measure_popc_peak(int device);

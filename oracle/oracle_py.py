@@ -207,3 +207,45 @@ def stereo_match(left: "OracleExtractor", right: "OracleExtractor", kl, dl, kr, 
     dp = np.empty(len(kl), np.float32)
     kept = lib().orb_oracle_stereo_match(left.h, right.h, _p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), bf, b, _p(ur), _p(dp))
     return ur, dp, kept
+
+
+QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("angle", "<f4"),
+                        ("min_level", "<i2"), ("max_level", "<i2"), ("flags", "<i4"), ("reserved", "<i4")])
+
+
+class _SearchParams(C.Structure):
+    _fields_ = [("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float), ("max_y", C.c_float),
+                ("th_dist", C.c_int32), ("nn_ratio", C.c_float), ("check_orientation", C.c_int32), ("reserved", C.c_int32)]
+
+
+def search_by_projection(kps_un, desc, queries, qdesc, bounds, th_dist=100, nn_ratio=0.0, check_orientation=True, uright=None,
+                         claimed=None):
+    """One (query set, target frame) pair through the restated guided search (src/ORBmatcher.cc:69-184, 1702-1866;
+    src/Frame.cc:432-460, 633-745). Returns (assigned [n], query_match [m], nmatches)."""
+    L = lib()
+    L.orb_oracle_search_by_projection.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(_SearchParams),
+                                                                  C.c_void_p, C.c_void_p]
+    kps_un, desc = np.ascontiguousarray(kps_un), np.ascontiguousarray(desc)
+    queries, qdesc = np.ascontiguousarray(queries), np.ascontiguousarray(qdesc)
+    assert queries.dtype == QUERY_DTYPE and kps_un.dtype.itemsize == 28
+    n, m = len(kps_un), len(queries)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    cl = None if claimed is None else np.ascontiguousarray(claimed, np.uint8)
+    prm = _SearchParams(*[float(b) for b in bounds], int(th_dist), float(nn_ratio), int(check_orientation), 0)
+    assigned = np.full(max(n, 1), -1, np.int32)
+    qmatch = np.full(max(m, 1), -1, np.int32)
+    nm = L.orb_oracle_search_by_projection(_p(kps_un), _p(desc), None if ur is None else _p(ur), None if cl is None else _p(cl), n,
+                                           _p(queries), _p(qdesc), m, C.byref(prm), _p(assigned), _p(qmatch))
+    return assigned[:n], qmatch[:m], nm
+
+
+def features_in_area(kps_un, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (src/Frame.cc:633-717) with its scan order."""
+    L = lib()
+    L.orb_oracle_features_in_area.argtypes = [C.c_void_p, C.c_int, C.POINTER(_SearchParams), C.c_float, C.c_float, C.c_float, C.c_int,
+                                              C.c_int, C.c_void_p]
+    kps_un = np.ascontiguousarray(kps_un)
+    prm = _SearchParams(*[float(b) for b in bounds], 0, 0.0, 0, 0)
+    out = np.empty(max(len(kps_un), 1), np.int32)
+    n = L.orb_oracle_features_in_area(_p(kps_un), len(kps_un), C.byref(prm), x, y, r, min_level, max_level, _p(out))
+    return out[:n].copy()

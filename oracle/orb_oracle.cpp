@@ -609,6 +609,131 @@ int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_e
   return kept;
 }
 
+// ---- guided matching: Frame grid + SearchByProjection candidate loops + ComputeThreeMaxima ------------------------------------
+namespace {
+constexpr int GRID_COLS = 64, GRID_ROWS = 48, HISTO_LENGTH = 30;   // include/Frame.h FRAME_GRID_COLS / ROWS, include/ORBmatcher.h:54
+
+struct FrameGrid {   // mGrid, mfGridElementWidthInv / HeightInv (src/Frame.cc:200-202, 432-460)
+  float min_x, min_y, inv_w, inv_h;
+  std::vector<int> cell[GRID_COLS][GRID_ROWS];
+  FrameGrid(const orb_oracle_kp* k, int n, const orb_oracle_search_params& p) : min_x(p.min_x), min_y(p.min_y) {
+    inv_w = static_cast<float>(GRID_COLS) / static_cast<float>(p.max_x - p.min_x);
+    inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(p.max_y - p.min_y);
+    for (int i = 0; i < n; ++i) {   // AssignFeaturesToGrid + PosInGrid (src/Frame.cc:447-459, 734-744)
+      const int px = (int)std::round((k[i].x - min_x) * inv_w);
+      const int py = (int)std::round((k[i].y - min_y) * inv_h);
+      if (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) continue;
+      cell[px][py].push_back(i);
+    }
+  }
+  // GetFeaturesInArea (src/Frame.cc:633-717)
+  void in_area(const orb_oracle_kp* k, float x, float y, float r, int min_level, int max_level, std::vector<int>& out) const {
+    out.clear();
+    const int cx0 = std::max(0, (int)std::floor((x - min_x - r) * inv_w));
+    if (cx0 >= GRID_COLS) return;
+    const int cx1 = std::min(GRID_COLS - 1, (int)std::ceil((x - min_x + r) * inv_w));
+    if (cx1 < 0) return;
+    const int cy0 = std::max(0, (int)std::floor((y - min_y - r) * inv_h));
+    if (cy0 >= GRID_ROWS) return;
+    const int cy1 = std::min(GRID_ROWS - 1, (int)std::ceil((y - min_y + r) * inv_h));
+    if (cy1 < 0) return;
+    const bool check_levels = (min_level > 0) || (max_level >= 0);
+    for (int ix = cx0; ix <= cx1; ++ix)
+      for (int iy = cy0; iy <= cy1; ++iy)
+        for (int i : cell[ix][iy]) {
+          if (check_levels) {
+            if (k[i].octave < min_level) continue;
+            if (max_level >= 0 && k[i].octave > max_level) continue;
+          }
+          const float dx = k[i].x - x, dy = k[i].y - y;
+          if (std::fabs(dx) < r && std::fabs(dy) < r) out.push_back(i);
+        }
+  }
+};
+}  // namespace
+
+int orb_oracle_features_in_area(const orb_oracle_kp* kps, int n, const orb_oracle_search_params* prm, float x, float y, float r,
+                                int min_level, int max_level, int32_t* out) {
+  FrameGrid grid(kps, n, *prm);
+  std::vector<int> v;
+  grid.in_area(kps, x, y, r, min_level, max_level, v);
+  std::copy(v.begin(), v.end(), out);
+  return (int)v.size();
+}
+
+int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* desc, const float* uright, const uint8_t* claimed_in,
+                                    int n, const orb_oracle_query* q, const uint8_t* qdesc, int m,
+                                    const orb_oracle_search_params* prm, int32_t* assigned, int32_t* query_match) {
+  FrameGrid grid(kps, n, *prm);
+  std::vector<uint8_t> claimed(n, 0);   // "F.mvpMapPoints[idx] && F.mvpMapPoints[idx]->Observations() > 0" (src/ORBmatcher.cc:127-130)
+  if (claimed_in) std::copy(claimed_in, claimed_in + n, claimed.begin());
+  std::fill(assigned, assigned + n, -1);
+  if (query_match) std::fill(query_match, query_match + m, -1);
+  std::vector<std::pair<int, int>> rot_hist[HISTO_LENGTH];   // (query, keypoint) per accepted match (:1839)
+  const float factor = HISTO_LENGTH / 360.0f;                // this fork's corrected factor (:1713)
+  int nmatches = 0;
+  std::vector<int> cand;
+  for (int iq = 0; iq < m; ++iq) {
+    const orb_oracle_query& Q = q[iq];
+    if (Q.flags & 1) continue;
+    grid.in_area(kps, Q.u, Q.v, Q.radius, Q.min_level, Q.max_level, cand);
+    if (cand.empty()) continue;
+    int best = 256, best2 = 256, best_level = -1, best_level2 = -1, best_idx = -1;   // :112-116, :1791-1792
+    for (int idx : cand) {
+      if (claimed[idx]) continue;
+      if (uright && uright[idx] > 0) {   // :134-141, :1804-1811
+        const float er = std::fabs(Q.ur - uright[idx]);
+        if (er > Q.radius) continue;
+      }
+      const int dist = orb_oracle_descriptor_distance(qdesc + (size_t)iq * 32, desc + (size_t)idx * 32);
+      if (dist < best) {
+        best2 = best; best = dist;
+        best_level2 = best_level; best_level = kps[idx].octave;
+        best_idx = idx;
+      } else if (dist < best2) {
+        best_level2 = kps[idx].octave;
+        best2 = dist;
+      }
+    }
+    if (best <= prm->th_dist) {   // :170, :1824 (best_idx >= 0 is implied for th_dist < 256)
+      if (best_idx < 0) continue;
+      if (prm->nn_ratio > 0.f && best_level == best_level2 && best > prm->nn_ratio * best2) continue;   // :174
+      assigned[best_idx] = iq;    // F.mvpMapPoints[bestIdx] = pMP (:177, :1826)
+      if (Q.flags & 2) claimed[best_idx] = 1;
+      if (query_match) query_match[iq] = best_idx;
+      ++nmatches;
+      if (prm->check_orientation) {   // :1828-1839
+        float rot = Q.angle - kps[best_idx].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)std::round(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        if (bin >= 0 && bin < HISTO_LENGTH) rot_hist[bin].push_back({iq, best_idx});   // the reference asserts the range
+      }
+    }
+  }
+  if (prm->check_orientation) {
+    // ComputeThreeMaxima (:2026-2068)
+    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int s = (int)rot_hist[i].size();
+      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+      else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    for (int i = 0; i < HISTO_LENGTH; ++i) {   // :1849-1860
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (const auto& e : rot_hist[i]) {
+        assigned[e.second] = -1;
+        if (query_match) query_match[e.first] = -1;
+        --nmatches;
+      }
+    }
+  }
+  return nmatches;
+}
+
 int64_t orb_oracle_extract_many(int nf, float sf, int nl, int ini, int mn, int flags, const uint8_t* frames, int width,
                                 int height, int n, int nthreads) {
   nthreads = std::max(1, std::min(nthreads, n));

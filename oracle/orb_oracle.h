@@ -92,6 +92,28 @@ int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_e
                             const uint8_t* dl, int nL, const orb_oracle_kp* kr, const uint8_t* dr, int nR, float bf, float b,
                             float* uright, float* depth);
 
+/* Guided matching core, one (query set, target frame) pair: Frame::AssignFeaturesToGrid / PosInGrid /
+ * GetFeaturesInArea (src/Frame.cc:432-460, 729-745, 633-717), the candidate loops of ORBmatcher::SearchByProjection
+ * (src/ORBmatcher.cc:69-184 and 1702-1866) and ComputeThreeMaxima (:2026-2068). Layouts as include/orb_b200.h
+ * (orb_proj_query = 32 bytes, orb_search_params = 32 bytes). Returns nmatches. */
+typedef struct orb_oracle_query {
+  float u, v, radius, ur, angle;
+  int16_t min_level, max_level;
+  int32_t flags, reserved;
+} orb_oracle_query;
+typedef struct orb_oracle_search_params {
+  float min_x, min_y, max_x, max_y;
+  int32_t th_dist;
+  float nn_ratio;
+  int32_t check_orientation, reserved;
+} orb_oracle_search_params;
+int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
+                                    int n_kps, const orb_oracle_query* queries, const uint8_t* qdesc, int n_queries,
+                                    const orb_oracle_search_params* prm, int32_t* assigned, int32_t* query_match);
+/* Frame::GetFeaturesInArea alone (scan order included): returns the number of indices written to out (cap >= n_kps). */
+int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const orb_oracle_search_params* prm, float x, float y, float r,
+                                int min_level, int max_level, int32_t* out);
+
 /* Multi-threaded extraction over frames, one extractor per thread (bench cpu baseline).
  * Returns total keypoints. frames: n contiguous w*h images. */
 int64_t orb_oracle_extract_many(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int flags,

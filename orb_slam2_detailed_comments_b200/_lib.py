@@ -18,7 +18,11 @@ _LIB = None
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
                      ("octave", "<i4"), ("class_id", "<i4")])
 KNN_DTYPE = np.dtype([("d1", "<i4"), ("d2", "<i4"), ("i1", "<i8"), ("i2", "<i8")])
-assert KP_DTYPE.itemsize == 28 and KNN_DTYPE.itemsize == 24
+# orb_proj_query / orb_search_params (guided matching)
+QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("angle", "<f4"),
+                        ("min_level", "<i2"), ("max_level", "<i2"), ("flags", "<i4"), ("reserved", "<i4")])
+QUERY_SKIP, QUERY_CLAIMS = 1, 2
+assert KP_DTYPE.itemsize == 28 and KNN_DTYPE.itemsize == 24 and QUERY_DTYPE.itemsize == 32
 
 ORB_OK, ORB_E_BADARG, ORB_E_CAPACITY, ORB_E_CUDA, ORB_E_SHAPE = 0, -1, -2, -3, -4
 MEM_HOST, MEM_DEVICE = 0, 1
@@ -33,12 +37,18 @@ SYMBOLS = [
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
+    "orb_search_by_projection",
 ]
 
 
 class OrbParams(C.Structure):
     _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
                 ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("flags", C.c_int32)]
+
+
+class OrbSearchParams(C.Structure):
+    _fields_ = [("min_x", C.c_float), ("min_y", C.c_float), ("max_x", C.c_float), ("max_y", C.c_float),
+                ("th_dist", C.c_int32), ("nn_ratio", C.c_float), ("check_orientation", C.c_int32), ("reserved", C.c_int32)]
 
 
 class OrbError(RuntimeError):
@@ -90,6 +100,7 @@ def lib():
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
     L.orb_matcher_launch_count.restype = i64
+    L.orb_search_by_projection.argtypes = [i32, vp, vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]
     L.orb_measure_popc_peak.argtypes = [i32]
     L.orb_measure_popc_peak.restype = C.c_double
     _LIB = L

@@ -350,15 +350,21 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
   const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)max_h * FAST_BP * 4 +
                       (size_t)FAST_WARPS * list_cap * 2 + FAST_WP;
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
-  // (227 KB), so that concurrent callers with different level sizes never lower each other's limit.
+  // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
   static std::atomic<bool> configured[64][2];
   const int small = g.ini_th <= 126;      // both thresholds (min <= ini) in the carry-free byte-compare range
   int dev = 0;
   cudaGetDevice(&dev);
   dev &= 63;
   if (!configured[dev][small].load(std::memory_order_acquire)) {
-    if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    int optin = 0;
+    cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaFuncAttributes fa;
+    if (small) cudaFuncGetAttributes(&fa, orb_fast_band_kernel<true>);
+    else cudaFuncGetAttributes(&fa, orb_fast_band_kernel<false>);
+    const int dyn_max = optin - (int)fa.sharedSizeBytes;   // the limit covers static + dynamic shared memory
+    if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max);
+    else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max);
     configured[dev][small].store(true, std::memory_order_release);
   }
   const dim3 grid(g.fast_tiles_total, batch);

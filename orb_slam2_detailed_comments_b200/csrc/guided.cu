@@ -1,0 +1,330 @@
+// Guided matching core: Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
+// (src/Frame.cc:432-460, 729-745, 633-717), the candidate loops of ORBmatcher::SearchByProjection
+// (src/ORBmatcher.cc:69-184, 1702-1866) and ComputeThreeMaxima (src/ORBmatcher.cc:2026-2068).
+//
+// The reference walks the queries (projected map points) in order and a matched keypoint blocks later queries
+// ("mvpMapPoints[idx]->Observations() > 0"), so the result is order-dependent. Three kernels keep that order exact while
+// doing the Hamming work in parallel:
+//   1. orb_guided_grid_kernel   (CTA per frame): counting sort of the keypoints into the 64 x 48 grid, cells numbered
+//      column-major (ix * 48 + iy) and keypoints in index order inside a cell. GetFeaturesInArea's scan order
+//      (ix, then iy, then insertion order) is then simply ascending position in the sorted array, and the cells
+//      iy0..iy1 of one column are ONE contiguous range.
+//   2. orb_guided_top2_kernel   (warp per query): best / second best over the query's window, ignoring claims made by
+//      other queries. Key = dist << 32 | sorted position, so "strict <, first in scan order wins" is a plain min.
+//   3. orb_guided_resolve_kernel (warp per frame): walks the queries in order. A precomputed result is final unless one
+//      of its two keypoints has been claimed since — only then the warp rescans that query with the claims applied.
+//      Accept rule, assignment, claim bit, rotation histogram and the three-maxima filter follow.
+#include "orb_common.cuh"
+
+#define GRID_COLS 64
+#define GRID_ROWS 48
+#define GRID_CELLS (GRID_COLS * GRID_ROWS)
+#define HISTO_LENGTH 30
+#define GUIDED_WARPS 8
+
+struct GuidedQuery {   // == orb_proj_query
+  float u, v, radius, ur, angle;
+  short min_level, max_level;
+  int flags, reserved;
+};
+static_assert(sizeof(GuidedQuery) == 32, "orb_proj_query layout");
+
+struct GuidedFrame {
+  const uint4* items;        // sorted keypoints: x bits, y bits, octave, index
+  const int* cell_start;     // [GRID_CELLS + 1]
+  const uint4* desc;         // [n][2]
+  const float* uright;       // or nullptr
+  const uint8_t* claimed;    // or nullptr (static claims)
+  const unsigned* dyn;       // shared-memory claim bits of the resolve kernel, or nullptr
+  float min_x, min_y, inv_w, inv_h;
+};
+
+__device__ __forceinline__ void top2_insert(unsigned long long& k1, unsigned long long& k2, unsigned long long k) {
+  if (k < k1) { k2 = k1; k1 = k; }
+  else if (k < k2) k2 = k;
+}
+
+// GetFeaturesInArea + the candidate filters + DescriptorDistance for one query, by one warp. Returns the two smallest
+// keys (dist << 32 | sorted position), ~0 = none, identical in all lanes.
+__device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQuery& q, const uint4 qd0, const uint4 qd1, int lane,
+                                            unsigned long long& k1, unsigned long long& k2) {
+  k1 = k2 = ~0ull;
+  const float x = q.u, y = q.v, r = q.radius;
+  // src/Frame.cc:649-668
+  const int cx0 = max(0, (int)floorf((x - F.min_x - r) * F.inv_w));
+  const int cx1 = min(GRID_COLS - 1, (int)ceilf((x - F.min_x + r) * F.inv_w));
+  const int cy0 = max(0, (int)floorf((y - F.min_y - r) * F.inv_h));
+  const int cy1 = min(GRID_ROWS - 1, (int)ceilf((y - F.min_y + r) * F.inv_h));
+  if (cx0 >= GRID_COLS || cx1 < 0 || cy0 >= GRID_ROWS || cy1 < 0) return;
+  const int min_level = q.min_level, max_level = q.max_level;
+  const bool check_levels = (min_level > 0) || (max_level >= 0);
+  for (int ix = cx0; ix <= cx1; ++ix) {
+    const int e0 = F.cell_start[ix * GRID_ROWS + cy0], e1 = F.cell_start[ix * GRID_ROWS + cy1 + 1];
+    for (int e = e0 + lane; e < e1; e += 32) {
+      const uint4 it = F.items[e];
+      const int oct = (int)it.z, idx = (int)it.w;
+      if (check_levels && (oct < min_level || (max_level >= 0 && oct > max_level))) continue;
+      const float dx = __uint_as_float(it.x) - x, dy = __uint_as_float(it.y) - y;
+      if (!(fabsf(dx) < r && fabsf(dy) < r)) continue;
+      if (F.claimed && F.claimed[idx]) continue;
+      if (F.dyn && ((F.dyn[idx >> 5] >> (idx & 31)) & 1u)) continue;
+      if (F.uright) {
+        const float ur = F.uright[idx];
+        if (ur > 0.f && fabsf(q.ur - ur) > r) continue;
+      }
+      const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
+      const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
+                       __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
+      top2_insert(k1, k2, ((unsigned long long)dist << 32) | (unsigned)e);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+    const unsigned long long lo = min(k1, o1), hi = max(k1, o1);
+    k2 = min(hi, min(k2, o2));
+    k1 = lo;
+  }
+}
+
+// packed result: x = idx1, y = idx2, z = d1 | d2 << 16, w = (l1 & 0xff) | (l2 & 0xff) << 8 | flags << 16
+__device__ __forceinline__ int4 guided_pack(const GuidedFrame& F, unsigned long long k1, unsigned long long k2, int flags) {
+  int4 r = make_int4(-1, -1, 256 | (256 << 16), 0xffff | (flags << 16));
+  if (k1 != ~0ull) {
+    const uint4 it = F.items[(unsigned)k1];
+    int idx2 = -1, d2 = 256, l2 = -1;   // bestDist2 = 256, bestLevel2 = -1 (src/ORBmatcher.cc:114-115)
+    if (k2 != ~0ull) {
+      const uint4 it2 = F.items[(unsigned)k2];
+      idx2 = (int)it2.w; d2 = (int)(k2 >> 32); l2 = (int)it2.z;
+    }
+    r = make_int4((int)it.w, idx2, (int)(k1 >> 32) | (d2 << 16), ((int)it.z & 0xff) | ((l2 & 0xff) << 8) | (flags << 16));
+  }
+  return r;
+}
+
+// ---- 1. grid ----------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) orb_guided_grid_kernel(const OrbKeypoint* __restrict__ kps, const int* __restrict__ n_kps, int cap,
+                                                              float min_x, float min_y, float inv_w, float inv_h,
+                                                              uint4* __restrict__ items, int* __restrict__ cell_start) {
+  __shared__ int s_cnt[GRID_CELLS];
+  __shared__ int s_warp[8];
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const int n = min(n_kps[f], cap);
+  kps += (size_t)f * cap;
+  items += (size_t)f * cap;
+  cell_start += (size_t)f * (GRID_CELLS + 1);
+  for (int c = tid; c < GRID_CELLS; c += 256) s_cnt[c] = 0;
+  __syncthreads();
+  auto cell_of = [&](const OrbKeypoint& k) {   // PosInGrid (src/Frame.cc:734-744)
+    const int px = (int)roundf((k.x - min_x) * inv_w), py = (int)roundf((k.y - min_y) * inv_h);
+    return (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) ? -1 : px * GRID_ROWS + py;
+  };
+  for (int i = tid; i < n; i += 256) {
+    const int c = cell_of(kps[i]);
+    if (c >= 0) atomicAdd(&s_cnt[c], 1);
+  }
+  __syncthreads();
+  // exclusive scan of the 3072 counts: 12 consecutive cells per thread
+  int local[12], sum = 0;
+#pragma unroll
+  for (int j = 0; j < 12; ++j) { local[j] = s_cnt[tid * 12 + j]; sum += local[j]; }
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((tid & 31) >= o) incl += v;
+  }
+  if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+  __syncthreads();
+  int base = incl - sum;
+  for (int w = 0; w < (tid >> 5); ++w) base += s_warp[w];
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 12; ++j) {
+    cell_start[tid * 12 + j] = base;
+    s_cnt[tid * 12 + j] = base;   // becomes the fill cursor
+    base += local[j];
+  }
+  if (tid == 255) cell_start[GRID_CELLS] = base;
+  __syncthreads();
+  for (int i = tid; i < n; i += 256) {
+    const OrbKeypoint k = kps[i];
+    const int c = cell_of(k);
+    if (c >= 0) {
+      const int pos = atomicAdd(&s_cnt[c], 1);
+      items[pos] = make_uint4(__float_as_uint(k.x), __float_as_uint(k.y), (unsigned)k.octave, (unsigned)i);
+    }
+  }
+  __syncthreads();
+  // insertion order inside a cell = ascending keypoint index: sort each (short) cell segment
+  for (int c = tid; c < GRID_CELLS; c += 256) {
+    const int e0 = cell_start[c], e1 = s_cnt[c];
+    for (int a = e0 + 1; a < e1; ++a) {
+      const uint4 v = items[a];
+      int b = a - 1;
+      while (b >= e0 && items[b].w > v.w) { items[b + 1] = items[b]; --b; }
+      items[b + 1] = v;
+    }
+  }
+}
+
+// ---- 2. top-2 per query, no dynamic claims --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(GUIDED_WARPS * 32)
+orb_guided_top2_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const uint8_t* __restrict__ desc,
+                       const float* __restrict__ uright, const uint8_t* __restrict__ claimed, int cap,
+                       const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc, const int* __restrict__ n_queries,
+                       int qcap, float min_x, float min_y, float inv_w, float inv_h, int4* __restrict__ result) {
+  const int f = blockIdx.y, lane = threadIdx.x & 31;
+  const int iq = blockIdx.x * GUIDED_WARPS + (threadIdx.x >> 5);
+  if (iq >= min(n_queries[f], qcap)) return;
+  GuidedFrame F;
+  F.items = items + (size_t)f * cap;
+  F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
+  F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
+  F.uright = uright ? uright + (size_t)f * cap : nullptr;
+  F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
+  F.dyn = nullptr;
+  F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  const GuidedQuery q = queries[(size_t)f * qcap + iq];
+  int4 r = make_int4(-1, -1, 256 | (256 << 16), 0xffff | (q.flags << 16));
+  if (!(q.flags & 1)) {
+    const uint4* qd = reinterpret_cast<const uint4*>(qdesc + ((size_t)f * qcap + iq) * 32);
+    unsigned long long k1, k2;
+    guided_scan(F, q, qd[0], qd[1], lane, k1, k2);
+    r = guided_pack(F, k1, k2, q.flags);
+  }
+  if (lane == 0) result[(size_t)f * qcap + iq] = r;
+}
+
+// ---- 3. sequential claims, accept rule, rotation filter --------------------------------------------------------------------
+__global__ void __launch_bounds__(32)
+orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const OrbKeypoint* __restrict__ kps,
+                          const uint8_t* __restrict__ desc, const float* __restrict__ uright, const uint8_t* __restrict__ claimed,
+                          int cap, const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc,
+                          const int* __restrict__ n_queries, int qcap, float min_x, float min_y, float inv_w, float inv_h,
+                          int th_dist, float nn_ratio, int check_orientation, const int4* __restrict__ result,
+                          int* __restrict__ assigned, int* __restrict__ query_match, int* __restrict__ nmatches) {
+  extern __shared__ unsigned s_dyn[];   // claim bits, (cap + 31) / 32 words
+  __shared__ int s_hist[HISTO_LENGTH];
+  const int f = blockIdx.x, lane = threadIdx.x;
+  const int m = min(n_queries[f], qcap);
+  GuidedFrame F;
+  F.items = items + (size_t)f * cap;
+  F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
+  F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
+  F.uright = uright ? uright + (size_t)f * cap : nullptr;
+  F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
+  F.dyn = s_dyn;
+  F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  kps += (size_t)f * cap;
+  queries += (size_t)f * qcap;
+  qdesc += (size_t)f * qcap * 32;
+  result += (size_t)f * qcap;
+  assigned += (size_t)f * cap;
+  query_match += (size_t)f * qcap;
+  for (int i = lane; i < (cap + 31) / 32; i += 32) s_dyn[i] = 0u;
+  for (int i = lane; i < cap; i += 32) assigned[i] = -1;
+  for (int i = lane; i < qcap; i += 32) query_match[i] = -1;
+  if (lane < HISTO_LENGTH) s_hist[lane] = 0;
+  __syncwarp();
+  const bool use_second = nn_ratio > 0.f;
+  int nm = 0;
+  for (int g0 = 0; g0 < m; g0 += 32) {
+    const int cnt = min(32, m - g0);
+    int4 mine = make_int4(-1, -1, 0, 0);
+    if (lane < cnt) mine = result[g0 + lane];
+    for (int j = 0; j < cnt; ++j) {
+      int idx1 = __shfl_sync(0xffffffffu, mine.x, j);
+      if (idx1 < 0) continue;
+      int idx2 = __shfl_sync(0xffffffffu, mine.y, j);
+      int dd = __shfl_sync(0xffffffffu, mine.z, j);
+      int ll = __shfl_sync(0xffffffffu, mine.w, j);
+      const int iq = g0 + j;
+      bool hit = (s_dyn[idx1 >> 5] >> (idx1 & 31)) & 1u;
+      if (use_second && idx2 >= 0) hit = hit || ((s_dyn[idx2 >> 5] >> (idx2 & 31)) & 1u);
+      if (hit) {   // a keypoint of the precomputed pair has been claimed since: redo this query with the claims applied
+        const GuidedQuery q = queries[iq];
+        const uint4* qd = reinterpret_cast<const uint4*>(qdesc + (size_t)iq * 32);
+        unsigned long long k1, k2;
+        guided_scan(F, q, qd[0], qd[1], lane, k1, k2);
+        const int4 r = guided_pack(F, k1, k2, q.flags);
+        idx1 = r.x; idx2 = r.y; dd = r.z; ll = r.w;
+        if (idx1 < 0) continue;
+      }
+      const int d1 = dd & 0xffff, d2 = (dd >> 16) & 0xffff;
+      const int l1 = (signed char)(ll & 0xff), l2 = (signed char)((ll >> 8) & 0xff);
+      bool accept = d1 <= th_dist;                                                          // src/ORBmatcher.cc:170, 1824
+      if (use_second && l1 == l2 && (float)d1 > nn_ratio * (float)d2) accept = false;      // :174
+      if (accept) {
+        ++nm;
+        if (lane == 0) {
+          assigned[idx1] = iq;          // F.mvpMapPoints[bestIdx] = pMP (:177, :1826)
+          query_match[iq] = idx1;
+          if ((ll >> 16) & 2) s_dyn[idx1 >> 5] |= 1u << (idx1 & 31);
+        }
+        __syncwarp();
+      }
+    }
+  }
+  if (check_orientation) {   // :1828-1863
+    const float factor = HISTO_LENGTH / 360.0f;
+    __syncwarp();
+    auto bin_of = [&](int iq, int t) {
+      float rot = queries[iq].angle - kps[t].angle;
+      if (rot < 0.0f) rot += 360.0f;
+      int bin = (int)roundf(rot * factor);
+      if (bin == HISTO_LENGTH) bin = 0;
+      return bin;
+    };
+    for (int iq = lane; iq < m; iq += 32) {
+      const int t = query_match[iq];
+      if (t >= 0) {
+        const int bin = bin_of(iq, t);
+        if (bin >= 0 && bin < HISTO_LENGTH) atomicAdd(&s_hist[bin], 1);
+      }
+    }
+    __syncwarp();
+    // ComputeThreeMaxima (:2026-2068), every lane redundantly
+    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int s = s_hist[i];
+      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+      else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+    int removed = 0;
+    for (int iq = lane; iq < m; iq += 32) {
+      const int t = query_match[iq];
+      if (t >= 0) {
+        const int bin = bin_of(iq, t);
+        if (bin >= 0 && bin < HISTO_LENGTH && bin != ind1 && bin != ind2 && bin != ind3) {
+          assigned[t] = -1;
+          query_match[iq] = -1;
+          ++removed;
+        }
+      }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, removed);
+  }
+  if (lane == 0) nmatches[f] = nm;
+}
+
+void orb_launch_guided(const OrbKeypoint* kps, const uint8_t* desc, const float* uright, const uint8_t* claimed, const int* n_kps, int cap,
+                       const void* queries, const uint8_t* qdesc, const int* n_queries, int qcap, int frames, float min_x, float min_y,
+                       float max_x, float max_y, int th_dist, float nn_ratio, int check_orientation, uint4* items, int* cell_start,
+                       int4* result, int* assigned, int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
+  // mfGridElementWidthInv / HeightInv (src/Frame.cc:200-202)
+  const float inv_w = static_cast<float>(GRID_COLS) / static_cast<float>(max_x - min_x);
+  const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
+  const GuidedQuery* q = static_cast<const GuidedQuery*>(queries);
+  orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
+  orb_guided_top2_kernel<<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, result);
+  const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
+  orb_guided_resolve_kernel<<<frames, 32, smem, st>>>(items, cell_start, kps, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x,
+                                                      min_y, inv_w, inv_h, th_dist, nn_ratio, check_orientation, result, assigned,
+                                                      query_match, nmatches);
+  *launches += 3;
+}

@@ -148,6 +148,7 @@ __global__ void orb_popc_peak_kernel(unsigned* out, int iters, unsigned seed) {
 
 static std::atomic<long long> g_knn_launches{0};   // the kNN entry points are callable from any thread
 long long orb_knn_launches() { return g_knn_launches.load(std::memory_order_relaxed); }
+void orb_knn_count_launches(long long n) { g_knn_launches += n; }
 
 int orb_knn_num_chunks(int Q, long long D, int num_sms) {
   const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);

@@ -28,6 +28,9 @@ void orb_launch_knn(const uint8_t*, int, const uint8_t*, long long, long long, i
 void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaStream_t);
 void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
 long long orb_knn_launches();
+void orb_knn_count_launches(long long n);
+void orb_launch_guided(const OrbKeypoint*, const uint8_t*, const float*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*,
+                       int, int, float, float, float, float, int, float, int, uint4*, int*, int4*, int*, int*, int*, cudaStream_t, long long*);
 double orb_popc_peak(int num_sms);
 
 static_assert(sizeof(orb_keypoint) == 28 && sizeof(OrbKeypoint) == 28, "cv::KeyPoint layout");
@@ -752,6 +755,8 @@ int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keyp
 struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mutex (calls on one device serialise their setup)
   std::mutex mu;
   DevBuf partial, q, db, out;
+  // orb_search_by_projection: sorted keypoints + cell starts + per-query top-2, and the staging copies of host arguments
+  DevBuf g_items, g_cells, g_res, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
   int num_sms = 0;
 };
 static KnnWorkspace g_knn_ws[16];
@@ -845,6 +850,72 @@ int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, 
 }
 
 int64_t orb_matcher_launch_count(void) { return orb_knn_launches(); }
+
+int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
+                             const int32_t* n_kps, int cap, const orb_proj_query* queries, const uint8_t* qdesc,
+                             const int32_t* n_queries, int qcap, int frames, const orb_search_params* prm, int32_t* assigned,
+                             int32_t* query_match, int32_t* nmatches, void* stream) {
+  static_assert(sizeof(orb_proj_query) == 32 && sizeof(orb_search_params) == 32, "ABI struct layout");
+  if (!kps_un || !desc || !n_kps || !queries || !qdesc || !n_queries || !prm || !assigned || !nmatches)
+    return fail(ORB_E_BADARG, "null argument");
+  if (cap <= 0 || cap >= (1 << 18) || qcap <= 0 || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap < 2^18, qcap > 0, frames > 0)");
+  if (!(prm->max_x > prm->min_x) || !(prm->max_y > prm->min_y)) return fail(ORB_E_BADARG, "empty image bounds");
+  if (prm->th_dist < 0 || prm->th_dist > 255) return fail(ORB_E_BADARG, "th_dist must be in [0, 255]");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const size_t F = (size_t)frames;
+  const bool host = mem != ORB_MEM_DEVICE;
+  // device views of the arguments (staged when the caller's arrays are host memory)
+  const void* d_in[7] = {kps_un, desc, uright, claimed, n_kps, queries, qdesc};
+  const void* d_nq = n_queries;
+  int* d_assigned = assigned;
+  int* d_qmatch = query_match;
+  int* d_nm = nmatches;
+  if (host) {
+    DevBuf* bufs[7] = {&ws->g_kps, &ws->g_desc, &ws->g_ur, &ws->g_claim, &ws->g_nk, &ws->g_q, &ws->g_qd};
+    const size_t bytes[7] = {F * cap * sizeof(orb_keypoint), F * cap * 32, F * cap * sizeof(float), F * cap, F * sizeof(int),
+                             F * qcap * sizeof(orb_proj_query), F * qcap * 32};
+    for (int i = 0; i < 7; ++i) {
+      if (!d_in[i]) continue;
+      if ((rc = bufs[i]->ensure(bytes[i])) != ORB_OK) return rc;
+      CU(cudaMemcpyAsync(bufs[i]->p, d_in[i], bytes[i], cudaMemcpyHostToDevice, st));
+      d_in[i] = bufs[i]->p;
+    }
+    if ((rc = ws->g_nq.ensure(F * sizeof(int))) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->g_nq.p, n_queries, F * sizeof(int), cudaMemcpyHostToDevice, st));
+    d_nq = ws->g_nq.p;
+    if ((rc = ws->g_assigned.ensure(F * cap * sizeof(int))) != ORB_OK) return rc;
+    if ((rc = ws->g_nm.ensure(F * sizeof(int))) != ORB_OK) return rc;
+    d_assigned = ws->g_assigned.as<int>();
+    d_nm = ws->g_nm.as<int>();
+  }
+  if (host || !query_match) {   // the resolve kernel always keeps the per-query record (rotation filter)
+    if ((rc = ws->g_qmatch.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
+    d_qmatch = ws->g_qmatch.as<int>();
+  }
+  if ((rc = ws->g_items.ensure(F * cap * sizeof(uint4))) != ORB_OK) return rc;
+  if ((rc = ws->g_cells.ensure(F * (64 * 48 + 1) * sizeof(int))) != ORB_OK) return rc;
+  if ((rc = ws->g_res.ensure(F * qcap * sizeof(int4))) != ORB_OK) return rc;
+  long long launched = 0;
+  orb_launch_guided((const OrbKeypoint*)d_in[0], (const uint8_t*)d_in[1], (const float*)d_in[2], (const uint8_t*)d_in[3], (const int*)d_in[4],
+                    cap, d_in[5], (const uint8_t*)d_in[6], (const int*)d_nq, qcap, frames, prm->min_x, prm->min_y, prm->max_x, prm->max_y,
+                    prm->th_dist, prm->nn_ratio, prm->check_orientation, ws->g_items.as<uint4>(), ws->g_cells.as<int>(),
+                    ws->g_res.as<int4>(), d_assigned, d_qmatch, d_nm, st, &launched);
+  orb_knn_count_launches(launched);
+  CU(cudaGetLastError());
+  if (host) {
+    CU(cudaMemcpyAsync(assigned, d_assigned, F * cap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (query_match) CU(cudaMemcpyAsync(query_match, d_qmatch, F * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORB_OK;
+}
 
 double orb_measure_popc_peak(int device) {
   if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return 0.0; }

@@ -132,3 +132,38 @@ class ORBmatcher:
         """Brute-force k=2 + ratio test. Returns (knn records, accept mask)."""
         knn = hamming_knn(query, db)
         return knn, self.accept(knn, th)
+
+    # ---- guided matching (SURVEY 8(f) N2) ----
+    def SearchByProjection(self, kps_un: np.ndarray, desc: np.ndarray, n_kps: np.ndarray, queries: np.ndarray, qdesc: np.ndarray,
+                           n_queries: np.ndarray, bounds, th_dist: int | None = None, use_ratio: bool = False, uright=None,
+                           claimed=None):
+        """The candidate search of ORBmatcher::SearchByProjection for `frames` independent (query set, target frame) pairs.
+
+        use_ratio=False : Frame-to-Frame tracking form (src/ORBmatcher.cc:1702-1866): best only, rotation histogram iff
+                          mbCheckOrientation.
+        use_ratio=True  : local-map form (src/ORBmatcher.cc:69-184): best / second best with the level-conditional
+                          mfNNratio test, no rotation histogram.
+        kps_un [F,cap] KP_DTYPE (undistorted keypoints of the target frames), desc [F,cap,32], n_kps [F];
+        queries [F,qcap] QUERY_DTYPE (projection, radius, level window, flags), qdesc [F,qcap,32], n_queries [F];
+        bounds = (mnMinX, mnMinY, mnMaxX, mnMaxY); uright [F,cap] float32 (mvuRight) or None; claimed [F,cap] uint8 or None.
+        Returns (assigned [F,cap] int32: query index per keypoint or -1, query_match [F,qcap] int32, nmatches [F])."""
+        from ._lib import QUERY_DTYPE, KP_DTYPE, OrbSearchParams
+        F, cap = kps_un.shape
+        qcap = queries.shape[1]
+        assert kps_un.dtype == KP_DTYPE and queries.dtype == QUERY_DTYPE and queries.shape[0] == F
+        assert desc.shape == (F, cap, 32) and qdesc.shape == (F, qcap, 32) and desc.dtype == np.uint8 and qdesc.dtype == np.uint8
+        arrs = [np.ascontiguousarray(a) for a in (kps_un, desc, queries, qdesc)]
+        nk = np.ascontiguousarray(n_kps, np.int32)
+        nq = np.ascontiguousarray(n_queries, np.int32)
+        ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        cl = None if claimed is None else np.ascontiguousarray(claimed, np.uint8)
+        prm = OrbSearchParams(float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]),
+                              int(self.TH_HIGH if th_dist is None else th_dist), float(self.mfNNratio) if use_ratio else 0.0,
+                              int(self.mbCheckOrientation and not use_ratio), 0)
+        assigned = np.empty((F, cap), np.int32)
+        qmatch = np.empty((F, qcap), np.int32)
+        nm = np.empty(F, np.int32)
+        check(_lib.lib().orb_search_by_projection(MEM_HOST, _vp(arrs[0]), _vp(arrs[1]), None if ur is None else _vp(ur),
+                                                  None if cl is None else _vp(cl), _vp(nk), cap, _vp(arrs[2]), _vp(arrs[3]), _vp(nq),
+                                                  qcap, F, C.byref(prm), _vp(assigned), _vp(qmatch), _vp(nm), None))
+        return assigned, qmatch, nm
