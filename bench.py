@@ -299,6 +299,69 @@ def bench_stereo_e2e(ex, frames_host, steps, warmup, world, bf=386.1448, b=0.537
     return _max_over_ranks(dt * 1e3, world), nm / steps
 
 
+GUIDED_FRAMES, GUIDED_N, GUIDED_M = 512, 2000, 2000
+
+
+def _guided_cases(W, H, distinct=8):
+    return [synth.synth_guided_case(900 + s, n=GUIDED_N, m=GUIDED_M, w=W, h=H, radius=15.0, stereo=True) for s in range(distinct)]
+
+
+def bench_guided(W, H, steps, warmup, world):
+    """Secondary (SURVEY 8(f) N2): ORBmatcher::SearchByProjection(CurrentFrame, LastFrame) candidate search for 512 independent
+    frame pairs per step, 2000 projected map points against 2000 keypoints each, arrays resident in HBM. Returns (ms for
+    `steps` steps max over ranks, matches per frame, kernel launches)."""
+    import ctypes as C
+    import torch
+    from orb_slam2_detailed_comments_b200._lib import lib, check, OrbSearchParams, MEM_DEVICE
+    cases = _guided_cases(W, H)
+    F = GUIDED_FRAMES
+    pick = [cases[i % len(cases)] for i in range(F)]
+    dev = lambda key, dt: torch.from_numpy(np.stack([c[key] for c in pick]).view(np.uint8).reshape(F, -1)).cuda()
+    t = {k: dev(k, None) for k in ("kps", "desc", "uright", "claimed", "queries", "qdesc")}
+    nk = torch.full((F,), GUIDED_N, dtype=torch.int32, device="cuda")
+    nq = torch.full((F,), GUIDED_M, dtype=torch.int32, device="cuda")
+    a = torch.empty((F, GUIDED_N), dtype=torch.int32, device="cuda")
+    qm = torch.empty((F, GUIDED_M), dtype=torch.int32, device="cuda")
+    nm = torch.empty((F,), dtype=torch.int32, device="cuda")
+    prm = OrbSearchParams(*[float(b) for b in cases[0]["bounds"]], 100, 0.0, 1, 0)
+    st = torch.cuda.current_stream().cuda_stream
+    p = lambda x: C.c_void_p(x.data_ptr())
+    L = lib()
+
+    def step():
+        check(L.orb_search_by_projection(MEM_DEVICE, p(t["kps"]), p(t["desc"]), p(t["uright"]), p(t["claimed"]), p(nk), GUIDED_N,
+                                         p(t["queries"]), p(t["qdesc"]), p(nq), GUIDED_M, F, C.byref(prm), p(a), p(qm), p(nm), C.c_void_p(st)))
+    for _ in range(max(warmup, 1)):
+        step()
+    l0 = L.orb_matcher_launch_count()
+    _barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    _barrier(world)
+    return _max_over_ranks(ms, world), float(nm.float().mean().item()), L.orb_matcher_launch_count() - l0
+
+
+def cpu_guided_rate(W, H, threads, frames=4096):
+    """The oracle's SearchByProjection on `frames` frame pairs of the same workload, one frame per task on `threads` threads."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle_py
+    cases = _guided_cases(W, H)
+    oracle_py.search_by_projection(cases[0]["kps"], cases[0]["desc"], cases[0]["queries"], cases[0]["qdesc"], cases[0]["bounds"])   # load + argtypes
+    def one(i):
+        c = cases[i % len(cases)]
+        return oracle_py.search_by_projection(c["kps"], c["desc"], c["queries"], c["qdesc"], c["bounds"], 100, 0.0, True, c["uright"], c["claimed"])[2]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(one, range(frames)))
+    dt = time.perf_counter() - t0
+    return frames / dt, dt
+
+
 def bench_knn(rank, world, steps, warmup):
     """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks, one all_gather
     of the per-query records + device merge when world > 1. pairs/s = Q*D / time (max over ranks)."""
@@ -361,6 +424,8 @@ def run_b200(args):
 
     st_ms, st_matches = bench_stereo_e2e(ex, frames, e_steps, args.warmup, world)
     knn_rate, knn_ms, knn_launches = bench_knn(rank, world, max(args.steps, 5), args.warmup)
+    g_steps = max(args.steps, 5)
+    g_ms, g_matches, g_launches = bench_guided(W, H, g_steps, args.warmup, world)
     popc_peak = pkg.lib().orb_measure_popc_peak(local) if rank == 0 else 0.0
 
     if rank != 0:
@@ -408,6 +473,10 @@ def run_b200(args):
         "stereo": {"metric": "stereo frame pairs/sec (extract L+R + Frame::ComputeStereoMatches on device, host to host)",
                    "value": (B // 2) * world * e_steps / (st_ms * 1e-3), "unit": "pairs/s", "ms_per_step": st_ms / e_steps,
                    "stereo_matches_per_pair": st_matches / (B // 2), "api": "orb_extract_stereo_batch (pinned host in/out)"},
+        "guided": {"metric": "guided searches/sec (ORBmatcher::SearchByProjection frame-to-frame form: grid + window scan + claims + rotation filter)",
+                   "value": GUIDED_FRAMES * world * g_steps / (g_ms * 1e-3), "unit": "frame pairs/s", "ms_per_step": g_ms / g_steps,
+                   "config": f"{GUIDED_FRAMES} frame pairs per step per GPU, {GUIDED_M} projected map points x {GUIDED_N} keypoints each, resident in HBM",
+                   "matches_per_pair": g_matches, "gpu_launches": int(g_launches), "api": "orb_search_by_projection (device memory)"},
         "knn": {"metric": "Hamming matches/sec (k=2 brute force)", "value": knn_rate, "unit": "pairs/s",
                 "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
                           + (", NCCL all_gather + device top-2 merge" if world > 1 else ""),
@@ -425,6 +494,9 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n} images of the same workload, one oracle extractor per thread, {dt:.1f} s wall",
                                 "knn_pairs_per_s": kv}
+        gv, gdt = cpu_guided_rate(W, H, cores)
+        line["guided"]["cpu_baseline"] = {"value": gv, "unit": "frame pairs/s", "cores": cores, "kind": "port",
+                                          "sample": f"4096 frame pairs of the same workload, {gdt:.1f} s wall"}
     print(json.dumps(line), flush=True)
 
 

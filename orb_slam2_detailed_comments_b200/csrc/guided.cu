@@ -9,10 +9,13 @@
 //      column-major (ix * 48 + iy) and keypoints in index order inside a cell. GetFeaturesInArea's scan order
 //      (ix, then iy, then insertion order) is then simply ascending position in the sorted array, and the cells
 //      iy0..iy1 of one column are ONE contiguous range.
-//   2. orb_guided_top2_kernel   (warp per query): best / second best over the query's window, ignoring claims made by
-//      other queries. Key = dist << 32 | sorted position, so "strict <, first in scan order wins" is a plain min.
-//   3. orb_guided_resolve_kernel (warp per frame): walks the queries in order. A precomputed result is final unless one
-//      of its two keypoints has been claimed since — only then the warp rescans that query with the claims applied.
+//   2. orb_guided_candidates_kernel (warp per query): window scan, static filters (level window, |dx|,|dy| < r, caller's
+//      claimed flags, stereo column check) and DescriptorDistance; writes the query's candidate list, up to 32 words
+//      (dist, sorted position | level, keypoint index), in any order — the position inside the word carries the scan order.
+//   3. orb_guided_resolve_kernel (warp per frame): walks the queries in order; lane l holds candidate l of the current
+//      query, drops it if its keypoint has been claimed since, and two REDUX.MIN give best and second best ("strict <,
+//      first in scan order wins" == unsigned min over dist << 18 | position). Lists are staged one group of 32 queries
+//      ahead with cp.async. A query with more than 32 candidates is rescanned by the warp with the claims applied.
 //      Accept rule, assignment, claim bit, rotation histogram and the three-maxima filter follow.
 #include "orb_common.cuh"
 
@@ -35,20 +38,21 @@ struct GuidedFrame {
   const uint4* desc;         // [n][2]
   const float* uright;       // or nullptr
   const uint8_t* claimed;    // or nullptr (static claims)
-  const unsigned* dyn;       // shared-memory claim bits of the resolve kernel, or nullptr
   float min_x, min_y, inv_w, inv_h;
 };
 
-__device__ __forceinline__ void top2_insert(unsigned long long& k1, unsigned long long& k2, unsigned long long k) {
-  if (k < k1) { k2 = k1; k1 = k; }
-  else if (k < k2) k2 = k;
-}
+// A candidate is one 64-bit word {hi, lo}. hi = dist << 18 | sorted position: "strict <, first in scan order wins" is a plain
+// unsigned min over it and it is unique per candidate. lo = level << 18 | keypoint index.
+#define GUIDED_LIST 32   // candidates kept per query (one per lane of the resolving warp); longer lists fall back to a rescan
+#define GUIDED_NONE 0xffffffffu
 
-// GetFeaturesInArea + the candidate filters + DescriptorDistance for one query, by one warp. Returns the two smallest
-// keys (dist << 32 | sorted position), ~0 = none, identical in all lanes.
+// GetFeaturesInArea + the static candidate filters + DescriptorDistance for one query, by one warp. Four groups of 8 lanes
+// take the grid columns of the window in turn; the lanes of a group stride over the column's contiguous range of sorted
+// keypoints. Every slot is handed to emit(hi, lo) by its lane, hi == GUIDED_NONE for "no candidate"; the trip count is
+// warp-uniform so emit() may use warp collectives.
+template <typename Emit>
 __device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQuery& q, const uint4 qd0, const uint4 qd1, int lane,
-                                            unsigned long long& k1, unsigned long long& k2) {
-  k1 = k2 = ~0ull;
+                                            Emit emit) {
   const float x = q.u, y = q.v, r = q.radius;
   // src/Frame.cc:649-668
   const int cx0 = max(0, (int)floorf((x - F.min_x - r) * F.inv_w));
@@ -58,48 +62,39 @@ __device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQu
   if (cx0 >= GRID_COLS || cx1 < 0 || cy0 >= GRID_ROWS || cy1 < 0) return;
   const int min_level = q.min_level, max_level = q.max_level;
   const bool check_levels = (min_level > 0) || (max_level >= 0);
-  for (int ix = cx0; ix <= cx1; ++ix) {
-    const int e0 = F.cell_start[ix * GRID_ROWS + cy0], e1 = F.cell_start[ix * GRID_ROWS + cy1 + 1];
-    for (int e = e0 + lane; e < e1; e += 32) {
-      const uint4 it = F.items[e];
-      const int oct = (int)it.z, idx = (int)it.w;
-      if (check_levels && (oct < min_level || (max_level >= 0 && oct > max_level))) continue;
-      const float dx = __uint_as_float(it.x) - x, dy = __uint_as_float(it.y) - y;
-      if (!(fabsf(dx) < r && fabsf(dy) < r)) continue;
-      if (F.claimed && F.claimed[idx]) continue;
-      if (F.dyn && ((F.dyn[idx >> 5] >> (idx & 31)) & 1u)) continue;
-      if (F.uright) {
-        const float ur = F.uright[idx];
-        if (ur > 0.f && fabsf(q.ur - ur) > r) continue;
+  const int grp = lane >> 3, sub = lane & 7;
+  for (int cx = cx0; cx <= cx1; cx += 4) {   // warp-uniform
+    const int ix = cx + grp;
+    int e0 = 0, e1 = 0;
+    if (ix <= cx1) { e0 = F.cell_start[ix * GRID_ROWS + cy0]; e1 = F.cell_start[ix * GRID_ROWS + cy1 + 1]; }
+    int trips = (e1 - e0 + 7) >> 3;
+    trips = max(trips, __shfl_xor_sync(0xffffffffu, trips, 8));
+    trips = max(trips, __shfl_xor_sync(0xffffffffu, trips, 16));
+    for (int t = 0; t < trips; ++t) {
+      const int e = e0 + t * 8 + sub;
+      unsigned hi = GUIDED_NONE, lo = 0;
+      if (e < e1) {
+        const uint4 it = F.items[e];
+        const int oct = (int)it.z, idx = (int)it.w;
+        bool ok = !(check_levels && (oct < min_level || (max_level >= 0 && oct > max_level)));
+        const float dx = __uint_as_float(it.x) - x, dy = __uint_as_float(it.y) - y;
+        ok = ok && fabsf(dx) < r && fabsf(dy) < r;
+        if (ok && F.claimed && F.claimed[idx]) ok = false;
+        if (ok && F.uright) {
+          const float ur = F.uright[idx];
+          if (ur > 0.f && fabsf(q.ur - ur) > r) ok = false;
+        }
+        if (ok) {
+          const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
+          const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
+                           __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
+          hi = ((unsigned)dist << 18) | (unsigned)e;
+          lo = ((unsigned)(oct & 0xff) << 18) | (unsigned)idx;
+        }
       }
-      const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
-      const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
-                       __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
-      top2_insert(k1, k2, ((unsigned long long)dist << 32) | (unsigned)e);
+      emit(hi, lo);
     }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
-    const unsigned long long lo = min(k1, o1), hi = max(k1, o1);
-    k2 = min(hi, min(k2, o2));
-    k1 = lo;
-  }
-}
-
-// packed result: x = idx1, y = idx2, z = d1 | d2 << 16, w = (l1 & 0xff) | (l2 & 0xff) << 8 | flags << 16
-__device__ __forceinline__ int4 guided_pack(const GuidedFrame& F, unsigned long long k1, unsigned long long k2, int flags) {
-  int4 r = make_int4(-1, -1, 256 | (256 << 16), 0xffff | (flags << 16));
-  if (k1 != ~0ull) {
-    const uint4 it = F.items[(unsigned)k1];
-    int idx2 = -1, d2 = 256, l2 = -1;   // bestDist2 = 256, bestLevel2 = -1 (src/ORBmatcher.cc:114-115)
-    if (k2 != ~0ull) {
-      const uint4 it2 = F.items[(unsigned)k2];
-      idx2 = (int)it2.w; d2 = (int)(k2 >> 32); l2 = (int)it2.z;
-    }
-    r = make_int4((int)it.w, idx2, (int)(k1 >> 32) | (d2 << 16), ((int)it.z & 0xff) | ((l2 & 0xff) << 8) | (flags << 16));
-  }
-  return r;
 }
 
 // ---- 1. grid ----------------------------------------------------------------------------------------------------------
@@ -168,12 +163,13 @@ __global__ void __launch_bounds__(256) orb_guided_grid_kernel(const OrbKeypoint*
   }
 }
 
-// ---- 2. top-2 per query, no dynamic claims --------------------------------------------------------------------------------
+// ---- 2. candidate list per query -------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(GUIDED_WARPS * 32)
-orb_guided_top2_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const uint8_t* __restrict__ desc,
-                       const float* __restrict__ uright, const uint8_t* __restrict__ claimed, int cap,
-                       const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc, const int* __restrict__ n_queries,
-                       int qcap, float min_x, float min_y, float inv_w, float inv_h, int4* __restrict__ result) {
+orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const uint8_t* __restrict__ desc,
+                             const float* __restrict__ uright, const uint8_t* __restrict__ claimed, int cap,
+                             const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc, const int* __restrict__ n_queries,
+                             int qcap, float min_x, float min_y, float inv_w, float inv_h, uint2* __restrict__ lists,
+                             int* __restrict__ list_cnt) {
   const int f = blockIdx.y, lane = threadIdx.x & 31;
   const int iq = blockIdx.x * GUIDED_WARPS + (threadIdx.x >> 5);
   if (iq >= min(n_queries[f], qcap)) return;
@@ -183,28 +179,39 @@ orb_guided_top2_kernel(const uint4* __restrict__ items, const int* __restrict__ 
   F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
   F.uright = uright ? uright + (size_t)f * cap : nullptr;
   F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
-  F.dyn = nullptr;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
-  const GuidedQuery q = queries[(size_t)f * qcap + iq];
-  int4 r = make_int4(-1, -1, 256 | (256 << 16), 0xffff | (q.flags << 16));
+  const size_t qi = (size_t)f * qcap + iq;
+  const GuidedQuery q = queries[qi];
+  uint2* out = lists + qi * GUIDED_LIST;
+  int n = 0;
   if (!(q.flags & 1)) {
-    const uint4* qd = reinterpret_cast<const uint4*>(qdesc + ((size_t)f * qcap + iq) * 32);
-    unsigned long long k1, k2;
-    guided_scan(F, q, qd[0], qd[1], lane, k1, k2);
-    r = guided_pack(F, k1, k2, q.flags);
+    const uint4* qd = reinterpret_cast<const uint4*>(qdesc + qi * 32);
+    guided_scan(F, q, qd[0], qd[1], lane, [&](unsigned hi, unsigned lo) {
+      const unsigned m = __ballot_sync(0xffffffffu, hi != GUIDED_NONE);
+      const int pos = n + __popc(m & ((1u << lane) - 1u));
+      if (hi != GUIDED_NONE && pos < GUIDED_LIST) out[pos] = make_uint2(lo, hi);
+      n += __popc(m);
+    });
   }
-  if (lane == 0) result[(size_t)f * qcap + iq] = r;
+  if (lane >= n && lane < GUIDED_LIST) out[lane] = make_uint2(0u, GUIDED_NONE);   // pad: the resolving warp reads all 32 slots
+  if (lane == 0) list_cnt[qi] = n;   // > GUIDED_LIST = overflow, the list is incomplete
 }
 
 // ---- 3. sequential claims, accept rule, rotation filter --------------------------------------------------------------------
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+
 __global__ void __launch_bounds__(32)
 orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const OrbKeypoint* __restrict__ kps,
                           const uint8_t* __restrict__ desc, const float* __restrict__ uright, const uint8_t* __restrict__ claimed,
                           int cap, const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc,
                           const int* __restrict__ n_queries, int qcap, float min_x, float min_y, float inv_w, float inv_h,
-                          int th_dist, float nn_ratio, int check_orientation, const int4* __restrict__ result,
-                          int* __restrict__ assigned, int* __restrict__ query_match, int* __restrict__ nmatches) {
+                          int th_dist, float nn_ratio, int check_orientation, const uint2* __restrict__ lists,
+                          const int* __restrict__ list_cnt, int* __restrict__ assigned, int* __restrict__ query_match,
+                          int* __restrict__ nmatches) {
   extern __shared__ unsigned s_dyn[];   // claim bits, (cap + 31) / 32 words
+  __shared__ uint2 s_list[2][32][GUIDED_LIST];   // candidate lists of two groups of 32 queries (16 KB)
   __shared__ int s_hist[HISTO_LENGTH];
   const int f = blockIdx.x, lane = threadIdx.x;
   const int m = min(n_queries[f], qcap);
@@ -214,14 +221,20 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
   F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
   F.uright = uright ? uright + (size_t)f * cap : nullptr;
   F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
-  F.dyn = s_dyn;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
   kps += (size_t)f * cap;
   queries += (size_t)f * qcap;
   qdesc += (size_t)f * qcap * 32;
-  result += (size_t)f * qcap;
+  lists += (size_t)f * qcap * GUIDED_LIST;
+  list_cnt += (size_t)f * qcap;
   assigned += (size_t)f * cap;
   query_match += (size_t)f * qcap;
+  auto stage = [&](int g0, int buf) {   // lists of queries [g0, g0 + 32) -> s_list[buf]; one 256-byte row per instruction
+    const int cnt = min(32, m - g0);
+    for (int j = 0; j < cnt; ++j) cp_async8(&s_list[buf][j][lane], lists + (size_t)(g0 + j) * GUIDED_LIST + lane);
+    asm volatile("cp.async.commit_group;");
+  };
+  if (m > 0) stage(0, 0);
   for (int i = lane; i < (cap + 31) / 32; i += 32) s_dyn[i] = 0u;
   for (int i = lane; i < cap; i += 32) assigned[i] = -1;
   for (int i = lane; i < qcap; i += 32) query_match[i] = -1;
@@ -229,38 +242,72 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
   __syncwarp();
   const bool use_second = nn_ratio > 0.f;
   int nm = 0;
-  for (int g0 = 0; g0 < m; g0 += 32) {
+  for (int g0 = 0, buf = 0; g0 < m; g0 += 32, buf ^= 1) {
     const int cnt = min(32, m - g0);
-    int4 mine = make_int4(-1, -1, 0, 0);
-    if (lane < cnt) mine = result[g0 + lane];
+    int my_cnt = 0, my_flags = 0;
+    if (lane < cnt) { my_cnt = list_cnt[g0 + lane]; my_flags = queries[g0 + lane].flags; }
+    if (g0 + 32 < m) {
+      stage(g0 + 32, buf ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncwarp();
     for (int j = 0; j < cnt; ++j) {
-      int idx1 = __shfl_sync(0xffffffffu, mine.x, j);
-      if (idx1 < 0) continue;
-      int idx2 = __shfl_sync(0xffffffffu, mine.y, j);
-      int dd = __shfl_sync(0xffffffffu, mine.z, j);
-      int ll = __shfl_sync(0xffffffffu, mine.w, j);
+      const int n = __shfl_sync(0xffffffffu, my_cnt, j);
+      if (n == 0) continue;
+      const int flags = __shfl_sync(0xffffffffu, my_flags, j);
       const int iq = g0 + j;
-      bool hit = (s_dyn[idx1 >> 5] >> (idx1 & 31)) & 1u;
-      if (use_second && idx2 >= 0) hit = hit || ((s_dyn[idx2 >> 5] >> (idx2 & 31)) & 1u);
-      if (hit) {   // a keypoint of the precomputed pair has been claimed since: redo this query with the claims applied
+      unsigned hi1 = GUIDED_NONE, lo1 = 0, hi2 = GUIDED_NONE, lo2 = 0;   // best / second best, identical in all lanes
+      if (n <= GUIDED_LIST) {
+        const uint2 c = s_list[buf][j][lane];
+        const unsigned idx = c.x & 0x3ffffu;
+        const bool live = c.y != GUIDED_NONE && !((s_dyn[idx >> 5] >> (idx & 31)) & 1u);
+        const unsigned hi = live ? c.y : GUIDED_NONE;
+        hi1 = __reduce_min_sync(0xffffffffu, hi);
+        if (hi1 == GUIDED_NONE) continue;
+        const int l1 = __ffs(__ballot_sync(0xffffffffu, hi == hi1)) - 1;
+        lo1 = __shfl_sync(0xffffffffu, c.x, l1);
+        if (use_second) {
+          hi2 = __reduce_min_sync(0xffffffffu, lane == l1 ? GUIDED_NONE : hi);
+          if (hi2 != GUIDED_NONE) lo2 = __shfl_sync(0xffffffffu, c.x, __ffs(__ballot_sync(0xffffffffu, hi == hi2)) - 1);
+        }
+      } else {   // more candidates than list slots: rescan the window with the claims applied
         const GuidedQuery q = queries[iq];
         const uint4* qd = reinterpret_cast<const uint4*>(qdesc + (size_t)iq * 32);
-        unsigned long long k1, k2;
-        guided_scan(F, q, qd[0], qd[1], lane, k1, k2);
-        const int4 r = guided_pack(F, k1, k2, q.flags);
-        idx1 = r.x; idx2 = r.y; dd = r.z; ll = r.w;
-        if (idx1 < 0) continue;
+        unsigned long long k1 = ~0ull, k2 = ~0ull;
+        guided_scan(F, q, qd[0], qd[1], lane, [&](unsigned hi, unsigned lo) {
+          const unsigned idx = lo & 0x3ffffu;
+          if (hi != GUIDED_NONE && !((s_dyn[idx >> 5] >> (idx & 31)) & 1u)) {
+            const unsigned long long k = ((unsigned long long)hi << 32) | lo;
+            if (k < k1) { k2 = k1; k1 = k; }
+            else if (k < k2) k2 = k;
+          }
+        });
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+          const unsigned long long lo = min(k1, o1), hi = max(k1, o1);
+          k2 = min(hi, min(k2, o2));
+          k1 = lo;
+        }
+        hi1 = (unsigned)(k1 >> 32); lo1 = (unsigned)k1;
+        hi2 = (unsigned)(k2 >> 32); lo2 = (unsigned)k2;
+        if (hi1 == GUIDED_NONE) continue;
       }
-      const int d1 = dd & 0xffff, d2 = (dd >> 16) & 0xffff;
-      const int l1 = (signed char)(ll & 0xff), l2 = (signed char)((ll >> 8) & 0xff);
+      const int d1 = (int)(hi1 >> 18), idx1 = (int)(lo1 & 0x3ffffu), l1 = (int)(lo1 >> 18);
       bool accept = d1 <= th_dist;                                                          // src/ORBmatcher.cc:170, 1824
-      if (use_second && l1 == l2 && (float)d1 > nn_ratio * (float)d2) accept = false;      // :174
+      if (use_second) {
+        const int d2 = hi2 == GUIDED_NONE ? 256 : (int)(hi2 >> 18);                         // bestDist2 = 256, bestLevel2 = -1 (:114-115)
+        const int l2 = hi2 == GUIDED_NONE ? -1 : (int)(lo2 >> 18);
+        if (l1 == l2 && (float)d1 > nn_ratio * (float)d2) accept = false;                   // :174
+      }
       if (accept) {
         ++nm;
         if (lane == 0) {
           assigned[idx1] = iq;          // F.mvpMapPoints[bestIdx] = pMP (:177, :1826)
           query_match[iq] = idx1;
-          if ((ll >> 16) & 2) s_dyn[idx1 >> 5] |= 1u << (idx1 & 31);
+          if (flags & 2) s_dyn[idx1 >> 5] |= 1u << (idx1 & 31);
         }
         __syncwarp();
       }
@@ -314,17 +361,17 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
 void orb_launch_guided(const OrbKeypoint* kps, const uint8_t* desc, const float* uright, const uint8_t* claimed, const int* n_kps, int cap,
                        const void* queries, const uint8_t* qdesc, const int* n_queries, int qcap, int frames, float min_x, float min_y,
                        float max_x, float max_y, int th_dist, float nn_ratio, int check_orientation, uint4* items, int* cell_start,
-                       int4* result, int* assigned, int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
+                       uint2* lists, int* list_cnt, int* assigned, int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
   // mfGridElementWidthInv / HeightInv (src/Frame.cc:200-202)
   const float inv_w = static_cast<float>(GRID_COLS) / static_cast<float>(max_x - min_x);
   const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
   const GuidedQuery* q = static_cast<const GuidedQuery*>(queries);
   orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
-  orb_guided_top2_kernel<<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
-      items, cell_start, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, result);
+  orb_guided_candidates_kernel<<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
   const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
   orb_guided_resolve_kernel<<<frames, 32, smem, st>>>(items, cell_start, kps, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x,
-                                                      min_y, inv_w, inv_h, th_dist, nn_ratio, check_orientation, result, assigned,
+                                                      min_y, inv_w, inv_h, th_dist, nn_ratio, check_orientation, lists, list_cnt, assigned,
                                                       query_match, nmatches);
   *launches += 3;
 }

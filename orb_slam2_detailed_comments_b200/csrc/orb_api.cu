@@ -30,7 +30,7 @@ void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, 
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
 void orb_launch_guided(const OrbKeypoint*, const uint8_t*, const float*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*,
-                       int, int, float, float, float, float, int, float, int, uint4*, int*, int4*, int*, int*, int*, cudaStream_t, long long*);
+                       int, int, float, float, float, float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
 double orb_popc_peak(int num_sms);
 
 static_assert(sizeof(orb_keypoint) == 28 && sizeof(OrbKeypoint) == 28, "cv::KeyPoint layout");
@@ -756,7 +756,7 @@ struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mut
   std::mutex mu;
   DevBuf partial, q, db, out;
   // orb_search_by_projection: sorted keypoints + cell starts + per-query top-2, and the staging copies of host arguments
-  DevBuf g_items, g_cells, g_res, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
+  DevBuf g_items, g_cells, g_lists, g_lcnt, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
   int num_sms = 0;
 };
 static KnnWorkspace g_knn_ws[16];
@@ -900,12 +900,13 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
   }
   if ((rc = ws->g_items.ensure(F * cap * sizeof(uint4))) != ORB_OK) return rc;
   if ((rc = ws->g_cells.ensure(F * (64 * 48 + 1) * sizeof(int))) != ORB_OK) return rc;
-  if ((rc = ws->g_res.ensure(F * qcap * sizeof(int4))) != ORB_OK) return rc;
+  if ((rc = ws->g_lists.ensure(F * qcap * 32 * sizeof(uint2))) != ORB_OK) return rc;
+  if ((rc = ws->g_lcnt.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
   long long launched = 0;
   orb_launch_guided((const OrbKeypoint*)d_in[0], (const uint8_t*)d_in[1], (const float*)d_in[2], (const uint8_t*)d_in[3], (const int*)d_in[4],
                     cap, d_in[5], (const uint8_t*)d_in[6], (const int*)d_nq, qcap, frames, prm->min_x, prm->min_y, prm->max_x, prm->max_y,
                     prm->th_dist, prm->nn_ratio, prm->check_orientation, ws->g_items.as<uint4>(), ws->g_cells.as<int>(),
-                    ws->g_res.as<int4>(), d_assigned, d_qmatch, d_nm, st, &launched);
+                    ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, d_qmatch, d_nm, st, &launched);
   orb_knn_count_launches(launched);
   CU(cudaGetLastError());
   if (host) {
