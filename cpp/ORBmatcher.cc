@@ -71,4 +71,39 @@ int ORBmatcher::MatchBruteForce(const cv::Mat& queries, const cv::Mat& database,
   return n;
 }
 
+int ORBmatcher::SearchByProjection(const TargetFrame& F, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors, int th,
+                                   bool useRatio, std::vector<int>& assigned, std::vector<int>* pointMatch) const {
+  static_assert(sizeof(cv::KeyPoint) == sizeof(orb_keypoint), "cv::KeyPoint must be the 28-byte POD the C ABI reads");
+  const int n = (int)F.mvKeysUn->size(), m = (int)points.size();
+  assigned.assign(n, -1);
+  if (pointMatch) pointMatch->assign(m, -1);
+  if (n == 0 || m == 0) return 0;
+  if (F.mDescriptors->rows != n || pointDescriptors.rows != m) throw std::runtime_error("SearchByProjection: descriptor rows != keypoints / points");
+  std::vector<uint8_t> tmp_d, tmp_q;
+  const uint8_t* d = rows32(*F.mDescriptors, tmp_d);
+  const uint8_t* qd = rows32(pointDescriptors, tmp_q);
+  std::vector<orb_proj_query> q(m);
+  for (int i = 0; i < m; ++i) {
+    const ProjectedPoint& p = points[i];
+    q[i].u = p.u; q[i].v = p.v; q[i].radius = p.radius; q[i].ur = p.uRight; q[i].angle = p.angle;
+    q[i].min_level = (int16_t)p.minLevel; q[i].max_level = (int16_t)p.maxLevel;
+    q[i].flags = (p.skip ? ORB_QUERY_SKIP : 0) | (p.claims ? ORB_QUERY_CLAIMS : 0);
+    q[i].reserved = 0;
+  }
+  orb_search_params prm;
+  prm.min_x = F.mnMinX; prm.min_y = F.mnMinY; prm.max_x = F.mnMaxX; prm.max_y = F.mnMaxY;
+  prm.th_dist = th;
+  prm.nn_ratio = useRatio ? mfNNratio : 0.f;
+  prm.check_orientation = (!useRatio && mbCheckOrientation) ? 1 : 0;
+  prm.reserved = 0;
+  std::vector<int32_t> qm(m);
+  int32_t nmatches = 0;
+  check(orb_search_by_projection(ORB_MEM_HOST, reinterpret_cast<const orb_keypoint*>(F.mvKeysUn->data()), d,
+                                 F.mvuRight ? F.mvuRight->data() : nullptr, F.claimed ? F.claimed->data() : nullptr, &n, n, q.data(), qd,
+                                 &m, m, 1, &prm, assigned.data(), qm.data(), &nmatches, nullptr),
+        "orb_search_by_projection");
+  if (pointMatch) pointMatch->assign(qm.begin(), qm.end());
+  return nmatches;
+}
+
 }  // namespace ORB_SLAM2

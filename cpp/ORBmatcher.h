@@ -1,8 +1,9 @@
 // Drop-in for the hot-path part of the reference's include/ORBmatcher.h: DescriptorDistance (include/ORBmatcher.h:62,
 // src/ORBmatcher.cc:2073-2093), the public thresholds (:223-225) and the best / second-best + ratio idiom every Search*
 // function repeats (canonical form src/ORBmatcher.cc:304-342) as a brute-force k=2 call on the GPU.
-// The nine guided Search* / Fuse functions are NOT part of this path and are not declared here; when
-// integrating, keep the reference's own ORBmatcher.cc for them and add the members below.
+// Of the guided Search* / Fuse functions the shared core — GetFeaturesInArea, the candidate scan with
+// sequential claims and the rotation histogram — is offered as one flat call, SearchByProjection(TargetFrame, points, ...);
+// pose / camera projection stay in the reference's own ORBmatcher.cc (INTEGRATION.md shows the rewritten loop).
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
@@ -40,6 +41,30 @@ class ORBmatcher {
   bool Accept(const Knn2& m, int th) const { return m.bestDist <= th && (float)m.bestDist < mfNNratio * (float)m.bestDist2; }
   // Convenience: indices of accepted matches (-1 = rejected), threshold TH_LOW by default.
   int MatchBruteForce(const cv::Mat& queries, const cv::Mat& database, std::vector<int64_t>& matches, int th = TH_LOW) const;
+
+  // ---- guided search (src/ORBmatcher.cc:69-184 and 1702-1866 after the projection step) ----
+  struct ProjectedPoint {    // one map point projected into the target frame
+    float u, v;              // mTrackProjX/Y (:101) or the pinhole projection (:1755-1756)
+    float radius;            // window half-size handed to GetFeaturesInArea (:102, :1769), also the stereo tolerance
+    float uRight;            // mTrackProjXR (:137) or u - mbf * invzc (:1806); only read where the keypoint has a right match
+    float angle;             // angle of the point's own keypoint (rotation histogram, :1830)
+    int minLevel, maxLevel;  // GetFeaturesInArea level window; maxLevel < 0 = open
+    bool skip;               // !mbTrackInView / isBad() / outlier / behind the camera / outside the image
+    bool claims;             // pMP->Observations() > 0 (:127-130, :1798-1801)
+  };
+  struct TargetFrame {       // the members of Frame the search reads
+    const std::vector<cv::KeyPoint>* mvKeysUn;
+    const cv::Mat* mDescriptors;                 // N x 32 CV_8U
+    const std::vector<float>* mvuRight;          // nullptr for monocular
+    const std::vector<unsigned char>* claimed;   // per keypoint: mvpMapPoints[i] && mvpMapPoints[i]->Observations() > 0; nullptr = none
+    float mnMinX, mnMinY, mnMaxX, mnMaxY;
+  };
+  // Points are processed in index order, exactly like the reference's loops. assigned[i] = index of the point matched to
+  // keypoint i (what the reference stores as F.mvpMapPoints[i] = pMP) or -1. useRatio selects the local-map form
+  // (best / second best, level-conditional mfNNratio test, :174); otherwise best only plus the rotation histogram when
+  // mbCheckOrientation (:1828-1863). Returns nmatches. GPU only.
+  int SearchByProjection(const TargetFrame& F, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors, int th,
+                         bool useRatio, std::vector<int>& assigned, std::vector<int>* pointMatch = nullptr) const;
 
   static const int TH_LOW;        // 50
   static const int TH_HIGH;       // 100

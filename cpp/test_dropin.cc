@@ -151,6 +151,38 @@ int main(int argc, char** argv) {
       orb_oracle_destroy(oR);
       std::printf("ExtractStereo: %d stereo matches, mvuRight / mvDepth bit-exact vs oracle\n", kept);
     }
+    // guided search: the left keypoints projected into the right image (constant shift unknown to the matcher: window 40 px),
+    // frame-to-frame form with rotation histogram, then the local-map form with the ratio test
+    {
+      std::vector<ORB_SLAM2::ORBmatcher::ProjectedPoint> pts(bk[0].size());
+      for (size_t i = 0; i < pts.size(); ++i) {
+        const cv::KeyPoint& k = bk[0][i];
+        pts[i] = {k.pt.x, k.pt.y, 40.f, -1.f, k.angle, k.octave - 1, k.octave + 1, (i % 17) == 3, (i % 5) != 0};
+      }
+      std::vector<unsigned char> claimed(bk[1].size(), 0);
+      for (size_t i = 0; i < claimed.size(); i += 11) claimed[i] = 1;
+      ORB_SLAM2::ORBmatcher::TargetFrame F{&bk[1], &bd[1], nullptr, &claimed, 0.f, 0.f, (float)W, (float)H};
+      std::vector<orb_oracle_query> oq(pts.size());
+      for (size_t i = 0; i < pts.size(); ++i) {
+        oq[i] = {pts[i].u, pts[i].v, pts[i].radius, pts[i].uRight, pts[i].angle, (int16_t)pts[i].minLevel, (int16_t)pts[i].maxLevel,
+                 (pts[i].skip ? 1 : 0) | (pts[i].claims ? 2 : 0), 0};
+      }
+      for (int form = 0; form < 2; ++form) {
+        ORB_SLAM2::ORBmatcher gm(0.8f, true);
+        std::vector<int> assigned, pm;
+        const int nm = gm.SearchByProjection(F, pts, bd[0], ORB_SLAM2::ORBmatcher::TH_HIGH, form == 1, assigned, &pm);
+        orb_oracle_search_params op{0.f, 0.f, (float)W, (float)H, ORB_SLAM2::ORBmatcher::TH_HIGH, form == 1 ? 0.8f : 0.f, form == 0 ? 1 : 0, 0};
+        std::vector<int32_t> oa(bk[1].size()), oqm(pts.size());
+        const int onm = orb_oracle_search_by_projection(reinterpret_cast<const orb_oracle_kp*>(bk[1].data()), bd[1].ptr<unsigned char>(0), nullptr,
+                                                        claimed.data(), (int)bk[1].size(), oq.data(), bd[0].ptr<unsigned char>(0), (int)pts.size(),
+                                                        &op, oa.data(), oqm.data());
+        REQUIRE(nm == onm, "SearchByProjection form %d: nmatches %d vs oracle %d", form, nm, onm);
+        REQUIRE(std::memcmp(assigned.data(), oa.data(), oa.size() * 4) == 0 && std::memcmp(pm.data(), oqm.data(), oqm.size() * 4) == 0,
+                "SearchByProjection form %d: assignment differs from the oracle", form);
+        REQUIRE(nm > 50, "SearchByProjection form %d: too few matches (%d)", form, nm);
+        std::printf("SearchByProjection (%s): %d matches, assignment bit-exact vs oracle\n", form ? "local-map form" : "frame-to-frame form", nm);
+      }
+    }
     std::printf("ORBmatcher: kNN over %d x %d bit-exact, %d ratio-test accepts, DescriptorDistance x %d exact\n", bd[0].rows, bd[1].rows, nacc, m);
   }
   orb_oracle_destroy(oe);
