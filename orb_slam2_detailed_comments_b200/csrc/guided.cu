@@ -79,17 +79,16 @@ __device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQu
         bool ok = !(check_levels && (oct < min_level || (max_level >= 0 && oct > max_level)));
         const float dx = __uint_as_float(it.x) - x, dy = __uint_as_float(it.y) - y;
         ok = ok && fabsf(dx) < r && fabsf(dy) < r;
-        if (ok && F.claimed && F.claimed[idx]) ok = false;
-        if (ok && F.uright) {
-          const float ur = F.uright[idx];
-          if (ur > 0.f && fabsf(q.ur - ur) > r) ok = false;
-        }
-        if (ok) {
+        if (ok) {   // the three per-keypoint loads are independent of each other: issue them together
+          const uint8_t cl = F.claimed ? F.claimed[idx] : (uint8_t)0;
+          const float ur = F.uright ? F.uright[idx] : -1.f;
           const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
           const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
                            __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
-          hi = ((unsigned)dist << 18) | (unsigned)e;
-          lo = ((unsigned)(oct & 0xff) << 18) | (unsigned)idx;
+          if (!cl && !(ur > 0.f && fabsf(q.ur - ur) > r)) {
+            hi = ((unsigned)dist << 18) | (unsigned)e;
+            lo = ((unsigned)(oct & 0xff) << 18) | (unsigned)idx;
+          }
         }
       }
       emit(hi, lo);

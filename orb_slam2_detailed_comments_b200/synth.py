@@ -105,7 +105,8 @@ def synth_guided_case(seed, n=600, m=500, w=752, h=480, radius=12.0, levels=8, d
     c = centres[rng.integers(0, len(centres), n)]
     k["x"] = np.round(c[:, 0] + rng.normal(0, 14, n)).astype(np.float32)   # extractor output sits on (scaled) integer pixels
     k["y"] = np.round(c[:, 1] + rng.normal(0, 14, n)).astype(np.float32)
-    k["octave"] = rng.integers(0, levels, n)
+    pl = (1.0 / 1.2) ** np.arange(levels)   # keypoints per level fall off like mnFeaturesPerLevel (src/ORBextractor.cc:809-826)
+    k["octave"] = rng.choice(levels, n, p=pl / pl.sum())
     k["angle"] = rng.uniform(0, 360, n).astype(np.float32)
     k["size"], k["response"], k["class_id"] = 31, 50, -1
     desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
