@@ -106,4 +106,13 @@ int ORBmatcher::SearchByProjection(const TargetFrame& F, const std::vector<Proje
   return nmatches;
 }
 
+void ORBmatcher::ComputeDistinctiveDescriptors(const cv::Mat& observations, const std::vector<int64_t>& offsets, std::vector<int>& bestIdx) {
+  const int points = (int)offsets.size() - 1;
+  bestIdx.assign(points > 0 ? points : 0, -1);
+  if (points <= 0) return;
+  std::vector<uint8_t> tmp;
+  const uint8_t* d = observations.rows > 0 ? rows32(observations, tmp) : nullptr;
+  check(orb_distinctive_descriptors(ORB_MEM_HOST, d, offsets.data(), points, bestIdx.data(), nullptr, nullptr), "orb_distinctive_descriptors");
+}
+
 }  // namespace ORB_SLAM2

@@ -66,6 +66,11 @@ class ORBmatcher {
   int SearchByProjection(const TargetFrame& F, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors, int th,
                          bool useRatio, std::vector<int>& assigned, std::vector<int>* pointMatch = nullptr) const;
 
+  // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) for many map points in one call: rows
+  // [offsets[p], offsets[p+1]) of `observations` (total x 32 CV_8U) are point p's descriptors in the reference's map order;
+  // bestIdx[p] = the row (relative to offsets[p]) the reference would clone into mDescriptor, -1 for a point without rows.
+  static void ComputeDistinctiveDescriptors(const cv::Mat& observations, const std::vector<int64_t>& offsets, std::vector<int>& bestIdx);
+
   static const int TH_LOW;        // 50
   static const int TH_HIGH;       // 100
   static const int HISTO_LENGTH;  // 30

@@ -183,6 +183,18 @@ int main(int argc, char** argv) {
         std::printf("SearchByProjection (%s): %d matches, assignment bit-exact vs oracle\n", form ? "local-map form" : "frame-to-frame form", nm);
       }
     }
+    // distinctive descriptors: groups of consecutive left descriptors stand in for the observations of map points
+    {
+      std::vector<int64_t> off{0};
+      for (int n = 1; off.back() + n <= bd[0].rows && n <= 40; ++n) off.push_back(off.back() + n);
+      cv::Mat obs((int)off.back(), 32, CV_8U, bd[0].ptr<unsigned char>(0));
+      std::vector<int> best;
+      ORB_SLAM2::ORBmatcher::ComputeDistinctiveDescriptors(obs, off, best);
+      std::vector<int32_t> want(off.size() - 1);
+      orb_oracle_distinctive_descriptors(obs.ptr<unsigned char>(0), off.data(), (int)want.size(), want.data(), nullptr, 2);
+      REQUIRE(best.size() == want.size() && std::memcmp(best.data(), want.data(), want.size() * 4) == 0, "ComputeDistinctiveDescriptors differs from the oracle");
+      std::printf("ComputeDistinctiveDescriptors: %zu map points exact vs oracle\n", want.size());
+    }
     std::printf("ORBmatcher: kNN over %d x %d bit-exact, %d ratio-test accepts, DescriptorDistance x %d exact\n", bd[0].rows, bd[1].rows, nacc, m);
   }
   orb_oracle_destroy(oe);

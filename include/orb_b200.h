@@ -16,6 +16,7 @@
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
+ *   orb_distinctive_descriptors <- MapPoint::ComputeDistinctiveDescriptors, batched over map points   src/MapPoint.cc:424-517
  *   orb_search_by_projection  <- the guided matchers' core: Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
  *                                (src/Frame.cc:432-460, 729-745, 633-717), the candidate scan with sequential claims of
  *                                ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) (src/ORBmatcher.cc:69-184) and
@@ -208,6 +209,15 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
 double orb_measure_popc_peak(int device);
+
+/* ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) ----------------------------
+ * For every map point p < points with the descriptors desc[offsets[p] .. offsets[p+1]) of its observations (N_p rows, in
+ * the order the reference's std::map<KeyFrame*, size_t> walk pushes them): all-pairs DescriptorDistance, per row the
+ * median = element (int)(0.5 * (N_p - 1)) of the sorted row (the zero self-distance included), best = the first row with
+ * the smallest median (strict <). best_idx[p] = that row (relative to offsets[p]; -1 for N_p == 0), best_median[p]
+ * (optional) its median. All arrays in `mem` memory; offsets has points + 1 entries. */
+int orb_distinctive_descriptors(int mem, const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,
+                                int32_t* best_median, void* stream);
 
 #ifdef __cplusplus
 }

@@ -249,3 +249,17 @@ def features_in_area(kps_un, bounds, x, y, r, min_level=-1, max_level=-1):
     out = np.empty(max(len(kps_un), 1), np.int32)
     n = L.orb_oracle_features_in_area(_p(kps_un), len(kps_un), C.byref(prm), x, y, r, min_level, max_level, _p(out))
     return out[:n].copy()
+
+
+def distinctive_descriptors(desc, offsets, nthreads=1):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517), batched. Returns (best_idx, best_median)."""
+    L = lib()
+    L.orb_oracle_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    L.orb_oracle_distinctive_descriptors.restype = None
+    desc = np.ascontiguousarray(desc, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    P = len(offsets) - 1
+    bi, bm = np.empty(max(P, 1), np.int32), np.empty(max(P, 1), np.int32)
+    if P > 0:
+        L.orb_oracle_distinctive_descriptors(_p(desc), _p(offsets), P, _p(bi), _p(bm), nthreads)
+    return bi[:P], bm[:P]

@@ -734,6 +734,39 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
   return nmatches;
 }
 
+void orb_oracle_distinctive_descriptors(const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,
+                                        int32_t* best_median, int nthreads) {
+  auto work = [&](int p0, int p1) {
+    std::vector<std::vector<float>> D;
+    for (int p = p0; p < p1; ++p) {
+      const uint8_t* d = desc + offsets[p] * 32;
+      const size_t N = (size_t)(offsets[p + 1] - offsets[p]);
+      if (N == 0) { best_idx[p] = -1; if (best_median) best_median[p] = -1; continue; }   // "observations.empty() -> return" (:434-435)
+      D.assign(N, std::vector<float>(N, 0));   // the reference keeps the distances as float (:455-456)
+      for (size_t i = 0; i < N; ++i) {
+        D[i][i] = 0;
+        for (size_t j = i + 1; j < N; ++j) {
+          const int dij = orb_oracle_descriptor_distance(d + i * 32, d + j * 32);
+          D[i][j] = dij; D[j][i] = dij;
+        }
+      }
+      int best_med = INT_MAX, best = 0;   // :474-475
+      for (size_t i = 0; i < N; ++i) {
+        std::vector<int> v(D[i].begin(), D[i].end());
+        std::sort(v.begin(), v.end());
+        const int median = v[0.5 * (N - 1)];   // :483
+        if (median < best_med) { best_med = median; best = (int)i; }
+      }
+      best_idx[p] = best;
+      if (best_median) best_median[p] = best_med;
+    }
+  };
+  nthreads = std::max(1, std::min(nthreads, points));
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; ++t) th.emplace_back(work, (int)((int64_t)points * t / nthreads), (int)((int64_t)points * (t + 1) / nthreads));
+  for (auto& t : th) t.join();
+}
+
 int64_t orb_oracle_extract_many(int nf, float sf, int nl, int ini, int mn, int flags, const uint8_t* frames, int width,
                                 int height, int n, int nthreads) {
   nthreads = std::max(1, std::min(nthreads, n));

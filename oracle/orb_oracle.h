@@ -114,6 +114,11 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* 
 int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const orb_oracle_search_params* prm, float x, float y, float r,
                                 int min_level, int max_level, int32_t* out);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) for `points` map points; desc rows
+ * [offsets[p], offsets[p+1]) are the observations of point p. best_idx -1 for a point without observations. */
+void orb_oracle_distinctive_descriptors(const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,
+                                        int32_t* best_median, int nthreads);
+
 /* Multi-threaded extraction over frames, one extractor per thread (bench cpu baseline).
  * Returns total keypoints. frames: n contiguous w*h images. */
 int64_t orb_oracle_extract_many(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th, int flags,

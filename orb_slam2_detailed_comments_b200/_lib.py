@@ -37,7 +37,7 @@ SYMBOLS = [
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
-    "orb_search_by_projection",
+    "orb_search_by_projection", "orb_distinctive_descriptors",
 ]
 
 
@@ -100,6 +100,7 @@ def lib():
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
     L.orb_matcher_launch_count.restype = i64
+    L.orb_distinctive_descriptors.argtypes = [i32, vp, vp, i32, vp, vp, vp]
     L.orb_search_by_projection.argtypes = [i32, vp, vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]
     L.orb_measure_popc_peak.argtypes = [i32]
     L.orb_measure_popc_peak.restype = C.c_double

@@ -146,6 +146,66 @@ __global__ void orb_popc_peak_kernel(unsigned* out, int iters, unsigned seed) {
   if (s == 0xdeadbeefu) out[0] = s;
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517): one warp per map point. For row i the lanes stride over
+// the N descriptors, histogram the distances (0..256) in shared memory, and the median = element (int)(0.5 * (N - 1)) of the
+// sorted row is read off the histogram's prefix sums; best row = min over (median << 22 | i).
+#define DISTINCT_WARPS 8
+__global__ void __launch_bounds__(DISTINCT_WARPS * 32)
+orb_distinctive_kernel(const uint4* __restrict__ desc, const long long* __restrict__ offsets, int points, int* __restrict__ best_idx,
+                       int* __restrict__ best_median) {
+  __shared__ int s_hist[DISTINCT_WARPS][288];   // 257 bins, padded to 9 per lane
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x * DISTINCT_WARPS + w;
+  if (p >= points) return;
+  const long long o0 = offsets[p];
+  const int n = (int)(offsets[p + 1] - o0);
+  const uint4* d = desc + 2 * o0;
+  int* hist = s_hist[w];
+  const int k = (int)(0.5 * (n - 1));   // vDists[0.5 * (N - 1)]
+  unsigned best = 0xffffffffu;
+  for (int i = 0; i < n; ++i) {
+#pragma unroll
+    for (int b = 0; b < 9; ++b) hist[lane * 9 + b] = 0;
+    __syncwarp();
+    const uint4 a0 = d[2 * i], a1 = d[2 * i + 1];
+    for (int j = lane; j < n; j += 32) {
+      const uint4 b0 = d[2 * j], b1 = d[2 * j + 1];
+      const int dist = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                       __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+      atomicAdd(&hist[dist], 1);
+    }
+    __syncwarp();
+    int c[9], sum = 0;
+#pragma unroll
+    for (int b = 0; b < 9; ++b) { c[b] = hist[lane * 9 + b]; sum += c[b]; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    // the lane whose bins contain rank k (first lane with inclusive count > k)
+    const unsigned has = __ballot_sync(0xffffffffu, incl > k);
+    const int src = __ffs(has) - 1;
+    int median = 0;
+    if (lane == src) {
+      int run = incl - sum;
+#pragma unroll
+      for (int b = 0; b < 9; ++b) {
+        run += c[b];
+        if (run > k) { median = lane * 9 + b; break; }
+      }
+    }
+    median = __shfl_sync(0xffffffffu, median, src);
+    best = min(best, ((unsigned)median << 22) | (unsigned)i);   // strict <: the first row with the smallest median wins
+    __syncwarp();
+  }
+  if (lane == 0) {
+    best_idx[p] = n > 0 ? (int)(best & 0x3fffffu) : -1;
+    if (best_median) best_median[p] = n > 0 ? (int)(best >> 22) : -1;
+  }
+}
+
 static std::atomic<long long> g_knn_launches{0};   // the kNN entry points are callable from any thread
 long long orb_knn_launches() { return g_knn_launches.load(std::memory_order_relaxed); }
 void orb_knn_count_launches(long long n) { g_knn_launches += n; }
@@ -179,6 +239,12 @@ void orb_launch_knn_merge_shards(const OrbKnn2* shards, int nshards, int Q, int 
 
 void orb_launch_distance_batch(const uint8_t* a, const uint8_t* b, long long n, int* out, cudaStream_t st) {
   orb_distance_batch_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint4*)a, (const uint4*)b, n, out);
+  ++g_knn_launches;
+}
+
+void orb_launch_distinctive(const uint8_t* desc, const long long* offsets, int points, int* best_idx, int* best_median, cudaStream_t st) {
+  orb_distinctive_kernel<<<(points + DISTINCT_WARPS - 1) / DISTINCT_WARPS, DISTINCT_WARPS * 32, 0, st>>>((const uint4*)desc, offsets, points,
+                                                                                                   best_idx, best_median);
   ++g_knn_launches;
 }
 

@@ -29,6 +29,7 @@ void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaSt
 void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
+void orb_launch_distinctive(const uint8_t*, const long long*, int, int*, int*, cudaStream_t);
 void orb_launch_guided(const OrbKeypoint*, const uint8_t*, const float*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*,
                        int, int, float, float, float, float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
 double orb_popc_peak(int num_sms);
@@ -850,6 +851,43 @@ int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, 
 }
 
 int64_t orb_matcher_launch_count(void) { return orb_knn_launches(); }
+
+int orb_distinctive_descriptors(int mem, const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,
+                                int32_t* best_median, void* stream) {
+  if (!offsets || !best_idx || points < 0) return fail(ORB_E_BADARG, "bad argument");
+  if (points == 0) return ORB_OK;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const bool host = mem != ORB_MEM_DEVICE;
+  if (!host) {
+    if (!desc || ((uintptr_t)desc & 15)) return fail(ORB_E_BADARG, "descriptor array must be 16-byte aligned device memory");
+    orb_launch_distinctive(desc, (const long long*)offsets, points, best_idx, best_median, st);
+    CU(cudaGetLastError());
+    return ORB_OK;
+  }
+  const int64_t total = offsets[points];
+  if (offsets[0] != 0 || total < 0 || (total > 0 && !desc)) return fail(ORB_E_BADARG, "offsets must start at 0 and be ascending");
+  for (int p = 0; p < points; ++p)
+    if (offsets[p + 1] < offsets[p] || offsets[p + 1] - offsets[p] >= (1 << 22)) return fail(ORB_E_BADARG, "offsets not ascending / more than 2^22 observations");
+  if ((rc = ws->db.ensure((size_t)std::max<int64_t>(total, 1) * 32)) != ORB_OK) return rc;
+  if ((rc = ws->q.ensure((size_t)(points + 1) * sizeof(int64_t))) != ORB_OK) return rc;
+  if ((rc = ws->out.ensure((size_t)points * 2 * sizeof(int))) != ORB_OK) return rc;
+  if (total > 0) CU(cudaMemcpyAsync(ws->db.p, desc, (size_t)total * 32, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(ws->q.p, offsets, (size_t)(points + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  int* d_idx = ws->out.as<int>();
+  int* d_med = d_idx + points;
+  orb_launch_distinctive(ws->db.as<uint8_t>(), ws->q.as<long long>(), points, d_idx, d_med, st);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(best_idx, d_idx, (size_t)points * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (best_median) CU(cudaMemcpyAsync(best_median, d_med, (size_t)points * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return ORB_OK;
+}
 
 int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
                              const int32_t* n_kps, int cap, const orb_proj_query* queries, const uint8_t* qdesc,

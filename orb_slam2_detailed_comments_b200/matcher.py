@@ -167,3 +167,14 @@ class ORBmatcher:
                                                   None if cl is None else _vp(cl), _vp(nk), cap, _vp(arrs[2]), _vp(arrs[3]), _vp(nq),
                                                   qcap, F, C.byref(prm), _vp(assigned), _vp(qmatch), _vp(nm), None))
         return assigned, qmatch, nm
+
+    @staticmethod
+    def ComputeDistinctiveDescriptors(desc: np.ndarray, offsets: np.ndarray):
+        """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) for many map points at once: desc rows
+        [offsets[p], offsets[p+1]) are the observations of point p. Returns (best_idx [P] relative row or -1, best_median [P])."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        P = len(offsets) - 1
+        bi, bm = np.empty(max(P, 1), np.int32), np.empty(max(P, 1), np.int32)
+        check(_lib.lib().orb_distinctive_descriptors(MEM_HOST, _vp(desc) if len(desc) else None, _vp(offsets), P, _vp(bi), _vp(bm), None))
+        return bi[:P], bm[:P]
