@@ -9,6 +9,7 @@
 #include "../oracle/orb_oracle.h"
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ORBVocabulary.h"
 
 #define REQUIRE(cond, ...)                      \
   do {                                          \
@@ -194,6 +195,58 @@ int main(int argc, char** argv) {
       orb_oracle_distinctive_descriptors(obs.ptr<unsigned char>(0), off.data(), (int)want.size(), want.data(), nullptr, 2);
       REQUIRE(best.size() == want.size() && std::memcmp(best.data(), want.data(), want.size() * 4) == 0, "ComputeDistinctiveDescriptors differs from the oracle");
       std::printf("ComputeDistinctiveDescriptors: %zu map points exact vs oracle\n", want.size());
+    }
+    // ComputeBoW: a random k = 8, L = 3 vocabulary whose nodes are drawn from the frame's own descriptors
+    {
+      const int k = 8, L = 3;
+      std::vector<int> parent(1, 0);
+      std::vector<unsigned char> leaf(1, 0), vd(32, 0);
+      std::vector<double> weight(1, 0.0);
+      unsigned lcg = 12345u;
+      auto rnd = [&]() { lcg = lcg * 1664525u + 1013904223u; return lcg >> 8; };
+      std::vector<int> frontier(1, 0);
+      for (int lvl = 1; lvl <= L; ++lvl) {
+        std::vector<int> next;
+        for (int pid : frontier)
+          for (int c = 0; c < k; ++c) {
+            const int nid = (int)parent.size();
+            parent.push_back(pid);
+            leaf.push_back(lvl == L);
+            const unsigned char* src = bd[1].ptr<unsigned char>((int)(rnd() % (unsigned)bd[1].rows));
+            vd.insert(vd.end(), src, src + 32);
+            weight.push_back(lvl == L ? ((rnd() % 19u) == 0 ? 0.0 : 0.25 + (double)(rnd() % 1000u) / 137.0) : 0.0);
+            next.push_back(nid);
+          }
+        frontier.swap(next);
+      }
+      ORB_SLAM2::ORBVocabulary voc;
+      voc.create(k, L, parent, leaf, vd, weight);
+      orb_oracle_vocabulary* ov = orb_oracle_vocabulary_create(k, L, (int)parent.size(), parent.data(), leaf.data(), vd.data(), weight.data());
+      REQUIRE((int)voc.size() == k * k * k, "vocabulary size %u", voc.size());
+      ORB_SLAM2::ORBVocabulary::BowVector bow;
+      ORB_SLAM2::ORBVocabulary::FeatureVector fv;
+      std::vector<cv::Mat> rows;
+      for (int r = 0; r < bd[0].rows; ++r) rows.push_back(bd[0].row(r));   // Converter::toDescriptorVector
+      voc.transform(rows, bow, fv, 2);
+      const int n = bd[0].rows;
+      std::vector<int32_t> bw(n), fn(n), fs(n + 1), ff(n);
+      std::vector<double> bv(n);
+      int32_t bc = 0, fc = 0;
+      orb_oracle_bow_transform(ov, bd[0].ptr<unsigned char>(0), n, 2, nullptr, nullptr, bw.data(), bv.data(), &bc, fn.data(), fs.data(), ff.data(), &fc);
+      REQUIRE((int)bow.size() == bc && (int)fv.size() == fc && bc > 20, "BowVector / FeatureVector sizes %zu / %zu vs oracle %d / %d", bow.size(), fv.size(), bc, fc);
+      int i = 0;
+      for (const auto& e : bow) {
+        REQUIRE((int)e.first == bw[i] && std::memcmp(&e.second, &bv[i], 8) == 0, "BowVector entry %d differs from the oracle", i);
+        ++i;
+      }
+      i = 0;
+      for (const auto& e : fv) {
+        REQUIRE((int)e.first == fn[i] && (int)e.second.size() == fs[i + 1] - fs[i] &&
+                    std::memcmp(e.second.data(), &ff[fs[i]], e.second.size() * 4) == 0, "FeatureVector node %d differs from the oracle", i);
+        ++i;
+      }
+      orb_oracle_vocabulary_destroy(ov);
+      std::printf("ORBVocabulary::transform: %d words, %d nodes, doubles bit-exact vs oracle\n", bc, fc);
     }
     std::printf("ORBmatcher: kNN over %d x %d bit-exact, %d ratio-test accepts, DescriptorDistance x %d exact\n", bd[0].rows, bd[1].rows, nacc, m);
   }

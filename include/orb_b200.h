@@ -16,6 +16,8 @@
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
+ *   orb_vocabulary_*, orb_bow_transform <- Frame::ComputeBoW = DBoW2 TemplatedVocabulary::transform   src/Frame.cc:750-765,
+ *                                Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280
  *   orb_distinctive_descriptors <- MapPoint::ComputeDistinctiveDescriptors, batched over map points   src/MapPoint.cc:424-517
  *   orb_search_by_projection  <- the guided matchers' core: Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
  *                                (src/Frame.cc:432-460, 729-745, 633-717), the candidate scan with sequential claims of
@@ -209,6 +211,28 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
 double orb_measure_popc_peak(int device);
+
+/* ---- Frame::ComputeBoW (src/Frame.cc:750-765) --------------------------------------------------------
+ * = DBoW2 TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280) for the ORB vocabulary's configuration
+ * (TF_IDF weighting, L1_NORM scoring: ORBvoc.txt header "10 6 0 0").
+ * orb_vocabulary_create takes the node table exactly as loadFromTextFile reads it (TemplatedVocabulary.h:1330-1420):
+ * node 0 is the root; for node i in 1..n_nodes-1 (file line order) parent[i], is_leaf[i], desc[i][32], weight[i]
+ * (entry 0 of every array is ignored). Children keep file order, word ids are assigned to leaves in file order. */
+typedef struct orb_vocabulary orb_vocabulary;
+int orb_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc,
+                          const double* weight, int device, orb_vocabulary** out);
+void orb_vocabulary_destroy(orb_vocabulary* v);
+int orb_vocabulary_words(const orb_vocabulary* v);   /* number of leaves = vocabulary size */
+/* transform() for `frames` descriptor sets desc [frames][cap][32], n [frames] rows used. Per feature: word [frames][cap] (word id) and
+ * node [frames][cap] (ancestor at level L - levelsup; 0 = root when levelsup >= L), also for stopped words (weight 0).
+ * BowVector per frame: bow_count[f] entries (bow_word ascending, bow_value L1-normalised doubles) in [frames][cap] arrays.
+ * FeatureVector per frame as CSR: fv_count[f] nodes (fv_node ascending), features of node j =
+ * fv_feature[f][fv_start[f][j] .. fv_start[f][j+1]) ascending; fv_start is [frames][cap + 1]. All arrays in `mem` memory;
+ * cap <= 16384. Results equal the reference's std::map contents bit for bit (doubles included). */
+int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int32_t* n, int cap, int frames, int levelsup, int32_t* word,
+                      int32_t* node, int32_t* bow_word, double* bow_value, int32_t* bow_count, int32_t* fv_node, int32_t* fv_start,
+                      int32_t* fv_feature, int32_t* fv_count, void* stream);
 
 /* ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) ----------------------------
  * For every map point p < points with the descriptors desc[offsets[p] .. offsets[p+1]) of its observations (N_p rows, in

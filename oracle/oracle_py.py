@@ -263,3 +263,37 @@ def distinctive_descriptors(desc, offsets, nthreads=1):
     if P > 0:
         L.orb_oracle_distinctive_descriptors(_p(desc), _p(offsets), P, _p(bi), _p(bm), nthreads)
     return bi[:P], bm[:P]
+
+
+class OracleVocabulary:
+    """DBoW2 vocabulary restatement (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) — transform() for one descriptor set."""
+
+    def __init__(self, k, L, parent, is_leaf, desc, weight):
+        L_ = lib()
+        L_.orb_oracle_vocabulary_create.restype = C.c_void_p
+        L_.orb_oracle_vocabulary_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L_.orb_oracle_vocabulary_destroy.argtypes = [C.c_void_p]
+        L_.orb_oracle_vocabulary_destroy.restype = None
+        L_.orb_oracle_bow_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 9
+        L_.orb_oracle_bow_transform.restype = None
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8); weight = np.ascontiguousarray(weight, np.float64)
+        self.h = C.c_void_p(L_.orb_oracle_vocabulary_create(k, L, len(parent), _p(parent), _p(is_leaf), _p(desc), _p(weight)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orb_oracle_vocabulary_destroy(self.h)
+            self.h = None
+
+    def transform(self, desc, levelsup=4):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        m = max(n, 1)
+        word, node = np.empty(m, np.int32), np.empty(m, np.int32)
+        bw, bv, bc = np.empty(m, np.int32), np.empty(m, np.float64), np.zeros(1, np.int32)
+        fn, fs, ff, fc = np.empty(m, np.int32), np.empty(m + 1, np.int32), np.empty(m, np.int32), np.zeros(1, np.int32)
+        lib().orb_oracle_bow_transform(self.h, _p(desc), n, levelsup, _p(word), _p(node), _p(bw), _p(bv), _p(bc), _p(fn), _p(fs), _p(ff), _p(fc))
+        b, f = int(bc[0]), int(fc[0])
+        bow = {int(w): float(v) for w, v in zip(bw[:b], bv[:b])}
+        fv = {int(fn[j]): ff[fs[j]:fs[j + 1]].tolist() for j in range(f)}
+        return word[:n], node[:n], bow, fv

@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstring>
 #include <list>
+#include <map>
 #include <thread>
 #include <utility>
 #include <vector>
@@ -732,6 +733,90 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
     }
   }
   return nmatches;
+}
+
+// ---- DBoW2 vocabulary transform ----------------------------------------------------------------------------------------------
+struct orb_oracle_vocabulary {
+  struct Node {   // TemplatedVocabulary::Node (TemplatedVocabulary.h:270-310)
+    int parent = 0;
+    std::vector<int> children;
+    uint8_t descriptor[32] = {0};
+    double weight = 0;
+    int word_id = -1;
+    bool is_leaf() const { return children.empty(); }
+  };
+  int k, L;
+  std::vector<Node> nodes;
+  int n_words = 0;
+};
+
+orb_oracle_vocabulary* orb_oracle_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf,
+                                                    const uint8_t* desc, const double* weight) {
+  auto* v = new orb_oracle_vocabulary;
+  v->k = k; v->L = L;
+  v->nodes.resize(n_nodes);
+  for (int nid = 1; nid < n_nodes; ++nid) {   // loadFromTextFile (TemplatedVocabulary.h:1380-1420): one node per line, ids in line order
+    auto& nd = v->nodes[nid];
+    nd.parent = parent[nid];
+    v->nodes[parent[nid]].children.push_back(nid);
+    std::memcpy(nd.descriptor, desc + (size_t)nid * 32, 32);
+    nd.weight = weight[nid];
+    if (is_leaf[nid]) nd.word_id = v->n_words++;
+  }
+  return v;
+}
+void orb_oracle_vocabulary_destroy(orb_oracle_vocabulary* v) { delete v; }
+
+void orb_oracle_bow_transform(const orb_oracle_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* word, int32_t* node,
+                              int32_t* bow_word, double* bow_value, int32_t* bow_count, int32_t* fv_node, int32_t* fv_start,
+                              int32_t* fv_feature, int32_t* fv_count) {
+  std::map<unsigned, double> bow;                       // BowVector
+  std::map<unsigned, std::vector<unsigned>> fv;         // FeatureVector
+  for (int i = 0; i < n; ++i) {
+    // transform(feature, word_id, weight, nid, levelsup) (TemplatedVocabulary.h:1240-1280)
+    const uint8_t* f = desc + (size_t)i * 32;
+    const int nid_level = v->L - levelsup;
+    int nid = 0, final_id = 0, current_level = 0;
+    do {
+      ++current_level;
+      const std::vector<int>& ch = v->nodes[final_id].children;
+      final_id = ch[0];
+      double best_d = orb_oracle_descriptor_distance(f, v->nodes[final_id].descriptor);
+      for (size_t c = 1; c < ch.size(); ++c) {
+        const double d = orb_oracle_descriptor_distance(f, v->nodes[ch[c]].descriptor);
+        if (d < best_d) { best_d = d; final_id = ch[c]; }
+      }
+      if (current_level == nid_level) nid = final_id;
+    } while (!v->nodes[final_id].is_leaf());
+    const int wid = v->nodes[final_id].word_id;
+    const double w = v->nodes[final_id].weight;
+    if (word) word[i] = wid;
+    if (node) node[i] = nid;
+    if (w > 0) {   // not stopped (:1163)
+      auto it = bow.lower_bound(wid);   // BowVector::addWeight
+      if (it != bow.end() && !(bow.key_comp()(wid, it->first))) it->second += w;
+      else bow.insert(it, {(unsigned)wid, w});
+      fv[nid].push_back(i);             // FeatureVector::addFeature
+    }
+  }
+  // TF_IDF with L1 scoring: mustNormalize -> v.normalize(L1) (BowVector.cpp)
+  double norm = 0.0;
+  for (auto& e : bow) norm += std::fabs(e.second);
+  if (norm > 0.0)
+    for (auto& e : bow) e.second /= norm;
+  int c = 0;
+  for (auto& e : bow) { bow_word[c] = (int)e.first; bow_value[c] = e.second; ++c; }
+  *bow_count = c;
+  c = 0;
+  int pos = 0;
+  for (auto& e : fv) {
+    fv_node[c] = (int)e.first;
+    fv_start[c] = pos;
+    for (unsigned i : e.second) fv_feature[pos++] = (int)i;
+    ++c;
+  }
+  fv_start[c] = pos;
+  *fv_count = c;
 }
 
 void orb_oracle_distinctive_descriptors(const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,

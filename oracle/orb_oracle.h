@@ -114,6 +114,19 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* 
 int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const orb_oracle_search_params* prm, float x, float y, float r,
                                 int min_level, int max_level, int32_t* out);
 
+/* Frame::ComputeBoW (src/Frame.cc:750-765) = DBoW2 TemplatedVocabulary::transform(features, BowVector, FeatureVector, levelsup)
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280; BowVector.cpp; FeatureVector.cpp) with TF_IDF + L1_NORM.
+ * Vocabulary node table as loadFromTextFile reads it (node 0 = root, entries 0 ignored). One descriptor set per call. Outputs as
+ * include/orb_b200.h: word/node [n]; bow_word/bow_value [<= n] with *bow_count; fv_node [<= n], fv_start [<= n + 1], fv_feature [<= n]
+ * with *fv_count. */
+typedef struct orb_oracle_vocabulary orb_oracle_vocabulary;
+orb_oracle_vocabulary* orb_oracle_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf,
+                                                    const uint8_t* desc, const double* weight);
+void orb_oracle_vocabulary_destroy(orb_oracle_vocabulary* v);
+void orb_oracle_bow_transform(const orb_oracle_vocabulary* v, const uint8_t* desc, int n, int levelsup, int32_t* word, int32_t* node,
+                              int32_t* bow_word, double* bow_value, int32_t* bow_count, int32_t* fv_node, int32_t* fv_start,
+                              int32_t* fv_feature, int32_t* fv_count);
+
 /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) for `points` map points; desc rows
  * [offsets[p], offsets[p+1]) are the observations of point p. best_idx -1 for a point without observations. */
 void orb_oracle_distinctive_descriptors(const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,

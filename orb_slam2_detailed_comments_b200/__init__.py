@@ -9,3 +9,4 @@ There is no CPU fallback; the CUDA library must be built (`__graft_entry__.build
 from ._lib import KNN_DTYPE, KP_DTYPE, OrbError, build, lib  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import ORBmatcher, hamming_knn, hamming_knn_sharded  # noqa: F401
+from .vocabulary import ORBVocabulary  # noqa: F401

@@ -38,6 +38,7 @@ SYMBOLS = [
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
     "orb_search_by_projection", "orb_distinctive_descriptors",
+    "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_words", "orb_bow_transform",
 ]
 
 

@@ -29,6 +29,13 @@ void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaSt
 void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
+struct BowVoc {   // == bow.cu
+  const int* child_start; const int* child_id; const uint4* child_desc; const uint8_t* is_leaf; const int* word_of; const double* word_weight;
+  int L;
+};
+void orb_launch_bow(const BowVoc&, int, const uint8_t*, const int*, int, int, int*, int*, int*, double*, int*, int*, int*, int*, int*,
+                    cudaStream_t, long long*);
+
 void orb_launch_distinctive(const uint8_t*, const long long*, int, int*, int*, cudaStream_t);
 void orb_launch_guided(const OrbKeypoint*, const uint8_t*, const float*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*,
                        int, int, float, float, float, float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
@@ -851,6 +858,128 @@ int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, 
 }
 
 int64_t orb_matcher_launch_count(void) { return orb_knn_launches(); }
+
+// ---- vocabulary / ComputeBoW ------------------------------------------------------------------------------------------------
+
+struct orb_vocabulary {
+  int device = 0, k = 0, L = 0, n_nodes = 0, n_words = 0;
+  DevBuf child_start, child_id, child_desc, is_leaf, word_of, word_weight;
+  DevBuf s_desc, s_n, s_word, s_node, s_bw, s_bv, s_bc, s_fn, s_fs, s_ff, s_fc;   // staging for host-memory calls
+  std::mutex mu;
+};
+
+int orb_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc,
+                          const double* weight, int device, orb_vocabulary** out) {
+  if (!out) return fail(ORB_E_BADARG, "null argument");
+  *out = nullptr;
+  if (!parent || !is_leaf || !desc || !weight || k < 1 || L < 1 || n_nodes < 2) return fail(ORB_E_BADARG, "bad vocabulary arguments");
+  std::vector<int> cnt(n_nodes + 1, 0);
+  for (int i = 1; i < n_nodes; ++i) {
+    if (parent[i] < 0 || parent[i] >= n_nodes || parent[i] == i) return fail(ORB_E_BADARG, "node %d: parent %d out of range", i, parent[i]);
+    if (is_leaf[parent[i]] && parent[i] != 0) return fail(ORB_E_BADARG, "node %d hangs below leaf %d", i, parent[i]);
+    ++cnt[parent[i] + 1];
+  }
+  for (int i = 1; i < n_nodes; ++i)
+    if (!is_leaf[i] && cnt[i + 1] == 0) return fail(ORB_E_BADARG, "inner node %d has no children", i);
+  if (cnt[1] == 0) return fail(ORB_E_BADARG, "root has no children");
+  std::vector<int> start(n_nodes + 1, 0);
+  for (int i = 0; i < n_nodes; ++i) start[i + 1] = start[i] + cnt[i + 1];
+  const int slots = start[n_nodes];   // == n_nodes - 1
+  std::vector<int> cursor(start.begin(), start.end() - 1), child_id(slots), word_of(n_nodes, -1);
+  std::vector<uint8_t> child_desc((size_t)slots * 32), leaf(n_nodes, 0);
+  std::vector<double> word_weight;
+  for (int i = 1; i < n_nodes; ++i) {   // file order: children in push_back order, words numbered as the leaves appear
+    const int s = cursor[parent[i]]++;
+    child_id[s] = i;
+    memcpy(&child_desc[(size_t)s * 32], desc + (size_t)i * 32, 32);
+    leaf[i] = is_leaf[i] ? 1 : 0;
+    if (leaf[i]) { word_of[i] = (int)word_weight.size(); word_weight.push_back(weight[i]); }
+  }
+  // a walk deeper than n_nodes levels would mean a cycle; parents precede nothing in particular, so check by depth
+  for (int i = 1; i < n_nodes; ++i) {
+    int d = 0, p = i;
+    while (p != 0 && d <= n_nodes) { p = parent[p]; ++d; }
+    if (p != 0) return fail(ORB_E_BADARG, "node %d is not connected to the root", i);
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  CU(cudaSetDevice(device));
+  orb_vocabulary* v = new orb_vocabulary;
+  v->device = device; v->k = k; v->L = L; v->n_nodes = n_nodes; v->n_words = (int)word_weight.size();
+  struct Up { DevBuf* b; const void* src; size_t bytes; } ups[] = {
+      {&v->child_start, start.data(), start.size() * sizeof(int)}, {&v->child_id, child_id.data(), child_id.size() * sizeof(int)},
+      {&v->child_desc, child_desc.data(), child_desc.size()},      {&v->is_leaf, leaf.data(), leaf.size()},
+      {&v->word_of, word_of.data(), word_of.size() * sizeof(int)}, {&v->word_weight, word_weight.data(), word_weight.size() * sizeof(double)}};
+  for (const Up& u : ups) {
+    int rc = u.b->ensure(std::max<size_t>(u.bytes, 16));
+    if (rc == ORB_OK && cudaMemcpy(u.b->p, u.src, u.bytes, cudaMemcpyHostToDevice) != cudaSuccess) rc = fail(ORB_E_CUDA, "vocabulary upload failed");
+    if (rc != ORB_OK) { orb_vocabulary_destroy(v); return rc; }
+  }
+  *out = v;
+  return ORB_OK;
+}
+
+void orb_vocabulary_destroy(orb_vocabulary* v) {
+  if (!v) return;
+  cudaSetDevice(v->device);
+  DevBuf* bufs[] = {&v->child_start, &v->child_id, &v->child_desc, &v->is_leaf, &v->word_of, &v->word_weight, &v->s_desc, &v->s_n, &v->s_word,
+                    &v->s_node, &v->s_bw, &v->s_bv, &v->s_bc, &v->s_fn, &v->s_fs, &v->s_ff, &v->s_fc};
+  for (DevBuf* b : bufs) b->release();
+  delete v;
+}
+
+int orb_vocabulary_words(const orb_vocabulary* v) { return v ? v->n_words : 0; }
+
+int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int32_t* n, int cap, int frames, int levelsup, int32_t* word,
+                      int32_t* node, int32_t* bow_word, double* bow_value, int32_t* bow_count, int32_t* fv_node, int32_t* fv_start,
+                      int32_t* fv_feature, int32_t* fv_count, void* stream) {
+  if (!v || !desc || !n || !bow_word || !bow_value || !bow_count || !fv_node || !fv_start || !fv_feature || !fv_count)
+    return fail(ORB_E_BADARG, "null argument");
+  if (cap <= 0 || cap > 16384 || frames <= 0 || levelsup < 0) return fail(ORB_E_BADARG, "bad size (0 < cap <= 16384, frames > 0, levelsup >= 0)");
+  std::lock_guard<std::mutex> lk(v->mu);
+  CU(cudaSetDevice(v->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t F = (size_t)frames;
+  const bool host = mem != ORB_MEM_DEVICE;
+  int rc;
+  const uint8_t* d_desc = desc; const int* d_n = n;
+  int *d_word = word, *d_node = node, *d_bw = bow_word, *d_bc = bow_count, *d_fn = fv_node, *d_fs = fv_start, *d_ff = fv_feature, *d_fc = fv_count;
+  double* d_bv = bow_value;
+  if (host) {
+    struct S { DevBuf* b; size_t bytes; } st_bufs[] = {{&v->s_desc, F * cap * 32}, {&v->s_n, F * 4}, {&v->s_bw, F * cap * 4}, {&v->s_bv, F * cap * 8},
+                                                      {&v->s_bc, F * 4}, {&v->s_fn, F * cap * 4}, {&v->s_fs, F * (cap + 1) * 4},
+                                                      {&v->s_ff, F * cap * 4}, {&v->s_fc, F * 4}};
+    for (const S& s : st_bufs) if ((rc = s.b->ensure(s.bytes)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(v->s_desc.p, desc, F * cap * 32, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(v->s_n.p, n, F * 4, cudaMemcpyHostToDevice, st));
+    d_desc = v->s_desc.as<uint8_t>(); d_n = v->s_n.as<int>();
+    d_bw = v->s_bw.as<int>(); d_bv = v->s_bv.as<double>(); d_bc = v->s_bc.as<int>();
+    d_fn = v->s_fn.as<int>(); d_fs = v->s_fs.as<int>(); d_ff = v->s_ff.as<int>(); d_fc = v->s_fc.as<int>();
+  } else if ((uintptr_t)desc & 15) {
+    return fail(ORB_E_BADARG, "descriptor array must be 16-byte aligned device memory");
+  }
+  if (host || !word) { if ((rc = v->s_word.ensure(F * cap * 4)) != ORB_OK) return rc; d_word = v->s_word.as<int>(); }
+  if (host || !node) { if ((rc = v->s_node.ensure(F * cap * 4)) != ORB_OK) return rc; d_node = v->s_node.as<int>(); }
+  BowVoc V{v->child_start.as<int>(), v->child_id.as<int>(), v->child_desc.as<uint4>(), v->is_leaf.as<uint8_t>(), v->word_of.as<int>(),
+           v->word_weight.as<double>(), v->L};
+  long long launched = 0;
+  orb_launch_bow(V, levelsup, d_desc, d_n, cap, frames, d_word, d_node, d_bw, d_bv, d_bc, d_fn, d_fs, d_ff, d_fc, st, &launched);
+  orb_knn_count_launches(launched);
+  CU(cudaGetLastError());
+  if (host) {
+    if (word) CU(cudaMemcpyAsync(word, d_word, F * cap * 4, cudaMemcpyDeviceToHost, st));
+    if (node) CU(cudaMemcpyAsync(node, d_node, F * cap * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(bow_word, d_bw, F * cap * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(bow_value, d_bv, F * cap * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(bow_count, d_bc, F * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(fv_node, d_fn, F * cap * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(fv_start, d_fs, F * (cap + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(fv_feature, d_ff, F * cap * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(fv_count, d_fc, F * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORB_OK;
+}
 
 int orb_distinctive_descriptors(int mem, const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,
                                 int32_t* best_median, void* stream) {

@@ -138,3 +138,31 @@ def synth_guided_case(seed, n=600, m=500, w=752, h=480, radius=12.0, levels=8, d
         q["ur"] = np.where(rng.random(m) < 0.8, ur[src] + rng.normal(0, 4, m), q["u"] - 300).astype(np.float32)
     claimed = (rng.random(n) < 0.1).astype(np.uint8)
     return dict(kps=k, desc=desc, queries=q, qdesc=qdesc, bounds=bounds or (0.0, 0.0, float(w), float(h)), uright=ur, claimed=claimed)
+
+
+def synth_vocabulary(k=10, L=3, seed=11, prune=0.05, stop=0.03):
+    """Random DBoW2-style vocabulary tree in the node-table form of ORBvoc.txt (breadth-first ids): children = noisy copies of
+    their parent (so descents are decided by few bits and ties occur), `prune` of the inner nodes end early as leaves or have
+    fewer than k children, `stop` of the words have weight 0 (stopped words). Returns (k, L, parent, is_leaf, desc, weight)."""
+    rng = np.random.default_rng(seed)
+    parent, is_leaf, desc, weight = [0], [0], [np.zeros(32, np.uint8)], [0.0]
+    frontier = [(0, 0, rng.integers(0, 256, 32, dtype=np.uint8))]   # (id, level, descriptor)
+    while frontier:
+        nxt = []
+        for pid, lvl, pd in frontier:
+            nch = k if rng.random() > prune else int(rng.integers(1, k + 1))
+            for c in range(nch):
+                d = pd.copy()
+                flips = rng.integers(0, 256, int(rng.integers(0, 64 >> lvl) + 1))
+                for b in flips:
+                    d[b >> 3] ^= np.uint8(1 << (b & 7))
+                if c > 0 and rng.random() < 0.03:
+                    d = desc[-1].copy()   # identical siblings: equal distances, the first child must win
+                nid = len(parent)
+                leaf = lvl + 1 == L or (lvl + 1 >= 2 and rng.random() < prune)
+                parent.append(pid); is_leaf.append(int(leaf)); desc.append(d)
+                weight.append(0.0 if (leaf and rng.random() < stop) else float(rng.uniform(0.1, 9.0)) if leaf else 0.0)
+                if not leaf:
+                    nxt.append((nid, lvl + 1, d))
+        frontier = nxt
+    return k, L, np.array(parent, np.int32), np.array(is_leaf, np.uint8), np.stack(desc), np.array(weight, np.float64)

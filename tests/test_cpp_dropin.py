@@ -25,6 +25,8 @@ def test_dropin_builds_and_exports_reference_symbols():
     for sym in ("ORB_SLAM2::ORBextractor::ORBextractor(int, float, int, int, int, int)",
                 "ORB_SLAM2::ORBextractor::operator()(cv::Mat const&, cv::Mat const&, std::vector<cv::KeyPoint",
                 "ORB_SLAM2::ORBmatcher::DescriptorDistance(cv::Mat const&, cv::Mat const&)",
+                "ORB_SLAM2::ORBmatcher::SearchByProjection(", "ORB_SLAM2::ORBmatcher::ComputeDistinctiveDescriptors(",
+                "ORB_SLAM2::ORBVocabulary::loadFromTextFile(", "ORB_SLAM2::ORBVocabulary::transform(",
                 "ORB_SLAM2::ORBmatcher::TH_LOW", "ORB_SLAM2::ORBmatcher::TH_HIGH", "ORB_SLAM2::ORBmatcher::HISTO_LENGTH"):
         assert sym in out, sym
     # the product layer must not link the oracle
@@ -48,3 +50,6 @@ def test_dropin_matches_oracle_on_gpu(tmp_path, shape):
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "PASS" in r.stdout
+    for part in ("operator():", "ExtractBatch:", "ExtractStereo:", "SearchByProjection (frame-to-frame form)", "SearchByProjection (local-map form)",
+                 "ComputeDistinctiveDescriptors:", "ORBVocabulary::transform:", "ORBmatcher: kNN"):
+        assert part in r.stdout, part
