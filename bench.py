@@ -362,6 +362,64 @@ def cpu_guided_rate(W, H, threads, frames=4096):
     return frames / dt, dt
 
 
+BOW_FRAMES, BOW_N = 512, 2000
+
+
+def _bow_inputs():
+    voc = synth.synth_vocabulary_full(10, 6, seed=5)
+    rng = np.random.default_rng(17)
+    leaves = np.flatnonzero(voc[3])
+    base = voc[4][leaves[rng.integers(0, len(leaves), (8, BOW_N))]]   # descriptors near words, 8 distinct frames
+    base ^= np.packbits(rng.random((8, BOW_N, 256)) < 0.05, axis=2)
+    return voc, base
+
+
+def bench_bow(steps, warmup, world, voc, base):
+    """Secondary (SURVEY 8(f) N3): Frame::ComputeBoW for 512 frames x 2000 descriptors per step against a 10^6-word vocabulary
+    (k = 10, L = 6, the ORB vocabulary's shape), descriptors resident in HBM."""
+    import ctypes as C
+    import torch
+    import orb_slam2_detailed_comments_b200 as pkg
+    from orb_slam2_detailed_comments_b200._lib import lib, check, MEM_DEVICE
+    gv = pkg.ORBVocabulary(*voc)
+    F, cap = BOW_FRAMES, BOW_N
+    desc = torch.from_numpy(np.stack([base[i % len(base)] for i in range(F)])).cuda()
+    n = torch.full((F,), BOW_N, dtype=torch.int32, device="cuda")
+    i32 = lambda *shape: torch.empty(shape, dtype=torch.int32, device="cuda")
+    word, node, bw, bc, fn, fs, ff, fc = i32(F, cap), i32(F, cap), i32(F, cap), i32(F), i32(F, cap), i32(F, cap + 1), i32(F, cap), i32(F)
+    bv = torch.empty((F, cap), dtype=torch.float64, device="cuda")
+    p = lambda x: C.c_void_p(x.data_ptr())
+    st = torch.cuda.current_stream().cuda_stream
+    L = lib()
+
+    def step():
+        check(L.orb_bow_transform(gv._h, MEM_DEVICE, p(desc), p(n), cap, F, 4, p(word), p(node), p(bw), p(bv), p(bc), p(fn), p(fs), p(ff), p(fc),
+                                  C.c_void_p(st)))
+    for _ in range(max(warmup, 1)):
+        step()
+    _barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    _barrier(world)
+    return _max_over_ranks(ms, world), float(bc.float().mean().item())
+
+
+def cpu_bow_rate(voc, base, threads, frames=4096):
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle_py
+    ov = oracle_py.OracleVocabulary(*voc)
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(lambda i: len(ov.transform(base[i % len(base)], 4)[2]), range(frames)))
+    dt = time.perf_counter() - t0
+    return frames / dt, dt
+
+
 def bench_knn(rank, world, steps, warmup):
     """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks, one all_gather
     of the per-query records + device merge when world > 1. pairs/s = Q*D / time (max over ranks)."""
@@ -426,6 +484,8 @@ def run_b200(args):
     knn_rate, knn_ms, knn_launches = bench_knn(rank, world, max(args.steps, 5), args.warmup)
     g_steps = max(args.steps, 5)
     g_ms, g_matches, g_launches = bench_guided(W, H, g_steps, args.warmup, world)
+    bow_voc, bow_base = _bow_inputs()
+    b_ms, b_words = bench_bow(g_steps, args.warmup, world, bow_voc, bow_base)
     popc_peak = pkg.lib().orb_measure_popc_peak(local) if rank == 0 else 0.0
 
     if rank != 0:
@@ -477,6 +537,10 @@ def run_b200(args):
                    "value": GUIDED_FRAMES * world * g_steps / (g_ms * 1e-3), "unit": "frame pairs/s", "ms_per_step": g_ms / g_steps,
                    "config": f"{GUIDED_FRAMES} frame pairs per step per GPU, {GUIDED_M} projected map points x {GUIDED_N} keypoints each, resident in HBM",
                    "matches_per_pair": g_matches, "gpu_launches": int(g_launches), "api": "orb_search_by_projection (device memory)"},
+        "bow": {"metric": "ComputeBoW frames/sec (DBoW2 transform: tree walk + BowVector + FeatureVector, levelsup 4)",
+                "value": BOW_FRAMES * world * g_steps / (b_ms * 1e-3), "unit": "frames/s", "ms_per_step": b_ms / g_steps,
+                "config": f"{BOW_FRAMES} frames x {BOW_N} descriptors per step per GPU, vocabulary k=10 L=6 (10^6 words), resident in HBM",
+                "words_per_frame": b_words, "gpu_launches": 2 * g_steps, "api": "orb_bow_transform (device memory)"},
         "knn": {"metric": "Hamming matches/sec (k=2 brute force)", "value": knn_rate, "unit": "pairs/s",
                 "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
                           + (", NCCL all_gather + device top-2 merge" if world > 1 else ""),
@@ -494,6 +558,9 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n} images of the same workload, one oracle extractor per thread, {dt:.1f} s wall",
                                 "knn_pairs_per_s": kv}
+        bwv, bwdt = cpu_bow_rate(bow_voc, bow_base, cores)
+        line["bow"]["cpu_baseline"] = {"value": bwv, "unit": "frames/s", "cores": cores, "kind": "port",
+                                       "sample": f"4096 frames of the same workload, {bwdt:.1f} s wall"}
         gv, gdt = cpu_guided_rate(W, H, cores)
         line["guided"]["cpu_baseline"] = {"value": gv, "unit": "frame pairs/s", "cores": cores, "kind": "port",
                                           "sample": f"4096 frame pairs of the same workload, {gdt:.1f} s wall"}

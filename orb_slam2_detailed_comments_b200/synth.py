@@ -166,3 +166,26 @@ def synth_vocabulary(k=10, L=3, seed=11, prune=0.05, stop=0.03):
                     nxt.append((nid, lvl + 1, d))
         frontier = nxt
     return k, L, np.array(parent, np.int32), np.array(is_leaf, np.uint8), np.stack(desc), np.array(weight, np.float64)
+
+
+def synth_vocabulary_full(k=10, L=6, seed=5):
+    """Balanced k^L-word vocabulary of the ORB vocabulary's shape (k = 10, L = 6: 1,111,110 nodes + root, 35 MB of descriptors),
+    generated level by level without Python loops over nodes. Node ids breadth-first. Returns (k, L, parent, is_leaf, desc, weight)."""
+    rng = np.random.default_rng(seed)
+    parents, leaves, descs, weights = [np.zeros(1, np.int32)], [np.zeros(1, np.uint8)], [np.zeros((1, 32), np.uint8)], [np.zeros(1)]
+    prev_ids = np.zeros(1, np.int64)
+    prev_desc = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    next_id = 1
+    for lvl in range(1, L + 1):
+        n = len(prev_ids) * k
+        par = np.repeat(prev_ids, k)
+        d = np.repeat(prev_desc, k, axis=0)
+        flips = rng.random((n, 256)) < (0.25 / lvl)   # children drift away from their parent, less at deeper levels
+        d ^= np.packbits(flips, axis=1)
+        ids = np.arange(next_id, next_id + n, dtype=np.int64)
+        next_id += n
+        parents.append(par.astype(np.int32)); descs.append(d)
+        leaves.append(np.full(n, int(lvl == L), np.uint8))
+        weights.append(rng.uniform(0.1, 9.0, n) if lvl == L else np.zeros(n))
+        prev_ids, prev_desc = ids, d
+    return k, L, np.concatenate(parents), np.concatenate(leaves), np.concatenate(descs), np.concatenate(weights)
