@@ -1,6 +1,7 @@
 // C++ parity test of the drop-in classes (built against cv_shim.h): ORB_SLAM2::ORBextractor / ORBmatcher on the GPU versus
 // the CPU oracle (oracle/orb_oracle.h, test infrastructure). Run by tests/test_cpp_dropin.py on a B200; exit code 0 = pass.
 //   usage: test_dropin <frame.raw> <width> <height> <nfeatures> [<frame2.raw>]
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -10,6 +11,7 @@
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
 #include "ORBVocabulary.h"
+#include "FrameOps.h"
 
 #define REQUIRE(cond, ...)                      \
   do {                                          \
@@ -247,6 +249,24 @@ int main(int argc, char** argv) {
       }
       orb_oracle_vocabulary_destroy(ov);
       std::printf("ORBVocabulary::transform: %d words, %d nodes, doubles bit-exact vs oracle\n", bc, fc);
+    }
+    // UndistortKeyPoints / ComputeImageBounds with the TUM1 camera (Examples/Monocular/TUM1.yaml)
+    {
+      const std::vector<float> dc{0.262383f, -0.953104f, -0.005358f, 0.002628f, 1.163314f};
+      const float fx = 517.306408f, fy = 516.469215f, cx = 318.643040f, cy = 255.313989f;
+      std::vector<cv::KeyPoint> un;
+      ORB_SLAM2::UndistortKeyPoints(bk[0], fx, fy, cx, cy, dc, un);
+      std::vector<float> xy(bk[0].size() * 2);
+      for (size_t i = 0; i < bk[0].size(); ++i) { xy[2 * i] = bk[0][i].pt.x; xy[2 * i + 1] = bk[0][i].pt.y; }
+      orb_oracle_undistort_points(fx, fy, cx, cy, dc.data(), (int)dc.size(), xy.data(), (int)bk[0].size());
+      for (size_t i = 0; i < un.size(); ++i)
+        REQUIRE(std::memcmp(&un[i].pt.x, &xy[2 * i], 8) == 0 && un[i].octave == bk[0][i].octave && un[i].angle == bk[0][i].angle, "UndistortKeyPoints %zu", i);
+      float x0, x1, y0, y1;
+      ORB_SLAM2::ComputeImageBounds(W, H, fx, fy, cx, cy, dc, x0, x1, y0, y1);
+      float c4[8] = {0.f, 0.f, (float)W, 0.f, 0.f, (float)H, (float)W, (float)H};
+      orb_oracle_undistort_points(fx, fy, cx, cy, dc.data(), (int)dc.size(), c4, 4);
+      REQUIRE(x0 == std::min(c4[0], c4[4]) && x1 == std::max(c4[2], c4[6]) && y0 == std::min(c4[1], c4[3]) && y1 == std::max(c4[5], c4[7]), "ComputeImageBounds");
+      std::printf("UndistortKeyPoints: %zu keypoints bit-exact vs oracle, bounds [%g, %g] x [%g, %g]\n", un.size(), x0, x1, y0, y1);
     }
     std::printf("ORBmatcher: kNN over %d x %d bit-exact, %d ratio-test accepts, DescriptorDistance x %d exact\n", bd[0].rows, bd[1].rows, nacc, m);
   }

@@ -18,6 +18,8 @@
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
  *   orb_vocabulary_*, orb_bow_transform <- Frame::ComputeBoW = DBoW2 TemplatedVocabulary::transform   src/Frame.cc:750-765,
  *                                Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280
+ *   orb_undistort_keypoints, orb_image_bounds <- Frame::UndistortKeyPoints / ComputeImageBounds (cv::undistortPoints)
+ *                                                                                     src/Frame.cc:770-806, 832-868
  *   orb_distinctive_descriptors <- MapPoint::ComputeDistinctiveDescriptors, batched over map points   src/MapPoint.cc:424-517
  *   orb_search_by_projection  <- the guided matchers' core: Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea
  *                                (src/Frame.cc:432-460, 729-745, 633-717), the candidate scan with sequential claims of
@@ -233,6 +235,22 @@ int orb_vocabulary_words(const orb_vocabulary* v);   /* number of leaves = vocab
 int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int32_t* n, int cap, int frames, int levelsup, int32_t* word,
                       int32_t* node, int32_t* bow_word, double* bow_value, int32_t* bow_count, int32_t* fv_node, int32_t* fv_start,
                       int32_t* fv_feature, int32_t* fv_count, void* stream);
+
+/* ---- Frame::UndistortKeyPoints / ComputeImageBounds (src/Frame.cc:770-806, 832-868) ---------------------
+ * cv::undistortPoints(pts, pts, mK, mDistCoef, cv::Mat(), mK): 5 fixed iterations in double precision (OpenCV >= 4 default
+ * criteria), bit-exact against cv2 4.13. The camera holds mK and mDistCoef as the reference does (CV_32F). */
+typedef struct orb_camera {
+  float fx, fy, cx, cy;  /* mK */
+  float dist[8];         /* mDistCoef: k1 k2 p1 p2 [k3 [k4 k5 k6]] */
+  int32_t n_dist;        /* 4, 5 or 8 */
+} orb_camera;
+/* kps_un[f][i] = kps[f][i] with pt replaced by the undistorted point, i < n[f] (kps_un may alias kps). dist[0] == 0 copies the
+ * keypoints unchanged (src/Frame.cc:772-776). Arrays in `mem` memory. */
+int orb_undistort_keypoints(int mem, const orb_camera* cam, const orb_keypoint* kps, const int32_t* n, int cap, int frames,
+                            orb_keypoint* kps_un, void* stream);
+/* bounds[4] = mnMinX, mnMinY, mnMaxX, mnMaxY of a cols x rows image (the four undistorted corners, src/Frame.cc:836-858;
+ * 0, 0, cols, rows without distortion). Host output; runs the same device code on the four corners. */
+int orb_image_bounds(const orb_camera* cam, int cols, int rows, float* bounds);
 
 /* ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) ----------------------------
  * For every map point p < points with the descriptors desc[offsets[p] .. offsets[p+1]) of its observations (N_p rows, in

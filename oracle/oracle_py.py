@@ -297,3 +297,14 @@ class OracleVocabulary:
         bow = {int(w): float(v) for w, v in zip(bw[:b], bv[:b])}
         fv = {int(fn[j]): ff[fs[j]:fs[j + 1]].tolist() for j in range(f)}
         return word[:n], node[:n], bow, fv
+
+
+def undistort_points(xy, fx, fy, cx, cy, dist):
+    """cv::undistortPoints(pts, pts, K, dist, Mat(), K) as Frame::UndistortKeyPoints calls it (src/Frame.cc:787-793). xy [n,2] float32."""
+    L = lib()
+    L.orb_oracle_undistort_points.argtypes = [C.c_float] * 4 + [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+    L.orb_oracle_undistort_points.restype = None
+    out = np.ascontiguousarray(xy, np.float32).copy()
+    d = np.ascontiguousarray(dist, np.float32)
+    L.orb_oracle_undistort_points(fx, fy, cx, cy, _p(d), len(d), _p(out), len(out))
+    return out

@@ -735,6 +735,33 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
   return nmatches;
 }
 
+// ---- cv::undistortPoints as Frame::UndistortKeyPoints calls it (src/Frame.cc:787-793) -----------------------------------------
+void orb_oracle_undistort_points(float ffx, float ffy, float fcx, float fcy, const float* dist, int n_dist, float* xy, int n) {
+  if (dist[0] == 0.0f) return;   // :772-776
+  const double fx = ffx, fy = ffy, cx = fcx, cy = fcy;
+  double k[14] = {0};
+  for (int i = 0; i < n_dist && i < 14; ++i) k[i] = dist[i];
+  const double ifx = 1. / fx, ify = 1. / fy;
+  for (int i = 0; i < n; ++i) {
+    const double u = xy[2 * i], v = xy[2 * i + 1];
+    double x = (u - cx) * ifx, y = (v - cy) * ify;
+    const double x0 = x, y0 = y;
+    for (int j = 0; j < 5; ++j) {   // TermCriteria(MAX_ITER, 5, 0.01)
+      const double r2 = x * x + y * y;
+      const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+      if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+      const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+      const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+      x = (x0 - deltaX) * icdist;
+      y = (y0 - deltaY) * icdist;
+    }
+    // RR = P * I with P = K: rows (fx 0 cx), (0 fy cy), (0 0 1)
+    const double xx = fx * x + 0.0 * y + cx, yy = 0.0 * x + fy * y + cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+    xy[2 * i] = (float)(xx * ww);
+    xy[2 * i + 1] = (float)(yy * ww);
+  }
+}
+
 // ---- DBoW2 vocabulary transform ----------------------------------------------------------------------------------------------
 struct orb_oracle_vocabulary {
   struct Node {   // TemplatedVocabulary::Node (TemplatedVocabulary.h:270-310)

@@ -114,6 +114,10 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* 
 int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const orb_oracle_search_params* prm, float x, float y, float r,
                                 int min_level, int max_level, int32_t* out);
 
+/* Frame::UndistortKeyPoints (src/Frame.cc:770-806): cv::undistortPoints(pts, pts, K, dist, Mat(), K), OpenCV >= 4 default criteria
+ * (5 iterations), on n points xy [n][2] (float, in place). k: n_dist (4, 5 or 8) float coefficients. dist[0] == 0 leaves xy unchanged. */
+void orb_oracle_undistort_points(float fx, float fy, float cx, float cy, const float* dist, int n_dist, float* xy, int n);
+
 /* Frame::ComputeBoW (src/Frame.cc:750-765) = DBoW2 TemplatedVocabulary::transform(features, BowVector, FeatureVector, levelsup)
  * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280; BowVector.cpp; FeatureVector.cpp) with TF_IDF + L1_NORM.
  * Vocabulary node table as loadFromTextFile reads it (node 0 = root, entries 0 ignored). One descriptor set per call. Outputs as

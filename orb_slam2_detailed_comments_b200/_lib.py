@@ -39,12 +39,22 @@ SYMBOLS = [
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
     "orb_search_by_projection", "orb_distinctive_descriptors",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_words", "orb_bow_transform",
+    "orb_undistort_keypoints", "orb_image_bounds",
 ]
 
 
 class OrbParams(C.Structure):
     _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
                 ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("flags", C.c_int32)]
+
+
+class OrbCamera(C.Structure):
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("dist", C.c_float * 8), ("n_dist", C.c_int32)]
+
+    @classmethod
+    def make(cls, fx, fy, cx, cy, dist):
+        d = list(dist) + [0.0] * (8 - len(dist))
+        return cls(fx, fy, cx, cy, (C.c_float * 8)(*d), len(dist))
 
 
 class OrbSearchParams(C.Structure):
@@ -101,6 +111,8 @@ def lib():
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
     L.orb_matcher_launch_count.restype = i64
+    L.orb_undistort_keypoints.argtypes = [i32, C.POINTER(OrbCamera), vp, vp, i32, i32, vp, vp]
+    L.orb_image_bounds.argtypes = [C.POINTER(OrbCamera), i32, i32, vp]
     L.orb_distinctive_descriptors.argtypes = [i32, vp, vp, i32, vp, vp, vp]
     L.orb_search_by_projection.argtypes = [i32, vp, vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]
     L.orb_measure_popc_peak.argtypes = [i32]

@@ -29,6 +29,7 @@ void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaSt
 void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
+void orb_launch_undistort(const void*, const OrbKeypoint*, const int*, int, int, OrbKeypoint*, cudaStream_t);
 struct BowVoc {   // == bow.cu
   const int* child_start; const int* child_id; const uint4* child_desc; const uint8_t* is_leaf; const int* word_of; const double* word_weight;
   int L;
@@ -978,6 +979,62 @@ int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int
     CU(cudaMemcpyAsync(fv_count, d_fc, F * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
   }
+  return ORB_OK;
+}
+
+int orb_undistort_keypoints(int mem, const orb_camera* cam, const orb_keypoint* kps, const int32_t* n, int cap, int frames,
+                            orb_keypoint* kps_un, void* stream) {
+  if (!cam || !kps || !n || !kps_un || cap <= 0 || frames <= 0) return fail(ORB_E_BADARG, "bad argument");
+  if (cam->n_dist != 4 && cam->n_dist != 5 && cam->n_dist != 8) return fail(ORB_E_BADARG, "n_dist must be 4, 5 or 8");
+  if (!(cam->fx != 0.f) || !(cam->fy != 0.f)) return fail(ORB_E_BADARG, "fx / fy must be non-zero");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const size_t bytes = (size_t)frames * cap * sizeof(orb_keypoint);
+  if (mem == ORB_MEM_DEVICE) {
+    orb_launch_undistort(cam, (const OrbKeypoint*)kps, n, cap, frames, (OrbKeypoint*)kps_un, st);
+    orb_knn_count_launches(1);
+    CU(cudaGetLastError());
+    return ORB_OK;
+  }
+  if ((rc = ws->g_kps.ensure(bytes)) != ORB_OK) return rc;
+  if ((rc = ws->g_nk.ensure((size_t)frames * sizeof(int))) != ORB_OK) return rc;
+  CU(cudaMemcpyAsync(ws->g_kps.p, kps, bytes, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(ws->g_nk.p, n, (size_t)frames * sizeof(int), cudaMemcpyHostToDevice, st));
+  orb_launch_undistort(cam, ws->g_kps.as<OrbKeypoint>(), ws->g_nk.as<int>(), cap, frames, ws->g_kps.as<OrbKeypoint>(), st);
+  orb_knn_count_launches(1);
+  CU(cudaGetLastError());
+  if (kps_un != kps) memcpy(kps_un, kps, bytes);   // rows >= n[f] keep the caller's content (the kernel only rewrites rows < n[f])
+  for (int f = 0; f < frames; ++f) {
+    const int m = std::min(std::max(n[f], 0), cap);
+    if (m > 0)
+      CU(cudaMemcpyAsync(kps_un + (size_t)f * cap, ws->g_kps.as<orb_keypoint>() + (size_t)f * cap, (size_t)m * sizeof(orb_keypoint),
+                         cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(st));
+  return ORB_OK;
+}
+
+int orb_image_bounds(const orb_camera* cam, int cols, int rows, float* bounds) {
+  if (!cam || !bounds || cols <= 0 || rows <= 0) return fail(ORB_E_BADARG, "bad argument");
+  if (cam->dist[0] == 0.0f) {   // src/Frame.cc:861-867
+    bounds[0] = 0.f; bounds[1] = 0.f; bounds[2] = (float)cols; bounds[3] = (float)rows;
+    return ORB_OK;
+  }
+  orb_keypoint c[4];
+  memset(c, 0, sizeof(c));
+  c[1].x = (float)cols; c[2].y = (float)rows; c[3].x = (float)cols; c[3].y = (float)rows;   // :838-845
+  const int32_t four = 4;
+  const int rc = orb_undistort_keypoints(ORB_MEM_HOST, cam, c, &four, 4, 1, c, nullptr);
+  if (rc != ORB_OK) return rc;
+  bounds[0] = std::min(c[0].x, c[2].x);   // mnMinX (:855)
+  bounds[2] = std::max(c[1].x, c[3].x);   // mnMaxX
+  bounds[1] = std::min(c[0].y, c[1].y);   // mnMinY
+  bounds[3] = std::max(c[2].y, c[3].y);   // mnMaxY
   return ORB_OK;
 }
 

@@ -15,7 +15,7 @@ from orb_slam2_detailed_comments_b200 import synth
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 PIPELINES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                   if os.path.basename(p) not in ("fast_atan2.npz", "primitives_333x257.npz") and not os.path.basename(p).startswith("stereo_"))
+                   if os.path.basename(p) not in ("fast_atan2.npz", "primitives_333x257.npz") and not os.path.basename(p).startswith(("stereo_", "undistort_")))
 STEREO = sorted(glob.glob(os.path.join(GOLDEN, "stereo_*.npz")))   # tests/golden/make_golden_stereo.py
 
 
