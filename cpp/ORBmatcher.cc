@@ -115,4 +115,41 @@ void ORBmatcher::ComputeDistinctiveDescriptors(const cv::Mat& observations, cons
   check(orb_distinctive_descriptors(ORB_MEM_HOST, d, offsets.data(), points, bestIdx.data(), nullptr, nullptr), "orb_distinctive_descriptors");
 }
 
+static void to_csr(const ORBmatcher::FeatureVector& fv, int cap, std::vector<int32_t>& node, std::vector<int32_t>& start, std::vector<int32_t>& feat,
+                   int32_t& count) {
+  node.assign(cap, 0); start.assign(cap + 1, 0); feat.assign(cap, 0);
+  count = 0;
+  int pos = 0;
+  for (const auto& e : fv) {
+    if (count >= cap || pos + (int)e.second.size() > cap) throw std::runtime_error("SearchByBoW: FeatureVector larger than the feature count");
+    node[count] = (int32_t)e.first;
+    start[count] = pos;
+    for (unsigned int i : e.second) feat[pos++] = (int32_t)i;
+    ++count;
+  }
+  start[count] = pos;
+}
+
+int ORBmatcher::SearchByBoW(const cv::Mat& kfDescriptors, const std::vector<cv::KeyPoint>& kfKeysUn, const std::vector<unsigned char>& kfHasPoint,
+                            const FeatureVector& kfFeatVec, const cv::Mat& fDescriptors, const std::vector<cv::KeyPoint>& fKeys,
+                            const FeatureVector& fFeatVec, std::vector<int>& assigned) const {
+  const int nk = (int)kfKeysUn.size(), nf = (int)fKeys.size();
+  assigned.assign(nf, -1);
+  if (nk == 0 || nf == 0) return 0;
+  if (kfDescriptors.rows != nk || fDescriptors.rows != nf || (int)kfHasPoint.size() != nk) throw std::runtime_error("SearchByBoW: array sizes differ");
+  std::vector<uint8_t> tk, tf;
+  const uint8_t* dk = rows32(kfDescriptors, tk);
+  const uint8_t* df = rows32(fDescriptors, tf);
+  std::vector<int32_t> kn, ks, kfe, fn, fs, ffe;
+  int32_t kc = 0, fc = 0;
+  to_csr(kfFeatVec, nk, kn, ks, kfe, kc);
+  to_csr(fFeatVec, nf, fn, fs, ffe, fc);
+  int32_t nm = 0;
+  check(orb_search_by_bow(ORB_MEM_HOST, dk, reinterpret_cast<const orb_keypoint*>(kfKeysUn.data()), kfHasPoint.data(), kn.data(), ks.data(), kfe.data(),
+                          &kc, nk, df, reinterpret_cast<const orb_keypoint*>(fKeys.data()), fn.data(), fs.data(), ffe.data(), &fc, nf, 1, TH_LOW,
+                          mfNNratio, mbCheckOrientation ? 1 : 0, assigned.data(), &nm, nullptr),
+        "orb_search_by_bow");
+  return nm;
+}
+
 }  // namespace ORB_SLAM2

@@ -8,6 +8,7 @@
 #define ORBMATCHER_H
 
 #include <cstdint>
+#include <map>
 #include <vector>
 
 #ifdef ORB_B200_USE_OPENCV
@@ -65,6 +66,15 @@ class ORBmatcher {
   // mbCheckOrientation (:1828-1863). Returns nmatches. GPU only.
   int SearchByProjection(const TargetFrame& F, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors, int th,
                          bool useRatio, std::vector<int>& assigned, std::vector<int>* pointMatch = nullptr) const;
+
+  // SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:248-410) on flat inputs: keyframe descriptors / mvKeysUn /
+  // "has a good map point" flags / mFeatVec, frame descriptors / mvKeys / mFeatVec (DBoW2::FeatureVector derives from this map type).
+  // assigned[i] = keyframe feature matched to frame feature i (vpMapPointMatches[i] = vpMapPointsKF[assigned[i]]) or -1. Threshold
+  // TH_LOW, ratio mfNNratio, rotation histogram iff mbCheckOrientation. Returns nmatches. GPU only.
+  typedef std::map<unsigned int, std::vector<unsigned int>> FeatureVector;
+  int SearchByBoW(const cv::Mat& kfDescriptors, const std::vector<cv::KeyPoint>& kfKeysUn, const std::vector<unsigned char>& kfHasPoint,
+                  const FeatureVector& kfFeatVec, const cv::Mat& fDescriptors, const std::vector<cv::KeyPoint>& fKeys,
+                  const FeatureVector& fFeatVec, std::vector<int>& assigned) const;
 
   // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) for many map points in one call: rows
   // [offsets[p], offsets[p+1]) of `observations` (total x 32 CV_8U) are point p's descriptors in the reference's map order;

@@ -247,6 +247,32 @@ int main(int argc, char** argv) {
                     std::memcmp(e.second.data(), &ff[fs[i]], e.second.size() * 4) == 0, "FeatureVector node %d differs from the oracle", i);
         ++i;
       }
+      // SearchByBoW between the two images through their FeatureVectors
+      {
+        ORB_SLAM2::ORBVocabulary::BowVector bow2;
+        ORB_SLAM2::ORBVocabulary::FeatureVector fv2;
+        voc.transform(bd[1], bow2, fv2, 2);
+        std::vector<unsigned char> has(bk[0].size(), 1);
+        for (size_t q = 0; q < has.size(); q += 9) has[q] = 0;
+        ORB_SLAM2::ORBmatcher bm(0.7f, true);
+        std::vector<int> asg;
+        const int nmb = bm.SearchByBoW(bd[0], bk[0], has, fv, bd[1], bk[1], fv2, asg);
+        auto csr = [](const ORB_SLAM2::ORBVocabulary::FeatureVector& m, int cap, std::vector<int32_t>& nd, std::vector<int32_t>& st, std::vector<int32_t>& fe) {
+          nd.assign(cap, 0); st.assign(cap + 1, 0); fe.assign(cap, 0);
+          int c = 0, pos = 0;
+          for (const auto& e : m) { nd[c] = (int)e.first; st[c] = pos; for (unsigned v : e.second) fe[pos++] = (int)v; ++c; }
+          st[c] = pos;
+          return c;
+        };
+        std::vector<int32_t> kn, ks, ke, f2n, f2s, f2e, want(bk[1].size());
+        const int kc = csr(fv, (int)bk[0].size(), kn, ks, ke), fc2 = csr(fv2, (int)bk[1].size(), f2n, f2s, f2e);
+        const int onm = orb_oracle_search_by_bow(bd[0].ptr<unsigned char>(0), reinterpret_cast<const orb_oracle_kp*>(bk[0].data()), has.data(), kn.data(),
+                                                 ks.data(), ke.data(), kc, bd[1].ptr<unsigned char>(0), reinterpret_cast<const orb_oracle_kp*>(bk[1].data()),
+                                                 (int)bk[1].size(), f2n.data(), f2s.data(), f2e.data(), fc2, ORB_SLAM2::ORBmatcher::TH_LOW, 0.7f, 1, want.data());
+        REQUIRE(nmb == onm && std::memcmp(asg.data(), want.data(), want.size() * 4) == 0, "SearchByBoW: %d matches vs oracle %d", nmb, onm);
+        REQUIRE(nmb > 30, "SearchByBoW: too few matches (%d)", nmb);
+        std::printf("SearchByBoW: %d matches, assignment bit-exact vs oracle\n", nmb);
+      }
       orb_oracle_vocabulary_destroy(ov);
       std::printf("ORBVocabulary::transform: %d words, %d nodes, doubles bit-exact vs oracle\n", bc, fc);
     }

@@ -16,6 +16,7 @@
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
+ *   orb_search_by_bow         <- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)                  src/ORBmatcher.cc:248-410
  *   orb_vocabulary_*, orb_bow_transform <- Frame::ComputeBoW = DBoW2 TemplatedVocabulary::transform   src/Frame.cc:750-765,
  *                                Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280
  *   orb_undistort_keypoints, orb_image_bounds <- Frame::UndistortKeyPoints / ComputeImageBounds (cv::undistortPoints)
@@ -213,6 +214,21 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
 double orb_measure_popc_peak(int device);
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:248-410) for `frames` independent
+ * (keyframe, frame) pairs: keyframe features with a valid map point are matched against the frame's features of the same
+ * vocabulary node (both FeatureVectors in the CSR layout of orb_bow_transform), best / second best with strict <, accept iff
+ * best <= th_dist && (float)best < nn_ratio * (float)second (:339-342), a matched frame feature is skipped by later keyframe
+ * features (:300-301), rotation histogram + ComputeThreeMaxima when check_orientation (:349-365, :393-408).
+ * kf_desc [frames][qcap][32], kf_kps_un [frames][qcap] (angle read), kf_valid [frames][qcap] (vpMapPointsKF[i] && !isBad()),
+ * kf_fv_* / f_fv_* as written by orb_bow_transform with cap = qcap / cap; f_desc [frames][cap][32], f_kps [frames][cap] (mvKeys,
+ * angle read). assigned [frames][cap] = keyframe feature index matched to frame feature i (vpMapPointMatches[i] =
+ * vpMapPointsKF[assigned]) or -1; nmatches [frames]. All arrays in `mem` memory; cap, qcap < 2^18. */
+int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
+                      const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
+                      const orb_keypoint* f_kps, const int32_t* f_fv_node, const int32_t* f_fv_start, const int32_t* f_fv_feature,
+                      const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
+                      int32_t* nmatches, void* stream);
 
 /* ---- Frame::ComputeBoW (src/Frame.cc:750-765) --------------------------------------------------------
  * = DBoW2 TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)

@@ -308,3 +308,22 @@ def undistort_points(xy, fx, fy, cx, cy, dist):
     d = np.ascontiguousarray(dist, np.float32)
     L.orb_oracle_undistort_points(fx, fy, cx, cy, _p(d), len(d), _p(out), len(out))
     return out
+
+
+def search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv, f_desc, f_kps, f_fv, th_dist=50, nn_ratio=0.7, check_orientation=True):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (src/ORBmatcher.cc:248-410). kf_fv / f_fv = (node, start, feature, count)
+    CSR FeatureVectors. Returns (assigned [n_f], nmatches)."""
+    L = lib()
+    vp = C.c_void_p
+    L.orb_oracle_search_by_bow.argtypes = [vp] * 6 + [C.c_int, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp]
+    c = lambda a, dt: np.ascontiguousarray(a, dt)
+    kf_desc, f_desc = c(kf_desc, np.uint8), c(f_desc, np.uint8)
+    kf_kps_un, f_kps = np.ascontiguousarray(kf_kps_un), np.ascontiguousarray(f_kps)
+    kf_valid = c(kf_valid, np.uint8)
+    kn, ks, kfe, kc = (c(a, np.int32) for a in kf_fv[:3]) if False else (c(kf_fv[0], np.int32), c(kf_fv[1], np.int32), c(kf_fv[2], np.int32), int(kf_fv[3]))
+    fn, fs, ffe, fc = c(f_fv[0], np.int32), c(f_fv[1], np.int32), c(f_fv[2], np.int32), int(f_fv[3])
+    n_f = len(f_kps)
+    assigned = np.full(max(n_f, 1), -1, np.int32)
+    nm = L.orb_oracle_search_by_bow(_p(kf_desc), _p(kf_kps_un), _p(kf_valid), _p(kn), _p(ks), _p(kfe), kc, _p(f_desc), _p(f_kps), n_f,
+                                    _p(fn), _p(fs), _p(ffe), fc, th_dist, nn_ratio, int(check_orientation), _p(assigned))
+    return assigned[:n_f], nm

@@ -735,6 +735,74 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
   return nmatches;
 }
 
+int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_node,
+                             const int32_t* kf_start, const int32_t* kf_feature, int kf_count, const uint8_t* f_desc,
+                             const orb_oracle_kp* f_kps, int n_f, const int32_t* f_node, const int32_t* f_start, const int32_t* f_feature,
+                             int f_count, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned) {
+  typedef std::map<unsigned, std::vector<unsigned>> FeatureVector;
+  FeatureVector fvKF, fvF;
+  for (int j = 0; j < kf_count; ++j) fvKF[kf_node[j]].assign(kf_feature + kf_start[j], kf_feature + kf_start[j + 1]);
+  for (int j = 0; j < f_count; ++j) fvF[f_node[j]].assign(f_feature + f_start[j], f_feature + f_start[j + 1]);
+  std::fill(assigned, assigned + n_f, -1);   // vpMapPointMatches = vector<MapPoint*>(F.N, NULL) (:255)
+  int nmatches = 0;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  const float factor = HISTO_LENGTH / 360.0f;   // :268
+  FeatureVector::const_iterator KFit = fvKF.begin(), Fit = fvF.begin(), KFend = fvKF.end(), Fend = fvF.end();
+  while (KFit != KFend && Fit != Fend) {
+    if (KFit->first == Fit->first) {
+      const std::vector<unsigned>& vKF = KFit->second;
+      const std::vector<unsigned>& vF = Fit->second;
+      for (size_t iKF = 0; iKF < vKF.size(); ++iKF) {
+        const unsigned realIdxKF = vKF[iKF];
+        if (!kf_valid[realIdxKF]) continue;   // !pMP || pMP->isBad() (:283-289)
+        const uint8_t* dKF = kf_desc + (size_t)realIdxKF * 32;
+        int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+        for (size_t iF = 0; iF < vF.size(); ++iF) {
+          const unsigned realIdxF = vF[iF];
+          if (assigned[realIdxF] >= 0) continue;   // :300-301
+          const int dist = orb_oracle_descriptor_distance(dKF, f_desc + (size_t)realIdxF * 32);
+          if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = (int)realIdxF; }
+          else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist1 <= th_dist) {   // :339
+          if (static_cast<float>(bestDist1) < nn_ratio * static_cast<float>(bestDist2)) {   // :342
+            assigned[bestIdxF] = (int)realIdxKF;
+            if (check_orientation) {
+              float rot = kf_kps_un[realIdxKF].angle - f_kps[bestIdxF].angle;
+              if (rot < 0.0) rot += 360.0f;
+              int bin = (int)std::round(rot * factor);
+              if (bin == HISTO_LENGTH) bin = 0;
+              if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(bestIdxF);
+            }
+            ++nmatches;
+          }
+        }
+      }
+      ++KFit; ++Fit;
+    } else if (KFit->first < Fit->first) {
+      KFit = fvKF.lower_bound(Fit->first);
+    } else {
+      Fit = fvF.lower_bound(KFit->first);
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int sz = (int)rotHist[i].size();
+      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+      else if (sz > max3) { max3 = sz; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx : rotHist[i]) { assigned[idx] = -1; --nmatches; }
+    }
+  }
+  return nmatches;
+}
+
 // ---- cv::undistortPoints as Frame::UndistortKeyPoints calls it (src/Frame.cc:787-793) -----------------------------------------
 void orb_oracle_undistort_points(float ffx, float ffy, float fcx, float fcy, const float* dist, int n_dist, float* xy, int n) {
   if (dist[0] == 0.0f) return;   // :772-776

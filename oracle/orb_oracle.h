@@ -114,6 +114,13 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* 
 int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const orb_oracle_search_params* prm, float x, float y, float r,
                                 int min_level, int max_level, int32_t* out);
 
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:248-410), one pair. FeatureVectors as CSR
+ * (node ascending, features of node j = feature[start[j] .. start[j+1])). assigned [n_f] = keyframe feature index or -1. Returns nmatches. */
+int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_node,
+                             const int32_t* kf_start, const int32_t* kf_feature, int kf_count, const uint8_t* f_desc,
+                             const orb_oracle_kp* f_kps, int n_f, const int32_t* f_node, const int32_t* f_start, const int32_t* f_feature,
+                             int f_count, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned);
+
 /* Frame::UndistortKeyPoints (src/Frame.cc:770-806): cv::undistortPoints(pts, pts, K, dist, Mat(), K), OpenCV >= 4 default criteria
  * (5 iterations), on n points xy [n][2] (float, in place). k: n_dist (4, 5 or 8) float coefficients. dist[0] == 0 leaves xy unchanged. */
 void orb_oracle_undistort_points(float fx, float fy, float cx, float cy, const float* dist, int n_dist, float* xy, int n);

@@ -39,6 +39,9 @@ struct GuidedFrame {
   const float* uright;       // or nullptr
   const uint8_t* claimed;    // or nullptr (static claims)
   float min_x, min_y, inv_w, inv_h;
+  // SearchByBoW: FeatureVector of the target frame as CSR (orb_bow_transform layout)
+  const int* fv_start;
+  const int* fv_feature;
 };
 
 // A candidate is one 64-bit word {hi, lo}. hi = dist << 18 | sorted position: "strict <, first in scan order wins" is a plain
@@ -93,6 +96,28 @@ __device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQu
       }
       emit(hi, lo);
     }
+  }
+}
+
+// SearchByBoW candidates (src/ORBmatcher.cc:296-322): the target frame's features in the query's vocabulary node, i.e. one
+// contiguous range of the FeatureVector CSR (slot = q.reserved, resolved by orb_bow_queries_kernel); ascending position in
+// the CSR is the reference's loop order. Same emit() contract as guided_scan.
+template <typename Emit>
+__device__ __forceinline__ void bow_scan(const GuidedFrame& F, const GuidedQuery& q, const uint4 qd0, const uint4 qd1, int lane, Emit emit) {
+  if (q.reserved < 0) return;
+  const int e0 = F.fv_start[q.reserved], e1 = F.fv_start[q.reserved + 1];
+  for (int base = e0; base < e1; base += 32) {
+    const int e = base + lane;
+    unsigned hi = GUIDED_NONE, lo = 0;
+    if (e < e1) {
+      const int idx = F.fv_feature[e];
+      const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
+      const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
+                       __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
+      hi = ((unsigned)dist << 18) | (unsigned)e;
+      lo = (unsigned)idx;
+    }
+    emit(hi, lo);
   }
 }
 
@@ -163,8 +188,10 @@ __global__ void __launch_bounds__(256) orb_guided_grid_kernel(const OrbKeypoint*
 }
 
 // ---- 2. candidate list per query -------------------------------------------------------------------------------------------
+template <bool BOW>
 __global__ void __launch_bounds__(GUIDED_WARPS * 32)
-orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const uint8_t* __restrict__ desc,
+orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const int* __restrict__ fv_start,
+                             const int* __restrict__ fv_feature, const uint8_t* __restrict__ desc,
                              const float* __restrict__ uright, const uint8_t* __restrict__ claimed, int cap,
                              const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc, const int* __restrict__ n_queries,
                              int qcap, float min_x, float min_y, float inv_w, float inv_h, uint2* __restrict__ lists,
@@ -179,18 +206,22 @@ orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restr
   F.uright = uright ? uright + (size_t)f * cap : nullptr;
   F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  F.fv_start = BOW ? fv_start + (size_t)f * (cap + 1) : nullptr;
+  F.fv_feature = BOW ? fv_feature + (size_t)f * cap : nullptr;
   const size_t qi = (size_t)f * qcap + iq;
   const GuidedQuery q = queries[qi];
   uint2* out = lists + qi * GUIDED_LIST;
   int n = 0;
   if (!(q.flags & 1)) {
     const uint4* qd = reinterpret_cast<const uint4*>(qdesc + qi * 32);
-    guided_scan(F, q, qd[0], qd[1], lane, [&](unsigned hi, unsigned lo) {
+    auto emit = [&](unsigned hi, unsigned lo) {
       const unsigned m = __ballot_sync(0xffffffffu, hi != GUIDED_NONE);
       const int pos = n + __popc(m & ((1u << lane) - 1u));
       if (hi != GUIDED_NONE && pos < GUIDED_LIST) out[pos] = make_uint2(lo, hi);
       n += __popc(m);
-    });
+    };
+    if (BOW) bow_scan(F, q, qd[0], qd[1], lane, emit);
+    else guided_scan(F, q, qd[0], qd[1], lane, emit);
   }
   if (lane >= n && lane < GUIDED_LIST) out[lane] = make_uint2(0u, GUIDED_NONE);   // pad: the resolving warp reads all 32 slots
   if (lane == 0) list_cnt[qi] = n;   // > GUIDED_LIST = overflow, the list is incomplete
@@ -201,12 +232,14 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
 
+template <bool BOW>
 __global__ void __launch_bounds__(32)
-orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const OrbKeypoint* __restrict__ kps,
+orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const int* __restrict__ fv_start,
+                          const int* __restrict__ fv_feature, const OrbKeypoint* __restrict__ kps,
                           const uint8_t* __restrict__ desc, const float* __restrict__ uright, const uint8_t* __restrict__ claimed,
                           int cap, const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc,
                           const int* __restrict__ n_queries, int qcap, float min_x, float min_y, float inv_w, float inv_h,
-                          int th_dist, float nn_ratio, int check_orientation, const uint2* __restrict__ lists,
+                          int th_dist, float nn_ratio, int ratio_rule, int check_orientation, const uint2* __restrict__ lists,
                           const int* __restrict__ list_cnt, int* __restrict__ assigned, int* __restrict__ query_match,
                           int* __restrict__ nmatches) {
   extern __shared__ unsigned s_dyn[];   // claim bits, (cap + 31) / 32 words
@@ -221,6 +254,8 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
   F.uright = uright ? uright + (size_t)f * cap : nullptr;
   F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  F.fv_start = BOW ? fv_start + (size_t)f * (cap + 1) : nullptr;
+  F.fv_feature = BOW ? fv_feature + (size_t)f * cap : nullptr;
   kps += (size_t)f * cap;
   queries += (size_t)f * qcap;
   qdesc += (size_t)f * qcap * 32;
@@ -275,14 +310,16 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
         const GuidedQuery q = queries[iq];
         const uint4* qd = reinterpret_cast<const uint4*>(qdesc + (size_t)iq * 32);
         unsigned long long k1 = ~0ull, k2 = ~0ull;
-        guided_scan(F, q, qd[0], qd[1], lane, [&](unsigned hi, unsigned lo) {
+        auto emit = [&](unsigned hi, unsigned lo) {
           const unsigned idx = lo & 0x3ffffu;
           if (hi != GUIDED_NONE && !((s_dyn[idx >> 5] >> (idx & 31)) & 1u)) {
             const unsigned long long k = ((unsigned long long)hi << 32) | lo;
             if (k < k1) { k2 = k1; k1 = k; }
             else if (k < k2) k2 = k;
           }
-        });
+        };
+        if (BOW) bow_scan(F, q, qd[0], qd[1], lane, emit);
+        else guided_scan(F, q, qd[0], qd[1], lane, emit);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
           const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
@@ -299,7 +336,11 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
       if (use_second) {
         const int d2 = hi2 == GUIDED_NONE ? 256 : (int)(hi2 >> 18);                         // bestDist2 = 256, bestLevel2 = -1 (:114-115)
         const int l2 = hi2 == GUIDED_NONE ? -1 : (int)(lo2 >> 18);
-        if (l1 == l2 && (float)d1 > nn_ratio * (float)d2) accept = false;                   // :174
+        if (ratio_rule == 0) {
+          if (l1 == l2 && (float)d1 > nn_ratio * (float)d2) accept = false;                 // :174 (level-conditional reject)
+        } else if (!((float)d1 < nn_ratio * (float)d2)) {
+          accept = false;                                                                  // :342 (SearchByBoW: accept iff best < r * second)
+        }
       }
       if (accept) {
         ++nm;
@@ -366,11 +407,70 @@ void orb_launch_guided(const OrbKeypoint* kps, const uint8_t* desc, const float*
   const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
   const GuidedQuery* q = static_cast<const GuidedQuery*>(queries);
   orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
-  orb_guided_candidates_kernel<<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
-      items, cell_start, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
+  orb_guided_candidates_kernel<false><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, nullptr, nullptr, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
   const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
-  orb_guided_resolve_kernel<<<frames, 32, smem, st>>>(items, cell_start, kps, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x,
-                                                      min_y, inv_w, inv_h, th_dist, nn_ratio, check_orientation, lists, list_cnt, assigned,
-                                                      query_match, nmatches);
+  orb_guided_resolve_kernel<false><<<frames, 32, smem, st>>>(items, cell_start, nullptr, nullptr, kps, desc, uright, claimed, cap, q, qdesc,
+                                                             n_queries, qcap, min_x, min_y, inv_w, inv_h, th_dist, nn_ratio, 0,
+                                                             check_orientation, lists, list_cnt, assigned, query_match, nmatches);
+  *launches += 3;
+}
+
+// ---- SearchByBoW (src/ORBmatcher.cc:248-410) -----------------------------------------------------------------------------------
+// Builds the query records from the keyframe's FeatureVector: feature i of node N becomes a query with the slot of N in the
+// target frame's FeatureVector (-1 = node not shared: skipped, the reference's lower_bound jumps :376-385), its own angle and the
+// CLAIMS flag (every match blocks its keypoint, :300-301). Features outside the FeatureVector, or without a valid map point
+// (:283-289), stay SKIP. Queries are resolved in feature-index order, which is the reference's order inside every node.
+__global__ void __launch_bounds__(256)
+orb_bow_queries_kernel(const OrbKeypoint* __restrict__ kf_kps, const uint8_t* __restrict__ kf_valid, const int* __restrict__ kf_node,
+                       const int* __restrict__ kf_start, const int* __restrict__ kf_feature, const int* __restrict__ kf_count, int qcap,
+                       const int* __restrict__ f_node, const int* __restrict__ f_count, int cap, GuidedQuery* __restrict__ q,
+                       int* __restrict__ n_queries) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  kf_kps += (size_t)f * qcap; kf_valid += (size_t)f * qcap;
+  kf_node += (size_t)f * qcap; kf_start += (size_t)f * (qcap + 1); kf_feature += (size_t)f * qcap;
+  f_node += (size_t)f * cap;
+  q += (size_t)f * qcap;
+  for (int i = tid; i < qcap; i += 256) {
+    GuidedQuery e;
+    e.u = e.v = e.radius = e.ur = e.angle = 0.f;
+    e.min_level = e.max_level = -1;
+    e.flags = 1;   // SKIP
+    e.reserved = -1;
+    q[i] = e;
+  }
+  __syncthreads();
+  const int nk = min(kf_count[f], qcap), nf = min(f_count[f], cap);
+  const int total = nk > 0 ? kf_start[nk] : 0;
+  for (int e = tid; e < total; e += 256) {
+    int lo = 0, hi = nk;   // node slot of CSR entry e: last j with kf_start[j] <= e
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (kf_start[mid] <= e) lo = mid; else hi = mid; }
+    const int node = kf_node[lo];
+    int a = 0, b = nf;     // slot of the same node id in the target frame's (ascending) node list
+    while (a < b) { const int mid = (a + b) >> 1; if (f_node[mid] < node) a = mid + 1; else b = mid; }
+    const int slot = (a < nf && f_node[a] == node) ? a : -1;
+    const int i = kf_feature[e];
+    if (i >= 0 && i < qcap && kf_valid[i] && slot >= 0) {
+      q[i].angle = kf_kps[i].angle;
+      q[i].reserved = slot;
+      q[i].flags = 2;   // CLAIMS
+    }
+  }
+  if (tid == 0) n_queries[f] = qcap;
+}
+
+void orb_launch_search_by_bow(const uint8_t* kf_desc, const OrbKeypoint* kf_kps, const uint8_t* kf_valid, const int* kf_node, const int* kf_start,
+                              const int* kf_feature, const int* kf_count, int qcap, const uint8_t* f_desc, const OrbKeypoint* f_kps,
+                              const int* f_node, const int* f_start, const int* f_feature, const int* f_count, int cap, int frames, int th_dist,
+                              float nn_ratio, int check_orientation, void* queries, int* n_queries, uint2* lists, int* list_cnt, int* assigned,
+                              int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
+  GuidedQuery* q = static_cast<GuidedQuery*>(queries);
+  orb_bow_queries_kernel<<<frames, 256, 0, st>>>(kf_kps, kf_valid, kf_node, kf_start, kf_feature, kf_count, qcap, f_node, f_count, cap, q, n_queries);
+  orb_guided_candidates_kernel<true><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      nullptr, nullptr, f_start, f_feature, f_desc, nullptr, nullptr, cap, q, kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, lists, list_cnt);
+  const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
+  orb_guided_resolve_kernel<true><<<frames, 32, smem, st>>>(nullptr, nullptr, f_start, f_feature, f_kps, f_desc, nullptr, nullptr, cap, q, kf_desc,
+                                                            n_queries, qcap, 0.f, 0.f, 0.f, 0.f, th_dist, nn_ratio, 1, check_orientation, lists,
+                                                            list_cnt, assigned, query_match, nmatches);
   *launches += 3;
 }

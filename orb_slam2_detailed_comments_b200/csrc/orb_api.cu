@@ -29,6 +29,9 @@ void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaSt
 void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
+void orb_launch_search_by_bow(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, const uint8_t*,
+                              const OrbKeypoint*, const int*, const int*, const int*, const int*, int, int, int, float, int, void*, int*, uint2*, int*,
+                              int*, int*, int*, cudaStream_t, long long*);
 void orb_launch_undistort(const void*, const OrbKeypoint*, const int*, int, int, OrbKeypoint*, cudaStream_t);
 struct BowVoc {   // == bow.cu
   const int* child_start; const int* child_id; const uint4* child_desc; const uint8_t* is_leaf; const int* word_of; const double* word_weight;
@@ -765,6 +768,7 @@ struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mut
   std::mutex mu;
   DevBuf partial, q, db, out;
   // orb_search_by_projection: sorted keypoints + cell starts + per-query top-2, and the staging copies of host arguments
+  DevBuf g_bq, g_bnq, g_stage[16];   // orb_search_by_bow: device-built queries, staging of host arguments
   DevBuf g_items, g_cells, g_lists, g_lcnt, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
   int num_sms = 0;
 };
@@ -977,6 +981,63 @@ int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int
     CU(cudaMemcpyAsync(fv_start, d_fs, F * (cap + 1) * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(fv_feature, d_ff, F * cap * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(fv_count, d_fc, F * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORB_OK;
+}
+
+int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
+                      const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
+                      const orb_keypoint* f_kps, const int32_t* f_fv_node, const int32_t* f_fv_start, const int32_t* f_fv_feature,
+                      const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
+                      int32_t* nmatches, void* stream) {
+  const void* in[14] = {kf_desc, kf_kps_un, kf_valid, kf_fv_node, kf_fv_start, kf_fv_feature, kf_fv_count,
+                        f_desc,  f_kps,     f_fv_node, f_fv_start, f_fv_feature, f_fv_count, nullptr};
+  for (int i = 0; i < 13; ++i)
+    if (!in[i]) return fail(ORB_E_BADARG, "null argument");
+  if (!assigned || !nmatches) return fail(ORB_E_BADARG, "null argument");
+  if (cap <= 0 || cap >= (1 << 18) || qcap <= 0 || qcap >= (1 << 18) || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap, qcap < 2^18, frames > 0)");
+  if (th_dist < 0 || th_dist > 255 || !(nn_ratio > 0.f)) return fail(ORB_E_BADARG, "th_dist in [0, 255] and nn_ratio > 0 required");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const size_t F = (size_t)frames, Q = (size_t)qcap, N = (size_t)cap;
+  const bool host = mem != ORB_MEM_DEVICE;
+  int* d_assigned = assigned;
+  int* d_nm = nmatches;
+  if (host) {
+    const size_t bytes[13] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
+                              F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4};
+    for (int i = 0; i < 13; ++i) {
+      if ((rc = ws->g_stage[i].ensure(bytes[i])) != ORB_OK) return rc;
+      CU(cudaMemcpyAsync(ws->g_stage[i].p, in[i], bytes[i], cudaMemcpyHostToDevice, st));
+      in[i] = ws->g_stage[i].p;
+    }
+    if ((rc = ws->g_assigned.ensure(F * N * sizeof(int))) != ORB_OK) return rc;
+    if ((rc = ws->g_nm.ensure(F * sizeof(int))) != ORB_OK) return rc;
+    d_assigned = ws->g_assigned.as<int>();
+    d_nm = ws->g_nm.as<int>();
+  }
+  if ((rc = ws->g_bq.ensure(F * Q * 32)) != ORB_OK) return rc;
+  if ((rc = ws->g_bnq.ensure(F * sizeof(int))) != ORB_OK) return rc;
+  if ((rc = ws->g_qmatch.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
+  if ((rc = ws->g_lists.ensure(F * Q * 32 * sizeof(uint2))) != ORB_OK) return rc;
+  if ((rc = ws->g_lcnt.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
+  long long launched = 0;
+  orb_launch_search_by_bow((const uint8_t*)in[0], (const OrbKeypoint*)in[1], (const uint8_t*)in[2], (const int*)in[3], (const int*)in[4],
+                           (const int*)in[5], (const int*)in[6], qcap, (const uint8_t*)in[7], (const OrbKeypoint*)in[8], (const int*)in[9],
+                           (const int*)in[10], (const int*)in[11], (const int*)in[12], cap, frames, th_dist, nn_ratio, check_orientation,
+                           ws->g_bq.p, ws->g_bnq.as<int>(), ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, ws->g_qmatch.as<int>(),
+                           d_nm, st, &launched);
+  orb_knn_count_launches(launched);
+  CU(cudaGetLastError());
+  if (host) {
+    CU(cudaMemcpyAsync(assigned, d_assigned, F * N * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
   }
   return ORB_OK;
