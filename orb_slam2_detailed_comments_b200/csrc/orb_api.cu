@@ -81,6 +81,7 @@ struct DevBuf {
   template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+#define ORB_MAX_WS 4
 struct orb_extractor {
   orb_params prm;
   int device = 0, num_sms = 148;
@@ -105,15 +106,17 @@ struct orb_extractor {
     DevBuf q_key, q_knode, q_kchild, q_bbox, q_ncount, q_pidx, q_best, q_ordA, q_ordB, q_par, q_cand, q_ccnt, q_cslot, q_scan, q_rawn;
     DevBuf* all[25] = {&st_rows, &st_sorted, &st_sad, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
                        &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
-  } ws[2];
+  } ws[ORB_MAX_WS];
+  int nws = 2;             // compute streams / workspaces in use (ORB_B200_STREAMS, 1..ORB_MAX_WS)
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
   cudaEvent_t ev_fork = nullptr;
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  // Output staging is triple-buffered: pass p+2 runs on the workspace of pass p and must not wait for pass p's D2H copy.
-  DevBuf stage_in[2], out_kps[3], out_desc[3], out_ur[3], out_dp[3];
+  // Output staging has one buffer more than there are workspaces: pass p + nws runs on the workspace of pass p and must not
+  // wait for pass p's D2H copy.
+  DevBuf stage_in[2], out_kps[ORB_MAX_WS + 1], out_desc[ORB_MAX_WS + 1], out_ur[ORB_MAX_WS + 1], out_dp[ORB_MAX_WS + 1];
   DevBuf cnt_all;   // per call: counts [batch], level counts [batch][nlevels], stereo matches [batch/2]; one D2H at the end
-  cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[3] = {}, ev_staged[2] = {};   // ev_staged: level 0 has consumed stage_in[b]
+  cudaEvent_t ev_in[2] = {}, ev_done[ORB_MAX_WS] = {}, ev_out[ORB_MAX_WS + 1] = {}, ev_staged[2] = {};   // ev_staged: level 0 has consumed stage_in[b]
   size_t h_cnt_cap = 0;    // ints in h_cnt
   int* h_err = nullptr;    // pinned
   int* h_cnt = nullptr;    // pinned [batch * (1 + nlevels)]: counts, then per-level counts
@@ -287,13 +290,17 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
   }
   const OrbGeom& g = e->geom;
   const int want = std::min(batch, default_chunk(g));
-  if (want > e->chunk || cap > e->cap_ws || (batch > e->chunk && e->ws[1].pyr.p == nullptr)) {
-    for (int w = 0; w < 2; ++w) CU(cudaStreamSynchronize(e->ws[w].st));
-    const size_t B = (size_t)std::max(want, e->chunk);
+  const int chunk_now = std::max(want, e->chunk);
+  const int ws_needed = std::min(e->nws, (batch + chunk_now - 1) / chunk_now);   // later workspaces only exist once a call needs them
+  if (want > e->chunk || cap > e->cap_ws || e->ws[ws_needed - 1].pyr.p == nullptr) {
+    for (int w = 0; w < ORB_MAX_WS; ++w) CU(cudaStreamSynchronize(e->ws[w].st));
+    const size_t B = (size_t)chunk_now;
     const int capw = std::max(cap, e->cap_ws);
     const int nl = g.nlevels;
     if ((rc = e->err.ensure(sizeof(int))) != ORB_OK) return rc;
-    const int nws = (batch > (int)B) ? 2 : 1;   // the second workspace only exists once a call needs more than one pass
+    int nws = ws_needed;
+    for (int w = 0; w < ORB_MAX_WS; ++w)
+      if (e->ws[w].pyr.p) nws = std::max(nws, w + 1);   // existing workspaces grow with the others
     for (int w = 0; w < nws; ++w) {
       orb_extractor::PassWs& P = e->ws[w];
 #define ENS(buf, bytes) if ((rc = P.buf.ensure(bytes)) != ORB_OK) return rc
@@ -372,8 +379,7 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
 
 static void resolve_stage_events(orb_extractor* e) {
   if (e->ev_used == 0) return;
-  cudaStreamSynchronize(e->stream);
-  cudaStreamSynchronize(e->ws[1].st);
+  for (int w = 0; w < ORB_MAX_WS; ++w) cudaStreamSynchronize(e->ws[w].st);
   for (size_t b = 0; b + ORB_NUM_STAGES < e->ev_used; b += ORB_NUM_STAGES + 1) {
     for (int i = 0; i < ORB_NUM_STAGES; ++i) {
       float ms = 0.f;
@@ -386,7 +392,7 @@ static void resolve_stage_events(orb_extractor* e) {
 
 static int check_err_flag(orb_extractor* e) {
   int flag = 0;
-  CU(cudaStreamSynchronize(e->ws[1].st));
+  for (int w = 1; w < ORB_MAX_WS; ++w) CU(cudaStreamSynchronize(e->ws[w].st));
   CU(cudaMemcpyAsync(&flag, e->err.p, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   CU(cudaGetLastError());
@@ -426,11 +432,14 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
   cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
-  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->ws[1].st, cudaStreamNonBlocking);
-  if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[1].ev_join, cudaEventDisableTiming);
+  for (int w = 1; w < ORB_MAX_WS; ++w) {
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->ws[w].st, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_join, cudaEventDisableTiming);
+  }
+  if (const char* s = getenv("ORB_B200_STREAMS")) e->nws = std::min(std::max(atoi(s), 1), ORB_MAX_WS);
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
-  if (ce != cudaSuccess) { delete e; return fail(ORB_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce)); }
   e->ws[0].st = e->stream;
+  if (ce != cudaSuccess) { orb_extractor_destroy(e); return fail(ORB_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce)); }
   *out = e;
   return ORB_OK;
 }
@@ -439,23 +448,26 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (!e) return;
   cudaSetDevice(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
-  if (e->ws[1].st) { cudaStreamSynchronize(e->ws[1].st); cudaStreamDestroy(e->ws[1].st); }
-  if (e->ws[1].ev_join) cudaEventDestroy(e->ws[1].ev_join);
+  for (int w = 1; w < ORB_MAX_WS; ++w) {
+    if (e->ws[w].st) { cudaStreamSynchronize(e->ws[w].st); cudaStreamDestroy(e->ws[w].st); }
+    if (e->ws[w].ev_join) cudaEventDestroy(e->ws[w].ev_join);
+  }
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
-  for (int w = 0; w < 2; ++w)
+  for (int w = 0; w < ORB_MAX_WS; ++w)
     for (DevBuf* b : e->ws[w].all) b->release();
   DevBuf* bufs[] = {&e->tabs, &e->err, &e->cnt_all, &e->stage_in[0], &e->stage_in[1]};
   for (DevBuf* b : bufs) b->release();
-  for (int b = 0; b < 3; ++b) { e->out_kps[b].release(); e->out_desc[b].release(); e->out_ur[b].release(); e->out_dp[b].release(); }
+  for (int b = 0; b <= ORB_MAX_WS; ++b) { e->out_kps[b].release(); e->out_desc[b].release(); e->out_ur[b].release(); e->out_dp[b].release(); }
   if (e->h_cnt) cudaFreeHost(e->h_cnt);
   if (e->s_in) cudaStreamDestroy(e->s_in);
   if (e->s_out) cudaStreamDestroy(e->s_out);
   for (int b = 0; b < 2; ++b) {
     if (e->ev_in[b]) cudaEventDestroy(e->ev_in[b]);
-    if (e->ev_done[b]) cudaEventDestroy(e->ev_done[b]);
     if (e->ev_staged[b]) cudaEventDestroy(e->ev_staged[b]);
   }
-  for (int b = 0; b < 3; ++b)
+  for (int b = 0; b < ORB_MAX_WS; ++b)
+    if (e->ev_done[b]) cudaEventDestroy(e->ev_done[b]);
+  for (int b = 0; b <= ORB_MAX_WS; ++b)
     if (e->ev_out[b]) cudaEventDestroy(e->ev_out[b]);
   for (cudaEvent_t ev : e->ev)
     if (ev) cudaEventDestroy(ev);
@@ -513,21 +525,21 @@ int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, 
   int rc = ensure_shape(e, width, height, batch, cap);
   if (rc != ORB_OK) return rc;
   const long long istride = (long long)step * height;
-  // passes alternate between the two workspaces / streams; stage profiling keeps everything on the public stream
-  const bool two = batch > e->chunk && !e->profile;
-  if (two) {
+  // passes rotate over the workspaces / streams; stage profiling keeps everything on the public stream
+  const int used = e->profile ? 1 : std::min(e->nws, (batch + e->chunk - 1) / e->chunk);
+  if (used > 1) {
     CU(cudaEventRecord(e->ev_fork, e->stream));
-    CU(cudaStreamWaitEvent(e->ws[1].st, e->ev_fork, 0));
+    for (int w = 1; w < used; ++w) CU(cudaStreamWaitEvent(e->ws[w].st, e->ev_fork, 0));
   }
   int pass = 0;
   for (int f0 = 0; f0 < batch; f0 += e->chunk, ++pass) {
     const int n = std::min(e->chunk, batch - f0);
-    run_pass(e, two ? (pass & 1) : 0, images + (long long)f0 * istride, step, istride, n,
+    run_pass(e, pass % used, images + (long long)f0 * istride, step, istride, n,
              reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap, desc + (long long)f0 * cap * 32, cap, counts_dev + f0);
   }
-  if (two) {
-    CU(cudaEventRecord(e->ws[1].ev_join, e->ws[1].st));
-    CU(cudaStreamWaitEvent(e->stream, e->ws[1].ev_join, 0));
+  for (int w = 1; w < used; ++w) {
+    CU(cudaEventRecord(e->ws[w].ev_join, e->ws[w].st));
+    CU(cudaStreamWaitEvent(e->stream, e->ws[w].ev_join, 0));
   }
   CU(cudaGetLastError());
   if (sync) return check_err_flag(e);
@@ -560,30 +572,32 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
   const int nl = g.nlevels;
   const bool host_out = out_mem != ORB_MEM_DEVICE;
   if (sr && e->chunk < 2) return fail(ORB_E_BADARG, "stereo needs passes of at least 2 frames (ORB_B200_CHUNK)");
-  // Three streams, two buffer sets: the H2D copy of pass p+1 and the D2H copy of pass p-1 overlap the kernels of pass p.
+  // A copy-in and a copy-out stream beside the compute streams: the H2D copy of pass p+1 and the D2H copy of pass p-1 overlap the
+  // kernels of pass p.
   if (!e->s_in) {
     CU(cudaStreamCreateWithFlags(&e->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     for (int b = 0; b < 2; ++b) {
       CU(cudaEventCreateWithFlags(&e->ev_in[b], cudaEventDisableTiming));
-      CU(cudaEventCreateWithFlags(&e->ev_done[b], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&e->ev_staged[b], cudaEventDisableTiming));
     }
-    for (int b = 0; b < 3; ++b) CU(cudaEventCreateWithFlags(&e->ev_out[b], cudaEventDisableTiming));
+    for (int b = 0; b < ORB_MAX_WS; ++b) CU(cudaEventCreateWithFlags(&e->ev_done[b], cudaEventDisableTiming));
+    for (int b = 0; b <= ORB_MAX_WS; ++b) CU(cudaEventCreateWithFlags(&e->ev_out[b], cudaEventDisableTiming));
   }
   const size_t fbytes = (size_t)step * height;   // frames are staged with the caller's pitch (level 0 reads any pitch)
   const int nbuf = batch > e->chunk ? 2 : 1;
-  const int nout = batch > 2 * e->chunk ? 3 : nbuf;
+  const int nused = e->profile ? 1 : std::min(e->nws, (batch + e->chunk - 1) / e->chunk);   // workspaces ensure_shape has sized
+  const int nout = batch > e->chunk ? nused + 1 : 1;
   if ((rc = e->cnt_all.ensure((size_t)batch * (2 + nl) * sizeof(int))) != ORB_OK) return rc;
-  for (int b = 0; b < nout; ++b) {
+  for (int b = 0; b < std::max(nout, nused); ++b) {
     if (b < nbuf && (rc = e->stage_in[b].ensure((size_t)e->chunk * fbytes)) != ORB_OK) return rc;
-    if (host_out) {
+    if (host_out && b < nout) {
       if ((rc = e->out_kps[b].ensure((size_t)e->chunk * cap * sizeof(OrbKeypoint))) != ORB_OK) return rc;
       if ((rc = e->out_desc[b].ensure((size_t)e->chunk * cap * 32)) != ORB_OK) return rc;
       if (sr && (rc = e->out_ur[b].ensure((size_t)e->chunk / 2 * cap * sizeof(float) + 16)) != ORB_OK) return rc;
       if (sr && (rc = e->out_dp[b].ensure((size_t)e->chunk / 2 * cap * sizeof(float) + 16)) != ORB_OK) return rc;
     }
-    if (sr && b < nbuf) {
+    if (sr && b < nused) {
       if ((rc = e->ws[b].st_sad.ensure((size_t)e->chunk / 2 * cap * sizeof(int) + 16)) != ORB_OK) return rc;
       if ((rc = e->ws[b].st_rows.ensure((size_t)e->chunk / 2 * (g.lv[0].rows + 1) * sizeof(int) + 16)) != ORB_OK) return rc;
       if ((rc = e->ws[b].st_sorted.ensure((size_t)e->chunk / 2 * cap * sizeof(unsigned short) + 16)) != ORB_OK) return rc;
@@ -629,7 +643,7 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
     }
     if (sr && (n & 1)) n = n < full ? n + 1 : n - 1;   // a pair never straddles two passes (batch is even, chunk >= 2)
     n = std::min(n, batch - f0);
-    const int b = pass & 1, ob = pass % 3;
+    const int b = pass & 1, ob = pass % nout;
     // ---- copy-in stream: stage_in[b] is free once level 0 of pass-2 has read it (the rest of that pass works on the pyramid)
     if (pass >= 2) CU(cudaStreamWaitEvent(e->s_in, e->ev_staged[b], 0));
     tmark(e->s_in);
@@ -643,11 +657,11 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
     }
     CU(cudaEventRecord(e->ev_in[b], e->s_in));
     tmark(e->s_in);
-    // ---- compute stream of workspace w (= b unless stage profiling serialises everything on the public stream)
-    const int w = e->profile ? 0 : b;
+    // ---- compute stream of workspace w (stage profiling serialises everything on the public stream)
+    const int w = pass % nused;
     orb_extractor::PassWs& P = e->ws[w];
     CU(cudaStreamWaitEvent(P.st, e->ev_in[b], 0));
-    if (pass >= 3) CU(cudaStreamWaitEvent(P.st, e->ev_out[ob], 0));   // output staging [ob] drained (pass - 3)
+    if (pass >= nout) CU(cudaStreamWaitEvent(P.st, e->ev_out[ob], 0));   // output staging [ob] drained (pass - nout)
     tmark(P.st);
     OrbKeypoint* dk = host_out ? e->out_kps[ob].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
     uint8_t* dd = host_out ? e->out_desc[ob].as<uint8_t>() : desc + (long long)f0 * cap * 32;
@@ -660,10 +674,10 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
       orb_launch_stereo(P.pyr.as<uint8_t>(), dk, dd, d_counts + f0, cap, sr->bf, sr->b, dur, ddp, P.st_sad.as<int>(),
                         d_matched + f0 / 2, P.st_rows.as<int>(), P.st_sorted.as<unsigned short>(), g, n / 2, P.st, &e->launches);
     }
-    CU(cudaEventRecord(e->ev_done[b], P.st));
+    CU(cudaEventRecord(e->ev_done[w], P.st));
     tmark(P.st);
     // ---- copy-out stream; the count arrays of all passes are fetched once, after the last pass
-    CU(cudaStreamWaitEvent(e->s_out, e->ev_done[b], 0));
+    CU(cudaStreamWaitEvent(e->s_out, e->ev_done[w], 0));
     if (host_out) {
       CU(cudaMemcpyAsync(kps + (long long)f0 * cap, dk, (size_t)n * cap * sizeof(OrbKeypoint), cudaMemcpyDeviceToHost, e->s_out));
       CU(cudaMemcpyAsync(desc + (long long)f0 * cap * 32, dd, (size_t)n * cap * 32, cudaMemcpyDeviceToHost, e->s_out));
@@ -679,14 +693,14 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
     tn.push_back(n);
     if (trace) thost.push_back(host_ms());
   }
-  // s_out has waited for the last pass of either compute stream (ev_done of the last two passes), so all counts are final
+  // s_out has waited for every pass (ev_done of each), so all counts are final
   CU(cudaMemcpyAsync(h_counts, d_counts, (size_t)batch * (2 + nl) * sizeof(int), cudaMemcpyDeviceToHost, e->s_out));
   CU(cudaStreamSynchronize(e->s_out));
   if (trace) {
     fprintf(stderr, "host: all passes issued at %.3f ms, outputs on the host at %.3f ms after entry; pass issue times:", thost.back(), host_ms());
     for (double t : thost) fprintf(stderr, " %.3f", t);
     fprintf(stderr, "\n");
-    for (int w = 0; w < 2; ++w) cudaStreamSynchronize(e->ws[w].st);
+    for (int w = 0; w < ORB_MAX_WS; ++w) cudaStreamSynchronize(e->ws[w].st);
     fprintf(stderr, "pass frames | h2d start..end | compute start..end | d2h end   (ms since the first copy was issued)\n");
     for (size_t p = 0; p * 5 + 4 < tev.size(); ++p) {
       float t[5];
