@@ -1,85 +1,19 @@
-// C ABI (include/orb_b200.h) over the sm_100a kernels. Host logic only: parameter tables exactly as the
+// C ABI (include/orb_b200.h) over the sm_100a kernels, extractor part. Host logic only: parameter tables exactly as the
 // reference constructor computes them (src/ORBextractor.cc:776-925), per-shape geometry, workspaces, launches.
 // No CPU fallback: every compute entry point needs a CUDA device.
-#include <algorithm>
-#include <cmath>
-#include <cstdarg>
-#include <cstdio>
-#include <cstring>
-#include <mutex>
-#include <chrono>
-#include <vector>
-
-#include "../../include/orb_b200.h"
-#include "orb_common.cuh"
-
-// ---- kernel launchers (other translation units) -------------------------------------------------------------
-struct OrbKnn2;
-void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const OrbGeom&, int, cudaStream_t, long long*, cudaEvent_t);
-void orb_launch_fast(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t*, int*, int*, const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_describe(const uint8_t*, const uint8_t*, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
-                         const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, int, float, float, float*, float*, int*, int*, int*,
-                       unsigned short*, const OrbGeom&, int, cudaStream_t, long long*);
-int orb_knn_num_chunks(int Q, long long D, int num_sms);
-void orb_launch_knn(const uint8_t*, int, const uint8_t*, long long, long long, int, unsigned long long*, int, OrbKnn2*, cudaStream_t);
-void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaStream_t);
-void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
-long long orb_knn_launches();
-void orb_knn_count_launches(long long n);
-void orb_launch_search_by_bow(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, const uint8_t*,
-                              const OrbKeypoint*, const int*, const int*, const int*, const int*, int, int, int, float, int, void*, int*, uint2*, int*,
-                              int*, int*, int*, cudaStream_t, long long*);
-void orb_launch_undistort(const void*, const OrbKeypoint*, const int*, int, int, OrbKeypoint*, cudaStream_t);
-struct BowVoc {   // == bow.cu
-  const int* child_start; const int* child_id; const uint4* child_desc; const uint8_t* is_leaf; const int* word_of; const double* word_weight;
-  int L;
-};
-void orb_launch_bow(const BowVoc&, int, const uint8_t*, const int*, int, int, int*, int*, int*, double*, int*, int*, int*, int*, int*,
-                    cudaStream_t, long long*);
-
-void orb_launch_distinctive(const uint8_t*, const long long*, int, int*, int*, cudaStream_t);
-void orb_launch_guided(const OrbKeypoint*, const uint8_t*, const float*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*,
-                       int, int, float, float, float, float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
-double orb_popc_peak(int num_sms);
-
-static_assert(sizeof(orb_keypoint) == 28 && sizeof(OrbKeypoint) == 28, "cv::KeyPoint layout");
-static_assert(sizeof(orb_knn2) == 24, "orb_knn2 layout");
+#include "orb_host.h"
 
 // ---- errors ------------------------------------------------------------------------------------------
 static thread_local char t_err[512] = "";
-static int fail(int code, const char* fmt, ...) {
+int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(t_err, sizeof(t_err), fmt, ap);
   va_end(ap);
   return code;
 }
-#define CU(call)                                                                                         \
-  do {                                                                                                   \
-    cudaError_t e_ = (call);                                                                             \
-    if (e_ != cudaSuccess) return fail(ORB_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
-  } while (0)
 
 static inline int cv_round_f(float v) { return (int)lrintf(v); }
-
-struct DevBuf {
-  void* p = nullptr;
-  size_t bytes = 0;
-  int ensure(size_t need) {
-    if (need <= bytes) return ORB_OK;
-    if (p) cudaFree(p);
-    p = nullptr; bytes = 0;
-    cudaError_t e = cudaMalloc(&p, need);
-    if (e != cudaSuccess) return fail(ORB_E_CUDA, "cudaMalloc(%zu): %s", need, cudaGetErrorString(e));
-    bytes = need;
-    return ORB_OK;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
-  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
-};
 
 #define ORB_MAX_WS 4
 struct orb_extractor {
@@ -775,453 +709,6 @@ int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keyp
     out[i].octave = 0; out[i].class_id = -1;
   }
   return n;
-}
-
-// ---- matcher ------------------------------------------------------------------------------------------------
-struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mutex (calls on one device serialise their setup)
-  std::mutex mu;
-  DevBuf partial, q, db, out;
-  // orb_search_by_projection: sorted keypoints + cell starts + per-query top-2, and the staging copies of host arguments
-  DevBuf g_bq, g_bnq, g_stage[16];   // orb_search_by_bow: device-built queries, staging of host arguments
-  DevBuf g_items, g_cells, g_lists, g_lcnt, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
-  int num_sms = 0;
-};
-static KnnWorkspace g_knn_ws[16];
-
-static int current_device_ws(KnnWorkspace** ws) {
-  int dev = 0;
-  CU(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 16) return fail(ORB_E_BADARG, "device index %d unsupported", dev);
-  *ws = &g_knn_ws[dev];
-  if ((*ws)->num_sms == 0) {
-    cudaDeviceProp prop;
-    CU(cudaGetDeviceProperties(&prop, dev));
-    (*ws)->num_sms = prop.multiProcessorCount;
-  }
-  return ORB_OK;
-}
-
-int orb_hamming_knn(const uint8_t* query, int q_mem, int Q, const uint8_t* db, int db_mem, int64_t D, int64_t index_base,
-                    int sentinel, orb_knn2* out, int out_mem, void* stream) {
-  if (!query || !out || Q <= 0 || D < 0 || (D > 0 && !db) || sentinel < 1) return fail(ORB_E_BADARG, "bad argument");
-  if (index_base < 0 || index_base + D >= (1LL << 40)) return fail(ORB_E_BADARG, "index range exceeds 2^40");
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  KnnWorkspace* ws;
-  int rc = current_device_ws(&ws);
-  if (rc != ORB_OK) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  std::lock_guard<std::mutex> lk(ws->mu);
-  const uint8_t* dq = query;
-  const uint8_t* ddb = db;
-  orb_knn2* dout = out;
-  const bool any_host = q_mem != ORB_MEM_DEVICE || db_mem != ORB_MEM_DEVICE || out_mem != ORB_MEM_DEVICE;
-  if (q_mem != ORB_MEM_DEVICE || ((uintptr_t)query & 15)) {
-    if ((rc = ws->q.ensure((size_t)Q * 32)) != ORB_OK) return rc;
-    CU(cudaMemcpyAsync(ws->q.p, query, (size_t)Q * 32, q_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
-    dq = ws->q.as<uint8_t>();
-  }
-  if (D > 0 && (db_mem != ORB_MEM_DEVICE || ((uintptr_t)db & 15))) {
-    if ((rc = ws->db.ensure((size_t)D * 32)) != ORB_OK) return rc;
-    CU(cudaMemcpyAsync(ws->db.p, db, (size_t)D * 32, db_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
-    ddb = ws->db.as<uint8_t>();
-  }
-  if (out_mem != ORB_MEM_DEVICE) {
-    if ((rc = ws->out.ensure((size_t)Q * sizeof(orb_knn2))) != ORB_OK) return rc;
-    dout = ws->out.as<orb_knn2>();
-  }
-  const int nchunks = orb_knn_num_chunks(Q, D, ws->num_sms);
-  if ((rc = ws->partial.ensure((size_t)nchunks * Q * 2 * sizeof(unsigned long long))) != ORB_OK) return rc;
-  orb_launch_knn(dq, Q, ddb, D, index_base, sentinel, ws->partial.as<unsigned long long>(), nchunks, (OrbKnn2*)dout, st);
-  CU(cudaGetLastError());
-  if (out_mem != ORB_MEM_DEVICE) CU(cudaMemcpyAsync(out, dout, (size_t)Q * sizeof(orb_knn2), cudaMemcpyDeviceToHost, st));
-  if (any_host) CU(cudaStreamSynchronize(st));
-  return ORB_OK;
-}
-
-int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentinel, orb_knn2* out, void* stream) {
-  if (!shards || !out || nshards < 1 || Q <= 0) return fail(ORB_E_BADARG, "bad argument");
-  orb_launch_knn_merge_shards((const OrbKnn2*)shards, nshards, Q, sentinel, (OrbKnn2*)out, (cudaStream_t)stream);
-  CU(cudaGetLastError());
-  return ORB_OK;
-}
-
-int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream) {
-  if (!a || !b || !out || n < 0) return fail(ORB_E_BADARG, "bad argument");
-  if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return fail(ORB_E_BADARG, "descriptor arrays must be 16-byte aligned");
-  if (n == 0) return ORB_OK;
-  orb_launch_distance_batch(a, b, n, out, (cudaStream_t)stream);
-  CU(cudaGetLastError());
-  return ORB_OK;
-}
-
-int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out) {
-  if (!a || !b || !out || n < 0) return fail(ORB_E_BADARG, "bad argument");
-  if (n == 0) return ORB_OK;
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  KnnWorkspace* ws;
-  int rc = current_device_ws(&ws);
-  if (rc != ORB_OK) return rc;
-  std::lock_guard<std::mutex> lk(ws->mu);
-  if ((rc = ws->q.ensure((size_t)n * 32)) != ORB_OK) return rc;
-  if ((rc = ws->db.ensure((size_t)n * 32)) != ORB_OK) return rc;
-  if ((rc = ws->out.ensure((size_t)n * sizeof(int))) != ORB_OK) return rc;
-  CU(cudaMemcpyAsync(ws->q.p, a, (size_t)n * 32, cudaMemcpyHostToDevice, 0));
-  CU(cudaMemcpyAsync(ws->db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice, 0));
-  orb_launch_distance_batch(ws->q.as<uint8_t>(), ws->db.as<uint8_t>(), n, ws->out.as<int>(), 0);
-  CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(out, ws->out.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, 0));
-  CU(cudaStreamSynchronize(0));
-  return ORB_OK;
-}
-
-int64_t orb_matcher_launch_count(void) { return orb_knn_launches(); }
-
-// ---- vocabulary / ComputeBoW ------------------------------------------------------------------------------------------------
-
-struct orb_vocabulary {
-  int device = 0, k = 0, L = 0, n_nodes = 0, n_words = 0;
-  DevBuf child_start, child_id, child_desc, is_leaf, word_of, word_weight;
-  DevBuf s_desc, s_n, s_word, s_node, s_bw, s_bv, s_bc, s_fn, s_fs, s_ff, s_fc;   // staging for host-memory calls
-  std::mutex mu;
-};
-
-int orb_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc,
-                          const double* weight, int device, orb_vocabulary** out) {
-  if (!out) return fail(ORB_E_BADARG, "null argument");
-  *out = nullptr;
-  if (!parent || !is_leaf || !desc || !weight || k < 1 || L < 1 || n_nodes < 2) return fail(ORB_E_BADARG, "bad vocabulary arguments");
-  std::vector<int> cnt(n_nodes + 1, 0);
-  for (int i = 1; i < n_nodes; ++i) {
-    if (parent[i] < 0 || parent[i] >= n_nodes || parent[i] == i) return fail(ORB_E_BADARG, "node %d: parent %d out of range", i, parent[i]);
-    if (is_leaf[parent[i]] && parent[i] != 0) return fail(ORB_E_BADARG, "node %d hangs below leaf %d", i, parent[i]);
-    ++cnt[parent[i] + 1];
-  }
-  for (int i = 1; i < n_nodes; ++i)
-    if (!is_leaf[i] && cnt[i + 1] == 0) return fail(ORB_E_BADARG, "inner node %d has no children", i);
-  if (cnt[1] == 0) return fail(ORB_E_BADARG, "root has no children");
-  std::vector<int> start(n_nodes + 1, 0);
-  for (int i = 0; i < n_nodes; ++i) start[i + 1] = start[i] + cnt[i + 1];
-  const int slots = start[n_nodes];   // == n_nodes - 1
-  std::vector<int> cursor(start.begin(), start.end() - 1), child_id(slots), word_of(n_nodes, -1);
-  std::vector<uint8_t> child_desc((size_t)slots * 32), leaf(n_nodes, 0);
-  std::vector<double> word_weight;
-  for (int i = 1; i < n_nodes; ++i) {   // file order: children in push_back order, words numbered as the leaves appear
-    const int s = cursor[parent[i]]++;
-    child_id[s] = i;
-    memcpy(&child_desc[(size_t)s * 32], desc + (size_t)i * 32, 32);
-    leaf[i] = is_leaf[i] ? 1 : 0;
-    if (leaf[i]) { word_of[i] = (int)word_weight.size(); word_weight.push_back(weight[i]); }
-  }
-  // a walk deeper than n_nodes levels would mean a cycle; parents precede nothing in particular, so check by depth
-  for (int i = 1; i < n_nodes; ++i) {
-    int d = 0, p = i;
-    while (p != 0 && d <= n_nodes) { p = parent[p]; ++d; }
-    if (p != 0) return fail(ORB_E_BADARG, "node %d is not connected to the root", i);
-  }
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  CU(cudaSetDevice(device));
-  orb_vocabulary* v = new orb_vocabulary;
-  v->device = device; v->k = k; v->L = L; v->n_nodes = n_nodes; v->n_words = (int)word_weight.size();
-  struct Up { DevBuf* b; const void* src; size_t bytes; } ups[] = {
-      {&v->child_start, start.data(), start.size() * sizeof(int)}, {&v->child_id, child_id.data(), child_id.size() * sizeof(int)},
-      {&v->child_desc, child_desc.data(), child_desc.size()},      {&v->is_leaf, leaf.data(), leaf.size()},
-      {&v->word_of, word_of.data(), word_of.size() * sizeof(int)}, {&v->word_weight, word_weight.data(), word_weight.size() * sizeof(double)}};
-  for (const Up& u : ups) {
-    int rc = u.b->ensure(std::max<size_t>(u.bytes, 16));
-    if (rc == ORB_OK && cudaMemcpy(u.b->p, u.src, u.bytes, cudaMemcpyHostToDevice) != cudaSuccess) rc = fail(ORB_E_CUDA, "vocabulary upload failed");
-    if (rc != ORB_OK) { orb_vocabulary_destroy(v); return rc; }
-  }
-  *out = v;
-  return ORB_OK;
-}
-
-void orb_vocabulary_destroy(orb_vocabulary* v) {
-  if (!v) return;
-  cudaSetDevice(v->device);
-  DevBuf* bufs[] = {&v->child_start, &v->child_id, &v->child_desc, &v->is_leaf, &v->word_of, &v->word_weight, &v->s_desc, &v->s_n, &v->s_word,
-                    &v->s_node, &v->s_bw, &v->s_bv, &v->s_bc, &v->s_fn, &v->s_fs, &v->s_ff, &v->s_fc};
-  for (DevBuf* b : bufs) b->release();
-  delete v;
-}
-
-int orb_vocabulary_words(const orb_vocabulary* v) { return v ? v->n_words : 0; }
-
-int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int32_t* n, int cap, int frames, int levelsup, int32_t* word,
-                      int32_t* node, int32_t* bow_word, double* bow_value, int32_t* bow_count, int32_t* fv_node, int32_t* fv_start,
-                      int32_t* fv_feature, int32_t* fv_count, void* stream) {
-  if (!v || !desc || !n || !bow_word || !bow_value || !bow_count || !fv_node || !fv_start || !fv_feature || !fv_count)
-    return fail(ORB_E_BADARG, "null argument");
-  if (cap <= 0 || cap > 16384 || frames <= 0 || levelsup < 0) return fail(ORB_E_BADARG, "bad size (0 < cap <= 16384, frames > 0, levelsup >= 0)");
-  std::lock_guard<std::mutex> lk(v->mu);
-  CU(cudaSetDevice(v->device));
-  cudaStream_t st = (cudaStream_t)stream;
-  const size_t F = (size_t)frames;
-  const bool host = mem != ORB_MEM_DEVICE;
-  int rc;
-  const uint8_t* d_desc = desc; const int* d_n = n;
-  int *d_word = word, *d_node = node, *d_bw = bow_word, *d_bc = bow_count, *d_fn = fv_node, *d_fs = fv_start, *d_ff = fv_feature, *d_fc = fv_count;
-  double* d_bv = bow_value;
-  if (host) {
-    struct S { DevBuf* b; size_t bytes; } st_bufs[] = {{&v->s_desc, F * cap * 32}, {&v->s_n, F * 4}, {&v->s_bw, F * cap * 4}, {&v->s_bv, F * cap * 8},
-                                                      {&v->s_bc, F * 4}, {&v->s_fn, F * cap * 4}, {&v->s_fs, F * (cap + 1) * 4},
-                                                      {&v->s_ff, F * cap * 4}, {&v->s_fc, F * 4}};
-    for (const S& s : st_bufs) if ((rc = s.b->ensure(s.bytes)) != ORB_OK) return rc;
-    CU(cudaMemcpyAsync(v->s_desc.p, desc, F * cap * 32, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(v->s_n.p, n, F * 4, cudaMemcpyHostToDevice, st));
-    d_desc = v->s_desc.as<uint8_t>(); d_n = v->s_n.as<int>();
-    d_bw = v->s_bw.as<int>(); d_bv = v->s_bv.as<double>(); d_bc = v->s_bc.as<int>();
-    d_fn = v->s_fn.as<int>(); d_fs = v->s_fs.as<int>(); d_ff = v->s_ff.as<int>(); d_fc = v->s_fc.as<int>();
-  } else if ((uintptr_t)desc & 15) {
-    return fail(ORB_E_BADARG, "descriptor array must be 16-byte aligned device memory");
-  }
-  if (host || !word) { if ((rc = v->s_word.ensure(F * cap * 4)) != ORB_OK) return rc; d_word = v->s_word.as<int>(); }
-  if (host || !node) { if ((rc = v->s_node.ensure(F * cap * 4)) != ORB_OK) return rc; d_node = v->s_node.as<int>(); }
-  BowVoc V{v->child_start.as<int>(), v->child_id.as<int>(), v->child_desc.as<uint4>(), v->is_leaf.as<uint8_t>(), v->word_of.as<int>(),
-           v->word_weight.as<double>(), v->L};
-  long long launched = 0;
-  orb_launch_bow(V, levelsup, d_desc, d_n, cap, frames, d_word, d_node, d_bw, d_bv, d_bc, d_fn, d_fs, d_ff, d_fc, st, &launched);
-  orb_knn_count_launches(launched);
-  CU(cudaGetLastError());
-  if (host) {
-    if (word) CU(cudaMemcpyAsync(word, d_word, F * cap * 4, cudaMemcpyDeviceToHost, st));
-    if (node) CU(cudaMemcpyAsync(node, d_node, F * cap * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(bow_word, d_bw, F * cap * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(bow_value, d_bv, F * cap * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(bow_count, d_bc, F * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(fv_node, d_fn, F * cap * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(fv_start, d_fs, F * (cap + 1) * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(fv_feature, d_ff, F * cap * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(fv_count, d_fc, F * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-  }
-  return ORB_OK;
-}
-
-int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
-                      const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
-                      const orb_keypoint* f_kps, const int32_t* f_fv_node, const int32_t* f_fv_start, const int32_t* f_fv_feature,
-                      const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
-                      int32_t* nmatches, void* stream) {
-  const void* in[14] = {kf_desc, kf_kps_un, kf_valid, kf_fv_node, kf_fv_start, kf_fv_feature, kf_fv_count,
-                        f_desc,  f_kps,     f_fv_node, f_fv_start, f_fv_feature, f_fv_count, nullptr};
-  for (int i = 0; i < 13; ++i)
-    if (!in[i]) return fail(ORB_E_BADARG, "null argument");
-  if (!assigned || !nmatches) return fail(ORB_E_BADARG, "null argument");
-  if (cap <= 0 || cap >= (1 << 18) || qcap <= 0 || qcap >= (1 << 18) || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap, qcap < 2^18, frames > 0)");
-  if (th_dist < 0 || th_dist > 255 || !(nn_ratio > 0.f)) return fail(ORB_E_BADARG, "th_dist in [0, 255] and nn_ratio > 0 required");
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  KnnWorkspace* ws;
-  int rc = current_device_ws(&ws);
-  if (rc != ORB_OK) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  std::lock_guard<std::mutex> lk(ws->mu);
-  const size_t F = (size_t)frames, Q = (size_t)qcap, N = (size_t)cap;
-  const bool host = mem != ORB_MEM_DEVICE;
-  int* d_assigned = assigned;
-  int* d_nm = nmatches;
-  if (host) {
-    const size_t bytes[13] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
-                              F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4};
-    for (int i = 0; i < 13; ++i) {
-      if ((rc = ws->g_stage[i].ensure(bytes[i])) != ORB_OK) return rc;
-      CU(cudaMemcpyAsync(ws->g_stage[i].p, in[i], bytes[i], cudaMemcpyHostToDevice, st));
-      in[i] = ws->g_stage[i].p;
-    }
-    if ((rc = ws->g_assigned.ensure(F * N * sizeof(int))) != ORB_OK) return rc;
-    if ((rc = ws->g_nm.ensure(F * sizeof(int))) != ORB_OK) return rc;
-    d_assigned = ws->g_assigned.as<int>();
-    d_nm = ws->g_nm.as<int>();
-  }
-  if ((rc = ws->g_bq.ensure(F * Q * 32)) != ORB_OK) return rc;
-  if ((rc = ws->g_bnq.ensure(F * sizeof(int))) != ORB_OK) return rc;
-  if ((rc = ws->g_qmatch.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
-  if ((rc = ws->g_lists.ensure(F * Q * 32 * sizeof(uint2))) != ORB_OK) return rc;
-  if ((rc = ws->g_lcnt.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
-  long long launched = 0;
-  orb_launch_search_by_bow((const uint8_t*)in[0], (const OrbKeypoint*)in[1], (const uint8_t*)in[2], (const int*)in[3], (const int*)in[4],
-                           (const int*)in[5], (const int*)in[6], qcap, (const uint8_t*)in[7], (const OrbKeypoint*)in[8], (const int*)in[9],
-                           (const int*)in[10], (const int*)in[11], (const int*)in[12], cap, frames, th_dist, nn_ratio, check_orientation,
-                           ws->g_bq.p, ws->g_bnq.as<int>(), ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, ws->g_qmatch.as<int>(),
-                           d_nm, st, &launched);
-  orb_knn_count_launches(launched);
-  CU(cudaGetLastError());
-  if (host) {
-    CU(cudaMemcpyAsync(assigned, d_assigned, F * N * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-  }
-  return ORB_OK;
-}
-
-int orb_undistort_keypoints(int mem, const orb_camera* cam, const orb_keypoint* kps, const int32_t* n, int cap, int frames,
-                            orb_keypoint* kps_un, void* stream) {
-  if (!cam || !kps || !n || !kps_un || cap <= 0 || frames <= 0) return fail(ORB_E_BADARG, "bad argument");
-  if (cam->n_dist != 4 && cam->n_dist != 5 && cam->n_dist != 8) return fail(ORB_E_BADARG, "n_dist must be 4, 5 or 8");
-  if (!(cam->fx != 0.f) || !(cam->fy != 0.f)) return fail(ORB_E_BADARG, "fx / fy must be non-zero");
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  KnnWorkspace* ws;
-  int rc = current_device_ws(&ws);
-  if (rc != ORB_OK) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  std::lock_guard<std::mutex> lk(ws->mu);
-  const size_t bytes = (size_t)frames * cap * sizeof(orb_keypoint);
-  if (mem == ORB_MEM_DEVICE) {
-    orb_launch_undistort(cam, (const OrbKeypoint*)kps, n, cap, frames, (OrbKeypoint*)kps_un, st);
-    orb_knn_count_launches(1);
-    CU(cudaGetLastError());
-    return ORB_OK;
-  }
-  if ((rc = ws->g_kps.ensure(bytes)) != ORB_OK) return rc;
-  if ((rc = ws->g_nk.ensure((size_t)frames * sizeof(int))) != ORB_OK) return rc;
-  CU(cudaMemcpyAsync(ws->g_kps.p, kps, bytes, cudaMemcpyHostToDevice, st));
-  CU(cudaMemcpyAsync(ws->g_nk.p, n, (size_t)frames * sizeof(int), cudaMemcpyHostToDevice, st));
-  orb_launch_undistort(cam, ws->g_kps.as<OrbKeypoint>(), ws->g_nk.as<int>(), cap, frames, ws->g_kps.as<OrbKeypoint>(), st);
-  orb_knn_count_launches(1);
-  CU(cudaGetLastError());
-  if (kps_un != kps) memcpy(kps_un, kps, bytes);   // rows >= n[f] keep the caller's content (the kernel only rewrites rows < n[f])
-  for (int f = 0; f < frames; ++f) {
-    const int m = std::min(std::max(n[f], 0), cap);
-    if (m > 0)
-      CU(cudaMemcpyAsync(kps_un + (size_t)f * cap, ws->g_kps.as<orb_keypoint>() + (size_t)f * cap, (size_t)m * sizeof(orb_keypoint),
-                         cudaMemcpyDeviceToHost, st));
-  }
-  CU(cudaStreamSynchronize(st));
-  return ORB_OK;
-}
-
-int orb_image_bounds(const orb_camera* cam, int cols, int rows, float* bounds) {
-  if (!cam || !bounds || cols <= 0 || rows <= 0) return fail(ORB_E_BADARG, "bad argument");
-  if (cam->dist[0] == 0.0f) {   // src/Frame.cc:861-867
-    bounds[0] = 0.f; bounds[1] = 0.f; bounds[2] = (float)cols; bounds[3] = (float)rows;
-    return ORB_OK;
-  }
-  orb_keypoint c[4];
-  memset(c, 0, sizeof(c));
-  c[1].x = (float)cols; c[2].y = (float)rows; c[3].x = (float)cols; c[3].y = (float)rows;   // :838-845
-  const int32_t four = 4;
-  const int rc = orb_undistort_keypoints(ORB_MEM_HOST, cam, c, &four, 4, 1, c, nullptr);
-  if (rc != ORB_OK) return rc;
-  bounds[0] = std::min(c[0].x, c[2].x);   // mnMinX (:855)
-  bounds[2] = std::max(c[1].x, c[3].x);   // mnMaxX
-  bounds[1] = std::min(c[0].y, c[1].y);   // mnMinY
-  bounds[3] = std::max(c[2].y, c[3].y);   // mnMaxY
-  return ORB_OK;
-}
-
-int orb_distinctive_descriptors(int mem, const uint8_t* desc, const int64_t* offsets, int points, int32_t* best_idx,
-                                int32_t* best_median, void* stream) {
-  if (!offsets || !best_idx || points < 0) return fail(ORB_E_BADARG, "bad argument");
-  if (points == 0) return ORB_OK;
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  KnnWorkspace* ws;
-  int rc = current_device_ws(&ws);
-  if (rc != ORB_OK) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  std::lock_guard<std::mutex> lk(ws->mu);
-  const bool host = mem != ORB_MEM_DEVICE;
-  if (!host) {
-    if (!desc || ((uintptr_t)desc & 15)) return fail(ORB_E_BADARG, "descriptor array must be 16-byte aligned device memory");
-    orb_launch_distinctive(desc, (const long long*)offsets, points, best_idx, best_median, st);
-    CU(cudaGetLastError());
-    return ORB_OK;
-  }
-  const int64_t total = offsets[points];
-  if (offsets[0] != 0 || total < 0 || (total > 0 && !desc)) return fail(ORB_E_BADARG, "offsets must start at 0 and be ascending");
-  for (int p = 0; p < points; ++p)
-    if (offsets[p + 1] < offsets[p] || offsets[p + 1] - offsets[p] >= (1 << 22)) return fail(ORB_E_BADARG, "offsets not ascending / more than 2^22 observations");
-  if ((rc = ws->db.ensure((size_t)std::max<int64_t>(total, 1) * 32)) != ORB_OK) return rc;
-  if ((rc = ws->q.ensure((size_t)(points + 1) * sizeof(int64_t))) != ORB_OK) return rc;
-  if ((rc = ws->out.ensure((size_t)points * 2 * sizeof(int))) != ORB_OK) return rc;
-  if (total > 0) CU(cudaMemcpyAsync(ws->db.p, desc, (size_t)total * 32, cudaMemcpyHostToDevice, st));
-  CU(cudaMemcpyAsync(ws->q.p, offsets, (size_t)(points + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
-  int* d_idx = ws->out.as<int>();
-  int* d_med = d_idx + points;
-  orb_launch_distinctive(ws->db.as<uint8_t>(), ws->q.as<long long>(), points, d_idx, d_med, st);
-  CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(best_idx, d_idx, (size_t)points * sizeof(int), cudaMemcpyDeviceToHost, st));
-  if (best_median) CU(cudaMemcpyAsync(best_median, d_med, (size_t)points * sizeof(int), cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
-  return ORB_OK;
-}
-
-int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
-                             const int32_t* n_kps, int cap, const orb_proj_query* queries, const uint8_t* qdesc,
-                             const int32_t* n_queries, int qcap, int frames, const orb_search_params* prm, int32_t* assigned,
-                             int32_t* query_match, int32_t* nmatches, void* stream) {
-  static_assert(sizeof(orb_proj_query) == 32 && sizeof(orb_search_params) == 32, "ABI struct layout");
-  if (!kps_un || !desc || !n_kps || !queries || !qdesc || !n_queries || !prm || !assigned || !nmatches)
-    return fail(ORB_E_BADARG, "null argument");
-  if (cap <= 0 || cap >= (1 << 18) || qcap <= 0 || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap < 2^18, qcap > 0, frames > 0)");
-  if (!(prm->max_x > prm->min_x) || !(prm->max_y > prm->min_y)) return fail(ORB_E_BADARG, "empty image bounds");
-  if (prm->th_dist < 0 || prm->th_dist > 255) return fail(ORB_E_BADARG, "th_dist must be in [0, 255]");
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  KnnWorkspace* ws;
-  int rc = current_device_ws(&ws);
-  if (rc != ORB_OK) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  std::lock_guard<std::mutex> lk(ws->mu);
-  const size_t F = (size_t)frames;
-  const bool host = mem != ORB_MEM_DEVICE;
-  // device views of the arguments (staged when the caller's arrays are host memory)
-  const void* d_in[7] = {kps_un, desc, uright, claimed, n_kps, queries, qdesc};
-  const void* d_nq = n_queries;
-  int* d_assigned = assigned;
-  int* d_qmatch = query_match;
-  int* d_nm = nmatches;
-  if (host) {
-    DevBuf* bufs[7] = {&ws->g_kps, &ws->g_desc, &ws->g_ur, &ws->g_claim, &ws->g_nk, &ws->g_q, &ws->g_qd};
-    const size_t bytes[7] = {F * cap * sizeof(orb_keypoint), F * cap * 32, F * cap * sizeof(float), F * cap, F * sizeof(int),
-                             F * qcap * sizeof(orb_proj_query), F * qcap * 32};
-    for (int i = 0; i < 7; ++i) {
-      if (!d_in[i]) continue;
-      if ((rc = bufs[i]->ensure(bytes[i])) != ORB_OK) return rc;
-      CU(cudaMemcpyAsync(bufs[i]->p, d_in[i], bytes[i], cudaMemcpyHostToDevice, st));
-      d_in[i] = bufs[i]->p;
-    }
-    if ((rc = ws->g_nq.ensure(F * sizeof(int))) != ORB_OK) return rc;
-    CU(cudaMemcpyAsync(ws->g_nq.p, n_queries, F * sizeof(int), cudaMemcpyHostToDevice, st));
-    d_nq = ws->g_nq.p;
-    if ((rc = ws->g_assigned.ensure(F * cap * sizeof(int))) != ORB_OK) return rc;
-    if ((rc = ws->g_nm.ensure(F * sizeof(int))) != ORB_OK) return rc;
-    d_assigned = ws->g_assigned.as<int>();
-    d_nm = ws->g_nm.as<int>();
-  }
-  if (host || !query_match) {   // the resolve kernel always keeps the per-query record (rotation filter)
-    if ((rc = ws->g_qmatch.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
-    d_qmatch = ws->g_qmatch.as<int>();
-  }
-  if ((rc = ws->g_items.ensure(F * cap * sizeof(uint4))) != ORB_OK) return rc;
-  if ((rc = ws->g_cells.ensure(F * (64 * 48 + 1) * sizeof(int))) != ORB_OK) return rc;
-  if ((rc = ws->g_lists.ensure(F * qcap * 32 * sizeof(uint2))) != ORB_OK) return rc;
-  if ((rc = ws->g_lcnt.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
-  long long launched = 0;
-  orb_launch_guided((const OrbKeypoint*)d_in[0], (const uint8_t*)d_in[1], (const float*)d_in[2], (const uint8_t*)d_in[3], (const int*)d_in[4],
-                    cap, d_in[5], (const uint8_t*)d_in[6], (const int*)d_nq, qcap, frames, prm->min_x, prm->min_y, prm->max_x, prm->max_y,
-                    prm->th_dist, prm->nn_ratio, prm->check_orientation, ws->g_items.as<uint4>(), ws->g_cells.as<int>(),
-                    ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, d_qmatch, d_nm, st, &launched);
-  orb_knn_count_launches(launched);
-  CU(cudaGetLastError());
-  if (host) {
-    CU(cudaMemcpyAsync(assigned, d_assigned, F * cap * sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (query_match) CU(cudaMemcpyAsync(query_match, d_qmatch, F * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-  }
-  return ORB_OK;
-}
-
-double orb_measure_popc_peak(int device) {
-  if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return 0.0; }
-  cudaDeviceProp prop;
-  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0.0;
-  return orb_popc_peak(prop.multiProcessorCount);
 }
 
 }  // extern "C"
