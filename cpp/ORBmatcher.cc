@@ -146,8 +146,8 @@ int ORBmatcher::SearchByBoW(const cv::Mat& kfDescriptors, const std::vector<cv::
   to_csr(fFeatVec, nf, fn, fs, ffe, fc);
   int32_t nm = 0;
   check(orb_search_by_bow(ORB_MEM_HOST, dk, reinterpret_cast<const orb_keypoint*>(kfKeysUn.data()), kfHasPoint.data(), kn.data(), ks.data(), kfe.data(),
-                          &kc, nk, df, reinterpret_cast<const orb_keypoint*>(fKeys.data()), fn.data(), fs.data(), ffe.data(), &fc, nf, 1, TH_LOW,
-                          mfNNratio, mbCheckOrientation ? 1 : 0, assigned.data(), &nm, nullptr),
+                          &kc, nk, df, reinterpret_cast<const orb_keypoint*>(fKeys.data()), nullptr, fn.data(), fs.data(), ffe.data(), &fc, nf, 1,
+                          TH_LOW, mfNNratio, mbCheckOrientation ? 1 : 0, assigned.data(), nullptr, &nm, nullptr),
         "orb_search_by_bow");
   return nm;
 }

@@ -268,7 +268,7 @@ int main(int argc, char** argv) {
         const int kc = csr(fv, (int)bk[0].size(), kn, ks, ke), fc2 = csr(fv2, (int)bk[1].size(), f2n, f2s, f2e);
         const int onm = orb_oracle_search_by_bow(bd[0].ptr<unsigned char>(0), reinterpret_cast<const orb_oracle_kp*>(bk[0].data()), has.data(), kn.data(),
                                                  ks.data(), ke.data(), kc, bd[1].ptr<unsigned char>(0), reinterpret_cast<const orb_oracle_kp*>(bk[1].data()),
-                                                 (int)bk[1].size(), f2n.data(), f2s.data(), f2e.data(), fc2, ORB_SLAM2::ORBmatcher::TH_LOW, 0.7f, 1, want.data());
+                                                 (int)bk[1].size(), f2n.data(), f2s.data(), f2e.data(), fc2, ORB_SLAM2::ORBmatcher::TH_LOW, 0.7f, 1, want.data(), nullptr, nullptr, 0);
         REQUIRE(nmb == onm && std::memcmp(asg.data(), want.data(), want.size() * 4) == 0, "SearchByBoW: %d matches vs oracle %d", nmb, onm);
         REQUIRE(nmb > 30, "SearchByBoW: too few matches (%d)", nmb);
         std::printf("SearchByBoW: %d matches, assignment bit-exact vs oracle\n", nmb);

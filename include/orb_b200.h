@@ -223,12 +223,16 @@ double orb_measure_popc_peak(int device);
  * kf_desc [frames][qcap][32], kf_kps_un [frames][qcap] (angle read), kf_valid [frames][qcap] (vpMapPointsKF[i] && !isBad()),
  * kf_fv_* / f_fv_* as written by orb_bow_transform with cap = qcap / cap; f_desc [frames][cap][32], f_kps [frames][cap] (mvKeys,
  * angle read). assigned [frames][cap] = keyframe feature index matched to frame feature i (vpMapPointMatches[i] =
- * vpMapPointsKF[assigned]) or -1; nmatches [frames]. All arrays in `mem` memory; cap, qcap < 2^18. */
+ * vpMapPointsKF[assigned]) or -1; nmatches [frames]. All arrays in `mem` memory; cap, qcap < 2^18.
+ * The KeyFrame-KeyFrame form SearchByBoW(pKF1, pKF2, vpMatches12) (src/ORBmatcher.cc:722-880) is the same walk with
+ * f_blocked [frames][cap] (optional, may be NULL) = "!pMP2 || pMP2->isBad()" (:771-776), th_dist = TH_LOW - 1 ("bestDist1 <
+ * TH_LOW", :792) and the per-keyframe-feature result kf_match [frames][qcap] (optional, may be NULL; vpMatches12[idx1] =
+ * vpMapPoints2[kf_match], -1 = none). */
 int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
                       const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
-                      const orb_keypoint* f_kps, const int32_t* f_fv_node, const int32_t* f_fv_start, const int32_t* f_fv_feature,
-                      const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
-                      int32_t* nmatches, void* stream);
+                      const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,
+                      const int32_t* f_fv_feature, const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio,
+                      int check_orientation, int32_t* assigned, int32_t* kf_match, int32_t* nmatches, void* stream);
 
 /* ---- Frame::ComputeBoW (src/Frame.cc:750-765) --------------------------------------------------------
  * = DBoW2 TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)

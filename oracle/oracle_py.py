@@ -310,20 +310,24 @@ def undistort_points(xy, fx, fy, cx, cy, dist):
     return out
 
 
-def search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv, f_desc, f_kps, f_fv, th_dist=50, nn_ratio=0.7, check_orientation=True):
-    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (src/ORBmatcher.cc:248-410). kf_fv / f_fv = (node, start, feature, count)
-    CSR FeatureVectors. Returns (assigned [n_f], nmatches)."""
+def search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv, f_desc, f_kps, f_fv, th_dist=50, nn_ratio=0.7, check_orientation=True, f_blocked=None):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (src/ORBmatcher.cc:248-410); with f_blocked and th_dist = TH_LOW - 1 the
+    KeyFrame-KeyFrame form (:722-880). kf_fv / f_fv = (node, start, feature, count) CSR FeatureVectors.
+    Returns (assigned [n_f], nmatches, kf_match [n_kf])."""
     L = lib()
     vp = C.c_void_p
-    L.orb_oracle_search_by_bow.argtypes = [vp] * 6 + [C.c_int, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp]
+    L.orb_oracle_search_by_bow.argtypes = [vp] * 6 + [C.c_int, vp, vp, C.c_int, vp, vp, vp, C.c_int, C.c_int, C.c_float, C.c_int, vp, vp, vp, C.c_int]
     c = lambda a, dt: np.ascontiguousarray(a, dt)
     kf_desc, f_desc = c(kf_desc, np.uint8), c(f_desc, np.uint8)
     kf_kps_un, f_kps = np.ascontiguousarray(kf_kps_un), np.ascontiguousarray(f_kps)
     kf_valid = c(kf_valid, np.uint8)
-    kn, ks, kfe, kc = (c(a, np.int32) for a in kf_fv[:3]) if False else (c(kf_fv[0], np.int32), c(kf_fv[1], np.int32), c(kf_fv[2], np.int32), int(kf_fv[3]))
+    kn, ks, kfe, kc = c(kf_fv[0], np.int32), c(kf_fv[1], np.int32), c(kf_fv[2], np.int32), int(kf_fv[3])
     fn, fs, ffe, fc = c(f_fv[0], np.int32), c(f_fv[1], np.int32), c(f_fv[2], np.int32), int(f_fv[3])
-    n_f = len(f_kps)
+    n_f, n_kf = len(f_kps), len(kf_kps_un)
+    fb = None if f_blocked is None else c(f_blocked, np.uint8)
     assigned = np.full(max(n_f, 1), -1, np.int32)
+    kf_match = np.full(max(n_kf, 1), -1, np.int32)
     nm = L.orb_oracle_search_by_bow(_p(kf_desc), _p(kf_kps_un), _p(kf_valid), _p(kn), _p(ks), _p(kfe), kc, _p(f_desc), _p(f_kps), n_f,
-                                    _p(fn), _p(fs), _p(ffe), fc, th_dist, nn_ratio, int(check_orientation), _p(assigned))
-    return assigned[:n_f], nm
+                                    _p(fn), _p(fs), _p(ffe), fc, th_dist, nn_ratio, int(check_orientation), _p(assigned),
+                                    None if fb is None else _p(fb), _p(kf_match), n_kf)
+    return assigned[:n_f], nm, kf_match[:n_kf]

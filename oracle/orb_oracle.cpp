@@ -738,12 +738,14 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
 int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_node,
                              const int32_t* kf_start, const int32_t* kf_feature, int kf_count, const uint8_t* f_desc,
                              const orb_oracle_kp* f_kps, int n_f, const int32_t* f_node, const int32_t* f_start, const int32_t* f_feature,
-                             int f_count, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned) {
+                             int f_count, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
+                             const uint8_t* f_blocked, int32_t* kf_match, int n_kf) {
   typedef std::map<unsigned, std::vector<unsigned>> FeatureVector;
   FeatureVector fvKF, fvF;
   for (int j = 0; j < kf_count; ++j) fvKF[kf_node[j]].assign(kf_feature + kf_start[j], kf_feature + kf_start[j + 1]);
   for (int j = 0; j < f_count; ++j) fvF[f_node[j]].assign(f_feature + f_start[j], f_feature + f_start[j + 1]);
   std::fill(assigned, assigned + n_f, -1);   // vpMapPointMatches = vector<MapPoint*>(F.N, NULL) (:255)
+  if (kf_match) std::fill(kf_match, kf_match + n_kf, -1);   // vpMatches12 of the KeyFrame-KeyFrame form (:735)
   int nmatches = 0;
   std::vector<int> rotHist[HISTO_LENGTH];
   const float factor = HISTO_LENGTH / 360.0f;   // :268
@@ -759,7 +761,8 @@ int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps
         int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
         for (size_t iF = 0; iF < vF.size(); ++iF) {
           const unsigned realIdxF = vF[iF];
-          if (assigned[realIdxF] >= 0) continue;   // :300-301
+          if (assigned[realIdxF] >= 0) continue;   // :300-301 (vbMatched2[idx2], :771)
+          if (f_blocked && f_blocked[realIdxF]) continue;   // !pMP2 || pMP2->isBad() (:771-776)
           const int dist = orb_oracle_descriptor_distance(dKF, f_desc + (size_t)realIdxF * 32);
           if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = (int)realIdxF; }
           else if (dist < bestDist2) bestDist2 = dist;
@@ -767,6 +770,7 @@ int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps
         if (bestDist1 <= th_dist) {   // :339
           if (static_cast<float>(bestDist1) < nn_ratio * static_cast<float>(bestDist2)) {   // :342
             assigned[bestIdxF] = (int)realIdxKF;
+            if (kf_match) kf_match[realIdxKF] = bestIdxF;
             if (check_orientation) {
               float rot = kf_kps_un[realIdxKF].angle - f_kps[bestIdxF].angle;
               if (rot < 0.0) rot += 360.0f;
@@ -797,7 +801,11 @@ int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps
     else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
     for (int i = 0; i < HISTO_LENGTH; ++i) {
       if (i == ind1 || i == ind2 || i == ind3) continue;
-      for (int idx : rotHist[i]) { assigned[idx] = -1; --nmatches; }
+      for (int idx : rotHist[i]) {
+        if (kf_match && assigned[idx] >= 0) kf_match[assigned[idx]] = -1;
+        assigned[idx] = -1;
+        --nmatches;
+      }
     }
   }
   return nmatches;

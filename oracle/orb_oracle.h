@@ -119,7 +119,9 @@ int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const or
 int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_node,
                              const int32_t* kf_start, const int32_t* kf_feature, int kf_count, const uint8_t* f_desc,
                              const orb_oracle_kp* f_kps, int n_f, const int32_t* f_node, const int32_t* f_start, const int32_t* f_feature,
-                             int f_count, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned);
+                             int f_count, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
+                             const uint8_t* f_blocked /* optional: KeyFrame-KeyFrame form, :771-776 */, int32_t* kf_match /* optional [n_kf] */,
+                             int n_kf);
 
 /* Frame::UndistortKeyPoints (src/Frame.cc:770-806): cv::undistortPoints(pts, pts, K, dist, Mat(), K), OpenCV >= 4 default criteria
  * (5 iterations), on n points xy [n][2] (float, in place). k: n_dist (4, 5 or 8) float coefficients. dist[0] == 0 leaves xy unchanged. */

@@ -111,7 +111,7 @@ def lib():
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
     L.orb_matcher_launch_count.restype = i64
-    L.orb_search_by_bow.argtypes = [i32] + [vp] * 7 + [i32] + [vp] * 6 + [i32, i32, i32, f32, i32, vp, vp, vp]
+    L.orb_search_by_bow.argtypes = [i32] + [vp] * 7 + [i32] + [vp] * 7 + [i32, i32, i32, f32, i32, vp, vp, vp, vp]
     L.orb_undistort_keypoints.argtypes = [i32, C.POINTER(OrbCamera), vp, vp, i32, i32, vp, vp]
     L.orb_image_bounds.argtypes = [C.POINTER(OrbCamera), i32, i32, vp]
     L.orb_distinctive_descriptors.argtypes = [i32, vp, vp, i32, vp, vp, vp]

@@ -111,11 +111,14 @@ __device__ __forceinline__ void bow_scan(const GuidedFrame& F, const GuidedQuery
     unsigned hi = GUIDED_NONE, lo = 0;
     if (e < e1) {
       const int idx = F.fv_feature[e];
+      const uint8_t blocked = F.claimed ? F.claimed[idx] : (uint8_t)0;   // KeyFrame-KeyFrame form: "!pMP2 || pMP2->isBad()" (:771-776)
       const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
       const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
                        __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
-      hi = ((unsigned)dist << 18) | (unsigned)e;
-      lo = (unsigned)idx;
+      if (!blocked) {
+        hi = ((unsigned)dist << 18) | (unsigned)e;
+        lo = (unsigned)idx;
+      }
     }
     emit(hi, lo);
   }
@@ -461,15 +464,16 @@ orb_bow_queries_kernel(const OrbKeypoint* __restrict__ kf_kps, const uint8_t* __
 
 void orb_launch_search_by_bow(const uint8_t* kf_desc, const OrbKeypoint* kf_kps, const uint8_t* kf_valid, const int* kf_node, const int* kf_start,
                               const int* kf_feature, const int* kf_count, int qcap, const uint8_t* f_desc, const OrbKeypoint* f_kps,
-                              const int* f_node, const int* f_start, const int* f_feature, const int* f_count, int cap, int frames, int th_dist,
+                              const uint8_t* f_blocked, const int* f_node, const int* f_start, const int* f_feature, const int* f_count, int cap,
+                              int frames, int th_dist,
                               float nn_ratio, int check_orientation, void* queries, int* n_queries, uint2* lists, int* list_cnt, int* assigned,
                               int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
   GuidedQuery* q = static_cast<GuidedQuery*>(queries);
   orb_bow_queries_kernel<<<frames, 256, 0, st>>>(kf_kps, kf_valid, kf_node, kf_start, kf_feature, kf_count, qcap, f_node, f_count, cap, q, n_queries);
   orb_guided_candidates_kernel<true><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
-      nullptr, nullptr, f_start, f_feature, f_desc, nullptr, nullptr, cap, q, kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, lists, list_cnt);
+      nullptr, nullptr, f_start, f_feature, f_desc, nullptr, f_blocked, cap, q, kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, lists, list_cnt);
   const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
-  orb_guided_resolve_kernel<true><<<frames, 32, smem, st>>>(nullptr, nullptr, f_start, f_feature, f_kps, f_desc, nullptr, nullptr, cap, q, kf_desc,
+  orb_guided_resolve_kernel<true><<<frames, 32, smem, st>>>(nullptr, nullptr, f_start, f_feature, f_kps, f_desc, nullptr, f_blocked, cap, q, kf_desc,
                                                             n_queries, qcap, 0.f, 0.f, 0.f, 0.f, th_dist, nn_ratio, 1, check_orientation, lists,
                                                             list_cnt, assigned, query_match, nmatches);
   *launches += 3;

@@ -230,11 +230,11 @@ int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int
 
 int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
                       const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
-                      const orb_keypoint* f_kps, const int32_t* f_fv_node, const int32_t* f_fv_start, const int32_t* f_fv_feature,
-                      const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio, int check_orientation, int32_t* assigned,
-                      int32_t* nmatches, void* stream) {
+                      const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,
+                      const int32_t* f_fv_feature, const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio,
+                      int check_orientation, int32_t* assigned, int32_t* kf_match, int32_t* nmatches, void* stream) {
   const void* in[14] = {kf_desc, kf_kps_un, kf_valid, kf_fv_node, kf_fv_start, kf_fv_feature, kf_fv_count,
-                        f_desc,  f_kps,     f_fv_node, f_fv_start, f_fv_feature, f_fv_count, nullptr};
+                        f_desc,  f_kps,     f_fv_node, f_fv_start, f_fv_feature, f_fv_count, f_blocked /* optional */};
   for (int i = 0; i < 13; ++i)
     if (!in[i]) return fail(ORB_E_BADARG, "null argument");
   if (!assigned || !nmatches) return fail(ORB_E_BADARG, "null argument");
@@ -251,10 +251,12 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
   const bool host = mem != ORB_MEM_DEVICE;
   int* d_assigned = assigned;
   int* d_nm = nmatches;
+  int* d_qmatch = kf_match;
   if (host) {
-    const size_t bytes[13] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
-                              F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4};
-    for (int i = 0; i < 13; ++i) {
+    const size_t bytes[14] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
+                              F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4, F * N};
+    for (int i = 0; i < 14; ++i) {
+      if (!in[i]) continue;
       if ((rc = ws->g_stage[i].ensure(bytes[i])) != ORB_OK) return rc;
       CU(cudaMemcpyAsync(ws->g_stage[i].p, in[i], bytes[i], cudaMemcpyHostToDevice, st));
       in[i] = ws->g_stage[i].p;
@@ -264,21 +266,25 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
     d_assigned = ws->g_assigned.as<int>();
     d_nm = ws->g_nm.as<int>();
   }
+  if (host || !kf_match) {
+    if ((rc = ws->g_qmatch.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
+    d_qmatch = ws->g_qmatch.as<int>();
+  }
   if ((rc = ws->g_bq.ensure(F * Q * 32)) != ORB_OK) return rc;
   if ((rc = ws->g_bnq.ensure(F * sizeof(int))) != ORB_OK) return rc;
-  if ((rc = ws->g_qmatch.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
   if ((rc = ws->g_lists.ensure(F * Q * 32 * sizeof(uint2))) != ORB_OK) return rc;
   if ((rc = ws->g_lcnt.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
   long long launched = 0;
   orb_launch_search_by_bow((const uint8_t*)in[0], (const OrbKeypoint*)in[1], (const uint8_t*)in[2], (const int*)in[3], (const int*)in[4],
-                           (const int*)in[5], (const int*)in[6], qcap, (const uint8_t*)in[7], (const OrbKeypoint*)in[8], (const int*)in[9],
-                           (const int*)in[10], (const int*)in[11], (const int*)in[12], cap, frames, th_dist, nn_ratio, check_orientation,
-                           ws->g_bq.p, ws->g_bnq.as<int>(), ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, ws->g_qmatch.as<int>(),
+                           (const int*)in[5], (const int*)in[6], qcap, (const uint8_t*)in[7], (const OrbKeypoint*)in[8], (const uint8_t*)in[13],
+                           (const int*)in[9], (const int*)in[10], (const int*)in[11], (const int*)in[12], cap, frames, th_dist, nn_ratio,
+                           check_orientation, ws->g_bq.p, ws->g_bnq.as<int>(), ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, d_qmatch,
                            d_nm, st, &launched);
   orb_knn_count_launches(launched);
   CU(cudaGetLastError());
   if (host) {
     CU(cudaMemcpyAsync(assigned, d_assigned, F * N * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (kf_match) CU(cudaMemcpyAsync(kf_match, d_qmatch, F * Q * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
   }

@@ -30,7 +30,7 @@ void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, 
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
 void orb_launch_search_by_bow(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, const uint8_t*,
-                              const OrbKeypoint*, const int*, const int*, const int*, const int*, int, int, int, float, int, void*, int*, uint2*, int*,
+                              const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, int, int, float, int, void*, int*, uint2*, int*,
                               int*, int*, int*, cudaStream_t, long long*);
 void orb_launch_undistort(const void*, const OrbKeypoint*, const int*, int, int, OrbKeypoint*, cudaStream_t);
 struct BowVoc {   // == bow.cu

@@ -179,20 +179,23 @@ class ORBmatcher:
         check(_lib.lib().orb_distinctive_descriptors(MEM_HOST, _vp(desc) if len(desc) else None, _vp(offsets), P, _vp(bi), _vp(bm), None))
         return bi[:P], bm[:P]
 
-    def SearchByBoW(self, kf_desc, kf_kps_un, kf_valid, kf_bow: dict, f_desc, f_kps, f_bow: dict, th_dist: int | None = None):
+    def SearchByBoW(self, kf_desc, kf_kps_un, kf_valid, kf_bow: dict, f_desc, f_kps, f_bow: dict, th_dist: int | None = None, f_blocked=None):
         """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:248-410) for F independent pairs.
         kf_desc [F,qcap,32], kf_kps_un [F,qcap], kf_valid [F,qcap] (feature has a good map point), f_desc [F,cap,32], f_kps [F,cap];
-        kf_bow / f_bow = the dicts returned by ORBVocabulary.transform for the same arrays. Returns (assigned [F,cap], nmatches [F])."""
+        kf_bow / f_bow = the dicts returned by ORBVocabulary.transform for the same arrays. f_blocked [F,cap] (optional) marks target
+        features that may not be matched: with it and th_dist = TH_LOW - 1 this is the KeyFrame-KeyFrame form (:722-880).
+        Returns (assigned [F,cap], kf_match [F,qcap], nmatches [F])."""
         F, qcap = kf_kps_un.shape
         cap = f_kps.shape[1]
         c = np.ascontiguousarray
         args = [c(kf_desc, np.uint8), c(kf_kps_un), c(kf_valid, np.uint8), c(kf_bow["fv_node"]), c(kf_bow["fv_start"]), c(kf_bow["fv_feature"]),
-                c(kf_bow["fv_count"]), c(f_desc, np.uint8), c(f_kps), c(f_bow["fv_node"]), c(f_bow["fv_start"]), c(f_bow["fv_feature"]),
-                c(f_bow["fv_count"])]
-        assert args[4].shape == (F, qcap + 1) and args[10].shape == (F, cap + 1)
+                c(kf_bow["fv_count"]), c(f_desc, np.uint8), c(f_kps), None if f_blocked is None else c(f_blocked, np.uint8), c(f_bow["fv_node"]),
+                c(f_bow["fv_start"]), c(f_bow["fv_feature"]), c(f_bow["fv_count"])]
+        assert args[4].shape == (F, qcap + 1) and args[11].shape == (F, cap + 1)
         assigned = np.empty((F, cap), np.int32)
+        kf_match = np.empty((F, qcap), np.int32)
         nm = np.empty(F, np.int32)
-        check(_lib.lib().orb_search_by_bow(MEM_HOST, *[_vp(a) for a in args[:7]], qcap, *[_vp(a) for a in args[7:]], cap, F,
-                                           int(self.TH_LOW if th_dist is None else th_dist), float(self.mfNNratio),
-                                           int(self.mbCheckOrientation), _vp(assigned), _vp(nm), None))
-        return assigned, nm
+        p = [None if a is None else _vp(a) for a in args]
+        check(_lib.lib().orb_search_by_bow(MEM_HOST, *p[:7], qcap, *p[7:], cap, F, int(self.TH_LOW if th_dist is None else th_dist),
+                                           float(self.mfNNratio), int(self.mbCheckOrientation), _vp(assigned), _vp(kf_match), _vp(nm), None))
+        return assigned, kf_match, nm

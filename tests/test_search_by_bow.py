@@ -39,7 +39,7 @@ def _csr(fv: dict, cap):
     return node, start, feat, len(nodes)
 
 
-def _python_rule(kf, kk, valid, kfv, f, fk, ffv, th, ratio, ori):
+def _python_rule(kf, kk, valid, kfv, f, fk, ffv, th, ratio, ori, blocked=None):
     assigned = np.full(len(f), -1, np.int32)
     bits_k, bits_f = np.unpackbits(kf, axis=1), np.unpackbits(f, axis=1)
     events = []
@@ -47,7 +47,7 @@ def _python_rule(kf, kk, valid, kfv, f, fk, ffv, th, ratio, ori):
         for ik in kfv[node]:
             if not valid[ik]:
                 continue
-            cand = [i for i in ffv[node] if assigned[i] < 0]
+            cand = [i for i in ffv[node] if assigned[i] < 0 and not (blocked is not None and blocked[i])]
             if not cand:
                 continue
             d = np.array([int(np.count_nonzero(bits_k[ik] != bits_f[i])) for i in cand])
@@ -74,20 +74,25 @@ def _python_rule(kf, kk, valid, kfv, f, fk, ffv, th, ratio, ori):
     return assigned, nm
 
 
-@pytest.mark.parametrize("seed,ori,ratio", [(1, True, 0.7), (2, False, 0.6), (3, True, 0.9)])
-def test_oracle_equals_python_statement(oracle, seed, ori, ratio):
+@pytest.mark.parametrize("seed,ori,ratio,kfkf", [(1, True, 0.7, False), (2, False, 0.6, False), (3, True, 0.9, False), (4, True, 0.8, True)])
+def test_oracle_equals_python_statement(oracle, seed, ori, ratio, kfkf):
     voc = synth.synth_vocabulary(10, 3, seed=11)
     ov = oracle.OracleVocabulary(*voc)
     kf, kk, valid, f, fk = _pair(voc, seed, 300, 340)
     kfv, ffv = ov.transform(kf, 2)[3], ov.transform(f, 2)[3]   # levelsup 2 on L = 3: ten big nodes, long candidate lists
-    got = oracle.search_by_bow(kf, kk, valid, _csr(kfv, len(kf)), f, fk, _csr(ffv, len(f)), 50, ratio, ori)
-    want = _python_rule(kf, kk, valid, kfv, f, fk, ffv, 50, ratio, ori)
+    blocked = (np.random.default_rng(seed).random(len(f)) < 0.2).astype(np.uint8) if kfkf else None   # KeyFrame-KeyFrame form
+    th = 49 if kfkf else 50
+    got = oracle.search_by_bow(kf, kk, valid, _csr(kfv, len(kf)), f, fk, _csr(ffv, len(f)), th, ratio, ori, blocked)
+    want = _python_rule(kf, kk, valid, kfv, f, fk, ffv, th, ratio, ori, blocked)
     assert got[1] == want[1] and np.array_equal(got[0], want[0]) and want[1] > 30
+    inv = np.full(len(kf), -1, np.int32)
+    inv[want[0][want[0] >= 0]] = np.flatnonzero(want[0] >= 0)
+    assert np.array_equal(got[2], inv)   # kf_match is the inverse map of assigned
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("levelsup,ori", [(1, True), (2, True), (0, False)])
-def test_gpu_equals_oracle(oracle, levelsup, ori):
+@pytest.mark.parametrize("levelsup,ori,kfkf", [(1, True, False), (2, True, False), (0, False, False), (2, True, True)])
+def test_gpu_equals_oracle(oracle, levelsup, ori, kfkf):
     import orb_slam2_detailed_comments_b200 as pkg
     voc = synth.synth_vocabulary(10, 3, seed=11)
     gv, ov = pkg.ORBVocabulary(*voc), oracle.OracleVocabulary(*voc)
@@ -106,13 +111,17 @@ def test_gpu_equals_oracle(oracle, levelsup, ori):
     nk, nf = np.array([s[0] for s in sizes], np.int32), np.array([s[1] for s in sizes], np.int32)
     kbow, fbow = gv.transform(kf_desc, nk, levelsup), gv.transform(f_desc, nf, levelsup)
     m = pkg.ORBmatcher(0.7, ori)
-    assigned, nm = m.SearchByBoW(kf_desc, kf_kps, kf_valid, kbow, f_desc, f_kps, fbow)
+    blocked = (rng.random((len(sizes), cap)) < 0.2).astype(np.uint8) if kfkf else None
+    th = 49 if kfkf else 50
+    assigned, kf_match, nm = m.SearchByBoW(kf_desc, kf_kps, kf_valid, kbow, f_desc, f_kps, fbow, th_dist=th, f_blocked=blocked)
     total = 0
     for i, (kf, kk, valid, f, fk) in enumerate(pairs):
         kfv, ffv = ov.transform(kf, levelsup)[3], ov.transform(f, levelsup)[3]
-        want = oracle.search_by_bow(kf, kk, valid, _csr(kfv, max(len(kf), 1)), f, fk, _csr(ffv, max(len(f), 1)), 50, 0.7, ori)
+        want = oracle.search_by_bow(kf, kk, valid, _csr(kfv, max(len(kf), 1)), f, fk, _csr(ffv, max(len(f), 1)), th, 0.7, ori,
+                                    None if blocked is None else blocked[i, :len(f)])
         assert nm[i] == want[1], f"pair {i}: nmatches {nm[i]} vs {want[1]}"
         assert np.array_equal(assigned[i, :len(f)], want[0]), f"pair {i}: assignment differs"
+        assert np.array_equal(kf_match[i, :len(kf)], want[2]) and (kf_match[i, len(kf):] == -1).all(), f"pair {i}: kf_match differs"
         assert (assigned[i, len(f):] == -1).all()
         total += want[1]
     assert total > 500
