@@ -510,6 +510,15 @@ def run_b200(args):
             traffic = (t["read"] + t["write"]) / tj["frames_per_launch"] * frames_per_launch
     except Exception:
         traffic = None
+    issue = None   # instruction-issue view of the same step (the extraction kernels are issue bound)
+    try:
+        if args.workload == "kitti" and clocks.get("sm_mhz"):
+            wi = sum(v for v in tj["warp_instructions_per_launch"].values() if isinstance(v, int)) / tj["frames_per_launch"]
+            peak_ips = 148 * 4 * clocks["sm_mhz"] * 1e6   # one warp instruction per cycle per SM sub-partition
+            issue = {"warp_instructions_per_image": wi, "achieved": per_rank_rate * wi, "peak": peak_ips, "unit": "warp instr/s",
+                     "frac": per_rank_rate * wi / peak_ips, "source": "profiles/ncu_traffic.json (smsp__inst_executed.sum of the committed ncu capture)"}
+    except Exception:
+        issue = None
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": dom_achieved, "peak": peak, "unit": "GB/s",
         "frac": dom_achieved / peak, "traffic": traffic, "peak_source": peak_src,
@@ -517,6 +526,7 @@ def run_b200(args):
         "share_of_step": stage_ms[dom] / total_stage,
         "pipeline": {"algorithmic_bytes_per_image": A, "achieved": per_rank_rate * A / 1e9, "frac": per_rank_rate * A / 1e9 / peak},
         "stages_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
+        "issue": issue,
     }
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

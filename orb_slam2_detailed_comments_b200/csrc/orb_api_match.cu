@@ -253,6 +253,20 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
   int* d_nm = nmatches;
   int* d_qmatch = kf_match;
   if (host) {
+    // FeatureVectors in host memory are checked before they index device arrays (device-memory callers pass orb_bow_transform output)
+    auto csr_ok = [](const int32_t* start, const int32_t* feature, int count, int limit) {
+      if (count < 0 || count > limit || (count > 0 && start[0] != 0)) return false;
+      for (int j = 0; j < count; ++j)
+        if (start[j + 1] < start[j] || start[j + 1] > limit) return false;
+      for (int e = 0; e < (count > 0 ? start[count] : 0); ++e)
+        if (feature[e] < 0 || feature[e] >= limit) return false;
+      return true;
+    };
+    for (int f = 0; f < frames; ++f) {
+      if (!csr_ok(kf_fv_start + (size_t)f * (Q + 1), kf_fv_feature + (size_t)f * Q, kf_fv_count[f], qcap) ||
+          !csr_ok(f_fv_start + (size_t)f * (N + 1), f_fv_feature + (size_t)f * N, f_fv_count[f], cap))
+        return fail(ORB_E_BADARG, "frame %d: malformed FeatureVector (counts, ascending starts, feature indices in range)", f);
+    }
     const size_t bytes[14] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
                               F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4, F * N};
     for (int i = 0; i < 14; ++i) {

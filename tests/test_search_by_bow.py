@@ -125,3 +125,21 @@ def test_gpu_equals_oracle(oracle, levelsup, ori, kfkf):
         assert (assigned[i, len(f):] == -1).all()
         total += want[1]
     assert total > 500
+
+
+@pytest.mark.gpu
+def test_malformed_feature_vector_rejected(oracle):
+    import orb_slam2_detailed_comments_b200 as pkg
+    from orb_slam2_detailed_comments_b200._lib import OrbError
+    voc = synth.synth_vocabulary(6, 2, seed=4)
+    gv = pkg.ORBVocabulary(*voc)
+    kf, kk, valid, f, fk = _pair(voc, 9, 50, 60)
+    kbow, fbow = gv.transform(kf[None], np.array([50], np.int32), 1), gv.transform(f[None], np.array([60], np.int32), 1)
+    bad = {k: v.copy() for k, v in fbow.items()}
+    bad["fv_feature"][0, 0] = 60   # out of range
+    with pytest.raises(OrbError):
+        pkg.ORBmatcher().SearchByBoW(kf[None], kk[None], valid[None], kbow, f[None], fk[None], bad)
+    bad = {k: v.copy() for k, v in fbow.items()}
+    bad["fv_start"][0, 1] = -3
+    with pytest.raises(OrbError):
+        pkg.ORBmatcher().SearchByBoW(kf[None], kk[None], valid[None], kbow, f[None], fk[None], bad)
