@@ -10,3 +10,4 @@ from ._lib import KNN_DTYPE, KP_DTYPE, OrbError, build, lib  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import ORBmatcher, hamming_knn, hamming_knn_sharded  # noqa: F401
 from .vocabulary import ORBVocabulary  # noqa: F401
+from .frontend import FrameFrontEnd  # noqa: F401
