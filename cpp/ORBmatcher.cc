@@ -152,4 +152,34 @@ int ORBmatcher::SearchByBoW(const cv::Mat& kfDescriptors, const std::vector<cv::
   return nm;
 }
 
+int ORBmatcher::SearchForInitialization(const std::vector<cv::KeyPoint>& keys1Un, const cv::Mat& descriptors1, const TargetFrame& F2,
+                                        std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize) const {
+  const int m = (int)keys1Un.size(), n = (int)F2.mvKeysUn->size();
+  vnMatches12.assign(m, -1);   // :574
+  if (m == 0 || n == 0) return 0;
+  if (descriptors1.rows != m || F2.mDescriptors->rows != n || (int)vbPrevMatched.size() != m)
+    throw std::runtime_error("SearchForInitialization: array sizes differ");
+  std::vector<uint8_t> t1, t2;
+  const uint8_t* d1 = rows32(descriptors1, t1);
+  const uint8_t* d2 = rows32(*F2.mDescriptors, t2);
+  std::vector<orb_proj_query> q(m);
+  for (int i = 0; i < m; ++i) {
+    q[i].u = vbPrevMatched[i].x; q[i].v = vbPrevMatched[i].y; q[i].radius = (float)windowSize; q[i].ur = -1.f;
+    q[i].angle = keys1Un[i].angle;
+    q[i].min_level = 0; q[i].max_level = 0;                      // GetFeaturesInArea(x, y, windowSize, level1, level1) with level1 == 0 (:602)
+    q[i].flags = keys1Un[i].octave > 0 ? ORB_QUERY_SKIP : 0;     // :596-597
+    q[i].reserved = 0;
+  }
+  orb_search_params prm;
+  prm.min_x = F2.mnMinX; prm.min_y = F2.mnMinY; prm.max_x = F2.mnMaxX; prm.max_y = F2.mnMaxY;
+  prm.th_dist = TH_LOW; prm.nn_ratio = mfNNratio; prm.check_orientation = mbCheckOrientation ? 1 : 0; prm.reserved = 0;
+  int32_t nm = 0;
+  check(orb_search_for_initialization(ORB_MEM_HOST, reinterpret_cast<const orb_keypoint*>(F2.mvKeysUn->data()), d2, &n, n, q.data(), d1, &m, m, 1,
+                                      &prm, vnMatches12.data(), nullptr, &nm, nullptr),
+        "orb_search_for_initialization");
+  for (int i = 0; i < m; ++i)
+    if (vnMatches12[i] >= 0) vbPrevMatched[i] = (*F2.mvKeysUn)[vnMatches12[i]].pt;   // :707-709
+  return nm;
+}
+
 }  // namespace ORB_SLAM2

@@ -67,6 +67,12 @@ class ORBmatcher {
   int SearchByProjection(const TargetFrame& F, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors, int th,
                          bool useRatio, std::vector<int>& assigned, std::vector<int>* pointMatch = nullptr) const;
 
+  // SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) with the members of F1 / F2 it
+  // reads passed explicitly: F1.mvKeysUn + F1.mDescriptors, F2 as TargetFrame (mvuRight / claimed unused). vbPrevMatched is updated
+  // for the matched keypoints (:707-709). Threshold TH_LOW, ratio mfNNratio. Returns nmatches. GPU only.
+  int SearchForInitialization(const std::vector<cv::KeyPoint>& keys1Un, const cv::Mat& descriptors1, const TargetFrame& F2,
+                              std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize) const;
+
   // SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:248-410) on flat inputs: keyframe descriptors / mvKeysUn /
   // "has a good map point" flags / mFeatVec, frame descriptors / mvKeys / mFeatVec (DBoW2::FeatureVector derives from this map type).
   // assigned[i] = keyframe feature matched to frame feature i (vpMapPointMatches[i] = vpMapPointsKF[assigned[i]]) or -1. Threshold

@@ -186,6 +186,27 @@ int main(int argc, char** argv) {
         std::printf("SearchByProjection (%s): %d matches, assignment bit-exact vs oracle\n", form ? "local-map form" : "frame-to-frame form", nm);
       }
     }
+    // SearchForInitialization: left keypoints search a 100-px window around their own position in the right image
+    {
+      std::vector<cv::Point2f> prev(bk[0].size());
+      for (size_t i = 0; i < prev.size(); ++i) prev[i] = bk[0][i].pt;
+      ORB_SLAM2::ORBmatcher::TargetFrame F2{&bk[1], &bd[1], nullptr, nullptr, 0.f, 0.f, (float)W, (float)H};
+      ORB_SLAM2::ORBmatcher im(0.9f, true);
+      std::vector<int> m12;
+      const int nmi = im.SearchForInitialization(bk[0], bd[0], F2, prev, m12, 100);
+      std::vector<orb_oracle_query> oq(bk[0].size());
+      for (size_t i = 0; i < oq.size(); ++i)
+        oq[i] = {bk[0][i].pt.x, bk[0][i].pt.y, 100.f, -1.f, bk[0][i].angle, 0, 0, bk[0][i].octave > 0 ? 1 : 0, 0};
+      orb_oracle_search_params op{0.f, 0.f, (float)W, (float)H, ORB_SLAM2::ORBmatcher::TH_LOW, 0.9f, 1, 0};
+      std::vector<int32_t> want(oq.size());
+      const int onm = orb_oracle_search_for_initialization(reinterpret_cast<const orb_oracle_kp*>(bk[1].data()), bd[1].ptr<unsigned char>(0), (int)bk[1].size(),
+                                                           oq.data(), bd[0].ptr<unsigned char>(0), (int)oq.size(), &op, want.data(), nullptr);
+      REQUIRE(nmi == onm && std::memcmp(m12.data(), want.data(), want.size() * 4) == 0, "SearchForInitialization: %d matches vs oracle %d", nmi, onm);
+      REQUIRE(nmi > 30, "SearchForInitialization: too few matches (%d)", nmi);
+      for (size_t i = 0; i < m12.size(); ++i)
+        if (m12[i] >= 0) REQUIRE(prev[i].x == bk[1][m12[i]].pt.x && prev[i].y == bk[1][m12[i]].pt.y, "vbPrevMatched %zu not updated", i);
+      std::printf("SearchForInitialization: %d matches, vnMatches12 bit-exact vs oracle\n", nmi);
+    }
     // distinctive descriptors: groups of consecutive left descriptors stand in for the observations of map points
     {
       std::vector<int64_t> off{0};

@@ -16,6 +16,7 @@
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
+ *   orb_search_for_initialization <- ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   src/ORBmatcher.cc:570-712
  *   orb_search_by_bow         <- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)                  src/ORBmatcher.cc:248-410
  *   orb_vocabulary_*, orb_bow_transform <- Frame::ComputeBoW = DBoW2 TemplatedVocabulary::transform   src/Frame.cc:750-765,
  *                                Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280
@@ -214,6 +215,19 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
 double orb_measure_popc_peak(int device);
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) for `frames`
+ * independent frame pairs. Queries = the keypoints of F1 in index order: u, v = vbPrevMatched[i1], radius = windowSize,
+ * min_level = max_level = 0 (GetFeaturesInArea(…, level1, level1), :602), angle = mvKeysUn[i1].angle, ORB_QUERY_SKIP for
+ * level1 > 0 (:596-597); kps_un / desc = F2. A keypoint of F2 matched at distance d stays available to a later, strictly closer
+ * query, which evicts the earlier match (:624, :647-651); accept iff bestDist <= th_dist && bestDist < (float)bestDist2 * nn_ratio
+ * with bestDist2 = INT_MAX when there is no second candidate (:611-612, :641-644); rotation histogram over all accepts, removal
+ * of the standing matches outside the three maxima (:680-703). matches12 [frames][qcap] = vnMatches12, matches21 [frames][cap]
+ * (optional) = inverse map of the standing matches, nmatches [frames]. prm as for orb_search_by_projection (bounds, th_dist = TH_LOW,
+ * nn_ratio, check_orientation). cap <= 32768. The caller updates vbPrevMatched from matches12 (:707-709). */
+int orb_search_for_initialization(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const int32_t* n_kps, int cap,
+                                  const orb_proj_query* queries, const uint8_t* qdesc, const int32_t* n_queries, int qcap, int frames,
+                                  const orb_search_params* prm, int32_t* matches12, int32_t* matches21, int32_t* nmatches, void* stream);
 
 /* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:248-410) for `frames` independent
  * (keyframe, frame) pairs: keyframe features with a valid map point are matched against the frame's features of the same

@@ -331,3 +331,17 @@ def search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv, f_desc, f_kps, f_fv, th_d
                                     _p(fn), _p(fs), _p(ffe), fc, th_dist, nn_ratio, int(check_orientation), _p(assigned),
                                     None if fb is None else _p(fb), _p(kf_match), n_kf)
     return assigned[:n_f], nm, kf_match[:n_kf]
+
+
+def search_for_initialization(kps_un, desc, queries, qdesc, bounds, th_dist=50, nn_ratio=0.9, check_orientation=True):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:570-712), one frame pair. Returns (matches12 [m], matches21 [n], nmatches)."""
+    L = lib()
+    L.orb_oracle_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(_SearchParams),
+                                                       C.c_void_p, C.c_void_p]
+    kps_un, desc = np.ascontiguousarray(kps_un), np.ascontiguousarray(desc)
+    queries, qdesc = np.ascontiguousarray(queries), np.ascontiguousarray(qdesc)
+    n, m = len(kps_un), len(queries)
+    prm = _SearchParams(*[float(b) for b in bounds], int(th_dist), float(nn_ratio), int(check_orientation), 0)
+    m12, m21 = np.full(max(m, 1), -1, np.int32), np.full(max(n, 1), -1, np.int32)
+    nm = L.orb_oracle_search_for_initialization(_p(kps_un), _p(desc), n, _p(queries), _p(qdesc), m, C.byref(prm), _p(m12), _p(m21))
+    return m12[:m], m21[:n], nm

@@ -735,6 +735,68 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
   return nmatches;
 }
 
+int orb_oracle_search_for_initialization(const orb_oracle_kp* kps, const uint8_t* desc, int n, const orb_oracle_query* q, const uint8_t* qdesc,
+                                         int m, const orb_oracle_search_params* prm, int32_t* vnMatches12, int32_t* matches21) {
+  FrameGrid grid(kps, n, *prm);
+  int nmatches = 0;
+  std::fill(vnMatches12, vnMatches12 + m, -1);                       // :574
+  std::vector<int> rotHist[HISTO_LENGTH];
+  const float factor = HISTO_LENGTH / 360.0f;                        // :583
+  std::vector<int> vMatchedDistance(n, INT_MAX), vnMatches21(n, -1); // :586-588
+  std::vector<int> vIndices2;
+  for (int i1 = 0; i1 < m; ++i1) {
+    if (q[i1].flags & 1) continue;                                   // level1 > 0 (:596-597)
+    grid.in_area(kps, q[i1].u, q[i1].v, q[i1].radius, q[i1].min_level, q[i1].max_level, vIndices2);
+    if (vIndices2.empty()) continue;
+    const uint8_t* d1 = qdesc + (size_t)i1 * 32;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;      // :611-613
+    for (int i2 : vIndices2) {
+      const int dist = orb_oracle_descriptor_distance(d1, desc + (size_t)i2 * 32);
+      if (vMatchedDistance[i2] <= dist) continue;                    // :624
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) bestDist2 = dist;
+    }
+    if (bestDist <= prm->th_dist) {                                  // :641
+      if (bestDist < (float)bestDist2 * prm->nn_ratio) {             // :644
+        if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; nmatches--; }   // :647-651
+        vnMatches12[i1] = bestIdx2;
+        vnMatches21[bestIdx2] = i1;
+        vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (prm->check_orientation) {
+          float rot = q[i1].angle - kps[bestIdx2].angle;
+          if (rot < 0.0) rot += 360.0f;
+          int bin = (int)std::round(rot * factor);
+          if (bin == HISTO_LENGTH) bin = 0;
+          if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back(i1);   // :673
+        }
+      }
+    }
+  }
+  if (prm->check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int sz = (int)rotHist[i].size();
+      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+      else if (sz > max3) { max3 = sz; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i])
+        if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }   // :696-700
+    }
+  }
+  if (matches21) {
+    std::fill(matches21, matches21 + n, -1);
+    for (int i1 = 0; i1 < m; ++i1)
+      if (vnMatches12[i1] >= 0) matches21[vnMatches12[i1]] = i1;
+  }
+  return nmatches;
+}
+
 int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_node,
                              const int32_t* kf_start, const int32_t* kf_feature, int kf_count, const uint8_t* f_desc,
                              const orb_oracle_kp* f_kps, int n_f, const int32_t* f_node, const int32_t* f_start, const int32_t* f_feature,

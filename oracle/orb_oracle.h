@@ -110,6 +110,11 @@ typedef struct orb_oracle_search_params {
 int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
                                     int n_kps, const orb_oracle_query* queries, const uint8_t* qdesc, int n_queries,
                                     const orb_oracle_search_params* prm, int32_t* assigned, int32_t* query_match);
+/* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:570-712), one frame pair; queries as in include/orb_b200.h. matches12 [n_queries],
+ * matches21 [n_kps] (inverse of the standing matches). Returns nmatches. */
+int orb_oracle_search_for_initialization(const orb_oracle_kp* kps_un, const uint8_t* desc, int n_kps, const orb_oracle_query* queries,
+                                         const uint8_t* qdesc, int n_queries, const orb_oracle_search_params* prm, int32_t* matches12,
+                                         int32_t* matches21);
 /* Frame::GetFeaturesInArea alone (scan order included): returns the number of indices written to out (cap >= n_kps). */
 int orb_oracle_features_in_area(const orb_oracle_kp* kps_un, int n_kps, const orb_oracle_search_params* prm, float x, float y, float r,
                                 int min_level, int max_level, int32_t* out);

@@ -39,7 +39,7 @@ SYMBOLS = [
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
     "orb_search_by_projection", "orb_distinctive_descriptors",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_words", "orb_bow_transform",
-    "orb_undistort_keypoints", "orb_image_bounds", "orb_search_by_bow",
+    "orb_undistort_keypoints", "orb_image_bounds", "orb_search_by_bow", "orb_search_for_initialization",
 ]
 
 
@@ -111,6 +111,7 @@ def lib():
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
     L.orb_matcher_launch_count.restype = i64
+    L.orb_search_for_initialization.argtypes = [i32, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]
     L.orb_search_by_bow.argtypes = [i32] + [vp] * 7 + [i32] + [vp] * 7 + [i32, i32, i32, f32, i32, vp, vp, vp, vp]
     L.orb_undistort_keypoints.argtypes = [i32, C.POINTER(OrbCamera), vp, vp, i32, i32, vp, vp]
     L.orb_image_bounds.argtypes = [C.POINTER(OrbCamera), i32, i32, vp]

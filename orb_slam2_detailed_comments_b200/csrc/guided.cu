@@ -17,6 +17,8 @@
 //      first in scan order wins" == unsigned min over dist << 18 | position). Lists are staged one group of 32 queries
 //      ahead with cp.async. A query with more than 32 candidates is rescanned by the warp with the claims applied.
 //      Accept rule, assignment, claim bit, rotation histogram and the three-maxima filter follow.
+#include <atomic>
+
 #include "orb_common.cuh"
 
 #define GRID_COLS 64
@@ -416,6 +418,156 @@ void orb_launch_guided(const OrbKeypoint* kps, const uint8_t* desc, const float*
   orb_guided_resolve_kernel<false><<<frames, 32, smem, st>>>(items, cell_start, nullptr, nullptr, kps, desc, uright, claimed, cap, q, qdesc,
                                                              n_queries, qcap, min_x, min_y, inv_w, inv_h, th_dist, nn_ratio, 0,
                                                              check_orientation, lists, list_cnt, assigned, query_match, nmatches);
+  *launches += 3;
+}
+
+// ---- SearchForInitialization (src/ORBmatcher.cc:570-712) -------------------------------------------------------------------------
+// Same window scan, different bookkeeping: a keypoint matched at distance d stays available to later queries that are strictly
+// closer ("if (vMatchedDistance[i2] <= dist) continue", :624); a better match evicts the previous owner (:647-651). The rotation
+// histogram counts every accept, evicted ones included (:673), but only standing matches are removed (:696-700).
+// One warp per frame pair; shared memory holds vMatchedDistance (u16, 0xffff = INT_MAX) and vnMatches21 per keypoint.
+__global__ void __launch_bounds__(32)
+orb_guided_resolve_init_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const OrbKeypoint* __restrict__ kps,
+                               const uint8_t* __restrict__ desc, int cap, const GuidedQuery* __restrict__ queries,
+                               const uint8_t* __restrict__ qdesc, const int* __restrict__ n_queries, int qcap, float min_x, float min_y,
+                               float inv_w, float inv_h, int th_dist, float nn_ratio, int check_orientation,
+                               const uint2* __restrict__ lists, const int* __restrict__ list_cnt, int* __restrict__ assigned,
+                               int* __restrict__ query_match, int* __restrict__ nmatches) {
+  extern __shared__ int s_owner[];                                            // [cap] vnMatches21
+  unsigned short* s_mdist = reinterpret_cast<unsigned short*>(s_owner + cap);   // [cap] vMatchedDistance
+  __shared__ int s_hist[HISTO_LENGTH];
+  const int f = blockIdx.x, lane = threadIdx.x;
+  const int m = min(n_queries[f], qcap);
+  GuidedFrame F;
+  F.items = items + (size_t)f * cap;
+  F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
+  F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
+  F.uright = nullptr; F.claimed = nullptr; F.fv_start = nullptr; F.fv_feature = nullptr;
+  F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  kps += (size_t)f * cap;
+  queries += (size_t)f * qcap;
+  qdesc += (size_t)f * qcap * 32;
+  lists += (size_t)f * qcap * GUIDED_LIST;
+  list_cnt += (size_t)f * qcap;
+  assigned += (size_t)f * cap;
+  query_match += (size_t)f * qcap;
+  for (int i = lane; i < cap; i += 32) { s_owner[i] = -1; s_mdist[i] = 0xffffu; assigned[i] = -1; }
+  for (int i = lane; i < qcap; i += 32) query_match[i] = -1;
+  if (lane < HISTO_LENGTH) s_hist[lane] = 0;
+  __syncwarp();
+  const float factor = HISTO_LENGTH / 360.0f;
+  int nm = 0;
+  for (int iq = 0; iq < m; ++iq) {
+    const int n = list_cnt[iq];
+    if (n == 0) continue;
+    unsigned hi1, lo1 = 0, hi2;
+    if (n <= GUIDED_LIST) {
+      const uint2 c = lists[(size_t)iq * GUIDED_LIST + lane];
+      const unsigned idx = c.x & 0x3ffffu;
+      const bool live = c.y != GUIDED_NONE && (c.y >> 18) < (unsigned)s_mdist[idx];   // vMatchedDistance[i2] <= dist -> skip (:624)
+      const unsigned hi = live ? c.y : GUIDED_NONE;
+      hi1 = __reduce_min_sync(0xffffffffu, hi);
+      if (hi1 == GUIDED_NONE) continue;
+      const int l1 = __ffs(__ballot_sync(0xffffffffu, hi == hi1)) - 1;
+      lo1 = __shfl_sync(0xffffffffu, c.x, l1);
+      hi2 = __reduce_min_sync(0xffffffffu, lane == l1 ? GUIDED_NONE : hi);
+    } else {
+      const GuidedQuery q = queries[iq];
+      const uint4* qd = reinterpret_cast<const uint4*>(qdesc + (size_t)iq * 32);
+      unsigned long long k1 = ~0ull, k2 = ~0ull;
+      guided_scan(F, q, qd[0], qd[1], lane, [&](unsigned hi, unsigned lo) {
+        if (hi != GUIDED_NONE && (hi >> 18) < (unsigned)s_mdist[lo & 0x3ffffu]) {
+          const unsigned long long k = ((unsigned long long)hi << 32) | lo;
+          if (k < k1) { k2 = k1; k1 = k; }
+          else if (k < k2) k2 = k;
+        }
+      });
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        const unsigned long long lo = min(k1, o1), hi = max(k1, o1);
+        k2 = min(hi, min(k2, o2));
+        k1 = lo;
+      }
+      hi1 = (unsigned)(k1 >> 32); lo1 = (unsigned)k1; hi2 = (unsigned)(k2 >> 32);
+      if (hi1 == GUIDED_NONE) continue;
+    }
+    const int d1 = (int)(hi1 >> 18), idx1 = (int)(lo1 & 0x3ffffu);
+    const float second = hi2 == GUIDED_NONE ? (float)2147483647 : (float)(int)(hi2 >> 18);   // bestDist2 = INT_MAX (:612)
+    if (d1 <= th_dist && (float)d1 < second * nn_ratio) {                                   // :641-644
+      const int prev = s_owner[idx1];
+      if (prev >= 0) --nm;                                                                   // :647-651
+      ++nm;
+      if (lane == 0) {
+        if (prev >= 0) query_match[prev] = -1;
+        query_match[iq] = idx1;
+        s_owner[idx1] = iq;
+        s_mdist[idx1] = (unsigned short)d1;
+        if (check_orientation) {
+          float rot = queries[iq].angle - kps[idx1].angle;
+          if (rot < 0.0f) rot += 360.0f;
+          int bin = (int)roundf(rot * factor);
+          if (bin == HISTO_LENGTH) bin = 0;
+          if (bin >= 0 && bin < HISTO_LENGTH) ++s_hist[bin];
+        }
+      }
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int s = s_hist[i];
+      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+      else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+    int removed = 0;
+    for (int iq = lane; iq < m; iq += 32) {
+      const int t = query_match[iq];
+      if (t >= 0) {
+        float rot = queries[iq].angle - kps[t].angle;
+        if (rot < 0.0f) rot += 360.0f;
+        int bin = (int)roundf(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        if (bin >= 0 && bin < HISTO_LENGTH && bin != ind1 && bin != ind2 && bin != ind3) { query_match[iq] = -1; ++removed; }   // :696-700
+      }
+    }
+    nm -= __reduce_add_sync(0xffffffffu, removed);
+    __syncwarp();
+  }
+  for (int iq = lane; iq < m; iq += 32) {   // inverse map of the standing matches
+    const int t = query_match[iq];
+    if (t >= 0) assigned[t] = iq;
+  }
+  if (lane == 0) nmatches[f] = nm;
+}
+
+void orb_launch_search_init(const OrbKeypoint* kps, const uint8_t* desc, const int* n_kps, int cap, const void* queries, const uint8_t* qdesc,
+                            const int* n_queries, int qcap, int frames, float min_x, float min_y, float max_x, float max_y, int th_dist,
+                            float nn_ratio, int check_orientation, uint4* items, int* cell_start, uint2* lists, int* list_cnt, int* assigned,
+                            int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
+  const float inv_w = static_cast<float>(GRID_COLS) / static_cast<float>(max_x - min_x);
+  const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
+  const GuidedQuery* q = static_cast<const GuidedQuery*>(queries);
+  orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
+  orb_guided_candidates_kernel<false><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, nullptr, nullptr, desc, nullptr, nullptr, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
+  const size_t smem = (size_t)cap * (sizeof(int) + sizeof(unsigned short)) + 16;
+  static std::atomic<bool> configured[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (smem > 48 * 1024 && !configured[dev].load(std::memory_order_acquire)) {
+    cudaFuncSetAttribute(orb_guided_resolve_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    configured[dev].store(true, std::memory_order_release);
+  }
+  orb_guided_resolve_init_kernel<<<frames, 32, smem, st>>>(items, cell_start, kps, desc, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w,
+                                                           inv_h, th_dist, nn_ratio, check_orientation, lists, list_cnt, assigned, query_match,
+                                                           nmatches);
   *launches += 3;
 }
 

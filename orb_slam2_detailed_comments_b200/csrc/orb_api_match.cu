@@ -228,6 +228,63 @@ int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int
   return ORB_OK;
 }
 
+int orb_search_for_initialization(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const int32_t* n_kps, int cap,
+                                  const orb_proj_query* queries, const uint8_t* qdesc, const int32_t* n_queries, int qcap, int frames,
+                                  const orb_search_params* prm, int32_t* matches12, int32_t* matches21, int32_t* nmatches, void* stream) {
+  if (!kps_un || !desc || !n_kps || !queries || !qdesc || !n_queries || !prm || !matches12 || !nmatches) return fail(ORB_E_BADARG, "null argument");
+  if (cap <= 0 || cap > 32768 || qcap <= 0 || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap <= 32768, qcap > 0, frames > 0)");
+  if (!(prm->max_x > prm->min_x) || !(prm->max_y > prm->min_y)) return fail(ORB_E_BADARG, "empty image bounds");
+  if (prm->th_dist < 0 || prm->th_dist > 255 || !(prm->nn_ratio > 0.f)) return fail(ORB_E_BADARG, "th_dist in [0, 255] and nn_ratio > 0 required");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const size_t F = (size_t)frames;
+  const bool host = mem != ORB_MEM_DEVICE;
+  const void* d_in[6] = {kps_un, desc, n_kps, queries, qdesc, n_queries};
+  int* d_m12 = matches12;
+  int* d_m21 = matches21;
+  int* d_nm = nmatches;
+  if (host) {
+    DevBuf* bufs[6] = {&ws->g_kps, &ws->g_desc, &ws->g_nk, &ws->g_q, &ws->g_qd, &ws->g_nq};
+    const size_t bytes[6] = {F * cap * sizeof(orb_keypoint), F * cap * 32, F * sizeof(int), F * qcap * sizeof(orb_proj_query), F * qcap * 32, F * sizeof(int)};
+    for (int i = 0; i < 6; ++i) {
+      if ((rc = bufs[i]->ensure(bytes[i])) != ORB_OK) return rc;
+      CU(cudaMemcpyAsync(bufs[i]->p, d_in[i], bytes[i], cudaMemcpyHostToDevice, st));
+      d_in[i] = bufs[i]->p;
+    }
+    if ((rc = ws->g_qmatch.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
+    if ((rc = ws->g_nm.ensure(F * sizeof(int))) != ORB_OK) return rc;
+    d_m12 = ws->g_qmatch.as<int>();
+    d_nm = ws->g_nm.as<int>();
+  }
+  if (host || !matches21) {
+    if ((rc = ws->g_assigned.ensure(F * cap * sizeof(int))) != ORB_OK) return rc;
+    d_m21 = ws->g_assigned.as<int>();
+  }
+  if ((rc = ws->g_items.ensure(F * cap * sizeof(uint4))) != ORB_OK) return rc;
+  if ((rc = ws->g_cells.ensure(F * (64 * 48 + 1) * sizeof(int))) != ORB_OK) return rc;
+  if ((rc = ws->g_lists.ensure(F * qcap * 32 * sizeof(uint2))) != ORB_OK) return rc;
+  if ((rc = ws->g_lcnt.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
+  long long launched = 0;
+  orb_launch_search_init((const OrbKeypoint*)d_in[0], (const uint8_t*)d_in[1], (const int*)d_in[2], cap, d_in[3], (const uint8_t*)d_in[4],
+                         (const int*)d_in[5], qcap, frames, prm->min_x, prm->min_y, prm->max_x, prm->max_y, prm->th_dist, prm->nn_ratio,
+                         prm->check_orientation, ws->g_items.as<uint4>(), ws->g_cells.as<int>(), ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(),
+                         d_m21, d_m12, d_nm, st, &launched);
+  orb_knn_count_launches(launched);
+  CU(cudaGetLastError());
+  if (host) {
+    CU(cudaMemcpyAsync(matches12, d_m12, F * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (matches21) CU(cudaMemcpyAsync(matches21, d_m21, F * cap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return ORB_OK;
+}
+
 int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
                       const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
                       const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,

@@ -32,6 +32,8 @@ void orb_knn_count_launches(long long n);
 void orb_launch_search_by_bow(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, const uint8_t*,
                               const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, int, int, float, int, void*, int*, uint2*, int*,
                               int*, int*, int*, cudaStream_t, long long*);
+void orb_launch_search_init(const OrbKeypoint*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*, int, int, float, float, float,
+                            float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
 void orb_launch_undistort(const void*, const OrbKeypoint*, const int*, int, int, OrbKeypoint*, cudaStream_t);
 struct BowVoc {   // == bow.cu
   const int* child_start; const int* child_id; const uint4* child_desc; const uint8_t* is_leaf; const int* word_of; const double* word_weight;

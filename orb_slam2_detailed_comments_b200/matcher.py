@@ -199,3 +199,19 @@ class ORBmatcher:
         check(_lib.lib().orb_search_by_bow(MEM_HOST, *p[:7], qcap, *p[7:], cap, F, int(self.TH_LOW if th_dist is None else th_dist),
                                            float(self.mfNNratio), int(self.mbCheckOrientation), _vp(assigned), _vp(kf_match), _vp(nm), None))
         return assigned, kf_match, nm
+
+    def SearchForInitialization(self, kps2_un, desc2, n2, queries, qdesc, n_queries, bounds, th_dist: int | None = None):
+        """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) for F frame
+        pairs. queries [F,qcap] QUERY_DTYPE: u, v = vbPrevMatched, radius = windowSize, levels (0, 0), angle, SKIP for level > 0.
+        Returns (vnMatches12 [F,qcap], matches21 [F,cap], nmatches [F])."""
+        from ._lib import OrbSearchParams
+        F, cap = kps2_un.shape
+        qcap = queries.shape[1]
+        c = np.ascontiguousarray
+        a = [c(kps2_un), c(desc2, np.uint8), c(n2, np.int32), c(queries), c(qdesc, np.uint8), c(n_queries, np.int32)]
+        prm = OrbSearchParams(float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), int(self.TH_LOW if th_dist is None else th_dist),
+                              float(self.mfNNratio), int(self.mbCheckOrientation), 0)
+        m12, m21, nm = np.empty((F, qcap), np.int32), np.empty((F, cap), np.int32), np.empty(F, np.int32)
+        check(_lib.lib().orb_search_for_initialization(MEM_HOST, _vp(a[0]), _vp(a[1]), _vp(a[2]), cap, _vp(a[3]), _vp(a[4]), _vp(a[5]), qcap, F,
+                                                       C.byref(prm), _vp(m12), _vp(m21), _vp(nm), None))
+        return m12, m21, nm

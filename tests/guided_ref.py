@@ -138,3 +138,61 @@ def search_by_projection(kps, desc, queries, qdesc, bounds, th_dist=100, nn_rati
                 qmatch[iq] = -1
                 nm -= 1
     return assigned, qmatch, nm
+
+
+def search_for_initialization(kps, desc, queries, qdesc, bounds, th_dist=50, nn_ratio=0.9, check_orientation=True):
+    """src/ORBmatcher.cc:570-712, independent Python statement."""
+    grid = Grid(kps, bounds)
+    n, m = len(kps), len(queries)
+    m12 = np.full(m, -1, np.int32)
+    m21 = np.full(n, -1, np.int32)
+    mdist = np.full(n, 2 ** 31 - 1, np.int64)
+    hist = [[] for _ in range(HISTO)]
+    factor = f32(HISTO) / f32(360.0)
+    bits = np.unpackbits(desc, axis=1) if n else np.zeros((0, 256), np.uint8)
+    qbits = np.unpackbits(qdesc, axis=1) if m else np.zeros((0, 256), np.uint8)
+    nm = 0
+    for i1 in range(m):
+        Q = queries[i1]
+        if Q["flags"] & 1:
+            continue
+        cand = grid.in_area(Q["u"], Q["v"], Q["radius"], int(Q["min_level"]), int(Q["max_level"]))
+        best = best2 = 2 ** 31 - 1
+        bidx = -1
+        for i2 in cand:
+            d = int(np.count_nonzero(bits[i2] != qbits[i1]))
+            if mdist[i2] <= d:
+                continue
+            if d < best:
+                best2, best, bidx = best, d, i2
+            elif d < best2:
+                best2 = d
+        if best <= th_dist and f32(best) < f32(f32(best2) * f32(nn_ratio)):
+            if m21[bidx] >= 0:
+                m12[m21[bidx]] = -1
+                nm -= 1
+            m12[i1], m21[bidx], mdist[bidx] = bidx, i1, best
+            nm += 1
+            if check_orientation:
+                rot = f32(Q["angle"]) - f32(kps["angle"][bidx])
+                if rot < 0:
+                    rot = f32(rot + f32(360.0))
+                b = _round_away(f32(rot * factor))
+                if b == HISTO:
+                    b = 0
+                if 0 <= b < HISTO:
+                    hist[b].append(i1)
+    if check_orientation:
+        keep = three_maxima([len(h) for h in hist])
+        for b in range(HISTO):
+            if b in keep:
+                continue
+            for i1 in hist[b]:
+                if m12[i1] >= 0:
+                    m12[i1] = -1
+                    nm -= 1
+    inv = np.full(n, -1, np.int32)
+    for i1 in range(m):
+        if m12[i1] >= 0:
+            inv[m12[i1]] = i1
+    return m12, inv, nm

@@ -51,5 +51,5 @@ def test_dropin_matches_oracle_on_gpu(tmp_path, shape):
     assert r.returncode == 0, r.stdout + r.stderr
     assert "PASS" in r.stdout
     for part in ("operator():", "ExtractBatch:", "ExtractStereo:", "SearchByProjection (frame-to-frame form)", "SearchByProjection (local-map form)",
-                 "ComputeDistinctiveDescriptors:", "SearchByBoW:", "ORBVocabulary::transform:", "UndistortKeyPoints:", "ORBmatcher: kNN"):
+                 "ComputeDistinctiveDescriptors:", "SearchForInitialization:", "SearchByBoW:", "ORBVocabulary::transform:", "UndistortKeyPoints:", "ORBmatcher: kNN"):
         assert part in r.stdout, part
