@@ -22,10 +22,7 @@ template <bool CLAMP>   // CLAMP: tap sum > 256 (legacy taps sum to 257): satura
 __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
                                                               const __grid_constant__ OrbGeom g) {
   __shared__ uint4 s_p[(BL_TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
-  int level = 0;
-#pragma unroll 1
-  for (int l = 1; l < g.nlevels; ++l)
-    if ((int)blockIdx.x >= g.lv[l].blur_tile_base) level = l;
+  const int level = orb_level_of(g.blur_base, (int)blockIdx.x);
   const OrbLevel& L = g.lv[level];
   const unsigned t = blockIdx.x - L.blur_tile_base;
   const unsigned ty_ = (t * L.blur_inv_tx) >> 20;            // t / blur_tiles_x (host-checked range)

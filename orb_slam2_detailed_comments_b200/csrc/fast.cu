@@ -161,8 +161,7 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
 //   SECOND == true : corners in the columns marked in `need` (cells that found no ini survivor) -> plane `pl` (min survivors).
 template <bool SECOND>
 __device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const uint8_t* __restrict__ need, const uint16_t* __restrict__ list,
-                                         int n, int lane, uint32_t* __restrict__ pl, int wCell, int xa, int xlim, int ini_th) {
-  const unsigned inv = (1u << 20) / (unsigned)wCell + 1u;      // p / wCell == (p * inv) >> 20 for p < 4096, wCell < 256
+                                         int n, int lane, uint32_t* __restrict__ pl, int wCell, unsigned inv, int xa, int xlim, int ini_th) {
   for (int i = lane; i < n; i += 32) {
     const int e = list[i];
     const int y = e >> 9, x = e & 511;
@@ -170,7 +169,7 @@ __device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const u
     const int s = q[0];
     if (SECOND ? (need[x] == 0) : (s < ini_th)) continue;
     const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);
-    const unsigned r = p - ((p * inv) >> 20) * (unsigned)wCell;   // column inside the cell's detection window
+    const unsigned r = p - __umulhi(p, inv) * (unsigned)wCell;   // column inside the cell's detection window (inv = 2^32 / wCell + 1)
     bool ok = s > q[-FAST_SP] && s > q[FAST_SP];
     if (r > 0) ok = ok && s > q[-1] && s > q[-FAST_SP - 1] && s > q[FAST_SP - 1];
     if ((int)r < wCell - 1 && x + 1 < xlim) ok = ok && s > q[1] && s > q[-FAST_SP + 1] && s > q[FAST_SP + 1];
@@ -192,13 +191,10 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   __shared__ int s_retry;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
-  int level = 0;
-#pragma unroll 1
-  for (int l = 1; l < g.nlevels; ++l)
-    if ((int)blockIdx.x >= g.lv[l].fast_tile_base) level = l;
+  const int level = orb_level_of(g.fast_base, (int)blockIdx.x);
   const OrbLevel& L = g.lv[level];
   const int t = blockIdx.x - L.fast_tile_base;
-  const int ci = t / L.fast_nseg, sg = t - ci * L.fast_nseg;
+  const int ci = (int)(((unsigned)t * L.fast_inv_nseg) >> 20), sg = t - ci * L.fast_nseg;   // t / fast_nseg
   const int j0 = sg * L.fast_G, j1 = min(j0 + L.fast_G, L.nCols);
   const int wCell = L.wCell;
   int* cnt_row = cell_cnt + (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
@@ -216,7 +212,8 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   const int nvec = (X1 - xa + 15) >> 4;
   const uint8_t* src = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)iniY * L.pitch + xa;
   // 1. stage the window; clear the score plane and the survivor bit planes
-  const unsigned inv_nvec = 65536u / (unsigned)nvec + 1u;   // i / nvec == (i * inv) >> 16 for i < 65 * 18
+  // i / nvec == (i * inv) >> 16 for i < 65 * 18 holds for any inv in [65536 / nvec, 65536 / nvec + 2]: one MUFU.RCP instead of a division
+  const unsigned inv_nvec = (unsigned)(__frcp_rn((float)nvec) * 65536.f) + 1u;
   for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
     const int y = (int)(((unsigned)i * inv_nvec) >> 16), v = i - y * nvec;
     *reinterpret_cast<uint4*>(win + y * FAST_WP + 16 + 16 * v) = *reinterpret_cast<const uint4*>(src + (long long)y * L.pitch + 16 * v);
@@ -240,7 +237,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   __syncthreads();
   // 3. NMS of the corners with S >= iniTh -> ini survivor plane. A suppressor of such a corner has S >= iniTh itself, so it was
   //    scored above. `need` is re-initialised meanwhile (nobody reads it until the next barrier).
-  fast_nms<false>(sc, need, list, ncorner, lane, pl_ini, wCell, xa, xlim, g.ini_th);
+  fast_nms<false>(sc, need, list, ncorner, lane, pl_ini, wCell, L.inv_wcell, xa, xlim, g.ini_th);
   for (int i = tid; i < FAST_WP / 4; i += FAST_THREADS) reinterpret_cast<unsigned*>(need)[i] = 0u;
   __syncthreads();
   // 4. cells without an ini survivor retry at minTh (:1521): mark their detection columns
@@ -274,7 +271,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
     ncorner += n2;
     __syncthreads();
     // 4b. NMS of every corner (S >= minTh) of the retry cells -> min survivor plane
-    fast_nms<true>(sc, need, list, ncorner, lane, pl_min, wCell, xa, xlim, g.ini_th);
+    fast_nms<true>(sc, need, list, ncorner, lane, pl_min, wCell, L.inv_wcell, xa, xlim, g.ini_th);
     __syncthreads();
   }
 

@@ -151,6 +151,9 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.fast_G = std::max(1, ORB_FAST_TILE_W / L.wCell);
     L.fast_nseg = (L.nCols + L.fast_G - 1) / L.fast_G;
     L.fast_tile_base = ftiles;
+    L.fast_inv_nseg = (1u << 20) / (unsigned)L.fast_nseg + 1u;   // t / nseg == (t * inv) >> 20 while t * nseg < 2^20 (nseg == 1 included)
+    if ((long long)L.fast_nseg * L.nRows * L.fast_nseg >= (1 << 20)) return fail(ORB_E_SHAPE, "level %d: FAST tile index out of the reciprocal's range", l);
+    L.inv_wcell = (unsigned)((1ull << 32) / (unsigned)L.wCell + 1ull);
     ftiles += L.fast_nseg * L.nRows;
     L.blur_tiles_x = (L.cols + 127) / 128;
     L.blur_tile_base = btiles;
@@ -192,6 +195,10 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     }
   }
   g.blur_tiles_total = btiles;
+  for (int l = 0; l < ORB_MAX_LEVELS; ++l) {
+    g.blur_base[l] = l < g.nlevels ? g.lv[l].blur_tile_base : INT_MAX;
+    g.fast_base[l] = l < g.nlevels ? g.lv[l].fast_tile_base : INT_MAX;
+  }
   g.ncells_total = cells; g.raw_total = raw; g.node_total = nodes; g.fast_tiles_total = ftiles;
   g.frame_stride = plane;
   e->geom = g;

@@ -38,6 +38,8 @@ struct OrbLevel {
   int pyr_fast;              // 1: 4-pixel window kernel applies (horizontal ratio <= 2)
   int fast_G, fast_nseg;     // FAST tile = one cell row x fast_G cells; segments per cell row
   int fast_tile_base;        // first FAST tile of this level
+  unsigned fast_inv_nseg;    // 2^20 / fast_nseg + 1: t / fast_nseg == (t * inv) >> 20
+  unsigned inv_wcell;        // 2^32 / wCell + 1: p / wCell == __umulhi(p, inv) for p < 2^16 (wCell >= 30)
   int blur_tile_base, blur_tiles_x;   // 128 x 32 blur tiles: first tile of this level, tiles per row
   unsigned blur_inv_tx;      // t / blur_tiles_x == (t * blur_inv_tx) >> 20
 };
@@ -52,8 +54,22 @@ struct OrbGeom {
   int blur_taps[7];
   unsigned blur_k[10];       // packed tap words of the blur kernel: tapA, tapB (DP4A), e0..e3, o0..o3 (DP2A)
   int blur_tiles_total;
+  // first tile of every level (INT_MAX beyond nlevels): a 4-step binary search finds a CTA's level (orb_level_of)
+  int blur_base[ORB_MAX_LEVELS];
+  int fast_base[ORB_MAX_LEVELS];
   OrbLevel lv[ORB_MAX_LEVELS];
 };
+
+#ifdef __CUDACC__
+// level l with base[l] <= tile < base[l + 1]; base is ascending, base[0] == 0, padded with INT_MAX to 16 entries
+__device__ __forceinline__ int orb_level_of(const int* base, int tile) {
+  int l = tile >= base[8] ? 8 : 0;
+  if (tile >= base[l + 4]) l += 4;
+  if (tile >= base[l + 2]) l += 2;
+  if (tile >= base[l + 1]) l += 1;
+  return l;
+}
+#endif
 
 struct ResizeTab {   // per PADDED destination index of cv::resize INTER_LINEAR: source offset + 11-bit coefficients
   int ofs;           // first source pixel (second = ofs + 1; its coefficient is 0 where that would leave the image)

@@ -2,6 +2,7 @@
 // geometry): error reporting, the CUDA-call guard, the grow-only device buffer and the kernel launchers of the other .cu files.
 #pragma once
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
