@@ -121,30 +121,60 @@ def cpu_knn_rate(threads, q_n=256, d_n=200_000):
     return q_n * d_n / dt, dt
 
 
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "orb_ref_extract")
+
+
+def _ref_binary_rate(frames, nf, threads, repeat):
+    """oracle/_ref/orb_ref_extract --time: the reference's own src/ORBextractor.cc (compiled unmodified against oracle/cvshim,
+    DESIGN.md §2), one ORBextractor per thread over the frames. Returns (images, seconds)."""
+    import struct
+    import subprocess
+    import tempfile
+    n, H, W = frames.shape
+    with tempfile.TemporaryDirectory() as d:
+        fin = os.path.join(d, "in.bin")
+        with open(fin, "wb") as f:
+            f.write(struct.pack("<8if", 0x4F524231, n, W, H, nf, 8, 20, 7, 1.2))
+            f.write(np.ascontiguousarray(frames, np.uint8).tobytes())
+        out = subprocess.run([REF_BIN, "--time", fin, str(threads), str(repeat)], check=True, capture_output=True, text=True, timeout=900)
+    images, sec, _ = out.stdout.split()
+    return int(images), float(sec)
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port; the reference itself cannot be compiled here)
-    on all host cores, same config/metric/unit. Rank 0 only."""
+    """--impl reference: the reference's CPU path on all host cores, same config/metric/unit. Rank 0 only.
+    kind "reference" = oracle/_ref/orb_ref_extract (the reference's own ORBextractor.cc; its OpenCV primitives are the cv2-pinned
+    restatements of oracle/cv_primitives.cpp, because the image has no OpenCV C++); kind "port" = the oracle, if the binary is absent."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     label, W, H, nf, _ = WORKLOADS[args.workload]
     cores = _host_cores()
-    from oracle import oracle_py
     n = max(2 * cores, 16)   # images per step: a bounded sample of the workload
     frames = synth.synth_batch(W, H, n, seed0=4321, distinct=min(8, n))
-    for _ in range(args.warmup):
-        oracle_py.extract_many(frames, nf, cores)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        oracle_py.extract_many(frames, nf, cores)
-    dt = time.perf_counter() - t0
+    if os.access(REF_BIN, os.X_OK):
+        kind = "reference"
+        how = "one reference ORBextractor (src/ORBextractor.cc compiled against oracle/cvshim) per thread"
+        if args.warmup:
+            _ref_binary_rate(frames, nf, cores, args.warmup)
+        images, dt = _ref_binary_rate(frames, nf, cores, args.steps)   # the binary warms one pass itself, then times `steps` passes
+        assert images == n * args.steps
+    else:
+        kind, how = "port", "one oracle extractor per thread"
+        from oracle import oracle_py
+        for _ in range(args.warmup):
+            oracle_py.extract_many(frames, nf, cores)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            oracle_py.extract_many(frames, nf, cores)
+        dt = time.perf_counter() - t0
     v = n * args.steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": label, "images_per_step": n, "timing": "host wall clock"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{n} images per step x {args.steps} steps, one oracle extractor per thread"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{n} images per step x {args.steps} steps, {how}"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

@@ -11,6 +11,7 @@
 //   cv::FAST(th, nonmax=true) TYPE_9_16 (src/ORBextractor.cc:1510, 1521)
 //   cv::fastAtan2                       (src/ORBextractor.cc:160)
 #pragma once
+#include <cstddef>
 #include <cstdint>
 #include <vector>
 

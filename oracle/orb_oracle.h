@@ -6,8 +6,10 @@
  * computeOrbDescriptor :177-254) and src/ORBmatcher.cc (DescriptorDistance :2073-2093 and the
  * best/second-best idiom :304-342), on top of the OpenCV primitives restated in cv_primitives.*.
  *
- * The reference itself cannot be compiled in the build container (needs OpenCV C++ headers;
- * include/ORBextractor.h:26) and ships no tests or golden vectors, so parity is pinned by
+ * The reference ships no tests or golden vectors and cannot be built against OpenCV in the build
+ * container (no OpenCV C++ headers; include/ORBextractor.h:26), so parity is pinned by
+ * (0) the reference's own src/ORBextractor.cc and Thirdparty/DBoW2 compiled unmodified against
+ * oracle/cvshim (oracle/_ref, tests/test_reference_binary.py: this oracle == that binary bit for bit),
  * (1) the primitives checked bit-exact against the real OpenCV (cv2 4.13) and (2) a whole-pipeline
  * composition of real cv2 calls (tests/golden/make_golden.py) whose outputs are committed under
  * tests/golden/ and compared with this oracle.

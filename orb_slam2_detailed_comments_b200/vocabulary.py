@@ -33,12 +33,16 @@ def read_text_vocabulary(path: str):
     return k, L, scoring, weighting, parent, is_leaf, desc, weight
 
 
-def write_text_vocabulary(path: str, k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0):
-    """saveToTextFile counterpart (TemplatedVocabulary.h:1560-1590): repr() keeps every bit of the double weights."""
+def write_text_vocabulary(path: str, k, L, parent, is_leaf, desc, weight, scoring=0, weighting=0, trailing_newline=True):
+    """saveToTextFile counterpart (TemplatedVocabulary.h:1560-1590): repr() keeps every bit of the double weights.
+    trailing_newline=False writes the last node line without '\n': the reference's loadFromTextFile loops on `!f.eof()`
+    (TemplatedVocabulary.h:1411) and turns the empty line after a final newline into one more child of the root whose
+    descriptor is uninitialised memory; read_text_vocabulary() here skips blank lines (canonicalisation 7)."""
     with open(path, "w") as f:
         f.write(f"{k} {L} {scoring} {weighting}\n")
-        for i in range(1, len(parent)):
-            f.write(f"{int(parent[i])} {int(is_leaf[i])} " + " ".join(str(int(b)) for b in desc[i]) + f" {float(weight[i])!r}\n")
+        lines = (f"{int(parent[i])} {int(is_leaf[i])} " + " ".join(str(int(b)) for b in desc[i]) + f" {float(weight[i])!r}"
+                 for i in range(1, len(parent)))
+        f.write("\n".join(lines) + ("\n" if trailing_newline else ""))
 
 
 class ORBVocabulary:
