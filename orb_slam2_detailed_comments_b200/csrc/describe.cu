@@ -161,14 +161,14 @@ __device__ __forceinline__ void orb_sincos(float angle, float* s, float* c) {
 //     two REDUX adds finish the moments (exact int32).
 //   * rBRIEF: lane = descriptor byte; its 8 test pairs (x0, y0, x1, y1 as floats) come from shared memory, one LDS.128 each;
 //     the 512 pixel gathers hit the staged 37 x 40-byte patch in shared memory.
-#define DESC_WARPS 8
+#define DESC_WARPS 4     // 128-thread CTAs, 14.5 KB of shared memory: one fits beside five resident FAST CTAs of the other pass stream
 #define DESC_KPW 8
 __device__ __forceinline__ int dp4a_u8_s8(unsigned a, unsigned b, int c) {   // a: unsigned bytes, b: signed bytes
   int d;
   asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
   return d;
 }
-__global__ void __launch_bounds__(DESC_WARPS * 32, 3)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 24 / DESC_WARPS)
 orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr, const uint32_t* __restrict__ kept,
                     const int* __restrict__ kept_cnt, OrbKeypoint* __restrict__ kps, uint8_t* __restrict__ desc, int cap,
                     int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
@@ -189,11 +189,12 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
   }
   const int w_first = (blockIdx.x * DESC_WARPS + warp) * DESC_KPW;
   const int w_end = min(min(w_first + DESC_KPW, total), cap);
-  // rBRIEF pattern as floats, [test bit][lane] so that one LDS.128 per test is conflict-free (256 threads = 256 test pairs)
+  // rBRIEF pattern as floats, [test bit][lane] so that one LDS.128 per test is conflict-free (256 test pairs)
   __shared__ float4 s_pat[8 * 32];
-  {
-    const char4 p = reinterpret_cast<const char4*>(d_pattern)[lane * 8 + warp];
-    s_pat[warp * 32 + lane] = make_float4((float)p.x, (float)p.y, (float)p.z, (float)p.w);
+#pragma unroll
+  for (int b = warp; b < 8; b += DESC_WARPS) {
+    const char4 p = reinterpret_cast<const char4*>(d_pattern)[lane * 8 + b];
+    s_pat[b * 32 + lane] = make_float4((float)p.x, (float)p.y, (float)p.z, (float)p.w);
   }
   __syncthreads();
   if (w_first >= w_end) return;

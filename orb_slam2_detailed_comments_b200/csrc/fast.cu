@@ -20,13 +20,14 @@
 //      min / ini survivor bit planes;
 //   5. per cell (one warp each, lane = row): 64-bit row masks from the bit planes, popc + warp scan give every
 //      survivor its row-major rank; ini/min selection by the cell's ini count.
+#include <algorithm>
 #include <atomic>
 #include "orb_common.cuh"
 
 #define FAST_THREADS 256
 #define FAST_WARPS 8
-#define FAST_WP 304      // window row pitch in smem: 16 B front pad + <= 272 B; 76 words: 8 consecutive rows start in 8 different banks
-#define FAST_SP 272      // score plane row pitch
+#define FAST_WP 256      // window row pitch in smem: 16 B front pad + 15 alignment + ORB_FAST_TILE_W (219) + 6 halo = 256
+#define FAST_SP 240      // score plane row pitch: 15 + 219 + 4 <= 240
 #define FAST_BP 11       // survivor bit plane row pitch in words (window columns < 288 -> 9 words, +2 for the 64-bit extract)
 
 // cornerScore (OpenCV fast_score.cpp, 16-pixel ring, K = 8): S = max(max_arcs min_9(v - r), max_arcs min_9(r - v)) - 1,
@@ -61,7 +62,9 @@ __device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned t1) {
   return (((a & 0x7f7f7f7fu) | 0x80808080u) - t1) | a;
 }
 
-// Quick reject + compaction + scoring for the rows [row0, row1) of one warp.
+// Quick reject + compaction + scoring for the rows row0, row0 + FAST_WARPS, row0 + 2 * FAST_WARPS, ... < row1 of one warp (rows are
+// dealt round-robin to the warps: a textured blob spans adjacent rows, so every warp gets a share of its candidates and the
+// barrier after the scoring does not wait for one loaded warp).
 //   SECOND == false: candidates = pixels passing the compass test at iniTh (superset of all S >= iniTh);
 //   SECOND == true : candidates = pixels passing at minTh but not at iniTh (not scored yet), in the columns marked in `need`.
 // Candidate codes go to list[start ..], corners (S >= minTh) are compacted in place to list[start ..] as (y << 9) | x and
@@ -76,8 +79,8 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
   // candidate bits of this thread: nibble ri of cand[hi] = the 4 pixels of quad ((lane + 5*ri) & 31) + 32*hi in row row0 + ri.
   // The per-row rotation spreads a textured blob (candidates cluster in 2-D) over many lanes.
   unsigned cand[2] = {0u, 0u};
-  for (int ri = 0; row0 + ri < row1; ++ri) {
-    const int y = row0 + ri;
+  for (int ri = 0; row0 + FAST_WARPS * ri < row1; ++ri) {
+    const int y = row0 + FAST_WARPS * ri;
     const int rot = (lane + 5 * ri) & 31;
 #pragma unroll
     for (int hi = 0; hi < 2; ++hi) {
@@ -141,7 +144,7 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
       const int code = list[start + i];
       const int ri = (code >> 2) & 7;
       const int q = (((code >> 5) + 5 * ri) & 31) + ((code >> 10) << 5);
-      e = ((row0 + ri) << 9) | (qbase + 4 * q + (code & 3));
+      e = ((row0 + FAST_WARPS * ri) << 9) | (qbase + 4 * q + (code & 3));
       s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
     }
     const bool corner = s >= min_th;
@@ -180,14 +183,14 @@ __device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const u
 template <bool SMALL_TH>   // SMALL_TH: iniTh <= 126 (carry-free byte compares); otherwise the generic video intrinsic
 __global__ void __launch_bounds__(FAST_THREADS)
 orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ cell_kp,
-                     int* __restrict__ err_flag, int win_rows, int sc_rows, int list_cap, const __grid_constant__ OrbGeom g) {
+                     int* __restrict__ err_flag, int win_rows, int sc_rows, int row_cap, const __grid_constant__ OrbGeom g) {
   extern __shared__ __align__(16) uint8_t smem[];
   uint8_t* win = smem;                                    // [win_rows][FAST_WP], pixel x at column 16 + x
   uint8_t* sc = win + win_rows * FAST_WP;                 // [sc_rows][FAST_SP], score of domain row y at row y + 1
   uint32_t* pl_min = reinterpret_cast<uint32_t*>(sc + sc_rows * FAST_SP);   // [sc_rows - 2][FAST_BP] NMS survivors, S >= minTh
   uint32_t* pl_ini = pl_min + (sc_rows - 2) * FAST_BP;                       //                         S >= iniTh
-  uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + (sc_rows - 2) * FAST_BP);   // [FAST_WARPS][list_cap]
-  uint8_t* need = reinterpret_cast<uint8_t*>(lists + FAST_WARPS * list_cap);          // [FAST_WP] 0x80 = column takes part in the pass
+  uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + (sc_rows - 2) * FAST_BP);   // [max_h][row_cap], a warp's rows are contiguous
+  uint8_t* need = reinterpret_cast<uint8_t*>(lists + (sc_rows - 2) * row_cap);        // [FAST_WP] 0x80 = column takes part in the pass
   __shared__ int s_retry;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
@@ -228,10 +231,10 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   // 2. first detection at iniTh (the reference's first cv::FAST call per cell, :1510)
   const int qbase = dx0 & ~3;
   const int nq = (dx1 - qbase + 3) >> 2;                 // <= 64
-  uint16_t* list = lists + warp * list_cap;
-  // warp w owns the detection rows [w * R, (w + 1) * R), R = ceil(dh / 8) <= 8
-  const int rpw = (dh + FAST_WARPS - 1) / FAST_WARPS;
-  const int row0 = warp * rpw, row1 = min(row0 + rpw, dh);
+  // warp w owns max_h / 8 (+ 1 if w < max_h % 8) rows of the largest level: its list starts after the rows of the warps before it
+  uint16_t* list = lists + (warp * ((sc_rows - 2) >> 3) + min(warp, (sc_rows - 2) & 7)) * row_cap;
+  // warp w owns the detection rows w, w + 8, w + 16, ... (<= 8 rows, dh <= 64)
+  const int row0 = warp, row1 = dh;
   const int xlim = L.maxBX - 3 - xa;                     // detection columns end here (last cell may be clipped)
   int ncorner = fast_detect<SMALL_TH, false>(win, sc, need, list, 0, row0, row1, qbase, nq, lane, g.ini_th, g.min_th);
   __syncthreads();
@@ -343,13 +346,22 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
   int max_h = 0;
   for (int l = 0; l < g.nlevels; ++l) max_h = max(max_h, g.lv[l].hCell);
   const int win_rows = max_h + 6, sc_rows = max_h + 2;
-  const int list_cap = ((max_h + FAST_WARPS - 1) / FAST_WARPS) * 256;   // a warp's rows x <= 256 detection columns
+  // a warp's list holds one entry per detection pixel of its rows at most: rows x (aligned quads of the widest tile) x 4
+  int row_cap = 0;
+  for (int l = 0; l < g.nlevels; ++l) {
+    const int dw = std::min(g.lv[l].fast_G * g.lv[l].wCell, g.lv[l].maxBX - ORB_MIN_BORDER - 6);   // detection columns of a tile
+    row_cap = std::max(row_cap, 4 * ((dw + 3 + 3) / 4));                                           // + quad alignment at the front
+  }
+  row_cap = std::min(row_cap, 256);
   const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)max_h * FAST_BP * 4 +
-                      (size_t)FAST_WARPS * list_cap * 2 + FAST_WP;
+                      (size_t)max_h * row_cap * 2 + FAST_WP;   // KITTI: 40 KB -> 5 resident CTAs per SM
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
   // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
+  typedef void (*Kern)(const uint8_t*, int*, uint32_t*, int*, int, int, int, const OrbGeom);
+  static const Kern kerns[2] = {orb_fast_band_kernel<false>, orb_fast_band_kernel<true>};
   static std::atomic<bool> configured[64][2];
   const int small = g.ini_th <= 126;      // both thresholds (min <= ini) in the carry-free byte-compare range
+  const Kern kern = kerns[small];
   int dev = 0;
   cudaGetDevice(&dev);
   dev &= 63;
@@ -357,15 +369,11 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
     int optin = 0;
     cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaFuncAttributes fa;
-    if (small) cudaFuncGetAttributes(&fa, orb_fast_band_kernel<true>);
-    else cudaFuncGetAttributes(&fa, orb_fast_band_kernel<false>);
-    const int dyn_max = optin - (int)fa.sharedSizeBytes;   // the limit covers static + dynamic shared memory
-    if (small) cudaFuncSetAttribute(orb_fast_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max);
-    else cudaFuncSetAttribute(orb_fast_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max);
+    cudaFuncGetAttributes(&fa, kern);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);   // the limit covers static + dynamic
     configured[dev][small].store(true, std::memory_order_release);
   }
   const dim3 grid(g.fast_tiles_total, batch);
-  if (small) orb_fast_band_kernel<true><<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, list_cap, g);
-  else orb_fast_band_kernel<false><<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, list_cap, g);
+  kern<<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, row_cap, g);
   ++*launches;
 }

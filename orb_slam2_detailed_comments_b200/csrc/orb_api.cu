@@ -150,6 +150,8 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     cells += L.nCols * L.nRows;
     L.fast_G = std::max(1, ORB_FAST_TILE_W / L.wCell);
     L.fast_nseg = (L.nCols + L.fast_G - 1) / L.fast_G;
+    L.fast_G = (L.nCols + L.fast_nseg - 1) / L.fast_nseg;          // same number of tiles, balanced widths (41 cells: 7,7,7,7,7,6 instead of 8 x 5 + 1)
+    if (L.fast_G * L.wCell > ORB_FAST_TILE_W) return fail(ORB_E_SHAPE, "level %d: FAST cell wider than a tile", l);   // wCell < 60 by construction
     L.fast_tile_base = ftiles;
     L.fast_inv_nseg = (1u << 20) / (unsigned)L.fast_nseg + 1u;   // t / nseg == (t * inv) >> 20 while t * nseg < 2^20 (nseg == 1 included)
     if ((long long)L.fast_nseg * L.nRows * L.fast_nseg >= (1 << 20)) return fail(ORB_E_SHAPE, "level %d: FAST tile index out of the reciprocal's range", l);

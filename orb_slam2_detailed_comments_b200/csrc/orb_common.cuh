@@ -14,7 +14,7 @@
 #define ORB_MIN_BORDER 16    // EDGE_THRESHOLD - 3, :1443
 #define ORB_APRON 4          // reflect-101 apron columns written around every padded plane (3 used by the blur)
 #define ORB_APRON_ROWS 4     // allocated apron rows above/below a plane (3 written; the 4th is only ever multiplied by 0)
-#define ORB_FAST_TILE_W 248  // max detection-domain width of one FAST tile (<= 64 aligned pixel quads)
+#define ORB_FAST_TILE_W 219  // max detection-domain width of one FAST tile: 16 + 15 + 219 + 6 = the 256-byte window pitch in fast.cu
 #define ORB_CELL_CAP 128     // NMS survivors kept per 30-px cell (overflow -> ORB_E_CAPACITY)
 
 struct OrbLevel {
