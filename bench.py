@@ -598,6 +598,12 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n} images of the same workload, one oracle extractor per thread, {dt:.1f} s wall",
                                 "knn_pairs_per_s": kv}
+        if os.access(REF_BIN, os.X_OK):   # the reference's own ORBextractor.cc (oracle/_ref), same frames, all host cores
+            rframes = synth.synth_batch(W, H, max(2 * cores, 16), seed0=4321, distinct=8)
+            rimg, rdt = _ref_binary_rate(rframes, nf, cores, 2)
+            line["cpu_baseline"]["reference_binary"] = {
+                "value": rimg / rdt, "unit": UNIT, "cores": cores, "kind": "reference",
+                "sample": f"{rimg} images, one reference ORBextractor (src/ORBextractor.cc over oracle/cvshim) per thread, {rdt:.1f} s wall"}
         bwv, bwdt = cpu_bow_rate(bow_voc, bow_base, cores)
         line["bow"]["cpu_baseline"] = {"value": bwv, "unit": "frames/s", "cores": cores, "kind": "port",
                                        "sample": f"4096 frames of the same workload, {bwdt:.1f} s wall"}
