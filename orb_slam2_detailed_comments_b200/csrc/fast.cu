@@ -76,42 +76,49 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
   const unsigned thi4 = (unsigned)ini_th * 0x01010101u, ti1 = thi4 + 0x01010101u;
   const unsigned thm4 = (unsigned)min_th * 0x01010101u, tm1 = thm4 + 0x01010101u;
   const uint32_t lt = (1u << lane) - 1u;
-  // candidate bits of this thread: nibble ri of cand[hi] = the 4 pixels of quad ((lane + 5*ri) & 31) + 32*hi in row row0 + ri.
-  // The per-row rotation spreads a textured blob (candidates cluster in 2-D) over many lanes.
+  // candidate bits of this thread: byte (ri & 3) of cand[ri >> 2] = the 8 pixels of group (lane + 5*ri) & 31 in row row0 + 8*ri
+  // (a tile row is <= 29 aligned groups of 8 pixels: one pass per row). The per-row rotation spreads a textured blob
+  // (candidates cluster in 2-D) over many lanes.
   unsigned cand[2] = {0u, 0u};
   for (int ri = 0; row0 + FAST_WARPS * ri < row1; ++ri) {
     const int y = row0 + FAST_WARPS * ri;
-    const int rot = (lane + 5 * ri) & 31;
+    const int o = (lane + 5 * ri) & 31;
+    if (o < nq) {
+      const int x = qbase + 8 * o;
+      const uint2 colmask = *reinterpret_cast<const uint2*>(need + x);   // bit 7 of byte k: column x + k takes part
+      if (colmask.x | colmask.y) {
+        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
+        const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c3 = *reinterpret_cast<const unsigned*>(row + 8);
+        const uint2 c = *reinterpret_cast<const uint2*>(row);
+        const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const uint2*>(row + 3 * FAST_WP);
+        unsigned pass[2];
 #pragma unroll
-    for (int hi = 0; hi < 2; ++hi) {
-      const int q = rot + 32 * hi;
-      if (q < nq) {
-        const int x = qbase + 4 * q;
-        const unsigned colmask = *reinterpret_cast<const unsigned*>(need + x);   // bit 7 of byte k: column x + k takes part
-        if (colmask) {
-          const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
-          const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c1 = *reinterpret_cast<const unsigned*>(row),
-                         c2 = *reinterpret_cast<const unsigned*>(row + 4);
-          const unsigned up = *reinterpret_cast<const unsigned*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const unsigned*>(row + 3 * FAST_WP);
-          const unsigned lf = __byte_perm(c0, c1, 0x4321), rt = __byte_perm(c1, c2, 0x6543);
-          const unsigned au = __vabsdiffu4(c1, up), ad = __vabsdiffu4(c1, dn), al = __vabsdiffu4(c1, lf), ar = __vabsdiffu4(c1, rt);
-          unsigned pass;
+        for (int h = 0; h < 2; ++h) {
+          const unsigned c1 = h ? c.y : c.x;
+          const unsigned lf = h ? __byte_perm(c.x, c.y, 0x4321) : __byte_perm(c0, c.x, 0x4321);
+          const unsigned rt = h ? __byte_perm(c.y, c3, 0x6543) : __byte_perm(c.x, c.y, 0x6543);
+          const unsigned au = __vabsdiffu4(c1, h ? up.y : up.x), ad = __vabsdiffu4(c1, h ? dn.y : dn.x), al = __vabsdiffu4(c1, lf),
+                         ar = __vabsdiffu4(c1, rt);
+          unsigned ps;
           if (SMALL_TH) {
-            pass = (fast_gt4(au, SECOND ? tm1 : ti1) | fast_gt4(ad, SECOND ? tm1 : ti1)) &
-                   (fast_gt4(al, SECOND ? tm1 : ti1) | fast_gt4(ar, SECOND ? tm1 : ti1));
-            if (SECOND) pass &= ~((fast_gt4(au, ti1) | fast_gt4(ad, ti1)) & (fast_gt4(al, ti1) | fast_gt4(ar, ti1)));
+            ps = (fast_gt4(au, SECOND ? tm1 : ti1) | fast_gt4(ad, SECOND ? tm1 : ti1)) &
+                 (fast_gt4(al, SECOND ? tm1 : ti1) | fast_gt4(ar, SECOND ? tm1 : ti1));
+            if (SECOND) ps &= ~((fast_gt4(au, ti1) | fast_gt4(ad, ti1)) & (fast_gt4(al, ti1) | fast_gt4(ar, ti1)));
           } else {
-            pass = (__vcmpgtu4(au, SECOND ? thm4 : thi4) | __vcmpgtu4(ad, SECOND ? thm4 : thi4)) &
-                   (__vcmpgtu4(al, SECOND ? thm4 : thi4) | __vcmpgtu4(ar, SECOND ? thm4 : thi4));
-            if (SECOND) pass &= ~((__vcmpgtu4(au, thi4) | __vcmpgtu4(ad, thi4)) & (__vcmpgtu4(al, thi4) | __vcmpgtu4(ar, thi4)));
+            ps = (__vcmpgtu4(au, SECOND ? thm4 : thi4) | __vcmpgtu4(ad, SECOND ? thm4 : thi4)) &
+                 (__vcmpgtu4(al, SECOND ? thm4 : thi4) | __vcmpgtu4(ar, SECOND ? thm4 : thi4));
+            if (SECOND) ps &= ~((__vcmpgtu4(au, thi4) | __vcmpgtu4(ad, thi4)) & (__vcmpgtu4(al, thi4) | __vcmpgtu4(ar, thi4)));
           }
-          pass &= colmask;
-          cand[hi] |= ((pass * 0x204081u) >> 28) << (4 * ri);   // bits 7, 15, 23, 31 -> one nibble (the partial products never carry)
+          pass[h] = ps & (h ? colmask.y : colmask.x) & 0x80808080u;
         }
+        // bits 7, 15, 23, 31 of each half -> one nibble each (the partial products never carry)
+        const unsigned bits8 = ((pass[0] * 0x204081u) >> 28) | (((pass[1] * 0x204081u) >> 28) << 4);
+        const unsigned b = bits8 << ((8 * ri) & 31);
+        if (ri < 4) cand[0] |= b; else cand[1] |= b;
       }
     }
   }
-  // one warp scan places every thread's candidates in the warp's list (order is irrelevant). Entry = hi:1 | lane:5 | ri:3 | k:2,
+  // one warp scan places every thread's candidates in the warp's list (order is irrelevant). Entry = lane:5 | ri:3 | k:3,
   // decoded by full warps in the scoring loop
   int cnt;
   {
@@ -127,7 +134,7 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
 #pragma unroll
     for (int hi = 0; hi < 2; ++hi) {
       unsigned m = cand[hi];
-      const unsigned code = (unsigned)((hi << 10) | (lane << 5));
+      const unsigned code = (unsigned)((lane << 6) | (hi << 5));
       while (m) {
         *out++ = (uint16_t)(code | (unsigned)(__ffs(m) - 1));
         m &= m - 1;
@@ -142,9 +149,9 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
     int e = 0, s = 0;
     if (i < cnt) {
       const int code = list[start + i];
-      const int ri = (code >> 2) & 7;
-      const int q = (((code >> 5) + 5 * ri) & 31) + ((code >> 10) << 5);
-      e = ((row0 + FAST_WARPS * ri) << 9) | (qbase + 4 * q + (code & 3));
+      const int ri = (code >> 3) & 7;
+      const int o = ((code >> 6) + 5 * ri) & 31;
+      e = ((row0 + FAST_WARPS * ri) << 9) | (qbase + 8 * o + (code & 7));
       s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
     }
     const bool corner = s >= min_th;
@@ -222,15 +229,16 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
     *reinterpret_cast<uint4*>(win + y * FAST_WP + 16 + 16 * v) = *reinterpret_cast<const uint4*>(src + (long long)y * L.pitch + 16 * v);
   }
   for (int i = tid; i < (dh + 2) * (FAST_SP / 16); i += FAST_THREADS) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = tid; i < 2 * (sc_rows - 2) * FAST_BP; i += FAST_THREADS) pl_min[i] = 0u;
+  // both bit planes, 16 bytes per thread (the rounding may run a few words into the still empty lists)
+  for (int i = tid; i < (2 * (sc_rows - 2) * FAST_BP + 3) / 4; i += FAST_THREADS) reinterpret_cast<uint4*>(pl_min)[i] = make_uint4(0, 0, 0, 0);
   const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
   for (int i = tid; i < FAST_WP; i += FAST_THREADS) need[i] = (i >= dx0 && i < dx1) ? 0x80 : 0;   // pass 1: every detection column
   if (tid == 0) s_retry = 0;
   __syncthreads();
 
   // 2. first detection at iniTh (the reference's first cv::FAST call per cell, :1510)
-  const int qbase = dx0 & ~3;
-  const int nq = (dx1 - qbase + 3) >> 2;                 // <= 64
+  const int qbase = dx0 & ~7;                            // groups of 8 aligned pixels
+  const int nq = (dx1 - qbase + 7) >> 3;                 // <= 29
   // warp w owns max_h / 8 (+ 1 if w < max_h % 8) rows of the largest level: its list starts after the rows of the warps before it
   uint16_t* list = lists + (warp * ((sc_rows - 2) >> 3) + min(warp, (sc_rows - 2) & 7)) * row_cap;
   // warp w owns the detection rows w, w + 8, w + 16, ... (<= 8 rows, dh <= 64)
