@@ -411,7 +411,7 @@ def bench_bow(steps, warmup, world, voc, base):
     import torch
     import orb_slam2_detailed_comments_b200 as pkg
     from orb_slam2_detailed_comments_b200._lib import lib, check, MEM_DEVICE
-    gv = pkg.ORBVocabulary(*voc)
+    gv = pkg.ORBVocabulary(*voc, device=torch.cuda.current_device())
     F, cap = BOW_FRAMES, BOW_N
     desc = torch.from_numpy(np.stack([base[i % len(base)] for i in range(F)])).cuda()
     n = torch.full((F,), BOW_N, dtype=torch.int32, device="cuda")

@@ -366,7 +366,7 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
   if (device < 0 || device >= ndev) return fail(ORB_E_BADARG, "device %d out of range (%d devices)", device, ndev);
-  CU(cudaSetDevice(device));
+  ORB_ON_DEVICE(device);
   orb_extractor* e = new orb_extractor();
   e->prm = *p;
   e->device = device;
@@ -389,7 +389,7 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
 
 void orb_extractor_destroy(orb_extractor* e) {
   if (!e) return;
-  cudaSetDevice(e->device);
+  OrbDeviceGuard guard(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
   for (int w = 1; w < ORB_MAX_WS; ++w) {
     if (e->ws[w].st) { cudaStreamSynchronize(e->ws[w].st); cudaStreamDestroy(e->ws[w].st); }
@@ -440,7 +440,7 @@ void* orb_extractor_stream(orb_extractor* e) { return e ? (void*)e->stream : nul
 int orb_extractor_set_profiling(orb_extractor* e, int on) {
   if (!e) return fail(ORB_E_BADARG, "null argument");
   std::lock_guard<std::mutex> lk(e->mu);
-  CU(cudaSetDevice(e->device));
+  ORB_ON_DEVICE(e->device);
   resolve_stage_events(e);
   e->profile = on != 0;
   for (int i = 0; i < ORB_NUM_STAGES; ++i) e->stage_ms[i] = 0.0;
@@ -451,7 +451,7 @@ int orb_extractor_set_profiling(orb_extractor* e, int on) {
 int orb_extractor_stage_times(orb_extractor* e, double* ms, int64_t* passes) {
   if (!e || !ms) return fail(ORB_E_BADARG, "null argument");
   std::lock_guard<std::mutex> lk(e->mu);
-  CU(cudaSetDevice(e->device));
+  ORB_ON_DEVICE(e->device);
   resolve_stage_events(e);
   for (int i = 0; i < ORB_NUM_STAGES; ++i) ms[i] = e->stage_ms[i];
   if (passes) *passes = e->stage_passes;
@@ -464,7 +464,7 @@ int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, 
   if (!e || !images || !kps || !desc || !counts_dev) return fail(ORB_E_BADARG, "null argument");
   if (width <= 0 || height <= 0 || step < width || batch <= 0 || cap <= 0) return fail(ORB_E_BADARG, "bad size");
   std::lock_guard<std::mutex> lk(e->mu);
-  CU(cudaSetDevice(e->device));
+  ORB_ON_DEVICE(e->device);
   int rc = ensure_shape(e, width, height, batch, cap);
   if (rc != ORB_OK) return rc;
   const long long istride = (long long)step * height;
@@ -508,7 +508,7 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
   for (int i = 0; i < batch; ++i)
     if (!images[i]) return fail(ORB_E_BADARG, "null image %d", i);   // the reference returns silently on an empty image (:1966)
   std::lock_guard<std::mutex> lk(e->mu);
-  CU(cudaSetDevice(e->device));
+  ORB_ON_DEVICE(e->device);
   int rc = ensure_shape(e, width, height, batch, cap);
   if (rc != ORB_OK) return rc;
   const OrbGeom& g = e->geom;
@@ -689,7 +689,7 @@ int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurr
   if (index < 0 || index >= P.frames) return fail(ORB_E_BADARG, "image %d is not resident (last pass held %d frames)", index, P.frames);
   const OrbLevel& L = e->geom.lv[level];
   if (dst_step < L.cols) return fail(ORB_E_BADARG, "dst_step too small");
-  CU(cudaSetDevice(e->device));
+  ORB_ON_DEVICE(e->device);
   const uint8_t* src = (blurred ? P.blr.as<uint8_t>() : P.pyr.as<uint8_t>()) + (size_t)index * e->geom.frame_stride + L.plane_off;
   CU(cudaMemcpy2DAsync(dst, dst_step, src, L.pitch, L.cols, L.rows, cudaMemcpyDeviceToHost, P.st));
   CU(cudaStreamSynchronize(P.st));
@@ -701,7 +701,7 @@ int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keyp
   std::lock_guard<std::mutex> lk(e->mu);
   orb_extractor::PassWs& P = e->ws[e->last_ws];
   if (index < 0 || index >= P.frames) return fail(ORB_E_BADARG, "image %d is not resident", index);
-  CU(cudaSetDevice(e->device));
+  ORB_ON_DEVICE(e->device);
   const OrbGeom& g = e->geom;
   const OrbLevel& L = g.lv[level];
   int n = 0;

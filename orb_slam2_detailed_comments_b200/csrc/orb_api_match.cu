@@ -150,7 +150,7 @@ int orb_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, cons
   }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
-  CU(cudaSetDevice(device));
+  ORB_ON_DEVICE(device);
   orb_vocabulary* v = new orb_vocabulary;
   v->device = device; v->k = k; v->L = L; v->n_nodes = n_nodes; v->n_words = (int)word_weight.size();
   struct Up { DevBuf* b; const void* src; size_t bytes; } ups[] = {
@@ -168,7 +168,7 @@ int orb_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, cons
 
 void orb_vocabulary_destroy(orb_vocabulary* v) {
   if (!v) return;
-  cudaSetDevice(v->device);
+  OrbDeviceGuard guard(v->device);
   DevBuf* bufs[] = {&v->child_start, &v->child_id, &v->child_desc, &v->is_leaf, &v->word_of, &v->word_weight, &v->s_desc, &v->s_n, &v->s_word,
                     &v->s_node, &v->s_bw, &v->s_bv, &v->s_bc, &v->s_fn, &v->s_fs, &v->s_ff, &v->s_fc};
   for (DevBuf* b : bufs) b->release();
@@ -184,7 +184,7 @@ int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int
     return fail(ORB_E_BADARG, "null argument");
   if (cap <= 0 || cap > 16384 || frames <= 0 || levelsup < 0) return fail(ORB_E_BADARG, "bad size (0 < cap <= 16384, frames > 0, levelsup >= 0)");
   std::lock_guard<std::mutex> lk(v->mu);
-  CU(cudaSetDevice(v->device));
+  ORB_ON_DEVICE(v->device);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t F = (size_t)frames;
   const bool host = mem != ORB_MEM_DEVICE;
@@ -523,7 +523,8 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
 }
 
 double orb_measure_popc_peak(int device) {
-  if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return 0.0; }
+  OrbDeviceGuard guard(device);
+  if (guard.err != cudaSuccess) { cudaGetLastError(); return 0.0; }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0.0;
   return orb_popc_peak(prop.multiProcessorCount);

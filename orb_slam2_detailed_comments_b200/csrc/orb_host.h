@@ -60,6 +60,24 @@ int fail(int code, const char* fmt, ...);   // stores the message for orb_last_e
     if (e_ != cudaSuccess) return fail(ORB_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
   } while (0)
 
+// A handle lives on one device; an entry point works on that device and leaves the CALLER's current device as it found it
+// (a drop-in library must not move the host thread to another GPU behind the application's back).
+struct OrbDeviceGuard {
+  int prev = -1;
+  cudaError_t err;
+  explicit OrbDeviceGuard(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+    else if (err == cudaSuccess) prev = -1;   // already there: nothing to restore
+  }
+  ~OrbDeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  OrbDeviceGuard(const OrbDeviceGuard&) = delete;
+  OrbDeviceGuard& operator=(const OrbDeviceGuard&) = delete;
+};
+#define ORB_ON_DEVICE(dev)                                                                                            \
+  OrbDeviceGuard orb_dev_guard_(dev);                                                                                 \
+  if (orb_dev_guard_.err != cudaSuccess) return fail(ORB_E_CUDA, "cudaSetDevice(%d): %s", (int)(dev), cudaGetErrorString(orb_dev_guard_.err))
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;

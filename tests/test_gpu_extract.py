@@ -129,3 +129,25 @@ def test_errors():
         ex(np.zeros((900, 300), np.uint8))
     with pytest.raises(TypeError):
         ex.extract_batch(np.zeros((1, 100, 100), np.float32))
+
+
+def test_caller_device_preserved():
+    """A handle on another GPU must not move the calling thread's current CUDA device (extractor and vocabulary entry points)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import orb_slam2_detailed_comments_b200 as pkg
+    torch.cuda.set_device(0)
+    ex = pkg.ORBextractor(500, 1.2, 8, 20, 7, device=1)
+    img = synth.synth_frame(320, 240, 5)
+    k1, d1 = ex(img)
+    assert torch.cuda.current_device() == 0
+    t = torch.zeros(4, device="cuda")
+    assert t.device.index == 0
+    k0, d0 = pkg.ORBextractor(500, 1.2, 8, 20, 7, device=0)(img)
+    assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8)) and np.array_equal(d0, d1)
+    voc = synth.synth_vocabulary(10, 3, seed=11)
+    gv = pkg.ORBVocabulary(*voc, device=1)
+    assert torch.cuda.current_device() == 0
+    del gv, ex
+    assert torch.cuda.current_device() == 0
