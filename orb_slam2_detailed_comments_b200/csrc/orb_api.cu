@@ -33,6 +33,8 @@ struct orb_extractor {
   struct PassWs {
     cudaStream_t st = nullptr;
     cudaEvent_t ev_join = nullptr;
+    cudaStream_t st_side = nullptr;                       // high-priority side stream of the pass: quadtree (latency-bound) beside blur
+    cudaEvent_t ev_fast = nullptr, ev_side = nullptr;
     int frames = 0;          // frames of the last pass run here
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
     DevBuf st_sad;   // stereo: SAD of every kept match [chunk/2][cap]
@@ -42,6 +44,7 @@ struct orb_extractor {
                        &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
   } ws[ORB_MAX_WS];
   int nws = 2;             // compute streams / workspaces in use (ORB_B200_STREAMS, 1..ORB_MAX_WS)
+  int side = 2;            // ORB_B200_SIDE: 0 = off, 1 = quadtree, 2 (default) = quadtree + descriptors on the pass's high-priority side stream
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
   cudaEvent_t ev_fork = nullptr;
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
@@ -308,13 +311,26 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
   if (prof) cudaEventRecord(ev[1], st);
   orb_launch_fast(P.pyr.as<uint8_t>(), P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[2], st);
-  orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
-  if (prof) cudaEventRecord(ev[3], st);
+  // The quadtree is latency-bound (one CTA per frame x level, ~30 % issue-active) and only needs the FAST cells; the blur only needs
+  // the pyramid. Outside stage profiling the quadtree (side >= 1) and the descriptors (side >= 2) go to the pass's high-priority
+  // side stream: their CTAs are dispatched ahead of the queued blur / FAST CTAs of both pass streams and run beside them.
+  const int side = prof ? 0 : e->side;
+  cudaStream_t sq = side >= 1 ? P.st_side : st;
+  if (side >= 1) { cudaEventRecord(P.ev_fast, st); cudaStreamWaitEvent(sq, P.ev_fast, 0); }
+  if (side == 0) {
+    orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
+    if (prof) cudaEventRecord(ev[3], st);
+  }
   orb_launch_quadtree(P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), S, P.kept.as<uint32_t>(), kept_cnt,
-                      e->err.as<int>(), g, n, st, &e->launches);
+                      e->err.as<int>(), g, n, sq, &e->launches);
   if (prof) cudaEventRecord(ev[4], st);
+  if (side >= 1) orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
+  cudaStream_t sd = side >= 2 ? P.st_side : st;
+  if (side == 1) { cudaEventRecord(P.ev_side, sq); cudaStreamWaitEvent(st, P.ev_side, 0); }
+  if (side >= 2) { cudaEventRecord(P.ev_fast, st); cudaStreamWaitEvent(sd, P.ev_fast, 0); }      // blur done
   orb_launch_describe(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.kept.as<uint32_t>(), kept_cnt, kps, desc, cap,
-                      counts_dev, e->err.as<int>(), g, n, st, &e->launches);
+                      counts_dev, e->err.as<int>(), g, n, sd, &e->launches);
+  if (side >= 2) { cudaEventRecord(P.ev_side, sd); cudaStreamWaitEvent(st, P.ev_side, 0); }
   if (prof) cudaEventRecord(ev[5], st);
   P.frames = n;
   e->last_ws = w;
@@ -380,6 +396,16 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
     if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_join, cudaEventDisableTiming);
   }
   if (const char* s = getenv("ORB_B200_STREAMS")) e->nws = std::min(std::max(atoi(s), 1), ORB_MAX_WS);
+  if (const char* s = getenv("ORB_B200_SIDE")) e->side = atoi(s);
+  {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);   // hi = numerically lowest = greatest priority
+    for (int w = 0; w < ORB_MAX_WS; ++w) {
+      if (ce == cudaSuccess) ce = cudaStreamCreateWithPriority(&e->ws[w].st_side, cudaStreamNonBlocking, hi);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_fast, cudaEventDisableTiming);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_side, cudaEventDisableTiming);
+    }
+  }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
   e->ws[0].st = e->stream;
   if (ce != cudaSuccess) { orb_extractor_destroy(e); return fail(ORB_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce)); }
@@ -391,6 +417,11 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (!e) return;
   OrbDeviceGuard guard(e->device);
   if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+  for (int w = 0; w < ORB_MAX_WS; ++w) {
+    if (e->ws[w].st_side) { cudaStreamSynchronize(e->ws[w].st_side); cudaStreamDestroy(e->ws[w].st_side); }
+    if (e->ws[w].ev_fast) cudaEventDestroy(e->ws[w].ev_fast);
+    if (e->ws[w].ev_side) cudaEventDestroy(e->ws[w].ev_side);
+  }
   for (int w = 1; w < ORB_MAX_WS; ++w) {
     if (e->ws[w].st) { cudaStreamSynchronize(e->ws[w].st); cudaStreamDestroy(e->ws[w].st); }
     if (e->ws[w].ev_join) cudaEventDestroy(e->ws[w].ev_join);
