@@ -152,6 +152,47 @@ int ORBmatcher::SearchByBoW(const cv::Mat& kfDescriptors, const std::vector<cv::
   return nm;
 }
 
+int ORBmatcher::SearchForTriangulation(const cv::Mat& descriptors1, const std::vector<cv::KeyPoint>& keys1Un, const std::vector<unsigned char>& hasPoint1,
+                                       const std::vector<float>& uRight1, const FeatureVector& featVec1, const cv::Mat& descriptors2,
+                                       const std::vector<cv::KeyPoint>& keys2Un, const std::vector<unsigned char>& hasPoint2,
+                                       const std::vector<float>& uRight2, const FeatureVector& featVec2, const float F12[9], float ex, float ey,
+                                       const std::vector<float>& levelSigma2, const std::vector<float>& scaleFactors,
+                                       std::vector<std::pair<size_t, size_t>>& vMatchedPairs, bool bOnlyStereo) const {
+  const int n1 = (int)keys1Un.size(), n2 = (int)keys2Un.size();
+  vMatchedPairs.clear();
+  if (n1 == 0 || n2 == 0) return 0;
+  if (descriptors1.rows != n1 || descriptors2.rows != n2 || (int)hasPoint1.size() != n1 || (int)hasPoint2.size() != n2 || (int)uRight1.size() != n1 ||
+      (int)uRight2.size() != n2 || levelSigma2.size() > 16 || scaleFactors.size() != levelSigma2.size())
+    throw std::runtime_error("SearchForTriangulation: array sizes differ");
+  std::vector<uint8_t> t1, t2;
+  const uint8_t* d1 = rows32(descriptors1, t1);
+  const uint8_t* d2 = rows32(descriptors2, t2);
+  std::vector<int32_t> an, as, af, bn, bs, bf;
+  int32_t ac = 0, bc = 0;
+  to_csr(featVec1, n1, an, as, af, ac);
+  to_csr(featVec2, n2, bn, bs, bf, bc);
+  std::vector<unsigned char> free1(n1), blocked2(n2);
+  for (int i = 0; i < n1; ++i) free1[i] = !hasPoint1[i] && (!bOnlyStereo || uRight1[i] >= 0);        // :925-934
+  for (int i = 0; i < n2; ++i) blocked2[i] = hasPoint2[i] || (bOnlyStereo && !(uRight2[i] >= 0));    // :957-966
+  orb_epipolar epi;
+  std::memset(&epi, 0, sizeof(epi));
+  std::memcpy(epi.f12, F12, sizeof(epi.f12));
+  epi.ex = ex; epi.ey = ey;
+  std::copy(levelSigma2.begin(), levelSigma2.end(), epi.level_sigma2);
+  std::copy(scaleFactors.begin(), scaleFactors.end(), epi.scale_factor);
+  std::vector<int32_t> m12(n1, -1);
+  int32_t nm = 0;
+  check(orb_search_for_triangulation(ORB_MEM_HOST, d1, reinterpret_cast<const orb_keypoint*>(keys1Un.data()), free1.data(), uRight1.data(), an.data(),
+                                     as.data(), af.data(), &ac, n1, d2, reinterpret_cast<const orb_keypoint*>(keys2Un.data()), blocked2.data(),
+                                     uRight2.data(), bn.data(), bs.data(), bf.data(), &bc, n2, 1, &epi, TH_LOW, mbCheckOrientation ? 1 : 0, m12.data(),
+                                     &nm, nullptr),
+        "orb_search_for_triangulation");
+  vMatchedPairs.reserve(nm);
+  for (int i = 0; i < n1; ++i)                                                                       // :1078-1086
+    if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[i]));
+  return nm;
+}
+
 int ORBmatcher::SearchForInitialization(const std::vector<cv::KeyPoint>& keys1Un, const cv::Mat& descriptors1, const TargetFrame& F2,
                                         std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize) const {
   const int m = (int)keys1Un.size(), n = (int)F2.mvKeysUn->size();

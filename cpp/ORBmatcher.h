@@ -9,6 +9,7 @@
 
 #include <cstdint>
 #include <map>
+#include <utility>
 #include <vector>
 
 #ifdef ORB_B200_USE_OPENCV
@@ -81,6 +82,15 @@ class ORBmatcher {
   int SearchByBoW(const cv::Mat& kfDescriptors, const std::vector<cv::KeyPoint>& kfKeysUn, const std::vector<unsigned char>& kfHasPoint,
                   const FeatureVector& kfFeatVec, const cv::Mat& fDescriptors, const std::vector<cv::KeyPoint>& fKeys,
                   const FeatureVector& fFeatVec, std::vector<int>& assigned) const;
+
+  // SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:879-1090) on flat inputs: per keyframe
+  // mDescriptors / mvKeysUn / "GetMapPoint(idx) != NULL" flags / mvuRight / mFeatVec; F12 (3x3 CV_32F); the epipole (ex, ey) of camera 1
+  // in image 2 computed by the caller as in :885-897; pKF2's mvLevelSigma2 and mvScaleFactors. Returns nmatches. GPU only.
+  int SearchForTriangulation(const cv::Mat& descriptors1, const std::vector<cv::KeyPoint>& keys1Un, const std::vector<unsigned char>& hasPoint1,
+                             const std::vector<float>& uRight1, const FeatureVector& featVec1, const cv::Mat& descriptors2,
+                             const std::vector<cv::KeyPoint>& keys2Un, const std::vector<unsigned char>& hasPoint2, const std::vector<float>& uRight2,
+                             const FeatureVector& featVec2, const float F12[9], float ex, float ey, const std::vector<float>& levelSigma2,
+                             const std::vector<float>& scaleFactors, std::vector<std::pair<size_t, size_t>>& vMatchedPairs, bool bOnlyStereo) const;
 
   // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:424-517) for many map points in one call: rows
   // [offsets[p], offsets[p+1]) of `observations` (total x 32 CV_8U) are point p's descriptors in the reference's map order;

@@ -293,6 +293,34 @@ int main(int argc, char** argv) {
         REQUIRE(nmb == onm && std::memcmp(asg.data(), want.data(), want.size() * 4) == 0, "SearchByBoW: %d matches vs oracle %d", nmb, onm);
         REQUIRE(nmb > 30, "SearchByBoW: too few matches (%d)", nmb);
         std::printf("SearchByBoW: %d matches, assignment bit-exact vs oracle\n", nmb);
+        // SearchForTriangulation between the same two feature sets: sideways-translation F12 (x1^T F12 x2 = y2 - y1), an epipole inside
+        // the image, a loose chi-square table so that the rows of the two synthetic images need not agree
+        {
+          const float F12[9] = {0.f, 0.f, 0.f, 0.f, 0.f, -1.f, 0.f, 1.f, 0.f};
+          std::vector<float> sig(8), scl(8), ur1(bk[0].size(), -1.f), ur2(bk[1].size(), -1.f);
+          for (int l = 0; l < 8; ++l) { scl[l] = l ? scl[l - 1] * 1.2f : 1.f; sig[l] = scl[l] * scl[l] * 2.0e4f; }
+          for (size_t q = 0; q < ur1.size(); q += 4) ur1[q] = bk[0][q].pt.x - 10.f;
+          for (size_t q = 1; q < ur2.size(); q += 5) ur2[q] = bk[1][q].pt.x - 10.f;
+          std::vector<unsigned char> has2(bk[1].size(), 0);
+          for (size_t q = 3; q < has2.size(); q += 7) has2[q] = 1;
+          std::vector<unsigned char> hp1(has.size());
+          for (size_t q = 0; q < has.size(); ++q) hp1[q] = !has[q];
+          std::vector<std::pair<size_t, size_t>> pairs;
+          const int nt = bm.SearchForTriangulation(bd[0], bk[0], hp1, ur1, fv, bd[1], bk[1], has2, ur2, fv2, F12, 300.5f, 200.25f, sig, scl, pairs, false);
+          std::vector<int32_t> want12(bk[0].size());
+          const int ont = orb_oracle_search_for_triangulation(
+              bd[0].ptr<unsigned char>(0), reinterpret_cast<const orb_oracle_kp*>(bk[0].data()), hp1.data(), ur1.data(), (int)bk[0].size(), kn.data(),
+              ks.data(), ke.data(), kc, bd[1].ptr<unsigned char>(0), reinterpret_cast<const orb_oracle_kp*>(bk[1].data()), has2.data(), ur2.data(),
+              (int)bk[1].size(), f2n.data(), f2s.data(), f2e.data(), fc2, F12, 300.5f, 200.25f, sig.data(), scl.data(), 0, ORB_SLAM2::ORBmatcher::TH_LOW, 1,
+              want12.data());
+          size_t np = 0;
+          bool same = nt == ont;
+          for (size_t q = 0; q < want12.size() && same; ++q)
+            if (want12[q] >= 0) { same = np < pairs.size() && pairs[np].first == q && pairs[np].second == (size_t)want12[q]; ++np; }
+          REQUIRE(same && np == pairs.size(), "SearchForTriangulation: %d matches vs oracle %d", nt, ont);
+          REQUIRE(nt > 10, "SearchForTriangulation: too few matches (%d)", nt);
+          std::printf("SearchForTriangulation: %d matched pairs bit-exact vs oracle\n", nt);
+        }
       }
       orb_oracle_vocabulary_destroy(ov);
       std::printf("ORBVocabulary::transform: %d words, %d nodes, doubles bit-exact vs oracle\n", bc, fc);

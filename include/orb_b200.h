@@ -18,6 +18,7 @@
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
  *   orb_search_for_initialization <- ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   src/ORBmatcher.cc:570-712
  *   orb_search_by_bow         <- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)                  src/ORBmatcher.cc:248-410
+ *   orb_search_for_triangulation <- ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) src/ORBmatcher.cc:879-1090
  *   orb_vocabulary_*, orb_bow_transform <- Frame::ComputeBoW = DBoW2 TemplatedVocabulary::transform   src/Frame.cc:750-765,
  *                                Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280
  *   orb_undistort_keypoints, orb_image_bounds <- Frame::UndistortKeyPoints / ComputeImageBounds (cv::undistortPoints)
@@ -247,6 +248,33 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
                       const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,
                       const int32_t* f_fv_feature, const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio,
                       int check_orientation, int32_t* assigned, int32_t* kf_match, int32_t* nmatches, void* stream);
+
+/* ---- ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:879-1090) ------------
+ * LocalMapping's matcher between two keyframes: features of KF1 without a map point against the features of KF2 in the same
+ * vocabulary node that have no map point and are not matched yet; a candidate needs DescriptorDistance <= th_dist (TH_LOW = 50)
+ * and <= the running best ("dist > bestDist -> continue": a later candidate of equal distance replaces the earlier one), must lie
+ * away from the epipole when both keypoints are monocular (:1005-1013) and satisfy CheckDistEpipolarLine (:206-245); the winner
+ * claims its KF2 keypoint (vbMatched2); then the rotation histogram / ComputeThreeMaxima filter. Same FeatureVector CSR layout as
+ * orb_search_by_bow, for `pairs` independent keyframe pairs.
+ *   kf1_free    [pairs][qcap] u8: 1 = feature takes part (!pKF1->GetMapPoint(idx1), and bStereo1 if bOnlyStereo)
+ *   kf2_blocked [pairs][cap]  u8: 1 = candidate excluded (pKF2->GetMapPoint(idx2), or !bStereo2 if bOnlyStereo)
+ *   kf?_uright  mvuRight of both keyframes (< 0 = monocular keypoint)
+ *   epi         [pairs]: F12 row-major, the epipole (ex, ey) of camera 1 in image 2 (:885-897), pKF2->mvLevelSigma2, mvScaleFactors
+ *   matches12   [pairs][qcap]: vMatches12 (index in KF2 or -1); vMatchedPairs = its non-negative entries in index order.
+ * Float arithmetic is float32 without contraction; the chi-square compare is done in double as in the reference. */
+typedef struct orb_epipolar {
+  float f12[9];
+  float ex, ey;
+  float level_sigma2[16];
+  float scale_factor[16];
+  float reserved;
+} orb_epipolar;
+int orb_search_for_triangulation(int mem, const uint8_t* kf1_desc, const orb_keypoint* kf1_kps_un, const uint8_t* kf1_free, const float* kf1_uright,
+                                 const int32_t* kf1_fv_node, const int32_t* kf1_fv_start, const int32_t* kf1_fv_feature, const int32_t* kf1_fv_count,
+                                 int qcap, const uint8_t* kf2_desc, const orb_keypoint* kf2_kps_un, const uint8_t* kf2_blocked, const float* kf2_uright,
+                                 const int32_t* kf2_fv_node, const int32_t* kf2_fv_start, const int32_t* kf2_fv_feature, const int32_t* kf2_fv_count,
+                                 int cap, int pairs, const orb_epipolar* epi, int th_dist, int check_orientation, int32_t* matches12,
+                                 int32_t* nmatches, void* stream);
 
 /* ---- Frame::ComputeBoW (src/Frame.cc:750-765) --------------------------------------------------------
  * = DBoW2 TemplatedVocabulary<FORB::TDescriptor, FORB>::transform(features, BowVector&, FeatureVector&, levelsup)

@@ -333,6 +333,30 @@ def search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv, f_desc, f_kps, f_fv, th_d
     return assigned[:n_f], nm, kf_match[:n_kf]
 
 
+def search_for_triangulation(desc1, kps1_un, has_mp1, uright1, fv1, desc2, kps2_un, has_mp2, uright2, fv2, f12, ex, ey, level_sigma2, scale_factor,
+                             only_stereo=False, th_low=50, check_orientation=True):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:879-1090), one keyframe pair; fv? = (node, start, feature, count) CSR.
+    Returns (vMatches12 [n1], nmatches)."""
+    L = lib()
+    vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+    L.orb_oracle_search_for_triangulation.argtypes = ([vp] * 4 + [ci] + [vp] * 3 + [ci]) * 2 + [vp, cf, cf, vp, vp, ci, ci, ci, vp]
+    c = lambda a, dt: np.ascontiguousarray(a, dt)
+    d1, d2 = c(desc1, np.uint8), c(desc2, np.uint8)
+    k1, k2 = np.ascontiguousarray(kps1_un), np.ascontiguousarray(kps2_un)
+    h1, h2, u1, u2 = c(has_mp1, np.uint8), c(has_mp2, np.uint8), c(uright1, np.float32), c(uright2, np.float32)
+    a1 = [c(fv1[0], np.int32), c(fv1[1], np.int32), c(fv1[2], np.int32)]
+    a2 = [c(fv2[0], np.int32), c(fv2[1], np.int32), c(fv2[2], np.int32)]
+    F = c(np.asarray(f12).reshape(9), np.float32)
+    ls, sf = c(level_sigma2, np.float32), c(scale_factor, np.float32)
+    n1, n2 = len(k1), len(k2)
+    m12 = np.full(max(n1, 1), -1, np.int32)
+    nm = L.orb_oracle_search_for_triangulation(_p(d1), _p(k1), _p(h1), _p(u1), n1, _p(a1[0]), _p(a1[1]), _p(a1[2]), int(fv1[3]),
+                                               _p(d2), _p(k2), _p(h2), _p(u2), n2, _p(a2[0]), _p(a2[1]), _p(a2[2]), int(fv2[3]),
+                                               _p(F), float(ex), float(ey), _p(ls), _p(sf), int(only_stereo), int(th_low), int(check_orientation),
+                                               _p(m12))
+    return m12[:n1], nm
+
+
 def search_for_initialization(kps_un, desc, queries, qdesc, bounds, th_dist=50, nn_ratio=0.9, check_orientation=True):
     """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:570-712), one frame pair. Returns (matches12 [m], matches21 [n], nmatches)."""
     L = lib()

@@ -797,6 +797,107 @@ int orb_oracle_search_for_initialization(const orb_oracle_kp* kps, const uint8_t
   return nmatches;
 }
 
+// ORBmatcher::CheckDistEpipolarLine (src/ORBmatcher.cc:206-245): float32, one rounding per operation (no contraction)
+static bool check_dist_epipolar_line(const orb_oracle_kp& kp1, const orb_oracle_kp& kp2, const float* F12, const float* level_sigma2) {
+  const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+  const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+  const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+  const float num = a * kp2.x + b * kp2.y + c;
+  const float den = a * a + b * b;
+  if (den == 0) return false;
+  const float dsqr = num * num / den;
+  return dsqr < 3.84 * level_sigma2[kp2.octave];   // double compare, as written in the reference
+}
+
+int orb_oracle_search_for_triangulation(const uint8_t* desc1, const orb_oracle_kp* kps1_un, const uint8_t* kf1_has_mp, const float* uright1, int n1,
+                                        const int32_t* node1, const int32_t* start1, const int32_t* feature1, int count1,
+                                        const uint8_t* desc2, const orb_oracle_kp* kps2_un, const uint8_t* kf2_has_mp, const float* uright2, int n2,
+                                        const int32_t* node2, const int32_t* start2, const int32_t* feature2, int count2,
+                                        const float* f12, float ex, float ey, const float* level_sigma2, const float* scale_factor,
+                                        int only_stereo, int th_low, int check_orientation, int32_t* matches12) {
+  typedef std::map<unsigned, std::vector<unsigned>> FeatureVector;
+  FeatureVector vFeatVec1, vFeatVec2;
+  for (int j = 0; j < count1; ++j) vFeatVec1[node1[j]].assign(feature1 + start1[j], feature1 + start1[j + 1]);
+  for (int j = 0; j < count2; ++j) vFeatVec2[node2[j]].assign(feature2 + start2[j], feature2 + start2[j + 1]);
+  int nmatches = 0;
+  std::vector<bool> vbMatched2(n2, false);          // :899
+  std::vector<int> vMatches12(n1, -1);              // :900
+  std::vector<int> rotHist[HISTO_LENGTH];
+  const float factor = HISTO_LENGTH / 360.0f;       // :906
+  FeatureVector::const_iterator f1it = vFeatVec1.begin(), f2it = vFeatVec2.begin(), f1end = vFeatVec1.end(), f2end = vFeatVec2.end();
+  while (f1it != f1end && f2it != f2end) {
+    if (f1it->first == f2it->first) {
+      for (size_t i1 = 0, iend1 = f1it->second.size(); i1 < iend1; i1++) {
+        const size_t idx1 = f1it->second[i1];
+        if (kf1_has_mp[idx1]) continue;                                  // :925-929
+        const bool bStereo1 = uright1[idx1] >= 0;
+        if (only_stereo && !bStereo1) continue;
+        const orb_oracle_kp& kp1 = kps1_un[idx1];
+        const uint8_t* d1 = desc1 + idx1 * 32;
+        int bestDist = th_low;                                           // :945
+        int bestIdx2 = -1;
+        for (size_t i2 = 0, iend2 = f2it->second.size(); i2 < iend2; i2++) {
+          const size_t idx2 = f2it->second[i2];
+          if (vbMatched2[idx2] || kf2_has_mp[idx2]) continue;            // :957
+          const bool bStereo2 = uright2[idx2] >= 0;
+          if (only_stereo && !bStereo2) continue;
+          const int dist = orb_oracle_descriptor_distance(d1, desc2 + idx2 * 32);
+          if (dist > th_low || dist > bestDist) continue;                // :975
+          const orb_oracle_kp& kp2 = kps2_un[idx2];
+          if (!bStereo1 && !bStereo2) {                                  // :1005-1013
+            const float distex = ex - kp2.x;
+            const float distey = ey - kp2.y;
+            if (distex * distex + distey * distey < 100 * scale_factor[kp2.octave]) continue;
+          }
+          if (check_dist_epipolar_line(kp1, kp2, f12, level_sigma2)) {
+            bestIdx2 = (int)idx2;
+            bestDist = dist;
+          }
+        }
+        if (bestIdx2 >= 0) {
+          const orb_oracle_kp& kp2 = kps2_un[bestIdx2];
+          vMatches12[idx1] = bestIdx2;
+          vbMatched2[bestIdx2] = true;
+          nmatches++;
+          if (check_orientation) {
+            float rot = kp1.angle - kp2.angle;
+            if (rot < 0.0) rot += 360.0f;
+            int bin = (int)std::round(rot * factor);
+            if (bin == HISTO_LENGTH) bin = 0;
+            if (bin >= 0 && bin < HISTO_LENGTH) rotHist[bin].push_back((int)idx1);
+          }
+        }
+      }
+      f1it++; f2it++;
+    } else if (f1it->first < f2it->first) {
+      f1it = vFeatVec1.lower_bound(f2it->first);
+    } else {
+      f2it = vFeatVec2.lower_bound(f1it->first);
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;   // ComputeThreeMaxima (:2026-2068)
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int sz = (int)rotHist[i].size();
+      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+      else if (sz > max3) { max3 = sz; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i]) {
+        vbMatched2[vMatches12[idx1]] = false;
+        vMatches12[idx1] = -1;
+        nmatches--;
+      }
+    }
+  }
+  for (int i = 0; i < n1; ++i) matches12[i] = vMatches12[i];
+  return nmatches;
+}
+
 int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_node,
                              const int32_t* kf_start, const int32_t* kf_feature, int kf_count, const uint8_t* f_desc,
                              const orb_oracle_kp* f_kps, int n_f, const int32_t* f_node, const int32_t* f_start, const int32_t* f_feature,

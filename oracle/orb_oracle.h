@@ -130,6 +130,16 @@ int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps
                              const uint8_t* f_blocked /* optional: KeyFrame-KeyFrame form, :771-776 */, int32_t* kf_match /* optional [n_kf] */,
                              int n_kf);
 
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:879-1090) + CheckDistEpipolarLine (:206-245), one keyframe pair.
+ * kf1_has_mp / kf2_has_mp: pKF->GetMapPoint(idx) != NULL; uright: mvuRight (< 0 = monocular); f12: F12 row-major; (ex, ey): the
+ * epipole computed by the caller as in :885-897; level_sigma2 / scale_factor: pKF2's tables. matches12 [n1] = vMatches12. Returns nmatches. */
+int orb_oracle_search_for_triangulation(const uint8_t* desc1, const orb_oracle_kp* kps1_un, const uint8_t* kf1_has_mp, const float* uright1, int n1,
+                                        const int32_t* node1, const int32_t* start1, const int32_t* feature1, int count1,
+                                        const uint8_t* desc2, const orb_oracle_kp* kps2_un, const uint8_t* kf2_has_mp, const float* uright2, int n2,
+                                        const int32_t* node2, const int32_t* start2, const int32_t* feature2, int count2,
+                                        const float* f12, float ex, float ey, const float* level_sigma2, const float* scale_factor,
+                                        int only_stereo, int th_low, int check_orientation, int32_t* matches12);
+
 /* Frame::UndistortKeyPoints (src/Frame.cc:770-806): cv::undistortPoints(pts, pts, K, dist, Mat(), K), OpenCV >= 4 default criteria
  * (5 iterations), on n points xy [n][2] (float, in place). k: n_dist (4, 5 or 8) float coefficients. dist[0] == 0 leaves xy unchanged. */
 void orb_oracle_undistort_points(float fx, float fy, float cx, float cy, const float* dist, int n_dist, float* xy, int n);

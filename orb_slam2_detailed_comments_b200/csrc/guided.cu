@@ -34,6 +34,15 @@ struct GuidedQuery {   // == orb_proj_query
 };
 static_assert(sizeof(GuidedQuery) == 32, "orb_proj_query layout");
 
+struct OrbEpi {   // == orb_epipolar: SearchForTriangulation's per-pair geometry
+  float f12[9];             // F12 row-major
+  float ex, ey;             // epipole of camera 1 in image 2 (src/ORBmatcher.cc:885-897)
+  float level_sigma2[16];   // pKF2->mvLevelSigma2
+  float scale_factor[16];   // pKF2->mvScaleFactors
+  float reserved;
+};
+static_assert(sizeof(OrbEpi) == 176, "orb_epipolar layout");
+
 struct GuidedFrame {
   const uint4* items;        // sorted keypoints: x bits, y bits, octave, index
   const int* cell_start;     // [GRID_CELLS + 1]
@@ -44,6 +53,9 @@ struct GuidedFrame {
   // SearchByBoW: FeatureVector of the target frame as CSR (orb_bow_transform layout)
   const int* fv_start;
   const int* fv_feature;
+  // SearchForTriangulation: undistorted keypoints of the target keyframe and the pair's epipolar geometry
+  const OrbKeypoint* kps2;
+  const OrbEpi* epi;
 };
 
 // A candidate is one 64-bit word {hi, lo}. hi = dist << 18 | sorted position: "strict <, first in scan order wins" is a plain
@@ -104,10 +116,23 @@ __device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQu
 // SearchByBoW candidates (src/ORBmatcher.cc:296-322): the target frame's features in the query's vocabulary node, i.e. one
 // contiguous range of the FeatureVector CSR (slot = q.reserved, resolved by orb_bow_queries_kernel); ascending position in
 // the CSR is the reference's loop order. Same emit() contract as guided_scan.
-template <typename Emit>
+//
+// TRI = SearchForTriangulation (src/ORBmatcher.cc:879-1090): the same node ranges, but a candidate must also lie away from the
+// epipole (both keypoints monocular, :1005-1013) and within the chi-square bound of the epipolar line (CheckDistEpipolarLine,
+// :206-245), and "dist > bestDist -> continue" lets a LATER candidate of equal distance replace the earlier one: the position
+// part of the key is reversed, so the unsigned min is "smallest distance, last in scan order". Both checks are pure functions
+// of the pair, so testing them for every candidate instead of only for those at or below the running best changes nothing.
+template <bool TRI, typename Emit>
 __device__ __forceinline__ void bow_scan(const GuidedFrame& F, const GuidedQuery& q, const uint4 qd0, const uint4 qd1, int lane, Emit emit) {
   if (q.reserved < 0) return;
   const int e0 = F.fv_start[q.reserved], e1 = F.fv_start[q.reserved + 1];
+  float la = 0.f, lb = 0.f, lc = 0.f;
+  if (TRI) {   // epipolar line of kp1 in image 2 (:208-214), float32 without contraction
+    const float* f = F.epi->f12;
+    la = __fadd_rn(__fadd_rn(__fmul_rn(q.u, f[0]), __fmul_rn(q.v, f[3])), f[6]);
+    lb = __fadd_rn(__fadd_rn(__fmul_rn(q.u, f[1]), __fmul_rn(q.v, f[4])), f[7]);
+    lc = __fadd_rn(__fadd_rn(__fmul_rn(q.u, f[2]), __fmul_rn(q.v, f[5])), f[8]);
+  }
   for (int base = e0; base < e1; base += 32) {
     const int e = base + lane;
     unsigned hi = GUIDED_NONE, lo = 0;
@@ -117,8 +142,27 @@ __device__ __forceinline__ void bow_scan(const GuidedFrame& F, const GuidedQuery
       const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
       const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
                        __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
-      if (!blocked) {
-        hi = ((unsigned)dist << 18) | (unsigned)e;
+      bool ok = !blocked;
+      if (TRI && ok) {
+        const OrbKeypoint k2 = F.kps2[idx];
+        const int oct = min(max(k2.octave, 0), 15);
+        const bool stereo1 = q.ur >= 0.f, stereo2 = F.uright ? F.uright[idx] >= 0.f : false;
+        if (!stereo1 && !stereo2) {   // :1005-1013
+          const float dex = __fsub_rn(F.epi->ex, k2.x), dey = __fsub_rn(F.epi->ey, k2.y);
+          if (__fadd_rn(__fmul_rn(dex, dex), __fmul_rn(dey, dey)) < __fmul_rn(100.f, F.epi->scale_factor[oct])) ok = false;
+        }
+        if (ok) {                     // CheckDistEpipolarLine (:215-245)
+          const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, k2.x), __fmul_rn(lb, k2.y)), lc);
+          const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+          if (den == 0.f) ok = false;
+          else {
+            const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+            ok = (double)dsqr < __dmul_rn(3.84, (double)F.epi->level_sigma2[oct]);
+          }
+        }
+      }
+      if (ok) {
+        hi = ((unsigned)dist << 18) | (unsigned)(TRI ? 0x3ffff - e : e);
         lo = (unsigned)idx;
       }
     }
@@ -193,18 +237,22 @@ __global__ void __launch_bounds__(256) orb_guided_grid_kernel(const OrbKeypoint*
 }
 
 // ---- 2. candidate list per query -------------------------------------------------------------------------------------------
-template <bool BOW>
+template <int MODE>   // 0 = grid window (SearchByProjection), 1 = vocabulary node (SearchByBoW), 2 = node + epipolar checks (SearchForTriangulation)
 __global__ void __launch_bounds__(GUIDED_WARPS * 32)
 orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const int* __restrict__ fv_start,
-                             const int* __restrict__ fv_feature, const uint8_t* __restrict__ desc,
+                             const int* __restrict__ fv_feature, const OrbKeypoint* __restrict__ kps2, const OrbEpi* __restrict__ epi,
+                             const uint8_t* __restrict__ desc,
                              const float* __restrict__ uright, const uint8_t* __restrict__ claimed, int cap,
                              const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc, const int* __restrict__ n_queries,
                              int qcap, float min_x, float min_y, float inv_w, float inv_h, uint2* __restrict__ lists,
                              int* __restrict__ list_cnt) {
+  constexpr bool BOW = MODE >= 1;
   const int f = blockIdx.y, lane = threadIdx.x & 31;
   const int iq = blockIdx.x * GUIDED_WARPS + (threadIdx.x >> 5);
   if (iq >= min(n_queries[f], qcap)) return;
   GuidedFrame F;
+  F.kps2 = MODE == 2 ? kps2 + (size_t)f * cap : nullptr;
+  F.epi = MODE == 2 ? epi + f : nullptr;
   F.items = items + (size_t)f * cap;
   F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
   F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
@@ -225,7 +273,7 @@ orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restr
       if (hi != GUIDED_NONE && pos < GUIDED_LIST) out[pos] = make_uint2(lo, hi);
       n += __popc(m);
     };
-    if (BOW) bow_scan(F, q, qd[0], qd[1], lane, emit);
+    if (BOW) bow_scan<MODE == 2>(F, q, qd[0], qd[1], lane, emit);
     else guided_scan(F, q, qd[0], qd[1], lane, emit);
   }
   if (lane >= n && lane < GUIDED_LIST) out[lane] = make_uint2(0u, GUIDED_NONE);   // pad: the resolving warp reads all 32 slots
@@ -237,10 +285,10 @@ __device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
 
-template <bool BOW>
+template <int MODE>
 __global__ void __launch_bounds__(32)
 orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const int* __restrict__ fv_start,
-                          const int* __restrict__ fv_feature, const OrbKeypoint* __restrict__ kps,
+                          const int* __restrict__ fv_feature, const OrbEpi* __restrict__ epi, const OrbKeypoint* __restrict__ kps,
                           const uint8_t* __restrict__ desc, const float* __restrict__ uright, const uint8_t* __restrict__ claimed,
                           int cap, const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc,
                           const int* __restrict__ n_queries, int qcap, float min_x, float min_y, float inv_w, float inv_h,
@@ -250,9 +298,12 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
   extern __shared__ unsigned s_dyn[];   // claim bits, (cap + 31) / 32 words
   __shared__ uint2 s_list[2][32][GUIDED_LIST];   // candidate lists of two groups of 32 queries (16 KB)
   __shared__ int s_hist[HISTO_LENGTH];
+  constexpr bool BOW = MODE >= 1;
   const int f = blockIdx.x, lane = threadIdx.x;
   const int m = min(n_queries[f], qcap);
   GuidedFrame F;
+  F.kps2 = MODE == 2 ? kps + (size_t)f * cap : nullptr;
+  F.epi = MODE == 2 ? epi + f : nullptr;
   F.items = items + (size_t)f * cap;
   F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
   F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
@@ -323,7 +374,7 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
             else if (k < k2) k2 = k;
           }
         };
-        if (BOW) bow_scan(F, q, qd[0], qd[1], lane, emit);
+        if (BOW) bow_scan<MODE == 2>(F, q, qd[0], qd[1], lane, emit);
         else guided_scan(F, q, qd[0], qd[1], lane, emit);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -412,10 +463,10 @@ void orb_launch_guided(const OrbKeypoint* kps, const uint8_t* desc, const float*
   const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
   const GuidedQuery* q = static_cast<const GuidedQuery*>(queries);
   orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
-  orb_guided_candidates_kernel<false><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
-      items, cell_start, nullptr, nullptr, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
+  orb_guided_candidates_kernel<0><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, nullptr, nullptr, nullptr, nullptr, desc, uright, claimed, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
   const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
-  orb_guided_resolve_kernel<false><<<frames, 32, smem, st>>>(items, cell_start, nullptr, nullptr, kps, desc, uright, claimed, cap, q, qdesc,
+  orb_guided_resolve_kernel<0><<<frames, 32, smem, st>>>(items, cell_start, nullptr, nullptr, nullptr, kps, desc, uright, claimed, cap, q, qdesc,
                                                              n_queries, qcap, min_x, min_y, inv_w, inv_h, th_dist, nn_ratio, 0,
                                                              check_orientation, lists, list_cnt, assigned, query_match, nmatches);
   *launches += 3;
@@ -439,6 +490,7 @@ orb_guided_resolve_init_kernel(const uint4* __restrict__ items, const int* __res
   const int f = blockIdx.x, lane = threadIdx.x;
   const int m = min(n_queries[f], qcap);
   GuidedFrame F;
+  F.kps2 = nullptr; F.epi = nullptr;
   F.items = items + (size_t)f * cap;
   F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
   F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
@@ -554,8 +606,8 @@ void orb_launch_search_init(const OrbKeypoint* kps, const uint8_t* desc, const i
   const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
   const GuidedQuery* q = static_cast<const GuidedQuery*>(queries);
   orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
-  orb_guided_candidates_kernel<false><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
-      items, cell_start, nullptr, nullptr, desc, nullptr, nullptr, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
+  orb_guided_candidates_kernel<0><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, nullptr, nullptr, nullptr, nullptr, desc, nullptr, nullptr, cap, q, qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, lists, list_cnt);
   const size_t smem = (size_t)cap * (sizeof(int) + sizeof(unsigned short)) + 16;
   static std::atomic<bool> configured[64];
   int dev = 0;
@@ -577,7 +629,8 @@ void orb_launch_search_init(const OrbKeypoint* kps, const uint8_t* desc, const i
 // CLAIMS flag (every match blocks its keypoint, :300-301). Features outside the FeatureVector, or without a valid map point
 // (:283-289), stay SKIP. Queries are resolved in feature-index order, which is the reference's order inside every node.
 __global__ void __launch_bounds__(256)
-orb_bow_queries_kernel(const OrbKeypoint* __restrict__ kf_kps, const uint8_t* __restrict__ kf_valid, const int* __restrict__ kf_node,
+orb_bow_queries_kernel(const OrbKeypoint* __restrict__ kf_kps, const uint8_t* __restrict__ kf_valid, const float* __restrict__ kf_uright,
+                       const int* __restrict__ kf_node,
                        const int* __restrict__ kf_start, const int* __restrict__ kf_feature, const int* __restrict__ kf_count, int qcap,
                        const int* __restrict__ f_node, const int* __restrict__ f_count, int cap, GuidedQuery* __restrict__ q,
                        int* __restrict__ n_queries) {
@@ -607,6 +660,8 @@ orb_bow_queries_kernel(const OrbKeypoint* __restrict__ kf_kps, const uint8_t* __
     const int i = kf_feature[e];
     if (i >= 0 && i < qcap && kf_valid[i] && slot >= 0) {
       q[i].angle = kf_kps[i].angle;
+      q[i].u = kf_kps[i].x; q[i].v = kf_kps[i].y;                               // SearchForTriangulation: kp1 and its stereo flag
+      q[i].ur = kf_uright ? kf_uright[(size_t)f * qcap + i] : -1.f;
       q[i].reserved = slot;
       q[i].flags = 2;   // CLAIMS
     }
@@ -619,14 +674,26 @@ void orb_launch_search_by_bow(const uint8_t* kf_desc, const OrbKeypoint* kf_kps,
                               const uint8_t* f_blocked, const int* f_node, const int* f_start, const int* f_feature, const int* f_count, int cap,
                               int frames, int th_dist,
                               float nn_ratio, int check_orientation, void* queries, int* n_queries, uint2* lists, int* list_cnt, int* assigned,
-                              int* query_match, int* nmatches, cudaStream_t st, long long* launches) {
+                              int* query_match, int* nmatches, cudaStream_t st, long long* launches, const void* epi, const float* kf_uright,
+                              const float* f_uright) {
   GuidedQuery* q = static_cast<GuidedQuery*>(queries);
-  orb_bow_queries_kernel<<<frames, 256, 0, st>>>(kf_kps, kf_valid, kf_node, kf_start, kf_feature, kf_count, qcap, f_node, f_count, cap, q, n_queries);
-  orb_guided_candidates_kernel<true><<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
-      nullptr, nullptr, f_start, f_feature, f_desc, nullptr, f_blocked, cap, q, kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, lists, list_cnt);
+  const OrbEpi* ep = static_cast<const OrbEpi*>(epi);   // non-null = SearchForTriangulation
+  orb_bow_queries_kernel<<<frames, 256, 0, st>>>(kf_kps, kf_valid, ep ? kf_uright : nullptr, kf_node, kf_start, kf_feature, kf_count, qcap, f_node,
+                                                  f_count, cap, q, n_queries);
+  const dim3 grid((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames);
   const size_t smem = (size_t)((cap + 31) / 32) * sizeof(unsigned);
-  orb_guided_resolve_kernel<true><<<frames, 32, smem, st>>>(nullptr, nullptr, f_start, f_feature, f_kps, f_desc, nullptr, f_blocked, cap, q, kf_desc,
-                                                            n_queries, qcap, 0.f, 0.f, 0.f, 0.f, th_dist, nn_ratio, 1, check_orientation, lists,
-                                                            list_cnt, assigned, query_match, nmatches);
+  if (ep) {
+    orb_guided_candidates_kernel<2><<<grid, GUIDED_WARPS * 32, 0, st>>>(nullptr, nullptr, f_start, f_feature, f_kps, ep, f_desc, f_uright, f_blocked,
+                                                                          cap, q, kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, lists, list_cnt);
+    orb_guided_resolve_kernel<2><<<frames, 32, smem, st>>>(nullptr, nullptr, f_start, f_feature, ep, f_kps, f_desc, f_uright, f_blocked, cap, q, kf_desc,
+                                                           n_queries, qcap, 0.f, 0.f, 0.f, 0.f, th_dist, nn_ratio, 1, check_orientation, lists,
+                                                           list_cnt, assigned, query_match, nmatches);
+  } else {
+    orb_guided_candidates_kernel<1><<<grid, GUIDED_WARPS * 32, 0, st>>>(nullptr, nullptr, f_start, f_feature, nullptr, nullptr, f_desc, nullptr,
+                                                                          f_blocked, cap, q, kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, lists, list_cnt);
+    orb_guided_resolve_kernel<1><<<frames, 32, smem, st>>>(nullptr, nullptr, f_start, f_feature, nullptr, f_kps, f_desc, nullptr, f_blocked, cap, q,
+                                                           kf_desc, n_queries, qcap, 0.f, 0.f, 0.f, 0.f, th_dist, nn_ratio, 1, check_orientation, lists,
+                                                           list_cnt, assigned, query_match, nmatches);
+  }
   *launches += 3;
 }

@@ -10,7 +10,7 @@ struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mut
   std::mutex mu;
   DevBuf partial, q, db, out;
   // orb_search_by_projection: sorted keypoints + cell starts + per-query top-2, and the staging copies of host arguments
-  DevBuf g_bq, g_bnq, g_stage[16];   // orb_search_by_bow: device-built queries, staging of host arguments
+  DevBuf g_bq, g_bnq, g_stage[17];   // orb_search_by_bow: device-built queries, staging of host arguments
   DevBuf g_items, g_cells, g_lists, g_lcnt, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
   int num_sms = 0;
 };
@@ -285,18 +285,24 @@ int orb_search_for_initialization(int mem, const orb_keypoint* kps_un, const uin
   return ORB_OK;
 }
 
-int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
-                      const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
-                      const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,
-                      const int32_t* f_fv_feature, const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio,
-                      int check_orientation, int32_t* assigned, int32_t* kf_match, int32_t* nmatches, void* stream) {
-  const void* in[14] = {kf_desc, kf_kps_un, kf_valid, kf_fv_node, kf_fv_start, kf_fv_feature, kf_fv_count,
-                        f_desc,  f_kps,     f_fv_node, f_fv_start, f_fv_feature, f_fv_count, f_blocked /* optional */};
+}  // extern "C"
+
+// SearchByBoW (epi == NULL) and SearchForTriangulation (epi != NULL: per-pair epipolar geometry, stereo flags of both keyframes,
+// no ratio test, later candidate wins ties) share the query builder, the candidate lists and the sequential resolve.
+static int search_by_bow_impl(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
+                              const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
+                              const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,
+                              const int32_t* f_fv_feature, const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio,
+                              int check_orientation, int32_t* assigned, int32_t* kf_match, int32_t* nmatches, void* stream,
+                              const orb_epipolar* epi, const float* kf_uright, const float* f_uright) {
+  const void* in[17] = {kf_desc, kf_kps_un, kf_valid, kf_fv_node, kf_fv_start, kf_fv_feature, kf_fv_count,
+                        f_desc,  f_kps,     f_fv_node, f_fv_start, f_fv_feature, f_fv_count, f_blocked /* optional */,
+                        epi /* optional from here */, kf_uright, f_uright};
   for (int i = 0; i < 13; ++i)
     if (!in[i]) return fail(ORB_E_BADARG, "null argument");
-  if (!assigned || !nmatches) return fail(ORB_E_BADARG, "null argument");
+  if (!nmatches || (!assigned && !epi) || (epi && !kf_match)) return fail(ORB_E_BADARG, "null argument");
   if (cap <= 0 || cap >= (1 << 18) || qcap <= 0 || qcap >= (1 << 18) || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap, qcap < 2^18, frames > 0)");
-  if (th_dist < 0 || th_dist > 255 || !(nn_ratio > 0.f)) return fail(ORB_E_BADARG, "th_dist in [0, 255] and nn_ratio > 0 required");
+  if (th_dist < 0 || th_dist > 255 || (!epi && !(nn_ratio > 0.f))) return fail(ORB_E_BADARG, "th_dist in [0, 255] and nn_ratio > 0 required");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
   KnnWorkspace* ws;
@@ -324,9 +330,10 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
           !csr_ok(f_fv_start + (size_t)f * (N + 1), f_fv_feature + (size_t)f * N, f_fv_count[f], cap))
         return fail(ORB_E_BADARG, "frame %d: malformed FeatureVector (counts, ascending starts, feature indices in range)", f);
     }
-    const size_t bytes[14] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
-                              F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4, F * N};
-    for (int i = 0; i < 14; ++i) {
+    const size_t bytes[17] = {F * Q * 32, F * Q * sizeof(orb_keypoint), F * Q, F * Q * 4, F * (Q + 1) * 4, F * Q * 4, F * 4,
+                              F * N * 32, F * N * sizeof(orb_keypoint), F * N * 4, F * (N + 1) * 4, F * N * 4, F * 4, F * N,
+                              F * sizeof(orb_epipolar), F * Q * 4, F * N * 4};
+    for (int i = 0; i < 17; ++i) {
       if (!in[i]) continue;
       if ((rc = ws->g_stage[i].ensure(bytes[i])) != ORB_OK) return rc;
       CU(cudaMemcpyAsync(ws->g_stage[i].p, in[i], bytes[i], cudaMemcpyHostToDevice, st));
@@ -341,6 +348,10 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
     if ((rc = ws->g_qmatch.ensure(F * Q * sizeof(int))) != ORB_OK) return rc;
     d_qmatch = ws->g_qmatch.as<int>();
   }
+  if (!host && !assigned) {   // SearchForTriangulation callers only want vMatches12
+    if ((rc = ws->g_assigned.ensure(F * N * sizeof(int))) != ORB_OK) return rc;
+    d_assigned = ws->g_assigned.as<int>();
+  }
   if ((rc = ws->g_bq.ensure(F * Q * 32)) != ORB_OK) return rc;
   if ((rc = ws->g_bnq.ensure(F * sizeof(int))) != ORB_OK) return rc;
   if ((rc = ws->g_lists.ensure(F * Q * 32 * sizeof(uint2))) != ORB_OK) return rc;
@@ -350,16 +361,40 @@ int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kp
                            (const int*)in[5], (const int*)in[6], qcap, (const uint8_t*)in[7], (const OrbKeypoint*)in[8], (const uint8_t*)in[13],
                            (const int*)in[9], (const int*)in[10], (const int*)in[11], (const int*)in[12], cap, frames, th_dist, nn_ratio,
                            check_orientation, ws->g_bq.p, ws->g_bnq.as<int>(), ws->g_lists.as<uint2>(), ws->g_lcnt.as<int>(), d_assigned, d_qmatch,
-                           d_nm, st, &launched);
+                           d_nm, st, &launched, in[14], (const float*)in[15], (const float*)in[16]);
   orb_knn_count_launches(launched);
   CU(cudaGetLastError());
   if (host) {
-    CU(cudaMemcpyAsync(assigned, d_assigned, F * N * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (assigned) CU(cudaMemcpyAsync(assigned, d_assigned, F * N * sizeof(int), cudaMemcpyDeviceToHost, st));
     if (kf_match) CU(cudaMemcpyAsync(kf_match, d_qmatch, F * Q * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(nmatches, d_nm, F * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
   }
   return ORB_OK;
+}
+
+extern "C" {
+
+int orb_search_by_bow(int mem, const uint8_t* kf_desc, const orb_keypoint* kf_kps_un, const uint8_t* kf_valid, const int32_t* kf_fv_node,
+                      const int32_t* kf_fv_start, const int32_t* kf_fv_feature, const int32_t* kf_fv_count, int qcap, const uint8_t* f_desc,
+                      const orb_keypoint* f_kps, const uint8_t* f_blocked, const int32_t* f_fv_node, const int32_t* f_fv_start,
+                      const int32_t* f_fv_feature, const int32_t* f_fv_count, int cap, int frames, int th_dist, float nn_ratio,
+                      int check_orientation, int32_t* assigned, int32_t* kf_match, int32_t* nmatches, void* stream) {
+  return search_by_bow_impl(mem, kf_desc, kf_kps_un, kf_valid, kf_fv_node, kf_fv_start, kf_fv_feature, kf_fv_count, qcap, f_desc, f_kps, f_blocked,
+                            f_fv_node, f_fv_start, f_fv_feature, f_fv_count, cap, frames, th_dist, nn_ratio, check_orientation, assigned, kf_match,
+                            nmatches, stream, nullptr, nullptr, nullptr);
+}
+
+int orb_search_for_triangulation(int mem, const uint8_t* kf1_desc, const orb_keypoint* kf1_kps_un, const uint8_t* kf1_free, const float* kf1_uright,
+                                 const int32_t* kf1_fv_node, const int32_t* kf1_fv_start, const int32_t* kf1_fv_feature, const int32_t* kf1_fv_count,
+                                 int qcap, const uint8_t* kf2_desc, const orb_keypoint* kf2_kps_un, const uint8_t* kf2_blocked, const float* kf2_uright,
+                                 const int32_t* kf2_fv_node, const int32_t* kf2_fv_start, const int32_t* kf2_fv_feature, const int32_t* kf2_fv_count,
+                                 int cap, int pairs, const orb_epipolar* epi, int th_dist, int check_orientation, int32_t* matches12,
+                                 int32_t* nmatches, void* stream) {
+  if (!epi || !kf1_uright || !kf2_uright || !kf2_blocked || !matches12) return fail(ORB_E_BADARG, "null argument");
+  return search_by_bow_impl(mem, kf1_desc, kf1_kps_un, kf1_free, kf1_fv_node, kf1_fv_start, kf1_fv_feature, kf1_fv_count, qcap, kf2_desc, kf2_kps_un,
+                            kf2_blocked, kf2_fv_node, kf2_fv_start, kf2_fv_feature, kf2_fv_count, cap, pairs, th_dist, 0.f, check_orientation, nullptr,
+                            matches12, nmatches, stream, epi, kf1_uright, kf2_uright);
 }
 
 int orb_undistort_keypoints(int mem, const orb_camera* cam, const orb_keypoint* kps, const int32_t* n, int cap, int frames,

@@ -32,7 +32,8 @@ long long orb_knn_launches();
 void orb_knn_count_launches(long long n);
 void orb_launch_search_by_bow(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, const uint8_t*,
                               const OrbKeypoint*, const uint8_t*, const int*, const int*, const int*, const int*, int, int, int, float, int, void*, int*, uint2*, int*,
-                              int*, int*, int*, cudaStream_t, long long*);
+                              int*, int*, int*, cudaStream_t, long long*, const void* epi = nullptr, const float* kf_uright = nullptr,
+                              const float* f_uright = nullptr);
 void orb_launch_search_init(const OrbKeypoint*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*, int, int, float, float, float,
                             float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
 void orb_launch_undistort(const void*, const OrbKeypoint*, const int*, int, int, OrbKeypoint*, cudaStream_t);

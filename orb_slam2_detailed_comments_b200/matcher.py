@@ -200,6 +200,34 @@ class ORBmatcher:
                                            float(self.mfNNratio), int(self.mbCheckOrientation), _vp(assigned), _vp(kf_match), _vp(nm), None))
         return assigned, kf_match, nm
 
+    def SearchForTriangulation(self, kf1_desc, kf1_kps_un, kf1_has_mp, kf1_uright, kf1_bow: dict, kf2_desc, kf2_kps_un, kf2_has_mp, kf2_uright,
+                               kf2_bow: dict, epi, only_stereo: bool = False, th_dist: int | None = None):
+        """ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:879-1090) for P independent
+        keyframe pairs. kf?_desc [P,n,32], kf?_kps_un [P,n] (mvKeysUn), kf?_has_mp [P,n] (GetMapPoint(idx) != NULL), kf?_uright [P,n]
+        (mvuRight), kf?_bow = ORBVocabulary.transform output; epi [P] EPI_DTYPE (F12, epipole, pKF2's sigma2 / scale tables).
+        Returns (vMatches12 [P,qcap], nmatches [P]); vMatchedPairs of pair p = [(i, m) for i, m in enumerate(vMatches12[p]) if m >= 0]."""
+        from ._lib import EPI_DTYPE
+        P, qcap = kf1_kps_un.shape
+        cap = kf2_kps_un.shape[1]
+        c = np.ascontiguousarray
+        ur1, ur2 = c(kf1_uright, np.float32), c(kf2_uright, np.float32)
+        free1 = (c(kf1_has_mp, np.uint8) == 0)
+        blocked2 = (c(kf2_has_mp, np.uint8) != 0)
+        if only_stereo:   # :931-934, :963-966
+            free1 &= ur1 >= 0
+            blocked2 |= ~(ur2 >= 0)
+        epi = c(epi)
+        assert epi.dtype == EPI_DTYPE and epi.shape == (P,)
+        args = [c(kf1_desc, np.uint8), c(kf1_kps_un), c(free1, np.uint8), ur1, c(kf1_bow["fv_node"]), c(kf1_bow["fv_start"]), c(kf1_bow["fv_feature"]),
+                c(kf1_bow["fv_count"]), c(kf2_desc, np.uint8), c(kf2_kps_un), c(blocked2, np.uint8), ur2, c(kf2_bow["fv_node"]),
+                c(kf2_bow["fv_start"]), c(kf2_bow["fv_feature"]), c(kf2_bow["fv_count"])]
+        assert args[5].shape == (P, qcap + 1) and args[13].shape == (P, cap + 1)
+        m12, nm = np.empty((P, qcap), np.int32), np.empty(P, np.int32)
+        p = [_vp(a) for a in args]
+        check(_lib.lib().orb_search_for_triangulation(MEM_HOST, *p[:8], qcap, *p[8:], cap, P, _vp(epi), int(self.TH_LOW if th_dist is None else th_dist),
+                                                      int(self.mbCheckOrientation), _vp(m12), _vp(nm), None))
+        return m12, nm
+
     def SearchForInitialization(self, kps2_un, desc2, n2, queries, qdesc, n_queries, bounds, th_dist: int | None = None):
         """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) for F frame
         pairs. queries [F,qcap] QUERY_DTYPE: u, v = vbPrevMatched, radius = windowSize, levels (0, 0), angle, SKIP for level > 0.
