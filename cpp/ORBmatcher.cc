@@ -106,6 +106,55 @@ int ORBmatcher::SearchByProjection(const TargetFrame& F, const std::vector<Proje
   return nmatches;
 }
 
+void ORBmatcher::FuseSearch(const TargetFrame& KF, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors,
+                            const std::vector<float>* invLevelSigma2, int th, std::vector<int>& bestIdx, std::vector<int>* bestDist) const {
+  const int n = (int)KF.mvKeysUn->size(), m = (int)points.size();
+  bestIdx.assign(m, -1);
+  if (bestDist) bestDist->assign(m, 256);
+  if (n == 0 || m == 0) return;
+  if (KF.mDescriptors->rows != n || pointDescriptors.rows != m) throw std::runtime_error("FuseSearch: descriptor rows != keypoints / points");
+  if (invLevelSigma2 && invLevelSigma2->size() > 16) throw std::runtime_error("FuseSearch: more than 16 pyramid levels");
+  std::vector<uint8_t> tmp_d, tmp_q;
+  const uint8_t* d = rows32(*KF.mDescriptors, tmp_d);
+  const uint8_t* qd = rows32(pointDescriptors, tmp_q);
+  std::vector<orb_proj_query> q(m);
+  for (int i = 0; i < m; ++i) {
+    const ProjectedPoint& p = points[i];
+    q[i].u = p.u; q[i].v = p.v; q[i].radius = p.radius; q[i].ur = p.uRight; q[i].angle = p.angle;
+    q[i].min_level = (int16_t)p.minLevel; q[i].max_level = (int16_t)p.maxLevel;
+    q[i].flags = p.skip ? ORB_QUERY_SKIP : 0;
+    q[i].reserved = 0;
+  }
+  orb_search_params prm;
+  prm.min_x = KF.mnMinX; prm.min_y = KF.mnMinY; prm.max_x = KF.mnMaxX; prm.max_y = KF.mnMaxY;
+  prm.th_dist = th; prm.nn_ratio = 0.f; prm.check_orientation = 0; prm.reserved = 0;
+  float sig[16] = {0.f};
+  if (invLevelSigma2) std::copy(invLevelSigma2->begin(), invLevelSigma2->end(), sig);
+  std::vector<int32_t> bd(m);
+  check(orb_fuse_search(ORB_MEM_HOST, reinterpret_cast<const orb_keypoint*>(KF.mvKeysUn->data()), d, KF.mvuRight ? KF.mvuRight->data() : nullptr, &n, n,
+                        q.data(), qd, &m, m, 1, &prm, invLevelSigma2 ? sig : nullptr, bestIdx.data(), bd.data(), nullptr),
+        "orb_fuse_search");
+  if (bestDist) bestDist->assign(bd.begin(), bd.end());
+}
+
+int ORBmatcher::SearchBySim3(const TargetFrame& KF1, const TargetFrame& KF2, const std::vector<ProjectedPoint>& points1in2, const cv::Mat& descriptors1,
+                             const std::vector<ProjectedPoint>& points2in1, const cv::Mat& descriptors2, std::vector<int>& matches12) const {
+  std::vector<int> vnMatch1, vnMatch2;
+  FuseSearch(KF2, points1in2, descriptors1, nullptr, TH_HIGH, vnMatch1);   // :1528-1580
+  FuseSearch(KF1, points2in1, descriptors2, nullptr, TH_HIGH, vnMatch2);   // :1590-1660
+  const int N1 = (int)points1in2.size();
+  matches12.assign(N1, -1);
+  int nFound = 0;
+  for (int i1 = 0; i1 < N1; ++i1) {                                        // :1672-1686
+    const int idx2 = vnMatch1[i1];
+    if (idx2 >= 0 && idx2 < (int)vnMatch2.size() && vnMatch2[idx2] == i1) {
+      matches12[i1] = idx2;
+      ++nFound;
+    }
+  }
+  return nFound;
+}
+
 void ORBmatcher::ComputeDistinctiveDescriptors(const cv::Mat& observations, const std::vector<int64_t>& offsets, std::vector<int>& bestIdx) {
   const int points = (int)offsets.size() - 1;
   bestIdx.assign(points > 0 ? points : 0, -1);

@@ -83,6 +83,20 @@ class ORBmatcher {
                   const FeatureVector& kfFeatVec, const cv::Mat& fDescriptors, const std::vector<cv::KeyPoint>& fKeys,
                   const FeatureVector& fFeatVec, std::vector<int>& assigned) const;
 
+  // The candidate search of Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1100-1280), Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+  // (:1282-1430) and of SearchBySim3's two projection passes (:1433-1700): every projected point on its own (these loops hold no
+  // claims between points). points[i].minLevel / maxLevel = nPredictedLevel - 1 / nPredictedLevel (:1188); skip = the reference's
+  // `continue`s before GetFeaturesInArea; invLevelSigma2 (pKF->mvInvLevelSigma2) switches the chi-square reprojection test of the
+  // first Fuse form on (:1193-1218), nullptr = off. bestIdx[i] = the keypoint the reference would fuse / match (bestDist <= th) or
+  // -1; bestDist[i] = 256 without a candidate. The Replace / AddObservation bookkeeping stays with the caller. GPU only.
+  void FuseSearch(const TargetFrame& KF, const std::vector<ProjectedPoint>& points, const cv::Mat& pointDescriptors,
+                  const std::vector<float>* invLevelSigma2, int th, std::vector<int>& bestIdx, std::vector<int>* bestDist = nullptr) const;
+  // SearchBySim3's matching (:1528-1690) after the caller projected KF1's points into KF2 (points1in2, SKIP where the reference
+  // `continue`s, vbAlreadyMatched1 included) and vice versa: vnMatch1 / vnMatch2 by FuseSearch with TH_HIGH, then the mutual check
+  // "vnMatch2[vnMatch1[i1]] == i1" (:1672-1686). matches12[i1] = index in KF2 or -1; returns nFound.
+  int SearchBySim3(const TargetFrame& KF1, const TargetFrame& KF2, const std::vector<ProjectedPoint>& points1in2, const cv::Mat& descriptors1,
+                   const std::vector<ProjectedPoint>& points2in1, const cv::Mat& descriptors2, std::vector<int>& matches12) const;
+
   // SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:879-1090) on flat inputs: per keyframe
   // mDescriptors / mvKeysUn / "GetMapPoint(idx) != NULL" flags / mvuRight / mFeatVec; F12 (3x3 CV_32F); the epipole (ex, ey) of camera 1
   // in image 2 computed by the caller as in :885-897; pKF2's mvLevelSigma2 and mvScaleFactors. Returns nmatches. GPU only.

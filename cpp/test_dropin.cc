@@ -2,6 +2,7 @@
 // the CPU oracle (oracle/orb_oracle.h, test infrastructure). Run by tests/test_cpp_dropin.py on a B200; exit code 0 = pass.
 //   usage: test_dropin <frame.raw> <width> <height> <nfeatures> [<frame2.raw>]
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -185,6 +186,59 @@ int main(int argc, char** argv) {
         REQUIRE(nm > 50, "SearchByProjection form %d: too few matches (%d)", form, nm);
         std::printf("SearchByProjection (%s): %d matches, assignment bit-exact vs oracle\n", form ? "local-map form" : "frame-to-frame form", nm);
       }
+    }
+    // Fuse candidate search (with and without the chi-square test) and SearchBySim3's mutual check on the same two feature sets
+    {
+      typedef ORB_SLAM2::ORBmatcher::ProjectedPoint PP;
+      std::vector<PP> p12(bk[0].size()), p21(bk[1].size());
+      for (size_t i = 0; i < p12.size(); ++i) { const cv::KeyPoint& k = bk[0][i]; p12[i] = {k.pt.x, k.pt.y, 40.f, k.pt.x - 12.f, k.angle, k.octave - 1, k.octave, (i % 13) == 5, false}; }
+      for (size_t i = 0; i < p21.size(); ++i) { const cv::KeyPoint& k = bk[1][i]; p21[i] = {k.pt.x, k.pt.y, 40.f, k.pt.x - 12.f, k.angle, k.octave - 1, k.octave, (i % 19) == 2, false}; }
+      std::vector<float> ur2(bk[1].size(), -1.f), inv(8);
+      for (size_t i = 0; i < ur2.size(); i += 3) ur2[i] = bk[1][i].pt.x - 10.f;
+      for (int l = 0; l < 8; ++l) inv[l] = 1.f / (400.f * (float)std::pow(1.44, l));   // loose table: the synthetic pair is not registered
+      ORB_SLAM2::ORBmatcher::TargetFrame K1{&bk[0], &bd[0], nullptr, nullptr, 0.f, 0.f, (float)W, (float)H};
+      ORB_SLAM2::ORBmatcher::TargetFrame K2{&bk[1], &bd[1], &ur2, nullptr, 0.f, 0.f, (float)W, (float)H};
+      auto to_oq = [](const std::vector<PP>& p) {
+        std::vector<orb_oracle_query> q(p.size());
+        for (size_t i = 0; i < p.size(); ++i) q[i] = {p[i].u, p[i].v, p[i].radius, p[i].uRight, p[i].angle, (int16_t)p[i].minLevel, (int16_t)p[i].maxLevel, p[i].skip ? 1 : 0, 0};
+        return q;
+      };
+      const std::vector<orb_oracle_query> q12 = to_oq(p12), q21 = to_oq(p21);
+      ORB_SLAM2::ORBmatcher fm(0.6f, true);
+      float sig16[16] = {0.f};
+      std::copy(inv.begin(), inv.end(), sig16);
+      for (int chi = 0; chi < 2; ++chi) {
+        std::vector<int> bi, bdist;
+        fm.FuseSearch(K2, p12, bd[0], chi ? &inv : nullptr, ORB_SLAM2::ORBmatcher::TH_LOW, bi, &bdist);
+        orb_oracle_search_params op{0.f, 0.f, (float)W, (float)H, ORB_SLAM2::ORBmatcher::TH_LOW, 0.f, 0, 0};
+        std::vector<int32_t> wi(p12.size()), wd(p12.size());
+        orb_oracle_fuse_search(reinterpret_cast<const orb_oracle_kp*>(bk[1].data()), bd[1].ptr<unsigned char>(0), ur2.data(), (int)bk[1].size(), q12.data(),
+                               bd[0].ptr<unsigned char>(0), (int)q12.size(), &op, chi ? sig16 : nullptr, wi.data(), wd.data());
+        int nf = 0;
+        for (int v : bi) nf += v >= 0;
+        REQUIRE(std::memcmp(bi.data(), wi.data(), wi.size() * 4) == 0 && std::memcmp(bdist.data(), wd.data(), wd.size() * 4) == 0,
+                "FuseSearch (chi-square %d) differs from the oracle", chi);
+        REQUIRE(nf > 20, "FuseSearch: too few fused points (%d)", nf);
+        std::printf("FuseSearch (%s): %d points with a fuse candidate, bestIdx / bestDist bit-exact vs oracle\n", chi ? "chi-square test" : "no chi-square test", nf);
+      }
+      std::vector<int> m12;
+      const int nfound = fm.SearchBySim3(K1, K2, p12, bd[0], p21, bd[1], m12);
+      orb_oracle_search_params oh{0.f, 0.f, (float)W, (float)H, ORB_SLAM2::ORBmatcher::TH_HIGH, 0.f, 0, 0};
+      std::vector<int32_t> v1(p12.size()), v2(p21.size()), dd(std::max(p12.size(), p21.size()));
+      orb_oracle_fuse_search(reinterpret_cast<const orb_oracle_kp*>(bk[1].data()), bd[1].ptr<unsigned char>(0), ur2.data(), (int)bk[1].size(), q12.data(),
+                             bd[0].ptr<unsigned char>(0), (int)q12.size(), &oh, nullptr, v1.data(), dd.data());
+      orb_oracle_fuse_search(reinterpret_cast<const orb_oracle_kp*>(bk[0].data()), bd[0].ptr<unsigned char>(0), nullptr, (int)bk[0].size(), q21.data(),
+                             bd[1].ptr<unsigned char>(0), (int)q21.size(), &oh, nullptr, v2.data(), dd.data());
+      int want_found = 0;
+      bool same = true;
+      for (size_t i1 = 0; i1 < v1.size(); ++i1) {
+        const bool mutual = v1[i1] >= 0 && v2[v1[i1]] == (int)i1;
+        want_found += mutual;
+        same = same && m12[i1] == (mutual ? v1[i1] : -1);
+      }
+      REQUIRE(same && nfound == want_found, "SearchBySim3: %d mutual matches vs oracle %d", nfound, want_found);
+      REQUIRE(nfound > 20, "SearchBySim3: too few mutual matches (%d)", nfound);
+      std::printf("SearchBySim3: %d mutual matches bit-exact vs oracle\n", nfound);
     }
     // SearchForInitialization: left keypoints search a 100-px window around their own position in the right image
     {

@@ -18,6 +18,7 @@
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
  *   orb_search_for_initialization <- ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   src/ORBmatcher.cc:570-712
  *   orb_search_by_bow         <- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)                  src/ORBmatcher.cc:248-410
+ *   orb_fuse_search           <- the candidate search of ORBmatcher::Fuse (both forms) and SearchBySim3      src/ORBmatcher.cc:1100-1700
  *   orb_search_for_triangulation <- ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) src/ORBmatcher.cc:879-1090
  *   orb_vocabulary_*, orb_bow_transform <- Frame::ComputeBoW = DBoW2 TemplatedVocabulary::transform   src/Frame.cc:750-765,
  *                                Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1136-1195, 1240-1280
@@ -213,6 +214,21 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
                              const int32_t* n_kps, int cap, const orb_proj_query* queries, const uint8_t* qdesc,
                              const int32_t* n_queries, int qcap, int frames, const orb_search_params* prm, int32_t* assigned,
                              int32_t* query_match, int32_t* nmatches, void* stream);
+
+/* ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1100-1280), Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1282-1430)
+ * and the two projection passes of SearchBySim3 (:1433-1700): the candidate search of every projected map point on its own (these
+ * loops have no claims between map points). For query j of frame f: candidates = GetFeaturesInArea(u, v, radius) with
+ * min_level <= octave <= max_level (the reference's "kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel", :1188);
+ * with inv_level_sigma2 != NULL (host table of 16 floats = pKF->mvInvLevelSigma2, zero-padded) a candidate is dropped when its
+ * reprojection error fails the chi-square test of the first Fuse form (:1193-1218: stereo keypoints, uright[i] >= 0, use
+ * ex^2 + ey^2 + er^2 against 7.8, monocular ones ex^2 + ey^2 against 5.99; float32 products, double compare); best =
+ * smallest DescriptorDistance, first in scan order on ties. best_dist [frames][qcap] (optional) = bestDist (256 = no candidate),
+ * best_idx [frames][qcap] = bestIdx if bestDist <= prm->th_dist (TH_LOW for Fuse, TH_HIGH for SearchBySim3) else -1. The map
+ * bookkeeping (Replace / AddObservation, the mutual-consistency check of SearchBySim3) stays with the caller. Arrays as for
+ * orb_search_by_projection; prm->nn_ratio and check_orientation are ignored. */
+int orb_fuse_search(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const int32_t* n_kps, int cap,
+                    const orb_proj_query* queries, const uint8_t* qdesc, const int32_t* n_queries, int qcap, int frames,
+                    const orb_search_params* prm, const float* inv_level_sigma2, int32_t* best_idx, int32_t* best_dist, void* stream);
 
 /* Register-resident xor+popc+add microbenchmark: returns measured popc.b32 per second on `device` (roofline denominator). */
 double orb_measure_popc_peak(int device);

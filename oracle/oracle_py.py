@@ -239,6 +239,28 @@ def search_by_projection(kps_un, desc, queries, qdesc, bounds, th_dist=100, nn_r
     return assigned[:n], qmatch[:m], nm
 
 
+def fuse_search(kps_un, desc, queries, qdesc, bounds, th_dist=50, uright=None, inv_level_sigma2=None):
+    """Candidate search of ORBmatcher::Fuse / SearchBySim3 (src/ORBmatcher.cc:1100-1700), one keyframe. Returns (best_idx [m], best_dist [m])."""
+    L = lib()
+    L.orb_oracle_fuse_search.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(_SearchParams), C.c_void_p,
+                                                         C.c_void_p, C.c_void_p]
+    L.orb_oracle_fuse_search.restype = None
+    kps_un, desc = np.ascontiguousarray(kps_un), np.ascontiguousarray(desc)
+    queries, qdesc = np.ascontiguousarray(queries), np.ascontiguousarray(qdesc)
+    assert queries.dtype == QUERY_DTYPE and kps_un.dtype.itemsize == 28
+    n, m = len(kps_un), len(queries)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    sig = None
+    if inv_level_sigma2 is not None:
+        sig = np.zeros(16, np.float32)
+        sig[:len(inv_level_sigma2)] = inv_level_sigma2
+    prm = _SearchParams(*[float(b) for b in bounds], int(th_dist), 0.0, 0, 0)
+    bi, bd = np.full(max(m, 1), -1, np.int32), np.full(max(m, 1), 256, np.int32)
+    L.orb_oracle_fuse_search(_p(kps_un), _p(desc), None if ur is None else _p(ur), n, _p(queries), _p(qdesc), m, C.byref(prm),
+                             None if sig is None else _p(sig), _p(bi), _p(bd))
+    return bi[:m], bd[:m]
+
+
 def features_in_area(kps_un, bounds, x, y, r, min_level=-1, max_level=-1):
     """Frame::GetFeaturesInArea (src/Frame.cc:633-717) with its scan order."""
     L = lib()

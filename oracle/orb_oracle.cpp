@@ -662,6 +662,46 @@ int orb_oracle_features_in_area(const orb_oracle_kp* kps, int n, const orb_oracl
   return (int)v.size();
 }
 
+// The candidate loop of ORBmatcher::Fuse (src/ORBmatcher.cc:1166-1232; without the chi-square test: the Scw form :1380-1405 and the
+// projection passes of SearchBySim3 :1540-1580, :1640-1680), one query at a time, no state between queries.
+void orb_oracle_fuse_search(const orb_oracle_kp* kps, const uint8_t* desc, const float* uright, int n, const orb_oracle_query* q,
+                            const uint8_t* qdesc, int m, const orb_oracle_search_params* prm, const float* inv_level_sigma2, int32_t* best_idx,
+                            int32_t* best_dist) {
+  FrameGrid grid(kps, n, *prm);
+  std::vector<int> vIndices;
+  for (int j = 0; j < m; ++j) {
+    best_idx[j] = -1;
+    best_dist[j] = 256;
+    if (q[j].flags & 1) continue;
+    const float u = q[j].u, v = q[j].v, ur = q[j].ur;
+    grid.in_area(kps, u, v, q[j].radius, -1, -1, vIndices);   // pKF->GetFeaturesInArea(u, v, radius) (:1166)
+    int bestDist = 256, bestIdx = -1;
+    for (int idx : vIndices) {
+      const orb_oracle_kp& kp = kps[idx];
+      const int kpLevel = kp.octave;
+      if (kpLevel < q[j].min_level || kpLevel > q[j].max_level) continue;   // nPredictedLevel - 1 .. nPredictedLevel (:1188)
+      if (inv_level_sigma2) {
+        if (uright && uright[idx] >= 0) {   // :1193-1206
+          const float ex = u - kp.x;
+          const float ey = v - kp.y;
+          const float er = ur - uright[idx];
+          const float e2 = ex * ex + ey * ey + er * er;
+          if (e2 * inv_level_sigma2[kpLevel] > 7.8) continue;
+        } else {                            // :1207-1218
+          const float ex = u - kp.x;
+          const float ey = v - kp.y;
+          const float e2 = ex * ex + ey * ey;
+          if (e2 * inv_level_sigma2[kpLevel] > 5.99) continue;
+        }
+      }
+      const int dist = orb_oracle_descriptor_distance(qdesc + (size_t)j * 32, desc + (size_t)idx * 32);
+      if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+    }
+    best_dist[j] = bestDist;
+    if (bestDist <= prm->th_dist) best_idx[j] = bestIdx;   // :1232 (TH_LOW), :1575 (TH_HIGH)
+  }
+}
+
 int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* desc, const float* uright, const uint8_t* claimed_in,
                                     int n, const orb_oracle_query* q, const uint8_t* qdesc, int m,
                                     const orb_oracle_search_params* prm, int32_t* assigned, int32_t* query_match) {

@@ -112,6 +112,11 @@ typedef struct orb_oracle_search_params {
 int orb_oracle_search_by_projection(const orb_oracle_kp* kps_un, const uint8_t* desc, const float* uright, const uint8_t* claimed,
                                     int n_kps, const orb_oracle_query* queries, const uint8_t* qdesc, int n_queries,
                                     const orb_oracle_search_params* prm, int32_t* assigned, int32_t* query_match);
+/* Candidate search of ORBmatcher::Fuse (src/ORBmatcher.cc:1100-1280; inv_level_sigma2 == NULL: the Scw form and SearchBySim3's passes),
+ * one keyframe: per query best_dist (256 = none) and best_idx (-1 unless best_dist <= prm->th_dist). Level window = [min_level, max_level]. */
+void orb_oracle_fuse_search(const orb_oracle_kp* kps_un, const uint8_t* desc, const float* uright, int n_kps, const orb_oracle_query* queries,
+                            const uint8_t* qdesc, int n_queries, const orb_oracle_search_params* prm, const float* inv_level_sigma2,
+                            int32_t* best_idx, int32_t* best_dist);
 /* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:570-712), one frame pair; queries as in include/orb_b200.h. matches12 [n_queries],
  * matches21 [n_kps] (inverse of the standing matches). Returns nmatches. */
 int orb_oracle_search_for_initialization(const orb_oracle_kp* kps_un, const uint8_t* desc, int n_kps, const orb_oracle_query* queries,

@@ -40,7 +40,7 @@ SYMBOLS = [
     "orb_search_by_projection", "orb_distinctive_descriptors",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_words", "orb_bow_transform",
     "orb_undistort_keypoints", "orb_image_bounds", "orb_search_by_bow", "orb_search_for_initialization",
-    "orb_search_for_triangulation",
+    "orb_search_for_triangulation", "orb_fuse_search",
 ]
 
 
@@ -119,6 +119,7 @@ def lib():
     L.orb_search_for_initialization.argtypes = [i32, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]
     L.orb_search_by_bow.argtypes = [i32] + [vp] * 7 + [i32] + [vp] * 7 + [i32, i32, i32, f32, i32, vp, vp, vp, vp]
     L.orb_search_for_triangulation.argtypes = [i32] + [vp] * 8 + [i32] + [vp] * 8 + [i32, i32, vp, i32, i32, vp, vp, vp]
+    L.orb_fuse_search.argtypes = [i32, vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]
     L.orb_undistort_keypoints.argtypes = [i32, C.POINTER(OrbCamera), vp, vp, i32, i32, vp, vp]
     L.orb_image_bounds.argtypes = [C.POINTER(OrbCamera), i32, i32, vp]
     L.orb_distinctive_descriptors.argtypes = [i32, vp, vp, i32, vp, vp, vp]

@@ -56,6 +56,10 @@ struct GuidedFrame {
   // SearchForTriangulation: undistorted keypoints of the target keyframe and the pair's epipolar geometry
   const OrbKeypoint* kps2;
   const OrbEpi* epi;
+  // Fuse: mvInvLevelSigma2 of the keyframe (16 floats) for the reprojection chi-square test, or nullptr; fuse != 0 also switches the
+  // SearchByProjection-style right-coordinate window test off (Fuse reads mvuRight only inside the chi-square test)
+  const float* inv_sigma2;
+  int fuse;
 };
 
 // A candidate is one 64-bit word {hi, lo}. hi = dist << 18 | sorted position: "strict <, first in scan order wins" is a plain
@@ -102,7 +106,23 @@ __device__ __forceinline__ void guided_scan(const GuidedFrame& F, const GuidedQu
           const uint4 a = F.desc[2 * idx], b = F.desc[2 * idx + 1];
           const int dist = __popc(a.x ^ qd0.x) + __popc(a.y ^ qd0.y) + __popc(a.z ^ qd0.z) + __popc(a.w ^ qd0.w) +
                            __popc(b.x ^ qd1.x) + __popc(b.y ^ qd1.y) + __popc(b.z ^ qd1.z) + __popc(b.w ^ qd1.w);
-          if (!cl && !(ur > 0.f && fabsf(q.ur - ur) > r)) {
+          bool keep = !cl;
+          if (F.fuse) {
+            if (F.inv_sigma2) {   // src/ORBmatcher.cc:1193-1218: float32 error, double compare against the chi-square bound
+              const float ex = __fsub_rn(x, __uint_as_float(it.x)), ey = __fsub_rn(y, __uint_as_float(it.y));
+              float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+              double bound = 5.99;
+              if (ur >= 0.f) {
+                const float er = __fsub_rn(q.ur, ur);
+                e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                bound = 7.8;
+              }
+              if ((double)__fmul_rn(e2, F.inv_sigma2[min(max(oct, 0), 15)]) > bound) keep = false;
+            }
+          } else if (ur > 0.f && fabsf(q.ur - ur) > r) {
+            keep = false;
+          }
+          if (keep) {
             hi = ((unsigned)dist << 18) | (unsigned)e;
             lo = ((unsigned)(oct & 0xff) << 18) | (unsigned)idx;
           }
@@ -259,6 +279,7 @@ orb_guided_candidates_kernel(const uint4* __restrict__ items, const int* __restr
   F.uright = uright ? uright + (size_t)f * cap : nullptr;
   F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  F.inv_sigma2 = nullptr; F.fuse = 0;
   F.fv_start = BOW ? fv_start + (size_t)f * (cap + 1) : nullptr;
   F.fv_feature = BOW ? fv_feature + (size_t)f * cap : nullptr;
   const size_t qi = (size_t)f * qcap + iq;
@@ -310,6 +331,7 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
   F.uright = uright ? uright + (size_t)f * cap : nullptr;
   F.claimed = claimed ? claimed + (size_t)f * cap : nullptr;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  F.inv_sigma2 = nullptr; F.fuse = 0;
   F.fv_start = BOW ? fv_start + (size_t)f * (cap + 1) : nullptr;
   F.fv_feature = BOW ? fv_feature + (size_t)f * cap : nullptr;
   kps += (size_t)f * cap;
@@ -454,6 +476,62 @@ orb_guided_resolve_kernel(const uint4* __restrict__ items, const int* __restrict
   if (lane == 0) nmatches[f] = nm;
 }
 
+// ---- Fuse / SearchBySim3 core: the best candidate of every query on its own ------------------------------------------------
+// ORBmatcher::Fuse (src/ORBmatcher.cc:1100-1280, 1282-1430) and the two projection passes of SearchBySim3 (:1433-1700) pick, for
+// every projected map point independently (no claims between queries), the keypoint of GetFeaturesInArea(u, v, radius) inside the
+// level window with the smallest DescriptorDistance, first in scan order on ties (strict <); Fuse(pKF, vpMapPoints, th)
+// additionally drops candidates whose reprojection error fails the chi-square test. One warp per query.
+__global__ void __launch_bounds__(GUIDED_WARPS * 32)
+orb_fuse_search_kernel(const uint4* __restrict__ items, const int* __restrict__ cell_start, const uint8_t* __restrict__ desc,
+                       const float* __restrict__ uright, int cap, const GuidedQuery* __restrict__ queries, const uint8_t* __restrict__ qdesc,
+                       const int* __restrict__ n_queries, int qcap, float min_x, float min_y, float inv_w, float inv_h,
+                       const float* __restrict__ inv_sigma2, int th_dist, int* __restrict__ best_idx, int* __restrict__ best_dist) {
+  const int f = blockIdx.y, lane = threadIdx.x & 31;
+  const int iq = blockIdx.x * GUIDED_WARPS + (threadIdx.x >> 5);
+  if (iq >= qcap) return;
+  const size_t qi = (size_t)f * qcap + iq;
+  int bi = -1, bd = 256;
+  if (iq < min(n_queries[f], qcap)) {
+    GuidedFrame F;
+    F.items = items + (size_t)f * cap;
+    F.cell_start = cell_start + (size_t)f * (GRID_CELLS + 1);
+    F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
+    F.uright = uright ? uright + (size_t)f * cap : nullptr;
+    F.claimed = nullptr; F.fv_start = nullptr; F.fv_feature = nullptr; F.kps2 = nullptr; F.epi = nullptr;
+    F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+    F.inv_sigma2 = inv_sigma2; F.fuse = 1;
+    const GuidedQuery q = queries[qi];
+    if (!(q.flags & 1)) {
+      const uint4* qd = reinterpret_cast<const uint4*>(qdesc + qi * 32);
+      unsigned long long k = ~0ull;
+      auto emit = [&](unsigned hi, unsigned lo) {
+        if (hi != GUIDED_NONE) k = min(k, ((unsigned long long)hi << 32) | lo);
+      };
+      guided_scan(F, q, qd[0], qd[1], lane, emit);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) k = min(k, __shfl_xor_sync(0xffffffffu, k, o));
+      if (k != ~0ull) { bd = (int)(k >> 50); bi = (int)(k & 0x3ffffull); }
+    }
+  }
+  if (lane == 0) {
+    best_dist[qi] = bd;                        // bestDist (256 = no candidate), reported even above the threshold
+    best_idx[qi] = bd <= th_dist ? bi : -1;    // "if (bestDist <= TH_LOW)" (:1232), TH_HIGH in SearchBySim3 (:1575)
+  }
+}
+
+void orb_launch_fuse_search(const OrbKeypoint* kps, const uint8_t* desc, const float* uright, const int* n_kps, int cap, const void* queries,
+                            const uint8_t* qdesc, const int* n_queries, int qcap, int frames, float min_x, float min_y, float max_x, float max_y,
+                            const float* inv_sigma2, int th_dist, uint4* items, int* cell_start, int* best_idx, int* best_dist, cudaStream_t st,
+                            long long* launches) {
+  const float inv_w = static_cast<float>(GRID_COLS) / static_cast<float>(max_x - min_x);
+  const float inv_h = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
+  orb_guided_grid_kernel<<<frames, 256, 0, st>>>(kps, n_kps, cap, min_x, min_y, inv_w, inv_h, items, cell_start);
+  orb_fuse_search_kernel<<<dim3((qcap + GUIDED_WARPS - 1) / GUIDED_WARPS, frames), GUIDED_WARPS * 32, 0, st>>>(
+      items, cell_start, desc, uright, cap, static_cast<const GuidedQuery*>(queries), qdesc, n_queries, qcap, min_x, min_y, inv_w, inv_h, inv_sigma2,
+      th_dist, best_idx, best_dist);
+  *launches += 2;
+}
+
 void orb_launch_guided(const OrbKeypoint* kps, const uint8_t* desc, const float* uright, const uint8_t* claimed, const int* n_kps, int cap,
                        const void* queries, const uint8_t* qdesc, const int* n_queries, int qcap, int frames, float min_x, float min_y,
                        float max_x, float max_y, int th_dist, float nn_ratio, int check_orientation, uint4* items, int* cell_start,
@@ -496,6 +574,7 @@ orb_guided_resolve_init_kernel(const uint4* __restrict__ items, const int* __res
   F.desc = reinterpret_cast<const uint4*>(desc + (size_t)f * cap * 32);
   F.uright = nullptr; F.claimed = nullptr; F.fv_start = nullptr; F.fv_feature = nullptr;
   F.min_x = min_x; F.min_y = min_y; F.inv_w = inv_w; F.inv_h = inv_h;
+  F.inv_sigma2 = nullptr; F.fuse = 0;
   kps += (size_t)f * cap;
   queries += (size_t)f * qcap;
   qdesc += (size_t)f * qcap * 32;

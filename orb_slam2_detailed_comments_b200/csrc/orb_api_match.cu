@@ -557,6 +557,70 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
   return ORB_OK;
 }
 
+int orb_fuse_search(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const int32_t* n_kps, int cap,
+                    const orb_proj_query* queries, const uint8_t* qdesc, const int32_t* n_queries, int qcap, int frames,
+                    const orb_search_params* prm, const float* inv_level_sigma2, int32_t* best_idx, int32_t* best_dist, void* stream) {
+  if (!kps_un || !desc || !n_kps || !queries || !qdesc || !n_queries || !prm || !best_idx) return fail(ORB_E_BADARG, "null argument");
+  if (cap <= 0 || cap >= (1 << 18) || qcap <= 0 || frames <= 0) return fail(ORB_E_BADARG, "bad size (0 < cap < 2^18, qcap > 0, frames > 0)");
+  if (!(prm->max_x > prm->min_x) || !(prm->max_y > prm->min_y)) return fail(ORB_E_BADARG, "empty image bounds");
+  if (prm->th_dist < 0 || prm->th_dist > 255) return fail(ORB_E_BADARG, "th_dist must be in [0, 255]");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  const size_t F = (size_t)frames;
+  const bool host = mem != ORB_MEM_DEVICE;
+  const void* d_in[7] = {kps_un, desc, uright, nullptr, n_kps, queries, qdesc};
+  const void* d_nq = n_queries;
+  int* d_bi = best_idx;
+  int* d_bd = best_dist;
+  if (host) {
+    DevBuf* bufs[7] = {&ws->g_kps, &ws->g_desc, &ws->g_ur, &ws->g_claim, &ws->g_nk, &ws->g_q, &ws->g_qd};
+    const size_t bytes[7] = {F * cap * sizeof(orb_keypoint), F * cap * 32, F * cap * sizeof(float), 0, F * sizeof(int),
+                             F * qcap * sizeof(orb_proj_query), F * qcap * 32};
+    for (int i = 0; i < 7; ++i) {
+      if (!d_in[i]) continue;
+      if ((rc = bufs[i]->ensure(bytes[i])) != ORB_OK) return rc;
+      CU(cudaMemcpyAsync(bufs[i]->p, d_in[i], bytes[i], cudaMemcpyHostToDevice, st));
+      d_in[i] = bufs[i]->p;
+    }
+    if ((rc = ws->g_nq.ensure(F * sizeof(int))) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->g_nq.p, n_queries, F * sizeof(int), cudaMemcpyHostToDevice, st));
+    d_nq = ws->g_nq.p;
+    if ((rc = ws->g_qmatch.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
+    d_bi = ws->g_qmatch.as<int>();
+  }
+  if (host || !best_dist) {
+    if ((rc = ws->g_lcnt.ensure(F * qcap * sizeof(int))) != ORB_OK) return rc;
+    d_bd = ws->g_lcnt.as<int>();
+  }
+  const float* d_sig = nullptr;
+  if (inv_level_sigma2) {   // always a host table of 16 floats (mvInvLevelSigma2, zero-padded), like prm
+    if ((rc = ws->g_nm.ensure(16 * sizeof(float))) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->g_nm.p, inv_level_sigma2, 16 * sizeof(float), cudaMemcpyHostToDevice, st));
+    d_sig = ws->g_nm.as<float>();
+  }
+  if ((rc = ws->g_items.ensure(F * cap * sizeof(uint4))) != ORB_OK) return rc;
+  if ((rc = ws->g_cells.ensure(F * (64 * 48 + 1) * sizeof(int))) != ORB_OK) return rc;
+  long long launched = 0;
+  orb_launch_fuse_search((const OrbKeypoint*)d_in[0], (const uint8_t*)d_in[1], (const float*)d_in[2], (const int*)d_in[4], cap, d_in[5],
+                         (const uint8_t*)d_in[6], (const int*)d_nq, qcap, frames, prm->min_x, prm->min_y, prm->max_x, prm->max_y, d_sig, prm->th_dist,
+                         ws->g_items.as<uint4>(), ws->g_cells.as<int>(), d_bi, d_bd, st, &launched);
+  orb_knn_count_launches(launched);
+  CU(cudaGetLastError());
+  if (host) {
+    CU(cudaMemcpyAsync(best_idx, d_bi, F * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (best_dist) CU(cudaMemcpyAsync(best_dist, d_bd, F * qcap * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  } else if (inv_level_sigma2) {
+    CU(cudaStreamSynchronize(st));   // the staged table must be consumed before the next call overwrites it
+  }
+  return ORB_OK;
+}
+
 double orb_measure_popc_peak(int device) {
   OrbDeviceGuard guard(device);
   if (guard.err != cudaSuccess) { cudaGetLastError(); return 0.0; }

@@ -47,6 +47,8 @@ void orb_launch_bow(const BowVoc&, int, const uint8_t*, const int*, int, int, in
 void orb_launch_distinctive(const uint8_t*, const long long*, int, int*, int*, cudaStream_t);
 void orb_launch_guided(const OrbKeypoint*, const uint8_t*, const float*, const uint8_t*, const int*, int, const void*, const uint8_t*, const int*,
                        int, int, float, float, float, float, int, float, int, uint4*, int*, uint2*, int*, int*, int*, int*, cudaStream_t, long long*);
+void orb_launch_fuse_search(const OrbKeypoint*, const uint8_t*, const float*, const int*, int, const void*, const uint8_t*, const int*, int, int, float,
+                            float, float, float, const float*, int, uint4*, int*, int*, int*, cudaStream_t, long long*);
 double orb_popc_peak(int num_sms);
 
 

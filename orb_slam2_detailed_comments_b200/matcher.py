@@ -200,6 +200,28 @@ class ORBmatcher:
                                            float(self.mfNNratio), int(self.mbCheckOrientation), _vp(assigned), _vp(kf_match), _vp(nm), None))
         return assigned, kf_match, nm
 
+    def FuseSearch(self, kps_un, desc, n_kps, queries, qdesc, n_queries, bounds, uright=None, inv_level_sigma2=None, th_dist: int | None = None):
+        """The candidate search of ORBmatcher::Fuse (src/ORBmatcher.cc:1100-1280, 1282-1430) and of SearchBySim3's two projection passes
+        (:1433-1700) for F keyframes: every projected map point on its own (no claims). queries [F,qcap] QUERY_DTYPE: u, v, radius,
+        ur, level window (min_level, max_level) = (nPredictedLevel - 1, nPredictedLevel). inv_level_sigma2 (mvInvLevelSigma2) switches
+        the chi-square reprojection test of Fuse(pKF, vpMapPoints, th) on. Returns (best_idx [F,qcap] or -1, best_dist [F,qcap])."""
+        from ._lib import OrbSearchParams
+        F, cap = kps_un.shape
+        qcap = queries.shape[1]
+        c = np.ascontiguousarray
+        a = [c(kps_un), c(desc, np.uint8), c(n_kps, np.int32), c(queries), c(qdesc, np.uint8), c(n_queries, np.int32)]
+        ur = None if uright is None else c(uright, np.float32)
+        sig = None
+        if inv_level_sigma2 is not None:
+            sig = np.zeros(16, np.float32)
+            sig[:len(inv_level_sigma2)] = inv_level_sigma2
+        prm = OrbSearchParams(float(bounds[0]), float(bounds[1]), float(bounds[2]), float(bounds[3]), int(self.TH_LOW if th_dist is None else th_dist),
+                              0.0, 0, 0)
+        bi, bd = np.empty((F, qcap), np.int32), np.empty((F, qcap), np.int32)
+        check(_lib.lib().orb_fuse_search(MEM_HOST, _vp(a[0]), _vp(a[1]), None if ur is None else _vp(ur), _vp(a[2]), cap, _vp(a[3]), _vp(a[4]),
+                                         _vp(a[5]), qcap, F, C.byref(prm), None if sig is None else _vp(sig), _vp(bi), _vp(bd), None))
+        return bi, bd
+
     def SearchForTriangulation(self, kf1_desc, kf1_kps_un, kf1_has_mp, kf1_uright, kf1_bow: dict, kf2_desc, kf2_kps_un, kf2_has_mp, kf2_uright,
                                kf2_bow: dict, epi, only_stereo: bool = False, th_dist: int | None = None):
         """ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:879-1090) for P independent
