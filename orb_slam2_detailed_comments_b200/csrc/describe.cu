@@ -168,7 +168,7 @@ __device__ __forceinline__ int dp4a_u8_s8(unsigned a, unsigned b, int c) {   // 
   asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
   return d;
 }
-__global__ void __launch_bounds__(DESC_WARPS * 32, 24 / DESC_WARPS)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 32 / DESC_WARPS)
 orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr, const uint32_t* __restrict__ kept,
                     const int* __restrict__ kept_cnt, OrbKeypoint* __restrict__ kps, uint8_t* __restrict__ desc, int cap,
                     int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
