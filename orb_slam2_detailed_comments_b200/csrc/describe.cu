@@ -168,7 +168,10 @@ __device__ __forceinline__ int dp4a_u8_s8(unsigned a, unsigned b, int c) {   // 
   asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
   return d;
 }
-__global__ void __launch_bounds__(DESC_WARPS * 32, 32 / DESC_WARPS)
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__global__ void __launch_bounds__(DESC_WARPS * 32, 40 / DESC_WARPS)
 orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr, const uint32_t* __restrict__ kept,
                     const int* __restrict__ kept_cnt, OrbKeypoint* __restrict__ kps, uint8_t* __restrict__ desc, int cap,
                     int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
@@ -236,15 +239,18 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     // three window rows per load instruction: lane = (row % 3, word); the per-lane offsets need one IMAD per keypoint
     const unsigned* icl = icg + ic_sub * pw + ic_w;
     const unsigned* ptl = ptg + pt_sub * pw + pt_w;
-    unsigned ra[11], rp[13];
-#pragma unroll
-    for (int i = 0; i < 11; ++i) ra[i] = (ic_act && 3 * i + ic_sub < 31) ? __ldg(icl + 3 * i * pw) : 0u;
-#pragma unroll
-    for (int i = 0; i < 13; ++i) rp[i] = (pt_act && 3 * i + pt_sub < 37) ? __ldg(ptl + 3 * i * pw) : 0u;
+    // global -> shared without a register round trip: one cp.async per window word, the IC_Angle window and the descriptor patch as
+    // two groups so that the orientation starts as soon as the first has landed
     __syncwarp();                                              // the previous keypoint's gathers are done
 #pragma unroll
     for (int i = 0; i < 11; ++i)
-      if (ic_act && 3 * i + ic_sub < 31) ic[27 * i + ic_idx] = ra[i];
+      if (ic_act && 3 * i + ic_sub < 31) cp_async4(&ic[27 * i + ic_idx], icl + 3 * i * pw);
+    asm volatile("cp.async.commit_group;");
+#pragma unroll
+    for (int i = 0; i < 13; ++i)
+      if (pt_act && 3 * i + pt_sub < 37) cp_async4(&pt[30 * i + pt_idx], ptl + 3 * i * pw);
+    asm volatile("cp.async.commit_group;");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
     // IC_Angle (:104-161): lane = row v
     int m10 = 0, rs = 0;
@@ -270,9 +276,7 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     float a, b;
     orb_sincos(__fmul_rn(angle, factorPI), &b, &a);
     // computeOrbDescriptor (:177-254) on the staged patch: byte (r, c) of the patch is pt[(r + 18) * 40 + c + x - xp]
-#pragma unroll
-    for (int i = 0; i < 13; ++i)
-      if (pt_act && 3 * i + pt_sub < 37) pt[30 * i + pt_idx] = rp[i];
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     const uint8_t* bc = ptb + 18 * 40 + (x - xp);
     int val = 0;
