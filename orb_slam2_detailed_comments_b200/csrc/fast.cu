@@ -226,14 +226,18 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   const unsigned inv_nvec = (unsigned)(__frcp_rn((float)nvec) * 65536.f) + 1u;
   for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
     const int y = (int)(((unsigned)i * inv_nvec) >> 16), v = i - y * nvec;
-    *reinterpret_cast<uint4*>(win + y * FAST_WP + 16 + 16 * v) = *reinterpret_cast<const uint4*>(src + (long long)y * L.pitch + 16 * v);
+    // global -> shared directly (LDGSTS.128); the copies land while the planes below are cleared
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(win + y * FAST_WP + 16 + 16 * v)),
+                 "l"(src + (long long)y * L.pitch + 16 * v));
   }
+  asm volatile("cp.async.commit_group;");
   for (int i = tid; i < (dh + 2) * (FAST_SP / 16); i += FAST_THREADS) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
   // both bit planes, 16 bytes per thread (the rounding may run a few words into the still empty lists)
   for (int i = tid; i < (2 * (sc_rows - 2) * FAST_BP + 3) / 4; i += FAST_THREADS) reinterpret_cast<uint4*>(pl_min)[i] = make_uint4(0, 0, 0, 0);
   const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
   for (int i = tid; i < FAST_WP; i += FAST_THREADS) need[i] = (i >= dx0 && i < dx1) ? 0x80 : 0;   // pass 1: every detection column
   if (tid == 0) s_retry = 0;
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
   // 2. first detection at iniTh (the reference's first cv::FAST call per cell, :1510)
