@@ -112,23 +112,30 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
   const int wbase = lo & ~3;
   const unsigned s0 = 17u * (unsigned)(o0 - lo) + 16u, s1 = 17u * (unsigned)(o1 - lo) + 16u, s2 = 17u * (unsigned)(o2 - lo) + 16u,
                  s3 = 17u * (unsigned)(o3 - lo) + 16u;   // PRMT selectors: bytes (r, r + 1) of the window
+  // all source words of the thread's four rows are requested before the first one is used (rows past the end re-read the last row)
+  const int nrows = D.rows + 2 * (ORB_APRON - 1);
+  unsigned a0[4], a1[4], a2[4], b0[4], b1[4], b2[4], cy0[4], cy1[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int y = min((int)(blockIdx.y * 32 + threadIdx.y + 8 * r), nrows - 1);
+    const ResizeTab ty = yt[y];
+    cy0[r] = (ty.coef & 0xffffu) << 16; cy1[r] = ty.coef & 0xffff0000u;   // pre-shifted: (cy * t) >> 16 == umulhi(cy << 16, t)
+    const unsigned* r0 = reinterpret_cast<const unsigned*>(src + (long long)ty.ofs * S.pitch + wbase);
+    const unsigned* r1 = reinterpret_cast<const unsigned*>(src + (long long)min(ty.ofs + 1, S.rows - 1) * S.pitch + wbase);
+    a0[r] = r0[0]; a1[r] = r0[1]; a2[r] = r0[2]; b0[r] = r1[0]; b1[r] = r1[1]; b2[r] = r1[2];
+  }
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     const int y = blockIdx.y * 32 + threadIdx.y + 8 * r;
-    if (y >= D.rows + 2 * (ORB_APRON - 1)) break;
-    const ResizeTab ty = yt[y];
-    const unsigned cy0 = (ty.coef & 0xffffu) << 16, cy1 = ty.coef & 0xffff0000u;   // pre-shifted: (cy * t) >> 16 == umulhi(cy << 16, t)
-    const unsigned* r0 = reinterpret_cast<const unsigned*>(src + (long long)ty.ofs * S.pitch + wbase);
-    const unsigned* r1 = reinterpret_cast<const unsigned*>(src + (long long)min(ty.ofs + 1, S.rows - 1) * S.pitch + wbase);
-    const unsigned a0 = r0[0], a1 = r0[1], a2 = r0[2], b0 = r1[0], b1 = r1[1], b2 = r1[2];
-    const unsigned al = __funnelshift_r(a0, a1, sh), ah = __funnelshift_r(a1, a2, sh);
-    const unsigned bl = __funnelshift_r(b0, b1, sh), bh = __funnelshift_r(b1, b2, sh);
+    if (y >= nrows) break;
+    const unsigned al = __funnelshift_r(a0[r], a1[r], sh), ah = __funnelshift_r(a1[r], a2[r], sh);
+    const unsigned bl = __funnelshift_r(b0[r], b1[r], sh), bh = __funnelshift_r(b1[r], b2[r], sh);
     unsigned v[4];
 #define ORB_PX(k, sel, coef)                                                                     \
     {                                                                                            \
       const unsigned t0 = __dp2a_lo(coef, __byte_perm(al, ah, sel), 0u);                         \
       const unsigned t1 = __dp2a_lo(coef, __byte_perm(bl, bh, sel), 0u);                         \
-      v[k] = (__umulhi(cy0, t0 >> 4) + __umulhi(cy1, t1 >> 4) + 2u) >> 2;                         \
+      v[k] = (__umulhi(cy0[r], t0 >> 4) + __umulhi(cy1[r], t1 >> 4) + 2u) >> 2;                   \
     }
     ORB_PX(0, s0, e01.y) ORB_PX(1, s1, e01.w) ORB_PX(2, s2, e23.y) ORB_PX(3, s3, e23.w)
 #undef ORB_PX
