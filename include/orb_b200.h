@@ -225,7 +225,8 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
  * smallest DescriptorDistance, first in scan order on ties. best_dist [frames][qcap] (optional) = bestDist (256 = no candidate),
  * best_idx [frames][qcap] = bestIdx if bestDist <= prm->th_dist (TH_LOW for Fuse, TH_HIGH for SearchBySim3) else -1. The map
  * bookkeeping (Replace / AddObservation, the mutual-consistency check of SearchBySim3) stays with the caller. Arrays as for
- * orb_search_by_projection; prm->nn_ratio and check_orientation are ignored. */
+ * orb_search_by_projection; prm->nn_ratio and check_orientation are ignored. With inv_level_sigma2 the call synchronises the stream
+ * before it returns (the table is staged through a per-device buffer). */
 int orb_fuse_search(int mem, const orb_keypoint* kps_un, const uint8_t* desc, const float* uright, const int32_t* n_kps, int cap,
                     const orb_proj_query* queries, const uint8_t* qdesc, const int32_t* n_queries, int qcap, int frames,
                     const orb_search_params* prm, const float* inv_level_sigma2, int32_t* best_idx, int32_t* best_dist, void* stream);
