@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 #include "../oracle/orb_oracle.h"
@@ -131,6 +132,28 @@ int main(int argc, char** argv) {
     for (int i = 0; i < m; ++i) {
       const int o = orb_oracle_descriptor_distance(a.ptr<unsigned char>(i), b.ptr<unsigned char>(i));
       REQUIRE(dist[i] == o && ORB_SLAM2::ORBmatcher::DescriptorDistance(a.row(i), b.row(i)) == o, "DescriptorDistance row %d", i);
+    }
+    // two extractors driven from two std::threads, like the stereo Frame constructor (src/Frame.cc:158-168)
+    {
+      ORB_SLAM2::ORBextractor exL(nf, 1.2f, 8, 20, 7), exR(nf, 1.2f, 8, 20, 7);
+      std::vector<cv::KeyPoint> kl, kr;
+      cv::Mat dl, dr;
+      bool same = true;
+      for (int round = 0; round < 5 && same; ++round) {
+        std::thread tl([&]() { exL(contiguous, cv::Mat(), kl, dl); });
+        std::thread tr([&]() { exR(right, cv::Mat(), kr, dr); });
+        tl.join();
+        tr.join();
+        same = kl.size() == bk[0].size() && kr.size() == bk[1].size() && dl.rows == bd[0].rows && dr.rows == bd[1].rows &&
+               std::memcmp(dl.ptr<unsigned char>(0), bd[0].ptr<unsigned char>(0), (size_t)dl.rows * 32) == 0 &&
+               std::memcmp(dr.ptr<unsigned char>(0), bd[1].ptr<unsigned char>(0), (size_t)dr.rows * 32) == 0;
+        for (size_t i = 0; same && i < kl.size(); ++i)
+          same = kl[i].pt.x == bk[0][i].pt.x && kl[i].pt.y == bk[0][i].pt.y && kl[i].angle == bk[0][i].angle && kl[i].octave == bk[0][i].octave;
+        for (size_t i = 0; same && i < kr.size(); ++i)
+          same = kr[i].pt.x == bk[1][i].pt.x && kr[i].pt.y == bk[1][i].pt.y && kr[i].angle == bk[1][i].angle && kr[i].octave == bk[1][i].octave;
+      }
+      REQUIRE(same, "left / right extractors on two threads differ from the batched call");
+      std::printf("two extractors on two std::threads: equal to the batched call\n");
     }
     // stereo Frame constructor in one call: keypoints as above, mvuRight / mvDepth equal to the oracle's ComputeStereoMatches
     {
