@@ -301,6 +301,29 @@ def bench_extract_e2e(ex, frames_host, steps, warmup, world):
     return ms, h2d, d2h, nk
 
 
+def bench_latency(ex, frames_host, iters=200):
+    """Per-call latency the way Frame::ExtractORB calls the extractor (src/Frame.cc:468-481): ONE image per call, pinned host buffers
+    in and out, wall clock around the public call. Reported beside the throughput numbers, not part of them."""
+    import torch
+    _, H, W = frames_host.shape
+    cap = ex.max_keypoints()
+    n = min(16, len(frames_host))
+    src = torch.from_numpy(frames_host[:n].copy()).pin_memory().numpy()
+    from orb_slam2_detailed_comments_b200 import KP_DTYPE
+    out = (torch.empty((1, cap, 28), dtype=torch.uint8).pin_memory().numpy().view(KP_DTYPE).reshape(1, cap),
+           torch.empty((1, cap, 32), dtype=torch.uint8).pin_memory().numpy())
+    for i in range(20):
+        ex.extract_batch(src[i % n:i % n + 1], out=out)
+    ts = []
+    for i in range(iters):
+        t0 = time.perf_counter()
+        ex.extract_batch(src[i % n:i % n + 1], out=out)
+        ts.append(time.perf_counter() - t0)
+    ts.sort()
+    return {"metric": "wall clock of one ORBextractor::operator() call (1 image, host in / host out)", "unit": "ms",
+            "median": 1e3 * ts[len(ts) // 2], "p99": 1e3 * ts[int(len(ts) * 0.99)], "calls": iters}
+
+
 def bench_stereo_e2e(ex, frames_host, steps, warmup, world, bf=386.1448, b=0.5372):
     """Secondary: the stereo Frame constructor (two operator() calls + Frame::ComputeStereoMatches, src/Frame.cc:158-168,
     880-1176) through orb_extract_stereo_batch with pinned host buffers; frames (2p, 2p+1) are treated as left / right."""
@@ -517,6 +540,11 @@ def run_b200(args):
     bow_voc, bow_base = _bow_inputs()
     b_ms, b_words = bench_bow(g_steps, args.warmup, world, bow_voc, bow_base)
     popc_peak = pkg.lib().orb_measure_popc_peak(local) if rank == 0 else 0.0
+    latency = None
+    if world == 1:
+        ex1 = pkg.ORBextractor(nf, 1.2, 8, 20, 7, device=local)   # its own handle: single-image workspaces
+        latency = bench_latency(ex1, frames)
+        ex1.close()
 
     if rank != 0:
         return
@@ -590,6 +618,8 @@ def run_b200(args):
     }
     if _NUMA:
         line["e2e"]["numa"] = _NUMA   # this rank's binding (rank 0); every rank binds to its own GPU's node
+    if world == 1:
+        line["latency"] = latency
     if world == 1 and not args.no_cpu:
         cores = _host_cores()
         n = 512   # ~20-30 core-seconds of CPU work
