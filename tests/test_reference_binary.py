@@ -6,6 +6,8 @@ What is the reference here and what is not: control flow, float/int arithmetic, 
 ORBextractor::operator() / ComputePyramid / ComputeKeyPointsOctTree / DistributeOctTree / IC_Angle / computeOrbDescriptor and of
 DBoW2's loadFromTextFile / transform are the reference's; the five OpenCV primitives under them are oracle/cv_primitives.cpp,
 which tests/test_oracle_golden.py pins bit-exact against the real cv2 4.13."""
+import os
+
 import numpy as np
 import pytest
 
@@ -144,3 +146,24 @@ def test_cuda_equals_reference_dbow2(tmp_path, vkw):
         for f, n in enumerate(sizes):
             gbow, gfv = pkg.ORBVocabulary.frame_maps(r, f)
             _check_bow(gbow, gfv, r["node"][f, :n], ref[f], voc[1] - levelsup)
+
+
+def test_avx2_timing_build_gives_the_same_output(tmp_path):
+    """bench.py's reference arm times oracle/_ref/orb_ref_extract_avx2 (-O3 -march=x86-64-v3, standing in for the reference's
+    -march=native): its output file must equal the plain build's byte for byte."""
+    import subprocess
+    fast = ref_binary.BIN + "_avx2"
+    if not os.access(fast, os.X_OK):
+        pytest.skip("oracle/_ref/orb_ref_extract_avx2 not built")
+    frames = synth.synth_batch(640, 480, 2, seed0=77, distinct=2)
+    fin = str(tmp_path / "in.bin")
+    ref_binary.write_input(fin, frames, 1000)
+    outs = []
+    for exe in (ref_binary.BIN, fast):
+        fout = str(tmp_path / (os.path.basename(exe) + ".out"))
+        r = subprocess.run([exe, fin, fout], capture_output=True)
+        if r.returncode != 0 and exe == fast:
+            pytest.skip("this host cannot run the AVX2 build")
+        assert r.returncode == 0
+        outs.append(open(fout, "rb").read())
+    assert outs[0] == outs[1]
