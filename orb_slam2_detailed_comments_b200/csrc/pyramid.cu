@@ -5,8 +5,17 @@
 // Border pixels are pure index remaps of interior pixels, so every padded output pixel is computed
 // directly from level l-1 (no second pass over the plane).
 #include <algorithm>
+#include <cstdlib>
 
 #include "orb_common.cuh"
+
+// Programmatic dependent launch (small passes only, see orb_launch_pyramid): the next kernel of the level chain may be scheduled while
+// this one drains; it blocks in orb_pdl_wait() until this grid has completed and its writes are visible. Both are no-ops for a
+// kernel launched the ordinary way. Every kernel of the chain waits before it reads OR exits, so completion stays transitive.
+__device__ __forceinline__ void orb_pdl_begin() {
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
 
 // Every plane is written together with its apron: columns [-4, cols + 4) and rows [-3, rows + 3) hold the
 // BORDER_REFLECT_101 extension of the PADDED image (what cv::GaussianBlur reads beyond it), so the blur kernel is branch-free.
@@ -19,6 +28,7 @@
 __global__ void __launch_bounds__(256) orb_pyr_level0_interior_kernel(const uint8_t* __restrict__ images, int step, long long image_stride,
                                                                       uint8_t* __restrict__ pyr, int c_lo, int c_hi,
                                                                       const __grid_constant__ OrbGeom g) {
+  orb_pdl_begin();
   const OrbLevel& L = g.lv[0];
   const int frame = blockIdx.z;
   const int c = c_lo + blockIdx.x * blockDim.x + threadIdx.x;
@@ -39,6 +49,7 @@ __global__ void __launch_bounds__(256) orb_pyr_level0_interior_kernel(const uint
 __global__ void __launch_bounds__(256) orb_pyr_level0_border_kernel(const uint8_t* __restrict__ images, int step, long long image_stride,
                                                                     uint8_t* __restrict__ pyr, int n_left, int c_hi, int n_edge,
                                                                     const __grid_constant__ OrbGeom g) {
+  orb_pdl_begin();
   const OrbLevel& L = g.lv[0];
   const int frame = blockIdx.z;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -62,6 +73,7 @@ __global__ void __launch_bounds__(256) orb_pyr_level0_border_kernel(const uint8_
 // Generic path (any scale factor): one thread = 4 adjacent padded output pixels, byte gathers.
 __global__ void __launch_bounds__(256) orb_pyr_resize_kernel(uint8_t* __restrict__ pyr, const ResizeTab* __restrict__ tabs,
                                                              int level, const __grid_constant__ OrbGeom g) {
+  orb_pdl_begin();
   const OrbLevel& D = g.lv[level];
   const OrbLevel& S = g.lv[level - 1];
   const int frame = blockIdx.z;
@@ -95,6 +107,7 @@ __global__ void __launch_bounds__(256) orb_pyr_resize_kernel(uint8_t* __restrict
 // the horizontal lerp (c0*s0 + c1*s1 with the 11-bit coefficient pair packed as 16-bit lanes).
 __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restrict__ pyr, const ResizeTab* __restrict__ tabs,
                                                               int level, const __grid_constant__ OrbGeom g) {
+  orb_pdl_begin();
   const OrbLevel& D = g.lv[level];
   const OrbLevel& S = g.lv[level - 1];
   const int frame = blockIdx.z;
@@ -144,9 +157,25 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
   }
 }
 
+template <typename... KArgs, typename... Args>
+static void launch_chain(void (*kern)(KArgs...), dim3 grd, dim3 blk, cudaStream_t st, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grd; cfg.blockDim = blk; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride, uint8_t* pyr, const ResizeTab* tabs,
                         const OrbGeom& g, int batch, cudaStream_t st, long long* launches, cudaEvent_t ev_input_consumed) {
   dim3 blk(32, 8);
+  // small passes (a Frame's one or two images) are a chain of launch latencies: overlap each launch with the tail of the previous
+  // kernel. Large passes keep ordinary launches: waiting CTAs would hold SM slots the other pass stream can use.
+  static const bool pdl_on = !getenv("ORB_B200_NO_PDL");
+  const bool pdl = pdl_on && batch <= 8;
+  bool first = true;
   {
     const OrbLevel& L = g.lv[0];
     const int nrows = L.rows + 2 * (ORB_APRON - 1);
@@ -159,23 +188,26 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
     const int n_left = std::min(c_lo, c_last + 1), n_edge = n_left + (c_last - hi_eff);
     if (n_int > 0) {
       dim3 grd((n_int + 31) / 32, (nrows + 7) / 8, batch);
-      orb_pyr_level0_interior_kernel<<<grd, blk, 0, st>>>(images, step, image_stride, pyr, c_lo, c_hi, g);
+      launch_chain(orb_pyr_level0_interior_kernel, grd, blk, st, false, images, step, image_stride, pyr, c_lo, c_hi, g);
+      first = false;
       ++*launches;
     }
     dim3 grd((nrows * n_edge * 4 + 255) / 256, 1, batch);
-    orb_pyr_level0_border_kernel<<<grd, 256, 0, st>>>(images, step, image_stride, pyr, n_left, hi_eff, n_edge, g);
+    launch_chain(orb_pyr_level0_border_kernel, grd, dim3(256), st, pdl && !first, images, step, image_stride, pyr, n_left, hi_eff, n_edge, g);
     ++*launches;
-    if (ev_input_consumed) cudaEventRecord(ev_input_consumed, st);   // only level 0 reads the input frames
+    // only level 0 reads the input frames (with dependent launches the record would break the kernel-to-kernel edge: it moves to the end)
+    if (ev_input_consumed && !pdl) cudaEventRecord(ev_input_consumed, st);
   }
   for (int l = 1; l < g.nlevels; ++l) {
     const OrbLevel& L = g.lv[l];
     if (L.pyr_fast) {
       dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 31) / 32, batch);
-      orb_pyr_resize4_kernel<<<grd, blk, 0, st>>>(pyr, tabs, l, g);
+      launch_chain(orb_pyr_resize4_kernel, grd, blk, st, pdl, pyr, tabs, l, g);
     } else {
       dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 7) / 8, batch);
-      orb_pyr_resize_kernel<<<grd, blk, 0, st>>>(pyr, tabs, l, g);
+      launch_chain(orb_pyr_resize_kernel, grd, blk, st, pdl, pyr, tabs, l, g);
     }
     ++*launches;
   }
+  if (ev_input_consumed && pdl) cudaEventRecord(ev_input_consumed, st);
 }
