@@ -15,15 +15,16 @@
 // Child slots: the first non-empty child reuses its parent's slot, so live slots == list size <= max(N+3, 4*nIni).
 #include "orb_common.cuh"
 
-#define QT_THREADS 256
+// CTA size NT: 256 threads for the usual levels (the kernel shares the SMs with the blur of the same pass and the FAST kernel of the
+// other pass stream: larger CTAs cost the KITTI step 3.5 %), 512 for large levels (4K: +11 % images/s), chosen by orb_launch_quadtree.
 #define QT_SORT_SMEM 2048
 
-template <typename T>
+template <int NT, typename T>
 __device__ T qt_block_scan_excl(T* a, int n, T* s_warp) {
   // in-place exclusive scan over a[0..n); every thread of the block calls it. Returns the total.
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   T carry = 0;
-  for (int base = 0; base < n; base += QT_THREADS) {
+  for (int base = 0; base < n; base += NT) {
     const int i = base + threadIdx.x;
     const T v = i < n ? a[i] : (T)0;
     T x = v;
@@ -35,7 +36,7 @@ __device__ T qt_block_scan_excl(T* a, int n, T* s_warp) {
     if (lane == 31) s_warp[warp] = x;
     __syncthreads();
     if (warp == 0) {
-      T w = lane < QT_THREADS / 32 ? s_warp[lane] : (T)0;
+      T w = lane < NT / 32 ? s_warp[lane] : (T)0;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const T y = __shfl_up_sync(0xffffffffu, w, o);
@@ -46,17 +47,18 @@ __device__ T qt_block_scan_excl(T* a, int n, T* s_warp) {
     __syncthreads();
     const T wo = warp ? s_warp[warp - 1] : (T)0;
     if (i < n) a[i] = carry + wo + x - v;
-    carry += s_warp[QT_THREADS / 32 - 1];
+    carry += s_warp[NT / 32 - 1];
     __syncthreads();
   }
   return carry;
 }
 
 // bitonic sort, descending, n2 = power of two >= n (padding zeros sort last)
+template <int NT>
 __device__ void qt_sort_desc(unsigned long long* a, int n2) {
   for (int k = 2; k <= n2; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < n2; i += QT_THREADS) {
+      for (int i = threadIdx.x; i < n2; i += NT) {
         const int ixj = i ^ j;
         if (ixj > i) {
           const unsigned long long x = a[i], y = a[ixj];
@@ -69,7 +71,8 @@ __device__ void qt_sort_desc(unsigned long long* a, int n2) {
   }
 }
 
-__global__ void __launch_bounds__(QT_THREADS)
+template <int NT>
+__global__ void __launch_bounds__(NT)
 orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_kp, QtScratch S,
                     uint32_t* __restrict__ kept /*[B][node_total] packed key*/, int* __restrict__ kept_cnt /*[B][nlevels]*/,
                     int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
@@ -107,7 +110,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
   const uint32_t* ckp = cell_kp + ((long long)frame * g.ncells_total + L.cell_base) * ORB_CELL_CAP;
   // scan cell counts in chunks, reusing `scan` storage is too small for 4K levels, so do a running carry
   int n = 0;
-  for (int base = 0; base < ncell; base += QT_THREADS) {
+  for (int base = 0; base < ncell; base += NT) {
     const int c = base + tid;
     const int v = c < ncell ? ccount[c] : 0;
     int x = v;
@@ -119,7 +122,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
     if (lane == 31) s_warp32[warp] = x;
     __syncthreads();
     if (warp == 0) {
-      int w = lane < QT_THREADS / 32 ? s_warp32[lane] : 0;
+      int w = lane < NT / 32 ? s_warp32[lane] : 0;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const int y = __shfl_up_sync(0xffffffffu, w, o);
@@ -135,7 +138,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
       for (int e = 0; e < v; ++e)
         if (off + e < L.raw_cap) key[off + e] = src[e];
     }
-    n += s_warp32[QT_THREADS / 32 - 1];
+    n += s_warp32[NT / 32 - 1];
     __syncthreads();
   }
   if (tid == 0) {
@@ -151,11 +154,11 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
   // ---- roots (:1060-1129)
   const int nIni = L.nIni;
   const float hX = L.hX;
-  for (int i = tid; i < L.node_cap; i += QT_THREADS) { ncount[i] = 0; pidx[i] = -1; }
+  for (int i = tid; i < L.node_cap; i += NT) { ncount[i] = 0; pidx[i] = -1; }
   __syncthreads();
-  for (int i = tid; i < nIni; i += QT_THREADS)
+  for (int i = tid; i < nIni; i += NT)
     bbox[i] = make_int4((int)__fmul_rn(hX, (float)i), 0, (int)__fmul_rn(hX, (float)(i + 1)), L.maxBY - ORB_MIN_BORDER);
-  for (int i = tid; i < n; i += QT_THREADS) {
+  for (int i = tid; i < n; i += NT) {
     const int r = (int)__fdiv_rn((float)(key[i] & 0xfffu), hX);
     knode[i] = r;
     atomicAdd(&ncount[r], 1);
@@ -180,14 +183,14 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
   bool phase2 = false;
   while (k > 0) {
     // A: register parents
-    for (int r = tid; r < k; r += QT_THREADS) {
+    for (int r = tid; r < k; r += NT) {
       pidx[par[r]] = r;
       ccnt[4 * r] = 0; ccnt[4 * r + 1] = 0; ccnt[4 * r + 2] = 0; ccnt[4 * r + 3] = 0;
     }
     if (tid == 0) { s_cut = k; s_ncand = 0; }
     __syncthreads();
     // B: classify keys of parents (DivideNode :968-1022)
-    for (int i = tid; i < n; i += QT_THREADS) {
+    for (int i = tid; i < n; i += NT) {
       const int nd = knode[i];
       const int r = pidx[nd];
       if (r >= 0) {
@@ -202,17 +205,17 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
     }
     __syncthreads();
     // C/D: scan nonempty / multi-key child counts over P, find the phase-2 cut
-    for (int r = tid; r < k; r += QT_THREADS) {
+    for (int r = tid; r < k; r += NT) {
       unsigned ne = 0, nc = 0;
 #pragma unroll
       for (int c = 0; c < 4; ++c) { const int v = ccnt[4 * r + c]; ne += v > 0; nc += v > 1; }
       scan[r] = (unsigned long long)ne | ((unsigned long long)nc << 32);
     }
     __syncthreads();
-    const unsigned long long tot = qt_block_scan_excl<unsigned long long>(scan, k, s_warp64);
+    const unsigned long long tot = qt_block_scan_excl<NT, unsigned long long>(scan, k, s_warp64);
     int kc = k;
     if (phase2) {
-      for (int r = tid; r < k; r += QT_THREADS) {
+      for (int r = tid; r < k; r += NT) {
         unsigned ne = 0;
 #pragma unroll
         for (int c = 0; c < 4; ++c) ne += ccnt[4 * r + c] > 0;
@@ -227,7 +230,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
     if (kc == k) { T = (int)(unsigned)(tot & 0xffffffffu); ncand = (int)(tot >> 32); }
     else { const unsigned long long e = scan[kc]; T = (int)(unsigned)(e & 0xffffffffu); ncand = (int)(e >> 32); }
     // E: create children
-    for (int r = tid; r < kc; r += QT_THREADS) {
+    for (int r = tid; r < kc; r += NT) {
       const int p = par[r];
       const int4 b = bbox[p];
       const int hx = (b.z - b.x + 1) >> 1, hy = (b.w - b.y + 1) >> 1;
@@ -258,7 +261,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
       return;
     }
     // F: move keys to their child nodes
-    for (int i = tid; i < n; i += QT_THREADS) {
+    for (int i = tid; i < n; i += NT) {
       const int nd = knode[i];
       const int r = pidx[nd];
       if (r >= 0 && r < kc) knode[i] = cslot[4 * r + kchild[i]];
@@ -266,7 +269,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
     // G: survivors keep their relative order behind the new children
     unsigned long long* sflag = scan;   // reuse (E is done with it after the barrier below)
     __syncthreads();
-    for (int q = tid; q < m; q += QT_THREADS) {
+    for (int q = tid; q < m; q += NT) {
       const int r = pidx[ordOld[q]];
       sflag[q] = (r >= 0 && r < kc) ? 0ull : 1ull;
     }
@@ -276,15 +279,15 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
       // (each element is touched by the same thread before and after: index q = base + tid)
     }
     // scan in place; recover flag as (next - cur) is not possible for the last one, so re-derive from pidx
-    qt_block_scan_excl<unsigned long long>(sflag, m, s_warp64);
-    for (int q = tid; q < m; q += QT_THREADS) {
+    qt_block_scan_excl<NT, unsigned long long>(sflag, m, s_warp64);
+    for (int q = tid; q < m; q += NT) {
       const int nd = ordOld[q];
       const int r = pidx[nd];
       if (!(r >= 0 && r < kc)) ordNew[T + (int)sflag[q]] = nd;
     }
     __syncthreads();
     // H: unregister parents
-    for (int r = tid; r < k; r += QT_THREADS) pidx[par[r]] = -1;
+    for (int r = tid; r < k; r += NT) pidx[par[r]] = -1;
     const int m_new = T + (m - kc);
     __syncthreads();
     { int* t = ordOld; ordOld = ordNew; ordNew = t; }
@@ -301,26 +304,26 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
       while (n2 < k) n2 <<= 1;
       unsigned long long* buf = n2 <= QT_SORT_SMEM ? s_sort : cand;
       if (buf == s_sort) {
-        for (int i = tid; i < n2; i += QT_THREADS) s_sort[i] = i < k ? cand[i] : 0ull;
+        for (int i = tid; i < n2; i += NT) s_sort[i] = i < k ? cand[i] : 0ull;
       } else {
-        for (int i = k + tid; i < n2; i += QT_THREADS) cand[i] = 0ull;
+        for (int i = k + tid; i < n2; i += NT) cand[i] = 0ull;
       }
       __syncthreads();
-      qt_sort_desc(buf, n2);
-      for (int r = tid; r < k; r += QT_THREADS) par[r] = (int)(buf[r] & 0xfffffu);
+      qt_sort_desc<NT>(buf, n2);
+      for (int r = tid; r < k; r += NT) par[r] = (int)(buf[r] & 0xfffffu);
     } else {
-      for (int r = tid; r < k; r += QT_THREADS) par[r] = (int)(cand[k - 1 - r] & 0xfffffu);   // list order = reverse creation
+      for (int r = tid; r < k; r += NT) par[r] = (int)(cand[k - 1 - r] & 0xfffffu);   // list order = reverse creation
     }
     __syncthreads();
   }
 
   // ---- per node keep the best key (:1387-1413), output in list order
-  for (int q = tid; q < m; q += QT_THREADS) best[ordOld[q]] = 0u;
+  for (int q = tid; q < m; q += NT) best[ordOld[q]] = 0u;
   __syncthreads();
-  for (int i = tid; i < n; i += QT_THREADS)
+  for (int i = tid; i < n; i += NT)
     atomicMax(&best[knode[i]], ((key[i] >> 24) << 24) | (0xffffffu - (unsigned)i));
   __syncthreads();
-  for (int q = tid; q < m; q += QT_THREADS) {
+  for (int q = tid; q < m; q += NT) {
     const unsigned b = best[ordOld[q]];
     kept_out[q] = key[0xffffffu - (b & 0xffffffu)];
   }
@@ -329,6 +332,9 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
 
 void orb_launch_quadtree(const int* cell_cnt, const uint32_t* cell_kp, const QtScratch& S, uint32_t* kept, int* kept_cnt,
                          int* err_flag, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
-  orb_quadtree_kernel<<<batch * g.nlevels, QT_THREADS, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
+  // large levels (4K: 9017 cells, quota 1737 at level 0) are a long chain of rounds over tens of thousands of keys: twice the threads
+  const bool big = g.lv[0].nCols * g.lv[0].nRows >= 2048 || g.lv[0].quota >= 1024;
+  if (big) orb_quadtree_kernel<512><<<batch * g.nlevels, 512, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
+  else orb_quadtree_kernel<256><<<batch * g.nlevels, 256, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
   ++*launches;
 }
