@@ -15,9 +15,13 @@
 // Child slots: the first non-empty child reuses its parent's slot, so live slots == list size <= max(N+3, 4*nIni).
 #include "orb_common.cuh"
 
-// CTA size NT: 256 threads for the usual levels (the kernel shares the SMs with the blur of the same pass and the FAST kernel of the
-// other pass stream: larger CTAs cost the KITTI step 3.5 %), 512 for large levels (4K: +11 % images/s), chosen by orb_launch_quadtree.
+// CTA size NT: 192 threads for the usual levels (the kernel shares the SMs with the blur of the same pass and the FAST kernel of the
+// other pass stream: 512-thread CTAs cost the KITTI step 3.5 %, 192 instead of 256 gains 0.8 % / TUM 1.7 %), 512 for large levels
+// (4K: +11 % images/s) and for small passes (per-call latency), chosen by orb_launch_quadtree.
 #define QT_SORT_SMEM 2048
+#ifndef QT_SMALL
+#define QT_SMALL 192
+#endif
 
 template <int NT, typename T>
 __device__ T qt_block_scan_excl(T* a, int n, T* s_warp) {
@@ -333,8 +337,9 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
 void orb_launch_quadtree(const int* cell_cnt, const uint32_t* cell_kp, const QtScratch& S, uint32_t* kept, int* kept_cnt,
                          int* err_flag, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
   // large levels (4K: 9017 cells, quota 1737 at level 0) are a long chain of rounds over tens of thousands of keys: twice the threads
-  const bool big = g.lv[0].nCols * g.lv[0].nRows >= 2048 || g.lv[0].quota >= 1024;
+  // ...and so are the few CTAs of a small pass (a Frame's one or two images: latency matters and the SMs are idle anyway)
+  const bool big = g.lv[0].nCols * g.lv[0].nRows >= 2048 || g.lv[0].quota >= 1024 || batch <= 8;
   if (big) orb_quadtree_kernel<512><<<batch * g.nlevels, 512, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
-  else orb_quadtree_kernel<256><<<batch * g.nlevels, 256, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
+  else orb_quadtree_kernel<QT_SMALL><<<batch * g.nlevels, QT_SMALL, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
   ++*launches;
 }
