@@ -19,9 +19,7 @@
 // other pass stream: 512-thread CTAs cost the KITTI step 3.5 %, 192 instead of 256 gains 0.8 % / TUM 1.7 %), 512 for large levels
 // (4K: +11 % images/s) and for small passes (per-call latency), chosen by orb_launch_quadtree.
 #define QT_SORT_SMEM 2048
-#ifndef QT_SMALL
-#define QT_SMALL 192
-#endif
+#define QT_SMALL 192   // CTA size for the usual levels (register caps below the natural 56 were measured too: no gain)
 
 template <int NT, typename T>
 __device__ T qt_block_scan_excl(T* a, int n, T* s_warp) {
