@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Host-to-host throughput of the LocalMapping / LoopClosing matchers built on the guided-search kernels:
 ORBmatcher::SearchForTriangulation (orb_search_for_triangulation) and the candidate search of ORBmatcher::Fuse (orb_fuse_search),
-next to the CPU oracle on all host cores (ThreadPool over pairs; the ctypes calls release the GIL). Prints one JSON line.
-usage: python tools/matcher_bench.py [--pairs 256] [--features 2000] [--steps 5]"""
+next to the CPU oracle (the checker and CPU baseline here: this script lives under tests/ because it runs the oracle) on all host cores (ThreadPool over pairs; the ctypes calls release the GIL). Prints one JSON line.
+usage: python tests/matcher_bench.py [--pairs 256] [--features 2000] [--steps 5]"""
 import argparse
 import json
 import os
