@@ -9,7 +9,7 @@
 #include <thread>
 #include <vector>
 
-#include "../oracle/orb_oracle.h"
+#include "../../oracle/orb_oracle.h"
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
 #include "ORBVocabulary.h"

@@ -2,7 +2,7 @@
 (include/ORBextractor.h:80-250, include/ORBmatcher.h:54-62, 223-225) over the C ABI.
 
 CPU part: the layer builds, exports the reference's symbols and needs nothing but liborb_b200.so.
-GPU part: cpp/test_dropin runs operator(), ExtractBatch, mvImagePyramid and the matcher against the oracle, bit-exact."""
+GPU part: tests/cpp/test_dropin runs operator(), ExtractBatch, mvImagePyramid and the matcher against the oracle, bit-exact."""
 import os
 import subprocess
 
@@ -17,6 +17,7 @@ def _build():
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "orb_slam2_detailed_comments_b200", "csrc")], stdout=subprocess.DEVNULL)
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
     subprocess.check_call(["make", "-C", CPP], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "tests", "cpp")], stdout=subprocess.DEVNULL)
 
 
 def test_dropin_builds_and_exports_reference_symbols():
@@ -38,7 +39,7 @@ def test_dropin_builds_and_exports_reference_symbols():
 @pytest.mark.parametrize("shape", [(640, 480, 1000), (1241, 376, 2000)])
 def test_dropin_matches_oracle_on_gpu(tmp_path, shape):
     from orb_slam2_detailed_comments_b200 import synth
-    exe = os.path.join(CPP, "test_dropin")
+    exe = os.path.join(ROOT, "tests", "cpp", "test_dropin")
     if not os.path.exists(exe):
         _build()
     W, H, nf = shape
