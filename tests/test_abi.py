@@ -36,12 +36,15 @@ def test_struct_layouts():
 
 
 def test_product_never_imports_oracle():
-    pkg = os.path.join(ROOT, "orb_slam2_detailed_comments_b200")
-    for dirpath, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".cc", "Makefile")):
-                txt = open(os.path.join(dirpath, f), errors="replace").read()
-                assert "oracle_py" not in txt and "liborb_oracle" not in txt and "orb_oracle.h" not in txt, f
+    """The package, the C++ drop-in layer, the public headers and the tools never import, include or link the oracle
+    (only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may)."""
+    for top in ("orb_slam2_detailed_comments_b200", "cpp", "include", "tools"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".cc", "Makefile")):
+                    txt = open(os.path.join(dirpath, f), errors="replace").read()
+                    for needle in ("oracle_py", "liborb_oracle", "orb_oracle.h", "lorb_oracle", "from oracle", "import oracle"):
+                        assert needle not in txt, (os.path.join(top, f), needle)
 
 
 def test_no_cpu_fallback_without_device():
