@@ -1,34 +1,45 @@
 // Per-cell FAST-9/16 with the iniThFAST / minThFAST retry: the cell loop of
 // ORBextractor::ComputeKeyPointsOctTree (src/ORBextractor.cc:1465-1548) and cv::FAST(cell, th, true).
 //
-// cornerScore is threshold-free (S = max(A,B) - 1) and "corner at T" <=> S >= T, so ONE score pass serves both
-// thresholds. The detection domains of the reference's 30-px cells ([ini+3, ini+cell+3) in x and y) tile the
-// level without overlap, so S is computed once per pixel; only the 3x3 NMS is per cell (neighbours outside the
-// cell's detection window count as 0, because the reference runs cv::FAST on the cell sub-image). A cell emits
-// its NMS survivors with S >= ini, or, if there are none, those with S >= min, row-major (cv::FAST's order).
+// cornerScore is threshold-free (S = max(A,B) - 1) and "corner at T" <=> S >= T, so ONE score serves both thresholds.
+// The detection domains of the reference's 30-px cells ([ini+3, ini+cell+3) in x and y) tile the level without
+// overlap, so S is computed once per pixel; only the 3x3 NMS is per cell (neighbours outside the cell's detection
+// window count as 0, because the reference runs cv::FAST on the cell sub-image). A cell emits its NMS survivors with
+// S >= ini, or, if there are none, those with S >= min, row-major (cv::FAST's order).
 //
-// One CTA = one cell row x up to fast_G cells (a band of <= 248 x hCell detection pixels):
-//   1. the band window (+3 px halo) is staged in shared memory with 16-byte loads;
-//   2. quick reject, 4 pixels per thread with byte-SIMD (VABSDIFF4 + carry-free byte compares): a 9-arc always
-//      holds one of {up, down} and one of {left, right}, so min(max|d_ud|, max|d_lr|) > minTh is necessary for
-//      S >= minTh; a thread keeps its survivors as bit masks and one warp scan compacts them into the warp's candidate list;
-//   3. candidates are scored 32 at a time with full lanes. The dark and the bright arc tests share one instruction
-//      stream: ring pixel r_k becomes the 16-bit lane pair [256 + v - r_k, 256 - v + r_k] (one IMAD) and
-//      max_arcs(min_9) of both lanes is 16 + 16 VIMNMX3.U16x2 + an 8-op max tree. Corners (S >= minTh) are
-//      compacted in place to the front of the warp's list;
-//   4. each corner does the 3x3 NMS on the shared score plane (cell-window masked) and sets its bit in the
-//      min / ini survivor bit planes;
-//   5. per cell (one warp each, lane = row): 64-bit row masks from the bit planes, popc + warp scan give every
-//      survivor its row-major rank; ini/min selection by the cell's ini count.
+// One CTA = one cell row x up to fast_G cells (a band of <= 219 x hCell detection pixels), 256 threads:
+//   1. ONE thread issues a TMA box load (cp.async.bulk.tensor.3d, per-level tensor map over [frame][row][byte]) of the
+//      band window (+3 px halo, 256-byte rows) into shared memory and arms an mbarrier; the others meanwhile clear the
+//      score plane / survivor planes and build the column tables (cell index, cell-edge flags, detection mask);
+//   2. ONE sweep over the window, 8 pixels per thread with byte-SIMD (VABSDIFF4 + carry-free byte compares): a 9-arc
+//      always holds one of {up, down} and one of {left, right}, so min(max|d_ud|, max|d_lr|) > T is necessary for
+//      S >= T. The four |d| words are compared against BOTH thresholds while they are in registers: a thread keeps
+//      "passes at iniTh" and "passes at minTh only" as two bit masks (<= 64 bits each: its <= 8 rows x 8 pixels);
+//   3. the iniTh candidates are compacted with one warp scan and scored 32 at a time with full lanes. The dark and the
+//      bright arc tests share one instruction stream: ring pixel r_k becomes the 16-bit lane pair
+//      [256 + v - r_k, 256 - v + r_k] (one IMAD) and max_arcs(min_9) of both lanes is 16 + 16 VIMNMX3.U16x2 + an
+//      8-op max tree. Corners (S >= minTh) are compacted in place to the front of the warp's list;
+//   4. 3x3 NMS of the corners with S >= iniTh (cell-edge flags from the column table) -> per-cell 64-bit survivor rows
+//      + a per-cell "has an ini survivor" flag;
+//   5. if a cell of the band has no ini survivor (:1521), the minTh-only bits of step 2 inside those cells are
+//      compacted and scored (no second sweep), and the NMS runs over every corner of those cells;
+//   6. per cell (one warp each, lane = row pair): popc + warp scan give every survivor its row-major rank.
 #include <algorithm>
 #include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <cuda.h>
+
 #include "orb_common.cuh"
 
 #define FAST_THREADS 256
 #define FAST_WARPS 8
 #define FAST_WP 256      // window row pitch in smem: 16 B front pad + 15 alignment + ORB_FAST_TILE_W (219) + 6 halo = 256
 #define FAST_SP 240      // score plane row pitch: 15 + 219 + 4 <= 240
-#define FAST_BP 11       // survivor bit plane row pitch in words (window columns < 288 -> 9 words, +2 for the 64-bit extract)
+#define FAST_MAXC 8      // cells per band (219 / 30 = 7) rounded up
+
+struct OrbFastMaps { CUtensorMap m[ORB_MAX_LEVELS]; };
 
 // cornerScore (OpenCV fast_score.cpp, 16-pixel ring, K = 8): S = max(max_arcs min_9(v - r), max_arcs min_9(r - v)) - 1,
 // clamped at 0. Lanes of every 32-bit value: lo = 256 + (v - r), hi = 256 + (r - v), both in [1, 511].
@@ -44,82 +55,45 @@ __device__ __forceinline__ int fast_score(const uint8_t* __restrict__ p) {
   e[12] = p[-3];          e[13] = p[wp - 3];      e[14] = p[2 * wp - 2];  e[15] = p[3 * wp - 1];
 #pragma unroll
   for (int k = 0; k < 16; ++k) e[k] = base + e[k] * 0xffffu;   // (r << 16) - r: no borrow, lo >= 1
-  unsigned m3[16], m9[16];
+  // max over the 16 arcs of min over 9 = max over even k of min(min(e[k+1 .. k+8]), max(e[k], e[k+9])):
+  // arcs k and k+1 share e[k+1 .. k+8]
+  unsigned p2[8];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) m3[k] = __vimin3_u16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+  for (int j = 0; j < 8; ++j) p2[j] = __vimin3_u16x2(e[2 * j + 1], e[(2 * j + 2) & 15], 0xffffffffu);   // min(e[2j+1], e[2j+2])
+  unsigned M[8];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) m9[k] = __vimin3_u16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
-  const unsigned a0 = __vimax3_u16x2(m9[0], m9[1], m9[2]), a1 = __vimax3_u16x2(m9[3], m9[4], m9[5]),
-                 a2 = __vimax3_u16x2(m9[6], m9[7], m9[8]), a3 = __vimax3_u16x2(m9[9], m9[10], m9[11]),
-                 a4 = __vimax3_u16x2(m9[12], m9[13], m9[14]);
-  const unsigned b = __vimax3_u16x2(__vimax3_u16x2(a0, a1, a2), __vimax3_u16x2(a3, a4, m9[15]), 0u);
+  for (int j = 0; j < 8; ++j) {   // even k = 2j: shared part = p2[j], p2[j+1], p2[j+2], p2[j+3]
+    const unsigned t = __vimin3_u16x2(p2[j], p2[(j + 1) & 7], p2[(j + 2) & 7]);
+    const unsigned u = __vimax3_u16x2(e[2 * j], e[(2 * j + 9) & 15], 0u);
+    M[j] = __vimin3_u16x2(t, p2[(j + 3) & 7], u);
+  }
+  const unsigned a0 = __vimax3_u16x2(M[0], M[1], M[2]), a1 = __vimax3_u16x2(M[3], M[4], M[5]);
+  const unsigned b = __vimax3_u16x2(__vimax3_u16x2(a0, a1, M[6]), M[7], 0u);
   const int s = (int)max(b & 0xffffu, b >> 16) - 257;
   return max(s, 0);
 }
 
-// per-byte a > t (bit 7 of each result byte), t <= 126: ((a & 0x7f) | 0x80) - (t + 1) never borrows across bytes
-__device__ __forceinline__ unsigned fast_gt4(unsigned a, unsigned t1) {
-  return (((a & 0x7f7f7f7fu) | 0x80808080u) - t1) | a;
+// bit 7 of each byte: a > t. SMALL (t <= 126): A = (a & 0x7f) | 0x80 is shared by both thresholds, (A - (t + 1)) | a never borrows
+// across bytes. Otherwise the generic video intrinsic.
+template <bool SMALL_TH>
+__device__ __forceinline__ void fast_gt2(unsigned a, unsigned ti, unsigned tm, unsigned& gi, unsigned& gm) {
+  if (SMALL_TH) {
+    const unsigned A = (a & 0x7f7f7f7fu) | 0x80808080u;
+    gi = A - ti;   // ti, tm = (t + 1) * 0x01010101
+    gm = A - tm;
+  } else {
+    gi = __vcmpgtu4(a, ti);   // ti, tm = t * 0x01010101
+    gm = __vcmpgtu4(a, tm);
+  }
 }
 
-// Quick reject + compaction + scoring for the rows row0, row0 + FAST_WARPS, row0 + 2 * FAST_WARPS, ... < row1 of one warp (rows are
-// dealt round-robin to the warps: a textured blob spans adjacent rows, so every warp gets a share of its candidates and the
-// barrier after the scoring does not wait for one loaded warp).
-//   SECOND == false: candidates = pixels passing the compass test at iniTh (superset of all S >= iniTh);
-//   SECOND == true : candidates = pixels passing at minTh but not at iniTh (not scored yet), in the columns marked in `need`.
-// Candidate codes go to list[start ..], corners (S >= minTh) are compacted in place to list[start ..] as (y << 9) | x and
-// their score is written to the score plane. Returns the number of corners appended.
-template <bool SMALL_TH, bool SECOND>
-__device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint8_t* __restrict__ sc, const uint8_t* __restrict__ need,
-                                           uint16_t* __restrict__ list, int start, int row0, int row1, int qbase, int nq, int lane,
-                                           int ini_th, int min_th) {
-  const unsigned thi4 = (unsigned)ini_th * 0x01010101u, ti1 = thi4 + 0x01010101u;
-  const unsigned thm4 = (unsigned)min_th * 0x01010101u, tm1 = thm4 + 0x01010101u;
+// The candidates of one warp (bit masks cand[2] of every lane: byte (ri & 3) of cand[ri >> 2] = the 8 pixels of group
+// (lane + 5 * ri) & 31 in row warp + 8 * ri) go to list[start ..] as codes lane:5 | bit:6, are scored 32 at a time, and the corners
+// (S >= minTh) are compacted in place to list[start ..] as (y << 9) | x with their score written to the score plane.
+// Returns the number of corners appended.
+__device__ __forceinline__ int fast_score_candidates(const unsigned (&cand)[2], const uint8_t* __restrict__ win, uint8_t* __restrict__ sc,
+                                                     uint16_t* __restrict__ list, int start, int warp, int qbase, int lane, int min_th) {
   const uint32_t lt = (1u << lane) - 1u;
-  // candidate bits of this thread: byte (ri & 3) of cand[ri >> 2] = the 8 pixels of group (lane + 5*ri) & 31 in row row0 + 8*ri
-  // (a tile row is <= 29 aligned groups of 8 pixels: one pass per row). The per-row rotation spreads a textured blob
-  // (candidates cluster in 2-D) over many lanes.
-  unsigned cand[2] = {0u, 0u};
-  for (int ri = 0; row0 + FAST_WARPS * ri < row1; ++ri) {
-    const int y = row0 + FAST_WARPS * ri;
-    const int o = (lane + 5 * ri) & 31;
-    if (o < nq) {
-      const int x = qbase + 8 * o;
-      const uint2 colmask = *reinterpret_cast<const uint2*>(need + x);   // bit 7 of byte k: column x + k takes part
-      if (colmask.x | colmask.y) {
-        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + x;
-        const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c3 = *reinterpret_cast<const unsigned*>(row + 8);
-        const uint2 c = *reinterpret_cast<const uint2*>(row);
-        const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const uint2*>(row + 3 * FAST_WP);
-        unsigned pass[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const unsigned c1 = h ? c.y : c.x;
-          const unsigned lf = h ? __byte_perm(c.x, c.y, 0x4321) : __byte_perm(c0, c.x, 0x4321);
-          const unsigned rt = h ? __byte_perm(c.y, c3, 0x6543) : __byte_perm(c.x, c.y, 0x6543);
-          const unsigned au = __vabsdiffu4(c1, h ? up.y : up.x), ad = __vabsdiffu4(c1, h ? dn.y : dn.x), al = __vabsdiffu4(c1, lf),
-                         ar = __vabsdiffu4(c1, rt);
-          unsigned ps;
-          if (SMALL_TH) {
-            ps = (fast_gt4(au, SECOND ? tm1 : ti1) | fast_gt4(ad, SECOND ? tm1 : ti1)) &
-                 (fast_gt4(al, SECOND ? tm1 : ti1) | fast_gt4(ar, SECOND ? tm1 : ti1));
-            if (SECOND) ps &= ~((fast_gt4(au, ti1) | fast_gt4(ad, ti1)) & (fast_gt4(al, ti1) | fast_gt4(ar, ti1)));
-          } else {
-            ps = (__vcmpgtu4(au, SECOND ? thm4 : thi4) | __vcmpgtu4(ad, SECOND ? thm4 : thi4)) &
-                 (__vcmpgtu4(al, SECOND ? thm4 : thi4) | __vcmpgtu4(ar, SECOND ? thm4 : thi4));
-            if (SECOND) ps &= ~((__vcmpgtu4(au, thi4) | __vcmpgtu4(ad, thi4)) & (__vcmpgtu4(al, thi4) | __vcmpgtu4(ar, thi4)));
-          }
-          pass[h] = ps & (h ? colmask.y : colmask.x) & 0x80808080u;
-        }
-        // bits 7, 15, 23, 31 of each half -> one nibble each (the partial products never carry)
-        const unsigned bits8 = ((pass[0] * 0x204081u) >> 28) | (((pass[1] * 0x204081u) >> 28) << 4);
-        const unsigned b = bits8 << ((8 * ri) & 31);
-        if (ri < 4) cand[0] |= b; else cand[1] |= b;
-      }
-    }
-  }
-  // one warp scan places every thread's candidates in the warp's list (order is irrelevant). Entry = lane:5 | ri:3 | k:3,
-  // decoded by full warps in the scoring loop
   int cnt;
   {
     const int c = __popc(cand[0]) + __popc(cand[1]);
@@ -142,7 +116,6 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
     }
   }
   __syncwarp();
-  // score the candidates, 32 per step
   int ncorner = 0;
   for (int c0 = 0; c0 < cnt; c0 += 32) {
     const int i = c0 + lane;
@@ -151,7 +124,7 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
       const int code = list[start + i];
       const int ri = (code >> 3) & 7;
       const int o = ((code >> 6) + 5 * ri) & 31;
-      e = ((row0 + FAST_WARPS * ri) << 9) | (qbase + 8 * o + (code & 7));
+      e = ((warp + FAST_WARPS * ri) << 9) | (qbase + 8 * o + (code & 7));
       s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
     }
     const bool corner = s >= min_th;
@@ -166,49 +139,61 @@ __device__ __forceinline__ int fast_detect(const uint8_t* __restrict__ win, uint
   return ncorner;
 }
 
-// 3x3 NMS of the corners list[0 .. n) against their neighbours inside the same cell's detection window.
-//   SECOND == false: corners with S >= iniTh -> plane `pl` (ini survivors);
-//   SECOND == true : corners in the columns marked in `need` (cells that found no ini survivor) -> plane `pl` (min survivors).
+// 3x3 NMS of the corners list[0 .. n) against their neighbours inside the same cell's detection window (coltab: cell:3 | left edge:1 |
+// right edge:1 | column inside the cell:6 per window column). Survivors set their bit in the cell's 64-bit row of plane `pl`.
+//   SECOND == false: corners with S >= iniTh, and the cell is flagged in hasini;
+//   SECOND == true : corners of the cells without an ini survivor.
 template <bool SECOND>
-__device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const uint8_t* __restrict__ need, const uint16_t* __restrict__ list,
-                                         int n, int lane, uint32_t* __restrict__ pl, int wCell, unsigned inv, int xa, int xlim, int ini_th) {
+__device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const uint16_t* __restrict__ coltab, uint8_t* __restrict__ hasini,
+                                         const uint16_t* __restrict__ list, int n, int lane, unsigned long long* __restrict__ pl, int prow,
+                                         int ini_th) {
   for (int i = lane; i < n; i += 32) {
     const int e = list[i];
     const int y = e >> 9, x = e & 511;
     const uint8_t* q = sc + (y + 1) * FAST_SP + x;
     const int s = q[0];
-    if (SECOND ? (need[x] == 0) : (s < ini_th)) continue;
-    const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);
-    const unsigned r = p - __umulhi(p, inv) * (unsigned)wCell;   // column inside the cell's detection window (inv = 2^32 / wCell + 1)
-    bool ok = s > q[-FAST_SP] && s > q[FAST_SP];
-    if (r > 0) ok = ok && s > q[-1] && s > q[-FAST_SP - 1] && s > q[FAST_SP - 1];
-    if ((int)r < wCell - 1 && x + 1 < xlim) ok = ok && s > q[1] && s > q[-FAST_SP + 1] && s > q[FAST_SP + 1];
-    if (ok) atomicOr(&pl[y * FAST_BP + (x >> 5)], 1u << (x & 31));
+    const unsigned ct = coltab[x + 16];
+    const int cl = ct & 7;
+    if (SECOND ? (hasini[cl] != 0) : (s < ini_th)) continue;
+    int m = max((int)q[-FAST_SP], (int)q[FAST_SP]);
+    if (!(ct & 8u)) m = max(m, __vimax3_s32((int)q[-1], (int)q[-FAST_SP - 1], (int)q[FAST_SP - 1]));
+    if (!(ct & 16u)) m = max(m, __vimax3_s32((int)q[1], (int)q[-FAST_SP + 1], (int)q[FAST_SP + 1]));
+    if (s > m) {
+      const unsigned r = ct >> 5;
+      atomicOr(reinterpret_cast<unsigned*>(pl + cl * prow + y) + (r >> 5), 1u << (r & 31));
+      if (!SECOND) hasini[cl] = 1;
+    }
   }
 }
 
-template <bool SMALL_TH>   // SMALL_TH: iniTh <= 126 (carry-free byte compares); otherwise the generic video intrinsic
+__device__ __forceinline__ unsigned fast_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+template <bool SMALL_TH, bool TMA>   // SMALL_TH: iniTh <= 126 (carry-free byte compares); TMA: window by one bulk tensor copy, else per-thread cp.async
 __global__ void __launch_bounds__(FAST_THREADS)
-orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt, uint32_t* __restrict__ cell_kp,
-                     int* __restrict__ err_flag, int win_rows, int sc_rows, int row_cap, const __grid_constant__ OrbGeom g) {
-  extern __shared__ __align__(16) uint8_t smem[];
+orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ tiles, int* __restrict__ cell_cnt,
+                     uint32_t* __restrict__ cell_kp, int* __restrict__ err_flag, int win_rows, int sc_rows, int row_cap,
+                     const __grid_constant__ OrbGeom g, const __grid_constant__ OrbFastMaps maps) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int prow = (sc_rows - 1) & ~1;                    // survivor rows per cell, even (sc_rows - 2 rounded up)
   uint8_t* win = smem;                                    // [win_rows][FAST_WP], pixel x at column 16 + x
   uint8_t* sc = win + win_rows * FAST_WP;                 // [sc_rows][FAST_SP], score of domain row y at row y + 1
-  uint32_t* pl_min = reinterpret_cast<uint32_t*>(sc + sc_rows * FAST_SP);   // [sc_rows - 2][FAST_BP] NMS survivors, S >= minTh
-  uint32_t* pl_ini = pl_min + (sc_rows - 2) * FAST_BP;                       //                         S >= iniTh
-  uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + (sc_rows - 2) * FAST_BP);   // [max_h][row_cap], a warp's rows are contiguous
-  uint8_t* need = reinterpret_cast<uint8_t*>(lists + (sc_rows - 2) * row_cap);        // [FAST_WP] 0x80 = column takes part in the pass
-  __shared__ int s_retry;
+  unsigned long long* pl_min = reinterpret_cast<unsigned long long*>(sc + sc_rows * FAST_SP);   // [FAST_MAXC][prow] NMS survivors, S >= minTh
+  unsigned long long* pl_ini = pl_min + FAST_MAXC * prow;                                        //                                S >= iniTh
+  uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + FAST_MAXC * prow);   // [max_h][row_cap], a warp's rows are contiguous
+  uint16_t* coltab = lists + (sc_rows - 2) * row_cap;     // [256] per window column: cell:3 | left:1 | right:1 | column in cell:6; 0xffff outside
+  uint8_t* det8 = reinterpret_cast<uint8_t*>(coltab + FAST_WP);   // [32] per 8-pixel group: detection columns
+  uint8_t* need8 = det8 + 32;                             // [32] per 8-pixel group: columns of the cells that retry at minTh
+  uint8_t* hasini = need8 + 32;                           // [FAST_MAXC] cell has an NMS survivor with S >= iniTh
+  unsigned long long* mbar = reinterpret_cast<unsigned long long*>(hasini + FAST_MAXC);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
-  const int level = orb_level_of(g.fast_base, (int)blockIdx.x);
+  const int4 T = __ldg(tiles + blockIdx.x);               // level, cell row, first cell, cells
+  const int level = T.x, ci = T.y, j0 = T.z, j1 = T.z + T.w;
   const OrbLevel& L = g.lv[level];
-  const int t = blockIdx.x - L.fast_tile_base;
-  const int ci = (int)(((unsigned)t * L.fast_inv_nseg) >> 20), sg = t - ci * L.fast_nseg;   // t / fast_nseg
-  const int j0 = sg * L.fast_G, j1 = min(j0 + L.fast_G, L.nCols);
   const int wCell = L.wCell;
-  int* cnt_row = cell_cnt + (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
-  uint32_t* kp_row = cell_kp + ((long long)frame * g.ncells_total + L.cell_base + ci * L.nCols) * ORB_CELL_CAP;
+  const long long cell0 = (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
+  int* cnt_row = cell_cnt + cell0;
+  uint32_t* kp_row = cell_kp + cell0 * ORB_CELL_CAP;
 
   const int iniY = ORB_MIN_BORDER + ci * L.hCell;
   const int wh = min(iniY + L.hCell + 6, L.maxBY) - iniY, dh = wh - 6;   // window rows, detection rows
@@ -218,122 +203,178 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
     for (int j = j0 + tid; j < j1; j += FAST_THREADS) cnt_row[j] = 0;
     return;
   }
-  const int xa = X0 & ~15;                         // 16-byte aligned global column of window column 0
-  const int nvec = (X1 - xa + 15) >> 4;
-  const uint8_t* src = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)iniY * L.pitch + xa;
-  // 1. stage the window; clear the score plane and the survivor bit planes
-  // i / nvec == (i * inv) >> 16 for i < 65 * 18 holds for any inv in [65536 / nvec, 65536 / nvec + 2]: one MUFU.RCP instead of a division
-  const unsigned inv_nvec = (unsigned)(__frcp_rn((float)nvec) * 65536.f) + 1u;
-  for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
-    const int y = (int)(((unsigned)i * inv_nvec) >> 16), v = i - y * nvec;
-    // global -> shared directly (LDGSTS.128); the copies land while the planes below are cleared
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(win + y * FAST_WP + 16 + 16 * v)),
-                 "l"(src + (long long)y * L.pitch + 16 * v));
+  const int xa = X0 & ~15;                         // 16-byte aligned level column of window column 16
+  // 1. stage the window
+  if (TMA) {
+    if (tid == 0) {
+      const unsigned bar = fast_smem_u32(mbar);
+      if (fast_smem_u32(win) & 127u) atomicOr(err_flag, 16);   // TMA destination alignment
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      // the box is the level's full window height (hCell + 6 rows x 256 bytes); rows / bytes outside the plane arrive as zeros
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((L.hCell + 6) * FAST_WP) : "memory");
+      // tensor coordinates: byte column of the plane allocation (16-byte lead + level column xa - 16), row incl. the apron rows, frame
+      asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                       fast_smem_u32(win)),
+                   "l"(reinterpret_cast<unsigned long long>(&maps.m[level])), "r"(xa), "r"(iniY + ORB_APRON_ROWS), "r"(frame), "r"(bar)
+                   : "memory");
+    }
+  } else {
+    const int nvec = (X1 - xa + 15) >> 4;
+    const uint8_t* src = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)iniY * L.pitch + xa;
+    // i / nvec == (i * inv) >> 16 for i < 65 * 18 holds for any inv in [65536 / nvec, 65536 / nvec + 2]: one MUFU.RCP instead of a division
+    const unsigned inv_nvec = (unsigned)(__frcp_rn((float)nvec) * 65536.f) + 1u;
+    for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
+      const int y = (int)(((unsigned)i * inv_nvec) >> 16), v = i - y * nvec;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(fast_smem_u32(win + y * FAST_WP + 16 + 16 * v)),
+                   "l"(src + (long long)y * L.pitch + 16 * v));
+    }
+    asm volatile("cp.async.commit_group;");
   }
-  asm volatile("cp.async.commit_group;");
-  for (int i = tid; i < (dh + 2) * (FAST_SP / 16); i += FAST_THREADS) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
-  // both bit planes, 16 bytes per thread (the rounding may run a few words into the still empty lists)
-  for (int i = tid; i < (2 * (sc_rows - 2) * FAST_BP + 3) / 4; i += FAST_THREADS) reinterpret_cast<uint4*>(pl_min)[i] = make_uint4(0, 0, 0, 0);
-  const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates
-  for (int i = tid; i < FAST_WP; i += FAST_THREADS) need[i] = (i >= dx0 && i < dx1) ? 0x80 : 0;   // pass 1: every detection column
-  if (tid == 0) s_retry = 0;
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncthreads();
-
-  // 2. first detection at iniTh (the reference's first cv::FAST call per cell, :1510)
+  // ... meanwhile: clear the score plane and both survivor planes (contiguous: sc, pl_min, pl_ini), build the column tables
+  {
+    uint4* z = reinterpret_cast<uint4*>(sc);
+    const int nz = (sc_rows * FAST_SP + 2 * FAST_MAXC * prow * 8) >> 4;
+    for (int i = tid; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates (window column 16 + x)
   const int qbase = dx0 & ~7;                            // groups of 8 aligned pixels
   const int nq = (dx1 - qbase + 7) >> 3;                 // <= 29
-  // warp w owns max_h / 8 (+ 1 if w < max_h % 8) rows of the largest level: its list starts after the rows of the warps before it
-  uint16_t* list = lists + (warp * ((sc_rows - 2) >> 3) + min(warp, (sc_rows - 2) & 7)) * row_cap;
-  // warp w owns the detection rows w, w + 8, w + 16, ... (<= 8 rows, dh <= 64)
-  const int row0 = warp, row1 = dh;
-  const int xlim = L.maxBX - 3 - xa;                     // detection columns end here (last cell may be clipped)
-  int ncorner = fast_detect<SMALL_TH, false>(win, sc, need, list, 0, row0, row1, qbase, nq, lane, g.ini_th, g.min_th);
+  {
+    const int x = tid - 16;                              // this thread's window column
+    const bool det = x >= dx0 && x < dx1;
+    unsigned ct = 0xffffu;
+    if (det) {
+      const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);   // detection column of the level
+      const unsigned cell = __umulhi(p, L.inv_wcell);               // p / wCell (inv = 2^32 / wCell + 1)
+      const unsigned r = p - cell * (unsigned)wCell;
+      ct = (cell - (unsigned)j0) | (r == 0u ? 8u : 0u) | ((r == (unsigned)wCell - 1u || x == dx1 - 1) ? 16u : 0u) | (r << 5);
+    }
+    coltab[tid] = (uint16_t)ct;
+    const unsigned b = __ballot_sync(0xffffffffu, det);
+    const int o = 4 * warp + lane - 2 - (qbase >> 3);    // group of window columns 32 * warp + 8 * lane .. + 7
+    if (lane < 4 && o >= 0 && o < 32) det8[o] = (uint8_t)(b >> (8 * lane));
+    if (tid < FAST_MAXC) hasini[tid] = 0;
+  }
+  if (!TMA) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
-  // 3. NMS of the corners with S >= iniTh -> ini survivor plane. A suppressor of such a corner has S >= iniTh itself, so it was
-  //    scored above. `need` is re-initialised meanwhile (nobody reads it until the next barrier).
-  fast_nms<false>(sc, need, list, ncorner, lane, pl_ini, wCell, L.inv_wcell, xa, xlim, g.ini_th);
-  for (int i = tid; i < FAST_WP / 4; i += FAST_THREADS) reinterpret_cast<unsigned*>(need)[i] = 0u;
-  __syncthreads();
-  // 4. cells without an ini survivor retry at minTh (:1521): mark their detection columns
-  for (int cj = j0 + warp; cj < j1; cj += FAST_WARPS) {
-    const int cx0 = ORB_MIN_BORDER + cj * wCell + 3 - xa;
-    const int cx1 = min(ORB_MIN_BORDER + (cj + 1) * wCell + 3, L.maxBX - 3) - xa;
-    const int dw = cx1 - cx0;
-    if (dw <= 0) continue;
-    const unsigned long long wmask = dw >= 64 ? ~0ull : ((1ull << dw) - 1ull);
-    const int w0 = cx0 >> 5, sh = cx0 & 31;
-    bool any = false;
+  if (TMA) {
+    const unsigned bar = fast_smem_u32(mbar);
+    unsigned done;
+    int spins = 0;
+    do {   // try_wait suspends the thread for a hardware time slice; the bound turns a lost copy into ORB_E_CAPACITY flag 16 instead of a hang
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+    } while (!done && ++spins < (1 << 20));
+    if (!done && tid == 0) atomicOr(err_flag, 16);
+  }
+
+  // 2. one sweep, both thresholds (the reference's two cv::FAST calls per cell, :1510 and :1521, differ only in the threshold).
+  //    Warp w owns the detection rows w, w + 8, w + 16, ... (<= 8 rows, dh <= 64): a textured blob spans adjacent rows, so every warp
+  //    gets a share of its candidates. The per-row lane rotation spreads it over the lanes as well.
+  unsigned cand_i[2] = {0u, 0u}, cand_m[2] = {0u, 0u};
+  {
+    const unsigned ti = SMALL_TH ? ((unsigned)g.ini_th + 1u) * 0x01010101u : (unsigned)g.ini_th * 0x01010101u;
+    const unsigned tm = SMALL_TH ? ((unsigned)g.min_th + 1u) * 0x01010101u : (unsigned)g.min_th * 0x01010101u;
+    for (int ri = 0; warp + FAST_WARPS * ri < dh; ++ri) {
+      const int y = warp + FAST_WARPS * ri;
+      const int o = (lane + 5 * ri) & 31;
+      if (o < nq) {
+        const uint8_t* row = win + (y + 3) * FAST_WP + 16 + qbase + 8 * o;
+        const unsigned c0 = *reinterpret_cast<const unsigned*>(row - 4), c3 = *reinterpret_cast<const unsigned*>(row + 8);
+        const uint2 c = *reinterpret_cast<const uint2*>(row);
+        const uint2 up = *reinterpret_cast<const uint2*>(row - 3 * FAST_WP), dn = *reinterpret_cast<const uint2*>(row + 3 * FAST_WP);
+        unsigned bi = 0u, bm = 0u;
 #pragma unroll
-    for (int r = 0; r < 2; ++r) {
-      const int y = lane + 32 * r;
-      if (y < dh) {
-        const uint32_t* b = pl_ini + y * FAST_BP + w0;
-        const unsigned long long m = (((unsigned long long)__funnelshift_r(b[1], b[2], sh) << 32) | __funnelshift_r(b[0], b[1], sh)) & wmask;
-        any = any || m != 0ull;
+        for (int h = 0; h < 2; ++h) {
+          const unsigned c1 = h ? c.y : c.x;
+          const unsigned lf = h ? __byte_perm(c.x, c.y, 0x4321) : __byte_perm(c0, c.x, 0x4321);
+          const unsigned rt = h ? __byte_perm(c.y, c3, 0x6543) : __byte_perm(c.x, c.y, 0x6543);
+          const unsigned au = __vabsdiffu4(c1, h ? up.y : up.x), ad = __vabsdiffu4(c1, h ? dn.y : dn.x), al = __vabsdiffu4(c1, lf),
+                         ar = __vabsdiffu4(c1, rt);
+          unsigned ui, um, di, dm, li, lm, ri_, rm;
+          fast_gt2<SMALL_TH>(au, ti, tm, ui, um);
+          fast_gt2<SMALL_TH>(ad, ti, tm, di, dm);
+          fast_gt2<SMALL_TH>(al, ti, tm, li, lm);
+          fast_gt2<SMALL_TH>(ar, ti, tm, ri_, rm);
+          unsigned gi, gm;
+          if (SMALL_TH) {
+            const unsigned pud = au | ad, plr = al | ar;
+            gi = (ui | di | pud) & (li | ri_ | plr) & 0x80808080u;
+            gm = (um | dm | pud) & (lm | rm | plr) & 0x80808080u;
+          } else {
+            gi = (ui | di) & (li | ri_) & 0x80808080u;
+            gm = (um | dm) & (lm | rm) & 0x80808080u;
+          }
+          // bits 7, 15, 23, 31 -> one nibble (the partial products never carry)
+          bi |= ((gi * 0x204081u) >> 28) << (4 * h);
+          bm |= ((gm * 0x204081u) >> 28) << (4 * h);
+        }
+        const unsigned d8 = det8[o];
+        bi &= d8;
+        bm = (bm ^ bi) & d8;                              // passes at minTh but not at iniTh (ini >= min: bi is a subset of bm)
+        const int sh = (8 * ri) & 31;
+        if (ri < 4) { cand_i[0] |= bi << sh; cand_m[0] |= bm << sh; }
+        else        { cand_i[1] |= bi << sh; cand_m[1] |= bm << sh; }
       }
     }
-    if (!__any_sync(0xffffffffu, any)) {
-      if (lane < dw) need[cx0 + lane] = 0x80;
-      if (lane + 32 < dw) need[cx0 + lane + 32] = 0x80;
-      if (lane == 0) s_retry = 1;
-    }
   }
+  // warp w owns max_h / 8 (+ 1 if w < max_h % 8) rows of the largest level: its list starts after the rows of the warps before it
+  uint16_t* list = lists + (warp * ((sc_rows - 2) >> 3) + min(warp, (sc_rows - 2) & 7)) * row_cap;
+  // 3. the iniTh candidates (superset of all S >= iniTh): exact scores, corners = S >= minTh
+  int ncorner = fast_score_candidates(cand_i, win, sc, list, 0, warp, qbase, lane, g.min_th);
   __syncthreads();
-  if (s_retry) {   // uniform over the CTA
-    // 4a. the pixels that pass the compass test at minTh but not at iniTh, in the retry cells only
-    const int n2 = fast_detect<SMALL_TH, true>(win, sc, need, list, ncorner, row0, row1, qbase, nq, lane, g.ini_th, g.min_th);
-    ncorner += n2;
+  // 4. NMS of the corners with S >= iniTh. A suppressor of such a corner has S >= iniTh itself, so it was scored above.
+  fast_nms<false>(sc, coltab, hasini, list, ncorner, lane, pl_ini, prow, g.ini_th);
+  __syncthreads();
+  // 5. cells without an ini survivor retry at minTh (:1521)
+  int retry;
+  {
+    const unsigned ct = coltab[tid];
+    const bool nd = ct != 0xffffu && hasini[ct & 7] == 0;
+    const unsigned b = __ballot_sync(0xffffffffu, nd);
+    const int o = 4 * warp + lane - 2 - (qbase >> 3);
+    if (lane < 4 && o >= 0 && o < 32) need8[o] = (uint8_t)(b >> (8 * lane));
+    retry = __syncthreads_or(nd);
+  }
+  if (retry) {   // uniform over the CTA
+    // 5a. the pixels that passed the compass test at minTh but not at iniTh, in the retry cells only
+    for (int ri = 0; warp + FAST_WARPS * ri < dh; ++ri) {
+      const unsigned keep = ~((0xffu ^ (unsigned)need8[(lane + 5 * ri) & 31]) << ((8 * ri) & 31));
+      if (ri < 4) cand_m[0] &= keep; else cand_m[1] &= keep;
+    }
+    ncorner += fast_score_candidates(cand_m, win, sc, list, ncorner, warp, qbase, lane, g.min_th);
     __syncthreads();
-    // 4b. NMS of every corner (S >= minTh) of the retry cells -> min survivor plane
-    fast_nms<true>(sc, need, list, ncorner, lane, pl_min, wCell, L.inv_wcell, xa, xlim, g.ini_th);
+    // 5b. NMS of every corner (S >= minTh) of the retry cells
+    fast_nms<true>(sc, coltab, hasini, list, ncorner, lane, pl_min, prow, g.ini_th);
     __syncthreads();
   }
 
-  // 5. per cell: row-major ranks from the survivor bit planes, ini/min selection, emission. Lane = detection row
-  //    (two row slots cover dh <= 64); a cell's detection window is < 64 columns wide.
+  // 6. per cell: row-major ranks from the cell's survivor rows (ini plane if the cell has an ini survivor), emission.
+  //    Lane = detection rows 2 * lane, 2 * lane + 1 (dh <= 64); rows >= dh hold no bits.
   for (int cj = j0 + warp; cj < j1; cj += FAST_WARPS) {
+    const int cl = cj - j0;
     const int cx0 = ORB_MIN_BORDER + cj * wCell + 3 - xa;
-    const int cx1 = min(ORB_MIN_BORDER + (cj + 1) * wCell + 3, L.maxBX - 3) - xa;
-    const int dw = cx1 - cx0;
-    if (dw <= 0) {
+    if (min(ORB_MIN_BORDER + (cj + 1) * wCell + 3, L.maxBX - 3) - xa - cx0 <= 0) {   // clipped away: no detection column
       if (lane == 0) cnt_row[cj] = 0;
       continue;
     }
-    const unsigned long long wmask = dw >= 64 ? ~0ull : ((1ull << dw) - 1ull);
-    const int w0 = cx0 >> 5, sh = cx0 & 31;
-    unsigned long long m_min[2], m_ini[2];
-    int n_ini = 0;
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-      const int y = lane + 32 * r;
-      m_min[r] = 0ull; m_ini[r] = 0ull;
-      if (y < dh) {
-        const uint32_t* a = pl_min + y * FAST_BP + w0;
-        const uint32_t* b = pl_ini + y * FAST_BP + w0;
-        m_min[r] = (((unsigned long long)__funnelshift_r(a[1], a[2], sh) << 32) | __funnelshift_r(a[0], a[1], sh)) & wmask;
-        m_ini[r] = (((unsigned long long)__funnelshift_r(b[1], b[2], sh) << 32) | __funnelshift_r(b[0], b[1], sh)) & wmask;
-        n_ini += __popcll(m_ini[r]);
-      }
-    }
-    n_ini = __reduce_add_sync(0xffffffffu, n_ini);
-    const unsigned long long m0 = n_ini > 0 ? m_ini[0] : m_min[0], m1 = n_ini > 0 ? m_ini[1] : m_min[1];
-    const int c0 = __popcll(m0), c1 = __popcll(m1);
-    // exclusive scan over rows 0..63 (slot 0 of all lanes, then slot 1)
-    int x0 = c0, x1 = c1;
+    const unsigned long long* pc = (hasini[cl] ? pl_ini : pl_min) + cl * prow;
+    ulonglong2 mm = make_ulonglong2(0ull, 0ull);
+    if (2 * lane < prow) mm = *reinterpret_cast<const ulonglong2*>(pc + 2 * lane);
+    const int c0 = __popcll(mm.x), c1 = __popcll(mm.y);
+    int incl = c0 + c1;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const int y0 = __shfl_up_sync(0xffffffffu, x0, o), y1 = __shfl_up_sync(0xffffffffu, x1, o);
-      if (lane >= o) { x0 += y0; x1 += y1; }
+      const int yv = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += yv;
     }
-    const int tot0 = __shfl_sync(0xffffffffu, x0, 31), tot1 = __shfl_sync(0xffffffffu, x1, 31);
-    const int total = tot0 + tot1;
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
     uint32_t* kp_out = kp_row + (long long)cj * ORB_CELL_CAP;
+    int rank = incl - c0 - c1;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
-      unsigned long long m = r ? m1 : m0;
-      int rank = r ? tot0 + x1 - c1 : x0 - c0;
-      const int y = lane + 32 * r;
+      unsigned long long m = r ? mm.y : mm.x;
+      const int y = 2 * lane + r;
       while (m) {
         const int bx = __ffsll((long long)m) - 1;
         m &= m - 1;
@@ -353,8 +394,59 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_cnt
   }
 }
 
-void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* err_flag, const OrbGeom& g, int batch,
-                     cudaStream_t st, long long* launches) {
+// ---- host side ------------------------------------------------------------------------------------------------
+// Band table: one int4 {level, cell row, first cell, cells} per CTA of a frame, levels in ascending order.
+void orb_fast_build_tiles(const OrbGeom& g, std::vector<int4>& tiles) {
+  tiles.clear();
+  for (int l = 0; l < g.nlevels; ++l) {
+    const OrbLevel& L = g.lv[l];
+    for (int ci = 0; ci < L.nRows; ++ci)
+      for (int sg = 0; sg < L.fast_nseg; ++sg) {
+        const int j0 = sg * L.fast_G, j1 = std::min(j0 + L.fast_G, L.nCols);
+        tiles.push_back(make_int4(l, ci, j0, std::max(j1 - j0, 0)));
+      }
+  }
+}
+
+// Per-level TMA descriptors over one pass workspace `pyr` holding `frames` frames: tensor [frames][plane rows][pitch bytes] u8 starting at
+// the plane allocation (apron rows and the 16-byte row lead included, so every window coordinate is >= 0), box = 256 bytes x (hCell + 6) rows.
+typedef CUresult (*OrbEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static OrbEncodeTiled orb_encode_tiled() {
+  static std::atomic<OrbEncodeTiled> fn{nullptr};
+  OrbEncodeTiled f = fn.load(std::memory_order_acquire);
+  if (!f) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+      f = reinterpret_cast<OrbEncodeTiled>(p);
+    fn.store(f, std::memory_order_release);
+  }
+  return f;
+}
+
+int orb_fast_build_maps(const uint8_t* pyr, int frames, const OrbGeom& g, void* maps_out) {
+  OrbFastMaps* M = reinterpret_cast<OrbFastMaps*>(maps_out);
+  memset(M, 0, sizeof(*M));
+  OrbEncodeTiled enc = orb_encode_tiled();
+  if (!enc) return -1;
+  for (int l = 0; l < g.nlevels; ++l) {
+    const OrbLevel& L = g.lv[l];
+    void* base = const_cast<uint8_t*>(pyr) + L.plane_off - (size_t)ORB_APRON_ROWS * L.pitch - 16;
+    const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.rows + 2 * ORB_APRON_ROWS), (cuuint64_t)frames};
+    const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)g.frame_stride};
+    const cuuint32_t box[3] = {FAST_WP, (cuuint32_t)(L.hCell + 6), 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&M->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return -1;
+  }
+  return 0;
+}
+size_t orb_fast_maps_bytes() { return sizeof(OrbFastMaps); }
+
+void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, int* cell_cnt, uint32_t* cell_kp, int* err_flag, const OrbGeom& g,
+                     int batch, cudaStream_t st, long long* launches) {
   int max_h = 0;
   for (int l = 0; l < g.nlevels; ++l) max_h = max(max_h, g.lv[l].hCell);
   const int win_rows = max_h + 6, sc_rows = max_h + 2;
@@ -365,27 +457,33 @@ void orb_launch_fast(const uint8_t* pyr, int* cell_cnt, uint32_t* cell_kp, int* 
     row_cap = std::max(row_cap, 4 * ((dw + 3 + 3) / 4));                                           // + quad alignment at the front
   }
   row_cap = std::min(row_cap, 256);
-  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)max_h * FAST_BP * 4 +
-                      (size_t)max_h * row_cap * 2 + FAST_WP;   // KITTI: 40 KB -> 5 resident CTAs per SM
+  const int prow = (sc_rows - 1) & ~1;
+  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)FAST_MAXC * prow * 8 + (size_t)max_h * row_cap * 2 +
+                      FAST_WP * 2 + 32 + 32 + FAST_MAXC + 8;   // KITTI: 37.5 KB
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
   // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
-  typedef void (*Kern)(const uint8_t*, int*, uint32_t*, int*, int, int, int, const OrbGeom);
-  static const Kern kerns[2] = {orb_fast_band_kernel<false>, orb_fast_band_kernel<true>};
-  static std::atomic<bool> configured[64][2];
+  typedef void (*Kern)(const uint8_t*, const int4*, int*, uint32_t*, int*, int, int, int, const OrbGeom, const OrbFastMaps);
+  static const Kern kerns[2][2] = {{orb_fast_band_kernel<false, false>, orb_fast_band_kernel<false, true>},
+                                   {orb_fast_band_kernel<true, false>, orb_fast_band_kernel<true, true>}};
+  static std::atomic<bool> configured[64][2][2];
+  static const bool no_tma = getenv("ORB_B200_NO_TMA") != nullptr;   // A/B switch: per-thread cp.async staging instead of the TMA box load
   const int small = g.ini_th <= 126;      // both thresholds (min <= ini) in the carry-free byte-compare range
-  const Kern kern = kerns[small];
+  const int tma = (maps != nullptr && !no_tma) ? 1 : 0;
+  const Kern kern = kerns[small][tma];
   int dev = 0;
   cudaGetDevice(&dev);
   dev &= 63;
-  if (!configured[dev][small].load(std::memory_order_acquire)) {
+  if (!configured[dev][small][tma].load(std::memory_order_acquire)) {
     int optin = 0;
     cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaFuncAttributes fa;
     cudaFuncGetAttributes(&fa, kern);
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);   // the limit covers static + dynamic
-    configured[dev][small].store(true, std::memory_order_release);
+    configured[dev][small][tma].store(true, std::memory_order_release);
   }
+  static const OrbFastMaps no_maps = {};
   const dim3 grid(g.fast_tiles_total, batch);
-  kern<<<grid, FAST_THREADS, smem, st>>>(pyr, cell_cnt, cell_kp, err_flag, win_rows, sc_rows, row_cap, g);
+  kern<<<grid, FAST_THREADS, smem, st>>>(pyr, reinterpret_cast<const int4*>(tiles), cell_cnt, cell_kp, err_flag, win_rows, sc_rows, row_cap, g,
+                                         tma ? *reinterpret_cast<const OrbFastMaps*>(maps) : no_maps);
   ++*launches;
 }

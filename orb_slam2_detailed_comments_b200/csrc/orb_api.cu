@@ -26,7 +26,7 @@ struct orb_extractor {
   int chunk = 0;           // frames per internal pass (workspace capacity)
   int cap_ws = 0;
   long long launches = 0;
-  DevBuf tabs, err;
+  DevBuf tabs, err, fast_tiles;
   // Two pass workspaces on two compute streams: consecutive internal passes alternate between them, so the latency-bound
   // tail of pass p (quadtree, descriptors) overlaps the bandwidth/issue-bound head of pass p+1 (pyramid, FAST, blur).
   // ws[0].st is the handle's public stream.
@@ -36,6 +36,8 @@ struct orb_extractor {
     cudaStream_t st_side = nullptr;                       // high-priority side stream of the pass: quadtree (latency-bound) beside blur
     cudaEvent_t ev_fast = nullptr, ev_side = nullptr;
     int frames = 0;          // frames of the last pass run here
+    alignas(64) unsigned char fast_maps[ORB_FAST_MAPS_BYTES];   // per-level TMA descriptors of `pyr` (FAST window loads)
+    bool maps_ok = false;
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
     DevBuf st_sad;   // stereo: SAD of every kept match [chunk/2][cap]
     DevBuf st_rows, st_sorted;   // stereo: right keypoints sorted by image row: starts [chunk/2][rows0 + 1], indices [chunk/2][cap]
@@ -232,6 +234,10 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     if ((rc = e->tabs.ensure(std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTab))) != ORB_OK) return rc;
     if (!tabs.empty()) CU(cudaMemcpyAsync(e->tabs.p, tabs.data(), tabs.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice, e->stream));
     CU(cudaStreamSynchronize(e->stream));
+    std::vector<int4> tiles;
+    orb_fast_build_tiles(e->geom, tiles);
+    if ((rc = e->fast_tiles.ensure(std::max<size_t>(tiles.size(), 1) * sizeof(int4))) != ORB_OK) return rc;
+    CU(cudaMemcpy(e->fast_tiles.p, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
     e->chunk = 0;
   }
   const OrbGeom& g = e->geom;
@@ -273,6 +279,8 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     ENS(q_scan, B * g.node_total * sizeof(unsigned long long));
     ENS(q_rawn, B * nl * sizeof(int));
       P.frames = 0;
+      // TMA descriptors follow the (re)allocated pyramid buffer; without the driver entry point the kernel stages with cp.async
+      P.maps_ok = orb_fast_maps_bytes() == ORB_FAST_MAPS_BYTES && orb_fast_build_maps(P.pyr.as<uint8_t>(), (int)B, g, P.fast_maps) == 0;
     }
 #undef ENS
     CU(cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream));
@@ -309,7 +317,10 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
   if (prof) cudaEventRecord(ev[0], st);
   orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches, ev_input_consumed);
   if (prof) cudaEventRecord(ev[1], st);
-  orb_launch_fast(P.pyr.as<uint8_t>(), P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
+  static const bool fast_v1 = getenv("ORB_B200_FAST_V1") != nullptr;   // round-1 kernel, same-box A/B only
+  if (fast_v1) orb_launch_fast_v1(P.pyr.as<uint8_t>(), P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
+  else orb_launch_fast(P.pyr.as<uint8_t>(), e->fast_tiles.p, P.maps_ok ? P.fast_maps : nullptr, P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(),
+                       e->err.as<int>(), g, n, st, &e->launches);
   if (prof) cudaEventRecord(ev[2], st);
   // The quadtree is latency-bound (one CTA per frame x level, ~30 % issue-active) and only needs the FAST cells; the blur only needs
   // the pyramid. Outside stage profiling the quadtree (side >= 1) and the descriptors (side >= 2) go to the pass's high-priority
@@ -357,7 +368,7 @@ static int check_err_flag(orb_extractor* e) {
   CU(cudaGetLastError());
   if (flag) {
     cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream);
-    return fail(ORB_E_CAPACITY, "capacity overflow (flags %d: 1 cell cap, 2 raw keypoints, 4 nodes, 8 output cap)", flag);
+    return fail(ORB_E_CAPACITY, "capacity overflow (flags %d: 1 cell cap, 2 raw keypoints, 4 nodes, 8 output cap, 16 TMA window load failed)", flag);
   }
   return ORB_OK;
 }
@@ -429,7 +440,7 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   for (int w = 0; w < ORB_MAX_WS; ++w)
     for (DevBuf* b : e->ws[w].all) b->release();
-  DevBuf* bufs[] = {&e->tabs, &e->err, &e->cnt_all, &e->stage_in[0], &e->stage_in[1]};
+  DevBuf* bufs[] = {&e->tabs, &e->err, &e->fast_tiles, &e->cnt_all, &e->stage_in[0], &e->stage_in[1]};
   for (DevBuf* b : bufs) b->release();
   for (int b = 0; b <= ORB_MAX_WS; ++b) { e->out_kps[b].release(); e->out_desc[b].release(); e->out_ur[b].release(); e->out_dp[b].release(); }
   if (e->h_cnt) cudaFreeHost(e->h_cnt);

@@ -17,7 +17,12 @@
 // ---- kernel launchers (other translation units) -------------------------------------------------------------
 struct OrbKnn2;
 void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const OrbGeom&, int, cudaStream_t, long long*, cudaEvent_t);
-void orb_launch_fast(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_fast(const uint8_t*, const void* tiles, const void* maps, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_fast_v1(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);   // round-1 kernel (A/B only)
+void orb_fast_build_tiles(const OrbGeom&, std::vector<int4>&);
+int orb_fast_build_maps(const uint8_t* pyr, int frames, const OrbGeom&, void* maps_out);   // 0 = ok; maps_out: ORB_FAST_MAPS_BYTES, 64-byte aligned
+size_t orb_fast_maps_bytes();
+#define ORB_FAST_MAPS_BYTES (128 * ORB_MAX_LEVELS)
 void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t*, int*, int*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_describe(const uint8_t*, const uint8_t*, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
