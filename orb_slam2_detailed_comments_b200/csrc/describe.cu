@@ -1,11 +1,9 @@
 // Gaussian blur (src/ORBextractor.cc:2039-2047), IC_Angle (:104-161), computeOrbDescriptor (:177-254) and the
 // output assembly of ORBextractor::operator() (:2020-2081).
-#include "orb_common.cuh"
+#include <cstdlib>
 
-__device__ const int8_t d_pattern[256 * 4] = {
-#include "../../include/orb_pattern_31.inc"
-};
-__constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};  // :866-910
+#include "describe_common.cuh"
+#include "orb_tma.cuh"
 
 // ---- 7x7 sigma-2 Gaussian, OpenCV 8-bit fixed-point path (taps 8.8): out = (sum_ij k_i k_j p_ij + 32768) >> 16,
 // BORDER_REFLECT_101 at the border of the PADDED level (this fork blurs the padded image; the pyramid kernels have already
@@ -105,81 +103,44 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __r
   }
 }
 
-// cv::fastAtan2 bit replica (float32, no FMA contraction).
-__device__ __forceinline__ float orb_fast_atan2(float y, float x) {
-  const float s = (float)(180.0 / 3.1415926535897932384626433832795);
-  const float p1 = __fmul_rn(0.9997878412794807f, s), p3 = __fmul_rn(-0.3258083974640975f, s),
-              p5 = __fmul_rn(0.1555786518463281f, s), p7 = __fmul_rn(-0.04432655554792128f, s);
-  const float eps = (float)2.2204460492503131e-16;
-  const float ax = fabsf(x), ay = fabsf(y);
-  float a;
-  if (ax >= ay) {
-    const float c = __fdiv_rn(ay, __fadd_rn(ax, eps)), c2 = __fmul_rn(c, c);
-    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
-  } else {
-    const float c = __fdiv_rn(ax, __fadd_rn(ay, eps)), c2 = __fmul_rn(c, c);
-    a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
-  }
-  if (x < 0.f) a = __fsub_rn(180.f, a);
-  if (y < 0.f) a = __fsub_rn(360.f, a);
-  return a;
-}
-
-// Canonical sin/cos of a float angle: fdlibm-style reduction + kernels in double with explicit
-// round-to-nearest mul/add (no FMA), one rounding to float. Same operation sequence as the oracle.
-__device__ __forceinline__ void orb_sincos(float angle, float* s, float* c) {
-  const double x = (double)angle;
-  const double invpio2 = 6.36619772367581382433e-01, pio2_1 = 1.57079632673412561417e+00, pio2_1t = 6.07710050650619224932e-11;
-  const double kf = floor(__dadd_rn(__dmul_rn(x, invpio2), 0.5));
-  const int k = (int)kf;
-  const double r = __dsub_rn(__dsub_rn(x, __dmul_rn(kf, pio2_1)), __dmul_rn(kf, pio2_1t));
-  const double z = __dmul_rn(r, r);
-  const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03, S3 = -1.98412698298579493134e-04,
-               S4 = 2.75573137070700676789e-06, S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
-  const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03, C3 = 2.48015872894767294178e-05,
-               C4 = -2.75573143513906633035e-07, C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
-#define DM(a, b) __dmul_rn(a, b)
-#define DA(a, b) __dadd_rn(a, b)
-  const double ps = DA(S2, DM(z, DA(S3, DM(z, DA(S4, DM(z, DA(S5, DM(z, S6))))))));
-  const double sn = DA(r, DM(DM(z, r), DA(S1, DM(z, ps))));
-  const double pc = DM(z, DA(C1, DM(z, DA(C2, DM(z, DA(C3, DM(z, DA(C4, DM(z, DA(C5, DM(z, C6)))))))))));
-  const double cs = __dsub_rn(1.0, __dsub_rn(DM(0.5, z), DM(z, pc)));
-#undef DM
-#undef DA
-  switch (k & 3) {
-    case 0: *s = (float)sn; *c = (float)cs; break;
-    case 1: *s = (float)cs; *c = (float)(-sn); break;
-    case 2: *s = (float)(-sn); *c = (float)(-cs); break;
-    default: *s = (float)(-cs); *c = (float)sn; break;
-  }
-}
-
 // Orientation (un-blurred level), descriptor (blurred level) and the final cv::KeyPoint (pt *= scale for level != 0).
-// One warp handles DESC_KPW keypoints of one frame back to back, so the per-lane tables stay in registers:
-//   * IC_Angle: lane = patch row v (31 rows). The row's 32 bytes u = -16..15 are 9 aligned words (staged through shared
-//     memory by coalesced loads) funnel-shifted into 8 words; m10 += dp4a(word, [u masked by the disc]), rowsum += dp4a(word, [disc mask]); m01 = v * rowsum;
-//     two REDUX adds finish the moments (exact int32).
-//   * rBRIEF: lane = descriptor byte; its 8 test pairs (x0, y0, x1, y1 as floats) come from shared memory, one LDS.128 each;
-//     the 512 pixel gathers hit the staged 37 x 40-byte patch in shared memory.
-#define DESC_WARPS 4     // 128-thread CTAs, 14.5 KB of shared memory: one fits beside five resident FAST CTAs of the other pass stream
-#define DESC_KPW 8
-__device__ __forceinline__ int dp4a_u8_s8(unsigned a, unsigned b, int c) {   // a: unsigned bytes, b: signed bytes
-  int d;
-  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-  return d;
+// One warp handles DESC_KPW keypoints of one frame back to back, so the per-lane tables stay in registers; lane i < DESC_KPW owns keypoint i
+// of the warp's batch (level lookup and the packed record are fetched once, up front; it writes that keypoint's 28-byte cv::KeyPoint at the end).
+//   * staging, TMA == false (default): the 31 x 36-byte IC_Angle window (un-blurred) and the 37 x 40-byte descriptor patch (blurred) are
+//     fetched with coalesced 4-byte cp.async copies (global -> shared without a register round trip), both windows issued up front as two
+//     groups: the orientation starts when the first has landed.
+//   * staging, TMA == true (ORB_B200_DESC_TMA=1, kept as the measured alternative): ONE lane issues two TMA box loads per keypoint
+//     (cp.async.bulk.tensor.3d, per-level tensor maps), 31 x 48 bytes and 37 x 64 bytes: the innermost box coordinate has to be 16-byte
+//     aligned (anything else raises an illegal-instruction fault, tests/cuda/tma_probe.cu), so a box starts at the 16-byte boundary below
+//     the window. 22 % fewer instructions, but 2 x 136 k boxes of ~34 short rows per pass saturate the TMA unit: 1.71 ms against 0.96 ms
+//     per 512 frames with 73 % of the stall samples on the mbarrier wait (profiles/r2_tma_ab.md).
+//   * IC_Angle: lane = patch row v (31 rows): the row's words are funnel-shifted to the window start; m10 += dp4a(word & disc mask, u),
+//     rowsum += dp4a(word & disc mask, 1), m01 = v * rowsum; two REDUX adds finish the moments (exact int32).
+//   * rBRIEF: lane = descriptor byte; its 8 test pairs (x0, y0, x1, y1 as floats) come from shared memory, one LDS.128 each. cvRound is
+//     the float add of 1.5 * 2^23 (round-half-even happens in the FADD; F2I would go through the quarter-rate conversion pipe); the
+//     integer bias of both coordinates is folded into the 32-bit shared-memory base address of the patch.
+template <bool TMA> struct DescLayout;
+template <> struct DescLayout<false> { enum { IC_PITCH = 36, PT_PITCH = 40, IC_BYTES = 31 * 36 + 4, PT_BYTES = 37 * 40 + 8 }; };
+template <> struct DescLayout<true> { enum { IC_PITCH = 48, PT_PITCH = 64, IC_BYTES = 1536, PT_BYTES = 2432 }; };   // rounded to the 128-byte TMA alignment
+
+__device__ __forceinline__ void cp_async4(unsigned smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem), "l"(gmem));
 }
-__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
-}
+
+template <bool TMA>
 __global__ void __launch_bounds__(DESC_WARPS * 32, 40 / DESC_WARPS)
 orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr, const uint32_t* __restrict__ kept,
                     const int* __restrict__ kept_cnt, OrbKeypoint* __restrict__ kps, uint8_t* __restrict__ desc, int cap,
-                    int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g) {
+                    int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g,
+                    const __grid_constant__ OrbLevelMaps ic_maps, const __grid_constant__ OrbLevelMaps pt_maps) {
+  typedef DescLayout<TMA> Lay;
+  __shared__ __align__(128) uint8_t s_win[DESC_WARPS][Lay::IC_BYTES + Lay::PT_BYTES];
+  __shared__ float4 s_pat[8 * 32];   // rBRIEF pattern as floats, [test bit][lane]: one conflict-free LDS.128 per test (256 test pairs)
+  __shared__ __align__(8) unsigned long long s_bar[DESC_WARPS][2];
   const int frame = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // cumulative kept counts: lane l holds the inclusive prefix of level l
   int cinc = lane < g.nlevels ? kept_cnt[frame * g.nlevels + lane] : 0;
-  const int cown = cinc;
 #pragma unroll
   for (int o = 1; o < 16; o <<= 1) {
     const int y = __shfl_up_sync(0xffffffffu, cinc, o);
@@ -191,16 +152,30 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     if (total > cap) atomicOr(err_flag, 8);
   }
   const int w_first = (blockIdx.x * DESC_WARPS + warp) * DESC_KPW;
-  const int w_end = min(min(w_first + DESC_KPW, total), cap);
-  // rBRIEF pattern as floats, [test bit][lane] so that one LDS.128 per test is conflict-free (256 test pairs)
-  __shared__ float4 s_pat[8 * 32];
+  const int n = min(min(w_first + DESC_KPW, total), cap) - w_first;   // keypoints of this warp
 #pragma unroll
   for (int b = warp; b < 8; b += DESC_WARPS) {
     const char4 p = reinterpret_cast<const char4*>(d_pattern)[lane * 8 + b];
     s_pat[b * 32 + lane] = make_float4((float)p.x, (float)p.y, (float)p.z, (float)p.w);
   }
+  const unsigned bar_ic = orb_smem_u32(&s_bar[warp][0]), bar_pt = orb_smem_u32(&s_bar[warp][1]);
+  if (TMA && lane == 0) { orb_mbar_init(bar_ic, 1); orb_mbar_init(bar_pt, 1); }
   __syncthreads();
-  if (w_first >= w_end) return;
+  if (n <= 0) return;
+
+  // lane i < n: level and packed record of keypoint w_first + i (level = number of levels whose inclusive prefix is <= w)
+  int my_level = 0;
+  uint32_t my_q = 0;
+  {
+    const int w = w_first + lane;
+    int base = 0;
+    for (int l = 0; l < g.nlevels - 1; ++l) {
+      const int c = __shfl_sync(0xffffffffu, cinc, l);
+      if (c <= w) { my_level = l + 1; base = c; }
+    }
+    if (lane < n) my_q = kept[(long long)frame * g.node_total + g.lv[my_level].node_off + (w - base)];
+  }
+  float my_angle = 0.f;
 
   // per-lane constants
   const int v = lane - ORB_HALF_PATCH;                   // patch row of this lane (lane 31: none)
@@ -212,57 +187,84 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
 #pragma unroll
     for (int i = 0; i < 8; ++i) dm[i] = ((((bits >> (4 * i)) & 15u) * 0x00204081u) & 0x01010101u) * 0xffu;
   }
-  // per-warp staging: the 31 x 36-byte IC_Angle window of the un-blurred level and the 37 x 40-byte descriptor patch of the
-  // blurred level are fetched with coalesced 32-bit loads (row-major over the lanes) and then gathered from shared memory
-  __shared__ unsigned s_ic[DESC_WARPS][31 * 9 + 1];
-  __shared__ unsigned s_pt[DESC_WARPS][37 * 10 + 2];
-  unsigned* ic = s_ic[warp];
-  unsigned* pt = s_pt[warp];
-  const uint8_t* ptb = reinterpret_cast<const uint8_t*>(pt);
-  const int ic_sub = lane / 9, ic_w = lane - 9 * ic_sub, ic_idx = 9 * ic_sub + ic_w;      // lanes 27..31 idle
-  const int pt_sub = lane / 10, pt_w = lane - 10 * pt_sub, pt_idx = 10 * pt_sub + pt_w;   // lanes 30, 31 idle
+  const uint8_t* ic = s_win[warp];
+  const unsigned ic_s = orb_smem_u32(ic), pt_s = ic_s + Lay::IC_BYTES;
+  // patch byte (r, c) relative to the keypoint sits at pt_s + (r + 18) * pitch + (c + 18) + (window misalignment); r and c arrive as float
+  // bit patterns 0x4B400000 + value
+  const unsigned pt_bias = pt_s + 18u * Lay::PT_PITCH + 18u - ((unsigned)Lay::PT_PITCH + 1u) * 0x4B400000u;
+  unsigned failed = 0;
+  // cp.async staging: three window rows per copy instruction, lane = (row % 3, word)
+  const int ic_sub = lane / 9, ic_w = lane - 9 * ic_sub;      // lanes 27..31 idle
+  const int pt_sub = lane / 10, pt_w = lane - 10 * pt_sub;    // lanes 30, 31 idle
   const bool ic_act = lane < 27, pt_act = lane < 30;
+  const unsigned ic_dst = ic_s + 4u * (unsigned)(9 * ic_sub + ic_w), pt_dst = pt_s + 4u * (unsigned)(10 * pt_sub + pt_w);
 
-  for (int w = w_first; w < w_end; ++w) {
-    const int level = __popc(__ballot_sync(0xffffffffu, lane < g.nlevels && cinc <= w));
-    const int base = __shfl_sync(0xffffffffu, cinc - cown, level);
-    const OrbLevel& L = g.lv[level];
-    const int pitch = L.pitch;
-    const uint32_t q = kept[(long long)frame * g.node_total + L.node_off + (w - base)];
+  for (int i = 0; i < n; ++i) {
+    const int level = __shfl_sync(0xffffffffu, my_level, i);
+    const uint32_t q = __shfl_sync(0xffffffffu, my_q, i);
     const int x = (int)(q & 0xfffu) + ORB_MIN_BORDER, y = (int)((q >> 12) & 0xfffu) + ORB_MIN_BORDER;   // :1573-1589
-    const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off;
-    // all global loads of this keypoint are issued up front
-    const int xi = (x - 16) & ~3, xp = (x - 18) & ~3;          // planes are 16-byte aligned: column alignment == address alignment
-    const unsigned* icg = reinterpret_cast<const unsigned*>(pyr + off + (long long)(y - 15) * pitch + xi);
-    const unsigned* ptg = reinterpret_cast<const unsigned*>(blr + off + (long long)(y - 18) * pitch + xp);
-    const int pw = pitch >> 2;
-    // three window rows per load instruction: lane = (row % 3, word); the per-lane offsets need one IMAD per keypoint
-    const unsigned* icl = icg + ic_sub * pw + ic_w;
-    const unsigned* ptl = ptg + pt_sub * pw + pt_w;
-    // global -> shared without a register round trip: one cp.async per window word, the IC_Angle window and the descriptor patch as
-    // two groups so that the orientation starts as soon as the first has landed
     __syncwarp();                                              // the previous keypoint's gathers are done
+    const unsigned parity = (unsigned)i & 1u;
+    unsigned s_ic, s_pt;                                       // byte offset of window column 0 inside the staged row
+    if (TMA) {
+      if (lane == 0) {
+        // tensor coordinates = level coordinates + (16-byte row lead, apron rows); planes are 16-byte aligned, so column alignment == address alignment
+        orb_mbar_expect_tx(bar_ic, 31 * Lay::IC_PITCH);
+        orb_tma_load_3d(ic_s, &ic_maps.m[level], ((x - 16) & ~15) + 16, y - 15 + ORB_APRON_ROWS, frame, bar_ic);
+        orb_mbar_expect_tx(bar_pt, 37 * Lay::PT_PITCH);
+        orb_tma_load_3d(pt_s, &pt_maps.m[level], ((x - 18) & ~15) + 16, y - 18 + ORB_APRON_ROWS, frame, bar_pt);
+      }
+      s_ic = (unsigned)(x - 16) & 15u;
+      s_pt = (unsigned)(x - 18) & 15u;
+      failed |= orb_mbar_wait(bar_ic, parity) ^ 1u;
+    } else {
+      const OrbLevel& L = g.lv[level];
+      const int pitch = L.pitch;
+      const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off;
+      const int xi = (x - 16) & ~3, xp = (x - 18) & ~3;      // planes are 16-byte aligned: column alignment == address alignment
+      const uint8_t* icl = pyr + off + (long long)(y - 15 + ic_sub) * pitch + xi + 4 * ic_w;
+      const uint8_t* ptl = blr + off + (long long)(y - 18 + pt_sub) * pitch + xp + 4 * pt_w;
+      const long long p3 = 3LL * pitch;
 #pragma unroll
-    for (int i = 0; i < 11; ++i)
-      if (ic_act && 3 * i + ic_sub < 31) cp_async4(&ic[27 * i + ic_idx], icl + 3 * i * pw);
-    asm volatile("cp.async.commit_group;");
+      for (int k = 0; k < 11; ++k)
+        if (ic_act && 3 * k + ic_sub < 31) cp_async4(ic_dst + 108u * k, icl + k * p3);
+      asm volatile("cp.async.commit_group;");
 #pragma unroll
-    for (int i = 0; i < 13; ++i)
-      if (pt_act && 3 * i + pt_sub < 37) cp_async4(&pt[30 * i + pt_idx], ptl + 3 * i * pw);
-    asm volatile("cp.async.commit_group;");
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    __syncwarp();
-    // IC_Angle (:104-161): lane = row v
+      for (int k = 0; k < 13; ++k)
+        if (pt_act && 3 * k + pt_sub < 37) cp_async4(pt_dst + 120u * k, ptl + k * p3);
+      asm volatile("cp.async.commit_group;");
+      s_ic = (unsigned)(x - 16) & 3u;
+      s_pt = (unsigned)(x - 18) & 3u;
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      __syncwarp();
+    }
+    // IC_Angle (:104-161): lane = row v, window column c <-> u = c - 16
     int m10 = 0, rs = 0;
     if (lane < 31) {
-      const unsigned sh = 8u * (unsigned)((x - 16) & 3);
-      unsigned a[9];
+      unsigned w[12];
+      if (TMA) {
+        const uint4* rowp = reinterpret_cast<const uint4*>(ic + lane * Lay::IC_PITCH);
+        const uint4 q0 = rowp[0], q1 = rowp[1], q2 = rowp[2];
+        w[0] = q0.x; w[1] = q0.y; w[2] = q0.z; w[3] = q0.w; w[4] = q1.x; w[5] = q1.y; w[6] = q1.z; w[7] = q1.w;
+        w[8] = q2.x; w[9] = q2.y; w[10] = q2.z; w[11] = q2.w;
+        if (s_ic & 8u) {
 #pragma unroll
-      for (int i = 0; i < 9; ++i) a[i] = ic[lane * 9 + i];
+          for (int k = 0; k < 10; ++k) w[k] = w[k + 2];
+        }
+        if (s_ic & 4u) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const unsigned wv = __funnelshift_r(a[i], a[i + 1], sh) & dm[i];
-        const int u0 = -16 + 4 * i;                       // signed byte coefficients u0 .. u0 + 3 (compile-time constant)
+          for (int k = 0; k < 9; ++k) w[k] = w[k + 1];
+        }
+      } else {
+        const unsigned* rowp = reinterpret_cast<const unsigned*>(ic + lane * Lay::IC_PITCH);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) w[k] = rowp[k];
+      }
+      const unsigned sh = 8u * (s_ic & 3u);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const unsigned wv = __funnelshift_r(w[k], w[k + 1], sh) & dm[k];
+        const int u0 = -16 + 4 * k;                       // signed byte coefficients u0 .. u0 + 3 (compile-time constant)
         const unsigned cu = ((unsigned)u0 & 0xffu) | (((unsigned)(u0 + 1) & 0xffu) << 8) | (((unsigned)(u0 + 2) & 0xffu) << 16) |
                             (((unsigned)(u0 + 3) & 0xffu) << 24);
         m10 = dp4a_u8_s8(wv, cu, m10);
@@ -272,39 +274,46 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     m10 = __reduce_add_sync(0xffffffffu, m10);
     const int m01 = __reduce_add_sync(0xffffffffu, v * rs);
     const float angle = orb_fast_atan2((float)m01, (float)m10);
+    if (lane == i) my_angle = angle;
     const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
     float a, b;
     orb_sincos(__fmul_rn(angle, factorPI), &b, &a);
-    // computeOrbDescriptor (:177-254) on the staged patch: byte (r, c) of the patch is pt[(r + 18) * 40 + c + x - xp]
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
-    const uint8_t* bc = ptb + 18 * 40 + (x - xp);
+    // computeOrbDescriptor (:177-254) on the staged patch
+    if (TMA) {
+      failed |= orb_mbar_wait(bar_pt, parity) ^ 1u;
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+    }
+    const unsigned pt_off = pt_bias + s_pt;
+    const float magic = 12582912.f;   // 1.5 * 2^23: (v + magic) has round-half-even(v) in its low mantissa bits, bit pattern 0x4B400000 + round(v)
     int val = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; ++bit) {
       const float4 p = s_pat[bit * 32 + lane];   // x0, y0, x1, y1
-      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)));
-      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)));
-      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)));
-      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)));
-      const int t0 = bc[r0 * 40 + c0], t1 = bc[r1 * 40 + c1];
+      const unsigned r0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)), magic));
+      const unsigned c0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)), magic));
+      const unsigned r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)), magic));
+      const unsigned c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)), magic));
+      unsigned t0, t1;
+      asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(r0 * (unsigned)Lay::PT_PITCH + c0 + pt_off));
+      asm volatile("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(r1 * (unsigned)Lay::PT_PITCH + c1 + pt_off));
       val |= (t0 < t1) << bit;
     }
-    const long long o = (long long)frame * cap + w;
-    desc[o * 32 + lane] = (uint8_t)val;
-    if (lane < 7) {   // the 28-byte cv::KeyPoint as seven coalesced 32-bit stores
-      float f;
-      switch (lane) {
-        case 0: f = level ? __fmul_rn((float)x, L.scale) : (float)x; break;
-        case 1: f = level ? __fmul_rn((float)y, L.scale) : (float)y; break;
-        case 2: f = L.patch_size; break;
-        case 3: f = angle; break;
-        case 4: f = (float)(q >> 24); break;
-        case 5: f = __int_as_float(level); break;
-        default: f = __int_as_float(-1); break;
-      }
-      reinterpret_cast<float*>(kps + o)[lane] = f;
-    }
+    desc[((long long)frame * cap + w_first + i) * 32 + lane] = (uint8_t)val;
+  }
+  if (failed && lane == 0) atomicOr(err_flag, 16);
+  if (lane < n) {   // the 28-byte cv::KeyPoint of the lane's keypoint
+    const OrbLevel& L = g.lv[my_level];
+    const int x = (int)(my_q & 0xfffu) + ORB_MIN_BORDER, y = (int)((my_q >> 12) & 0xfffu) + ORB_MIN_BORDER;
+    float* o = reinterpret_cast<float*>(kps + (long long)frame * cap + w_first + lane);
+    o[0] = my_level ? __fmul_rn((float)x, L.scale) : (float)x;
+    o[1] = my_level ? __fmul_rn((float)y, L.scale) : (float)y;
+    o[2] = L.patch_size;
+    o[3] = my_angle;
+    o[4] = (float)(my_q >> 24);
+    o[5] = __int_as_float(my_level);
+    o[6] = __int_as_float(-1);
   }
 }
 
@@ -316,11 +325,20 @@ void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const OrbGeom& g, int bat
   ++*launches;
 }
 
-void orb_launch_describe(const uint8_t* pyr, const uint8_t* blr, const uint32_t* kept, const int* kept_cnt, OrbKeypoint* kps,
-                         uint8_t* desc, int cap, int* counts, int* err_flag, const OrbGeom& g, int batch, cudaStream_t st,
+// ic_maps / pt_maps: per-level TMA descriptors of pyr (48 B x 31 rows) and blr (64 B x 37 rows), used only with ORB_B200_DESC_TMA=1 (the measured
+// alternative, see the kernel comment); the default stages with cp.async.
+void orb_launch_describe(const uint8_t* pyr, const uint8_t* blr, const void* ic_maps, const void* pt_maps, const uint32_t* kept, const int* kept_cnt,
+                         OrbKeypoint* kps, uint8_t* desc, int cap, int* counts, int* err_flag, const OrbGeom& g, int batch, cudaStream_t st,
                          long long* launches) {
-  const int per_cta = DESC_WARPS * DESC_KPW;
-  orb_describe_kernel<<<dim3((cap + per_cta - 1) / per_cta, batch), DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps,
-                                                                                                  desc, cap, counts, err_flag, g);
+  static const bool want_tma = getenv("ORB_B200_DESC_TMA") != nullptr;
+  static const OrbLevelMaps no_maps = {};
   ++*launches;
+  const int per_cta = DESC_WARPS * DESC_KPW;
+  const dim3 grid((cap + per_cta - 1) / per_cta, batch);
+  if (want_tma && ic_maps && pt_maps)
+    orb_describe_kernel<true><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g,
+                                                                *reinterpret_cast<const OrbLevelMaps*>(ic_maps),
+                                                                *reinterpret_cast<const OrbLevelMaps*>(pt_maps));
+  else
+    orb_describe_kernel<false><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g, no_maps, no_maps);
 }

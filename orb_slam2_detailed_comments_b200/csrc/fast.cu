@@ -29,17 +29,14 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
-#include <cuda.h>
-
 #include "orb_common.cuh"
+#include "orb_tma.cuh"
 
 #define FAST_THREADS 256
 #define FAST_WARPS 8
 #define FAST_WP 256      // window row pitch in smem: 16 B front pad + 15 alignment + ORB_FAST_TILE_W (219) + 6 halo = 256
 #define FAST_SP 240      // score plane row pitch: 15 + 219 + 4 <= 240
 #define FAST_MAXC 8      // cells per band (219 / 30 = 7) rounded up
-
-struct OrbFastMaps { CUtensorMap m[ORB_MAX_LEVELS]; };
 
 // cornerScore (OpenCV fast_score.cpp, 16-pixel ring, K = 8): S = max(max_arcs min_9(v - r), max_arcs min_9(r - v)) - 1,
 // clamped at 0. Lanes of every 32-bit value: lo = 256 + (v - r), hi = 256 + (r - v), both in [1, 511].
@@ -166,13 +163,11 @@ __device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const u
   }
 }
 
-__device__ __forceinline__ unsigned fast_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-
 template <bool SMALL_TH, bool TMA>   // SMALL_TH: iniTh <= 126 (carry-free byte compares); TMA: window by one bulk tensor copy, else per-thread cp.async
 __global__ void __launch_bounds__(FAST_THREADS)
 orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ tiles, int* __restrict__ cell_cnt,
                      uint32_t* __restrict__ cell_kp, int* __restrict__ err_flag, int win_rows, int sc_rows, int row_cap,
-                     const __grid_constant__ OrbGeom g, const __grid_constant__ OrbFastMaps maps) {
+                     const __grid_constant__ OrbGeom g, const __grid_constant__ OrbLevelMaps maps) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int prow = (sc_rows - 1) & ~1;                    // survivor rows per cell, even (sc_rows - 2 rounded up)
   uint8_t* win = smem;                                    // [win_rows][FAST_WP], pixel x at column 16 + x
@@ -207,17 +202,13 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   // 1. stage the window
   if (TMA) {
     if (tid == 0) {
-      const unsigned bar = fast_smem_u32(mbar);
-      if (fast_smem_u32(win) & 127u) atomicOr(err_flag, 16);   // TMA destination alignment
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      const unsigned bar = orb_smem_u32(mbar);
+      if (orb_smem_u32(win) & 127u) atomicOr(err_flag, 16);   // TMA destination alignment
+      orb_mbar_init(bar, 1);
       // the box is the level's full window height (hCell + 6 rows x 256 bytes); rows / bytes outside the plane arrive as zeros
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((L.hCell + 6) * FAST_WP) : "memory");
+      orb_mbar_expect_tx(bar, (unsigned)((L.hCell + 6) * FAST_WP));
       // tensor coordinates: byte column of the plane allocation (16-byte lead + level column xa - 16), row incl. the apron rows, frame
-      asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
-                       fast_smem_u32(win)),
-                   "l"(reinterpret_cast<unsigned long long>(&maps.m[level])), "r"(xa), "r"(iniY + ORB_APRON_ROWS), "r"(frame), "r"(bar)
-                   : "memory");
+      orb_tma_load_3d(orb_smem_u32(win), &maps.m[level], xa, iniY + ORB_APRON_ROWS, frame, bar);
     }
   } else {
     const int nvec = (X1 - xa + 15) >> 4;
@@ -226,7 +217,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
     const unsigned inv_nvec = (unsigned)(__frcp_rn((float)nvec) * 65536.f) + 1u;
     for (int i = tid; i < wh * nvec; i += FAST_THREADS) {
       const int y = (int)(((unsigned)i * inv_nvec) >> 16), v = i - y * nvec;
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(fast_smem_u32(win + y * FAST_WP + 16 + 16 * v)),
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(orb_smem_u32(win + y * FAST_WP + 16 + 16 * v)),
                    "l"(src + (long long)y * L.pitch + 16 * v));
     }
     asm volatile("cp.async.commit_group;");
@@ -259,12 +250,8 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   if (!TMA) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   if (TMA) {
-    const unsigned bar = fast_smem_u32(mbar);
-    unsigned done;
-    int spins = 0;
-    do {   // try_wait suspends the thread for a hardware time slice; the bound turns a lost copy into ORB_E_CAPACITY flag 16 instead of a hang
-      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
-    } while (!done && ++spins < (1 << 20));
+    const unsigned bar = orb_smem_u32(mbar);
+    const unsigned done = orb_mbar_wait(bar, 0);   // bounded: a lost copy becomes ORB_E_CAPACITY flag 16 instead of a hang
     if (!done && tid == 0) atomicOr(err_flag, 16);
   }
 
@@ -408,43 +395,6 @@ void orb_fast_build_tiles(const OrbGeom& g, std::vector<int4>& tiles) {
   }
 }
 
-// Per-level TMA descriptors over one pass workspace `pyr` holding `frames` frames: tensor [frames][plane rows][pitch bytes] u8 starting at
-// the plane allocation (apron rows and the 16-byte row lead included, so every window coordinate is >= 0), box = 256 bytes x (hCell + 6) rows.
-typedef CUresult (*OrbEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static OrbEncodeTiled orb_encode_tiled() {
-  static std::atomic<OrbEncodeTiled> fn{nullptr};
-  OrbEncodeTiled f = fn.load(std::memory_order_acquire);
-  if (!f) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
-      f = reinterpret_cast<OrbEncodeTiled>(p);
-    fn.store(f, std::memory_order_release);
-  }
-  return f;
-}
-
-int orb_fast_build_maps(const uint8_t* pyr, int frames, const OrbGeom& g, void* maps_out) {
-  OrbFastMaps* M = reinterpret_cast<OrbFastMaps*>(maps_out);
-  memset(M, 0, sizeof(*M));
-  OrbEncodeTiled enc = orb_encode_tiled();
-  if (!enc) return -1;
-  for (int l = 0; l < g.nlevels; ++l) {
-    const OrbLevel& L = g.lv[l];
-    void* base = const_cast<uint8_t*>(pyr) + L.plane_off - (size_t)ORB_APRON_ROWS * L.pitch - 16;
-    const cuuint64_t dims[3] = {(cuuint64_t)L.pitch, (cuuint64_t)(L.rows + 2 * ORB_APRON_ROWS), (cuuint64_t)frames};
-    const cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)g.frame_stride};
-    const cuuint32_t box[3] = {FAST_WP, (cuuint32_t)(L.hCell + 6), 1};
-    const cuuint32_t estr[3] = {1, 1, 1};
-    if (enc(&M->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-      return -1;
-  }
-  return 0;
-}
-size_t orb_fast_maps_bytes() { return sizeof(OrbFastMaps); }
-
 void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, int* cell_cnt, uint32_t* cell_kp, int* err_flag, const OrbGeom& g,
                      int batch, cudaStream_t st, long long* launches) {
   int max_h = 0;
@@ -462,7 +412,7 @@ void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, in
                       FAST_WP * 2 + 32 + 32 + FAST_MAXC + 8;   // KITTI: 37.5 KB
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
   // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
-  typedef void (*Kern)(const uint8_t*, const int4*, int*, uint32_t*, int*, int, int, int, const OrbGeom, const OrbFastMaps);
+  typedef void (*Kern)(const uint8_t*, const int4*, int*, uint32_t*, int*, int, int, int, const OrbGeom, const OrbLevelMaps);
   static const Kern kerns[2][2] = {{orb_fast_band_kernel<false, false>, orb_fast_band_kernel<false, true>},
                                    {orb_fast_band_kernel<true, false>, orb_fast_band_kernel<true, true>}};
   static std::atomic<bool> configured[64][2][2];
@@ -481,9 +431,9 @@ void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, in
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);   // the limit covers static + dynamic
     configured[dev][small][tma].store(true, std::memory_order_release);
   }
-  static const OrbFastMaps no_maps = {};
+  static const OrbLevelMaps no_maps = {};
   const dim3 grid(g.fast_tiles_total, batch);
   kern<<<grid, FAST_THREADS, smem, st>>>(pyr, reinterpret_cast<const int4*>(tiles), cell_cnt, cell_kp, err_flag, win_rows, sc_rows, row_cap, g,
-                                         tma ? *reinterpret_cast<const OrbFastMaps*>(maps) : no_maps);
+                                         tma ? *reinterpret_cast<const OrbLevelMaps*>(maps) : no_maps);
   ++*launches;
 }

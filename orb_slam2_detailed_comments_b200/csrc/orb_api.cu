@@ -36,7 +36,8 @@ struct orb_extractor {
     cudaStream_t st_side = nullptr;                       // high-priority side stream of the pass: quadtree (latency-bound) beside blur
     cudaEvent_t ev_fast = nullptr, ev_side = nullptr;
     int frames = 0;          // frames of the last pass run here
-    alignas(64) unsigned char fast_maps[ORB_FAST_MAPS_BYTES];   // per-level TMA descriptors of `pyr` (FAST window loads)
+    // per-level TMA descriptors of `pyr` / `blr`: FAST band windows (256 B x hCell + 6), IC_Angle windows (48 B x 31), descriptor patches (64 B x 37)
+    alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES];
     bool maps_ok = false;
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
     DevBuf st_sad;   // stereo: SAD of every kept match [chunk/2][cap]
@@ -280,7 +281,9 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     ENS(q_rawn, B * nl * sizeof(int));
       P.frames = 0;
       // TMA descriptors follow the (re)allocated pyramid buffer; without the driver entry point the kernel stages with cp.async
-      P.maps_ok = orb_fast_maps_bytes() == ORB_FAST_MAPS_BYTES && orb_fast_build_maps(P.pyr.as<uint8_t>(), (int)B, g, P.fast_maps) == 0;
+      P.maps_ok = orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 256, 0, P.fast_maps) == 0 &&
+                  orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 48, 31, P.ic_maps) == 0 &&
+                  orb_build_level_maps(P.blr.as<uint8_t>(), (int)B, g, 64, 37, P.pt_maps) == 0;
     }
 #undef ENS
     CU(cudaMemsetAsync(e->err.p, 0, sizeof(int), e->stream));
@@ -339,7 +342,7 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
   cudaStream_t sd = side >= 2 ? P.st_side : st;
   if (side == 1) { cudaEventRecord(P.ev_side, sq); cudaStreamWaitEvent(st, P.ev_side, 0); }
   if (side >= 2) { cudaEventRecord(P.ev_fast, st); cudaStreamWaitEvent(sd, P.ev_fast, 0); }      // blur done
-  orb_launch_describe(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.kept.as<uint32_t>(), kept_cnt, kps, desc, cap,
+  orb_launch_describe(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.maps_ok ? P.ic_maps : nullptr, P.maps_ok ? P.pt_maps : nullptr, P.kept.as<uint32_t>(), kept_cnt, kps, desc, cap,
                       counts_dev, e->err.as<int>(), g, n, sd, &e->launches);
   if (side >= 2) { cudaEventRecord(P.ev_side, sd); cudaStreamWaitEvent(st, P.ev_side, 0); }
   if (prof) cudaEventRecord(ev[5], st);

@@ -20,12 +20,12 @@ void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTa
 void orb_launch_fast(const uint8_t*, const void* tiles, const void* maps, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_fast_v1(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);   // round-1 kernel (A/B only)
 void orb_fast_build_tiles(const OrbGeom&, std::vector<int4>&);
-int orb_fast_build_maps(const uint8_t* pyr, int frames, const OrbGeom&, void* maps_out);   // 0 = ok; maps_out: ORB_FAST_MAPS_BYTES, 64-byte aligned
-size_t orb_fast_maps_bytes();
-#define ORB_FAST_MAPS_BYTES (128 * ORB_MAX_LEVELS)
+// per-level TMA descriptors (tma_maps.cu): 0 = ok; maps_out: ORB_LEVEL_MAPS_BYTES, 64-byte aligned; box_h == 0 -> hCell + 6 of each level
+int orb_build_level_maps(const uint8_t* base, int frames, const OrbGeom&, int box_w, int box_h, void* maps_out);
+#define ORB_LEVEL_MAPS_BYTES (128 * ORB_MAX_LEVELS)
 void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t*, int*, int*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_describe(const uint8_t*, const uint8_t*, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
+void orb_launch_describe(const uint8_t*, const uint8_t*, const void* ic_maps, const void* pt_maps, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
                          const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, int, float, float, float*, float*, int*, int*, int*,
                        unsigned short*, const OrbGeom&, int, cudaStream_t, long long*);
