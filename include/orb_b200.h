@@ -14,6 +14,7 @@
  *                                                                                     src/Frame.cc:158-168, 880-1176
  *   orb_hamming_knn           <- ORBmatcher::DescriptorDistance in the best/second-best scan
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
+ *   orb_hamming_knn_noalloc   <- (new, no reference counterpart) orb_hamming_knn without any allocation: fixed device scratch
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
  *   orb_search_for_initialization <- ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   src/ORBmatcher.cc:570-712
@@ -160,6 +161,21 @@ int orb_extractor_stage_times(orb_extractor* e, double* ms, int64_t* passes);
  * when any buffer is host memory. */
 int orb_hamming_knn(const uint8_t* query, int q_mem, int Q, const uint8_t* db, int db_mem, int64_t D,
                     int64_t index_base, int sentinel, orb_knn2* out, int out_mem, void* stream);
+/* Allocation-free variant of orb_hamming_knn. It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid allocation). It calls no
+ * cudaMalloc / cudaFree / allocating library routine: the per-chunk partial keys live in a file-scope device array of
+ * ORB_KNN_NOALLOC_SCRATCH_BYTES (4 MiB) that every GPU loading the library holds until exit. Same results as orb_hamming_knn.
+ * Requirements: query [Q][32] and db [D][32] in DEVICE memory, 16-byte aligned; out [Q] in DEVICE memory; the caller's CURRENT device is
+ * the one the buffers live on. Limits: Q <= ORB_KNN_NOALLOC_MAX_Q and ceil(D / 2^22) <= SCRATCH_BYTES / (16 * Q) (>= 64, i.e. D up to
+ * 2.6e8 rows at Q = 4096); beyond them the call returns ORB_E_CAPACITY (ORB_E_BADARG for misaligned buffers) and launches nothing.
+ * Asynchronous on `stream` (cudaStream_t or NULL). The first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress): make one warm-up call before capturing a graph. All calls on a device share the array; it keeps the last call's
+ * contents and nothing in it has to start at zero (each call writes every word it reads). Calls that OVERLAP on the GPU (different
+ * streams / threads) race on it: keep them on one stream. */
+#define ORB_KNN_NOALLOC_SCRATCH_BYTES (4 << 20)
+#define ORB_KNN_NOALLOC_MAX_Q 4096
+int orb_hamming_knn_noalloc(const uint8_t* query, int Q, const uint8_t* db, int64_t D, int64_t index_base, int sentinel,
+                            orb_knn2* out, void* stream);
 /* Merge `nshards` per-shard results (shard-major [nshards][Q], device memory, shards in ascending index order)
  * into out[Q] (device): equals one sequential scan over the concatenated database. */
 int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentinel, orb_knn2* out, void* stream);

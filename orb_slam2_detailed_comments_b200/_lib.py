@@ -35,7 +35,7 @@ SYMBOLS = [
     "orb_extractor_get_features_per_level", "orb_extractor_max_keypoints", "orb_extract_batch",
     "orb_extract_batch_device", "orb_extract_stereo_batch", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
-    "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn",
+    "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn", "orb_hamming_knn_noalloc",
     "orb_hamming_knn_merge", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
     "orb_search_by_projection", "orb_distinctive_descriptors",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_words", "orb_bow_transform",
@@ -114,6 +114,7 @@ def lib():
     L.orb_extractor_stage_times.argtypes = [vp, vp, vp]
     L.orb_hamming_knn.argtypes = [vp, i32, i32, vp, i32, i64, i64, i32, vp, i32, vp]
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
+    L.orb_hamming_knn_noalloc.argtypes = [vp, i32, vp, i64, i64, i32, vp, vp]
     L.orb_descriptor_distance_batch.argtypes = [vp, vp, i64, vp, vp]
     L.orb_matcher_launch_count.restype = i64
     L.orb_search_for_initialization.argtypes = [i32, vp, vp, vp, i32, vp, vp, vp, i32, i32, C.POINTER(OrbSearchParams), vp, vp, vp, vp]

@@ -8,9 +8,10 @@
 // the two smallest of all partial keys. INT pipe (popc) bound; the database streams through shared memory as
 // uint4 pairs read by broadcast, queries live in registers.
 #include <atomic>
+#include <mutex>
 #include <cuda_pipeline.h>
 
-#include "orb_common.cuh"
+#include "orb_host.h"
 
 #define KNN_THREADS 128
 #define KNN_QPT 2
@@ -271,4 +272,58 @@ double orb_popc_peak(int num_sms) {
   cudaEventDestroy(e1);
   cudaFree(d);
   return best;
+}
+
+// ---- allocation-free variant (no counterpart in the reference) -----------------------------
+// orb_hamming_knn keeps its per-chunk partial keys in a grow-only cudaMalloc'ed workspace, which callers under CUDA graph capture, tight
+// serving loops or harnesses that forbid allocation cannot use. This entry point runs the same two kernels with the partials in a
+// file-scope device array of fixed size: every GPU that loads the library holds these 4 MiB until the process exits.
+//   * In host code `g_knn_noalloc_scratch` is only a host-side stand-in for the symbol, NOT a device address: the address is resolved once
+//     per device (that device current) with cudaGetSymbolAddress and that pointer is what the kernels receive.
+//   * All calls on a device share the array and it keeps the previous call's contents. Nothing has to start at zero: the scan kernel writes
+//     every word [chunk][query][2] that the merge kernel of the same call reads (empty chunks write the "no candidate" key), so stale
+//     contents are never observed. Calls that OVERLAP on the GPU (two streams, two threads) race on it: issue them on one stream.
+static __device__ __align__(256) unsigned long long g_knn_noalloc_scratch[ORB_KNN_NOALLOC_SCRATCH_BYTES / 8];
+
+struct KnnNoAllocDev {
+  std::once_flag once;
+  cudaError_t err = cudaSuccess;
+  unsigned long long* scratch = nullptr;   // device address of g_knn_noalloc_scratch on this device
+  int num_sms = 0;
+};
+static KnnNoAllocDev g_knn_noalloc_dev[64];
+
+extern "C" int orb_hamming_knn_noalloc(const uint8_t* query, int Q, const uint8_t* db, int64_t D, int64_t index_base, int sentinel,
+                                       orb_knn2* out, void* stream) {
+  if (!query || !out || Q <= 0 || D < 0 || (D > 0 && !db) || sentinel < 1) return fail(ORB_E_BADARG, "bad argument");
+  if (index_base < 0 || index_base + D >= (1LL << 40)) return fail(ORB_E_BADARG, "index range exceeds 2^40");
+  if (((uintptr_t)query & 15) || ((uintptr_t)db & 15) || ((uintptr_t)out & 7))
+    return fail(ORB_E_BADARG, "orb_hamming_knn_noalloc: query / db must be 16-byte aligned DEVICE memory, out 8-byte aligned (no staging copy is possible without allocating)");
+  if (Q > ORB_KNN_NOALLOC_MAX_Q)
+    return fail(ORB_E_CAPACITY, "orb_hamming_knn_noalloc: Q = %d exceeds the fixed scratch (max %d queries per call; use orb_hamming_knn)", Q, ORB_KNN_NOALLOC_MAX_Q);
+  const long long words = ORB_KNN_NOALLOC_SCRATCH_BYTES / 8;
+  const long long fit_chunks = words / (2LL * Q);                       // chunks whose [Q][2] partial keys fit the array (>= 64)
+  const long long min_chunks = (D + (1LL << 22) - 1) >> 22;             // a chunk holds < 2^22 rows (packed local row index)
+  if (min_chunks > fit_chunks)
+    return fail(ORB_E_CAPACITY, "orb_hamming_knn_noalloc: D = %lld rows x Q = %d needs %lld chunks, the fixed scratch holds %lld (use orb_hamming_knn)",
+                (long long)D, Q, min_chunks, fit_chunks);
+  int dev = 0;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback): %s", cudaGetErrorString(ce)); }
+  if (dev < 0 || dev >= 64) return fail(ORB_E_BADARG, "device %d out of range", dev);
+  KnnNoAllocDev& S = g_knn_noalloc_dev[dev];
+  // set-up, once per device, with that device current (the caller's current device is the one the buffers live on)
+  std::call_once(S.once, [&S, dev]() {
+    void* p = nullptr;
+    S.err = cudaGetSymbolAddress(&p, g_knn_noalloc_scratch);
+    if (S.err == cudaSuccess) S.err = cudaDeviceGetAttribute(&S.num_sms, cudaDevAttrMultiProcessorCount, dev);
+    S.scratch = reinterpret_cast<unsigned long long*>(p);
+  });
+  if (S.err != cudaSuccess || !S.scratch)
+    return fail(ORB_E_CUDA, "orb_hamming_knn_noalloc: cudaGetSymbolAddress(g_knn_noalloc_scratch) on device %d: %s", dev, cudaGetErrorString(S.err));
+  long long nchunks = orb_knn_num_chunks(Q, D, S.num_sms);
+  if (nchunks > fit_chunks) nchunks = fit_chunks;   // >= min_chunks, checked above
+  orb_launch_knn(query, Q, db, D, index_base, sentinel, S.scratch, (int)nchunks, reinterpret_cast<OrbKnn2*>(out), (cudaStream_t)stream);
+  CU(cudaGetLastError());
+  return ORB_OK;
 }
