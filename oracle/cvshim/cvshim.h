@@ -130,11 +130,49 @@ class Mat {
 
   orb_oracle::Img img() const { return orb_oracle::Img{data, cols, rows, (int)step}; }
 
+  // ---- float patches of Frame::ComputeStereoMatches (src/Frame.cc:1035-1068): convertTo(CV_32F), Mat::ones, scalar * Mat, Mat - Mat ----
+  void convertTo(Mat& m, int rtype) const {   // 8U -> 32F (or a same-type copy); `m` may be *this (a view): the new buffer replaces it
+    Mat out(rows, cols, rtype);
+    for (int y = 0; y < rows; ++y)
+      for (int x = 0; x < cols; ++x) {
+        const float v = type_ == CV_32F ? at<float>(y, x) : (float)at<uchar>(y, x);
+        if (rtype == CV_32F) out.at<float>(y, x) = v; else out.at<uchar>(y, x) = (uchar)v;
+      }
+    m = out;
+  }
+  static Mat ones(int r, int c, int type) {
+    assert(type == CV_32F);
+    Mat m(r, c, type);
+    for (int y = 0; y < r; ++y) for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.f;
+    return m;
+  }
+
  private:
   static size_t esz(int type) { return type == CV_32F ? 4 : 1; }
   std::shared_ptr<uchar> store_;
   int type_;
 };
+
+inline Mat operator*(float k, const Mat& a) {   // MatExpr scale: float32 product per element
+  assert(a.type() == CV_32F);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = k * a.at<float>(y, x);
+  return m;
+}
+inline Mat operator-(const Mat& a, const Mat& b) {
+  assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = a.at<float>(y, x) - b.at<float>(y, x);
+  return m;
+}
+enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
+inline double norm(const Mat& a, const Mat& b, int normType) {   // cv::norm(a, b, NORM_L1) for 32F: sum |a - b| accumulated in double
+  assert(normType == NORM_L1 && a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+  (void)normType;
+  double s = 0;
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) s += std::fabs((double)a.at<float>(y, x) - (double)b.at<float>(y, x));
+  return s;
+}
 
 class _InputArray {
  public:

@@ -183,6 +183,17 @@ def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
     return lib().orb_oracle_descriptor_distance(_p(a), _p(b))
 
 
+def three_maxima(sizes: np.ndarray) -> np.ndarray:
+    """ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2026-2068) on bin sizes [L] -> (ind1, ind2, ind3)."""
+    L = lib()
+    L.orb_oracle_three_maxima.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    L.orb_oracle_three_maxima.restype = None
+    sizes = np.ascontiguousarray(sizes, np.int32)
+    out = np.zeros(3, np.int32)
+    L.orb_oracle_three_maxima(_p(sizes), len(sizes), _p(out))
+    return out
+
+
 def hamming_knn(q: np.ndarray, db: np.ndarray, index_base: int = 0, sentinel: int = 256, nthreads: int = 1) -> np.ndarray:
     q = np.ascontiguousarray(q, np.uint8)
     db = np.ascontiguousarray(db, np.uint8)

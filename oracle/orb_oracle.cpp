@@ -614,6 +614,26 @@ int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_e
 namespace {
 constexpr int GRID_COLS = 64, GRID_ROWS = 48, HISTO_LENGTH = 30;   // include/Frame.h FRAME_GRID_COLS / ROWS, include/ORBmatcher.h:54
 
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2026-2068) on the bin sizes: indices of the three fullest bins (first bin wins ties),
+// the 2nd / 3rd dropped when below 10 % of the fullest (float compare as written). Pinned against the reference's own function by
+// tests/test_reference_binary.py::test_three_maxima_equals_reference.
+static void three_maxima(const int* size, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  for (int i = 0; i < L; ++i) {
+    const int s = size[i];
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+extern "C" void orb_oracle_three_maxima(const int32_t* sizes, int L, int32_t* out3) {
+  int i1 = -1, i2 = -1, i3 = -1;
+  three_maxima(sizes, L, i1, i2, i3);
+  out3[0] = i1; out3[1] = i2; out3[2] = i3;
+}
+
 struct FrameGrid {   // mGrid, mfGridElementWidthInv / HeightInv (src/Frame.cc:200-202, 432-460)
   float min_x, min_y, inv_w, inv_h;
   std::vector<int> cell[GRID_COLS][GRID_ROWS];
@@ -753,16 +773,9 @@ int orb_oracle_search_by_projection(const orb_oracle_kp* kps, const uint8_t* des
     }
   }
   if (prm->check_orientation) {
-    // ComputeThreeMaxima (:2026-2068)
-    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
-    for (int i = 0; i < HISTO_LENGTH; ++i) {
-      const int s = (int)rot_hist[i].size();
-      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
-      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
-      else if (s > max3) { max3 = s; ind3 = i; }
-    }
-    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
-    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    int ind1 = -1, ind2 = -1, ind3 = -1, hsize[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; ++i) hsize[i] = (int)rot_hist[i].size();
+    three_maxima(hsize, HISTO_LENGTH, ind1, ind2, ind3);   // ComputeThreeMaxima (:2026-2068)
     for (int i = 0; i < HISTO_LENGTH; ++i) {   // :1849-1860
       if (i == ind1 || i == ind2 || i == ind3) continue;
       for (const auto& e : rot_hist[i]) {
@@ -814,15 +827,9 @@ int orb_oracle_search_for_initialization(const orb_oracle_kp* kps, const uint8_t
     }
   }
   if (prm->check_orientation) {
-    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
-    for (int i = 0; i < HISTO_LENGTH; ++i) {
-      const int sz = (int)rotHist[i].size();
-      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
-      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
-      else if (sz > max3) { max3 = sz; ind3 = i; }
-    }
-    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
-    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    int ind1 = -1, ind2 = -1, ind3 = -1, hsize[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; ++i) hsize[i] = (int)rotHist[i].size();
+    three_maxima(hsize, HISTO_LENGTH, ind1, ind2, ind3);   // ComputeThreeMaxima (:2026-2068)
     for (int i = 0; i < HISTO_LENGTH; ++i) {
       if (i == ind1 || i == ind2 || i == ind3) continue;
       for (int idx1 : rotHist[i])
@@ -916,15 +923,9 @@ int orb_oracle_search_for_triangulation(const uint8_t* desc1, const orb_oracle_k
     }
   }
   if (check_orientation) {
-    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;   // ComputeThreeMaxima (:2026-2068)
-    for (int i = 0; i < HISTO_LENGTH; ++i) {
-      const int sz = (int)rotHist[i].size();
-      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
-      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
-      else if (sz > max3) { max3 = sz; ind3 = i; }
-    }
-    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
-    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    int ind1 = -1, ind2 = -1, ind3 = -1, hsize[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; ++i) hsize[i] = (int)rotHist[i].size();
+    three_maxima(hsize, HISTO_LENGTH, ind1, ind2, ind3);   // ComputeThreeMaxima (:2026-2068)
     for (int i = 0; i < HISTO_LENGTH; ++i) {
       if (i == ind1 || i == ind2 || i == ind3) continue;
       for (int idx1 : rotHist[i]) {
@@ -993,15 +994,9 @@ int orb_oracle_search_by_bow(const uint8_t* kf_desc, const orb_oracle_kp* kf_kps
     }
   }
   if (check_orientation) {
-    int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
-    for (int i = 0; i < HISTO_LENGTH; ++i) {
-      const int sz = (int)rotHist[i].size();
-      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
-      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
-      else if (sz > max3) { max3 = sz; ind3 = i; }
-    }
-    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
-    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    int ind1 = -1, ind2 = -1, ind3 = -1, hsize[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; ++i) hsize[i] = (int)rotHist[i].size();
+    three_maxima(hsize, HISTO_LENGTH, ind1, ind2, ind3);   // ComputeThreeMaxima (:2026-2068)
     for (int i = 0; i < HISTO_LENGTH; ++i) {
       if (i == ind1 || i == ind2 || i == ind3) continue;
       for (int idx : rotHist[i]) {

@@ -76,6 +76,8 @@ void orb_oracle_sincos(float angle_rad, int libm, float* s, float* c);
 int orb_oracle_distribute(const orb_oracle_kp* in, int n, int minx, int maxx, int miny, int maxy, int nfeat,
                           orb_oracle_kp* out, int cap);
 
+/* ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:2026-2068) on L bin sizes -> out3 = {ind1, ind2, ind3}. */
+void orb_oracle_three_maxima(const int32_t* sizes, int L, int32_t* out3);
 /* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2073-2093). */
 int orb_oracle_descriptor_distance(const uint8_t* a, const uint8_t* b);
 /* Brute-force k=2 with the reference's strict-< update rule (src/ORBmatcher.cc:304-335); sentinel

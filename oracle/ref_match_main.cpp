@@ -11,8 +11,8 @@
 //   gen_three_maxima.inc  src/ORBmatcher.cc:2026-2068    ORBmatcher::ComputeThreeMaxima
 //   gen_scan.inc          src/ORBmatcher.cc:304-335      best / second-best scan of SearchByBoW (sentinel 256)
 //   gen_accept.inc        src/ORBmatcher.cc:339-343      `if (best <= TH_LOW) { if ((float)best < mfNNratio * (float)second) {`
-//   gen_scan_init.inc     src/ORBmatcher.cc:611-634      scan of SearchForInitialization (sentinel INT_MAX, vMatchedDistance skip)
-//   gen_accept_init.inc   src/ORBmatcher.cc:637-640      `if (best <= TH_LOW) { if (best < (float)second * mfNNratio) {`
+//   gen_scan_init.inc     src/ORBmatcher.cc:611-637      scan of SearchForInitialization (sentinel INT_MAX, vMatchedDistance skip)
+//   gen_accept_init.inc   src/ORBmatcher.cc:641-645      `if (best <= TH_LOW) { if (best < (float)second * mfNNratio) {`
 //   gen_distinctive.inc   src/MapPoint.cc:468-510        all-pairs distances + least-median row of ComputeDistinctiveDescriptors
 //   gen_stereo.inc        src/Frame.cc:880-1176          Frame::ComputeStereoMatches
 // FORB::distance (Thirdparty/DBoW2/DBoW2/FORB.cpp:81-103, the verbatim twin of DescriptorDistance) is linked in compiled unmodified.
@@ -91,7 +91,7 @@ void ORBmatcher::Scan(const cv::Mat& Q, const cv::Mat& D, int32_t* out) {
   }
 }
 
-// src/ORBmatcher.cc:611-640 with every keypoint of F2 in the search window
+// src/ORBmatcher.cc:611-645 with every keypoint of F2 in the search window
 void ORBmatcher::ScanInit(const cv::Mat& Q, const cv::Mat& D, const std::vector<int>& vMatchedDistance, int32_t* out) {
   FrameDescs F2;
   F2.mDescriptors = D;

@@ -93,3 +93,79 @@ def ref_bow(voc_path: str, frames, levelsup: int = 4):
         out.append((bow, fv))
     assert pos == len(buf)
     return out
+
+
+# ---- oracle/_ref/orb_ref_match: function bodies cut out of src/ORBmatcher.cc, src/MapPoint.cc, src/Frame.cc by line range at build time
+# (oracle/Makefile `_ref/gen_stamp`) and compiled inside oracle/ref_match_main.cpp, plus DBoW2's FORB::distance compiled unmodified.
+MATCH_BIN = os.path.join(ROOT, "oracle", "_ref", "orb_ref_match")
+
+
+def match_available() -> bool:
+    return os.access(MATCH_BIN, os.X_OK)
+
+
+def _run_match(mode: str, payload: bytes) -> bytes:
+    with tempfile.TemporaryDirectory() as d:
+        fin, fout = os.path.join(d, "in.bin"), os.path.join(d, "out.bin")
+        with open(fin, "wb") as f:
+            f.write(payload)
+        subprocess.run([MATCH_BIN, mode, fin, fout], check=True, timeout=600)
+        return open(fout, "rb").read()
+
+
+def ref_distance(a: np.ndarray, b: np.ndarray):
+    """n descriptor pairs -> (FORB::distance [n], ORBmatcher::DescriptorDistance [n]) by the reference's own code."""
+    a, b = np.ascontiguousarray(a, np.uint8).reshape(-1, 32), np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+    n = len(a)
+    inter = np.concatenate([a, b], axis=1)   # a[i], b[i] interleaved
+    out = np.frombuffer(_run_match("distance", struct.pack("<i", n) + inter.tobytes()), "<i4").reshape(n, 2)
+    return out[:, 0].copy(), out[:, 1].copy()
+
+
+def ref_scan(q: np.ndarray, db: np.ndarray, ratio: float = 0.6, matched_distance=None):
+    """The reference's best / second-best loop over every database row in index order. matched_distance=None: SearchByBoW form
+    (src/ORBmatcher.cc:304-343, sentinel 256, accept `(float)best < ratio * (float)second`); otherwise the SearchForInitialization form
+    (:611-645, sentinel INT_MAX, rows with vMatchedDistance[i] <= dist skipped, accept `best < (float)second * ratio`).
+    Returns int32 [Q, 4]: best, second, best index (-1 = none), accepted."""
+    q, db = np.ascontiguousarray(q, np.uint8).reshape(-1, 32), np.ascontiguousarray(db, np.uint8).reshape(-1, 32)
+    payload = struct.pack("<iif", len(q), len(db), ratio) + q.tobytes() + db.tobytes()
+    mode = "scan"
+    if matched_distance is not None:
+        payload += np.ascontiguousarray(matched_distance, "<i4").tobytes()
+        mode = "scan_init"
+    return np.frombuffer(_run_match(mode, payload), "<i4").reshape(len(q), 4).copy()
+
+
+def ref_three_maxima(sizes: np.ndarray) -> np.ndarray:
+    """sizes int32 [n, L] (bin populations) -> int32 [n, 3] (ind1, ind2, ind3) by ORBmatcher::ComputeThreeMaxima."""
+    sizes = np.ascontiguousarray(sizes, "<i4")
+    n, L = sizes.shape
+    return np.frombuffer(_run_match("three_maxima", struct.pack("<ii", n, L) + sizes.tobytes()), "<i4").reshape(n, 3).copy()
+
+
+def ref_distinctive(desc: np.ndarray, offsets: np.ndarray) -> np.ndarray:
+    """CSR of observation descriptors -> int32 [P, 2] (BestIdx, BestMedian) by the loop of MapPoint::ComputeDistinctiveDescriptors."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    P = len(offsets) - 1
+    payload = struct.pack("<i", P)
+    for p in range(P):
+        rows = desc[offsets[p]:offsets[p + 1]]
+        payload += struct.pack("<i", len(rows)) + rows.tobytes()
+    return np.frombuffer(_run_match("distinctive", payload), "<i4").reshape(P, 2).copy()
+
+
+def ref_stereo(scale, levels_left, levels_right, kl, dl, kr, dr, bf: float, b: float):
+    """Frame::ComputeStereoMatches (src/Frame.cc:880-1176) itself on padded pyramid levels, keypoints (28-byte cv::KeyPoint records) and
+    descriptors of both images -> (mvuRight [nL], mvDepth [nL])."""
+    nl = len(scale)
+    payload = struct.pack("<iff", nl, bf, b) + np.ascontiguousarray(scale, "<f4").tobytes()
+    for levels, k, d in ((levels_left, kl, dl), (levels_right, kr, dr)):
+        for im in levels:
+            im = np.ascontiguousarray(im, np.uint8)
+            payload += struct.pack("<ii", im.shape[1], im.shape[0]) + im.tobytes()
+        k = np.ascontiguousarray(k)
+        assert k.dtype.itemsize == 28
+        payload += struct.pack("<i", len(k)) + k.tobytes() + np.ascontiguousarray(d, np.uint8).tobytes()
+    out = np.frombuffer(_run_match("stereo", payload), "<f4")
+    n = len(kl)
+    return out[:n].copy(), out[n:2 * n].copy()

@@ -160,3 +160,21 @@ def test_stereo_matches_cv2_composition(oracle, path):
     assert np.array_equal(ur.view(np.uint32), g["uright"].view(np.uint32))
     assert np.array_equal(dp.view(np.uint32), g["depth"].view(np.uint32))
     assert kept == int((g["uright"] >= 0).sum()) and kept > 200
+
+
+def test_libm_trig_descriptor_bit_agreement(oracle):
+    """DESIGN.md §2 canonicalisation 2: cosf / sinf (src/ORBextractor.cc:184-186) are libm calls, not correctly rounded by contract; the
+    canonical sincos (double reduction + kernels, one rounding) is what oracle and CUDA share. This diagnostic reports how many descriptor
+    bits change when the oracle calls glibc's cosf / sinf instead (flag LIBM_TRIG) — north_star's "descriptor bit agreement reported"."""
+    total = diff = rows = rows_diff = 0
+    for name, seed in (("tum", 1234), ("kitti", 1236), ("euroc", 1237)):
+        w, h, nf = synth.CONFIGS[name]
+        img = synth.synth_frame(w, h, seed)
+        k0, d0, _ = oracle.OracleExtractor(nf, 1.2, 8, 20, 7)(img)
+        k1, d1, _ = oracle.OracleExtractor(nf, 1.2, 8, 20, 7, flags=oracle.LIBM_TRIG)(img)
+        assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8))          # keypoints and angles do not depend on cosf / sinf
+        x = np.unpackbits(d0 ^ d1, axis=1).sum(axis=1)
+        total += d0.size * 8; diff += int(x.sum()); rows += len(d0); rows_diff += int((x > 0).sum())
+    agreement = 1.0 - diff / total
+    print(f"descriptor bit agreement canonical vs glibc cosf/sinf: {agreement:.7f} ({diff} of {total} bits, {rows_diff} of {rows} rows)")
+    assert agreement >= 0.9999

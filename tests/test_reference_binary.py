@@ -28,6 +28,11 @@ CASES = [
     ("odd", 333, 257, 700, 2, 1239, (1.2, 8, 20, 7)),
     ("coarse", 480, 360, 300, 2, 77, (1.5, 4, 20, 7)),
     ("strict", 480, 360, 600, 1, 78, (1.2, 8, 40, 25)),
+    # tiny quotas (levels with a quota of 0 or 1; N < 4 * nIni in DistributeOctTree) and a 5:1 image (nIni = 5 quadtree roots)
+    ("nf5", 640, 480, 5, 1, 90, (1.2, 8, 20, 7)),
+    ("nf20", 640, 480, 20, 1, 91, (1.2, 8, 20, 7)),
+    ("nf50", 752, 480, 50, 1, 92, (1.2, 8, 20, 7)),
+    ("wide5to1", 1000, 200, 500, 1, 93, (1.2, 6, 20, 7)),
 ]
 
 
