@@ -39,6 +39,16 @@ WORKLOADS = {
 KNN_Q, KNN_D = 2000, 1_000_000
 
 
+def shared_config(workload: str) -> dict:
+    """The `config` object BOTH arms print, key for key and value for value (the driver compares them): what is computed, on which synthetic
+    input. Everything that differs between the arms (images per step, timing method, parallelism) goes to the line's `run` object."""
+    label, W, H, nf, B = WORKLOADS[workload]
+    return {"workload": label, "width": W, "height": H, "nfeatures": nf, "levels": 8, "scale_factor": 1.2, "fast_thresholds": [20, 7],
+            "frames": "synth.synth_batch: 64 distinct seeded frames per rank (8 at 4K), tiled with per-copy shifts",
+            "l2": "GPU arm: inputs larger than L2 (%.0f MB of frames per step per GPU, + pyramid workspaces), no flush needed; "
+                  "reference arm: host cores, not applicable" % (B * W * H / 1e6)}
+
+
 def _peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -160,7 +170,7 @@ def run_reference(args):
     label, W, H, nf, _ = WORKLOADS[args.workload]
     cores = _host_cores()
     n = max(2 * cores, 16)   # images per step: a bounded sample of the workload
-    frames = synth.synth_batch(W, H, n, seed0=4321, distinct=min(8, n))
+    frames = synth.synth_batch(W, H, n, seed0=4321, distinct=min(64, n))
     if os.access(REF_BIN, os.X_OK):
         kind = "reference"
         how = "one reference ORBextractor (src/ORBextractor.cc compiled -O3 + AVX2 against oracle/cvshim) per thread"
@@ -182,7 +192,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": label, "images_per_step": n, "timing": "host wall clock"},
+        "config": shared_config(args.workload),
+        "run": {"images_per_step": n, "timing": "host wall clock", "ranks": "rank 0's host cores only, whatever --gpus is: at N > 1 the ratio is "
+                "N GPUs against ONE host's cores"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                          "sample": f"{n} images per step x {args.steps} steps, {how}"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -334,6 +346,27 @@ def bench_latency(ex, frames_host, iters=200):
             "median": 1e3 * ts[len(ts) // 2], "p99": 1e3 * ts[int(len(ts) * 0.99)], "calls": iters}
 
 
+def bench_cpp_dropin_latency(frame: np.ndarray, nf: int):
+    """The call Frame::ExtractORB really makes: the C++ drop-in class (cpp/ORBextractor.cc) through tests/cpp/test_dropin --latency, a separate
+    process with its own CUDA context; pageable cv::Mat in, std::vector<cv::KeyPoint> + cv::Mat out, mvImagePyramid filled / not filled."""
+    exe = os.path.join(ROOT, "tests", "cpp", "test_dropin")
+    if not os.access(exe, os.X_OK):
+        return {"unavailable": "tests/cpp/test_dropin not built"}
+    H, W = frame.shape
+    with tempfile.NamedTemporaryFile(suffix=".raw", delete=False) as f:
+        f.write(np.ascontiguousarray(frame).tobytes())
+        path = f.name
+    try:
+        r = subprocess.run([exe, "--latency", path, str(W), str(H), str(nf), "300"], capture_output=True, text=True, timeout=300)
+        if r.returncode != 0:
+            return {"unavailable": "test_dropin --latency failed: " + (r.stderr or r.stdout)[-300:]}
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as e:   # noqa: BLE001
+        return {"unavailable": str(e)[:300]}
+    finally:
+        os.unlink(path)
+
+
 def bench_stereo_e2e(ex, frames_host, steps, warmup, world, bf=386.1448, b=0.5372):
     """Secondary: the stereo Frame constructor (two operator() calls + Frame::ComputeStereoMatches, src/Frame.cc:158-168,
     880-1176) through orb_extract_stereo_batch with pinned host buffers; frames (2p, 2p+1) are treated as left / right."""
@@ -483,6 +516,82 @@ def cpu_bow_rate(voc, base, threads, frames=4096):
     return frames / dt, dt
 
 
+def bench_sustained(ex, frames_dev, B, world, local, rank, seconds=2.0):
+    """The headline workload back to back for >= `seconds` (the default timed region is ~0.1 s: too short for the power / clock governor to show):
+    resident images/s over the whole loop with its own clock record."""
+    import torch
+    st = torch.cuda.ExternalStream(ex._L.orb_extractor_stream(ex._h))
+    kps, desc, counts = ex.extract_batch_device(frames_dev, sync=True)
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(world)
+    t0 = time.perf_counter()
+    e0.record(st)
+    steps = 0
+    while True:
+        for _ in range(8):
+            ex.extract_batch_device(frames_dev, kps, desc, counts, sync=False)
+        steps += 8
+        e1.record(st)
+        e1.synchronize()
+        done = time.perf_counter() - t0 >= seconds
+        if world > 1:   # every rank runs the same number of steps
+            import torch.distributed as dist
+            t = torch.tensor([0 if done else 1], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            done = int(t.item()) == 0
+        if done:
+            break
+    _barrier(world)
+    ms = _max_over_ranks(e0.elapsed_time(e1), world)
+    clocks = sampler.stop() if sampler else {}
+    return {"value": B * world * steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "seconds": ms * 1e-3, "clocks": clocks,
+            "what": "the headline workload back to back, frames resident in HBM, CUDA events around the whole loop"}
+
+
+def bench_other_config(name, rank, world, local, steps=4, warmup=3):
+    """One of the other BASELINE configs (TUM, EuRoC, 4K) in the same line: resident value, e2e, pipeline roofline fraction, clocks."""
+    import torch
+    import orb_slam2_detailed_comments_b200 as pkg
+    label, W, H, nf, B = WORKLOADS[name]
+    frames = synth.synth_batch(W, H, B, seed0=777 + 100000 * rank, distinct=min(32, B) if name != "4k" else min(4, B))
+    ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, device=local)
+    frames_dev = torch.from_numpy(frames).cuda()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, launches, stage_ms, passes, nkp = bench_extract_resident(ex, frames_dev, steps, warmup, world)
+    clocks = sampler.stop() if sampler else {}
+    value = B * world * steps / (ms * 1e-3)
+    e_ms, h2d, d2h, _ = bench_extract_e2e(ex, frames, 2, 1, world)
+    ex.close()
+    del frames_dev
+    torch.cuda.empty_cache()
+    peak, _ = _peaks()
+    A = geometry.algorithmic_bytes(W, H, nf)
+    return {"config": shared_config(name), "images_per_step_per_gpu": B, "steps": steps, "value": value, "unit": UNIT, "ms_per_step": ms / steps,
+            "e2e": {"value": B * world * 2 / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": 2},
+            "pipeline": {"algorithmic_bytes_per_image": A, "achieved": value / world * A / 1e9, "frac": value / world * A / 1e9 / peak},
+            "stages_ms_per_step": {k: v / steps for k, v in stage_ms.items()}, "keypoints_per_image": nkp / B,
+            "gpu_launches": int(launches), "clocks": clocks}
+
+
+def knn_parity(rank, world, out_merged, q, nsample=64):
+    """N > 1: the merged result of the sharded scan (all_gather + device merge) == ONE scan of rank 0 over the concatenated shards, for the
+    first `nsample` queries. Rank 0 regenerates every rank's shard from its generator seed (same device type, same seed -> same bytes)."""
+    import torch
+    from orb_slam2_detailed_comments_b200 import matcher
+    if world == 1 or rank != 0:
+        return None
+    per = KNN_D // world
+    shards = []
+    for r in range(world):
+        g = torch.Generator(device="cuda").manual_seed(100 + r)
+        shards.append(torch.randint(0, 256, (per, 32), dtype=torch.uint8, device="cuda", generator=g))
+    full = torch.cat(shards)
+    one = matcher.hamming_knn_device(q[:nsample].contiguous(), full)
+    torch.cuda.synchronize()
+    return bool(torch.equal(one, out_merged[:nsample]))
+
+
 def bench_knn(rank, world, steps, warmup):
     """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks, one all_gather
     of the per-query records + device merge when world > 1. pairs/s = Q*D / time (max over ranks)."""
@@ -518,7 +627,8 @@ def bench_knn(rank, world, steps, warmup):
     ms = _max_over_ranks(e0.elapsed_time(e1), world)
     launches = _lib.lib().orb_matcher_launch_count() - l0
     pairs = KNN_Q * per * world * steps
-    return pairs / (ms * 1e-3), ms / steps, launches
+    parity = knn_parity(rank, world, out, q)
+    return pairs / (ms * 1e-3), ms / steps, launches, parity
 
 
 def run_b200(args):
@@ -530,7 +640,7 @@ def run_b200(args):
     label, W, H, nf, B = WORKLOADS[args.workload]
     if args.batch:
         B = args.batch
-    frames = synth.synth_batch(W, H, B, seed0=1234 + 100000 * rank, distinct=8)
+    frames = synth.synth_batch(W, H, B, seed0=1234 + 100000 * rank, distinct=min(64, B) if args.workload != "4k" else min(8, B))
     ex = pkg.ORBextractor(nf, 1.2, 8, 20, 7, device=local)
     frames_dev = torch.from_numpy(frames).cuda()
 
@@ -544,7 +654,7 @@ def run_b200(args):
     e2e_value = B * world * e_steps / (e_ms * 1e-3)
 
     st_ms, st_matches = bench_stereo_e2e(ex, frames, e_steps, args.warmup, world)
-    knn_rate, knn_ms, knn_launches = bench_knn(rank, world, max(args.steps, 5), args.warmup)
+    knn_rate, knn_ms, knn_launches, knn_par = bench_knn(rank, world, max(args.steps, 5), args.warmup)
     g_steps = max(args.steps, 5)
     g_ms, g_matches, g_launches = bench_guided(W, H, g_steps, args.warmup, world)
     bow_voc, bow_base = _bow_inputs()
@@ -555,6 +665,15 @@ def run_b200(args):
         ex1 = pkg.ORBextractor(nf, 1.2, 8, 20, 7, device=local)   # its own handle: single-image workspaces
         latency = bench_latency(ex1, frames)
         ex1.close()
+        latency["cpp_dropin"] = bench_cpp_dropin_latency(frames[0], nf)
+
+    sustained = bench_sustained(ex, frames_dev, B, world, local, rank)
+    others = {}
+    if args.workload == "kitti" and not args.batch and not args.only_headline:
+        del frames_dev
+        torch.cuda.empty_cache()
+        for name in ("tum", "euroc", "4k"):
+            others[name] = bench_other_config(name, rank, world, local)
 
     if rank != 0:
         return
@@ -600,9 +719,9 @@ def run_b200(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": label, "images_per_step_per_gpu": B, "width": W, "height": H, "nfeatures": nf,
-                   "l2": "inputs larger than L2 (%.0f MB of frames per step, +pyramid workspaces)" % (B * W * H / 1e6),
-                   "keypoints_per_image": nkp / B, "parallelism": f"frames sharded over {world} GPU(s), no collective"},
+        "config": shared_config(args.workload),
+        "run": {"images_per_step_per_gpu": B, "keypoints_per_image": nkp / B, "parallelism": f"frames sharded over {world} GPU(s), no collective",
+                "timing": "CUDA events on the extractor's stream, max over ranks"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e_steps, "ms_per_step": e_ms / e_steps, "api": "orb_extract_batch (pinned host in/out)"},
@@ -623,9 +742,13 @@ def run_b200(args):
                 "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
                           + (", NCCL all_gather + device top-2 merge" if world > 1 else ""),
                 "ms_per_step": knn_ms, "gpu_launches": int(knn_launches),
+                "parity": knn_par if world > 1 else "n/a at 1 GPU (no merge; tests/test_gpu_knn.py checks the scan)",
                 "roofline": {"bound": "popc", "achieved": knn_rate * 8 / world, "peak": popc_peak, "unit": "popc.b32/s",
                              "frac": (knn_rate * 8 / world / popc_peak) if popc_peak else None}},
     }
+    line["sustained"] = sustained
+    if others:
+        line["configs"] = others
     if _NUMA:
         line["e2e"]["numa"] = _NUMA   # this rank's binding (rank 0); every rank binds to its own GPU's node
     if world == 1:
@@ -662,6 +785,7 @@ def main():
     ap.add_argument("--workload", default="kitti", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="images per step per GPU (default: per workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--only-headline", action="store_true", help="skip the `configs` entries (TUM / EuRoC / 4K)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

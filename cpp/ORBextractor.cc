@@ -33,7 +33,52 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int
   mvImagePyramid.resize(nlevels);
 }
 
-ORBextractor::~ORBextractor() { orb_extractor_destroy(mpHandle); }
+ORBextractor::~ORBextractor() { orb_extractor_destroy(mpHandle); }   // before the Pinned members are freed: nothing is in flight any more
+
+void ORBextractor::Pinned::ensure(size_t need) {
+  if (need <= bytes) return;
+  orb_host_free(p);
+  p = nullptr; bytes = 0;
+  check(orb_host_alloc(need, &p), "orb_host_alloc");
+  bytes = need;
+}
+ORBextractor::Pinned::~Pinned() { orb_host_free(p); }
+
+void ORBextractor::SetPyramidDownload(bool on) {
+  mbDownloadPyramid = on;
+  if (!on) {
+    orb_extractor_set_pyramid_download(mpHandle, nullptr, nullptr);
+    mPyrW = mPyrH = 0;
+  }
+}
+
+// mvImagePyramid after a call on a W x H image. First call with this size: the level sizes are known only now, so the staging is allocated,
+// the levels are fetched with one batched read and the destinations are registered; every later call finds them already filled by the
+// library (copy overlapped with FAST / quadtree / descriptors of the same call). The Mats are headers over the object's pinned staging: like
+// the reference's member they are overwritten by the next call (clone() what has to survive it).
+void ORBextractor::FinishPyramid(int W, int H) {
+  if (!mbDownloadPyramid || (W == mPyrW && H == mPyrH)) return;
+  uint8_t* dst[64];
+  int32_t steps[64];
+  size_t total = 0;
+  std::vector<int> cs(nlevels), rs(nlevels);
+  for (int l = 0; l < nlevels; ++l) {
+    check(orb_extractor_pyramid_dims(mpHandle, l, &cs[l], &rs[l]), "pyramid_dims");
+    total += ((size_t)cs[l] * rs[l] + 63) / 64 * 64;
+  }
+  orb_extractor_set_pyramid_download(mpHandle, nullptr, nullptr);   // the old staging may be freed by ensure()
+  mPyr.ensure(total);
+  size_t off = 0;
+  for (int l = 0; l < nlevels; ++l) {
+    dst[l] = static_cast<uint8_t*>(mPyr.p) + off;
+    steps[l] = cs[l];
+    mvImagePyramid[l] = cv::Mat(rs[l], cs[l], CV_8UC1, dst[l], (size_t)cs[l]);
+    off += ((size_t)cs[l] * rs[l] + 63) / 64 * 64;
+  }
+  check(orb_extractor_pyramid_read_all(mpHandle, -1, 0, dst, steps), "pyramid_read_all");
+  check(orb_extractor_set_pyramid_download(mpHandle, dst, steps), "set_pyramid_download");
+  mPyrW = W; mPyrH = H;
+}
 
 void ORBextractor::ExtractBatch(const std::vector<cv::Mat>& images, std::vector<std::vector<cv::KeyPoint>>& keypoints,
                                 std::vector<cv::Mat>& descriptors) {
@@ -62,11 +107,16 @@ void ORBextractor::ExtractBatch(const std::vector<cv::Mat>& images, std::vector<
     }
   }
   const int cap = orb_extractor_max_keypoints(mpHandle);
-  std::vector<orb_keypoint> kps((size_t)B * cap);
-  std::vector<uint8_t> desc((size_t)B * cap * 32);
+  mOutKps.ensure((size_t)B * cap * sizeof(orb_keypoint));
+  mOutDesc.ensure((size_t)B * cap * 32);
+  orb_keypoint* kps = static_cast<orb_keypoint*>(mOutKps.p);
+  uint8_t* desc = static_cast<uint8_t*>(mOutDesc.p);
   std::vector<int32_t> counts(B);
-  check(orb_extract_batch(mpHandle, ptrs.data(), ORB_MEM_HOST, use_step, W, H, B, kps.data(), desc.data(), ORB_MEM_HOST, cap,
-                          counts.data(), nullptr),
+  if (W != mPyrW || H != mPyrH) {   // another image size: the library drops the registration too; FinishPyramid makes the new one
+    orb_extractor_set_pyramid_download(mpHandle, nullptr, nullptr);
+    mPyrW = mPyrH = 0;
+  }
+  check(orb_extract_batch(mpHandle, ptrs.data(), ORB_MEM_HOST, use_step, W, H, B, kps, desc, ORB_MEM_HOST, cap, counts.data(), nullptr),
         "orb_extract_batch");
   for (int i = 0; i < B; ++i) {
     const int n = counts[i];
@@ -74,18 +124,10 @@ void ORBextractor::ExtractBatch(const std::vector<cv::Mat>& images, std::vector<
     if (n == 0) continue;   // descriptors stay released (src/ORBextractor.cc:1998-2013)
     std::memcpy((void*)keypoints[i].data(), &kps[(size_t)i * cap], (size_t)n * sizeof(orb_keypoint));
     descriptors[i].create(n, 32, CV_8U);
-    for (int r = 0; r < n; ++r) std::memcpy(descriptors[i].ptr<unsigned char>(r), &desc[((size_t)i * cap + r) * 32], 32);
+    if (descriptors[i].isContinuous()) std::memcpy(descriptors[i].ptr<unsigned char>(0), &desc[(size_t)i * cap * 32], (size_t)n * 32);
+    else for (int r = 0; r < n; ++r) std::memcpy(descriptors[i].ptr<unsigned char>(r), &desc[((size_t)i * cap + r) * 32], 32);
   }
-  if (mbDownloadPyramid) {
-    for (int l = 0; l < nlevels; ++l) {
-      int c = 0, r = 0;
-      check(orb_extractor_pyramid_dims(mpHandle, l, &c, &r), "pyramid_dims");
-      mvImagePyramid[l].create(r, c, CV_8UC1);
-      // the library keeps the frames of the last internal pass resident; the last image of the call is always among them
-      check(orb_extractor_pyramid_read(mpHandle, -1, l, 0, mvImagePyramid[l].ptr<unsigned char>(0), (int)mvImagePyramid[l].step),
-            "pyramid_read");
-    }
-  }
+  FinishPyramid(W, H);
 }
 
 void ORBextractor::ExtractStereo(const cv::Mat& left, const cv::Mat& right, float mbf, float mb, std::vector<cv::KeyPoint>& keysLeft,
@@ -101,12 +143,20 @@ void ORBextractor::ExtractStereo(const cv::Mat& left, const cv::Mat& right, floa
   }
   const uint8_t* ptrs[2] = {mStage.data(), mStage.data() + (size_t)W * H};
   const int cap = orb_extractor_max_keypoints(mpHandle);
-  std::vector<orb_keypoint> kps((size_t)2 * cap);
-  std::vector<uint8_t> desc((size_t)2 * cap * 32);
-  std::vector<float> ur(cap), dp(cap);
+  mOutKps.ensure((size_t)2 * cap * sizeof(orb_keypoint));
+  mOutDesc.ensure((size_t)2 * cap * 32);
+  mOutUr.ensure((size_t)cap * sizeof(float));
+  mOutDp.ensure((size_t)cap * sizeof(float));
+  orb_keypoint* kps = static_cast<orb_keypoint*>(mOutKps.p);
+  uint8_t* desc = static_cast<uint8_t*>(mOutDesc.p);
+  float* ur = static_cast<float*>(mOutUr.p);
+  float* dp = static_cast<float*>(mOutDp.p);
   int32_t counts[2] = {0, 0};
-  check(orb_extract_stereo_batch(mpHandle, ptrs, ORB_MEM_HOST, W, W, H, 1, kps.data(), desc.data(), ORB_MEM_HOST, cap, counts, nullptr, mbf, mb,
-                                 ur.data(), dp.data(), nullptr),
+  if (W != mPyrW || H != mPyrH) {
+    orb_extractor_set_pyramid_download(mpHandle, nullptr, nullptr);
+    mPyrW = mPyrH = 0;
+  }
+  check(orb_extract_stereo_batch(mpHandle, ptrs, ORB_MEM_HOST, W, W, H, 1, kps, desc, ORB_MEM_HOST, cap, counts, nullptr, mbf, mb, ur, dp, nullptr),
         "orb_extract_stereo_batch");
   std::vector<cv::KeyPoint>* keys[2] = {&keysLeft, &keysRight};
   cv::Mat* descs[2] = {&descLeft, &descRight};
@@ -116,18 +166,12 @@ void ORBextractor::ExtractStereo(const cv::Mat& left, const cv::Mat& right, floa
     if (n == 0) { descs[i]->release(); continue; }
     std::memcpy((void*)keys[i]->data(), &kps[(size_t)i * cap], (size_t)n * sizeof(orb_keypoint));
     descs[i]->create(n, 32, CV_8U);
-    for (int r = 0; r < n; ++r) std::memcpy(descs[i]->ptr<unsigned char>(r), &desc[((size_t)i * cap + r) * 32], 32);
+    if (descs[i]->isContinuous()) std::memcpy(descs[i]->ptr<unsigned char>(0), &desc[(size_t)i * cap * 32], (size_t)n * 32);
+    else for (int r = 0; r < n; ++r) std::memcpy(descs[i]->ptr<unsigned char>(r), &desc[((size_t)i * cap + r) * 32], 32);
   }
-  uRight.assign(ur.begin(), ur.begin() + counts[0]);
-  depth.assign(dp.begin(), dp.begin() + counts[0]);
-  if (mbDownloadPyramid) {
-    for (int l = 0; l < nlevels; ++l) {
-      int cc = 0, rr = 0;
-      check(orb_extractor_pyramid_dims(mpHandle, l, &cc, &rr), "pyramid_dims");
-      mvImagePyramid[l].create(rr, cc, CV_8UC1);
-      check(orb_extractor_pyramid_read(mpHandle, -1, l, 0, mvImagePyramid[l].ptr<unsigned char>(0), (int)mvImagePyramid[l].step), "pyramid_read");
-    }
-  }
+  uRight.assign(ur, ur + counts[0]);
+  depth.assign(dp, dp + counts[0]);
+  FinishPyramid(W, H);
 }
 
 void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint>& _keypoints,

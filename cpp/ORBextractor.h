@@ -59,7 +59,7 @@ class ORBextractor {
   // Padded CV_8UC1 levels of the last image of the last call (this fork stores the 19-px padded image,
   // src/ORBextractor.cc:2159-2166). Filled after every call unless SetPyramidDownload(false).
   std::vector<cv::Mat> mvImagePyramid;
-  void SetPyramidDownload(bool on) { mbDownloadPyramid = on; }
+  void SetPyramidDownload(bool on);
 
   orb_extractor* Handle() { return mpHandle; }
 
@@ -79,6 +79,17 @@ class ORBextractor {
   orb_extractor* mpHandle = nullptr;
   bool mbDownloadPyramid = true;
   std::vector<unsigned char> mStage;   // contiguous copy of non-contiguous / differently strided batches
+  // Page-locked staging owned by the object (no allocation per call): keypoints / descriptors / stereo columns of a whole batch, and the
+  // padded pyramid levels that mvImagePyramid's headers point into (the library copies them home while the rest of the call still runs).
+  struct Pinned {
+    void* p = nullptr;
+    size_t bytes = 0;
+    void ensure(size_t need);
+    ~Pinned();
+  };
+  Pinned mOutKps, mOutDesc, mOutUr, mOutDp, mPyr;
+  int mPyrW = 0, mPyrH = 0;            // image size the pyramid staging / registration was made for
+  void FinishPyramid(int W, int H);    // after a call: mvImagePyramid = headers over mPyr, registered for the following calls
 };
 
 }  // namespace ORB_SLAM2

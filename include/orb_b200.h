@@ -39,6 +39,7 @@
  */
 #ifndef ORB_B200_H_
 #define ORB_B200_H_
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -139,6 +140,20 @@ int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, 
  * blurred != 0 returns the Gaussian-blurred working copy instead (test hook). */
 int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int* rows);
 int orb_extractor_pyramid_read(orb_extractor* e, int index, int level, int blurred, uint8_t* dst, int dst_step);
+/* All levels of one resident image in one call: nlevels asynchronous 2-D copies and ONE synchronisation (orb_extractor_pyramid_read costs one
+ * synchronisation per level). level_dst[l] / level_steps[l] as dst / dst_step above. */
+int orb_extractor_pyramid_read_all(orb_extractor* e, int index, int blurred, uint8_t* const* level_dst, const int32_t* level_steps);
+/* Registers host destinations (pinned memory recommended: orb_host_alloc) for the padded levels of the LAST image of every following
+ * orb_extract_batch / orb_extract_stereo_batch call with this image size — what the drop-in's public mvImagePyramid has to hold after each
+ * operator() (include/ORBextractor.h:185, read by Frame::ComputeStereoMatches, src/Frame.cc:910, 1040). The copy is issued as soon as the
+ * pyramid kernels of the call's last pass are done and overlaps FAST / quadtree / descriptors; it is complete when the call returns.
+ * Needs the level sizes, i.e. one image of this size must have been processed (else ORB_E_BADARG); a call with another image size drops the
+ * registration. level_dst == NULL switches it off. The buffers stay the caller's and must outlive the registration. */
+int orb_extractor_set_pyramid_download(orb_extractor* e, uint8_t* const* level_dst, const int32_t* level_steps);
+/* Page-locked host memory for staging buffers that live as long as the caller's object (cudaMallocHost / cudaFreeHost without a CUDA
+ * dependency in the caller's build). */
+int orb_host_alloc(size_t bytes, void** out);
+void orb_host_free(void* p);
 /* Test hook: vToDistributeKeys of (image index, level) of the last batch: x, y (cell-shifted, border-relative) and response. */
 int orb_extractor_raw_keypoints(orb_extractor* e, int index, int level, orb_keypoint* out, int cap);
 /* CUDA stream of the handle (cudaStream_t) for callers that enqueue dependent work, and the number of kernels
@@ -154,6 +169,11 @@ int orb_extractor_set_profiling(orb_extractor* e, int on);
 int orb_extractor_stage_times(orb_extractor* e, double* ms, int64_t* passes);
 
 /* ---- matcher ------------------------------------------------------------------------------- */
+/* Threads and streams: the matcher / vocabulary / frame-geometry entry points keep their intermediates in one scratch per device (per
+ * vocabulary handle for orb_bow_transform). They may be called from any thread and on any stream: host-side set-up is serialised by a mutex,
+ * and every call makes its stream wait for the previous user of the scratch (an event recorded at the end of that call) before its own
+ * kernels run, so device-memory calls that return before their kernels have finished cannot overwrite each other's intermediates. The price:
+ * calls on one device execute one after another on the GPU, whatever their streams. orb_hamming_knn_noalloc is outside this chain (see there). */
 /* Brute-force k=2 over 256-bit descriptors with the reference update rule (strict <: earliest index wins,
  * a duplicate of the minimum becomes `second`). sentinel = initial best/second (256; INT_MAX at src/ORBmatcher.cc:611).
  * query [Q][32], db [D][32] in q_mem / db_mem memory; out [Q] in out_mem memory. index_base is added to i1/i2

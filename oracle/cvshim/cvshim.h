@@ -128,6 +128,7 @@ class Mat {
   template <typename T> T& at(int y, int x) { return reinterpret_cast<T*>(data + (size_t)y * step)[x]; }
   template <typename T> const T& at(int y, int x) const { return reinterpret_cast<const T*>(data + (size_t)y * step)[x]; }
 
+  void copyTo(const class _OutputArray& o) const;   // defined after _OutputArray
   orb_oracle::Img img() const { return orb_oracle::Img{data, cols, rows, (int)step}; }
 
   // ---- float patches of Frame::ComputeStereoMatches (src/Frame.cc:1035-1068): convertTo(CV_32F), Mat::ones, scalar * Mat, Mat - Mat ----
@@ -191,6 +192,11 @@ class _OutputArray : public _InputArray {
   void create(Size sz, int type) const { m_->create(sz, type); }
   void release() const { if (m_) m_->release(); }
 };
+inline void Mat::copyTo(const _OutputArray& o) const {   // cv::Mat::copyTo(OutputArray): (re)allocates the destination, then copies row by row
+  o.create(rows, cols, type_);
+  Mat d = o.getMat();
+  for (int y = 0; y < rows; ++y) std::memcpy(d.data + (size_t)y * d.step, data + (size_t)y * step, (size_t)cols * esz(type_));
+}
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
 

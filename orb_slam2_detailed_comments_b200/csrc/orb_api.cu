@@ -34,7 +34,7 @@ struct orb_extractor {
     cudaStream_t st = nullptr;
     cudaEvent_t ev_join = nullptr;
     cudaStream_t st_side = nullptr;                       // high-priority side stream of the pass: quadtree (latency-bound) beside blur
-    cudaEvent_t ev_fast = nullptr, ev_side = nullptr;
+    cudaEvent_t ev_fast = nullptr, ev_side = nullptr, ev_pyr = nullptr;   // ev_pyr: the pyramid of the pass is complete
     int frames = 0;          // frames of the last pass run here
     // per-level TMA descriptors of `pyr` / `blr`: FAST band windows (256 B x hCell + 6), IC_Angle windows (48 B x 31), descriptor patches (64 B x 37)
     alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES];
@@ -50,6 +50,11 @@ struct orb_extractor {
   int side = 2;            // ORB_B200_SIDE: 0 = off, 1 = quadtree, 2 (default) = quadtree + descriptors on the pass's high-priority side stream
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
   cudaEvent_t ev_fork = nullptr;
+  // orb_extractor_set_pyramid_download: host destinations of the padded levels of the LAST image of every host-facing call; the copy is issued on
+  // the copy-out stream as soon as the pyramid kernels of the last pass are done, so it overlaps FAST / quadtree / descriptors
+  uint8_t* pyr_dst[ORB_MAX_LEVELS] = {};
+  int pyr_dst_step[ORB_MAX_LEVELS] = {};
+  bool pyr_dst_on = false;
   // host-facing pipeline (orb_extract_batch): H2D of pass p+1 and D2H of pass p-1 overlap the kernels of pass p
   cudaStream_t s_in = nullptr, s_out = nullptr;
   // Output staging has one buffer more than there are workspaces: pass p + nws runs on the workspace of pass p and must not
@@ -240,6 +245,7 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     if ((rc = e->fast_tiles.ensure(std::max<size_t>(tiles.size(), 1) * sizeof(int4))) != ORB_OK) return rc;
     CU(cudaMemcpy(e->fast_tiles.p, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice));
     e->chunk = 0;
+    e->pyr_dst_on = false;   // level sizes changed: the caller registers new destinations
   }
   const OrbGeom& g = e->geom;
   const int want = std::min(batch, default_chunk(g));
@@ -295,7 +301,8 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
 
 // One internal pass over `n` (<= chunk) device-resident frames; outputs to device pointers.
 static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, long long image_stride, int n, OrbKeypoint* kps,
-                     uint8_t* desc, int cap, int* counts_dev, cudaEvent_t ev_input_consumed = nullptr, int* level_counts_dev = nullptr) {
+                     uint8_t* desc, int cap, int* counts_dev, cudaEvent_t ev_input_consumed = nullptr, int* level_counts_dev = nullptr,
+                     bool mark_pyramid = false) {
   const OrbGeom& g = e->geom;
   orb_extractor::PassWs& P = e->ws[w];
   cudaStream_t st = P.st;
@@ -319,6 +326,7 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
   }
   if (prof) cudaEventRecord(ev[0], st);
   orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches, ev_input_consumed);
+  if (mark_pyramid) cudaEventRecord(P.ev_pyr, st);
   if (prof) cudaEventRecord(ev[1], st);
   static const bool fast_v1 = getenv("ORB_B200_FAST_V1") != nullptr;   // round-1 kernel, same-box A/B only
   if (fast_v1) orb_launch_fast_v1(P.pyr.as<uint8_t>(), P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), e->err.as<int>(), g, n, st, &e->launches);
@@ -418,6 +426,7 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
       if (ce == cudaSuccess) ce = cudaStreamCreateWithPriority(&e->ws[w].st_side, cudaStreamNonBlocking, hi);
       if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_fast, cudaEventDisableTiming);
       if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_side, cudaEventDisableTiming);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_pyr, cudaEventDisableTiming);
     }
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
@@ -435,6 +444,7 @@ void orb_extractor_destroy(orb_extractor* e) {
     if (e->ws[w].st_side) { cudaStreamSynchronize(e->ws[w].st_side); cudaStreamDestroy(e->ws[w].st_side); }
     if (e->ws[w].ev_fast) cudaEventDestroy(e->ws[w].ev_fast);
     if (e->ws[w].ev_side) cudaEventDestroy(e->ws[w].ev_side);
+    if (e->ws[w].ev_pyr) cudaEventDestroy(e->ws[w].ev_pyr);
   }
   for (int w = 1; w < ORB_MAX_WS; ++w) {
     if (e->ws[w].st) { cudaStreamSynchronize(e->ws[w].st); cudaStreamDestroy(e->ws[w].st); }
@@ -653,7 +663,18 @@ static int extract_batch_impl(orb_extractor* e, const uint8_t* const* images, in
     tmark(P.st);
     OrbKeypoint* dk = host_out ? e->out_kps[ob].as<OrbKeypoint>() : reinterpret_cast<OrbKeypoint*>(kps) + (long long)f0 * cap;
     uint8_t* dd = host_out ? e->out_desc[ob].as<uint8_t>() : desc + (long long)f0 * cap * 32;
-    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, d_counts + f0, e->ev_staged[b], d_levels + (size_t)f0 * nl);
+    const bool last_pass = f0 + n >= batch;
+    const bool pyr_out = last_pass && e->pyr_dst_on;
+    run_pass(e, w, e->stage_in[b].as<uint8_t>(), step, (long long)fbytes, n, dk, dd, cap, d_counts + f0, e->ev_staged[b], d_levels + (size_t)f0 * nl,
+             pyr_out);
+    if (pyr_out) {   // the padded levels of the call's last image go home while the rest of the pass still runs
+      CU(cudaStreamWaitEvent(e->s_out, P.ev_pyr, 0));
+      for (int l = 0; l < nl; ++l) {
+        const OrbLevel& L = g.lv[l];
+        CU(cudaMemcpy2DAsync(e->pyr_dst[l], (size_t)e->pyr_dst_step[l], P.pyr.as<uint8_t>() + (size_t)(n - 1) * g.frame_stride + L.plane_off, L.pitch,
+                             L.cols, L.rows, cudaMemcpyDeviceToHost, e->s_out));
+      }
+    }
     float* dur = nullptr;
     float* ddp = nullptr;
     if (sr) {
@@ -717,6 +738,47 @@ int orb_extract_stereo_batch(orb_extractor* e, const uint8_t* const* images, int
   const StereoReq sr{bf, b, uright, depth, matched};
   if (pairs <= 0) return fail(ORB_E_BADARG, "bad size");
   return extract_batch_impl(e, images, in_mem, step, width, height, 2 * pairs, kps, desc, out_mem, cap, counts, level_counts, &sr);
+}
+
+int orb_host_alloc(size_t bytes, void** out) {
+  if (!out || bytes == 0) return fail(ORB_E_BADARG, "bad argument");
+  *out = nullptr;
+  CU(cudaMallocHost(out, bytes));
+  return ORB_OK;
+}
+void orb_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int orb_extractor_set_pyramid_download(orb_extractor* e, uint8_t* const* level_dst, const int32_t* level_steps) {
+  if (!e) return fail(ORB_E_BADARG, "null argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (!level_dst) { e->pyr_dst_on = false; return ORB_OK; }
+  if (!level_steps || e->geom.width == 0) return fail(ORB_E_BADARG, "bad argument / no image processed yet (level sizes unknown)");
+  for (int l = 0; l < e->geom.nlevels; ++l) {
+    if (!level_dst[l] || level_steps[l] < e->geom.lv[l].cols) return fail(ORB_E_BADARG, "level %d: null destination or step < %d", l, e->geom.lv[l].cols);
+    e->pyr_dst[l] = level_dst[l];
+    e->pyr_dst_step[l] = level_steps[l];
+  }
+  e->pyr_dst_on = true;
+  return ORB_OK;
+}
+
+int orb_extractor_pyramid_read_all(orb_extractor* e, int index, int blurred, uint8_t* const* level_dst, const int32_t* level_steps) {
+  if (!e || !level_dst || !level_steps || e->geom.width == 0) return fail(ORB_E_BADARG, "bad argument / no image processed yet");
+  std::lock_guard<std::mutex> lk(e->mu);
+  orb_extractor::PassWs& P = e->ws[e->last_ws];
+  if (index == -1) index = P.frames - 1;
+  if (index < 0 || index >= P.frames) return fail(ORB_E_BADARG, "image %d is not resident (last pass held %d frames)", index, P.frames);
+  ORB_ON_DEVICE(e->device);
+  for (int l = 0; l < e->geom.nlevels; ++l) {
+    const OrbLevel& L = e->geom.lv[l];
+    if (!level_dst[l] || level_steps[l] < L.cols) return fail(ORB_E_BADARG, "level %d: null destination or step < %d", l, L.cols);
+    const uint8_t* src = (blurred ? P.blr.as<uint8_t>() : P.pyr.as<uint8_t>()) + (size_t)index * e->geom.frame_stride + L.plane_off;
+    CU(cudaMemcpy2DAsync(level_dst[l], (size_t)level_steps[l], src, L.pitch, L.cols, L.rows, cudaMemcpyDeviceToHost, P.st));
+  }
+  CU(cudaStreamSynchronize(P.st));   // one synchronisation for all levels
+  return ORB_OK;
 }
 
 int orb_extractor_pyramid_dims(const orb_extractor* e, int level, int* cols, int* rows) {

@@ -1,6 +1,7 @@
 // C ABI (include/orb_b200.h), matcher / vocabulary / frame-geometry part: brute-force kNN, DescriptorDistance batches, guided
 // search (SearchByProjection, SearchByBoW), ComputeBoW, UndistortKeyPoints, ComputeDistinctiveDescriptors. Host logic only;
-// per-device scratch behind a mutex, so these entry points are callable from any thread. No CPU fallback.
+// per-device scratch behind a mutex + an event chain across streams (WsOrder), so these entry points are callable from any thread and on any
+// stream. No CPU fallback.
 #include "orb_host.h"
 
 extern "C" {
@@ -13,8 +14,25 @@ struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mut
   DevBuf g_bq, g_bnq, g_stage[17];   // orb_search_by_bow: device-built queries, staging of host arguments
   DevBuf g_items, g_cells, g_lists, g_lcnt, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
   int num_sms = 0;
+  cudaEvent_t ev_last = nullptr;   // recorded on the caller's stream at the end of every call that touched the scratch (see WsOrder)
 };
 static KnnWorkspace g_knn_ws[16];
+
+// The scratch is shared by all streams of a device. Device-mode calls return while their kernels are still queued, so the mutex alone would
+// let a call on ANOTHER stream overwrite lists / partials that are still being read (ORBmatcher is used by Tracking, LocalMapping and
+// LoopClosing at once). Every entry point that touches the scratch therefore makes its stream wait for the previous user's event first and
+// records its own event last — both while holding the mutex, so the chain of users is totally ordered on the GPU.
+struct WsOrder {
+  cudaEvent_t* ev;
+  cudaStream_t st;
+  WsOrder(cudaEvent_t* e, cudaStream_t s) : ev(e), st(s) {
+    if (!*ev && cudaEventCreateWithFlags(ev, cudaEventDisableTiming) != cudaSuccess) { *ev = nullptr; cudaGetLastError(); }
+    if (*ev) cudaStreamWaitEvent(st, *ev, 0);   // no-op for an event that was never recorded or was recorded on `st` itself
+  }
+  ~WsOrder() {
+    if (*ev) cudaEventRecord(*ev, st);
+  }
+};
 
 static int current_device_ws(KnnWorkspace** ws) {
   int dev = 0;
@@ -40,6 +58,7 @@ int orb_hamming_knn(const uint8_t* query, int q_mem, int Q, const uint8_t* db, i
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const uint8_t* dq = query;
   const uint8_t* ddb = db;
   orb_knn2* dout = out;
@@ -92,6 +111,7 @@ int orb_descriptor_distance_host(const uint8_t* a, const uint8_t* b, int64_t n, 
   int rc = current_device_ws(&ws);
   if (rc != ORB_OK) return rc;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, (cudaStream_t)0);
   if ((rc = ws->q.ensure((size_t)n * 32)) != ORB_OK) return rc;
   if ((rc = ws->db.ensure((size_t)n * 32)) != ORB_OK) return rc;
   if ((rc = ws->out.ensure((size_t)n * sizeof(int))) != ORB_OK) return rc;
@@ -113,6 +133,7 @@ struct orb_vocabulary {
   DevBuf child_start, child_id, child_desc, is_leaf, word_of, word_weight;
   DevBuf s_desc, s_n, s_word, s_node, s_bw, s_bv, s_bc, s_fn, s_fs, s_ff, s_fc;   // staging for host-memory calls
   std::mutex mu;
+  cudaEvent_t ev_last = nullptr;   // orders the users of the s_* scratch across streams (WsOrder)
 };
 
 int orb_vocabulary_create(int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc,
@@ -172,6 +193,7 @@ void orb_vocabulary_destroy(orb_vocabulary* v) {
   DevBuf* bufs[] = {&v->child_start, &v->child_id, &v->child_desc, &v->is_leaf, &v->word_of, &v->word_weight, &v->s_desc, &v->s_n, &v->s_word,
                     &v->s_node, &v->s_bw, &v->s_bv, &v->s_bc, &v->s_fn, &v->s_fs, &v->s_ff, &v->s_fc};
   for (DevBuf* b : bufs) b->release();
+  if (v->ev_last) cudaEventDestroy(v->ev_last);
   delete v;
 }
 
@@ -186,6 +208,7 @@ int orb_bow_transform(orb_vocabulary* v, int mem, const uint8_t* desc, const int
   std::lock_guard<std::mutex> lk(v->mu);
   ORB_ON_DEVICE(v->device);
   cudaStream_t st = (cudaStream_t)stream;
+  WsOrder order(&v->ev_last, st);
   const size_t F = (size_t)frames;
   const bool host = mem != ORB_MEM_DEVICE;
   int rc;
@@ -242,6 +265,7 @@ int orb_search_for_initialization(int mem, const orb_keypoint* kps_un, const uin
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const size_t F = (size_t)frames;
   const bool host = mem != ORB_MEM_DEVICE;
   const void* d_in[6] = {kps_un, desc, n_kps, queries, qdesc, n_queries};
@@ -310,6 +334,7 @@ static int search_by_bow_impl(int mem, const uint8_t* kf_desc, const orb_keypoin
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const size_t F = (size_t)frames, Q = (size_t)qcap, N = (size_t)cap;
   const bool host = mem != ORB_MEM_DEVICE;
   int* d_assigned = assigned;
@@ -409,6 +434,7 @@ int orb_undistort_keypoints(int mem, const orb_camera* cam, const orb_keypoint* 
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const size_t bytes = (size_t)frames * cap * sizeof(orb_keypoint);
   if (mem == ORB_MEM_DEVICE) {
     orb_launch_undistort(cam, (const OrbKeypoint*)kps, n, cap, frames, (OrbKeypoint*)kps_un, st);
@@ -464,6 +490,7 @@ int orb_distinctive_descriptors(int mem, const uint8_t* desc, const int64_t* off
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const bool host = mem != ORB_MEM_DEVICE;
   if (!host) {
     if (!desc || ((uintptr_t)desc & 15)) return fail(ORB_E_BADARG, "descriptor array must be 16-byte aligned device memory");
@@ -507,6 +534,7 @@ int orb_search_by_projection(int mem, const orb_keypoint* kps_un, const uint8_t*
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const size_t F = (size_t)frames;
   const bool host = mem != ORB_MEM_DEVICE;
   // device views of the arguments (staged when the caller's arrays are host memory)
@@ -571,6 +599,7 @@ int orb_fuse_search(int mem, const orb_keypoint* kps_un, const uint8_t* desc, co
   if (rc != ORB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
   const size_t F = (size_t)frames;
   const bool host = mem != ORB_MEM_DEVICE;
   const void* d_in[7] = {kps_un, desc, uright, nullptr, n_kps, queries, qdesc};

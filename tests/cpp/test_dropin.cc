@@ -3,6 +3,8 @@
 //   usage: test_dropin <frame.raw> <width> <height> <nfeatures> [<frame2.raw>]
 #include <algorithm>
 #include <cmath>
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -58,7 +60,44 @@ static int compare_with_oracle(orb_oracle_extractor* oe, const cv::Mat& img, con
   return 0;
 }
 
+// --latency frame.raw W H nfeatures [calls]: wall clock of ORBextractor::operator() the way Frame::ExtractORB calls it (src/Frame.cc:468-481: one
+// pageable cv::Mat in, std::vector<cv::KeyPoint> + cv::Mat out), with mvImagePyramid filled (the drop-in's default, what the stereo Frame needs)
+// and without. One JSON line; no oracle involved.
+static int latency_mode(int argc, char** argv) {
+  if (argc < 6) { std::fprintf(stderr, "usage: %s --latency frame.raw width height nfeatures [calls]\n", argv[0]); return 2; }
+  const int W = std::atoi(argv[3]), H = std::atoi(argv[4]), nf = std::atoi(argv[5]);
+  const int calls = argc > 6 ? std::atoi(argv[6]) : 300;
+  std::vector<unsigned char> f0;
+  REQUIRE(read_raw(argv[2], f0, (size_t)W * H), "cannot read %s", argv[2]);
+  // 8 shifted copies so that consecutive calls do not see identical pixels
+  std::vector<std::vector<unsigned char>> frames(8, f0);
+  for (int k = 1; k < 8; ++k) std::rotate(frames[k].begin(), frames[k].begin() + 131 * k, frames[k].end());
+  std::printf("{\"metric\": \"wall clock of one C++ ORB_SLAM2::ORBextractor::operator() call (cpp/ORBextractor.cc over the C ABI; 1 pageable image in, keypoints + descriptors out)\", \"unit\": \"ms\", \"width\": %d, \"height\": %d, \"nfeatures\": %d, \"calls\": %d", W, H, nf, calls);
+  for (int mode = 0; mode < 2; ++mode) {
+    ORB_SLAM2::ORBextractor ex(nf, 1.2f, 8, 20, 7);
+    ex.SetPyramidDownload(mode == 0);
+    std::vector<cv::KeyPoint> kps;
+    cv::Mat desc;
+    size_t nk = 0;
+    for (int i = 0; i < 30; ++i) { cv::Mat img(H, W, CV_8UC1, frames[i & 7].data(), (size_t)W); ex(img, cv::Mat(), kps, desc); }
+    std::vector<double> t(calls);
+    for (int i = 0; i < calls; ++i) {
+      cv::Mat img(H, W, CV_8UC1, frames[i & 7].data(), (size_t)W);
+      const auto t0 = std::chrono::steady_clock::now();
+      ex(img, cv::Mat(), kps, desc);
+      t[i] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      nk += kps.size();
+    }
+    std::sort(t.begin(), t.end());
+    std::printf(", \"%s\": {\"median\": %.4f, \"p99\": %.4f, \"min\": %.4f, \"keypoints_per_call\": %.1f}", mode == 0 ? "with_pyramid_download" : "without_pyramid_download",
+                t[calls / 2], t[(size_t)(calls * 0.99)], t[0], (double)nk / calls);
+  }
+  std::printf("}\n");
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && std::strcmp(argv[1], "--latency") == 0) return latency_mode(argc, argv);
   if (argc < 5) {
     std::fprintf(stderr, "usage: %s frame.raw width height nfeatures [frame2.raw]\n", argv[0]);
     return 2;

@@ -24,6 +24,12 @@ def test_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["metric"] == "ORB frames/sec (extract+describe)" and d["unit"] == "images/s"
     assert d["higher_is_better"] is True and d["steps"] == 1 and d["value"] > 0 and d["gpu_launches"] == 0
     assert "TUM" in d["config"]["workload"]
+    # both arms print the SAME config object (the driver compares them); arm-specific facts live in `run`
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["config"] == bench.shared_config("tum")
+    assert json.loads(json.dumps(bench.shared_config("kitti"))).keys() == d["config"].keys()
+    assert "images_per_step" in d["run"] and "rank 0" in d["run"]["ranks"]
     cb = d["cpu_baseline"]
     assert cb["kind"] in ("reference", "port") and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}

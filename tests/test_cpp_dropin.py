@@ -54,3 +54,31 @@ def test_dropin_matches_oracle_on_gpu(tmp_path, shape):
     for part in ("operator():", "ExtractBatch:", "ExtractStereo:", "SearchByProjection (frame-to-frame form)", "SearchByProjection (local-map form)",
                  "ComputeDistinctiveDescriptors:", "SearchForInitialization:", "SearchByBoW:", "ORBVocabulary::transform:", "UndistortKeyPoints:", "ORBmatcher: kNN"):
         assert part in r.stdout, part
+
+
+@pytest.mark.gpu
+def test_dropin_opencv_branch_through_input_output_arrays(tmp_path):
+    """The -DORB_B200_USE_OPENCV branch of cpp/ORBextractor.cc (cv::InputArray::getMat(), cv::OutputArray, Mat::copyTo) — the one a real
+    ORB-SLAM2 build takes — compiled against oracle/cvshim's OpenCV API model (tests only) and run against the oracle."""
+    import json  # noqa: F401
+    from orb_slam2_detailed_comments_b200 import synth
+    exe = os.path.join(ROOT, "tests", "cpp", "test_dropin_cvapi")
+    if not os.path.exists(exe):
+        _build()
+    for W, H, nf, seed in ((752, 480, 1200, 1237), (333, 257, 700, 1239)):
+        (tmp_path / "f.raw").write_bytes(synth.synth_frame(W, H, seed).tobytes())
+        r = subprocess.run([exe, str(tmp_path / "f.raw"), str(W), str(H), str(nf)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "cvapi ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_dropin_latency_mode_reports_both_paths(tmp_path):
+    import json
+    from orb_slam2_detailed_comments_b200 import synth
+    exe = os.path.join(ROOT, "tests", "cpp", "test_dropin")
+    (tmp_path / "f.raw").write_bytes(synth.synth_frame(1241, 376, 1236).tobytes())
+    r = subprocess.run([exe, "--latency", str(tmp_path / "f.raw"), "1241", "376", "2000", "60"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    for k in ("with_pyramid_download", "without_pyramid_download"):
+        assert 0 < d[k]["median"] <= d[k]["p99"] and d[k]["keypoints_per_call"] > 1500, d

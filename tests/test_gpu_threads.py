@@ -129,3 +129,34 @@ def test_matchers_from_four_threads(oracle):
     def t_ex():
         return all(eq(ex(frames[i % 3]), want_ex[i % 3]) for i in range(25))
     assert _run_threads([t_knn, t_sp, t_bow, t_ex]) == [True] * 4
+
+
+def test_device_mode_calls_on_two_streams_share_the_scratch_safely(oracle):
+    """the matcher entry points keep their intermediates in one per-device scratch; a device-mode call returns while its
+    kernels are queued, so a second device-mode call on ANOTHER stream used to overwrite partials that were still being read. The entry points
+    now chain the scratch's users with an event (csrc/orb_api_match.cu: WsOrder). A long scan on stream A is followed at once by a short one
+    on stream B whose partial keys land in the same words; both must equal the oracle, every round."""
+    import torch
+    from orb_slam2_detailed_comments_b200 import matcher
+    dev = torch.device("cuda:0")
+    q1, db1 = synth.synth_descriptors(2000, 300_000, seed=41)
+    q2, db2 = synth.synth_descriptors(2000, 3_000, seed=42)
+    want1, want2 = oracle.hamming_knn(q1, db1, nthreads=16), oracle.hamming_knn(q2, db2, nthreads=16)
+    tq1, tdb1, tq2, tdb2 = (torch.from_numpy(a).to(dev) for a in (q1, db1, q2, db2))
+    sa, sb = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    torch.cuda.synchronize(dev)
+    for rnd in range(12):
+        o1 = torch.zeros((2000, 3), dtype=torch.int64, device=dev)
+        o2 = torch.zeros((2000, 3), dtype=torch.int64, device=dev)
+        torch.cuda.synchronize(dev)
+        if rnd % 2 == 0:
+            matcher.hamming_knn_device(tq1, tdb1, out=o1, stream=sa)
+            matcher.hamming_knn_device(tq2, tdb2, out=o2, stream=sb)
+        else:
+            matcher.hamming_knn_device(tq2, tdb2, out=o2, stream=sb)
+            matcher.hamming_knn_device(tq1, tdb1, out=o1, stream=sa)
+        torch.cuda.synchronize(dev)
+        r1, r2 = matcher.knn_records(o1.cpu()), matcher.knn_records(o2.cpu())
+        for f in ("d1", "d2", "i1", "i2"):
+            assert np.array_equal(r1[f], want1[f]), (rnd, "long scan", f)
+            assert np.array_equal(r2[f], want2[f]), (rnd, "short scan", f)
