@@ -604,14 +604,13 @@ def bench_knn(rank, world, steps, warmup):
     gdb = torch.Generator(device="cuda").manual_seed(100 + rank)
     db = torch.randint(0, 256, (per, 32), dtype=torch.uint8, device="cuda", generator=gdb)
     out = torch.empty((KNN_Q, 3), dtype=torch.int64, device="cuda")
-    gathered = torch.empty((world, KNN_Q, 3), dtype=torch.int64, device="cuda") if world > 1 else None
+    comm = matcher.nccl_comm_ptr() if world > 1 else None   # torch.distributed's ncclComm_t, handed to the C ABI
 
     def step():
-        matcher.hamming_knn_device(q, db, out=out, index_base=base)
-        if world > 1:
-            import torch.distributed as dist
-            dist.all_gather_into_tensor(gathered, out)
-            matcher.knn_merge_device(gathered, world, KNN_Q, out=out)
+        if world > 1:   # shard scan + ncclAllGather + device merge behind ONE C-ABI call (orb_hamming_knn_sharded)
+            matcher.hamming_knn_sharded(q, db, base, out=out, comm=comm)
+        else:
+            matcher.hamming_knn_device(q, db, out=out, index_base=base)
 
     for _ in range(max(warmup, 3)):
         step()
@@ -740,7 +739,7 @@ def run_b200(args):
                 "words_per_frame": b_words, "gpu_launches": 2 * g_steps, "api": "orb_bow_transform (device memory)"},
         "knn": {"metric": "Hamming matches/sec (k=2 brute force)", "value": knn_rate, "unit": "pairs/s",
                 "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
-                          + (", NCCL all_gather + device top-2 merge" if world > 1 else ""),
+                          + (", orb_hamming_knn_sharded: shard scan + ncclAllGather + device top-2 merge in one C-ABI call" if world > 1 else ""),
                 "ms_per_step": knn_ms, "gpu_launches": int(knn_launches),
                 "parity": knn_par if world > 1 else "n/a at 1 GPU (no merge; tests/test_gpu_knn.py checks the scan)",
                 "roofline": {"bound": "popc", "achieved": knn_rate * 8 / world, "peak": popc_peak, "unit": "popc.b32/s",

@@ -61,6 +61,21 @@ void ORBmatcher::BruteForceKnn2(const cv::Mat& queries, const cv::Mat& database,
   for (int i = 0; i < queries.rows; ++i) out[i] = Knn2{res[i].d1, res[i].d2, res[i].i1, res[i].i2};
 }
 
+void ORBmatcher::BruteForceKnn2Sharded(const cv::Mat& queries, const cv::Mat& databaseShard, int64_t shardBase, void* ncclComm, std::vector<Knn2>& out,
+                                       int sentinel) {
+  out.clear();
+  if (queries.rows == 0) return;   // every rank sees the same queries, so every rank returns here together
+  std::vector<uint8_t> tq, td;
+  const uint8_t* pq = rows32(queries, tq);
+  const uint8_t* pd = databaseShard.rows ? rows32(databaseShard, td) : nullptr;
+  std::vector<orb_knn2> res(queries.rows);
+  check(orb_hamming_knn_sharded(pq, ORB_MEM_HOST, queries.rows, pd, ORB_MEM_HOST, databaseShard.rows, shardBase, sentinel, res.data(), ORB_MEM_HOST,
+                                ncclComm, nullptr),
+        "orb_hamming_knn_sharded");
+  out.resize(queries.rows);
+  for (int i = 0; i < queries.rows; ++i) out[i] = Knn2{res[i].d1, res[i].d2, res[i].i1, res[i].i2};
+}
+
 int ORBmatcher::MatchBruteForce(const cv::Mat& queries, const cv::Mat& database, std::vector<int64_t>& matches, int th) const {
   std::vector<Knn2> r;
   BruteForceKnn2(queries, database, r);

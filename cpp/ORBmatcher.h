@@ -38,6 +38,12 @@ class ORBmatcher {
   // For every query row: the scan `if (d < best) {second = best; best = d; idx = i} else if (d < second) second = d`
   // over all database rows in index order (strict <: the earliest index wins ties). GPU only.
   static void BruteForceKnn2(const cv::Mat& queries, const cv::Mat& database, std::vector<Knn2>& out, int sentinel = 256);
+  // The same scan over a database that is sharded over the ranks of an NCCL communicator (one process per GPU; contiguous shards, ascending rank =
+  // ascending rows; shardBase = global index of the shard's first row): every rank passes its shard and gets the result of the scan over
+  // the WHOLE database (orb_hamming_knn_sharded: shard scan + one ncclAllGather + device merge). Collective call. ncclComm: an ncclComm_t of
+  // the process's NCCL, or one made by orb_nccl_comm_create (include/orb_b200.h).
+  static void BruteForceKnn2Sharded(const cv::Mat& queries, const cv::Mat& databaseShard, int64_t shardBase, void* ncclComm, std::vector<Knn2>& out,
+                                    int sentinel = 256);
 
   // The accept test of src/ORBmatcher.cc:339-342: best <= th && best < mfNNratio * second (float32 product).
   bool Accept(const Knn2& m, int th) const { return m.bestDist <= th && (float)m.bestDist < mfNNratio * (float)m.bestDist2; }

@@ -15,6 +15,7 @@
  *   orb_hamming_knn           <- ORBmatcher::DescriptorDistance in the best/second-best scan
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_noalloc   <- (new, no reference counterpart) orb_hamming_knn without any allocation: fixed device scratch
+ *   orb_hamming_knn_sharded   <- (new) the 8-GPU database scan of config C4 behind one call: shard scan + ncclAllGather + merge
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
  *   orb_search_for_initialization <- ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   src/ORBmatcher.cc:570-712
@@ -199,6 +200,20 @@ int orb_hamming_knn_noalloc(const uint8_t* query, int Q, const uint8_t* db, int6
 /* Merge `nshards` per-shard results (shard-major [nshards][Q], device memory, shards in ascending index order)
  * into out[Q] (device): equals one sequential scan over the concatenated database. */
 int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentinel, orb_knn2* out, void* stream);
+/* Database sharded over the ranks of an NCCL communicator (contiguous shards, ascending rank = ascending rows, queries
+ * replicated): scan of this rank's shard with GLOBAL indices (index_base = first row of the shard), ONE ncclAllGather of the Q x 24-byte
+ * records, device merge. Every rank's out[Q] equals one sequential scan of src/ORBmatcher.cc:304-335 over the concatenated database (earliest
+ * global index wins ties, across shards too). Memory-space flags, alignment staging and synchronisation as orb_hamming_knn (device buffers on
+ * the caller's current device: asynchronous on `stream`). Collective: every rank of the communicator must call it, with the same Q. nccl_comm: an ncclComm_t of the NCCL
+ * library loaded in this process (libnccl.so.2 is dlopen'ed: an already loaded copy - torch.distributed's included - is the one used), e.g.
+ * from orb_nccl_comm_create or from the caller's own NCCL set-up. */
+int orb_hamming_knn_sharded(const uint8_t* query, int q_mem, int Q, const uint8_t* db_shard, int db_mem, int64_t D_shard, int64_t index_base,
+                            int sentinel, orb_knn2* out, int out_mem, void* nccl_comm, void* stream);
+/* Communicator plumbing for hosts without an NCCL set-up of their own: rank 0 makes the 128-byte id (ncclGetUniqueId) and hands it to the
+ * other ranks by any means (file, socket, MPI); every rank then creates its communicator on its CURRENT device (ncclCommInitRank). */
+int orb_nccl_unique_id(uint8_t* id128);
+int orb_nccl_comm_create(const uint8_t* id128, int nranks, int rank, void** comm);
+void orb_nccl_comm_destroy(void* comm);
 /* DescriptorDistance for n row pairs: out[i] = popcount(a[i] ^ b[i]); all device memory. */
 int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream);
 /* Same with HOST buffers (copies inside the call, default stream, synchronous). */

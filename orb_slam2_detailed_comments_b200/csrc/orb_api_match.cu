@@ -2,6 +2,8 @@
 // search (SearchByProjection, SearchByBoW), ComputeBoW, UndistortKeyPoints, ComputeDistinctiveDescriptors. Host logic only;
 // per-device scratch behind a mutex + an event chain across streams (WsOrder), so these entry points are callable from any thread and on any
 // stream. No CPU fallback.
+#include <dlfcn.h>
+
 #include "orb_host.h"
 
 extern "C" {
@@ -10,6 +12,7 @@ extern "C" {
 struct KnnWorkspace {   // per-device scratch, grown on demand; guarded by a mutex (calls on one device serialise their setup)
   std::mutex mu;
   DevBuf partial, q, db, out;
+  DevBuf sh_local, sh_gathered;   // orb_hamming_knn_sharded: this rank's records [Q], all ranks' records [nranks][Q]
   // orb_search_by_projection: sorted keypoints + cell starts + per-query top-2, and the staging copies of host arguments
   DevBuf g_bq, g_bnq, g_stage[17];   // orb_search_by_bow: device-built queries, staging of host arguments
   DevBuf g_items, g_cells, g_lists, g_lcnt, g_kps, g_desc, g_ur, g_claim, g_nk, g_q, g_qd, g_nq, g_assigned, g_qmatch, g_nm;
@@ -90,6 +93,121 @@ int orb_hamming_knn_merge(const orb_knn2* shards, int nshards, int Q, int sentin
   if (!shards || !out || nshards < 1 || Q <= 0) return fail(ORB_E_BADARG, "bad argument");
   orb_launch_knn_merge_shards((const OrbKnn2*)shards, nshards, Q, sentinel, (OrbKnn2*)out, (cudaStream_t)stream);
   CU(cudaGetLastError());
+  return ORB_OK;
+}
+
+// ---- NCCL (dlopen'ed: no header and no link-time dependency) ---------------------------------------------------------------------------
+// dlopen("libnccl.so.2") returns the NCCL the process has ALREADY loaded when there is one (glibc matches loaded objects by SONAME), so a
+// communicator created by the caller's NCCL - torch.distributed's included - is used with the library that made it.
+struct OrbNccl {
+  typedef struct ncclComm* comm_t;
+  struct unique_id { char internal[128]; };   // ncclUniqueId (NCCL_UNIQUE_ID_BYTES = 128)
+  int (*AllGather)(const void*, void*, size_t, int, comm_t, cudaStream_t) = nullptr;
+  int (*CommCount)(comm_t, int*) = nullptr;
+  int (*CommUserRank)(comm_t, int*) = nullptr;
+  int (*GetUniqueId)(unique_id*) = nullptr;
+  int (*CommInitRank)(comm_t*, int, unique_id, int) = nullptr;
+  int (*CommDestroy)(comm_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok = false;
+};
+static OrbNccl* orb_nccl() {
+  static OrbNccl N;
+  static std::once_flag once;
+  std::call_once(once, []() {
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return;
+    *(void**)&N.AllGather = dlsym(h, "ncclAllGather");
+    *(void**)&N.CommCount = dlsym(h, "ncclCommCount");
+    *(void**)&N.CommUserRank = dlsym(h, "ncclCommUserRank");
+    *(void**)&N.GetUniqueId = dlsym(h, "ncclGetUniqueId");
+    *(void**)&N.CommInitRank = dlsym(h, "ncclCommInitRank");
+    *(void**)&N.CommDestroy = dlsym(h, "ncclCommDestroy");
+    *(void**)&N.GetErrorString = dlsym(h, "ncclGetErrorString");
+    N.ok = N.AllGather && N.CommCount && N.CommUserRank && N.GetUniqueId && N.CommInitRank && N.CommDestroy && N.GetErrorString;
+  });
+  return N.ok ? &N : nullptr;
+}
+#define NC(call)                                                                                              \
+  do {                                                                                                        \
+    int r_ = (call);                                                                                          \
+    if (r_ != 0) return fail(ORB_E_CUDA, "%s: NCCL error %d (%s)", #call, r_, N->GetErrorString(r_));         \
+  } while (0)
+
+int orb_nccl_unique_id(uint8_t* id128) {
+  if (!id128) return fail(ORB_E_BADARG, "null argument");
+  OrbNccl* N = orb_nccl();
+  if (!N) return fail(ORB_E_CUDA, "libnccl.so.2 not found (dlopen)");
+  OrbNccl::unique_id id;
+  NC(N->GetUniqueId(&id));
+  memcpy(id128, id.internal, 128);
+  return ORB_OK;
+}
+int orb_nccl_comm_create(const uint8_t* id128, int nranks, int rank, void** comm) {
+  if (!id128 || !comm || nranks < 1 || rank < 0 || rank >= nranks) return fail(ORB_E_BADARG, "bad argument");
+  OrbNccl* N = orb_nccl();
+  if (!N) return fail(ORB_E_CUDA, "libnccl.so.2 not found (dlopen)");
+  OrbNccl::unique_id id;
+  memcpy(id.internal, id128, 128);
+  OrbNccl::comm_t c = nullptr;
+  NC(N->CommInitRank(&c, nranks, id, rank));   // on the caller's current device
+  *comm = c;
+  return ORB_OK;
+}
+void orb_nccl_comm_destroy(void* comm) {
+  OrbNccl* N = orb_nccl();
+  if (N && comm) N->CommDestroy((OrbNccl::comm_t)comm);
+}
+
+int orb_hamming_knn_sharded(const uint8_t* query, int q_mem, int Q, const uint8_t* db_shard, int db_mem, int64_t D_shard, int64_t index_base,
+                            int sentinel, orb_knn2* out, int out_mem, void* nccl_comm, void* stream) {
+  if (!query || !out || !nccl_comm || Q <= 0 || D_shard < 0 || (D_shard > 0 && !db_shard) || sentinel < 1) return fail(ORB_E_BADARG, "bad argument");
+  if (index_base < 0 || index_base + D_shard >= (1LL << 40)) return fail(ORB_E_BADARG, "index range exceeds 2^40");
+  OrbNccl* N = orb_nccl();
+  if (!N) return fail(ORB_E_CUDA, "libnccl.so.2 not found (dlopen)");
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  OrbNccl::comm_t comm = (OrbNccl::comm_t)nccl_comm;
+  int nranks = 0;
+  NC(N->CommCount(comm, &nranks));
+  if (nranks < 1) return fail(ORB_E_BADARG, "communicator with %d ranks", nranks);
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
+  const uint8_t* dq = query;
+  const uint8_t* ddb = db_shard;
+  orb_knn2* dout = out;
+  const bool any_host = q_mem != ORB_MEM_DEVICE || db_mem != ORB_MEM_DEVICE || out_mem != ORB_MEM_DEVICE;
+  if (q_mem != ORB_MEM_DEVICE || ((uintptr_t)query & 15)) {
+    if ((rc = ws->q.ensure((size_t)Q * 32)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->q.p, query, (size_t)Q * 32, q_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    dq = ws->q.as<uint8_t>();
+  }
+  if (D_shard > 0 && (db_mem != ORB_MEM_DEVICE || ((uintptr_t)db_shard & 15))) {
+    if ((rc = ws->db.ensure((size_t)D_shard * 32)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->db.p, db_shard, (size_t)D_shard * 32, db_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    ddb = ws->db.as<uint8_t>();
+  }
+  const size_t rec = (size_t)Q * sizeof(orb_knn2);
+  if (out_mem != ORB_MEM_DEVICE) {
+    if ((rc = ws->out.ensure(rec)) != ORB_OK) return rc;
+    dout = ws->out.as<orb_knn2>();
+  }
+  if ((rc = ws->sh_local.ensure(rec)) != ORB_OK) return rc;
+  if ((rc = ws->sh_gathered.ensure(rec * nranks)) != ORB_OK) return rc;
+  const int nchunks = orb_knn_num_chunks(Q, D_shard, ws->num_sms);
+  if ((rc = ws->partial.ensure((size_t)nchunks * Q * 2 * sizeof(unsigned long long))) != ORB_OK) return rc;
+  // 1. this rank's shard -> records with GLOBAL row indices; 2. one all-gather of Q x 24 bytes per rank (ascending rank = ascending rows);
+  // 3. the two lexicographically smallest (distance, index) of all shards = the sequential scan over the concatenated database
+  orb_launch_knn(dq, Q, ddb, D_shard, index_base, sentinel, ws->partial.as<unsigned long long>(), nchunks, ws->sh_local.as<OrbKnn2>(), st);
+  CU(cudaGetLastError());
+  NC(N->AllGather(ws->sh_local.p, ws->sh_gathered.p, rec, /*ncclInt8*/ 0, comm, st));
+  orb_launch_knn_merge_shards(ws->sh_gathered.as<OrbKnn2>(), nranks, Q, sentinel, (OrbKnn2*)dout, st);
+  CU(cudaGetLastError());
+  if (out_mem != ORB_MEM_DEVICE) CU(cudaMemcpyAsync(out, dout, rec, cudaMemcpyDeviceToHost, st));
+  if (any_host) CU(cudaStreamSynchronize(st));
   return ORB_OK;
 }
 

@@ -61,39 +61,61 @@ def knn_records(t) -> np.ndarray:
     return t.detach().cpu().numpy().view(KNN_DTYPE).reshape(-1)
 
 
-def hamming_knn_sharded(query, db_shard, shard_base: int, group=None, sentinel: int = 256):
-    """Database sharded contiguously over the ranks of `group` (ascending rank = ascending rows):
-    local k=2 on this rank's shard, ONE all_gather of the per-query records, local top-2 merge.
-    Equals one sequential scan over the concatenated database (earliest global index wins ties).
-    query / db_shard: torch uint8 tensors on this rank's device (CUDA -> NCCL; the merge of CPU tensors
-    used by the gloo tests goes through `merge_records_host`)."""
+_OWN_COMMS = {}   # (group id, device) -> communicator made through orb_nccl_comm_create
+
+
+def nccl_comm_ptr(group=None) -> int:
+    """The ncclComm_t (as an integer) the C ABI's sharded scan runs its all-gather on: torch.distributed's own communicator of `group`
+    (ProcessGroupNCCL._comm_ptr, created lazily by the first collective), or - where this torch does not expose it - one made by
+    orb_nccl_comm_create from an id broadcast through `group`."""
     import torch
     import torch.distributed as dist
-    world = dist.get_world_size(group)
-    if query.is_cuda:
-        local = hamming_knn_device(query, db_shard, index_base=shard_base, sentinel=sentinel)
-        gathered = torch.empty((world,) + tuple(local.shape), dtype=local.dtype, device=local.device)
-        dist.all_gather_into_tensor(gathered, local, group=group)
-        return knn_merge_device(gathered, world, query.shape[0], sentinel=sentinel)
-    raise RuntimeError("hamming_knn_sharded needs CUDA tensors (there is no CPU fallback)")
+    dev = torch.device("cuda", torch.cuda.current_device())
+    pg = group if group is not None else dist.distributed_c10d._get_default_group()
+    try:
+        be = pg._get_backend(dev)
+        if hasattr(be, "_comm_ptr"):
+            ptr = be._comm_ptr()
+            if not ptr:
+                dist.all_reduce(torch.zeros(1, device=dev), group=group)   # first collective creates the communicator
+                torch.cuda.synchronize(dev)
+                ptr = be._comm_ptr()
+            if ptr:
+                return int(ptr)
+    except Exception:   # noqa: BLE001 - fall through to a communicator of our own
+        pass
+    key = (id(pg), dev.index)
+    if key not in _OWN_COMMS:
+        L = _lib.lib()
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        ident = np.zeros(128, np.uint8)
+        if rank == 0:
+            check(L.orb_nccl_unique_id(_vp(ident)))
+        t = torch.from_numpy(ident).to(dev)
+        dist.broadcast(t, src=dist.get_global_rank(pg, 0) if group is not None else 0, group=group)
+        ident = t.cpu().numpy()
+        comm = C.c_void_p()
+        check(L.orb_nccl_comm_create(_vp(ident), world, rank, C.byref(comm)))
+        _OWN_COMMS[key] = comm.value
+    return _OWN_COMMS[key]
 
 
-def merge_records_host(parts: list, sentinel: int = 256) -> np.ndarray:
-    """Host-side statement of the shard merge rule (the two lexicographically smallest (d, i) with d < sentinel)
-    for the gloo tests of the exchange logic; the product path merges on the device (orb_hamming_knn_merge)."""
-    Q = len(parts[0])
-    d = np.stack([np.stack([p["d1"], p["d2"]], 1) for p in parts], 1).reshape(Q, -1).astype(np.int64)
-    i = np.stack([np.stack([p["i1"], p["i2"]], 1) for p in parts], 1).reshape(Q, -1).astype(np.int64)
-    key = np.where((i < 0) | (d >= sentinel), np.iinfo(np.int64).max, (d << 40) | np.maximum(i, 0))
-    key.sort(axis=1)
-    out = np.zeros(Q, KNN_DTYPE)
-    big = np.iinfo(np.int64).max
-    a, b = key[:, 0], key[:, 1]
-    out["d1"] = np.where(a == big, sentinel, a >> 40)
-    out["i1"] = np.where(a == big, -1, a & ((1 << 40) - 1))
-    ok2 = (a != big) & (b != big)
-    out["d2"] = np.where(ok2, b >> 40, sentinel)
-    out["i2"] = np.where(ok2, b & ((1 << 40) - 1), -1)
+def hamming_knn_sharded(query, db_shard, shard_base: int, group=None, sentinel: int = 256, out=None, comm: int | None = None, stream=None):
+    """Database sharded contiguously over the ranks of `group` (ascending rank = ascending rows): orb_hamming_knn_sharded = local k=2 on this
+    rank's shard, ONE ncclAllGather of the per-query records, device top-2 merge - all behind the C ABI, asynchronous on the stream.
+    Equals one sequential scan over the concatenated database (earliest global index wins ties). query / db_shard: torch uint8 CUDA tensors."""
+    import torch
+    if not query.is_cuda:
+        raise RuntimeError("hamming_knn_sharded needs CUDA tensors (there is no CPU fallback)")
+    assert db_shard.is_cuda and query.is_contiguous() and db_shard.is_contiguous()
+    Q = query.shape[0]
+    if out is None:
+        out = torch.empty((Q, 3), dtype=torch.int64, device=query.device)
+    if comm is None:
+        comm = nccl_comm_ptr(group)
+    st = (stream or torch.cuda.current_stream(query.device)).cuda_stream
+    check(_lib.lib().orb_hamming_knn_sharded(query.data_ptr(), MEM_DEVICE, Q, db_shard.data_ptr(), MEM_DEVICE, db_shard.shape[0], shard_base, sentinel,
+                                             out.data_ptr(), MEM_DEVICE, C.c_void_p(comm), C.c_void_p(st)))
     return out
 
 

