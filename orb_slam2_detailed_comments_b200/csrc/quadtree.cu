@@ -13,12 +13,15 @@
 //    (canonical replacement of the reference's (size, heap pointer) order), cut at the first
 //    parent after which size >= N. The cut is a prefix-sum over P of (nonempty children - 1).
 // Child slots: the first non-empty child reuses its parent's slot, so live slots == list size <= max(N+3, 4*nIni).
+#include <cstdlib>
+
 #include "orb_common.cuh"
 
 // CTA size NT: 192 threads for the usual levels (the kernel shares the SMs with the blur of the same pass and the FAST kernel of the
 // other pass stream: 512-thread CTAs cost the KITTI step 3.5 %, 192 instead of 256 gains 0.8 % / TUM 1.7 %), 512 for large levels
 // (4K: +11 % images/s) and for small passes (per-call latency), chosen by orb_launch_quadtree.
 #define QT_SORT_SMEM 2048
+#define QT_ILP 4       // keys in flight per thread in the per-round key passes
 #define QT_SMALL 192   // CTA size for the usual levels (register caps below the natural 56 were measured too: no gain)
 
 template <int NT, typename T>
@@ -160,10 +163,21 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
   __syncthreads();
   for (int i = tid; i < nIni; i += NT)
     bbox[i] = make_int4((int)__fmul_rn(hX, (float)i), 0, (int)__fmul_rn(hX, (float)(i + 1)), L.maxBY - ORB_MIN_BORDER);
-  for (int i = tid; i < n; i += NT) {
-    const int r = (int)__fdiv_rn((float)(key[i] & 0xfffu), hX);
-    knode[i] = r;
-    atomicAdd(&ncount[r], 1);
+  {   // n keys land on nIni (1..4, more only for aspect > 4.5) counters: per-thread counts, one warp reduction, one atomic per warp and root
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    for (int i = tid; i < n; i += NT) {
+      const int r = (int)__fdiv_rn((float)(key[i] & 0xfffu), hX);
+      knode[i] = r;
+      if (r == 0) ++c0; else if (r == 1) ++c1; else if (r == 2) ++c2; else if (r == 3) ++c3; else atomicAdd(&ncount[r], 1);
+    }
+    c0 = __reduce_add_sync(0xffffffffu, c0); c1 = __reduce_add_sync(0xffffffffu, c1);
+    c2 = __reduce_add_sync(0xffffffffu, c2); c3 = __reduce_add_sync(0xffffffffu, c3);
+    if (lane == 0) {
+      if (c0) atomicAdd(&ncount[0], c0);
+      if (c1) atomicAdd(&ncount[1], c1);
+      if (c2) atomicAdd(&ncount[2], c2);
+      if (c3) atomicAdd(&ncount[3], c3);
+    }
   }
   if (tid == 0) s_nalloc = nIni;
   __syncthreads();
@@ -191,18 +205,41 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
     }
     if (tid == 0) { s_cut = k; s_ncand = 0; }
     __syncthreads();
-    // B: classify keys of parents (DivideNode :968-1022)
-    for (int i = tid; i < n; i += NT) {
-      const int nd = knode[i];
-      const int r = pidx[nd];
-      if (r >= 0) {
-        const int4 b = bbox[nd];
-        const int hx = (b.z - b.x + 1) >> 1, hy = (b.w - b.y + 1) >> 1;   // ceil(w / 2.f), w >= 0
-        const uint32_t q = key[i];
-        const int x = q & 0xfffu, y = (q >> 12) & 0xfffu;
-        const int c = (x < b.x + hx ? 0 : 1) + (y < b.y + hy ? 0 : 2);
-        kchild[i] = (uint8_t)c;
-        atomicAdd(&ccnt[4 * r + c], 1);
+    // B: classify keys of parents (DivideNode :968-1022). Every key costs a chain of dependent loads (node -> parent slot -> box) that hit L2:
+    //    QT_ILP keys per thread are in flight together, each stage's loads issued before the previous stage's results are used.
+    const bool few_parents = 4 * k <= n / 8;   // on average >= 8 keys per child counter: aggregation pays
+    for (int i0 = tid; i0 - lane < n; i0 += NT * QT_ILP) {   // warp-uniform trip count (MATCH.ANY needs the full warp)
+      int nd[QT_ILP], r[QT_ILP];
+      uint32_t q[QT_ILP];
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) {
+        const int i = i0 + u * NT;
+        nd[u] = i < n ? knode[i] : -1;
+        q[u] = i < n ? key[i] : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) r[u] = nd[u] >= 0 ? pidx[nd[u]] : -1;
+      int4 b[QT_ILP];
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) b[u] = r[u] >= 0 ? bbox[nd[u]] : make_int4(0, 0, 0, 0);
+      // the early rounds have a handful of parents: thousands of keys count into the same few child counters. Lanes that hit the same counter
+      // are found with one MATCH.ANY and their leader adds the group's size (the loop is warp-uniform, so all lanes take part)
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) {
+        int slot = -1;
+        if (r[u] >= 0) {
+          const int hx = (b[u].z - b[u].x + 1) >> 1, hy = (b[u].w - b[u].y + 1) >> 1;   // ceil(w / 2.f), w >= 0
+          const int x = q[u] & 0xfffu, y = (q[u] >> 12) & 0xfffu;
+          const int c = (x < b[u].x + hx ? 0 : 1) + (y < b[u].y + hy ? 0 : 2);
+          kchild[i0 + u * NT] = (uint8_t)c;
+          slot = 4 * r[u] + c;
+        }
+        if (few_parents) {
+          const unsigned same = __match_any_sync(0xffffffffu, slot);
+          if (slot >= 0 && (int)(__ffs(same) - 1) == lane) atomicAdd(&ccnt[slot], __popc(same));
+        } else if (slot >= 0) {
+          atomicAdd(&ccnt[slot], 1);
+        }
       }
     }
     __syncthreads();
@@ -262,11 +299,23 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
       if (tid == 0) { atomicOr(err_flag, 4); kept_cnt[frame * g.nlevels + level] = 0; }
       return;
     }
-    // F: move keys to their child nodes
-    for (int i = tid; i < n; i += NT) {
-      const int nd = knode[i];
-      const int r = pidx[nd];
-      if (r >= 0 && r < kc) knode[i] = cslot[4 * r + kchild[i]];
+    // F: move keys to their child nodes (same software pipelining as B)
+    for (int i0 = tid; i0 < n; i0 += NT * QT_ILP) {
+      int nd[QT_ILP], r[QT_ILP], ch[QT_ILP];
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) {
+        const int i = i0 + u * NT;
+        nd[u] = i < n ? knode[i] : -1;
+        ch[u] = i < n ? (int)kchild[i] : 0;
+      }
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) r[u] = nd[u] >= 0 ? pidx[nd[u]] : -1;
+      int sl[QT_ILP];
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u) sl[u] = (r[u] >= 0 && r[u] < kc) ? cslot[4 * r[u] + ch[u]] : -1;
+#pragma unroll
+      for (int u = 0; u < QT_ILP; ++u)
+        if (sl[u] >= 0) knode[i0 + u * NT] = sl[u];
     }
     // G: survivors keep their relative order behind the new children
     unsigned long long* sflag = scan;   // reuse (E is done with it after the barrier below)
@@ -322,8 +371,19 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
   // ---- per node keep the best key (:1387-1413), output in list order
   for (int q = tid; q < m; q += NT) best[ordOld[q]] = 0u;
   __syncthreads();
-  for (int i = tid; i < n; i += NT)
-    atomicMax(&best[knode[i]], ((key[i] >> 24) << 24) | (0xffffffu - (unsigned)i));
+  for (int i0 = tid; i0 < n; i0 += NT * QT_ILP) {
+    int nd[QT_ILP];
+    uint32_t q[QT_ILP];
+#pragma unroll
+    for (int u = 0; u < QT_ILP; ++u) {
+      const int i = i0 + u * NT;
+      nd[u] = i < n ? knode[i] : -1;
+      q[u] = i < n ? key[i] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < QT_ILP; ++u)
+      if (nd[u] >= 0) atomicMax(&best[nd[u]], ((q[u] >> 24) << 24) | (0xffffffu - (unsigned)(i0 + u * NT)));
+  }
   __syncthreads();
   for (int q = tid; q < m; q += NT) {
     const unsigned b = best[ordOld[q]];
@@ -336,8 +396,12 @@ void orb_launch_quadtree(const int* cell_cnt, const uint32_t* cell_kp, const QtS
                          int* err_flag, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
   // large levels (4K: 9017 cells, quota 1737 at level 0) are a long chain of rounds over tens of thousands of keys: twice the threads
   // ...and so are the few CTAs of a small pass (a Frame's one or two images: latency matters and the SMs are idle anyway)
-  const bool big = g.lv[0].nCols * g.lv[0].nRows >= 2048 || g.lv[0].quota >= 1024 || batch <= 8;
-  if (big) orb_quadtree_kernel<512><<<batch * g.nlevels, 512, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
+  const bool huge = g.lv[0].nCols * g.lv[0].nRows >= 2048 || g.lv[0].quota >= 1024;   // 4K: tens of thousands of keys per level
+  const bool big = batch <= 8;
+  static const int force = getenv("ORB_B200_QT_THREADS") ? atoi(getenv("ORB_B200_QT_THREADS")) : 0;   // A/B switch
+  const int nt = force ? force : huge ? 1024 : big ? 512 : QT_SMALL;
+  if (nt >= 1024) orb_quadtree_kernel<1024><<<batch * g.nlevels, 1024, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
+  else if (nt >= 512) orb_quadtree_kernel<512><<<batch * g.nlevels, 512, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
   else orb_quadtree_kernel<QT_SMALL><<<batch * g.nlevels, QT_SMALL, 0, st>>>(cell_cnt, cell_kp, S, kept, kept_cnt, err_flag, g);
   ++*launches;
 }
