@@ -103,7 +103,9 @@ float orb_extractor_get_scale_factor(const orb_extractor* e);
 /* what: 0 mvScaleFactor, 1 mvInvScaleFactor, 2 mvLevelSigma2, 3 mvInvLevelSigma2; out[nlevels] */
 int orb_extractor_get_table(const orb_extractor* e, int what, float* out);
 int orb_extractor_get_features_per_level(const orb_extractor* e, int32_t* out); /* mnFeaturesPerLevel */
-/* Upper bound on keypoints per image for buffer sizing: nfeatures + 3*nlevels (a split can overshoot the quota by 3). */
+/* Keypoint capacity per image for buffer sizing: nfeatures + 16*nlevels. A level's list ends at max(quota + 3, 4*nIni) at most (a split can
+ * overshoot the quota by 3; DistributeOctTree starts from nIni = round(width / height) roots, src/ORBextractor.cc:1059-1063), so 16 per level covers
+ * nIni <= 4, i.e. aspect ratios up to 4.5. A `cap` below what a frame produces is reported as ORB_E_CAPACITY (flag 8), never written past. */
 int orb_extractor_max_keypoints(const orb_extractor* e);
 
 /* operator() over a batch of equally sized CV_8UC1 images.
@@ -132,10 +134,15 @@ int orb_extract_stereo_batch(orb_extractor* e, const uint8_t* const* images, int
 
 /* Device-resident fast path used by the benchmark: `images` is ONE device buffer [batch][height][step];
  * outputs stay in device memory (kps/desc as above, counts_dev [batch] int32 device). Asynchronous on the
- * extractor's stream unless `sync` != 0. */
+ * extractor's stream unless `sync` != 0. With sync == 0 the capacity flags (a FAST cell with more than 128 NMS survivors - the reference's
+ * vector simply grows -, raw keypoints, nodes, `cap`) are NOT read by the call: truncated cells change the quadtree input silently, so an
+ * asynchronous caller must poll orb_extractor_check() at a point where it synchronises anyway. */
 int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, int width, int height, int batch,
                              orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts_dev, int sync);
 
+/* Waits for the handle's queued work and returns ORB_E_CAPACITY (message: which limit) if any call since the last check overflowed a
+ * capacity, ORB_E_CUDA on a device error, else ORB_OK; clears the flags. The synchronous entry points do this themselves. */
+int orb_extractor_check(orb_extractor* e);
 /* mvImagePyramid of image `index` of the last internal pass (index -1 = the last image of the last call, which is what the
  * reference's member holds): padded level (cols x rows), copied to `dst` (host, pitch dst_step).
  * blurred != 0 returns the Gaussian-blurred working copy instead (test hook). */

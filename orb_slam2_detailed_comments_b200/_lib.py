@@ -35,7 +35,7 @@ SYMBOLS = [
     "orb_extractor_get_features_per_level", "orb_extractor_max_keypoints", "orb_extract_batch",
     "orb_extract_batch_device", "orb_extract_stereo_batch", "orb_extractor_pyramid_dims", "orb_extractor_pyramid_read",
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
-    "orb_extractor_pyramid_read_all", "orb_extractor_set_pyramid_download", "orb_host_alloc", "orb_host_free",
+    "orb_extractor_check", "orb_extractor_pyramid_read_all", "orb_extractor_set_pyramid_download", "orb_host_alloc", "orb_host_free",
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn", "orb_hamming_knn_noalloc",
     "orb_hamming_knn_merge", "orb_hamming_knn_sharded", "orb_nccl_unique_id", "orb_nccl_comm_create", "orb_nccl_comm_destroy", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
     "orb_search_by_projection", "orb_distinctive_descriptors",

@@ -16,36 +16,68 @@
 #define BL_TW 128
 #define BL_TH 32
 #define BL_THREADS 320
-template <bool CLAMP>   // CLAMP: tap sum > 256 (legacy taps sum to 257): saturate like OpenCV's ufixedpoint -> u8 cast
+#define BL_RAW_W 160      // TMA box: columns x0 - 16 .. x0 + 143 (16-byte aligned start; the taps need x0 - 4 .. x0 + 131)
+#define BL_RAW_H 40       // rows y0 - 4 .. y0 + 35 (row y0 - 4 and rows past y0 + 34 only ever meet a zero tap)
+// TMA == true (ORB_B200_BLUR_TMA=1; measured alternative, 7 % slower: the CTA idles for the box's latency, 41 % of the stall samples on the
+// mbarrier wait, while the instruction count only drops from 89.1 M to 87.6 M per pass): ONE thread fetches the tile's 160 x 40-byte source window with a cp.async.bulk.tensor box (per-level tensor map of the
+// un-blurred planes; bytes outside the plane allocation arrive as zeros and only feed outputs that are not written) and the H pass reads it
+// from shared memory. TMA == false (default): every thread loads its 12 source words from global memory, all issued before any arithmetic.
+template <bool CLAMP, bool TMA>   // CLAMP: tap sum > 256 (legacy taps sum to 257): saturate like OpenCV's ufixedpoint -> u8 cast
 __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
-                                                              const __grid_constant__ OrbGeom g) {
+                                                              const __grid_constant__ OrbGeom g, const __grid_constant__ OrbLevelMaps maps) {
   __shared__ uint4 s_p[(BL_TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
+  __shared__ __align__(128) unsigned s_raw[TMA ? BL_RAW_H * BL_RAW_W / 4 : 4];
+  __shared__ __align__(8) unsigned long long s_bar;
   const int level = orb_level_of(g.blur_base, (int)blockIdx.x);
   const OrbLevel& L = g.lv[level];
   const unsigned t = blockIdx.x - L.blur_tile_base;
   const unsigned ty_ = (t * L.blur_inv_tx) >> 20;            // t / blur_tiles_x (host-checked range)
   const int x0 = (int)(t - ty_ * L.blur_tiles_x) * BL_TW, y0 = (int)ty_ * BL_TH;
   const unsigned long long off = (unsigned long long)blockIdx.y * g.frame_stride + L.plane_off;
-  const uint8_t* src = pyr + off;
   const unsigned tapA = g.blur_k[0], tapB = g.blur_k[1];
-  const int pitch = L.pitch;
-  // local row r <-> plane row y0 - 4 + r (row -4 and rows past rows + 3 only ever meet a zero tap)
-  // all 12 loads of this thread's two H-pass items (item = 4 pixels x 2 rows) are issued before any arithmetic
   unsigned cw[2][2][3];
   bool act[2];
+  if (TMA) {
+    const unsigned bar = orb_smem_u32(&s_bar);
+    if (threadIdx.x == 0) {
+      orb_mbar_init(bar, 1);
+      orb_mbar_expect_tx(bar, BL_RAW_H * BL_RAW_W);
+      // tensor coordinates = plane coordinates + (16-byte row lead, apron rows): column (x0 - 16) + 16, row (y0 - 4) + 4
+      orb_tma_load_3d(orb_smem_u32(s_raw), &maps.m[level], x0, y0, (int)blockIdx.y, bar);
+    }
+    __syncthreads();                                          // the barrier's initialisation is visible to every waiter
+    orb_mbar_wait(bar, 0);
 #pragma unroll
-  for (int it = 0; it < 2; ++it) {
-    const int i = threadIdx.x + it * BL_THREADS;   // 20 row pairs x 32 quads = 640 items
-    const int k = i >> 5, q = i & 31;
-    const int x = x0 + 4 * q;
-    act[it] = x < L.cols;
+    for (int it = 0; it < 2; ++it) {
+      const int i = threadIdx.x + it * BL_THREADS;   // 20 row pairs x 32 quads = 640 items
+      const int k = i >> 5, q = i & 31;
+      act[it] = x0 + 4 * q < L.cols;
 #pragma unroll
-    for (int rr = 0; rr < 2; ++rr) {
-      const int ry = min(y0 - 4 + 2 * k + rr, L.rows + 3);
-      const unsigned* row = reinterpret_cast<const unsigned*>(src + (long long)ry * pitch + x);
-      if (act[it]) { cw[it][rr][0] = __ldg(row - 1); cw[it][rr][1] = __ldg(row); cw[it][rr][2] = __ldg(row + 1); }
+      for (int rr = 0; rr < 2; ++rr) {
+        const unsigned* row = s_raw + (2 * k + rr) * (BL_RAW_W / 4) + 3 + q;   // word holding pixels x - 4 .. x - 1
+        cw[it][rr][0] = row[0]; cw[it][rr][1] = row[1]; cw[it][rr][2] = row[2];
+      }
+    }
+  } else {
+    const uint8_t* src = pyr + off;
+    const int pitch = L.pitch;
+    // local row r <-> plane row y0 - 4 + r (row -4 and rows past rows + 3 only ever meet a zero tap)
+    // all 12 loads of this thread's two H-pass items (item = 4 pixels x 2 rows) are issued before any arithmetic
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int i = threadIdx.x + it * BL_THREADS;   // 20 row pairs x 32 quads = 640 items
+      const int k = i >> 5, q = i & 31;
+      const int x = x0 + 4 * q;
+      act[it] = x < L.cols;
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        const int ry = min(y0 - 4 + 2 * k + rr, L.rows + 3);
+        const unsigned* row = reinterpret_cast<const unsigned*>(src + (long long)ry * pitch + x);
+        if (act[it]) { cw[it][rr][0] = __ldg(row - 1); cw[it][rr][1] = __ldg(row); cw[it][rr][2] = __ldg(row + 1); }
+      }
     }
   }
+  const int pitch = L.pitch;
 #pragma unroll
   for (int it = 0; it < 2; ++it) {
     const int i = threadIdx.x + it * BL_THREADS;
@@ -317,11 +349,22 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
   }
 }
 
-void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
+// maps: per-level TMA descriptors of pyr with a 160 x 40-byte box, used with ORB_B200_BLUR_TMA=1 only
+void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const void* maps, const OrbGeom& g, int batch, cudaStream_t st, long long* launches) {
+  static const bool want_tma = getenv("ORB_B200_BLUR_TMA") != nullptr;   // measured alternative, off by default (profiles/r2_tma_ab.md)
+  static const OrbLevelMaps no_maps = {};
   int sum = g.blur_taps[3];
   for (int i = 0; i < 3; ++i) sum += 2 * g.blur_taps[i];
-  if (sum > 256) orb_blur_kernel<true><<<dim3(g.blur_tiles_total, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
-  else orb_blur_kernel<false><<<dim3(g.blur_tiles_total, batch), BL_THREADS, 0, st>>>(pyr, blr, g);
+  const dim3 grid(g.blur_tiles_total, batch);
+  const bool tma = maps != nullptr && want_tma;
+  const OrbLevelMaps& M = tma ? *reinterpret_cast<const OrbLevelMaps*>(maps) : no_maps;
+  if (sum > 256) {
+    if (tma) orb_blur_kernel<true, true><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
+    else orb_blur_kernel<true, false><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
+  } else {
+    if (tma) orb_blur_kernel<false, true><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
+    else orb_blur_kernel<false, false><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
+  }
   ++*launches;
 }
 

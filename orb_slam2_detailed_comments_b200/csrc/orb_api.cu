@@ -37,7 +37,8 @@ struct orb_extractor {
     cudaEvent_t ev_fast = nullptr, ev_side = nullptr, ev_pyr = nullptr;   // ev_pyr: the pyramid of the pass is complete
     int frames = 0;          // frames of the last pass run here
     // per-level TMA descriptors of `pyr` / `blr`: FAST band windows (256 B x hCell + 6), IC_Angle windows (48 B x 31), descriptor patches (64 B x 37)
-    alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES];
+    alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES],
+        blur_maps[ORB_LEVEL_MAPS_BYTES];   // blur tiles: 160 B x 40 rows of pyr
     bool maps_ok = false;
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
     DevBuf st_sad;   // stereo: SAD of every kept match [chunk/2][cap]
@@ -289,6 +290,7 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
       // TMA descriptors follow the (re)allocated pyramid buffer; without the driver entry point the kernel stages with cp.async
       P.maps_ok = orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 256, 0, P.fast_maps) == 0 &&
                   orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 48, 31, P.ic_maps) == 0 &&
+                  orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 160, 40, P.blur_maps) == 0 &&
                   orb_build_level_maps(P.blr.as<uint8_t>(), (int)B, g, 64, 37, P.pt_maps) == 0;
     }
 #undef ENS
@@ -340,13 +342,13 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
   cudaStream_t sq = side >= 1 ? P.st_side : st;
   if (side >= 1) { cudaEventRecord(P.ev_fast, st); cudaStreamWaitEvent(sq, P.ev_fast, 0); }
   if (side == 0) {
-    orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
+    orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.maps_ok ? P.blur_maps : nullptr, g, n, st, &e->launches);
     if (prof) cudaEventRecord(ev[3], st);
   }
   orb_launch_quadtree(P.cell_cnt.as<int>(), P.cell_kp.as<uint32_t>(), S, P.kept.as<uint32_t>(), kept_cnt,
                       e->err.as<int>(), g, n, sq, &e->launches);
   if (prof) cudaEventRecord(ev[4], st);
-  if (side >= 1) orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), g, n, st, &e->launches);
+  if (side >= 1) orb_launch_blur(P.pyr.as<uint8_t>(), P.blr.as<uint8_t>(), P.maps_ok ? P.blur_maps : nullptr, g, n, st, &e->launches);
   cudaStream_t sd = side >= 2 ? P.st_side : st;
   if (side == 1) { cudaEventRecord(P.ev_side, sq); cudaStreamWaitEvent(st, P.ev_side, 0); }
   if (side >= 2) { cudaEventRecord(P.ev_fast, st); cudaStreamWaitEvent(sd, P.ev_fast, 0); }      // blur done
@@ -738,6 +740,14 @@ int orb_extract_stereo_batch(orb_extractor* e, const uint8_t* const* images, int
   const StereoReq sr{bf, b, uright, depth, matched};
   if (pairs <= 0) return fail(ORB_E_BADARG, "bad size");
   return extract_batch_impl(e, images, in_mem, step, width, height, 2 * pairs, kps, desc, out_mem, cap, counts, level_counts, &sr);
+}
+
+int orb_extractor_check(orb_extractor* e) {
+  if (!e) return fail(ORB_E_BADARG, "null argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  ORB_ON_DEVICE(e->device);
+  if (!e->err.p) return ORB_OK;   // nothing has run yet
+  return check_err_flag(e);
 }
 
 int orb_host_alloc(size_t bytes, void** out) {

@@ -24,7 +24,7 @@ void orb_fast_build_tiles(const OrbGeom&, std::vector<int4>&);
 int orb_build_level_maps(const uint8_t* base, int frames, const OrbGeom&, int box_w, int box_h, void* maps_out);
 #define ORB_LEVEL_MAPS_BYTES (128 * ORB_MAX_LEVELS)
 void orb_launch_quadtree(const int*, const uint32_t*, const QtScratch&, uint32_t*, int*, int*, const OrbGeom&, int, cudaStream_t, long long*);
-void orb_launch_blur(const uint8_t*, uint8_t*, const OrbGeom&, int, cudaStream_t, long long*);
+void orb_launch_blur(const uint8_t*, uint8_t*, const void* maps, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_describe(const uint8_t*, const uint8_t*, const void* ic_maps, const void* pt_maps, const uint32_t*, const int*, OrbKeypoint*, uint8_t*, int, int*, int*,
                          const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const int*, int, float, float, float*, float*, int*, int*, int*,

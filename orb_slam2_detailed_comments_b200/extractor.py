@@ -174,6 +174,11 @@ class ORBextractor:
         self._last_n = B
         return kps, desc, counts
 
+    def check(self):
+        """orb_extractor_check: waits for queued work; raises OrbError(ORB_E_CAPACITY) if a call since the last check overflowed a capacity
+        (what an asynchronous extract_batch_device(sync=False) caller has to poll)."""
+        check(self._L.orb_extractor_check(self._h))
+
     # ---- mvImagePyramid, include/ORBextractor.h:185 ----
     def pyramid_level(self, level: int, index: int = 0, blurred: bool = False) -> np.ndarray:
         c, r = C.c_int(), C.c_int()
