@@ -26,7 +26,7 @@ struct orb_extractor {
   int chunk = 0;           // frames per internal pass (workspace capacity)
   int cap_ws = 0;
   long long launches = 0;
-  DevBuf tabs, err, fast_tiles;
+  DevBuf tabs, err, fast_tiles, rs_tiles;
   // Two pass workspaces on two compute streams: consecutive internal passes alternate between them, so the latency-bound
   // tail of pass p (quadtree, descriptors) overlaps the bandwidth/issue-bound head of pass p+1 (pyramid, FAST, blur).
   // ws[0].st is the handle's public stream.
@@ -38,7 +38,8 @@ struct orb_extractor {
     int frames = 0;          // frames of the last pass run here
     // per-level TMA descriptors of `pyr` / `blr`: FAST band windows (256 B x hCell + 6), IC_Angle windows (48 B x 31), descriptor patches (64 B x 37)
     alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES],
-        blur_maps[ORB_LEVEL_MAPS_BYTES];   // blur tiles: 160 B x 40 rows of pyr
+        blur_maps[ORB_LEVEL_MAPS_BYTES],   // blur tiles: 160 B x 40 rows of pyr
+        rs_maps[ORB_LEVEL_MAPS_BYTES];     // tiled resize: 192 B x 44 rows of the source level
     bool maps_ok = false;
     DevBuf pyr, blr, cell_cnt, cell_kp, kept, kept_cnt, out_cnt;
     DevBuf st_sad;   // stereo: SAD of every kept match [chunk/2][cap]
@@ -120,7 +121,7 @@ static void resize_table(int ssz, int dsz, int lead, int len, ResizeTab* out) {
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // Per-shape geometry: level sizes (:2099-2102), FAST cell grid (:1443-1462), quadtree roots (:1059-1063).
-static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>& tabs) {
+static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>& tabs, std::vector<int>& rs_tiles) {
   OrbGeom g;
   memset(&g, 0, sizeof(g));
   const int nl = e->prm.nlevels;
@@ -139,6 +140,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
   size_t plane = 0;
   int cells = 0, raw = 0, nodes = 0, tab = 0, ftiles = 0;
   tabs.clear();
+  rs_tiles.clear();
   for (int l = 0; l < nl; ++l) {
     OrbLevel& L = g.lv[l];
     L.iw = cv_round_f((float)W * e->invScale[l]);
@@ -205,6 +207,31 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
         if (hi + 1 - lo > 7) L.pyr_fast = 0;
       }
       if (getenv("ORB_B200_PYR_GENERIC")) L.pyr_fast = 0;
+      // tiled variant: per 128-column / 32-row tile the origin of its source window; usable if every window fits the TMA box
+      {
+        const ResizeTab* xt = tabs.data() + tab;
+        const ResizeTab* yt = xt + L.xtab_len;
+        L.rs_ntx = (L.xtab_len + ORB_RS_TW - 1) / ORB_RS_TW;
+        L.rs_nty = (yrows + ORB_RS_TH - 1) / ORB_RS_TH;
+        L.rs_off = (int)rs_tiles.size();
+        std::vector<int> ynr;   // source rows a tile row needs (the y table folds back inside the reflected border: not derivable from its ends)
+        L.pyr_tiled = L.pyr_fast;
+        for (int tx = 0; tx < L.rs_ntx; ++tx) {
+          int lo = INT_MAX, hi = 0;
+          for (int x = tx * ORB_RS_TW; x < std::min((tx + 1) * ORB_RS_TW, L.xtab_len); ++x) { lo = std::min(lo, xt[x].ofs); hi = std::max(hi, xt[x].ofs + 1); }
+          lo &= ~15;
+          if (hi - lo + 8 > ORB_RS_BW) L.pyr_tiled = 0;   // + 8: a thread reads an aligned 12-byte window around its 8 source bytes
+          rs_tiles.push_back(lo);
+        }
+        for (int ty = 0; ty < L.rs_nty; ++ty) {
+          int lo = INT_MAX, hi = 0;
+          for (int y = ty * ORB_RS_TH; y < std::min((ty + 1) * ORB_RS_TH, yrows); ++y) { lo = std::min(lo, yt[y].ofs); hi = std::max(hi, std::min(yt[y].ofs + 1, P.rows - 1)); }
+          if (hi - lo + 1 > ORB_RS_BH) L.pyr_tiled = 0;
+          rs_tiles.push_back(lo);
+          ynr.push_back(hi - lo + 1);
+        }
+        rs_tiles.insert(rs_tiles.end(), ynr.begin(), ynr.end());
+      }
       tab += L.xtab_len + ytab_len;
     }
   }
@@ -237,7 +264,10 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
   int rc;
   if (e->geom.width != W || e->geom.height != H) {
     std::vector<ResizeTab> tabs;
-    if ((rc = build_geometry(e, W, H, tabs)) != ORB_OK) return rc;
+    std::vector<int> rs_tiles;
+    if ((rc = build_geometry(e, W, H, tabs, rs_tiles)) != ORB_OK) return rc;
+    if ((rc = e->rs_tiles.ensure(std::max<size_t>(rs_tiles.size(), 1) * sizeof(int))) != ORB_OK) return rc;
+    if (!rs_tiles.empty()) CU(cudaMemcpy(e->rs_tiles.p, rs_tiles.data(), rs_tiles.size() * sizeof(int), cudaMemcpyHostToDevice));
     if ((rc = e->tabs.ensure(std::max<size_t>(tabs.size(), 1) * sizeof(ResizeTab))) != ORB_OK) return rc;
     if (!tabs.empty()) CU(cudaMemcpyAsync(e->tabs.p, tabs.data(), tabs.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice, e->stream));
     CU(cudaStreamSynchronize(e->stream));
@@ -291,6 +321,7 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
       P.maps_ok = orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 256, 0, P.fast_maps) == 0 &&
                   orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 48, 31, P.ic_maps) == 0 &&
                   orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, 160, 40, P.blur_maps) == 0 &&
+                  orb_build_level_maps(P.pyr.as<uint8_t>(), (int)B, g, ORB_RS_BW, ORB_RS_BH, P.rs_maps) == 0 &&
                   orb_build_level_maps(P.blr.as<uint8_t>(), (int)B, g, 64, 37, P.pt_maps) == 0;
     }
 #undef ENS
@@ -327,7 +358,8 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
     if (prof) { ev = e->ev.data() + e->ev_used; e->ev_used += ORB_NUM_STAGES + 1; }
   }
   if (prof) cudaEventRecord(ev[0], st);
-  orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), g, n, st, &e->launches, ev_input_consumed);
+  orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), e->rs_tiles.as<int>(), P.maps_ok ? P.rs_maps : nullptr,
+                     e->num_sms, g, n, st, &e->launches, ev_input_consumed);
   if (mark_pyramid) cudaEventRecord(P.ev_pyr, st);
   if (prof) cudaEventRecord(ev[1], st);
   static const bool fast_v1 = getenv("ORB_B200_FAST_V1") != nullptr;   // round-1 kernel, same-box A/B only
@@ -455,7 +487,7 @@ void orb_extractor_destroy(orb_extractor* e) {
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   for (int w = 0; w < ORB_MAX_WS; ++w)
     for (DevBuf* b : e->ws[w].all) b->release();
-  DevBuf* bufs[] = {&e->tabs, &e->err, &e->fast_tiles, &e->cnt_all, &e->stage_in[0], &e->stage_in[1]};
+  DevBuf* bufs[] = {&e->tabs, &e->err, &e->fast_tiles, &e->rs_tiles, &e->cnt_all, &e->stage_in[0], &e->stage_in[1]};
   for (DevBuf* b : bufs) b->release();
   for (int b = 0; b <= ORB_MAX_WS; ++b) { e->out_kps[b].release(); e->out_desc[b].release(); e->out_ur[b].release(); e->out_dp[b].release(); }
   if (e->h_cnt) cudaFreeHost(e->h_cnt);

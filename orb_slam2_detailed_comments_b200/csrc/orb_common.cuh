@@ -15,6 +15,10 @@
 #define ORB_APRON 4          // reflect-101 apron columns written around every padded plane (3 used by the blur)
 #define ORB_APRON_ROWS 4     // allocated apron rows above/below a plane (3 written; the 4th is only ever multiplied by 0)
 #define ORB_FAST_TILE_W 219  // max detection-domain width of one FAST tile: 16 + 15 + 219 + 6 = the 256-byte window pitch in fast.cu
+#define ORB_RS_TW 128        // tiled resize: output tile, TMA box of the source level
+#define ORB_RS_TH 32
+#define ORB_RS_BW 192
+#define ORB_RS_BH 52         // this fork resizes the PADDED level l-1 to the interior of level l: row ratio 1.32 .. 1.56 -> <= 51 source rows per 32
 #define ORB_CELL_CAP 128     // NMS survivors kept per 30-px cell (overflow -> ORB_E_CAPACITY)
 
 struct OrbLevel {
@@ -36,6 +40,9 @@ struct OrbLevel {
   int tab_off;               // level >= 1: resize tables in padded destination coordinates: x table [xtab_len], then y table [rows]
   int xtab_len;              // cols rounded up to a multiple of 4
   int pyr_fast;              // 1: 4-pixel window kernel applies (horizontal ratio <= 2)
+  int pyr_tiled;             // 1: the shared-memory tiled resize applies (every 128 x 32 tile's source window fits one 192 x 52-byte TMA box)
+  int rs_ntx, rs_nty;        // tiles per row / column of the (cols + 8) x (rows + 6) output incl. apron
+  int rs_off;                // first int of this level's tile table: xlo[rs_ntx], ylo[rs_nty] (box origin in the source level, xlo % 16 == 0), ynr[rs_nty] (source rows needed)
   int fast_G, fast_nseg;     // FAST tile = one cell row x fast_G cells; segments per cell row
   int fast_tile_base;        // first FAST tile of this level
   unsigned fast_inv_nseg;    // 2^20 / fast_nseg + 1: t / fast_nseg == (t * inv) >> 20

@@ -16,7 +16,8 @@
 
 // ---- kernel launchers (other translation units) -------------------------------------------------------------
 struct OrbKnn2;
-void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const OrbGeom&, int, cudaStream_t, long long*, cudaEvent_t);
+void orb_launch_pyramid(const uint8_t*, int, long long, uint8_t*, const ResizeTab*, const int* rs_tiles, const void* rs_maps, int num_sms, const OrbGeom&,
+                        int, cudaStream_t, long long*, cudaEvent_t);
 void orb_launch_fast(const uint8_t*, const void* tiles, const void* maps, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);
 void orb_launch_fast_v1(const uint8_t*, int*, uint32_t*, int*, const OrbGeom&, int, cudaStream_t, long long*);   // round-1 kernel (A/B only)
 void orb_fast_build_tiles(const OrbGeom&, std::vector<int4>&);

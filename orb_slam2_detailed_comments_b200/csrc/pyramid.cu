@@ -8,6 +8,7 @@
 #include <cstdlib>
 
 #include "orb_common.cuh"
+#include "orb_tma.cuh"
 
 // Programmatic dependent launch (small passes only, see orb_launch_pyramid): the next kernel of the level chain may be scheduled while
 // this one drains; it blocks in orb_pdl_wait() until this grid has completed and its writes are visible. Both are no-ops for a
@@ -157,6 +158,103 @@ __global__ void __launch_bounds__(256) orb_pyr_resize4_kernel(uint8_t* __restric
   }
 }
 
+// Tiled, separable form of the same resize for large passes (TMA + shared memory), ORB_B200_PYR_TILED=1: bit-exact, but measured 15 % slower than
+// the register-window kernel above (39 against 27 thread instructions per pixel: the shared-memory round trip and per-row addressing cost more
+// than the 1.5x reuse of horizontal lerps saves), so it is the alternative, not the default. A 128 x 32 output tile (table coordinates: apron
+// included) needs <= 192 x 52 bytes of the source level. Persistent CTAs loop over (frame, tile) items with a two-stage pipeline: ONE thread issues the
+// cp.async.bulk.tensor box of the NEXT item while all threads work on the current one, so the box latency is hidden (a single-stage box per
+// tile is not: profiles/r2_tma_ab.md).
+//   H pass: every source row of the box is lerped ONCE to the tile's 128 output columns (the 4-pixel kernel above does it for both source rows of
+//           every output row, i.e. 2 / 1.2 = 1.7 times per source row): thread = pixel quad x every 8th row; 8-byte window + PRMT + DP2A as
+//           above; (t >> 4) is kept as u16 (<= 32640) in shared memory;
+//   V pass: thread = pixel quad x every 8th output row: two LDS.64 fetch the quad's values of its two source rows, (cy * t) >> 16 by IMAD.HI,
+//           + 2 >> 2, one 32-bit store. Identical integer arithmetic, hence identical bytes.
+#define RS_THREADS 256
+__global__ void __launch_bounds__(RS_THREADS) orb_pyr_resize_tiled_kernel(uint8_t* __restrict__ pyr, const ResizeTab* __restrict__ tabs,
+                                                                         const int* __restrict__ rs_tiles, int level, int batch,
+                                                                         const __grid_constant__ OrbGeom g,
+                                                                         const __grid_constant__ OrbLevelMaps maps) {
+  __shared__ __align__(128) uint8_t s_raw[2][ORB_RS_BW * ORB_RS_BH];
+  __shared__ __align__(16) unsigned short s_h[ORB_RS_BH][ORB_RS_TW];
+  __shared__ __align__(8) unsigned long long s_bar[2];
+  const OrbLevel& D = g.lv[level];
+  const OrbLevel& S = g.lv[level - 1];
+  const int tid = threadIdx.x, q = tid & 31, grp = tid >> 5;
+  const ResizeTab* xt = tabs + D.tab_off;
+  const ResizeTab* yt = xt + D.xtab_len;
+  const int* xlo_t = rs_tiles + D.rs_off;
+  const int* ylo_t = xlo_t + D.rs_ntx;
+  const int per_frame = D.rs_ntx * D.rs_nty;
+  const int total = per_frame * batch;
+  const int nrows = D.rows + 2 * (ORB_APRON - 1);
+  const unsigned bar0 = orb_smem_u32(&s_bar[0]);
+  if (tid == 0) { orb_mbar_init(bar0, 1); orb_mbar_init(bar0 + 8, 1); }
+  __syncthreads();
+  auto issue = [&](int item, int buf) {   // one thread: the source window of `item` into s_raw[buf]
+    const int frame = item / per_frame, t = item - frame * per_frame;
+    const int ty = t / D.rs_ntx, tx = t - ty * D.rs_ntx;
+    orb_mbar_expect_tx(bar0 + 8 * buf, ORB_RS_BW * ORB_RS_BH);
+    // tensor coordinates = source-level coordinates + (16-byte row lead, apron rows); bytes outside the allocation arrive as zeros (never selected)
+    orb_tma_load_3d(orb_smem_u32(s_raw[buf]), &maps.m[level - 1], xlo_t[tx] + 16, ylo_t[ty] + ORB_APRON_ROWS, frame, bar0 + 8 * buf);
+  };
+  if (tid == 0 && (int)blockIdx.x < total) issue(blockIdx.x, 0);
+  int it = 0;
+  for (int item = blockIdx.x; item < total; item += gridDim.x, ++it) {
+    const int buf = it & 1;
+    // s_raw[buf ^ 1] was last read in the H pass of the previous iteration, which every thread left before that iteration's first barrier
+    if (tid == 0 && item + (int)gridDim.x < total) issue(item + gridDim.x, buf ^ 1);
+    const int frame = item / per_frame, t = item - frame * per_frame;
+    const int ty = t / D.rs_ntx, tx = t - ty * D.rs_ntx;
+    const int x4 = tx * ORB_RS_TW + 4 * q;                // first table column of this thread's quad
+    const int xlo = xlo_t[tx], ylo = ylo_t[ty];
+    const bool xact = x4 < D.xtab_len;
+    // ---- H pass
+    uint4 e01 = make_uint4(0, 0, 0, 0), e23 = make_uint4(0, 0, 0, 0);
+    if (xact) { e01 = *reinterpret_cast<const uint4*>(xt + x4); e23 = *reinterpret_cast<const uint4*>(xt + x4 + 2); }
+    const int o0 = (int)e01.x, o1 = (int)e01.z, o2 = (int)e23.x, o3 = (int)e23.z;
+    const int lo = min(min(o0, o1), min(o2, o3));
+    const unsigned sh = 8u * (unsigned)(lo & 3);
+    const int wbase = (lo & ~3) - xlo;                     // box origin is 16-byte aligned: same word alignment as in global memory
+    const unsigned s0 = 17u * (unsigned)(o0 - lo) + 16u, s1 = 17u * (unsigned)(o1 - lo) + 16u, s2 = 17u * (unsigned)(o2 - lo) + 16u,
+                   s3 = 17u * (unsigned)(o3 - lo) + 16u;   // PRMT selectors: bytes (r, r + 1) of the window
+    const int nsrc = ylo_t[D.rs_nty + ty];                // source rows this tile row needs (host table)
+    orb_mbar_wait(bar0 + 8 * buf, (unsigned)(it >> 1) & 1u);
+    if (xact) {
+      const uint8_t* raw = s_raw[buf] + wbase;
+      for (int r = grp; r < nsrc; r += RS_THREADS / 32) {
+        const unsigned* w = reinterpret_cast<const unsigned*>(raw + r * ORB_RS_BW);
+        const unsigned a0 = w[0], a1 = w[1], a2 = w[2];
+        const unsigned al = __funnelshift_r(a0, a1, sh), ah = __funnelshift_r(a1, a2, sh);
+        const unsigned t0 = __dp2a_lo(e01.y, __byte_perm(al, ah, s0), 0u) >> 4, t1 = __dp2a_lo(e01.w, __byte_perm(al, ah, s1), 0u) >> 4,
+                       t2 = __dp2a_lo(e23.y, __byte_perm(al, ah, s2), 0u) >> 4, t3 = __dp2a_lo(e23.w, __byte_perm(al, ah, s3), 0u) >> 4;
+        *reinterpret_cast<uint2*>(&s_h[r][4 * q]) = make_uint2(t0 | (t1 << 16), t2 | (t3 << 16));
+      }
+    }
+    __syncthreads();
+    // ---- V pass
+    if (xact) {
+      uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + D.plane_off;
+#pragma unroll
+      for (int j = 0; j < ORB_RS_TH / (RS_THREADS / 32); ++j) {
+        const int y = ty * ORB_RS_TH + grp + (RS_THREADS / 32) * j;
+        if (y < nrows) {
+          const ResizeTab tyy = yt[y];
+          const unsigned cy0 = (tyy.coef & 0xffffu) << 16, cy1 = tyy.coef & 0xffff0000u;   // pre-shifted: (cy * t) >> 16 == umulhi(cy << 16, t)
+          const int r0 = tyy.ofs - ylo, r1 = min(tyy.ofs + 1, S.rows - 1) - ylo;
+          const uint2 a = *reinterpret_cast<const uint2*>(&s_h[r0][4 * q]), b = *reinterpret_cast<const uint2*>(&s_h[r1][4 * q]);
+          const unsigned v0 = (__umulhi(cy0, a.x & 0xffffu) + __umulhi(cy1, b.x & 0xffffu) + 2u) >> 2;
+          const unsigned v1 = (__umulhi(cy0, a.x >> 16) + __umulhi(cy1, b.x >> 16) + 2u) >> 2;
+          const unsigned v2 = (__umulhi(cy0, a.y & 0xffffu) + __umulhi(cy1, b.y & 0xffffu) + 2u) >> 2;
+          const unsigned v3 = (__umulhi(cy0, a.y >> 16) + __umulhi(cy1, b.y >> 16) + 2u) >> 2;
+          *reinterpret_cast<unsigned*>(dst + (long long)(y - (ORB_APRON - 1)) * D.pitch + x4 - ORB_APRON) =
+              __byte_perm(__byte_perm(v0, v1, 0x0040), __byte_perm(v2, v3, 0x0040), 0x5410);
+        }
+      }
+    }
+    __syncthreads();   // s_h and s_raw[buf] may be overwritten
+  }
+}
+
 template <typename... KArgs, typename... Args>
 static void launch_chain(void (*kern)(KArgs...), dim3 grd, dim3 blk, cudaStream_t st, bool pdl, Args... args) {
   cudaLaunchConfig_t cfg = {};
@@ -168,8 +266,10 @@ static void launch_chain(void (*kern)(KArgs...), dim3 grd, dim3 blk, cudaStream_
   cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
-void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride, uint8_t* pyr, const ResizeTab* tabs,
-                        const OrbGeom& g, int batch, cudaStream_t st, long long* launches, cudaEvent_t ev_input_consumed) {
+void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride, uint8_t* pyr, const ResizeTab* tabs, const int* rs_tiles,
+                        const void* rs_maps, int num_sms, const OrbGeom& g, int batch, cudaStream_t st, long long* launches,
+                        cudaEvent_t ev_input_consumed) {
+  static const bool tiled = getenv("ORB_B200_PYR_TILED") != nullptr;   // measured alternative (15 % slower, profiles/r2_tma_ab.md): off by default
   dim3 blk(32, 8);
   // small passes (a Frame's one or two images) are a chain of launch latencies: overlap each launch with the tail of the previous
   // kernel. Large passes keep ordinary launches: waiting CTAs would hold SM slots the other pass stream can use.
@@ -200,7 +300,11 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
   }
   for (int l = 1; l < g.nlevels; ++l) {
     const OrbLevel& L = g.lv[l];
-    if (L.pyr_fast) {
+    if (L.pyr_tiled && rs_maps && !pdl && tiled) {   // large passes: persistent CTAs, two-stage TMA pipeline, separable lerp through shared memory
+      const int items = L.rs_ntx * L.rs_nty * batch;
+      const int ctas = std::min(items, num_sms * 5);     // 28 KB of shared memory each
+      orb_pyr_resize_tiled_kernel<<<ctas, RS_THREADS, 0, st>>>(pyr, tabs, rs_tiles, l, batch, g, *reinterpret_cast<const OrbLevelMaps*>(rs_maps));
+    } else if (L.pyr_fast) {
       dim3 grd((L.xtab_len / 4 + 31) / 32, (L.rows + 2 * (ORB_APRON - 1) + 31) / 32, batch);
       launch_chain(orb_pyr_resize4_kernel, grd, blk, st, pdl, pyr, tabs, l, g);
     } else {
