@@ -15,6 +15,13 @@
 //   gen_accept_init.inc   src/ORBmatcher.cc:641-645      `if (best <= TH_LOW) { if (best < (float)second * mfNNratio) {`
 //   gen_distinctive.inc   src/MapPoint.cc:468-510        all-pairs distances + least-median row of ComputeDistinctiveDescriptors
 //   gen_stereo.inc        src/Frame.cc:880-1176          Frame::ComputeStereoMatches
+//   gen_sbp.inc           src/ORBmatcher.cc:69-194       SearchByProjection(Frame&, vector<MapPoint*>&, th) + RadiusByViewingCos (N2, local-map form)
+//   gen_sbow.inc          src/ORBmatcher.cc:248-410      SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (N2: FeatureVector walk, rotation filter)
+//   gen_sinit.inc         src/ORBmatcher.cc:570-712      SearchForInitialization (N2: vMatchedDistance / eviction bookkeeping, rotation filter)
+//   gen_grid.inc          src/Frame.cc:432-460           Frame::AssignFeaturesToGrid
+//   gen_area.inc          src/Frame.cc:633-717           Frame::GetFeaturesInArea
+//   gen_posingrid.inc     src/Frame.cc:729-745           Frame::PosInGrid
+//   gen_griddefs.inc      include/Frame.h:54, 59         #define FRAME_GRID_ROWS 48 / FRAME_GRID_COLS 64
 // FORB::distance (Thirdparty/DBoW2/DBoW2/FORB.cpp:81-103, the verbatim twin of DescriptorDistance) is linked in compiled unmodified.
 //
 // usage: orb_ref_match MODE IN.bin OUT.bin     (formats: tests/ref_binary.py)
@@ -29,6 +36,7 @@
 #include <vector>
 
 #include "FORB.h"
+#include "FeatureVector.h"
 #include "cvshim/cvshim.h"
 
 using namespace std;   // the reference's sources say `vector`, `sort`, `pair` unqualified (src/ORBmatcher.cc:43)
@@ -40,6 +48,50 @@ class ORBextractor {   // include/ORBextractor.h:185: the one member ComputeSter
   std::vector<cv::Mat> mvImagePyramid;
 };
 
+#include "_ref/gen_griddefs.inc"
+
+class MapPoint {       // include/MapPoint.h: the members the matcher loops name
+ public:
+  bool mbTrackInView = true;
+  int mnTrackScaleLevel = 0;
+  float mTrackViewCos = 1.f, mTrackProjX = 0.f, mTrackProjY = 0.f, mTrackProjXR = 0.f;
+  bool isBad() { return bad; }
+  int Observations() { return nObs; }
+  cv::Mat GetDescriptor() { return mDescriptor.clone(); }   // include/MapPoint.h: returns mDescriptor.clone()
+  bool bad = false;
+  int nObs = 0;
+  cv::Mat mDescriptor;
+};
+
+class Frame {          // include/Frame.h: the members src/Frame.cc:880-1176, 432-460, 633-745 and the matcher loops name
+ public:
+  void ComputeStereoMatches();
+  void AssignFeaturesToGrid();
+  bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
+  vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1, const int maxLevel = -1) const;
+  int N;
+  std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
+  cv::Mat mDescriptors, mDescriptorsRight;
+  ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
+  std::vector<float> mvScaleFactors, mvInvScaleFactors;
+  std::vector<float> mvuRight, mvDepth;
+  std::vector<MapPoint*> mvpMapPoints;
+  DBoW2::FeatureVector mFeatVec;
+  float mb, mbf;
+  // static members of the reference's class (include/Frame.h:190-200): plain members here, named unqualified inside the member functions
+  float mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+  std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+};
+
+class KeyFrame {       // include/KeyFrame.h: what SearchByBoW reads
+ public:
+  std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+  DBoW2::FeatureVector mFeatVec;
+  cv::Mat mDescriptors;
+  std::vector<cv::KeyPoint> mvKeysUn;
+  std::vector<MapPoint*> mvpMapPoints;
+};
+
 class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
  public:
   ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
@@ -48,6 +100,10 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   static const int TH_HIGH;
   static const int HISTO_LENGTH;
   void ComputeThreeMaxima(vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
+  int SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th = 3);
+  int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
+  int SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12, int windowSize = 10);
+  float RadiusByViewingCos(const float& viewCos);
   // harness entry points around the extracted loop bodies (declared here so the bodies see the members unqualified)
   void Scan(const cv::Mat& Q, const cv::Mat& D, int32_t* out);
   void ScanInit(const cv::Mat& Q, const cv::Mat& D, const std::vector<int>& matched_distance, int32_t* out);
@@ -55,22 +111,16 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   bool mbCheckOrientation;
 };
 
-class Frame {          // include/Frame.h: the members src/Frame.cc:880-1176 names
- public:
-  void ComputeStereoMatches();
-  int N;
-  std::vector<cv::KeyPoint> mvKeys, mvKeysRight;
-  cv::Mat mDescriptors, mDescriptorsRight;
-  ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
-  std::vector<float> mvScaleFactors, mvInvScaleFactors;
-  std::vector<float> mvuRight, mvDepth;
-  float mb, mbf;
-};
-
 #include "_ref/gen_consts.inc"
 #include "_ref/gen_distance.inc"
 #include "_ref/gen_three_maxima.inc"
 #include "_ref/gen_stereo.inc"
+#include "_ref/gen_grid.inc"
+#include "_ref/gen_area.inc"
+#include "_ref/gen_posingrid.inc"
+#include "_ref/gen_sbp.inc"
+#include "_ref/gen_sbow.inc"
+#include "_ref/gen_sinit.inc"
 
 struct FrameDescs { cv::Mat mDescriptors; };
 
@@ -139,7 +189,7 @@ static cv::Mat mat_u8(const uint8_t* src, int rows, int cols) {
 }
 
 int main(int argc, char** argv) {
-  if (argc != 4) { std::fprintf(stderr, "usage: %s distance|scan|scan_init|three_maxima|distinctive|stereo IN OUT\n", argv[0]); return 1; }
+  if (argc != 4) { std::fprintf(stderr, "usage: %s distance|scan|scan_init|three_maxima|distinctive|stereo|sbp|sbow|sinit IN OUT\n", argv[0]); return 1; }
   const std::string mode = argv[1];
   std::vector<uint8_t> in = slurp(argv[2]);
   Reader r{in.data()};
@@ -210,6 +260,109 @@ int main(int argc, char** argv) {
     F.ComputeStereoMatches();
     outf = F.mvuRight;
     outf.insert(outf.end(), F.mvDepth.begin(), F.mvDepth.end());
+  } else if (mode == "sbp") {
+    // float bounds[4] (mnMinX, mnMinY, mnMaxX, mnMaxY), th, nnratio; int nlevels; nlevels x float scale; int n; n x KeyPoint (mvKeysUn); n x 32 B;
+    // n x float mvuRight; n x u8 "already holds a map point with observations"; int m; m x {float projX, projY, projXR, viewCos; int level, flags
+    // (1 = !mbTrackInView, 2 = Observations() > 0)} ; m x 32 B  ->  int nmatches; n x int32 index of the map point assigned by this call (-1 none)
+    ORB_SLAM2::Frame F;
+    F.mnMinX = r.get<float>(); F.mnMinY = r.get<float>(); F.mnMaxX = r.get<float>(); F.mnMaxY = r.get<float>();
+    const float th = r.get<float>(), nnratio = r.get<float>();
+    const int nl = r.get<int32_t>();
+    for (int l = 0; l < nl; ++l) F.mvScaleFactors.push_back(r.get<float>());
+    F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);     // src/Frame.cc:200-202
+    F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
+    const int n = r.get<int32_t>();
+    F.N = n;
+    F.mvKeysUn.resize(n);
+    std::memcpy(F.mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+    F.mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+    F.mvuRight.resize(n);
+    std::memcpy(F.mvuRight.data(), r.bytes((size_t)n * 4), (size_t)n * 4);
+    ORB_SLAM2::MapPoint taken;   // a map point with observations, standing for whatever the keypoint was matched to before the call
+    taken.nObs = 1;
+    F.mvpMapPoints.assign(n, nullptr);
+    const uint8_t* cl = r.bytes(n);
+    for (int i = 0; i < n; ++i) if (cl[i]) F.mvpMapPoints[i] = &taken;
+    F.AssignFeaturesToGrid();
+    const int m = r.get<int32_t>();
+    std::vector<ORB_SLAM2::MapPoint> pts(m);
+    for (int i = 0; i < m; ++i) {
+      pts[i].mTrackProjX = r.get<float>(); pts[i].mTrackProjY = r.get<float>(); pts[i].mTrackProjXR = r.get<float>(); pts[i].mTrackViewCos = r.get<float>();
+      pts[i].mnTrackScaleLevel = r.get<int32_t>();
+      const int fl = r.get<int32_t>();
+      pts[i].mbTrackInView = !(fl & 1);
+      pts[i].nObs = (fl & 2) ? 1 : 0;
+    }
+    std::vector<ORB_SLAM2::MapPoint*> vp(m);
+    for (int i = 0; i < m; ++i) { pts[i].mDescriptor = mat_u8(r.bytes(32), 1, 32); vp[i] = &pts[i]; }
+    ORB_SLAM2::ORBmatcher matcher(nnratio, true);
+    out.push_back(matcher.SearchByProjection(F, vp, th));
+    for (int i = 0; i < n; ++i) {
+      ORB_SLAM2::MapPoint* p = F.mvpMapPoints[i];
+      out.push_back(p && p != &taken ? (int32_t)(p - pts.data()) : -1);
+    }
+  } else if (mode == "sbow") {
+    // float nnratio; int checkOri; keyframe: int nkf; nkf x 32 B; nkf x KeyPoint (mvKeysUn); nkf x u8 "holds a good map point"; FeatureVector
+    // {int count; count x {uint32 node; int m; m x uint32 feature}}; frame: int nf; nf x 32 B; nf x KeyPoint (mvKeys); FeatureVector
+    // -> int nmatches; nf x int32 keyframe feature whose map point was assigned (-1 none)
+    const float nnratio = r.get<float>();
+    const int ori = r.get<int32_t>();
+    ORB_SLAM2::KeyFrame KF;
+    ORB_SLAM2::Frame F;
+    auto read_fv = [&](DBoW2::FeatureVector& fv) {
+      const int cnt = r.get<int32_t>();
+      for (int j = 0; j < cnt; ++j) {
+        const uint32_t node = r.get<uint32_t>();
+        const int mm = r.get<int32_t>();
+        std::vector<unsigned int>& v = fv[node];
+        for (int k = 0; k < mm; ++k) v.push_back(r.get<uint32_t>());
+      }
+    };
+    const int nkf = r.get<int32_t>();
+    KF.mDescriptors = mat_u8(r.bytes((size_t)nkf * 32), nkf, 32);
+    KF.mvKeysUn.resize(nkf);
+    std::memcpy(KF.mvKeysUn.data(), r.bytes((size_t)nkf * 28), (size_t)nkf * 28);
+    std::vector<ORB_SLAM2::MapPoint> pts(nkf);
+    const uint8_t* valid = r.bytes(nkf);
+    KF.mvpMapPoints.assign(nkf, nullptr);
+    for (int i = 0; i < nkf; ++i) if (valid[i]) KF.mvpMapPoints[i] = &pts[i];
+    read_fv(KF.mFeatVec);
+    const int nf = r.get<int32_t>();
+    F.N = nf;
+    F.mDescriptors = mat_u8(r.bytes((size_t)nf * 32), nf, 32);
+    F.mvKeys.resize(nf);
+    std::memcpy(F.mvKeys.data(), r.bytes((size_t)nf * 28), (size_t)nf * 28);
+    read_fv(F.mFeatVec);
+    ORB_SLAM2::ORBmatcher matcher(nnratio, ori != 0);
+    std::vector<ORB_SLAM2::MapPoint*> matches;
+    out.push_back(matcher.SearchByBoW(&KF, F, matches));
+    for (int i = 0; i < nf; ++i) out.push_back(matches[i] ? (int32_t)(matches[i] - pts.data()) : -1);
+  } else if (mode == "sinit") {
+    // float bounds[4], nnratio; int checkOri, windowSize; F2: int n; n x KeyPoint (mvKeysUn); n x 32 B; F1: int m; m x KeyPoint (mvKeysUn: octave,
+    // angle); m x 32 B; m x {float x, y} vbPrevMatched  ->  int nmatches; m x int32 vnMatches12
+    ORB_SLAM2::Frame F1, F2;
+    F2.mnMinX = r.get<float>(); F2.mnMinY = r.get<float>(); F2.mnMaxX = r.get<float>(); F2.mnMaxY = r.get<float>();
+    const float nnratio = r.get<float>();
+    const int ori = r.get<int32_t>(), window = r.get<int32_t>();
+    F2.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F2.mnMaxX - F2.mnMinX);   // src/Frame.cc:200-202
+    F2.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F2.mnMaxY - F2.mnMinY);
+    const int n = r.get<int32_t>();
+    F2.N = n;
+    F2.mvKeysUn.resize(n);
+    std::memcpy(F2.mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+    F2.mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+    F2.AssignFeaturesToGrid();
+    const int m = r.get<int32_t>();
+    F1.N = m;
+    F1.mvKeysUn.resize(m);
+    std::memcpy(F1.mvKeysUn.data(), r.bytes((size_t)m * 28), (size_t)m * 28);
+    F1.mDescriptors = mat_u8(r.bytes((size_t)m * 32), m, 32);
+    std::vector<cv::Point2f> prev(m);
+    for (int i = 0; i < m; ++i) { prev[i].x = r.get<float>(); prev[i].y = r.get<float>(); }
+    ORB_SLAM2::ORBmatcher matcher(nnratio, ori != 0);
+    std::vector<int> m12;
+    out.push_back(matcher.SearchForInitialization(F1, F2, prev, m12, window));
+    for (int i = 0; i < m; ++i) out.push_back(m12[i]);
   } else {
     std::fprintf(stderr, "unknown mode %s\n", mode.c_str());
     return 1;

@@ -169,3 +169,52 @@ def ref_stereo(scale, levels_left, levels_right, kl, dl, kr, dr, bf: float, b: f
     out = np.frombuffer(_run_match("stereo", payload), "<f4")
     n = len(kl)
     return out[:n].copy(), out[n:2 * n].copy()
+
+
+def ref_search_by_projection(kps_un, desc, uright, claimed, bounds, scale, th, nnratio, proj, qdesc):
+    """ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) (src/ORBmatcher.cc:69-184) with RadiusByViewingCos, on a Frame whose grid is
+    built by the reference's AssignFeaturesToGrid / PosInGrid and searched by its GetFeaturesInArea (src/Frame.cc:432-460, 729-745, 633-717).
+    proj: structured array (projx, projy, projxr, viewcos: f4; level, flags: i4; flags 1 = !mbTrackInView, 2 = Observations() > 0).
+    Returns (nmatches, assigned [n]: index of the map point this call assigned to the keypoint, -1 none)."""
+    n, m = len(kps_un), len(proj)
+    kps_un = np.ascontiguousarray(kps_un)
+    assert kps_un.dtype.itemsize == 28 and proj.dtype.itemsize == 24
+    payload = struct.pack("<4f2fi", *[float(b) for b in bounds], th, nnratio, len(scale)) + np.ascontiguousarray(scale, "<f4").tobytes()
+    payload += struct.pack("<i", n) + kps_un.tobytes() + np.ascontiguousarray(desc, np.uint8).tobytes()
+    payload += np.ascontiguousarray(uright if uright is not None else np.full(n, -1, np.float32), "<f4").tobytes()
+    payload += np.ascontiguousarray(claimed if claimed is not None else np.zeros(n, np.uint8), np.uint8).tobytes()
+    payload += struct.pack("<i", m) + np.ascontiguousarray(proj).tobytes() + np.ascontiguousarray(qdesc, np.uint8).tobytes()
+    out = np.frombuffer(_run_match("sbp", payload), "<i4")
+    return int(out[0]), out[1:1 + n].copy()
+
+
+def _fv_bytes(fv: dict) -> bytes:
+    b = struct.pack("<i", len(fv))
+    for node in sorted(fv):
+        idx = np.asarray(fv[node], "<u4")
+        b += struct.pack("<Ii", node, len(idx)) + idx.tobytes()
+    return b
+
+
+def ref_search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv: dict, f_desc, f_kps, f_fv: dict, nnratio: float, check_orientation: bool):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (src/ORBmatcher.cc:248-410). kf_fv / f_fv: {node: [feature indices]}.
+    Returns (nmatches, assigned [n_f]: keyframe feature whose map point the frame keypoint got, -1 none)."""
+    nkf, nf = len(kf_kps_un), len(f_kps)
+    payload = struct.pack("<fi", nnratio, int(check_orientation))
+    payload += struct.pack("<i", nkf) + np.ascontiguousarray(kf_desc, np.uint8).tobytes() + np.ascontiguousarray(kf_kps_un).tobytes()
+    payload += np.ascontiguousarray(kf_valid, np.uint8).tobytes() + _fv_bytes(kf_fv)
+    payload += struct.pack("<i", nf) + np.ascontiguousarray(f_desc, np.uint8).tobytes() + np.ascontiguousarray(f_kps).tobytes() + _fv_bytes(f_fv)
+    out = np.frombuffer(_run_match("sbow", payload), "<i4")
+    return int(out[0]), out[1:1 + nf].copy()
+
+
+def ref_search_for_initialization(kps2_un, desc2, kps1_un, desc1, prev_matched, bounds, nnratio, check_orientation, window):
+    """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) on F2's reference-built grid.
+    Returns (nmatches, vnMatches12 [m])."""
+    n, m = len(kps2_un), len(kps1_un)
+    payload = struct.pack("<4ffii", *[float(b) for b in bounds], nnratio, int(check_orientation), int(window))
+    payload += struct.pack("<i", n) + np.ascontiguousarray(kps2_un).tobytes() + np.ascontiguousarray(desc2, np.uint8).tobytes()
+    payload += struct.pack("<i", m) + np.ascontiguousarray(kps1_un).tobytes() + np.ascontiguousarray(desc1, np.uint8).tobytes()
+    payload += np.ascontiguousarray(prev_matched, "<f4").tobytes()
+    out = np.frombuffer(_run_match("sinit", payload), "<i4")
+    return int(out[0]), out[1:1 + m].copy()

@@ -1,6 +1,7 @@
 """Pins the matcher-side oracles — and on the GPU box the CUDA kernels directly — against the REFERENCE'S OWN CODE for
 M1 DescriptorDistance, M2 the best / second-best scan with both accept tests, ComputeThreeMaxima, N4 the least-median loop of
-MapPoint::ComputeDistinctiveDescriptors and N1 Frame::ComputeStereoMatches.
+MapPoint::ComputeDistinctiveDescriptors, N1 Frame::ComputeStereoMatches and N2: the frame grid, SearchByProjection (local-map form), SearchByBoW and
+SearchForInitialization.
 
 How: src/ORBmatcher.cc, src/MapPoint.cc and src/Frame.cc cannot be compiled whole in this image (they include the whole SLAM system, Eigen,
 g2o, Pangolin), but these function bodies touch none of it. `make -C oracle _ref` cuts them out of /root/reference BY LINE RANGE into
@@ -219,3 +220,99 @@ def test_cuda_distance_and_distinctive_equal_reference():
     ref = ref_binary.ref_distinctive(desc, offsets)
     bi, bm = ORBmatcher.ComputeDistinctiveDescriptors(desc, offsets)
     assert np.array_equal(bi, ref[:, 0]) and np.array_equal(bm, ref[:, 1])
+
+
+# ---- N2: guided matchers --------------------------------------------------------------------------------------------------------------------
+PROJ_DTYPE = np.dtype([("projx", "<f4"), ("projy", "<f4"), ("projxr", "<f4"), ("viewcos", "<f4"), ("level", "<i4"), ("flags", "<i4")])
+SCALE = np.cumprod(np.concatenate([[1.0], np.full(7, 1.2)])).astype(np.float32)
+
+
+def _local_map_case(seed, n=900, m=700, w=752, h=480, stereo=True, th=1.0, bounds=None):
+    """Keypoints / map points for the local-map SearchByProjection: the reference's inputs (projection, predicted level, viewing cosine per map
+    point) and the C ABI's query records derived from them the way the host code derives them: radius = RadiusByViewingCos(cos) [* th] *
+    mvScaleFactors[level] in float32, level window [level - 1, level] (src/ORBmatcher.cc:88-105)."""
+    from orb_slam2_detailed_comments_b200._lib import QUERY_DTYPE
+    c = synth.synth_guided_case(seed, n=n, m=m, w=w, h=h, stereo=stereo, bounds=bounds)
+    rng = np.random.default_rng(seed + 1000)
+    q = c["queries"]
+    proj = np.zeros(m, PROJ_DTYPE)
+    proj["projx"], proj["projy"], proj["projxr"] = q["u"], q["v"], q["ur"]
+    proj["viewcos"] = np.where(rng.random(m) < 0.5, 0.9995, 0.97).astype(np.float32)
+    proj["level"] = np.clip(q["max_level"], 0, 7)
+    proj["flags"] = q["flags"]
+    r = np.where(proj["viewcos"] > np.float32(0.998), np.float32(2.5), np.float32(4.0)).astype(np.float32)   # RadiusByViewingCos (:187-194)
+    if th != 1.0:
+        r = (r * np.float32(th)).astype(np.float32)
+    q2 = np.zeros(m, QUERY_DTYPE)
+    q2["u"], q2["v"], q2["ur"] = proj["projx"], proj["projy"], proj["projxr"]
+    q2["radius"] = (r * SCALE[proj["level"]]).astype(np.float32)
+    q2["min_level"], q2["max_level"] = proj["level"] - 1, proj["level"]
+    q2["flags"] = proj["flags"]
+    return c, proj, q2
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,stereo,th,ratio,bounds", [(1, True, 1.0, 0.8, None), (2, False, 3.0, 0.8, None), (3, True, 5.0, 0.6, (-11.5, -7.25, 770.0, 493.5)),
+                                                         (4, True, 1.0, 0.9, None)])
+def test_search_by_projection_equals_reference(oracle, seed, stereo, th, ratio, bounds):
+    """oracle.search_by_projection == the reference's own SearchByProjection(Frame&, vector<MapPoint*>&, th) + RadiusByViewingCos + frame grid
+    (AssignFeaturesToGrid, PosInGrid, GetFeaturesInArea), compiled from line-range cuts: window lookup and scan order, level window, stereo check,
+    claims through Observations(), level-conditional ratio test, TH_HIGH."""
+    c, proj, q2 = _local_map_case(seed, stereo=stereo, th=th, bounds=bounds)
+    nm_ref, as_ref = ref_binary.ref_search_by_projection(c["kps"], c["desc"], c["uright"], c["claimed"], c["bounds"], SCALE, th, ratio, proj, c["qdesc"])
+    assigned, qmatch, nm = oracle.search_by_projection(c["kps"], c["desc"], q2, c["qdesc"], c["bounds"], th_dist=100, nn_ratio=ratio,
+                                                       check_orientation=False, uright=c["uright"], claimed=c["claimed"])
+    assert nm == nm_ref and nm_ref > 100, (nm, nm_ref)
+    assert np.array_equal(assigned, as_ref), f"assignment differs at keypoints {np.flatnonzero(assigned != as_ref)[:10]}"
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,ori,ratio", [(1, True, 0.7), (2, False, 0.6), (3, True, 0.9)])
+def test_search_by_bow_equals_reference(oracle, seed, ori, ratio):
+    """oracle.search_by_bow == the reference's own SearchByBoW(KeyFrame*, Frame&, ...): FeatureVector walk with lower_bound, per-node scan, TH_LOW
+    + ratio accept, claims through vpMapPointMatches, rotation histogram + ComputeThreeMaxima."""
+    import test_search_by_bow as tb
+    voc = synth.synth_vocabulary(10, 3, seed=11)
+    ov = oracle.OracleVocabulary(*voc)
+    kf, kk, valid, f, fk = tb._pair(voc, seed, 500, 560)
+    kfv, ffv = ov.transform(kf, 2)[3], ov.transform(f, 2)[3]
+    # FeatureVectors that do not share every node: exercises both lower_bound branches
+    kfv = {n: v for n, v in kfv.items() if n % 5 != 1}
+    ffv = {n: v for n, v in ffv.items() if n % 7 != 2}
+    nm_ref, as_ref = ref_binary.ref_search_by_bow(kf, kk, valid, kfv, f, fk, ffv, ratio, ori)
+    got = oracle.search_by_bow(kf, kk, valid, tb._csr(kfv, len(kf)), f, fk, tb._csr(ffv, len(f)), 50, ratio, ori)
+    assert got[1] == nm_ref and nm_ref > 40, (got[1], nm_ref)
+    assert np.array_equal(got[0], as_ref)
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cuda_search_by_projection_equals_reference():
+    from orb_slam2_detailed_comments_b200.matcher import ORBmatcher
+    for seed, stereo, th, ratio in ((11, True, 1.0, 0.8), (12, False, 3.0, 0.8), (13, True, 5.0, 0.6)):
+        c, proj, q2 = _local_map_case(seed, stereo=stereo, th=th)
+        nm_ref, as_ref = ref_binary.ref_search_by_projection(c["kps"], c["desc"], c["uright"], c["claimed"], c["bounds"], SCALE, th, ratio, proj, c["qdesc"])
+        n, m = len(c["kps"]), len(q2)
+        assigned, qmatch, nm = ORBmatcher(ratio).SearchByProjection(c["kps"][None], c["desc"][None], np.array([n], np.int32), q2[None], c["qdesc"][None],
+                                                                    np.array([m], np.int32), c["bounds"], use_ratio=True,
+                                                                    uright=None if c["uright"] is None else c["uright"][None], claimed=c["claimed"][None])
+        assert nm[0] == nm_ref and np.array_equal(assigned[0], as_ref), (seed, nm[0], nm_ref)
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,ori", [(1, True), (2, False), (3, True)])
+def test_search_for_initialization_equals_reference(oracle, seed, ori):
+    """oracle.search_for_initialization == the reference's own SearchForInitialization: level-0 filter, window 100 on F2's grid, INT_MAX sentinels,
+    vMatchedDistance skip, eviction of an earlier match by a strictly closer one, rotation histogram over ALL accepts, three maxima."""
+    import test_search_init as ti
+    from orb_slam2_detailed_comments_b200._lib import KP_DTYPE
+    c = ti._case(seed, n=420, m=400)
+    q = c["queries"]
+    k1 = np.zeros(len(q), KP_DTYPE)
+    k1["angle"] = q["angle"]
+    k1["octave"] = np.where(q["flags"] & 1, 1, 0)        # `if (level1 > 0) continue;` (:597-599)
+    prev = np.stack([q["u"], q["v"]], axis=1)
+    nm_ref, m12_ref = ref_binary.ref_search_for_initialization(c["kps"], c["desc"], k1, c["qdesc"], prev, c["bounds"], 0.9, ori, 100)
+    m12, m21, nm = oracle.search_for_initialization(c["kps"], c["desc"], q, c["qdesc"], c["bounds"], 50, 0.9, ori)
+    assert nm == nm_ref and nm_ref > 40, (nm, nm_ref)
+    assert np.array_equal(m12, m12_ref)
