@@ -16,11 +16,11 @@ static void check(int rc, const char* what) {
   if (rc < 0) throw std::runtime_error(std::string(what) + ": " + orb_last_error());
 }
 
-ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST, int device)
+ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST, int device, int flags)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST) {
   orb_params p;
   p.nfeatures = _nfeatures; p.scale_factor = _scaleFactor; p.nlevels = _nlevels;
-  p.ini_th_fast = _iniThFAST; p.min_th_fast = _minThFAST; p.flags = 0;
+  p.ini_th_fast = _iniThFAST; p.min_th_fast = _minThFAST; p.flags = flags;
   check(orb_extractor_create(&p, device, &mpHandle), "orb_extractor_create");
   // the tables are computed once by the library with the reference's mixed float/double arithmetic (src/ORBextractor.cc:776-845)
   mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels); mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);

@@ -28,7 +28,8 @@ class ORBextractor {
   enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };   // include/ORBextractor.h:87-91 (unused by the reference as well)
 
   // include/ORBextractor.h:104. `device` selects the GPU (default: current CUDA device 0).
-  ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0);
+  // `flags`: orb_flags of include/orb_b200.h (1 = raulmur's un-padded pyramid instead of this fork's padded one, 2 = OpenCV <= 3.4.0 blur taps).
+  ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device = 0, int flags = 0);
   ~ORBextractor();
   ORBextractor(const ORBextractor&) = delete;
   ORBextractor& operator=(const ORBextractor&) = delete;

@@ -60,7 +60,10 @@ enum orb_status {
 enum orb_mem { ORB_MEM_HOST = 0, ORB_MEM_DEVICE = 1 };
 
 enum orb_flags {
-  ORB_FLAG_UPSTREAM_PYRAMID = 1, /* reserved: raulmur/ORB_SLAM2 ROI pyramid; NOT implemented on device (create fails) */
+  ORB_FLAG_UPSTREAM_PYRAMID = 1, /* raulmur/ORB_SLAM2's ComputePyramid, i.e. the reference without the line its annotator added
+                                    (`mvImagePyramid[level] = temp;`, src/ORBextractor.cc:2166): mvImagePyramid[l] is the w_l x h_l image, each
+                                    level is resized from it, keypoints are in its coordinates. Non-default; same kernels with a
+                                    stored border of 0 instead of 19 px. orb_extractor_pyramid_dims / _read return w_l x h_l then. */
   ORB_FLAG_LEGACY_BLUR = 2       /* OpenCV <= 3.4.0 Gaussian taps [18,34,49,55,49,34,18] instead of [18,34,48,56,48,34,18] */
 };
 

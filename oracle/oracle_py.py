@@ -79,7 +79,7 @@ class OracleExtractor:
         self.h = self.L.orb_oracle_create(nfeatures, scale_factor, nlevels, ini_th, min_th, flags)
         if not self.h:
             raise ValueError("bad ORB parameters")
-        self.nlevels, self.nfeatures = nlevels, nfeatures
+        self.nlevels, self.nfeatures, self.flags = nlevels, nfeatures, flags
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -119,6 +119,9 @@ class OracleExtractor:
         ptr = (self.L.orb_oracle_blurred_ptr if blurred else self.L.orb_oracle_level_ptr)(self.h, l)
         if not ptr:
             return None
+        if blurred and self.flags & UPSTREAM_PYRAMID:   # the blurred copy is made of mvImagePyramid[l] = the interior of the stored padded buffer
+            c.value -= 38
+            r.value -= 38
         buf = (C.c_uint8 * (c.value * r.value)).from_address(ptr)
         return np.frombuffer(buf, np.uint8).reshape(r.value, c.value).copy()
 

@@ -514,7 +514,9 @@ int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_e
   const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
   const Extractor& EL = left->ex;
   const Extractor& ER = right->ex;
-  const int nRows = EL.pyr[0].rows;
+  // UPSTREAM_PYRAMID: mvImagePyramid[l] is the interior of the stored padded buffer
+  const int off = (EL.flags & ORB_ORACLE_UPSTREAM_PYRAMID) ? kEdge : 0;
+  const int nRows = EL.pyr[0].rows - 2 * off;
   for (int i = 0; i < nL; ++i) { uright[i] = -1.0f; depth[i] = -1.0f; }
   std::vector<std::vector<int>> rowIdx(nRows);
   for (int iR = 0; iR < nR; ++iR) {
@@ -560,10 +562,10 @@ int orb_oracle_stereo_match(const orb_oracle_extractor* left, const orb_oracle_e
     const int w = 5, L = 5;
     const Plane& PL = EL.pyr[kpL.octave];
     const Plane& PR = ER.pyr[kpL.octave];
-    const int cy = (int)scaledvL, cxl = (int)scaleduL, cxr = (int)scaleduR0;
+    const int cy = (int)scaledvL + off, cxl = (int)scaleduL + off, cxr = (int)scaleduR0 + off;
     const float iniu = scaleduR0 - L - w;
     const float endu = scaleduR0 + L + w + 1;
-    if (iniu < 0 || endu >= PR.cols) continue;
+    if (iniu < 0 || endu >= PR.cols - 2 * off) continue;
     int bestSad = INT_MAX, bestinc = 0;
     float vd[2 * 5 + 1];
     const float cl = (float)PL.buf[(size_t)cy * PL.cols + cxl];

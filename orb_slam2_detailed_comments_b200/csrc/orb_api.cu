@@ -102,12 +102,12 @@ static void build_tables(orb_extractor* e) {
 // reflect101(reflect101(p, dsz + 38) - 19, dsz). The in-place copyMakeBorder of src/ORBextractor.cc:2138 is an index remap
 // of the interior, and the apron (p < 0, p >= dsz + 38) is the BORDER_REFLECT_101 extension of the padded image that the
 // 7x7 blur reads (:2042). `len` entries are written; entries past the apron repeat the last valid one.
-static void resize_table(int ssz, int dsz, int lead, int len, ResizeTab* out) {
+static void resize_table(int ssz, int dsz, int pad, int lead, int len, ResizeTab* out) {
   const double scale = 1.0 / ((double)dsz / ssz);
-  const int padded = dsz + 2 * ORB_EDGE;
+  const int padded = dsz + 2 * pad;
   for (int t = 0; t < len; ++t) {
     const int p = std::min(t - lead, padded + ORB_APRON - 1);
-    const int d = orb_reflect101(orb_reflect101(p, padded) - ORB_EDGE, dsz);
+    const int d = orb_reflect101(orb_reflect101(p, padded) - pad, dsz);
     float f = (float)((d + 0.5) * scale - 0.5);
     int s = (int)floorf(f);
     f -= s;
@@ -127,6 +127,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
   const int nl = e->prm.nlevels;
   g.nlevels = nl; g.width = W; g.height = H;
   g.ini_th = e->prm.ini_th_fast; g.min_th = e->prm.min_th_fast;
+  g.pad = (e->prm.flags & ORB_FLAG_UPSTREAM_PYRAMID) ? 0 : ORB_EDGE;
   static const int taps_new[7] = {18, 34, 48, 56, 48, 34, 18}, taps_old[7] = {18, 34, 49, 55, 49, 34, 18};
   memcpy(g.blur_taps, (e->prm.flags & ORB_FLAG_LEGACY_BLUR) ? taps_old : taps_new, sizeof(g.blur_taps));
   {
@@ -147,7 +148,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.ih = cv_round_f((float)H * e->invScale[l]);
     if (L.iw < 2 * ORB_EDGE + 2 || L.ih < 2 * ORB_EDGE + 2)
       return fail(ORB_E_SHAPE, "level %d is %dx%d: too small for the 19-px reflect border", l, L.iw, L.ih);
-    L.cols = L.iw + 2 * ORB_EDGE; L.rows = L.ih + 2 * ORB_EDGE;
+    L.cols = L.iw + 2 * g.pad; L.rows = L.ih + 2 * g.pad;
     // plane = [4 apron rows][rows][4 apron rows], row = [16 B lead][cols][>= 8 B]: the pyramid kernels also write the
     // reflect-101 extension of the padded image (4 columns / 3 rows each side) so the blur never remaps indices
     L.pitch = (int)align_up(16 + L.cols + 8, 64);
@@ -197,8 +198,8 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
       const int yrows = L.rows + 2 * (ORB_APRON - 1);                   // rows -3 .. rows + 3
       const int ytab_len = (yrows + 3) & ~3;   // keeps every table 16-byte aligned
       tabs.resize(tab + L.xtab_len + ytab_len);
-      resize_table(P.cols, L.iw, ORB_APRON, L.xtab_len, tabs.data() + tab);          // source = PADDED level l-1 (this fork, :2119)
-      resize_table(P.rows, L.ih, ORB_APRON - 1, ytab_len, tabs.data() + tab + L.xtab_len);
+      resize_table(P.cols, L.iw, g.pad, ORB_APRON, L.xtab_len, tabs.data() + tab);   // source = stored level l-1: PADDED in this fork (:2119), the plain image upstream
+      resize_table(P.rows, L.ih, g.pad, ORB_APRON - 1, ytab_len, tabs.data() + tab + L.xtab_len);
       // the 4-pixel kernel reads an 8-byte source window per thread: needs ofs(x+3) + 1 - ofs(x) <= 7
       L.pyr_fast = 1;
       for (int x = 0; x + 3 < L.xtab_len && L.pyr_fast; x += 4) {
@@ -434,7 +435,7 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
   if (p->nfeatures < 1 || p->nlevels < 1 || p->nlevels > ORB_MAX_LEVELS || !(p->scale_factor > 1.0f) || p->min_th_fast < 1 ||
       p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 254)
     return fail(ORB_E_BADARG, "unsupported ORB parameters (nfeatures>=1, 1<=nlevels<=%d, scale>1, 1<=minTh<=iniTh<=254)", ORB_MAX_LEVELS);
-  if (p->flags & ORB_FLAG_UPSTREAM_PYRAMID) return fail(ORB_E_BADARG, "ORB_FLAG_UPSTREAM_PYRAMID is not implemented on device");
+  if (p->flags & ~(ORB_FLAG_UPSTREAM_PYRAMID | ORB_FLAG_LEGACY_BLUR)) return fail(ORB_E_BADARG, "unknown bits in orb_params.flags (%d)", p->flags);
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
   if (device < 0 || device >= ndev) return fail(ORB_E_BADARG, "device %d out of range (%d devices)", device, ndev);

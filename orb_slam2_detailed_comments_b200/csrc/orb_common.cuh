@@ -53,6 +53,8 @@ struct OrbLevel {
 
 struct OrbGeom {
   int nlevels, width, height;
+  int pad;                   // border stored around every level: ORB_EDGE (this fork: mvImagePyramid[l] is the padded image, F1) or 0 (ORB_FLAG_UPSTREAM_PYRAMID:
+                             // raulmur's pyramid, mvImagePyramid[l] is the w_l x h_l image; its reflect-101 border lives in the apron only)
   int ncells_total;
   int raw_total, node_total;
   int fast_tiles_total;      // FAST tiles per frame (all levels)

@@ -35,9 +35,9 @@ __global__ void __launch_bounds__(256) orb_pyr_level0_interior_kernel(const uint
   const int c = c_lo + blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y * blockDim.y + threadIdx.y - (ORB_APRON - 1);
   if (y >= L.rows + ORB_APRON - 1 || c > c_hi) return;
-  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - ORB_EDGE, g.height);
+  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - g.pad, g.height);
   const int x0 = 16 * c - 16;
-  const uint8_t* p = images + (long long)frame * image_stride + (long long)sy * step + (x0 - ORB_EDGE);
+  const uint8_t* p = images + (long long)frame * image_stride + (long long)sy * step + (x0 - g.pad);
   const unsigned sh = 8u * (unsigned)((uintptr_t)p & 3);
   const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)p & ~(uintptr_t)3);
   const unsigned w0 = __ldg(ap), w1 = __ldg(ap + 1), w2 = __ldg(ap + 2), w3 = __ldg(ap + 3), w4 = __ldg(ap + 4);
@@ -59,13 +59,13 @@ __global__ void __launch_bounds__(256) orb_pyr_level0_border_kernel(const uint8_
   const int k = i & 3, e = (i >> 2) % n_edge, y = (i >> 2) / n_edge - (ORB_APRON - 1);
   const int c = e < n_left ? e : c_hi + 1 + (e - n_left);
   const int x4 = 16 * c - 16 + 4 * k;
-  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - ORB_EDGE, g.height);
+  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - g.pad, g.height);
   const uint8_t* srow = images + (long long)frame * image_stride + (long long)sy * step;
   uint32_t out = 0;
 #pragma unroll
   for (int b = 0; b < 4; ++b) {
     const int x = max(min(x4 + b, L.cols + ORB_APRON - 1), -ORB_APRON);   // columns outside the apron are never read
-    out |= (uint32_t)__ldg(srow + orb_reflect101(orb_reflect101(x, L.cols) - ORB_EDGE, g.width)) << (8 * b);
+    out |= (uint32_t)__ldg(srow + orb_reflect101(orb_reflect101(x, L.cols) - g.pad, g.width)) << (8 * b);
   }
   uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off;
   *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x4) = out;
@@ -280,9 +280,10 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
     const OrbLevel& L = g.lv[0];
     const int nrows = L.rows + 2 * (ORB_APRON - 1);
     const int c_last = (L.cols + ORB_APRON - 1 + 16) / 16;              // chunk holding the last apron column
-    // interior chunk: source columns 16c - 35 .. 16c - 20 and the aligned words around them lie inside the source row
-    const int c_lo = 3;
-    const int c_hi = std::min(c_last, (g.width - 20 + 35) / 16);         // 16c - 35 <= W - 20
+    // interior chunk c: source columns 16c - 16 - pad .. 16c - 1 - pad and the aligned words around them (3 bytes before, 5 words from there) lie inside
+    // the source row: 16c - 19 - pad >= 0 and 16c + 3 - pad <= W - 1 (pad 19: c = 3 .. (W + 15) / 16)
+    const int c_lo = (19 + g.pad + 15) / 16;
+    const int c_hi = std::min(c_last, (g.width + g.pad - 4) / 16);
     const int n_int = std::max(c_hi - c_lo + 1, 0);
     const int hi_eff = n_int > 0 ? c_hi : c_lo - 1;
     const int n_left = std::min(c_lo, c_last + 1), n_edge = n_left + (c_last - hi_eff);

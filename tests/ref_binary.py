@@ -10,6 +10,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "oracle", "_ref", "orb_ref_extract")
+BIN_UPSTREAM = os.path.join(ROOT, "oracle", "_ref", "orb_ref_extract_upstream")   # same source minus src/ORBextractor.cc:2166
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"),
                      ("class_id", "<i4")])
 
@@ -18,8 +19,13 @@ def available() -> bool:
     return os.access(BIN, os.X_OK)
 
 
-def ref_extract(frames: np.ndarray, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, legacy_blur=False):
-    """frames: [n, H, W] u8 -> (tables [4, nlevels] f32, list of (kps, desc, [padded level images]))."""
+def upstream_available() -> bool:
+    return os.access(BIN_UPSTREAM, os.X_OK)
+
+
+def ref_extract(frames: np.ndarray, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, legacy_blur=False, upstream=False):
+    """frames: [n, H, W] u8 -> (tables [4, nlevels] f32, list of (kps, desc, [mvImagePyramid level images])).
+    upstream=True runs the build without the fork's `mvImagePyramid[level] = temp;` (raulmur's un-padded pyramid)."""
     frames = np.ascontiguousarray(frames, dtype=np.uint8)
     n, H, W = frames.shape
     with tempfile.TemporaryDirectory() as d:
@@ -31,7 +37,7 @@ def ref_extract(frames: np.ndarray, nfeatures=1000, scale_factor=1.2, nlevels=8,
         env.pop("ORB_REF_LEGACY_BLUR", None)
         if legacy_blur:
             env["ORB_REF_LEGACY_BLUR"] = "1"
-        subprocess.run([BIN, fin, fout], check=True, env=env, timeout=600)
+        subprocess.run([BIN_UPSTREAM if upstream else BIN, fin, fout], check=True, env=env, timeout=600)
         buf = open(fout, "rb").read()
     pos = 0
     nl = struct.unpack_from("<i", buf, pos)[0]; pos += 4

@@ -73,7 +73,7 @@ def test_bad_arguments_rejected_before_cuda():
     h = C.c_void_p()
     assert L.orb_extractor_create(None, 0, C.byref(h)) == _lib.ORB_E_BADARG
     for bad in [(0, 1.2, 8, 20, 7, 0), (100, 1.0, 8, 20, 7, 0), (100, 1.2, 0, 20, 7, 0), (100, 1.2, 17, 20, 7, 0),
-                (100, 1.2, 8, 5, 7, 0), (100, 1.2, 8, 20, 0, 0), (100, 1.2, 8, 20, 7, 1)]:
+                (100, 1.2, 8, 5, 7, 0), (100, 1.2, 8, 20, 0, 0), (100, 1.2, 8, 20, 7, 4), (100, 1.2, 8, 20, 7, -1)]:
         p = _lib.OrbParams(*bad)
         assert L.orb_extractor_create(C.byref(p), 0, C.byref(h)) == _lib.ORB_E_BADARG, bad
     assert L.orb_hamming_knn(None, 0, 1, None, 0, 0, 0, 256, None, 0, None) == _lib.ORB_E_BADARG

@@ -23,7 +23,7 @@ def _build():
 def test_dropin_builds_and_exports_reference_symbols():
     _build()
     out = subprocess.check_output(["nm", "-DC", "--defined-only", os.path.join(CPP, "liborb_slam2_frontend.so")], text=True)
-    for sym in ("ORB_SLAM2::ORBextractor::ORBextractor(int, float, int, int, int, int)",
+    for sym in ("ORB_SLAM2::ORBextractor::ORBextractor(int, float, int, int, int, int, int)",
                 "ORB_SLAM2::ORBextractor::operator()(cv::Mat const&, cv::Mat const&, std::vector<cv::KeyPoint",
                 "ORB_SLAM2::ORBmatcher::DescriptorDistance(cv::Mat const&, cv::Mat const&)",
                 "ORB_SLAM2::ORBmatcher::SearchByProjection(", "ORB_SLAM2::ORBmatcher::ComputeDistinctiveDescriptors(",

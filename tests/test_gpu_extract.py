@@ -26,13 +26,14 @@ def _extractor(nf, **kw):
 def _compare(img, nf, oracle, ini=20, mn=7, nlevels=8, sf=1.2, flags=0):
     from orb_slam2_detailed_comments_b200 import ORBextractor
     ex = ORBextractor(nf, sf, nlevels, ini, mn, flags=flags)
-    oflags = oracle.LEGACY_BLUR if flags & 2 else 0
+    oflags = (oracle.LEGACY_BLUR if flags & 2 else 0) | (oracle.UPSTREAM_PYRAMID if flags & 1 else 0)
+    core = (lambda a: a[19:-19, 19:-19]) if flags & 1 else (lambda a: a)   # the oracle keeps the padded buffer, mvImagePyramid[l] is its interior
     oe = oracle.OracleExtractor(nf, sf, nlevels, ini, mn, flags=oflags)
     okps, odesc, olc = oe(img)
     kps, desc, counts, lcounts = ex.extract_batch(img[None])
     n = int(counts[0])
     for l in range(nlevels):
-        assert np.array_equal(ex.pyramid_level(l), oe.level(l)), f"pyramid level {l}"
+        assert np.array_equal(ex.pyramid_level(l), core(oe.level(l))), f"pyramid level {l}"
     for l in range(nlevels):
         r_o, r_g = oe.raw_keypoints(l), ex.raw_keypoints(l)
         assert len(r_o) == len(r_g), f"raw count level {l}: {len(r_g)} vs {len(r_o)}"
@@ -65,6 +66,44 @@ def test_thresholds_and_levels(oracle):
     _compare(img, 800, oracle, ini=12, mn=7)            # KITTI04-12 stereo uses ini 12
     _compare(img, 300, oracle, nlevels=4, sf=1.5)
     _compare(img, 600, oracle, flags=2)                 # legacy blur taps
+
+
+@pytest.mark.parametrize("name,w,h,nf,seed", CASES)
+def test_upstream_pyramid_switch(oracle, name, w, h, nf, seed):
+    """ORB_FLAG_UPSTREAM_PYRAMID: raulmur's un-padded pyramid - the same kernels with a stored border of 0 instead of 19."""
+    img = synth.synth_frame(w, h, seed)
+    if name == "small":
+        # un-padded, level 7 of a 200 x 160 image is 56 x 45: narrower than one 30-px cell plus its borders, where the reference divides by
+        # nCols == 0 (src/ORBextractor.cc:1459-1462). The library refuses the shape; five levels fit.
+        from orb_slam2_detailed_comments_b200 import ORBextractor
+        from orb_slam2_detailed_comments_b200._lib import OrbError
+        with pytest.raises(OrbError):
+            ORBextractor(nf, 1.2, 8, 20, 7, flags=1).extract_batch(img[None])
+        assert _compare(img, nf, oracle, nlevels=5, flags=1) > 0
+        return
+    n = _compare(img, nf, oracle, flags=1)
+    assert n > 0
+    if name == "tum":
+        _compare(img, nf, oracle, flags=3)             # together with the legacy blur taps
+        _compare(img, 300, oracle, nlevels=4, sf=1.5, flags=1)
+
+
+def test_upstream_pyramid_stereo(oracle):
+    """ComputeStereoMatches over the un-padded pyramid: the SAD windows read mvImagePyramid[l] = the interior."""
+    from orb_slam2_detailed_comments_b200 import ORBextractor
+    left, right = synth.synth_stereo_pair(752, 480, 41, 9)
+    ex = ORBextractor(1200, 1.2, 8, 20, 7, flags=1)
+    kps, desc, counts, ur, dp, matched = ex.extract_stereo_batch(left[None], right[None], 47.9, 0.11)
+    oL = oracle.OracleExtractor(1200, flags=oracle.UPSTREAM_PYRAMID)
+    oR = oracle.OracleExtractor(1200, flags=oracle.UPSTREAM_PYRAMID)
+    kl, dl, _ = oL(left)
+    kr, dr, _ = oR(right)
+    our, odp, kept = oracle.stereo_match(oL, oR, kl, dl, kr, dr, 47.9, 0.11)
+    nl = int(counts[0])
+    assert nl == len(kl) and int(counts[1]) == len(kr)
+    assert np.array_equal(ur[0, :nl].view(np.uint32), our.view(np.uint32)), "mvuRight differs"
+    assert np.array_equal(dp[0, :nl].view(np.uint32), odp.view(np.uint32)), "mvDepth differs"
+    assert int(matched[0]) == kept and kept > 100
 
 
 def test_flat_and_noise_images(oracle):

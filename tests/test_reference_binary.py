@@ -81,6 +81,44 @@ def test_oracle_equals_reference_extractor_noise_flat_legacy(oracle):
     _check_frame(ref[0], kps, desc)
 
 
+needs_ref_upstream = pytest.mark.skipif(not ref_binary.upstream_available(), reason="oracle/_ref/orb_ref_extract_upstream not built")
+UPSTREAM_CASES = [c for c in CASES if c[0] in ("tum", "kitti", "euroc", "odd", "coarse", "nf20", "wide5to1")]
+
+
+@needs_ref_upstream
+@pytest.mark.parametrize("name,w,h,nf,n,seed,prm", UPSTREAM_CASES, ids=[c[0] for c in UPSTREAM_CASES])
+def test_oracle_upstream_pyramid_equals_reference_without_fork_line(oracle, name, w, h, nf, n, seed, prm):
+    """SURVEY F1 switch: the oracle with UPSTREAM_PYRAMID == the reference's source minus `mvImagePyramid[level] = temp;` (src/ORBextractor.cc:2166),
+    i.e. raulmur's ComputePyramid: mvImagePyramid[l] is the w_l x h_l interior, levels are resized from it, keypoints are in its coordinates."""
+    sf, nl, ini, mn = prm
+    frames = synth.synth_batch(w, h, n, seed0=seed, distinct=n)
+    _, ref = ref_binary.ref_extract(frames, nf, sf, nl, ini, mn, upstream=True)
+    _, ref_fork = ref_binary.ref_extract(frames[:1], nf, sf, nl, ini, mn)
+    oe = oracle.OracleExtractor(nf, sf, nl, ini, mn, flags=oracle.UPSTREAM_PYRAMID)
+    for i in range(n):
+        kps, desc, _ = oe(frames[i])
+        _check_frame(ref[i], kps, desc, [oe.level(l)[19:-19, 19:-19] for l in range(nl)])
+    assert ref[0][2][0].shape == (h, w) and ref_fork[0][2][0].shape == (h + 38, w + 38)
+    # the two pyramids really differ beyond level 0 (otherwise the switch would test nothing)
+    assert not np.array_equal(ref[0][2][1], ref_fork[0][2][1][19:-19, 19:-19])
+
+
+@pytest.mark.gpu
+@needs_ref_upstream
+@pytest.mark.parametrize("name,w,h,nf,n,seed,prm", UPSTREAM_CASES[:4], ids=[c[0] for c in UPSTREAM_CASES[:4]])
+def test_cuda_upstream_pyramid_equals_reference_without_fork_line(name, w, h, nf, n, seed, prm):
+    from orb_slam2_detailed_comments_b200 import ORBextractor
+    from orb_slam2_detailed_comments_b200._lib import FLAG_UPSTREAM_PYRAMID
+    sf, nl, ini, mn = prm
+    frames = synth.synth_batch(w, h, n, seed0=seed, distinct=n)
+    _, ref = ref_binary.ref_extract(frames, nf, sf, nl, ini, mn, upstream=True)
+    ex = ORBextractor(nf, sf, nl, ini, mn, flags=FLAG_UPSTREAM_PYRAMID)
+    kps, desc, counts, _ = ex.extract_batch(frames)
+    for i in range(n):
+        c = int(counts[i])
+        _check_frame(ref[i], kps[i, :c], desc[i, :c], [ex.pyramid_level(l, index=i) for l in range(nl)])
+
+
 def _bow_case(tmp_path, vkw, levelsup, sizes):
     voc = synth.synth_vocabulary(**vkw)
     p = str(tmp_path / "voc.txt")

@@ -188,6 +188,27 @@ def test_stereo_matches_equal_reference(oracle, w, h, nf, shift, bf, b):
     assert int((rur >= 0).sum()) == kept
 
 
+@needs_ref
+def test_stereo_matches_equal_reference_upstream_pyramid(oracle):
+    """The oracle's ComputeStereoMatches under UPSTREAM_PYRAMID (mvImagePyramid[l] = the un-padded interior) against the reference's own
+    function body fed with those interior levels. With un-padded coordinates every keypoint row is inside vRowIndices: nothing is left out."""
+    w, h, nf, shift, bf, b = 752, 480, 1200, 14, 47.9, 0.11
+    left, right = synth.synth_stereo_pair(w, h, 977, shift)
+    oL = oracle.OracleExtractor(nf, 1.2, 8, 20, 7, flags=oracle.UPSTREAM_PYRAMID)
+    oR = oracle.OracleExtractor(nf, 1.2, 8, 20, 7, flags=oracle.UPSTREAM_PYRAMID)
+    kl, dl, _ = oL(left)
+    kr, dr, _ = oR(right)
+    scale = oL.table(0)
+    ml, mr = _safe_rows(kl, scale, h, False), _safe_rows(kr, scale, h, True)
+    kl, dl, kr, dr = kl[ml], dl[ml], kr[mr], dr[mr]
+    ur, dp, kept = oracle.stereo_match(oL, oR, kl, dl, kr, dr, bf, b)
+    core = lambda a: np.ascontiguousarray(a[19:-19, 19:-19])
+    rur, rdp = ref_binary.ref_stereo(scale, [core(oL.level(l)) for l in range(8)], [core(oR.level(l)) for l in range(8)], kl, dl, kr, dr, bf, b)
+    assert kept > 50, kept
+    assert np.array_equal(ur.view(np.uint32), rur.view(np.uint32)), f"mvuRight differs at {np.flatnonzero(ur != rur)[:8]}"
+    assert np.array_equal(dp.view(np.uint32), rdp.view(np.uint32)), "mvDepth"
+
+
 # ---- CUDA == reference code, directly ----------------------------------------------------------------------------------------------------------
 @needs_ref
 @pytest.mark.gpu
