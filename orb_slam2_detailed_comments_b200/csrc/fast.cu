@@ -35,7 +35,9 @@
 #define FAST_THREADS 256
 #define FAST_WARPS 8
 #define FAST_WP 256      // window row pitch in smem: 16 B front pad + 15 alignment + ORB_FAST_TILE_W (219) + 6 halo = 256
-#define FAST_SP 240      // score plane row pitch: 15 + 219 + 4 <= 240
+#define FAST_SP 256      // score plane row pitch = FAST_WP: the score of the pixel at window byte offset a lives at sc[a - FAST_SC_OFF]
+#define FAST_SC_OFF (2 * FAST_WP + 16)   // window offset (y + 3) * 256 + 16 + x  ->  score plane offset (y + 1) * 256 + x
+#define FAST_TAB_BYTES (2 * FAST_WP + 32)   // host-built per-band tables: coltab[256] u16 + det8[32] u8
 #define FAST_MAXC 8      // cells per band (219 / 30 = 7) rounded up
 
 // cornerScore (OpenCV fast_score.cpp, 16-pixel ring, K = 8): S = max(max_arcs min_9(v - r), max_arcs min_9(r - v)) - 1,
@@ -86,8 +88,8 @@ __device__ __forceinline__ void fast_gt2(unsigned a, unsigned ti, unsigned tm, u
 
 // The candidates of one warp (bit masks cand[2] of every lane: byte (ri & 3) of cand[ri >> 2] = the 8 pixels of group
 // (lane + 5 * ri) & 31 in row warp + 8 * ri) go to list[start ..] as codes lane:5 | bit:6, are scored 32 at a time, and the corners
-// (S >= minTh) are compacted in place to list[start ..] as (y << 9) | x with their score written to the score plane.
-// Returns the number of corners appended.
+// (S >= minTh) are compacted in place to list[start ..] as their byte offset in the window, a = (y + 3) * 256 + 16 + x, with their score
+// written to the score plane at a - FAST_SC_OFF (same pitch: NMS and emission address both planes from a). Returns the number of corners appended.
 __device__ __forceinline__ int fast_score_candidates(const unsigned (&cand)[2], const uint8_t* __restrict__ win, uint8_t* __restrict__ sc,
                                                      uint16_t* __restrict__ list, int start, int warp, int qbase, int lane, int min_th) {
   const uint32_t lt = (1u << lane) - 1u;
@@ -107,29 +109,31 @@ __device__ __forceinline__ int fast_score_candidates(const unsigned (&cand)[2], 
       unsigned m = cand[hi];
       const unsigned code = (unsigned)((lane << 6) | (hi << 5));
       while (m) {
-        *out++ = (uint16_t)(code | (unsigned)(__ffs(m) - 1));
+        *out++ = (uint16_t)(code | (unsigned)(__ffs(m) - 1));   // lane:5 | bit:6 (this loop is divergent: the decoding is left to the full-lane loop below)
         m &= m - 1;
       }
     }
   }
   __syncwarp();
+  // offset of pixel 0 of group 0 in row `warp`; row warp + 8 * ri is 8 * 256 bytes further per ri, group o 8 bytes per o
+  const unsigned a0 = (unsigned)((warp + 3) * FAST_WP + 16 + qbase);
   int ncorner = 0;
   for (int c0 = 0; c0 < cnt; c0 += 32) {
     const int i = c0 + lane;
-    int e = 0, s = 0;
+    unsigned a = 0;
+    int s = 0;
     if (i < cnt) {
-      const int code = list[start + i];
-      const int ri = (code >> 3) & 7;
-      const int o = ((code >> 6) + 5 * ri) & 31;
-      e = ((warp + FAST_WARPS * ri) << 9) | (qbase + 8 * o + (code & 7));
-      s = fast_score(win + ((e >> 9) + 3) * FAST_WP + 16 + (e & 511));
+      const unsigned code = list[start + i];
+      const unsigned ri = (code >> 3) & 7u;
+      a = a0 + ri * (8u * FAST_WP) + 8u * (((code >> 6) + 5u * ri) & 31u) + (code & 7u);
+      s = fast_score(win + a);
     }
     const bool corner = s >= min_th;
     __syncwarp();                                            // the reads of this chunk precede the in-place writes below
     const uint32_t b = __ballot_sync(0xffffffffu, corner);
     if (corner) {
-      sc[((e >> 9) + 1) * FAST_SP + (e & 511)] = (uint8_t)s;
-      list[start + ncorner + __popc(b & lt)] = (uint16_t)e;
+      sc[a - FAST_SC_OFF] = (uint8_t)s;
+      list[start + ncorner + __popc(b & lt)] = (uint16_t)a;
     }
     ncorner += __popc(b);
   }
@@ -145,11 +149,10 @@ __device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const u
                                          const uint16_t* __restrict__ list, int n, int lane, unsigned long long* __restrict__ pl, int prow,
                                          int ini_th) {
   for (int i = lane; i < n; i += 32) {
-    const int e = list[i];
-    const int y = e >> 9, x = e & 511;
-    const uint8_t* q = sc + (y + 1) * FAST_SP + x;
+    const unsigned a = list[i];                      // window offset (y + 3) * 256 + 16 + x
+    const uint8_t* q = sc + a - FAST_SC_OFF;
     const int s = q[0];
-    const unsigned ct = coltab[x + 16];
+    const unsigned ct = coltab[a & (FAST_WP - 1)];
     const int cl = ct & 7;
     if (SECOND ? (hasini[cl] != 0) : (s < ini_th)) continue;
     int m = max((int)q[-FAST_SP], (int)q[FAST_SP]);
@@ -157,6 +160,7 @@ __device__ __forceinline__ void fast_nms(const uint8_t* __restrict__ sc, const u
     if (!(ct & 16u)) m = max(m, __vimax3_s32((int)q[1], (int)q[-FAST_SP + 1], (int)q[FAST_SP + 1]));
     if (s > m) {
       const unsigned r = ct >> 5;
+      const int y = (int)(a >> 8) - 3;
       atomicOr(reinterpret_cast<unsigned*>(pl + cl * prow + y) + (r >> 5), 1u << (r & 31));
       if (!SECOND) hasini[cl] = 1;
     }
@@ -174,16 +178,18 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   uint8_t* sc = win + win_rows * FAST_WP;                 // [sc_rows][FAST_SP], score of domain row y at row y + 1
   unsigned long long* pl_min = reinterpret_cast<unsigned long long*>(sc + sc_rows * FAST_SP);   // [FAST_MAXC][prow] NMS survivors, S >= minTh
   unsigned long long* pl_ini = pl_min + FAST_MAXC * prow;                                        //                                S >= iniTh
-  uint16_t* lists = reinterpret_cast<uint16_t*>(pl_ini + FAST_MAXC * prow);   // [max_h][row_cap], a warp's rows are contiguous
-  uint16_t* coltab = lists + (sc_rows - 2) * row_cap;     // [256] per window column: cell:3 | left:1 | right:1 | column in cell:6; 0xffff outside
-  uint8_t* det8 = reinterpret_cast<uint8_t*>(coltab + FAST_WP);   // [32] per 8-pixel group: detection columns
+  uint16_t* coltab = reinterpret_cast<uint16_t*>(pl_ini + FAST_MAXC * prow);   // [256] per window column: cell:3 | left:1 | right:1 | column in cell:6; 0xffff outside
+  uint8_t* det8 = reinterpret_cast<uint8_t*>(coltab + FAST_WP);   // [32] per 8-pixel group: detection columns (coltab + det8 = the band's host-built table)
   uint8_t* need8 = det8 + 32;                             // [32] per 8-pixel group: columns of the cells that retry at minTh
   uint8_t* hasini = need8 + 32;                           // [FAST_MAXC] cell has an NMS survivor with S >= iniTh
   unsigned long long* mbar = reinterpret_cast<unsigned long long*>(hasini + FAST_MAXC);
+  uint16_t* lists = reinterpret_cast<uint16_t*>(mbar + 1);   // [max_h][row_cap] window offsets, a warp's rows are contiguous
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
   const int4 T = __ldg(tiles + blockIdx.x);               // level, cell row, first cell, cells
-  const int level = T.x, ci = T.y, j0 = T.z, j1 = T.z + T.w;
+  const int level = T.x, ci = T.y, j0 = T.z, j1 = T.z + (T.w & 255);
+  // the column tables depend on (level, first cell) only: built once per shape on the host, stored behind the band table
+  const uint8_t* tab = reinterpret_cast<const uint8_t*>(tiles + g.fast_tiles_total) + (size_t)(T.w >> 8) * FAST_TAB_BYTES;
   const OrbLevel& L = g.lv[level];
   const int wCell = L.wCell;
   const long long cell0 = (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
@@ -206,9 +212,10 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       if (orb_smem_u32(win) & 127u) atomicOr(err_flag, 16);   // TMA destination alignment
       orb_mbar_init(bar, 1);
       // the box is the level's full window height (hCell + 6 rows x 256 bytes); rows / bytes outside the plane arrive as zeros
-      orb_mbar_expect_tx(bar, (unsigned)((L.hCell + 6) * FAST_WP));
+      orb_mbar_expect_tx(bar, (unsigned)((L.hCell + 6) * FAST_WP + FAST_TAB_BYTES));
       // tensor coordinates: byte column of the plane allocation (16-byte lead + level column xa - 16), row incl. the apron rows, frame
       orb_tma_load_3d(orb_smem_u32(win), &maps.m[level], xa, iniY + ORB_APRON_ROWS, frame, bar);
+      orb_bulk_load_1d(orb_smem_u32(coltab), tab, FAST_TAB_BYTES, bar);   // column tables: same barrier, no thread instructions
     }
   } else {
     const int nvec = (X1 - xa + 15) >> 4;
@@ -220,33 +227,20 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(orb_smem_u32(win + y * FAST_WP + 16 + 16 * v)),
                    "l"(src + (long long)y * L.pitch + 16 * v));
     }
+    if (tid < FAST_TAB_BYTES / 16)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(orb_smem_u32(coltab) + 16 * tid), "l"(tab + 16 * tid));
     asm volatile("cp.async.commit_group;");
   }
-  // ... meanwhile: clear the score plane and both survivor planes (contiguous: sc, pl_min, pl_ini), build the column tables
+  // ... meanwhile: clear the score plane and both survivor planes (contiguous: sc, pl_min, pl_ini)
   {
     uint4* z = reinterpret_cast<uint4*>(sc);
     const int nz = (sc_rows * FAST_SP + 2 * FAST_MAXC * prow * 8) >> 4;
     for (int i = tid; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+    if (tid < FAST_MAXC) hasini[tid] = 0;
   }
   const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates (window column 16 + x)
   const int qbase = dx0 & ~7;                            // groups of 8 aligned pixels
   const int nq = (dx1 - qbase + 7) >> 3;                 // <= 29
-  {
-    const int x = tid - 16;                              // this thread's window column
-    const bool det = x >= dx0 && x < dx1;
-    unsigned ct = 0xffffu;
-    if (det) {
-      const unsigned p = (unsigned)(x + xa - ORB_MIN_BORDER - 3);   // detection column of the level
-      const unsigned cell = __umulhi(p, L.inv_wcell);               // p / wCell (inv = 2^32 / wCell + 1)
-      const unsigned r = p - cell * (unsigned)wCell;
-      ct = (cell - (unsigned)j0) | (r == 0u ? 8u : 0u) | ((r == (unsigned)wCell - 1u || x == dx1 - 1) ? 16u : 0u) | (r << 5);
-    }
-    coltab[tid] = (uint16_t)ct;
-    const unsigned b = __ballot_sync(0xffffffffu, det);
-    const int o = 4 * warp + lane - 2 - (qbase >> 3);    // group of window columns 32 * warp + 8 * lane .. + 7
-    if (lane < 4 && o >= 0 && o < 32) det8[o] = (uint8_t)(b >> (8 * lane));
-    if (tid < FAST_MAXC) hasini[tid] = 0;
-  }
   if (!TMA) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   if (TMA) {
@@ -382,17 +376,46 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
 }
 
 // ---- host side ------------------------------------------------------------------------------------------------
-// Band table: one int4 {level, cell row, first cell, cells} per CTA of a frame, levels in ascending order.
+// Band table: one int4 {level, cell row, first cell, cells | table << 8} per CTA of a frame, levels in ascending order, followed by the column
+// tables (FAST_TAB_BYTES each, one per (level, segment)): per window column cell:3 | left edge:1 | right edge:1 | column inside the cell:6
+// (0xffff outside the detection columns), then per 8-pixel group the mask of detection columns.
 void orb_fast_build_tiles(const OrbGeom& g, std::vector<int4>& tiles) {
   tiles.clear();
+  std::vector<uint8_t> tabs;
+  int ntab = 0;
   for (int l = 0; l < g.nlevels; ++l) {
     const OrbLevel& L = g.lv[l];
+    for (int sg = 0; sg < L.fast_nseg; ++sg) {
+      const int j0 = sg * L.fast_G, j1 = std::min(j0 + L.fast_G, L.nCols);
+      tabs.resize((size_t)(ntab + sg + 1) * FAST_TAB_BYTES);
+      uint16_t* coltab = reinterpret_cast<uint16_t*>(tabs.data() + (size_t)(ntab + sg) * FAST_TAB_BYTES);
+      uint8_t* det8 = reinterpret_cast<uint8_t*>(coltab + FAST_WP);
+      const int X0 = ORB_MIN_BORDER + j0 * L.wCell, X1 = std::min(ORB_MIN_BORDER + j1 * L.wCell + 6, L.maxBX);
+      const int xa = X0 & ~15, dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa, qbase = dx0 & ~7;
+      memset(det8, 0, 32);
+      for (int t = 0; t < FAST_WP; ++t) {
+        const int x = t - 16;
+        unsigned ct = 0xffffu;
+        if (x >= dx0 && x < dx1) {
+          const int p = x + xa - ORB_MIN_BORDER - 3;   // detection column of the level
+          const int cell = p / L.wCell, r = p - cell * L.wCell;
+          ct = (unsigned)(cell - j0) | (r == 0 ? 8u : 0u) | ((r == L.wCell - 1 || x == dx1 - 1) ? 16u : 0u) | ((unsigned)r << 5);
+          const int o = (x - qbase) >> 3;
+          if (o >= 0 && o < 32) det8[o] |= (uint8_t)(1u << ((x - qbase) & 7));
+        }
+        coltab[t] = (uint16_t)ct;
+      }
+    }
     for (int ci = 0; ci < L.nRows; ++ci)
       for (int sg = 0; sg < L.fast_nseg; ++sg) {
         const int j0 = sg * L.fast_G, j1 = std::min(j0 + L.fast_G, L.nCols);
-        tiles.push_back(make_int4(l, ci, j0, std::max(j1 - j0, 0)));
+        tiles.push_back(make_int4(l, ci, j0, std::max(j1 - j0, 0) | ((ntab + sg) << 8)));
       }
+    ntab += L.fast_nseg;
   }
+  const size_t nt = tiles.size();
+  tiles.resize(nt + (tabs.size() + 15) / 16);
+  if (!tabs.empty()) memcpy(reinterpret_cast<uint8_t*>(tiles.data() + nt), tabs.data(), tabs.size());
 }
 
 void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, int* cell_cnt, uint32_t* cell_kp, int* err_flag, const OrbGeom& g,
@@ -409,7 +432,7 @@ void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, in
   row_cap = std::min(row_cap, 256);
   const int prow = (sc_rows - 1) & ~1;
   const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)FAST_MAXC * prow * 8 + (size_t)max_h * row_cap * 2 +
-                      FAST_WP * 2 + 32 + 32 + FAST_MAXC + 8;   // KITTI: 37.5 KB
+                      FAST_TAB_BYTES + 32 + FAST_MAXC + 8;   // KITTI: 38 KB
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
   // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
   typedef void (*Kern)(const uint8_t*, const int4*, int*, uint32_t*, int*, int, int, int, const OrbGeom, const OrbLevelMaps);

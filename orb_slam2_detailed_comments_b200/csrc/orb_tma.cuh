@@ -46,4 +46,9 @@ __device__ __forceinline__ void orb_tma_load_3d(unsigned dst, const CUtensorMap*
                "l"(reinterpret_cast<unsigned long long>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
                : "memory");
 }
+// plain bulk copy global -> shared (both 16-byte aligned, bytes % 16 == 0), completion counted on the same kind of mbarrier
+__device__ __forceinline__ void orb_bulk_load_1d(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
 #endif
