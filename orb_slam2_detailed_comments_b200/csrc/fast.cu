@@ -176,8 +176,10 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   const int prow = (sc_rows - 1) & ~1;                    // survivor rows per cell, even (sc_rows - 2 rounded up)
   uint8_t* win = smem;                                    // [win_rows][FAST_WP], pixel x at column 16 + x
   uint8_t* sc = win + win_rows * FAST_WP;                 // [sc_rows][FAST_SP], score of domain row y at row y + 1
-  unsigned long long* pl_min = reinterpret_cast<unsigned long long*>(sc + sc_rows * FAST_SP);   // [FAST_MAXC][prow] NMS survivors, S >= minTh
-  unsigned long long* pl_ini = pl_min + FAST_MAXC * prow;                                        //                                S >= iniTh
+  // [FAST_MAXC][prow] NMS survivors, one 64-bit row per cell row. ONE plane serves both thresholds: a cell that retries at minTh has no
+  // iniTh survivor, i.e. its rows are still all zero when step 5 writes them
+  unsigned long long* pl_ini = reinterpret_cast<unsigned long long*>(sc + sc_rows * FAST_SP);
+  unsigned long long* pl_min = pl_ini;
   uint16_t* coltab = reinterpret_cast<uint16_t*>(pl_ini + FAST_MAXC * prow);   // [256] per window column: cell:3 | left:1 | right:1 | column in cell:6; 0xffff outside
   uint8_t* det8 = reinterpret_cast<uint8_t*>(coltab + FAST_WP);   // [32] per 8-pixel group: detection columns (coltab + det8 = the band's host-built table)
   uint8_t* need8 = det8 + 32;                             // [32] per 8-pixel group: columns of the cells that retry at minTh
@@ -231,10 +233,10 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(orb_smem_u32(coltab) + 16 * tid), "l"(tab + 16 * tid));
     asm volatile("cp.async.commit_group;");
   }
-  // ... meanwhile: clear the score plane and both survivor planes (contiguous: sc, pl_min, pl_ini)
+  // ... meanwhile: clear the score plane and the survivor plane (contiguous)
   {
     uint4* z = reinterpret_cast<uint4*>(sc);
-    const int nz = (sc_rows * FAST_SP + 2 * FAST_MAXC * prow * 8) >> 4;
+    const int nz = (sc_rows * FAST_SP + FAST_MAXC * prow * 8) >> 4;
     for (int i = tid; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     if (tid < FAST_MAXC) hasini[tid] = 0;
   }
@@ -256,7 +258,9 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   {
     const unsigned ti = SMALL_TH ? ((unsigned)g.ini_th + 1u) * 0x01010101u : (unsigned)g.ini_th * 0x01010101u;
     const unsigned tm = SMALL_TH ? ((unsigned)g.min_th + 1u) * 0x01010101u : (unsigned)g.min_th * 0x01010101u;
-    for (int ri = 0; warp + FAST_WARPS * ri < dh; ++ri) {
+#pragma unroll
+    for (int ri = 0; ri < 8; ++ri) {   // unrolled: ri, the lane rotation, the mask word and its shift are compile-time constants
+      if (warp + FAST_WARPS * ri >= dh) break;
       const int y = warp + FAST_WARPS * ri;
       const int o = (lane + 5 * ri) & 31;
       if (o < nq) {
@@ -339,7 +343,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       if (lane == 0) cnt_row[cj] = 0;
       continue;
     }
-    const unsigned long long* pc = (hasini[cl] ? pl_ini : pl_min) + cl * prow;
+    const unsigned long long* pc = pl_ini + cl * prow;
     ulonglong2 mm = make_ulonglong2(0ull, 0ull);
     if (2 * lane < prow) mm = *reinterpret_cast<const ulonglong2*>(pc + 2 * lane);
     const int c0 = __popcll(mm.x), c1 = __popcll(mm.y);
@@ -431,7 +435,7 @@ void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, in
   }
   row_cap = std::min(row_cap, 256);
   const int prow = (sc_rows - 1) & ~1;
-  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + 2 * (size_t)FAST_MAXC * prow * 8 + (size_t)max_h * row_cap * 2 +
+  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + (size_t)FAST_MAXC * prow * 8 + (size_t)max_h * row_cap * 2 +
                       FAST_TAB_BYTES + 32 + FAST_MAXC + 8;   // KITTI: 38 KB
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
   // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
