@@ -138,10 +138,12 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __r
 // Orientation (un-blurred level), descriptor (blurred level) and the final cv::KeyPoint (pt *= scale for level != 0).
 // One warp handles DESC_KPW keypoints of one frame back to back, so the per-lane tables stay in registers; lane i < DESC_KPW owns keypoint i
 // of the warp's batch (level lookup and the packed record are fetched once, up front; it writes that keypoint's 28-byte cv::KeyPoint at the end).
-//   * staging, TMA == false (default): the 31 x 36-byte IC_Angle window (un-blurred) and the 37 x 40-byte descriptor patch (blurred) are
-//     fetched with coalesced 4-byte cp.async copies (global -> shared without a register round trip), both windows issued up front as two
-//     groups: the orientation starts when the first has landed.
-//   * staging, TMA == true (ORB_B200_DESC_TMA=1, kept as the measured alternative): ONE lane issues two TMA box loads per keypoint
+//   * staging, MODE 2 (default): the IC_Angle window (un-blurred, 31 rows) and the descriptor patch (blurred, 37 rows) are fetched with 16-byte
+//     cp.async copies (global -> shared without a register round trip) from the 16-byte boundary below the window into 48- / 64-byte rows:
+//     3 + 5 copy instructions per lane and keypoint. Both windows are issued up front as two groups: the orientation starts when the first
+//     has landed. MODE 0 (ORB_B200_DESC_NARROW=1, rounds 1-2): 4-byte copies into tight 36- / 40-byte rows, 11 + 13 instructions per lane -
+//     a quarter of the kernel's instructions; the wide copies gave +6.6 % on the whole step (109.1 k -> 116.3 k images/s, same box).
+//   * staging, MODE 1 (ORB_B200_DESC_TMA=1, kept as the measured alternative): ONE lane issues two TMA box loads per keypoint
 //     (cp.async.bulk.tensor.3d, per-level tensor maps), 31 x 48 bytes and 37 x 64 bytes: the innermost box coordinate has to be 16-byte
 //     aligned (anything else raises an illegal-instruction fault, tests/cuda/tma_probe.cu), so a box starts at the 16-byte boundary below
 //     the window. 22 % fewer instructions, but 2 x 136 k boxes of ~34 short rows per pass saturate the TMA unit: 1.71 ms against 0.96 ms
@@ -151,21 +153,26 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __r
 //   * rBRIEF: lane = descriptor byte; its 8 test pairs (x0, y0, x1, y1 as floats) come from shared memory, one LDS.128 each. cvRound is
 //     the float add of 1.5 * 2^23 (round-half-even happens in the FADD; F2I would go through the quarter-rate conversion pipe); the
 //     integer bias of both coordinates is folded into the 32-bit shared-memory base address of the patch.
-template <bool TMA> struct DescLayout;
+template <bool WIDE> struct DescLayout;
 template <> struct DescLayout<false> { enum { IC_PITCH = 36, PT_PITCH = 40, IC_BYTES = 31 * 36 + 4, PT_BYTES = 37 * 40 + 8 }; };
 template <> struct DescLayout<true> { enum { IC_PITCH = 48, PT_PITCH = 64, IC_BYTES = 1536, PT_BYTES = 2432 }; };   // rounded to the 128-byte TMA alignment
 
 __device__ __forceinline__ void cp_async4(unsigned smem, const void* gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem), "l"(gmem));
 }
+__device__ __forceinline__ void cp_async16(unsigned smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem), "l"(gmem));
+}
 
-template <bool TMA>
+// MODE 0: 4-byte cp.async into tight rows; 1: TMA boxes; 2: 16-byte cp.async into the 16-byte-aligned rows of the TMA layout
+template <int MODE>
 __global__ void __launch_bounds__(DESC_WARPS * 32, 40 / DESC_WARPS)
 orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr, const uint32_t* __restrict__ kept,
                     const int* __restrict__ kept_cnt, OrbKeypoint* __restrict__ kps, uint8_t* __restrict__ desc, int cap,
                     int* __restrict__ counts, int* __restrict__ err_flag, const __grid_constant__ OrbGeom g,
                     const __grid_constant__ OrbLevelMaps ic_maps, const __grid_constant__ OrbLevelMaps pt_maps) {
-  typedef DescLayout<TMA> Lay;
+  constexpr bool TMA = MODE == 1, WIDE = MODE != 0;
+  typedef DescLayout<WIDE> Lay;
   __shared__ __align__(128) uint8_t s_win[DESC_WARPS][Lay::IC_BYTES + Lay::PT_BYTES];
   __shared__ float4 s_pat[8 * 32];   // rBRIEF pattern as floats, [test bit][lane]: one conflict-free LDS.128 per test (256 test pairs)
   __shared__ __align__(8) unsigned long long s_bar[DESC_WARPS][2];
@@ -249,6 +256,28 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
       s_ic = (unsigned)(x - 16) & 15u;
       s_pt = (unsigned)(x - 18) & 15u;
       failed |= orb_mbar_wait(bar_ic, parity) ^ 1u;
+    } else if (MODE == 2) {
+      // 31 x 3 and 37 x 4 sixteen-byte chunks: lane + 32 k -> (row, chunk); 8 copy instructions per lane instead of 24
+      const OrbLevel& L = g.lv[level];
+      const int pitch = L.pitch;
+      const unsigned long long off = (unsigned long long)frame * g.frame_stride + L.plane_off;
+      const uint8_t* icb = pyr + off + (long long)(y - 15) * pitch + ((x - 16) & ~15);
+      const uint8_t* ptb = blr + off + (long long)(y - 18) * pitch + ((x - 18) & ~15) + (lane >> 2) * pitch + 16 * (lane & 3);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int idx = lane + 32 * k, row = idx / 3, ch = idx - 3 * row;
+        if (idx < 93) cp_async16(ic_s + (unsigned)(row * Lay::IC_PITCH + 16 * ch), icb + row * pitch + 16 * ch);
+      }
+      asm volatile("cp.async.commit_group;");
+      const unsigned pt_d = pt_s + (unsigned)((lane >> 2) * Lay::PT_PITCH + 16 * (lane & 3));
+#pragma unroll
+      for (int k = 0; k < 5; ++k)
+        if (k < 4 || lane < 20) cp_async16(pt_d + (unsigned)(8 * k * Lay::PT_PITCH), ptb + 8 * k * pitch);
+      asm volatile("cp.async.commit_group;");
+      s_ic = (unsigned)(x - 16) & 15u;
+      s_pt = (unsigned)(x - 18) & 15u;
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      __syncwarp();
     } else {
       const OrbLevel& L = g.lv[level];
       const int pitch = L.pitch;
@@ -274,7 +303,7 @@ orb_describe_kernel(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__
     int m10 = 0, rs = 0;
     if (lane < 31) {
       unsigned w[12];
-      if (TMA) {
+      if (WIDE) {
         const uint4* rowp = reinterpret_cast<const uint4*>(ic + lane * Lay::IC_PITCH);
         const uint4 q0 = rowp[0], q1 = rowp[1], q2 = rowp[2];
         w[0] = q0.x; w[1] = q0.y; w[2] = q0.z; w[3] = q0.w; w[4] = q1.x; w[5] = q1.y; w[6] = q1.z; w[7] = q1.w;
@@ -378,10 +407,13 @@ void orb_launch_describe(const uint8_t* pyr, const uint8_t* blr, const void* ic_
   ++*launches;
   const int per_cta = DESC_WARPS * DESC_KPW;
   const dim3 grid((cap + per_cta - 1) / per_cta, batch);
+  static const bool want_wide = getenv("ORB_B200_DESC_NARROW") == nullptr;   // default; ORB_B200_DESC_NARROW=1: the 4-byte copies of rounds 1-2 (A/B)
   if (want_tma && ic_maps && pt_maps)
-    orb_describe_kernel<true><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g,
-                                                                *reinterpret_cast<const OrbLevelMaps*>(ic_maps),
-                                                                *reinterpret_cast<const OrbLevelMaps*>(pt_maps));
+    orb_describe_kernel<1><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g,
+                                                             *reinterpret_cast<const OrbLevelMaps*>(ic_maps),
+                                                             *reinterpret_cast<const OrbLevelMaps*>(pt_maps));
+  else if (want_wide)
+    orb_describe_kernel<2><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g, no_maps, no_maps);
   else
-    orb_describe_kernel<false><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g, no_maps, no_maps);
+    orb_describe_kernel<0><<<grid, DESC_WARPS * 32, 0, st>>>(pyr, blr, kept, kept_cnt, kps, desc, cap, counts, err_flag, g, no_maps, no_maps);
 }
