@@ -18,6 +18,100 @@
 #define BL_THREADS 320
 #define BL_RAW_W 160      // TMA box: columns x0 - 16 .. x0 + 143 (16-byte aligned start; the taps need x0 - 4 .. x0 + 131)
 #define BL_RAW_H 40       // rows y0 - 4 .. y0 + 35 (row y0 - 4 and rows past y0 + 34 only ever meet a zero tap)
+// V pass shared by both blur kernels: one thread = 4 pixels x 4 output rows from 6 staged row pairs.
+template <bool CLAMP>
+__device__ __forceinline__ void blur_v_pass(const uint4 (*s_p)[BL_TW / 4], uint8_t* __restrict__ out, const OrbLevel& L, int x0, int y0,
+                                            const OrbGeom& g) {
+  if (threadIdx.x >= 256) return;
+  const int q = threadIdx.x & 31, seg = threadIdx.x >> 5;   // output rows y0 + 4*seg .. + 3 = local rows 4*seg + 4 .. + 7
+  const int x = x0 + 4 * q;
+  if (x >= L.cols) return;
+  const int pitch = L.pitch;
+  uint4 P[6];                                                // pairs 2*seg .. 2*seg + 5 = local rows 4*seg .. 4*seg + 11
+#pragma unroll
+  for (int i = 0; i < 6; ++i) P[i] = s_p[2 * seg + i][q];
+  // even local row t = 2m: [0,k0].P(m-2) + [k1,k2].P(m-1) + [k3,k2].P(m) + [k1,k0].P(m+1)
+  // odd  local row t = 2m+1: [k0,k1].P(m-1) + [k2,k3].P(m) + [k2,k1].P(m+1) + [k0,0].P(m+2)
+  const unsigned e0 = g.blur_k[2], e1 = g.blur_k[3], e2 = g.blur_k[4], e3 = g.blur_k[5];
+  const unsigned o0 = g.blur_k[6], o1 = g.blur_k[7], o2 = g.blur_k[8], o3 = g.blur_k[9];
+  uint8_t* dst = out + (unsigned)((y0 + 4 * seg) * pitch + x);   // 32-bit offset inside the frame's plane
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int y = y0 + 4 * seg + r;
+    if (y < L.rows) {
+      const int m = 2 + (r >> 1);                           // pair index (relative to P[0]) holding local row t
+      unsigned c[4];
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+#define PW(i) (p == 0 ? P[i].x : p == 1 ? P[i].y : p == 2 ? P[i].z : P[i].w)
+        if ((r & 1) == 0)
+          c[p] = __dp2a_lo(PW(m - 2), e0, __dp2a_lo(PW(m - 1), e1, __dp2a_lo(PW(m), e2, __dp2a_lo(PW(m + 1), e3, 32768u))));
+        else
+          c[p] = __dp2a_lo(PW(m - 1), o0, __dp2a_lo(PW(m), o1, __dp2a_lo(PW(m + 1), o2, __dp2a_lo(PW(m + 2), o3, 32768u))));
+#undef PW
+        if (CLAMP) c[p] = min(c[p], 0xffffffu);
+      }
+      // byte 2 of each accumulator is the output pixel
+      const unsigned lo = __byte_perm(c[0], c[1], 0x0062), hi = __byte_perm(c[2], c[3], 0x0062);
+      *reinterpret_cast<unsigned*>(dst + r * pitch) = __byte_perm(lo, hi, 0x5410);
+    }
+  }
+}
+
+// Default blur kernel. Same tile, same shared layout and V pass as orb_blur_kernel below; the H pass is ONE round of 320 items:
+//   one thread = 8 adjacent pixels of two adjacent rows: one aligned 64-bit load per row plus the 32-bit words left and right of it, i.e.
+//   6 loads per 16 pixel-rows instead of 12, and one tile / row / address computation per 16 pixel-rows instead of per 8.
+template <bool CLAMP>
+__global__ void __launch_bounds__(BL_THREADS) orb_blur8_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
+                                                               const __grid_constant__ OrbGeom g) {
+  __shared__ uint4 s_p[(BL_TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
+  const int level = orb_level_of(g.blur_base, (int)blockIdx.x);
+  const OrbLevel& L = g.lv[level];
+  const unsigned t = blockIdx.x - L.blur_tile_base;
+  const unsigned ty_ = (t * L.blur_inv_tx) >> 20;            // t / blur_tiles_x (host-checked range)
+  const int x0 = (int)(t - ty_ * L.blur_tiles_x) * BL_TW, y0 = (int)ty_ * BL_TH;
+  const unsigned long long off = (unsigned long long)blockIdx.y * g.frame_stride + L.plane_off;
+  const unsigned tapA = g.blur_k[0], tapB = g.blur_k[1];
+  {
+    const int k = threadIdx.x >> 4, q = threadIdx.x & 15;    // row pair 0..19 (local rows 2k, 2k+1 <-> plane rows y0 - 4 + ..), 8-pixel group
+    const int pitch = L.pitch;
+    const uint8_t* src = pyr + off;                          // uniform; the per-thread part is a 32-bit offset
+    const int x = x0 + 8 * q;
+    // words past the level's apron are never used by a stored pixel: clamp the column so that every load stays inside the row
+    const int xl = min(x, (L.cols + 4) & ~7);
+    const int ry0 = min(y0 - 4 + 2 * k, L.rows + 3), ry1 = min(y0 - 3 + 2 * k, L.rows + 3);
+    const int o0 = ry0 * pitch + xl, o1 = ry1 * pitch + xl;   // ry0 = -4 for the first tile row: the plane's apron rows
+    const uint2 w0 = __ldg(reinterpret_cast<const uint2*>(src + o0));
+    const uint2 w1 = __ldg(reinterpret_cast<const uint2*>(src + o1));
+    // the words left and right of them: loaded as well (independent loads, all six in flight; fetching them from the neighbouring lanes by
+    // shuffle measured 1.3 % slower on the whole step: the shuffle can only issue once the load has landed)
+    const unsigned l0 = __ldg(reinterpret_cast<const unsigned*>(src + o0) - 1), l1 = __ldg(reinterpret_cast<const unsigned*>(src + o1) - 1);
+    const unsigned r0 = __ldg(reinterpret_cast<const unsigned*>(src + o0) + 2), r1 = __ldg(reinterpret_cast<const unsigned*>(src + o1) + 2);
+    if (x < L.cols) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        unsigned h[2][4];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const uint2 w = rr ? w1 : w0;
+          const unsigned c0 = half ? w.x : (rr ? l1 : l0), c1 = half ? w.y : w.x, c2 = half ? (rr ? r1 : r0) : w.y;
+          // W(a) = bytes B[a..a+3] of the 12 bytes B[0..11] = pixels x-4 .. x+7 of this half; pixel j: W(j+1).tapA + W(j+5).tapB
+          const unsigned w1_ = __byte_perm(c0, c1, 0x4321), w2_ = __byte_perm(c0, c1, 0x5432), w3_ = __byte_perm(c0, c1, 0x6543),
+                         w5_ = __byte_perm(c1, c2, 0x4321), w6_ = __byte_perm(c1, c2, 0x5432), w7_ = __byte_perm(c1, c2, 0x6543);
+          h[rr][0] = __dp4a(w1_, tapA, __dp4a(w5_, tapB, 0u));
+          h[rr][1] = __dp4a(w2_, tapA, __dp4a(w6_, tapB, 0u));
+          h[rr][2] = __dp4a(w3_, tapA, __dp4a(w7_, tapB, 0u));
+          h[rr][3] = __dp4a(c1, tapA, __dp4a(c2, tapB, 0u));
+        }
+        s_p[k][2 * q + half] = make_uint4(__byte_perm(h[0][0], h[1][0], 0x5410), __byte_perm(h[0][1], h[1][1], 0x5410),
+                                          __byte_perm(h[0][2], h[1][2], 0x5410), __byte_perm(h[0][3], h[1][3], 0x5410));
+      }
+    }
+  }
+  __syncthreads();
+  blur_v_pass<CLAMP>(s_p, blr + off, L, x0, y0, g);
+}
+
 // TMA == true (ORB_B200_BLUR_TMA=1; measured alternative, 7 % slower: the CTA idles for the box's latency, 41 % of the stall samples on the
 // mbarrier wait, while the instruction count only drops from 89.1 M to 87.6 M per pass): ONE thread fetches the tile's 160 x 40-byte source window with a cp.async.bulk.tensor box (per-level tensor map of the
 // un-blurred planes; bytes outside the plane allocation arrive as zeros and only feed outputs that are not written) and the H pass reads it
@@ -100,39 +194,7 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur_kernel(const uint8_t* __r
     }
   }
   __syncthreads();
-  if (threadIdx.x >= 256) return;
-  const int q = threadIdx.x & 31, seg = threadIdx.x >> 5;   // output rows y0 + 4*seg .. + 3 = local rows 4*seg + 4 .. + 7
-  const int x = x0 + 4 * q;
-  if (x >= L.cols) return;
-  uint4 P[6];                                                // pairs 2*seg .. 2*seg + 5 = local rows 4*seg .. 4*seg + 11
-#pragma unroll
-  for (int i = 0; i < 6; ++i) P[i] = s_p[2 * seg + i][q];
-  // even local row t = 2m: [0,k0].P(m-2) + [k1,k2].P(m-1) + [k3,k2].P(m) + [k1,k0].P(m+1)
-  // odd  local row t = 2m+1: [k0,k1].P(m-1) + [k2,k3].P(m) + [k2,k1].P(m+1) + [k0,0].P(m+2)
-  const unsigned e0 = g.blur_k[2], e1 = g.blur_k[3], e2 = g.blur_k[4], e3 = g.blur_k[5];
-  const unsigned o0 = g.blur_k[6], o1 = g.blur_k[7], o2 = g.blur_k[8], o3 = g.blur_k[9];
-  uint8_t* dst = blr + off + (long long)(y0 + 4 * seg) * pitch + x;
-#pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int y = y0 + 4 * seg + r;
-    if (y < L.rows) {
-      const int m = 2 + (r >> 1);                           // pair index (relative to P[0]) holding local row t
-      unsigned c[4];
-#pragma unroll
-      for (int p = 0; p < 4; ++p) {
-#define PW(i) (p == 0 ? P[i].x : p == 1 ? P[i].y : p == 2 ? P[i].z : P[i].w)
-        if ((r & 1) == 0)
-          c[p] = __dp2a_lo(PW(m - 2), e0, __dp2a_lo(PW(m - 1), e1, __dp2a_lo(PW(m), e2, __dp2a_lo(PW(m + 1), e3, 32768u))));
-        else
-          c[p] = __dp2a_lo(PW(m - 1), o0, __dp2a_lo(PW(m), o1, __dp2a_lo(PW(m + 1), o2, __dp2a_lo(PW(m + 2), o3, 32768u))));
-#undef PW
-        if (CLAMP) c[p] = min(c[p], 0xffffffu);
-      }
-      // byte 2 of each accumulator is the output pixel
-      const unsigned lo = __byte_perm(c[0], c[1], 0x0062), hi = __byte_perm(c[2], c[3], 0x0062);
-      *reinterpret_cast<unsigned*>(dst + r * pitch) = __byte_perm(lo, hi, 0x5410);
-    }
-  }
+  blur_v_pass<CLAMP>(s_p, blr + off, L, x0, y0, g);
 }
 
 // Orientation (un-blurred level), descriptor (blurred level) and the final cv::KeyPoint (pt *= scale for level != 0).
@@ -387,7 +449,11 @@ void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const void* maps, const O
   const dim3 grid(g.blur_tiles_total, batch);
   const bool tma = maps != nullptr && want_tma;
   const OrbLevelMaps& M = tma ? *reinterpret_cast<const OrbLevelMaps*>(maps) : no_maps;
-  if (sum > 256) {
+  static const bool v1 = getenv("ORB_B200_BLUR_V1") != nullptr;   // the 4-pixel H pass of rounds 1-2 (A/B)
+  if (!tma && !v1) {
+    if (sum > 256) orb_blur8_kernel<true><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+    else orb_blur8_kernel<false><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+  } else if (sum > 256) {
     if (tma) orb_blur_kernel<true, true><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
     else orb_blur_kernel<true, false><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
   } else {
