@@ -35,6 +35,7 @@ struct orb_extractor {
     cudaEvent_t ev_join = nullptr;
     cudaStream_t st_side = nullptr;                       // high-priority side stream of the pass: quadtree (latency-bound) beside blur
     cudaEvent_t ev_fast = nullptr, ev_side = nullptr, ev_pyr = nullptr;   // ev_pyr: the pyramid of the pass is complete
+    cudaEvent_t ev_pfork = nullptr, ev_pjoin = nullptr;                   // pyramid on the side stream (ORB_B200_PYR_SIDE)
     int frames = 0;          // frames of the last pass run here
     // per-level TMA descriptors of `pyr` / `blr`: FAST band windows (256 B x hCell + 6), IC_Angle windows (48 B x 31), descriptor patches (64 B x 37)
     alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES],
@@ -48,7 +49,7 @@ struct orb_extractor {
     DevBuf* all[25] = {&st_rows, &st_sorted, &st_sad, &pyr, &blr, &cell_cnt, &cell_kp, &kept, &kept_cnt, &out_cnt, &q_key, &q_knode, &q_kchild, &q_bbox, &q_ncount,
                        &q_pidx, &q_best, &q_ordA, &q_ordB, &q_par, &q_cand, &q_ccnt, &q_cslot, &q_scan, &q_rawn};
   } ws[ORB_MAX_WS];
-  int nws = 2;             // compute streams / workspaces in use (ORB_B200_STREAMS, 1..ORB_MAX_WS)
+  int nws = 4;             // compute streams / workspaces in use (ORB_B200_STREAMS, 1..ORB_MAX_WS)
   int side = 2;            // ORB_B200_SIDE: 0 = off, 1 = quadtree, 2 (default) = quadtree + descriptors on the pass's high-priority side stream
   int last_ws = 0;         // workspace of the most recent pass (mvImagePyramid / test hooks read it)
   cudaEvent_t ev_fork = nullptr;
@@ -249,16 +250,18 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
 
 // ---- workspace -------------------------------------------------------------------------------------------
 static int default_chunk(const OrbGeom& g) {
-  // Frames per internal pass. Every stage is issue/latency bound rather than DRAM bound (profiles/), so L2 residency of a
-  // pass buys nothing and large passes win: they fill the 148 SMs for the small pyramid levels and the one-CTA-per-
-  // (frame, level) quadtree. Bounded by ~1.5 GB of workspace per pass (two workspaces exist) and 64 frames, which keeps
-  // >= 8 passes in a 512-frame call for the copy/compute pipeline of orb_extract_batch.
+  // Frames per internal pass. Every stage is issue/latency bound rather than DRAM bound (profiles/), so L2 residency of a pass buys nothing;
+  // what counts is that a pass fills the 148 SMs for the small pyramid levels and the one-CTA-per-(frame, level) quadtree, and that several
+  // passes are in flight so that the chains of small launches hide behind the other passes' large kernels. With the pyramid on the
+  // high-priority stream, four workspaces of 32-frame passes are the best point on every shape (profiles/r2_stream_sweep.md: KITTI 95.4 k
+  // against 92.1 k images/s host to host with two 64-frame passes, TUM 152.0 k against 146.7 k, EuRoC 123.9 k against 118.8 k), bounded by
+  // ~0.75 GB of workspace per pass (4K: 7 frames).
   const char* env = getenv("ORB_B200_CHUNK");
   if (env && atoi(env) > 0) return atoi(env);
   const double per_frame = 2.0 * (double)g.frame_stride + (double)g.ncells_total * (ORB_CELL_CAP + 1) * 4 +
                            (double)g.raw_total * 9 + (double)g.node_total * 100;
-  int c = (int)(1.5e9 / per_frame);
-  return std::max(1, std::min(c, 64));
+  int c = (int)(0.75e9 / per_frame);
+  return std::max(1, std::min(c, 32));
 }
 
 static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
@@ -359,8 +362,15 @@ static void run_pass(orb_extractor* e, int w, const uint8_t* images, int step, l
     if (prof) { ev = e->ev.data() + e->ev_used; e->ev_used += ORB_NUM_STAGES + 1; }
   }
   if (prof) cudaEventRecord(ev[0], st);
+  // The pyramid's chain of small dependent launches runs on the pass's high-priority side stream: its CTAs are dispatched ahead of the queued
+  // FAST / blur CTAs of the other pass instead of waiting for that grid to drain, the chain's latency hides behind them, and the input staging
+  // buffer is released earlier for the next copy (118.3 k vs 116.7 k images/s resident, 91.9 k vs 88.5 k host to host; ORB_B200_PYR_MAIN=1 = before)
+  static const bool pyr_side = getenv("ORB_B200_PYR_MAIN") == nullptr;
+  const bool ps = pyr_side && !prof && e->side >= 1;
+  if (ps) { cudaEventRecord(P.ev_pfork, st); cudaStreamWaitEvent(P.st_side, P.ev_pfork, 0); }
   orb_launch_pyramid(images, step, image_stride, P.pyr.as<uint8_t>(), e->tabs.as<ResizeTab>(), e->rs_tiles.as<int>(), P.maps_ok ? P.rs_maps : nullptr,
-                     e->num_sms, g, n, st, &e->launches, ev_input_consumed);
+                     e->num_sms, g, n, ps ? P.st_side : st, &e->launches, ev_input_consumed);
+  if (ps) { cudaEventRecord(P.ev_pjoin, P.st_side); cudaStreamWaitEvent(st, P.ev_pjoin, 0); }
   if (mark_pyramid) cudaEventRecord(P.ev_pyr, st);
   if (prof) cudaEventRecord(ev[1], st);
   static const bool fast_v1 = getenv("ORB_B200_FAST_V1") != nullptr;   // round-1 kernel, same-box A/B only
@@ -462,6 +472,8 @@ int orb_extractor_create(const orb_params* p, int device, orb_extractor** out) {
       if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_fast, cudaEventDisableTiming);
       if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_side, cudaEventDisableTiming);
       if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_pyr, cudaEventDisableTiming);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_pfork, cudaEventDisableTiming);
+      if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ws[w].ev_pjoin, cudaEventDisableTiming);
     }
   }
   if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming);
@@ -480,6 +492,8 @@ void orb_extractor_destroy(orb_extractor* e) {
     if (e->ws[w].ev_fast) cudaEventDestroy(e->ws[w].ev_fast);
     if (e->ws[w].ev_side) cudaEventDestroy(e->ws[w].ev_side);
     if (e->ws[w].ev_pyr) cudaEventDestroy(e->ws[w].ev_pyr);
+    if (e->ws[w].ev_pfork) cudaEventDestroy(e->ws[w].ev_pfork);
+    if (e->ws[w].ev_pjoin) cudaEventDestroy(e->ws[w].ev_pjoin);
   }
   for (int w = 1; w < ORB_MAX_WS; ++w) {
     if (e->ws[w].st) { cudaStreamSynchronize(e->ws[w].st); cudaStreamDestroy(e->ws[w].st); }
