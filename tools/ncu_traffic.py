@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """profiles/ncu_traffic.json from an `ncu --set full` report of `bench.py --steps 1 --warmup 1 --batch 64 --no-cpu`:
 per-stage DRAM bytes and warp instructions of one pass (one launch of each stage kernel; the pyramid launches summed).
-usage: tools/ncu_traffic.py report.ncu-rep "source note" > profiles/ncu_traffic.json"""
+usage: tools/ncu_traffic.py report.ncu-rep "source note" [frames per launch, default 64] > profiles/ncu_traffic.json"""
 import csv, io, json, subprocess, sys
 rep, note = sys.argv[1], sys.argv[2]
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
@@ -22,4 +22,4 @@ for r in data:
     instr[st] = instr.get(st, 0) + int(float(r[ii].replace(",", "")))
 dram["pyramid"]["note"] = "level0 interior + border + 7 resize launches of one pass summed"
 instr["note"] = "smsp__inst_executed.sum of the same capture; the extraction kernels are bound by instruction issue, not by DRAM"
-print(json.dumps({"source": note, "frames_per_launch": 64, "dram_bytes_per_launch": dram, "warp_instructions_per_launch": instr}, indent=2))
+print(json.dumps({"source": note, "frames_per_launch": int(sys.argv[3]) if len(sys.argv) > 3 else 64, "dram_bytes_per_launch": dram, "warp_instructions_per_launch": instr}, indent=2))
