@@ -113,6 +113,8 @@ class Mat {
   Mat rowRange(int a, int b) const { return (*this)(Rect(0, a, cols, b - a)); }
   Mat colRange(int a, int b) const { return (*this)(Rect(a, 0, b - a, rows)); }
   Mat row(int y) const { return rowRange(y, y + 1); }
+  Mat col(int x) const { return colRange(x, x + 1); }
+  Mat t() const;   // 32F transpose (defined below)
   bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
   int type() const { return type_; }
   int depth() const { return type_; }
@@ -127,6 +129,9 @@ class Mat {
   const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
   template <typename T> T& at(int y, int x) { return reinterpret_cast<T*>(data + (size_t)y * step)[x]; }
   template <typename T> const T& at(int y, int x) const { return reinterpret_cast<const T*>(data + (size_t)y * step)[x]; }
+  // single index on a vector (cv::Mat::at(int i0)): element i of a row vector, row i of a column vector (views keep their row stride)
+  template <typename T> T& at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+  template <typename T> const T& at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
 
   void copyTo(const class _OutputArray& o) const;   // defined after _OutputArray
   orb_oracle::Img img() const { return orb_oracle::Img{data, cols, rows, (int)step}; }
@@ -164,6 +169,33 @@ inline Mat operator-(const Mat& a, const Mat& b) {
   assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
   Mat m(a.rows, a.cols, CV_32F);
   for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = a.at<float>(y, x) - b.at<float>(y, x);
+  return m;
+}
+// ---- the pose algebra at the head of the projection matchers (src/ORBmatcher.cc:1720-1733, 1753): small 32F matrices. cv::gemm accumulates
+// float products in double and rounds once; the pins feed identity rotations and power-of-two depths, for which every product and sum is exact
+// in any order, so this restatement cannot differ from OpenCV on them.
+inline Mat Mat::t() const {
+  assert(type_ == CV_32F);
+  Mat m(cols, rows, CV_32F);
+  for (int y = 0; y < rows; ++y) for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
+  return m;
+}
+inline Mat operator-(const Mat& a) { return -1.f * a; }
+inline Mat operator+(const Mat& a, const Mat& b) {
+  assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = a.at<float>(y, x) + b.at<float>(y, x);
+  return m;
+}
+inline Mat operator*(const Mat& a, const Mat& b) {
+  assert(a.type() == CV_32F && b.type() == CV_32F && a.cols == b.rows);
+  Mat m(a.rows, b.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y)
+    for (int x = 0; x < b.cols; ++x) {
+      double acc = 0;
+      for (int k = 0; k < a.cols; ++k) acc += (double)a.at<float>(y, k) * (double)b.at<float>(k, x);
+      m.at<float>(y, x) = (float)acc;
+    }
   return m;
 }
 enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };

@@ -58,9 +58,10 @@ class MapPoint {       // include/MapPoint.h: the members the matcher loops name
   bool isBad() { return bad; }
   int Observations() { return nObs; }
   cv::Mat GetDescriptor() { return mDescriptor.clone(); }   // include/MapPoint.h: returns mDescriptor.clone()
+  cv::Mat GetWorldPos() { return mWorldPos.clone(); }       // include/MapPoint.h / src/MapPoint.cc:117-121
   bool bad = false;
   int nObs = 0;
-  cv::Mat mDescriptor;
+  cv::Mat mDescriptor, mWorldPos;
 };
 
 class Frame {          // include/Frame.h: the members src/Frame.cc:880-1176, 432-460, 633-745 and the matcher loops name
@@ -78,6 +79,9 @@ class Frame {          // include/Frame.h: the members src/Frame.cc:880-1176, 43
   std::vector<MapPoint*> mvpMapPoints;
   DBoW2::FeatureVector mFeatVec;
   float mb, mbf;
+  cv::Mat mTcw;                                              // include/Frame.h:160
+  std::vector<bool> mvbOutlier;
+  float fx, fy, cx, cy;                                      // static in the reference (include/Frame.h:113-118)
   // static members of the reference's class (include/Frame.h:190-200): plain members here, named unqualified inside the member functions
   float mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
   std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
@@ -101,6 +105,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   static const int HISTO_LENGTH;
   void ComputeThreeMaxima(vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
   int SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th = 3);
+  int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
   int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
   int SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12, int windowSize = 10);
   float RadiusByViewingCos(const float& viewCos);
@@ -121,6 +126,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
 #include "_ref/gen_sbp.inc"
 #include "_ref/gen_sbow.inc"
 #include "_ref/gen_sinit.inc"
+#include "_ref/gen_sbpf.inc"
 
 struct FrameDescs { cv::Mat mDescriptors; };
 
@@ -297,6 +303,68 @@ int main(int argc, char** argv) {
     for (int i = 0; i < m; ++i) { pts[i].mDescriptor = mat_u8(r.bytes(32), 1, 32); vp[i] = &pts[i]; }
     ORB_SLAM2::ORBmatcher matcher(nnratio, true);
     out.push_back(matcher.SearchByProjection(F, vp, th));
+    for (int i = 0; i < n; ++i) {
+      ORB_SLAM2::MapPoint* p = F.mvpMapPoints[i];
+      out.push_back(p && p != &taken ? (int32_t)(p - pts.data()) : -1);
+    }
+  } else if (mode == "sbpf") {
+    // ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1702-1871), the TrackWithMotionModel matcher.
+    // float bounds[4], th, nnratio (unused by this form), mb, mbf, fx, fy, cx, cy, last_tz; int bMono, check_orientation, nlevels; nlevels x float
+    // scale; current frame: int n; n x KeyPoint (mvKeysUn); n x 32 B; n x float mvuRight; n x u8 claimed; last frame: int m; m x {float X, Y, Z,
+    // angle; int octave, flags (1 = no map point, 2 = Observations() > 0, 4 = outlier)}; m x 32 B
+    //   ->  int nmatches; n x int32 index of the last-frame point assigned by this call (-1 none).
+    // Poses: CurrentFrame.mTcw = identity, LastFrame.mTcw = translation (0, 0, last_tz): tlc(2) = last_tz decides forward / backward.
+    ORB_SLAM2::Frame F, LF;
+    F.mnMinX = r.get<float>(); F.mnMinY = r.get<float>(); F.mnMaxX = r.get<float>(); F.mnMaxY = r.get<float>();
+    const float th = r.get<float>(), nnratio = r.get<float>();
+    F.mb = r.get<float>(); F.mbf = r.get<float>();
+    F.fx = r.get<float>(); F.fy = r.get<float>(); F.cx = r.get<float>(); F.cy = r.get<float>();
+    const float last_tz = r.get<float>();
+    const int bMono = r.get<int32_t>(), ori = r.get<int32_t>();
+    const int nl = r.get<int32_t>();
+    for (int l = 0; l < nl; ++l) F.mvScaleFactors.push_back(r.get<float>());
+    F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);     // src/Frame.cc:200-202
+    F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
+    const int n = r.get<int32_t>();
+    F.N = n;
+    F.mvKeysUn.resize(n);
+    std::memcpy(F.mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+    F.mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+    F.mvuRight.resize(n);
+    std::memcpy(F.mvuRight.data(), r.bytes((size_t)n * 4), (size_t)n * 4);
+    ORB_SLAM2::MapPoint taken;
+    taken.nObs = 1;
+    F.mvpMapPoints.assign(n, nullptr);
+    const uint8_t* cl = r.bytes(n);
+    for (int i = 0; i < n; ++i) if (cl[i]) F.mvpMapPoints[i] = &taken;
+    F.AssignFeaturesToGrid();
+    auto pose = [](float tz) {
+      cv::Mat T(4, 4, CV_32F);
+      for (int y = 0; y < 4; ++y) for (int x = 0; x < 4; ++x) T.at<float>(y, x) = y == x ? 1.f : 0.f;
+      T.at<float>(2, 3) = tz;
+      return T;
+    };
+    F.mTcw = pose(0.f);
+    LF.mTcw = pose(last_tz);
+    const int m = r.get<int32_t>();
+    LF.N = m;
+    std::vector<ORB_SLAM2::MapPoint> pts(m);
+    LF.mvpMapPoints.assign(m, nullptr);
+    LF.mvbOutlier.assign(m, false);
+    LF.mvKeys.resize(m); LF.mvKeysUn.resize(m);
+    for (int i = 0; i < m; ++i) {
+      pts[i].mWorldPos = cv::Mat(3, 1, CV_32F);
+      for (int k = 0; k < 3; ++k) pts[i].mWorldPos.at<float>(k) = r.get<float>();
+      LF.mvKeysUn[i].angle = r.get<float>();
+      LF.mvKeys[i].octave = r.get<int32_t>();
+      const int fl = r.get<int32_t>();
+      if (!(fl & 1)) LF.mvpMapPoints[i] = &pts[i];
+      pts[i].nObs = (fl & 2) ? 1 : 0;
+      LF.mvbOutlier[i] = (fl & 4) != 0;
+    }
+    for (int i = 0; i < m; ++i) pts[i].mDescriptor = mat_u8(r.bytes(32), 1, 32);
+    ORB_SLAM2::ORBmatcher matcher(nnratio, ori != 0);
+    out.push_back(matcher.SearchByProjection(F, LF, th, bMono != 0));
     for (int i = 0; i < n; ++i) {
       ORB_SLAM2::MapPoint* p = F.mvpMapPoints[i];
       out.push_back(p && p != &taken ? (int32_t)(p - pts.data()) : -1);

@@ -194,6 +194,27 @@ def ref_search_by_projection(kps_un, desc, uright, claimed, bounds, scale, th, n
     return int(out[0]), out[1:1 + n].copy()
 
 
+LAST_DTYPE = np.dtype([("X", "<f4"), ("Y", "<f4"), ("Z", "<f4"), ("angle", "<f4"), ("octave", "<i4"), ("flags", "<i4")])
+
+
+def ref_search_by_projection_frames(kps_un, desc, uright, claimed, bounds, scale, th, cam, mb, mbf, last_tz, mono, check_orientation, last, qdesc):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1702-1871, the TrackWithMotionModel matcher) with
+    CurrentFrame.mTcw = identity and LastFrame.mTcw = translation (0, 0, last_tz). cam = (fx, fy, cx, cy). last: LAST_DTYPE per last-frame keypoint
+    (world point, angle of its keypoint, octave, flags 1 = no map point, 2 = Observations() > 0, 4 = outlier).
+    Returns (nmatches, assigned [n]: last-frame index whose map point the current keypoint got by this call, -1 none)."""
+    n, m = len(kps_un), len(last)
+    kps_un = np.ascontiguousarray(kps_un)
+    assert kps_un.dtype.itemsize == 28 and last.dtype == LAST_DTYPE
+    payload = struct.pack("<4f2f2f4ff3i", *[float(b) for b in bounds], th, 0.0, mb, mbf, *[float(c) for c in cam], last_tz, int(mono),
+                          int(check_orientation), len(scale)) + np.ascontiguousarray(scale, "<f4").tobytes()
+    payload += struct.pack("<i", n) + kps_un.tobytes() + np.ascontiguousarray(desc, np.uint8).tobytes()
+    payload += np.ascontiguousarray(uright if uright is not None else np.full(n, -1, np.float32), "<f4").tobytes()
+    payload += np.ascontiguousarray(claimed if claimed is not None else np.zeros(n, np.uint8), np.uint8).tobytes()
+    payload += struct.pack("<i", m) + np.ascontiguousarray(last).tobytes() + np.ascontiguousarray(qdesc, np.uint8).tobytes()
+    out = np.frombuffer(_run_match("sbpf", payload), "<i4")
+    return int(out[0]), out[1:1 + n].copy()
+
+
 def _fv_bytes(fv: dict) -> bytes:
     b = struct.pack("<i", len(fv))
     for node in sorted(fv):

@@ -287,6 +287,82 @@ def test_search_by_projection_equals_reference(oracle, seed, stereo, th, ratio, 
     assert np.array_equal(assigned, as_ref), f"assignment differs at keypoints {np.flatnonzero(assigned != as_ref)[:10]}"
 
 
+CAM = (512.0, 256.0, 320.0, 240.0)   # fx, fy, cx, cy: powers of two / small integers, so that the reference's projection is exact (see below)
+
+
+def _frame_to_frame_case(seed, mode, n=900, m=800, stereo=True, th=15.0, mb=0.1, mbf=40.0):
+    """Inputs of SearchByProjection(CurrentFrame, LastFrame, th, bMono) and the query records the host derives from them (src/ORBmatcher.cc:1744-1783).
+    The pose algebra in front of the scan is NOT part of the device op (the host projects); it is made exact here so that both sides see the same
+    u, v: identity rotation, zero translation of the current frame, depths that are powers of two, u and v with two fractional bits."""
+    from orb_slam2_detailed_comments_b200._lib import QUERY_DTYPE
+    c = synth.synth_guided_case(seed, n=n, m=m, stereo=stereo)
+    rng = np.random.default_rng(seed + 77)
+    q = c["queries"]
+    fx, fy, cx, cy = (np.float32(v) for v in CAM)
+    u = (np.round(q["u"] * 4) / 4).astype(np.float32)
+    v = (np.round(q["v"] * 4) / 4).astype(np.float32)
+    z = rng.choice(np.array([0.5, 1.0, 2.0, 4.0, -1.0], np.float32), m, p=[0.2, 0.3, 0.25, 0.2, 0.05])
+    last = np.zeros(m, ref_binary.LAST_DTYPE)
+    last["X"], last["Y"], last["Z"] = (u - cx) / fx * z, (v - cy) / fy * z, z
+    last["angle"] = q["angle"]
+    last["octave"] = np.clip(q["max_level"], 0, 7)
+    last["flags"] = (rng.random(m) < 0.05) * 1 + (rng.random(m) < 0.8) * 2 + (rng.random(m) < 0.05) * 4
+    invz = (np.float64(1.0) / z.astype(np.float64)).astype(np.float32)               # const float invzc = 1.0 / x3Dc.at<float>(2)
+    uu = fx * last["X"] * invz + cx                                                   # float32 throughout, as the reference's expression
+    vv = fy * last["Y"] * invz + cy
+    ok = z > 0
+    assert np.array_equal(uu[ok], u[ok]) and np.array_equal(vv[ok], v[ok])
+    mnx, mny, mxx, mxy = (np.float32(b) for b in c["bounds"])
+    skip = (last["flags"] & 1).astype(bool) | (last["flags"] & 4).astype(bool) | (invz < 0) | (uu < mnx) | (uu > mxx) | (vv < mny) | (vv > mxy)
+    last_tz, mono = {"forward": (1.0, False), "backward": (-1.0, False), "still": (0.0, False), "mono": (1.0, True)}[mode]
+    q2 = np.zeros(m, QUERY_DTYPE)
+    q2["u"], q2["v"] = uu, vv
+    q2["radius"] = (np.float32(th) * SCALE[last["octave"]]).astype(np.float32)
+    q2["ur"] = uu - np.float32(mbf) * invz
+    q2["angle"] = last["angle"]
+    o = last["octave"].astype(np.int16)
+    if mode == "forward":
+        q2["min_level"], q2["max_level"] = o, -1
+    elif mode == "backward":
+        q2["min_level"], q2["max_level"] = 0, o
+    else:
+        q2["min_level"], q2["max_level"] = o - 1, o + 1
+    q2["flags"] = np.where(skip, 1, np.where(last["flags"] & 2, 2, 0))
+    return c, last, q2, dict(th=th, mb=mb, mbf=mbf, last_tz=last_tz, mono=mono)
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,mode,stereo,ori", [(1, "still", True, True), (2, "forward", True, True), (3, "backward", True, False), (4, "mono", False, True),
+                                                   (5, "still", False, False)])
+def test_frame_to_frame_projection_equals_reference(oracle, seed, mode, stereo, ori):
+    """oracle.search_by_projection == the reference's own SearchByProjection(CurrentFrame, LastFrame, th, bMono), the matcher of
+    TrackWithMotionModel: forward / backward / neither level windows, outlier / null / behind-the-camera / out-of-bounds skips, stereo check with
+    u - mbf * invzc, best-only accept at TH_HIGH, claims through Observations(), rotation histogram + three maxima."""
+    c, last, q2, p = _frame_to_frame_case(seed, mode, stereo=stereo)
+    nm_ref, as_ref = ref_binary.ref_search_by_projection_frames(c["kps"], c["desc"], c["uright"], c["claimed"], c["bounds"], SCALE, p["th"], CAM, p["mb"],
+                                                                p["mbf"], p["last_tz"], p["mono"], ori, last, c["qdesc"])
+    assigned, qmatch, nm = oracle.search_by_projection(c["kps"], c["desc"], q2, c["qdesc"], c["bounds"], th_dist=100, nn_ratio=0.0,
+                                                       check_orientation=ori, uright=c["uright"], claimed=c["claimed"])
+    assert nm == nm_ref and nm_ref > 100, (nm, nm_ref)
+    assert np.array_equal(assigned, as_ref), f"assignment differs at keypoints {np.flatnonzero(assigned != as_ref)[:10]}"
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cuda_frame_to_frame_projection_equals_reference():
+    from orb_slam2_detailed_comments_b200.matcher import ORBmatcher
+    for seed, mode, stereo, ori in ((21, "still", True, True), (22, "forward", True, True), (23, "backward", False, True), (24, "mono", False, False)):
+        c, last, q2, p = _frame_to_frame_case(seed, mode, stereo=stereo)
+        nm_ref, as_ref = ref_binary.ref_search_by_projection_frames(c["kps"], c["desc"], c["uright"], c["claimed"], c["bounds"], SCALE, p["th"], CAM,
+                                                                    p["mb"], p["mbf"], p["last_tz"], p["mono"], ori, last, c["qdesc"])
+        n, m = len(c["kps"]), len(q2)
+        assigned, qmatch, nm = ORBmatcher(0.9, ori).SearchByProjection(c["kps"][None], c["desc"][None], np.array([n], np.int32), q2[None], c["qdesc"][None],
+                                                                       np.array([m], np.int32), c["bounds"], use_ratio=False,
+                                                                       uright=None if c["uright"] is None else c["uright"][None],
+                                                                       claimed=c["claimed"][None])
+        assert nm[0] == nm_ref and np.array_equal(assigned[0], as_ref), (seed, mode, nm[0], nm_ref)
+
+
 @needs_ref
 @pytest.mark.parametrize("seed,ori,ratio", [(1, True, 0.7), (2, False, 0.6), (3, True, 0.9)])
 def test_search_by_bow_equals_reference(oracle, seed, ori, ratio):
