@@ -107,6 +107,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   int SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th = 3);
   int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
   int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
+  int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12);
   int SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12, int windowSize = 10);
   float RadiusByViewingCos(const float& viewCos);
   // harness entry points around the extracted loop bodies (declared here so the bodies see the members unqualified)
@@ -127,6 +128,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
 #include "_ref/gen_sbow.inc"
 #include "_ref/gen_sinit.inc"
 #include "_ref/gen_sbpf.inc"
+#include "_ref/gen_sbow2.inc"
 
 struct FrameDescs { cv::Mat mDescriptors; };
 
@@ -405,6 +407,35 @@ int main(int argc, char** argv) {
     std::vector<ORB_SLAM2::MapPoint*> matches;
     out.push_back(matcher.SearchByBoW(&KF, F, matches));
     for (int i = 0; i < nf; ++i) out.push_back(matches[i] ? (int32_t)(matches[i] - pts.data()) : -1);
+  } else if (mode == "sbow2") {
+    // ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (src/ORBmatcher.cc:724-867), the loop-closing matcher.
+    // float nnratio; int checkOri; twice {int n; n x 32 B; n x KeyPoint (mvKeysUn); n x u8 "holds a good map point"; FeatureVector}
+    // -> int nmatches; n1 x int32 feature of keyframe 2 whose map point vpMatches12[i] is (-1 none)
+    const float nnratio = r.get<float>();
+    const int ori = r.get<int32_t>();
+    ORB_SLAM2::KeyFrame K[2];
+    std::vector<ORB_SLAM2::MapPoint> pts[2];
+    for (int k = 0; k < 2; ++k) {
+      const int n = r.get<int32_t>();
+      K[k].mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+      K[k].mvKeysUn.resize(n);
+      std::memcpy(K[k].mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+      pts[k].resize(n);
+      const uint8_t* valid = r.bytes(n);
+      K[k].mvpMapPoints.assign(n, nullptr);
+      for (int i = 0; i < n; ++i) if (valid[i]) K[k].mvpMapPoints[i] = &pts[k][i];
+      const int cnt = r.get<int32_t>();
+      for (int j = 0; j < cnt; ++j) {
+        const uint32_t node = r.get<uint32_t>();
+        const int mm = r.get<int32_t>();
+        std::vector<unsigned int>& v = K[k].mFeatVec[node];
+        for (int q = 0; q < mm; ++q) v.push_back(r.get<uint32_t>());
+      }
+    }
+    ORB_SLAM2::ORBmatcher matcher(nnratio, ori != 0);
+    std::vector<ORB_SLAM2::MapPoint*> matches;
+    out.push_back(matcher.SearchByBoW(&K[0], &K[1], matches));
+    for (size_t i = 0; i < matches.size(); ++i) out.push_back(matches[i] ? (int32_t)(matches[i] - pts[1].data()) : -1);
   } else if (mode == "sinit") {
     // float bounds[4], nnratio; int checkOri, windowSize; F2: int n; n x KeyPoint (mvKeysUn); n x 32 B; F1: int m; m x KeyPoint (mvKeysUn: octave,
     // angle); m x 32 B; m x {float x, y} vbPrevMatched  ->  int nmatches; m x int32 vnMatches12

@@ -235,6 +235,17 @@ def ref_search_by_bow(kf_desc, kf_kps_un, kf_valid, kf_fv: dict, f_desc, f_kps, 
     return int(out[0]), out[1:1 + nf].copy()
 
 
+def ref_search_by_bow_keyframes(desc1, kps1_un, valid1, fv1: dict, desc2, kps2_un, valid2, fv2: dict, nnratio: float, check_orientation: bool):
+    """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (src/ORBmatcher.cc:724-867). Returns (nmatches, vpMatches12 [n1] as the index of the
+    keyframe-2 feature whose map point was matched, -1 none)."""
+    payload = struct.pack("<fi", nnratio, int(check_orientation))
+    for d, k, v, fv in ((desc1, kps1_un, valid1, fv1), (desc2, kps2_un, valid2, fv2)):
+        payload += struct.pack("<i", len(k)) + np.ascontiguousarray(d, np.uint8).tobytes() + np.ascontiguousarray(k).tobytes()
+        payload += np.ascontiguousarray(v, np.uint8).tobytes() + _fv_bytes(fv)
+    out = np.frombuffer(_run_match("sbow2", payload), "<i4")
+    return int(out[0]), out[1:1 + len(kps1_un)].copy()
+
+
 def ref_search_for_initialization(kps2_un, desc2, kps1_un, desc1, prev_matched, bounds, nnratio, check_orientation, window):
     """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) on F2's reference-built grid.
     Returns (nmatches, vnMatches12 [m])."""

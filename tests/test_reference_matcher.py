@@ -383,6 +383,26 @@ def test_search_by_bow_equals_reference(oracle, seed, ori, ratio):
 
 
 @needs_ref
+@pytest.mark.parametrize("seed,ori,ratio", [(4, True, 0.75), (5, False, 0.6), (6, True, 0.9)])
+def test_search_by_bow_keyframes_equals_reference(oracle, seed, ori, ratio):
+    """The KeyFrame-KeyFrame form (loop closing, src/ORBmatcher.cc:724-867) == oracle.search_by_bow with the keyframe-2 features that hold no good
+    map point blocked and th_dist = TH_LOW - 1 (this form accepts on `bestDist1 < TH_LOW`): vbMatched2 claims, strict ratio test, histogram over idx1."""
+    import test_search_by_bow as tb
+    voc = synth.synth_vocabulary(10, 3, seed=11)
+    ov = oracle.OracleVocabulary(*voc)
+    d1, k1, valid1, d2, k2 = tb._pair(voc, seed, 520, 540)
+    rng = np.random.default_rng(seed)
+    valid2 = (rng.random(len(d2)) < 0.85).astype(np.uint8)
+    fv1, fv2 = ov.transform(d1, 2)[3], ov.transform(d2, 2)[3]
+    fv1 = {n: v for n, v in fv1.items() if n % 6 != 1}
+    fv2 = {n: v for n, v in fv2.items() if n % 5 != 3}
+    nm_ref, m12_ref = ref_binary.ref_search_by_bow_keyframes(d1, k1, valid1, fv1, d2, k2, valid2, fv2, ratio, ori)
+    got = oracle.search_by_bow(d1, k1, valid1, tb._csr(fv1, len(d1)), d2, k2, tb._csr(fv2, len(d2)), 49, ratio, ori, f_blocked=1 - valid2)
+    assert got[1] == nm_ref and nm_ref > 40, (got[1], nm_ref)
+    assert np.array_equal(got[2], m12_ref)
+
+
+@needs_ref
 @pytest.mark.gpu
 def test_cuda_search_by_projection_equals_reference():
     from orb_slam2_detailed_comments_b200.matcher import ORBmatcher
