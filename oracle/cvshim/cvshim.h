@@ -115,6 +115,11 @@ class Mat {
   Mat row(int y) const { return rowRange(y, y + 1); }
   Mat col(int x) const { return colRange(x, x + 1); }
   Mat t() const;   // 32F transpose (defined below)
+  double dot(const Mat& m) const {   // cv::Mat::dot for 32F: double accumulation
+    double acc = 0;
+    for (int y = 0; y < rows; ++y) for (int x = 0; x < cols; ++x) acc += (double)at<float>(y, x) * (double)m.at<float>(y, x);
+    return acc;
+  }
   bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
   int type() const { return type_; }
   int depth() const { return type_; }
@@ -199,6 +204,11 @@ inline Mat operator*(const Mat& a, const Mat& b) {
   return m;
 }
 enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
+inline double norm(const Mat& a) {   // cv::norm(a) = L2 for 32F, accumulated in double
+  double acc = 0;
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) acc += (double)a.at<float>(y, x) * (double)a.at<float>(y, x);
+  return std::sqrt(acc);
+}
 inline double norm(const Mat& a, const Mat& b, int normType) {   // cv::norm(a, b, NORM_L1) for 32F: sum |a - b| accumulated in double
   assert(normType == NORM_L1 && a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
   (void)normType;

@@ -50,6 +50,10 @@ class ORBextractor {   // include/ORBextractor.h:185: the one member ComputeSter
 
 #include "_ref/gen_griddefs.inc"
 
+class KeyFrame;
+class MapPoint;
+static MapPoint* g_cur_point = nullptr;   // the map point whose candidate scan is running (set by GetDescriptor, read by KeyFrame::GetMapPoint)
+
 class MapPoint {       // include/MapPoint.h: the members the matcher loops name
  public:
   bool mbTrackInView = true;
@@ -57,8 +61,20 @@ class MapPoint {       // include/MapPoint.h: the members the matcher loops name
   float mTrackViewCos = 1.f, mTrackProjX = 0.f, mTrackProjY = 0.f, mTrackProjXR = 0.f;
   bool isBad() { return bad; }
   int Observations() { return nObs; }
-  cv::Mat GetDescriptor() { return mDescriptor.clone(); }   // include/MapPoint.h: returns mDescriptor.clone()
+  cv::Mat GetDescriptor() { g_cur_point = this; return mDescriptor.clone(); }   // include/MapPoint.h: returns mDescriptor.clone()
   cv::Mat GetWorldPos() { return mWorldPos.clone(); }       // include/MapPoint.h / src/MapPoint.cc:117-121
+  // what Fuse asks of a map point (src/ORBmatcher.cc:1123-1160): host-side quantities here, plain stored values
+  bool IsInKeyFrame(KeyFrame*) { return inKF; }
+  float GetMaxDistanceInvariance() { return maxD; }
+  float GetMinDistanceInvariance() { return minD; }
+  cv::Mat GetNormal() { return mNormal.clone(); }
+  int PredictScale(const float&, KeyFrame*) { return predLevel; }
+  void Replace(MapPoint*) {}
+  void AddObservation(KeyFrame*, size_t) {}
+  bool inKF = false;
+  float maxD = 3.0e38f, minD = 0.f;
+  int predLevel = 0, fusedIdx = -1;
+  cv::Mat mNormal;
   bool bad = false;
   int nObs = 0;
   cv::Mat mDescriptor, mWorldPos;
@@ -87,9 +103,21 @@ class Frame {          // include/Frame.h: the members src/Frame.cc:880-1176, 43
   std::vector<std::size_t> mGrid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
 };
 
-class KeyFrame {       // include/KeyFrame.h: what SearchByBoW reads
+class KeyFrame {       // include/KeyFrame.h: what SearchByBoW and Fuse read
  public:
   std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+  cv::Mat GetRotation() { return Rcw.clone(); }
+  cv::Mat GetTranslation() { return tcw.clone(); }
+  cv::Mat GetCameraCenter() { return Ow.clone(); }
+  vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r) const;
+  bool IsInImage(const float& x, const float& y) const;
+  MapPoint* GetMapPoint(const size_t& idx) { if (g_cur_point) g_cur_point->fusedIdx = (int)idx; return mvpMapPoints[idx]; }   // called once per accepted point (:1243)
+  void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; }
+  cv::Mat Rcw, tcw, Ow;
+  int N = 0, mnGridCols = FRAME_GRID_COLS, mnGridRows = FRAME_GRID_ROWS;
+  float fx, fy, cx, cy, mbf, mnMinX, mnMinY, mnMaxX, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+  std::vector<float> mvScaleFactors, mvInvLevelSigma2, mvuRight;
+  std::vector<std::vector<std::vector<size_t>>> mGrid;
   DBoW2::FeatureVector mFeatVec;
   cv::Mat mDescriptors;
   std::vector<cv::KeyPoint> mvKeysUn;
@@ -108,6 +136,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
   int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
   int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12);
+  int Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th = 3.0);
   int SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12, int windowSize = 10);
   float RadiusByViewingCos(const float& viewCos);
   // harness entry points around the extracted loop bodies (declared here so the bodies see the members unqualified)
@@ -129,6 +158,8 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
 #include "_ref/gen_sinit.inc"
 #include "_ref/gen_sbpf.inc"
 #include "_ref/gen_sbow2.inc"
+#include "_ref/gen_kfarea.inc"
+#include "_ref/gen_fuse.inc"
 
 struct FrameDescs { cv::Mat mDescriptors; };
 
@@ -436,6 +467,63 @@ int main(int argc, char** argv) {
     std::vector<ORB_SLAM2::MapPoint*> matches;
     out.push_back(matcher.SearchByBoW(&K[0], &K[1], matches));
     for (size_t i = 0; i < matches.size(); ++i) out.push_back(matches[i] ? (int32_t)(matches[i] - pts[1].data()) : -1);
+  } else if (mode == "fuse") {
+    // ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1100-1270) with KeyFrame::GetFeaturesInArea / IsInImage (src/KeyFrame.cc:879-929) on a grid
+    // built by Frame::AssignFeaturesToGrid and copied as the KeyFrame constructor does (src/KeyFrame.cc:85-92). Pose = identity, camera centre = 0.
+    // float bounds[4], th, mbf, fx, fy, cx, cy; int nlevels; nlevels x float scale; nlevels x float invLevelSigma2; int n; n x KeyPoint; n x 32 B;
+    // n x float mvuRight; n x u8 "slot holds a map point"; int m; m x {float X, Y, Z, nz; int level, flags (1 null, 2 bad, 4 IsInKeyFrame)}; m x 32 B
+    //   -> int nFused; m x int32 bestIdx of the points that were fused (-1 otherwise)
+    ORB_SLAM2::Frame F;
+    ORB_SLAM2::KeyFrame KF;
+    F.mnMinX = r.get<float>(); F.mnMinY = r.get<float>(); F.mnMaxX = r.get<float>(); F.mnMaxY = r.get<float>();
+    const float th = r.get<float>();
+    KF.mbf = r.get<float>(); KF.fx = r.get<float>(); KF.fy = r.get<float>(); KF.cx = r.get<float>(); KF.cy = r.get<float>();
+    const int nl = r.get<int32_t>();
+    for (int l = 0; l < nl; ++l) KF.mvScaleFactors.push_back(r.get<float>());
+    for (int l = 0; l < nl; ++l) KF.mvInvLevelSigma2.push_back(r.get<float>());
+    F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);     // src/Frame.cc:200-202
+    F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
+    const int n = r.get<int32_t>();
+    F.N = n;
+    F.mvKeysUn.resize(n);
+    std::memcpy(F.mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+    KF.mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+    KF.mvuRight.resize(n);
+    std::memcpy(KF.mvuRight.data(), r.bytes((size_t)n * 4), (size_t)n * 4);
+    ORB_SLAM2::MapPoint held;   // whatever a keyframe slot held before the call
+    held.nObs = 1;
+    KF.mvpMapPoints.assign(n, nullptr);
+    const uint8_t* cl = r.bytes(n);
+    for (int i = 0; i < n; ++i) if (cl[i]) KF.mvpMapPoints[i] = &held;
+    F.AssignFeaturesToGrid();
+    KF.N = n; KF.mvKeysUn = F.mvKeysUn;
+    KF.mnMinX = F.mnMinX; KF.mnMinY = F.mnMinY; KF.mnMaxX = F.mnMaxX; KF.mnMaxY = F.mnMaxY;
+    KF.mfGridElementWidthInv = F.mfGridElementWidthInv; KF.mfGridElementHeightInv = F.mfGridElementHeightInv;
+    KF.mGrid.resize(KF.mnGridCols);
+    for (int i = 0; i < KF.mnGridCols; ++i) {
+      KF.mGrid[i].resize(KF.mnGridRows);
+      for (int j = 0; j < KF.mnGridRows; ++j) KF.mGrid[i][j] = F.mGrid[i][j];
+    }
+    KF.Rcw = cv::Mat(3, 3, CV_32F); KF.tcw = cv::Mat(3, 1, CV_32F); KF.Ow = cv::Mat(3, 1, CV_32F);
+    for (int y = 0; y < 3; ++y) { for (int x = 0; x < 3; ++x) KF.Rcw.at<float>(y, x) = y == x ? 1.f : 0.f; KF.tcw.at<float>(y) = 0.f; KF.Ow.at<float>(y) = 0.f; }
+    const int m = r.get<int32_t>();
+    std::vector<ORB_SLAM2::MapPoint> pts(m);
+    std::vector<ORB_SLAM2::MapPoint*> vp(m, nullptr);
+    for (int i = 0; i < m; ++i) {
+      pts[i].mWorldPos = cv::Mat(3, 1, CV_32F);
+      for (int k = 0; k < 3; ++k) pts[i].mWorldPos.at<float>(k) = r.get<float>();
+      pts[i].mNormal = cv::Mat(3, 1, CV_32F);
+      pts[i].mNormal.at<float>(0) = 0.f; pts[i].mNormal.at<float>(1) = 0.f; pts[i].mNormal.at<float>(2) = r.get<float>();
+      pts[i].predLevel = r.get<int32_t>();
+      const int fl = r.get<int32_t>();
+      if (!(fl & 1)) vp[i] = &pts[i];
+      pts[i].bad = (fl & 2) != 0;
+      pts[i].inKF = (fl & 4) != 0;
+    }
+    for (int i = 0; i < m; ++i) pts[i].mDescriptor = mat_u8(r.bytes(32), 1, 32);
+    ORB_SLAM2::ORBmatcher matcher(0.6f, true);
+    out.push_back(matcher.Fuse(&KF, vp, th));
+    for (int i = 0; i < m; ++i) out.push_back(pts[i].fusedIdx);
   } else if (mode == "sinit") {
     // float bounds[4], nnratio; int checkOri, windowSize; F2: int n; n x KeyPoint (mvKeysUn); n x 32 B; F1: int m; m x KeyPoint (mvKeysUn: octave,
     // angle); m x 32 B; m x {float x, y} vbPrevMatched  ->  int nmatches; m x int32 vnMatches12

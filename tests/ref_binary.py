@@ -246,6 +246,25 @@ def ref_search_by_bow_keyframes(desc1, kps1_un, valid1, fv1: dict, desc2, kps2_u
     return int(out[0]), out[1:1 + len(kps1_un)].copy()
 
 
+FUSE_DTYPE = np.dtype([("X", "<f4"), ("Y", "<f4"), ("Z", "<f4"), ("nz", "<f4"), ("level", "<i4"), ("flags", "<i4")])
+
+
+def ref_fuse(kps_un, desc, uright, held, bounds, scale, inv_sigma2, th, cam, mbf, points, qdesc):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1100-1270) on a keyframe with identity pose. points: FUSE_DTYPE (world point, z of the
+    viewing normal (0, 0, nz), PredictScale result, flags 1 = null, 2 = isBad(), 4 = IsInKeyFrame(pKF)). Returns (nFused, bestIdx [m], -1 = not fused)."""
+    n, m = len(kps_un), len(points)
+    kps_un = np.ascontiguousarray(kps_un)
+    assert kps_un.dtype.itemsize == 28 and points.dtype == FUSE_DTYPE
+    payload = struct.pack("<4ff5fi", *[float(b) for b in bounds], th, mbf, *[float(c) for c in cam], len(scale))
+    payload += np.ascontiguousarray(scale, "<f4").tobytes() + np.ascontiguousarray(inv_sigma2, "<f4").tobytes()
+    payload += struct.pack("<i", n) + kps_un.tobytes() + np.ascontiguousarray(desc, np.uint8).tobytes()
+    payload += np.ascontiguousarray(uright if uright is not None else np.full(n, -1, np.float32), "<f4").tobytes()
+    payload += np.ascontiguousarray(held if held is not None else np.zeros(n, np.uint8), np.uint8).tobytes()
+    payload += struct.pack("<i", m) + np.ascontiguousarray(points).tobytes() + np.ascontiguousarray(qdesc, np.uint8).tobytes()
+    out = np.frombuffer(_run_match("fuse", payload), "<i4")
+    return int(out[0]), out[1:1 + m].copy()
+
+
 def ref_search_for_initialization(kps2_un, desc2, kps1_un, desc1, prev_matched, bounds, nnratio, check_orientation, window):
     """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) on F2's reference-built grid.
     Returns (nmatches, vnMatches12 [m])."""

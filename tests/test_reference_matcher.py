@@ -402,6 +402,67 @@ def test_search_by_bow_keyframes_equals_reference(oracle, seed, ori, ratio):
     assert np.array_equal(got[2], m12_ref)
 
 
+def _fuse_case(seed, n=900, m=800, stereo=True, th=3.0, mbf=40.0):
+    """Inputs of Fuse(pKF, vpMapPoints, th) and the query records the host derives from them (src/ORBmatcher.cc:1117-1166): projection exact by
+    construction (identity pose, power-of-two depths, u / v with two fractional bits), PredictScale and the viewing checks are host-side values."""
+    from orb_slam2_detailed_comments_b200._lib import QUERY_DTYPE
+    c = synth.synth_guided_case(seed, n=n, m=m, stereo=stereo)
+    rng = np.random.default_rng(seed + 99)
+    q = c["queries"]
+    fx, fy, cx, cy = (np.float32(v) for v in CAM)
+    u = (np.round(q["u"] * 4) / 4).astype(np.float32)
+    v = (np.round(q["v"] * 4) / 4).astype(np.float32)
+    z = rng.choice(np.array([0.5, 1.0, 2.0, 4.0, -1.0], np.float32), m, p=[0.2, 0.3, 0.25, 0.2, 0.05])
+    pts = np.zeros(m, ref_binary.FUSE_DTYPE)
+    pts["X"], pts["Y"], pts["Z"] = (u - cx) / fx * z, (v - cy) / fy * z, z
+    pts["nz"] = np.where(rng.random(m) < 0.05, -1.0, 1.0)           # a normal pointing away fails PO.dot(Pn) < 0.5 * dist3D (:1153)
+    pts["level"] = np.clip(q["max_level"], 0, 7)
+    pts["flags"] = (rng.random(m) < 0.04) * 1 + (rng.random(m) < 0.04) * 2 + (rng.random(m) < 0.04) * 4
+    ok = z > 0
+    invz = (np.float32(1.0) / z).astype(np.float32)                  # const float invz = 1 / p3Dc.at<float>(2)
+    uu = fx * (pts["X"] * invz) + cx
+    vv = fy * (pts["Y"] * invz) + cy
+    assert np.array_equal(uu[ok], u[ok]) and np.array_equal(vv[ok], v[ok])
+    mnx, mny, mxx, mxy = (np.float32(b) for b in c["bounds"])
+    in_image = (uu >= mnx) & (uu < mxx) & (vv >= mny) & (vv < mxy)   # KeyFrame::IsInImage (src/KeyFrame.cc:926-929)
+    skip = (pts["flags"] != 0) | (z < 0) | ~in_image | (pts["nz"] < 0)
+    q2 = np.zeros(m, QUERY_DTYPE)
+    q2["u"], q2["v"] = uu, vv
+    q2["radius"] = (np.float32(th) * SCALE[pts["level"]]).astype(np.float32)
+    q2["ur"] = uu - np.float32(mbf) * invz
+    q2["min_level"], q2["max_level"] = pts["level"] - 1, pts["level"]
+    q2["flags"] = np.where(skip, 1, 0)
+    inv_sigma2 = (np.float32(1.0) / (SCALE * SCALE)).astype(np.float32)
+    return c, pts, q2, inv_sigma2, dict(th=th, mbf=mbf)
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,stereo,th", [(1, True, 3.0), (2, False, 3.0), (3, True, 6.0)])
+def test_fuse_equals_reference(oracle, seed, stereo, th):
+    """oracle.fuse_search == the candidate loop of the reference's own Fuse(pKF, vpMapPoints, th) over KeyFrame::GetFeaturesInArea: level window
+    [predicted - 1, predicted], chi-square gates 7.8 (stereo keypoints) / 5.99 (monocular) with mvInvLevelSigma2, best at TH_LOW."""
+    c, pts, q2, inv_sigma2, p = _fuse_case(seed, stereo=stereo, th=th)
+    held = c["claimed"]
+    nf_ref, best_ref = ref_binary.ref_fuse(c["kps"], c["desc"], c["uright"], held, c["bounds"], SCALE, inv_sigma2, th, CAM, p["mbf"], pts, c["qdesc"])
+    bi, bd = oracle.fuse_search(c["kps"], c["desc"], q2, c["qdesc"], c["bounds"], th_dist=50, uright=c["uright"], inv_level_sigma2=inv_sigma2)
+    assert int((bi >= 0).sum()) == nf_ref and nf_ref > 60, (int((bi >= 0).sum()), nf_ref)
+    assert np.array_equal(bi, best_ref), f"bestIdx differs at points {np.flatnonzero(bi != best_ref)[:10]}"
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cuda_fuse_equals_reference():
+    from orb_slam2_detailed_comments_b200.matcher import ORBmatcher
+    for seed, stereo, th in ((31, True, 3.0), (32, False, 4.0)):
+        c, pts, q2, inv_sigma2, p = _fuse_case(seed, stereo=stereo, th=th)
+        nf_ref, best_ref = ref_binary.ref_fuse(c["kps"], c["desc"], c["uright"], c["claimed"], c["bounds"], SCALE, inv_sigma2, th, CAM, p["mbf"], pts,
+                                               c["qdesc"])
+        n, m = len(c["kps"]), len(q2)
+        bi, bd = ORBmatcher().FuseSearch(c["kps"][None], c["desc"][None], np.array([n], np.int32), q2[None], c["qdesc"][None], np.array([m], np.int32),
+                                         c["bounds"], uright=None if c["uright"] is None else c["uright"][None], inv_level_sigma2=inv_sigma2)
+        assert int((bi[0] >= 0).sum()) == nf_ref and np.array_equal(bi[0], best_ref), (seed, nf_ref)
+
+
 @needs_ref
 @pytest.mark.gpu
 def test_cuda_search_by_projection_equals_reference():
