@@ -116,7 +116,7 @@ class KeyFrame {       // include/KeyFrame.h: what SearchByBoW and Fuse read
   cv::Mat Rcw, tcw, Ow;
   int N = 0, mnGridCols = FRAME_GRID_COLS, mnGridRows = FRAME_GRID_ROWS;
   float fx, fy, cx, cy, mbf, mnMinX, mnMinY, mnMaxX, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
-  std::vector<float> mvScaleFactors, mvInvLevelSigma2, mvuRight;
+  std::vector<float> mvScaleFactors, mvInvLevelSigma2, mvLevelSigma2, mvuRight;
   std::vector<std::vector<std::vector<size_t>>> mGrid;
   DBoW2::FeatureVector mFeatVec;
   cv::Mat mDescriptors;
@@ -137,6 +137,8 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
   int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12);
   int Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th = 3.0);
+  bool CheckDistEpipolarLine(const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const cv::Mat& F12, const KeyFrame* pKF);
+  int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, vector<pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo);
   int SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12, int windowSize = 10);
   float RadiusByViewingCos(const float& viewCos);
   // harness entry points around the extracted loop bodies (declared here so the bodies see the members unqualified)
@@ -160,6 +162,8 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
 #include "_ref/gen_sbow2.inc"
 #include "_ref/gen_kfarea.inc"
 #include "_ref/gen_fuse.inc"
+#include "_ref/gen_epiline.inc"
+#include "_ref/gen_stri.inc"
 
 struct FrameDescs { cv::Mat mDescriptors; };
 
@@ -524,6 +528,49 @@ int main(int argc, char** argv) {
     ORB_SLAM2::ORBmatcher matcher(0.6f, true);
     out.push_back(matcher.Fuse(&KF, vp, th));
     for (int i = 0; i < m; ++i) out.push_back(pts[i].fusedIdx);
+  } else if (mode == "stri") {
+    // ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) + CheckDistEpipolarLine (src/ORBmatcher.cc:879-1088, 206-233).
+    // int onlyStereo, checkOri, nlevels; nlevels x float scale; nlevels x float levelSigma2; 9 x float F12 (row-major); 3 x float Cw (camera centre of
+    // keyframe 1); 4 x float fx, fy, cx, cy of keyframe 2 (pose of keyframe 2 = identity); twice {int n; n x 32 B; n x KeyPoint (mvKeysUn); n x u8 "holds a
+    // map point"; n x float mvuRight; FeatureVector}  ->  int nmatches; n1 x int32 vMatches12 (from vMatchedPairs)
+    const int only_stereo = r.get<int32_t>(), ori = r.get<int32_t>(), nl = r.get<int32_t>();
+    ORB_SLAM2::KeyFrame K[2];
+    for (int l = 0; l < nl; ++l) K[1].mvScaleFactors.push_back(r.get<float>());
+    for (int l = 0; l < nl; ++l) K[1].mvLevelSigma2.push_back(r.get<float>());
+    cv::Mat F12(3, 3, CV_32F);
+    for (int y = 0; y < 3; ++y) for (int x = 0; x < 3; ++x) F12.at<float>(y, x) = r.get<float>();
+    K[0].Ow = cv::Mat(3, 1, CV_32F);
+    for (int k = 0; k < 3; ++k) K[0].Ow.at<float>(k) = r.get<float>();
+    K[1].fx = r.get<float>(); K[1].fy = r.get<float>(); K[1].cx = r.get<float>(); K[1].cy = r.get<float>();
+    K[1].Rcw = cv::Mat(3, 3, CV_32F); K[1].tcw = cv::Mat(3, 1, CV_32F);
+    for (int y = 0; y < 3; ++y) { for (int x = 0; x < 3; ++x) K[1].Rcw.at<float>(y, x) = y == x ? 1.f : 0.f; K[1].tcw.at<float>(y) = 0.f; }
+    ORB_SLAM2::MapPoint held;
+    for (int k = 0; k < 2; ++k) {
+      const int n = r.get<int32_t>();
+      K[k].N = n;
+      K[k].mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+      K[k].mvKeysUn.resize(n);
+      std::memcpy(K[k].mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+      const uint8_t* has = r.bytes(n);
+      K[k].mvpMapPoints.assign(n, nullptr);
+      for (int i = 0; i < n; ++i) if (has[i]) K[k].mvpMapPoints[i] = &held;
+      K[k].mvuRight.resize(n);
+      std::memcpy(K[k].mvuRight.data(), r.bytes((size_t)n * 4), (size_t)n * 4);
+      const int cnt = r.get<int32_t>();
+      for (int j = 0; j < cnt; ++j) {
+        const uint32_t node = r.get<uint32_t>();
+        const int mm = r.get<int32_t>();
+        std::vector<unsigned int>& v = K[k].mFeatVec[node];
+        for (int q = 0; q < mm; ++q) v.push_back(r.get<uint32_t>());
+      }
+    }
+    ORB_SLAM2::g_cur_point = nullptr;
+    ORB_SLAM2::ORBmatcher matcher(0.6f, ori != 0);
+    std::vector<std::pair<size_t, size_t>> pairs;
+    out.push_back(matcher.SearchForTriangulation(&K[0], &K[1], F12, pairs, only_stereo != 0));
+    std::vector<int32_t> m12(K[0].N, -1);
+    for (const auto& pr : pairs) m12[pr.first] = (int32_t)pr.second;
+    out.insert(out.end(), m12.begin(), m12.end());
   } else if (mode == "sinit") {
     // float bounds[4], nnratio; int checkOri, windowSize; F2: int n; n x KeyPoint (mvKeysUn); n x 32 B; F1: int m; m x KeyPoint (mvKeysUn: octave,
     // angle); m x 32 B; m x {float x, y} vbPrevMatched  ->  int nmatches; m x int32 vnMatches12

@@ -265,6 +265,20 @@ def ref_fuse(kps_un, desc, uright, held, bounds, scale, inv_sigma2, th, cam, mbf
     return int(out[0]), out[1:1 + m].copy()
 
 
+def ref_search_for_triangulation(desc1, kps1_un, has1, ur1, fv1: dict, desc2, kps2_un, has2, ur2, fv2: dict, f12, cw, cam2, level_sigma2, scale, only_stereo,
+                                 check_orientation):
+    """ORBmatcher::SearchForTriangulation + CheckDistEpipolarLine (src/ORBmatcher.cc:879-1088, 206-233); keyframe 2 has the identity pose, cw = camera
+    centre of keyframe 1 (the reference derives the epipole from it). Returns (nmatches, vMatches12 [n1])."""
+    payload = struct.pack("<3i", int(only_stereo), int(check_orientation), len(scale))
+    payload += np.ascontiguousarray(scale, "<f4").tobytes() + np.ascontiguousarray(level_sigma2, "<f4")[:len(scale)].tobytes()
+    payload += np.ascontiguousarray(f12, "<f4").reshape(9).tobytes() + np.ascontiguousarray(cw, "<f4").tobytes() + np.ascontiguousarray(cam2, "<f4").tobytes()
+    for d, k, h, u, fv in ((desc1, kps1_un, has1, ur1, fv1), (desc2, kps2_un, has2, ur2, fv2)):
+        payload += struct.pack("<i", len(k)) + np.ascontiguousarray(d, np.uint8).tobytes() + np.ascontiguousarray(k).tobytes()
+        payload += np.ascontiguousarray(h, np.uint8).tobytes() + np.ascontiguousarray(u, "<f4").tobytes() + _fv_bytes(fv)
+    out = np.frombuffer(_run_match("stri", payload), "<i4")
+    return int(out[0]), out[1:1 + len(kps1_un)].copy()
+
+
 def ref_search_for_initialization(kps2_un, desc2, kps1_un, desc1, prev_matched, bounds, nnratio, check_orientation, window):
     """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) on F2's reference-built grid.
     Returns (nmatches, vnMatches12 [m])."""

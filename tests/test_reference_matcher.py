@@ -464,6 +464,30 @@ def test_cuda_fuse_equals_reference():
 
 
 @needs_ref
+@pytest.mark.parametrize("seed,ori,only_stereo,general_f,wide", [(1, True, False, False, False), (2, False, False, True, False), (3, True, True, False, False),
+                                                                   (4, True, False, True, True)])
+def test_search_for_triangulation_equals_reference(oracle, seed, ori, only_stereo, general_f, wide):
+    """oracle.search_for_triangulation == the reference's own SearchForTriangulation + CheckDistEpipolarLine: FeatureVector walk, map-point / stereo
+    skips, `dist > TH_LOW || dist > bestDist` (the later of equal distances wins), epipole exclusion for monocular pairs, the float32 epipolar distance
+    against 3.84 * mvLevelSigma2, this fork's vbMatched2 bookkeeping (set on accept, cleared by the orientation filter), rotation histogram."""
+    import test_search_triangulation as tt
+    voc = synth.synth_vocabulary(10, 3, seed=11)
+    ov = oracle.OracleVocabulary(*voc)
+    d1, k1, has1, ur1, d2, k2, has2, ur2, epi = tt._pair(voc, seed, 320, 350, general_f=general_f, wide=wide)
+    fv1, fv2 = ov.transform(d1, 2)[3], ov.transform(d2, 2)[3]
+    fx, fy, cx, cy = (np.float32(v) for v in CAM)
+    z = np.float32(2.0)
+    cw = np.array([(epi["ex"] - cx) / fx * z, (epi["ey"] - cy) / fy * z, z], np.float32)
+    assert fx * cw[0] * (np.float32(1.0) / z) + cx == epi["ex"] and fy * cw[1] * (np.float32(1.0) / z) + cy == epi["ey"]   # the reference's expression, exact here
+    nm_ref, m12_ref = ref_binary.ref_search_for_triangulation(d1, k1, has1, ur1, fv1, d2, k2, has2, ur2, fv2, epi["f12"], cw, CAM, epi["level_sigma2"],
+                                                              epi["scale_factor"][:8], only_stereo, ori)
+    got = oracle.search_for_triangulation(d1, k1, has1, ur1, tt._csr(fv1, len(d1)), d2, k2, has2, ur2, tt._csr(fv2, len(d2)), epi["f12"], epi["ex"],
+                                          epi["ey"], epi["level_sigma2"], epi["scale_factor"], only_stereo, 50, ori)
+    assert got[1] == nm_ref and nm_ref > (5 if only_stereo else 25), (got[1], nm_ref)
+    assert np.array_equal(got[0], m12_ref)
+
+
+@needs_ref
 @pytest.mark.gpu
 def test_cuda_search_by_projection_equals_reference():
     from orb_slam2_detailed_comments_b200.matcher import ORBmatcher
