@@ -186,6 +186,12 @@ inline Mat Mat::t() const {
   return m;
 }
 inline Mat operator-(const Mat& a) { return -1.f * a; }
+inline Mat operator/(const Mat& a, float k) {   // MatExpr scale by 1 / k: cv computes a * (1.0 / k) in double and rounds once; exact for k = 1 (the pins)
+  assert(a.type() == CV_32F);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = (float)((double)a.at<float>(y, x) * (1.0 / (double)k));
+  return m;
+}
 inline Mat operator+(const Mat& a, const Mat& b) {
   assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
   Mat m(a.rows, a.cols, CV_32F);

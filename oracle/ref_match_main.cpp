@@ -106,6 +106,7 @@ class Frame {          // include/Frame.h: the members src/Frame.cc:880-1176, 43
 class KeyFrame {       // include/KeyFrame.h: what SearchByBoW and Fuse read
  public:
   std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
+  std::set<MapPoint*> GetMapPoints() { std::set<MapPoint*> s; for (MapPoint* p : mvpMapPoints) if (p) s.insert(p); return s; }   // src/KeyFrame.cc:548-563 without isBad (stub points are good)
   cv::Mat GetRotation() { return Rcw.clone(); }
   cv::Mat GetTranslation() { return tcw.clone(); }
   cv::Mat GetCameraCenter() { return Ow.clone(); }
@@ -137,6 +138,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
   int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12);
   int Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th = 3.0);
+  int Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, float th, vector<MapPoint*>& vpReplacePoint);
   bool CheckDistEpipolarLine(const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const cv::Mat& F12, const KeyFrame* pKF);
   int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, vector<pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo);
   int SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12, int windowSize = 10);
@@ -162,6 +164,7 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
 #include "_ref/gen_sbow2.inc"
 #include "_ref/gen_kfarea.inc"
 #include "_ref/gen_fuse.inc"
+#include "_ref/gen_fuse2.inc"
 #include "_ref/gen_epiline.inc"
 #include "_ref/gen_stri.inc"
 
@@ -471,7 +474,9 @@ int main(int argc, char** argv) {
     std::vector<ORB_SLAM2::MapPoint*> matches;
     out.push_back(matcher.SearchByBoW(&K[0], &K[1], matches));
     for (size_t i = 0; i < matches.size(); ++i) out.push_back(matches[i] ? (int32_t)(matches[i] - pts[1].data()) : -1);
-  } else if (mode == "fuse") {
+  } else if (mode == "fuse" || mode == "fuse2") {
+    // fuse2: Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1282-1421) with Scw = identity; flag 4 = the point is one of the keyframe's own
+    // map points (spAlreadyFound), flag 1 is not used (the reference dereferences every entry).
     // ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1100-1270) with KeyFrame::GetFeaturesInArea / IsInImage (src/KeyFrame.cc:879-929) on a grid
     // built by Frame::AssignFeaturesToGrid and copied as the KeyFrame constructor does (src/KeyFrame.cc:85-92). Pose = identity, camera centre = 0.
     // float bounds[4], th, mbf, fx, fy, cx, cy; int nlevels; nlevels x float scale; nlevels x float invLevelSigma2; int n; n x KeyPoint; n x 32 B;
@@ -526,7 +531,16 @@ int main(int argc, char** argv) {
     }
     for (int i = 0; i < m; ++i) pts[i].mDescriptor = mat_u8(r.bytes(32), 1, 32);
     ORB_SLAM2::ORBmatcher matcher(0.6f, true);
-    out.push_back(matcher.Fuse(&KF, vp, th));
+    if (mode == "fuse") {
+      out.push_back(matcher.Fuse(&KF, vp, th));
+    } else {
+      for (int i = 0, slot = 0; i < m; ++i)   // points the keyframe already holds sit in slots that hold a map point
+        if (pts[i].inKF) { while (slot < n && !cl[slot]) ++slot; if (slot < n) KF.mvpMapPoints[slot++] = &pts[i]; }
+      cv::Mat Scw(4, 4, CV_32F);
+      for (int y = 0; y < 4; ++y) for (int x = 0; x < 4; ++x) Scw.at<float>(y, x) = y == x ? 1.f : 0.f;
+      std::vector<ORB_SLAM2::MapPoint*> repl(m, nullptr);
+      out.push_back(matcher.Fuse(&KF, Scw, vp, th, repl));
+    }
     for (int i = 0; i < m; ++i) out.push_back(pts[i].fusedIdx);
   } else if (mode == "stri") {
     // ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) + CheckDistEpipolarLine (src/ORBmatcher.cc:879-1088, 206-233).

@@ -249,9 +249,10 @@ def ref_search_by_bow_keyframes(desc1, kps1_un, valid1, fv1: dict, desc2, kps2_u
 FUSE_DTYPE = np.dtype([("X", "<f4"), ("Y", "<f4"), ("Z", "<f4"), ("nz", "<f4"), ("level", "<i4"), ("flags", "<i4")])
 
 
-def ref_fuse(kps_un, desc, uright, held, bounds, scale, inv_sigma2, th, cam, mbf, points, qdesc):
+def ref_fuse(kps_un, desc, uright, held, bounds, scale, inv_sigma2, th, cam, mbf, points, qdesc, sim3_form=False):
     """ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1100-1270) on a keyframe with identity pose. points: FUSE_DTYPE (world point, z of the
-    viewing normal (0, 0, nz), PredictScale result, flags 1 = null, 2 = isBad(), 4 = IsInKeyFrame(pKF)). Returns (nFused, bestIdx [m], -1 = not fused)."""
+    viewing normal (0, 0, nz), PredictScale result, flags 1 = null, 2 = isBad(), 4 = IsInKeyFrame(pKF)). Returns (nFused, bestIdx [m], -1 = not fused).
+    sim3_form: Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1282-1419) with Scw = identity instead (flag 4 = among the keyframe's own map points)."""
     n, m = len(kps_un), len(points)
     kps_un = np.ascontiguousarray(kps_un)
     assert kps_un.dtype.itemsize == 28 and points.dtype == FUSE_DTYPE
@@ -261,7 +262,7 @@ def ref_fuse(kps_un, desc, uright, held, bounds, scale, inv_sigma2, th, cam, mbf
     payload += np.ascontiguousarray(uright if uright is not None else np.full(n, -1, np.float32), "<f4").tobytes()
     payload += np.ascontiguousarray(held if held is not None else np.zeros(n, np.uint8), np.uint8).tobytes()
     payload += struct.pack("<i", m) + np.ascontiguousarray(points).tobytes() + np.ascontiguousarray(qdesc, np.uint8).tobytes()
-    out = np.frombuffer(_run_match("fuse", payload), "<i4")
+    out = np.frombuffer(_run_match("fuse2" if sim3_form else "fuse", payload), "<i4")
     return int(out[0]), out[1:1 + m].copy()
 
 

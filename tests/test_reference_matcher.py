@@ -402,7 +402,7 @@ def test_search_by_bow_keyframes_equals_reference(oracle, seed, ori, ratio):
     assert np.array_equal(got[2], m12_ref)
 
 
-def _fuse_case(seed, n=900, m=800, stereo=True, th=3.0, mbf=40.0):
+def _fuse_case(seed, n=900, m=800, stereo=True, th=3.0, mbf=40.0, null_points=True):
     """Inputs of Fuse(pKF, vpMapPoints, th) and the query records the host derives from them (src/ORBmatcher.cc:1117-1166): projection exact by
     construction (identity pose, power-of-two depths, u / v with two fractional bits), PredictScale and the viewing checks are host-side values."""
     from orb_slam2_detailed_comments_b200._lib import QUERY_DTYPE
@@ -417,7 +417,7 @@ def _fuse_case(seed, n=900, m=800, stereo=True, th=3.0, mbf=40.0):
     pts["X"], pts["Y"], pts["Z"] = (u - cx) / fx * z, (v - cy) / fy * z, z
     pts["nz"] = np.where(rng.random(m) < 0.05, -1.0, 1.0)           # a normal pointing away fails PO.dot(Pn) < 0.5 * dist3D (:1153)
     pts["level"] = np.clip(q["max_level"], 0, 7)
-    pts["flags"] = (rng.random(m) < 0.04) * 1 + (rng.random(m) < 0.04) * 2 + (rng.random(m) < 0.04) * 4
+    pts["flags"] = (rng.random(m) < 0.04) * (1 if null_points else 0) + (rng.random(m) < 0.04) * 2 + (rng.random(m) < 0.04) * 4
     ok = z > 0
     invz = (np.float32(1.0) / z).astype(np.float32)                  # const float invz = 1 / p3Dc.at<float>(2)
     uu = fx * (pts["X"] * invz) + cx
@@ -445,6 +445,21 @@ def test_fuse_equals_reference(oracle, seed, stereo, th):
     held = c["claimed"]
     nf_ref, best_ref = ref_binary.ref_fuse(c["kps"], c["desc"], c["uright"], held, c["bounds"], SCALE, inv_sigma2, th, CAM, p["mbf"], pts, c["qdesc"])
     bi, bd = oracle.fuse_search(c["kps"], c["desc"], q2, c["qdesc"], c["bounds"], th_dist=50, uright=c["uright"], inv_level_sigma2=inv_sigma2)
+    assert int((bi >= 0).sum()) == nf_ref and nf_ref > 60, (int((bi >= 0).sum()), nf_ref)
+    assert np.array_equal(bi, best_ref), f"bestIdx differs at points {np.flatnonzero(bi != best_ref)[:10]}"
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,stereo,th", [(4, True, 4.0), (5, False, 3.0)])
+def test_fuse_sim3_form_equals_reference(oracle, seed, stereo, th):
+    """The loop-closing form Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (Scw = identity: scale 1): same candidate loop without the chi-square gates,
+    INT_MAX sentinel, spAlreadyFound skip == oracle.fuse_search without inv_level_sigma2."""
+    c, pts, q2, inv_sigma2, p = _fuse_case(seed, stereo=stereo, th=th, null_points=False)   # this form dereferences every entry
+    held = c["claimed"].copy()
+    held[:64] = 1                                          # enough occupied slots for the points the keyframe already holds
+    nf_ref, best_ref = ref_binary.ref_fuse(c["kps"], c["desc"], c["uright"], held, c["bounds"], SCALE, inv_sigma2, th, CAM, p["mbf"], pts, c["qdesc"],
+                                           sim3_form=True)
+    bi, bd = oracle.fuse_search(c["kps"], c["desc"], q2, c["qdesc"], c["bounds"], th_dist=50, uright=c["uright"], inv_level_sigma2=None)
     assert int((bi >= 0).sum()) == nf_ref and nf_ref > 60, (int((bi >= 0).sum()), nf_ref)
     assert np.array_equal(bi, best_ref), f"bestIdx differs at points {np.flatnonzero(bi != best_ref)[:10]}"
 
