@@ -16,6 +16,7 @@
  *                                                                                     include/ORBmatcher.h:62, src/ORBmatcher.cc:2073-2093, 304-342
  *   orb_hamming_knn_noalloc   <- (new, no reference counterpart) orb_hamming_knn without any allocation: fixed device scratch
  *   orb_hamming_knn_sharded   <- (new) the 8-GPU database scan of config C4 behind one call: shard scan + ncclAllGather + merge
+ *   orb_hamming_knn_peer      <- (new) the same scan with the exchange INSIDE the kernel: peer stores over NVLink instead of NCCL
  *   orb_hamming_knn_merge     <- (new) top-2 merge of per-shard results, order-equivalent to one sequential scan
  *   orb_descriptor_distance_batch <- DescriptorDistance over N row pairs (e.g. src/Frame.cc:1009, src/MapPoint.cc:484)
  *   orb_search_for_initialization <- ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)   src/ORBmatcher.cc:570-712
@@ -224,6 +225,27 @@ int orb_hamming_knn_sharded(const uint8_t* query, int q_mem, int Q, const uint8_
 int orb_nccl_unique_id(uint8_t* id128);
 int orb_nccl_comm_create(const uint8_t* id128, int nranks, int rank, void** comm);
 void orb_nccl_comm_destroy(void* comm);
+/* The sharded scan with the exchange fused into the reduction kernel (no NCCL, no collective launch): every rank owns a mailbox in device memory
+ * that the other ranks of the node open with CUDA IPC; the kernel that reduces a rank's per-chunk keys stores its two best keys per query straight
+ * into every peer's mailbox over NVLink, publishes an epoch flag, waits for the peers' flags in its own mailbox and merges. Same results as
+ * orb_hamming_knn_sharded (the two lexicographically smallest (distance, global row) over all shards).
+ *   orb_knn_peer_create   on the caller's CURRENT device; one process per GPU, 1 <= nranks <= ORB_KNN_PEER_MAX_RANKS, every call of the group has Q <= max_q;
+ *   orb_knn_peer_export   64 bytes (cudaIpcMemHandle_t) to hand to the other ranks by any means (all-gather over torch.distributed / MPI / files);
+ *   orb_knn_peer_connect  handles = nranks x 64 bytes in rank order (this rank's own entry is ignored); needs peer access between the GPUs (NVLink or PCIe P2P);
+ *   orb_hamming_knn_peer  collective: every rank calls it with the same Q, in the same order of calls. Buffers as orb_hamming_knn_sharded.
+ *                         A peer that never makes the matching call turns into ORB_E_CAPACITY (flag 32) after a bounded wait, reported by the next
+ *                         synchronising call (orb_knn_peer_check, or this call itself when a host buffer makes it synchronous).
+ *   orb_knn_peer_check    synchronises `stream` and returns ORB_E_CAPACITY if a wait timed out since the last check. */
+#define ORB_KNN_PEER_MAX_RANKS 16
+#define ORB_KNN_PEER_HANDLE_BYTES 64
+typedef struct orb_knn_peer orb_knn_peer;
+int orb_knn_peer_create(int rank, int nranks, int max_q, orb_knn_peer** out);
+int orb_knn_peer_export(orb_knn_peer* p, uint8_t* handle64);
+int orb_knn_peer_connect(orb_knn_peer* p, const uint8_t* handles);
+int orb_hamming_knn_peer(orb_knn_peer* p, const uint8_t* query, int q_mem, int Q, const uint8_t* db_shard, int db_mem, int64_t D_shard,
+                         int64_t index_base, int sentinel, orb_knn2* out, int out_mem, void* stream);
+int orb_knn_peer_check(orb_knn_peer* p, void* stream);
+void orb_knn_peer_destroy(orb_knn_peer* p);
 /* DescriptorDistance for n row pairs: out[i] = popcount(a[i] ^ b[i]); all device memory. */
 int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream);
 /* Same with HOST buffers (copies inside the call, default stream, synchronous). */

@@ -37,7 +37,7 @@ SYMBOLS = [
     "orb_extractor_raw_keypoints", "orb_extractor_stream", "orb_extractor_launch_count",
     "orb_extractor_check", "orb_extractor_pyramid_read_all", "orb_extractor_set_pyramid_download", "orb_host_alloc", "orb_host_free",
     "orb_extractor_set_profiling", "orb_extractor_stage_times", "orb_hamming_knn", "orb_hamming_knn_noalloc",
-    "orb_hamming_knn_merge", "orb_hamming_knn_sharded", "orb_nccl_unique_id", "orb_nccl_comm_create", "orb_nccl_comm_destroy", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
+    "orb_hamming_knn_merge", "orb_hamming_knn_sharded", "orb_knn_peer_create", "orb_knn_peer_export", "orb_knn_peer_connect", "orb_hamming_knn_peer", "orb_knn_peer_check", "orb_knn_peer_destroy", "orb_nccl_unique_id", "orb_nccl_comm_create", "orb_nccl_comm_destroy", "orb_descriptor_distance_batch", "orb_descriptor_distance_host", "orb_matcher_launch_count", "orb_measure_popc_peak",
     "orb_search_by_projection", "orb_distinctive_descriptors",
     "orb_vocabulary_create", "orb_vocabulary_destroy", "orb_vocabulary_words", "orb_bow_transform",
     "orb_undistort_keypoints", "orb_image_bounds", "orb_search_by_bow", "orb_search_for_initialization",
@@ -117,6 +117,13 @@ def lib():
     L.orb_hamming_knn_merge.argtypes = [vp, i32, i32, i32, vp, vp]
     L.orb_hamming_knn_noalloc.argtypes = [vp, i32, vp, i64, i64, i32, vp, vp]
     L.orb_hamming_knn_sharded.argtypes = [vp, i32, i32, vp, i32, i64, i64, i32, vp, i32, vp, vp]
+    L.orb_knn_peer_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
+    L.orb_knn_peer_export.argtypes = [vp, vp]
+    L.orb_knn_peer_connect.argtypes = [vp, vp]
+    L.orb_hamming_knn_peer.argtypes = [vp, vp, i32, i32, vp, i32, i64, i64, i32, vp, i32, vp]
+    L.orb_knn_peer_check.argtypes = [vp, vp]
+    L.orb_knn_peer_destroy.argtypes = [vp]
+    L.orb_knn_peer_destroy.restype = None
     L.orb_nccl_unique_id.argtypes = [vp]
     L.orb_nccl_comm_create.argtypes = [vp, i32, i32, C.POINTER(vp)]
     L.orb_nccl_comm_destroy.argtypes = [vp]

@@ -233,6 +233,94 @@ void orb_launch_knn(const uint8_t* q, int Q, const uint8_t* db, long long D, lon
   g_knn_launches += 2;
 }
 
+// ---- sharded scan with the exchange inside the kernel (orb_hamming_knn_peer) -------------------------------------------------------------------
+// ONE kernel = reduction of this rank's per-chunk keys + all-gather + merge, the gather done by plain stores into every peer's mailbox over
+// NVLink (the mailboxes are cudaMalloc'ed by each rank and opened in the others with CUDA IPC):
+//   1. thread = query: the two smallest packed keys (distance << 40 | GLOBAL row) of this rank's shard, written as one 16-byte store into slot
+//      [parity][my rank][query] of EVERY rank's mailbox (its own included);
+//   2. __threadfence_system(), a ticket per CTA; the CTA that draws the last ticket publishes: flag[my rank] = epoch in every mailbox
+//      (st.release.sys);
+//   3. every CTA waits until all flags of its OWN mailbox have reached the epoch (ld.acquire.sys on local memory; bounded: a missing peer becomes
+//      an error flag, not a hang), then merges the nranks slots of each query (L1-bypassing loads) and emits the record.
+// The grid is (Q + 127) / 128 CTAs, far below one wave, so every CTA is resident and the in-kernel wait cannot starve a publisher. Slots are
+// double-buffered by the parity of the epoch: a rank can only be one call ahead of the slowest peer (it needs that peer's flag of the current
+// call), so the buffer it overwrites two calls later has been read by everybody.
+struct OrbPeerBox {
+  unsigned long long* slots[ORB_KNN_PEER_MAX_RANKS];   // mailbox of rank r: [2][nranks][max_q] x 2 keys
+  unsigned* flags[ORB_KNN_PEER_MAX_RANKS];              // mailbox of rank r: [nranks] epochs
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(128)
+orb_knn_peer_kernel(const unsigned long long* __restrict__ partial, int nchunks, int Q, int sentinel, const __grid_constant__ OrbPeerBox box,
+                    int my_rank, int nranks, int max_q, unsigned epoch, unsigned* __restrict__ ticket, OrbKnn2* __restrict__ out,
+                    int* __restrict__ err_flag) {
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned par = epoch & 1u;
+  // 1. this rank's two best keys -> every mailbox
+  if (qi < Q) {
+    unsigned long long a = ~0ull, b = ~0ull;
+    for (int c = 0; c < nchunks; ++c) {
+      const unsigned long long* p = partial + ((long long)c * Q + qi) * 2;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const unsigned long long k = p[j];
+        b = min(b, max(a, k));
+        a = min(a, k);
+      }
+    }
+    const size_t slot = (((size_t)par * nranks + my_rank) * max_q + qi) * 2;
+    for (int r = 0; r < nranks; ++r) *reinterpret_cast<ulonglong2*>(box.slots[r] + slot) = make_ulonglong2(a, b);
+  }
+  // 2. publish once every CTA of this rank has written
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+      *ticket = 0u;                     // every CTA has drawn: ready for the next call
+      __threadfence_system();
+      for (int r = 0; r < nranks; ++r) st_release_sys(box.flags[r] + my_rank, epoch);
+    }
+  }
+  // 3. wait for all ranks' flags in MY mailbox, merge
+  if (threadIdx.x < nranks) {
+    const unsigned* f = box.flags[my_rank] + threadIdx.x;
+    long long spins = 0;
+    while ((int)(ld_acquire_sys(f) - epoch) < 0) {
+      if (++spins > (1ll << 26)) { atomicOr(err_flag, 32); break; }   // seconds: a peer that never called
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+  if (qi >= Q) return;
+  unsigned long long a = ~0ull, b = ~0ull;
+  const unsigned long long* mine = box.slots[my_rank] + (size_t)par * nranks * max_q * 2;
+  for (int r = 0; r < nranks; ++r) {
+    const ulonglong2 e = __ldcg(reinterpret_cast<const ulonglong2*>(mine + ((size_t)r * max_q + qi) * 2));   // written by a peer: not through L1
+    b = min(b, max(a, e.x)); a = min(a, e.x);
+    b = min(b, max(a, e.y)); a = min(a, e.y);
+  }
+  knn_emit(a, b, sentinel, out + qi);
+}
+
+void orb_launch_knn_peer(const uint8_t* q, int Q, const uint8_t* db, long long D, long long index_base, int sentinel, unsigned long long* partial,
+                         int nchunks, const void* box, int my_rank, int nranks, int max_q, unsigned epoch, unsigned* ticket, OrbKnn2* out,
+                         int* err_flag, cudaStream_t st) {
+  const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+  long long rows = (D + nchunks - 1) / nchunks;
+  rows = (rows + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+  orb_knn_kernel<<<dim3(qtiles, nchunks), KNN_THREADS, 0, st>>>((const uint4*)q, Q, (const uint4*)db, D, rows, index_base, partial);
+  orb_knn_peer_kernel<<<(Q + 127) / 128, 128, 0, st>>>(partial, nchunks, Q, sentinel, *reinterpret_cast<const OrbPeerBox*>(box), my_rank, nranks,
+                                                      max_q, epoch, ticket, out, err_flag);
+  g_knn_launches += 2;
+}
+
 void orb_launch_knn_merge_shards(const OrbKnn2* shards, int nshards, int Q, int sentinel, OrbKnn2* out, cudaStream_t st) {
   orb_knn_merge_shards_kernel<<<(Q + 127) / 128, 128, 0, st>>>(shards, nshards, Q, sentinel, out);
   ++g_knn_launches;

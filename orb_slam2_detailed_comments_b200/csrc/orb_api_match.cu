@@ -211,6 +211,140 @@ int orb_hamming_knn_sharded(const uint8_t* query, int q_mem, int Q, const uint8_
   return ORB_OK;
 }
 
+// ---- sharded scan with peer stores (no NCCL) -------------------------------------------------------------------------------------------------
+// Mailbox of a rank, one cudaMalloc (CUDA IPC exports whole allocations): [256 B: nranks epoch flags][256 B: ticket, error flag][2][nranks][max_q] x 16 B
+struct orb_knn_peer {
+  int device = 0, rank = 0, nranks = 0, max_q = 0;
+  void* box_mem = nullptr;                              // this rank's mailbox
+  void* peer_mem[ORB_KNN_PEER_MAX_RANKS] = {};          // every rank's mailbox as mapped in this process (own entry = box_mem)
+  struct { unsigned long long* slots[ORB_KNN_PEER_MAX_RANKS]; unsigned* flags[ORB_KNN_PEER_MAX_RANKS]; } box = {};
+  unsigned epoch = 0;
+  bool connected = false;
+};
+static size_t peer_box_bytes(int nranks, int max_q) { return 512 + (size_t)2 * nranks * max_q * 16; }
+
+int orb_knn_peer_create(int rank, int nranks, int max_q, orb_knn_peer** out) {
+  if (!out || nranks < 1 || nranks > ORB_KNN_PEER_MAX_RANKS || rank < 0 || rank >= nranks || max_q < 1) return fail(ORB_E_BADARG, "bad argument");
+  *out = nullptr;
+  orb_knn_peer* p = new orb_knn_peer();
+  p->rank = rank; p->nranks = nranks; p->max_q = max_q;
+  if (cudaGetDevice(&p->device) != cudaSuccess) { delete p; cudaGetLastError(); return fail(ORB_E_CUDA, "no CUDA device (there is no CPU fallback)"); }
+  const size_t bytes = peer_box_bytes(nranks, max_q);
+  cudaError_t e = cudaMalloc(&p->box_mem, bytes);
+  if (e == cudaSuccess) e = cudaMemset(p->box_mem, 0, bytes);
+  if (e != cudaSuccess) { if (p->box_mem) cudaFree(p->box_mem); delete p; return fail(ORB_E_CUDA, "mailbox: %s", cudaGetErrorString(e)); }
+  p->peer_mem[rank] = p->box_mem;
+  *out = p;
+  return ORB_OK;
+}
+
+int orb_knn_peer_export(orb_knn_peer* p, uint8_t* handle64) {
+  if (!p || !handle64) return fail(ORB_E_BADARG, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == ORB_KNN_PEER_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+  ORB_ON_DEVICE(p->device);
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, p->box_mem));
+  memcpy(handle64, &h, sizeof(h));
+  return ORB_OK;
+}
+
+int orb_knn_peer_connect(orb_knn_peer* p, const uint8_t* handles) {
+  if (!p || (!handles && p->nranks > 1)) return fail(ORB_E_BADARG, "null argument");
+  if (p->connected) return fail(ORB_E_BADARG, "already connected");
+  ORB_ON_DEVICE(p->device);
+  for (int r = 0; r < p->nranks; ++r) {
+    if (r != p->rank) {
+      cudaIpcMemHandle_t h;
+      memcpy(&h, handles + (size_t)r * ORB_KNN_PEER_HANDLE_BYTES, sizeof(h));
+      cudaError_t e = cudaIpcOpenMemHandle(&p->peer_mem[r], h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) { cudaGetLastError(); return fail(ORB_E_CUDA, "cudaIpcOpenMemHandle(rank %d): %s (peer access between the GPUs is required)", r, cudaGetErrorString(e)); }
+    }
+    p->box.flags[r] = reinterpret_cast<unsigned*>(p->peer_mem[r]);
+    p->box.slots[r] = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(p->peer_mem[r]) + 512);
+  }
+  p->connected = true;
+  return ORB_OK;
+}
+
+static int peer_error(orb_knn_peer* p, cudaStream_t st) {   // stream already synchronised
+  int flag = 0;
+  CU(cudaMemcpyAsync(&flag, static_cast<uint8_t*>(p->box_mem) + 256 + 4, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (flag) {
+    cudaMemsetAsync(static_cast<uint8_t*>(p->box_mem) + 256 + 4, 0, sizeof(int), st);
+    return fail(ORB_E_CAPACITY, "orb_hamming_knn_peer: a peer's flag did not arrive (flags %d: 32 = wait timed out; did every rank make the call?)", flag);
+  }
+  return ORB_OK;
+}
+
+int orb_knn_peer_check(orb_knn_peer* p, void* stream) {
+  if (!p) return fail(ORB_E_BADARG, "null argument");
+  ORB_ON_DEVICE(p->device);
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return peer_error(p, (cudaStream_t)stream);
+}
+
+int orb_hamming_knn_peer(orb_knn_peer* p, const uint8_t* query, int q_mem, int Q, const uint8_t* db_shard, int db_mem, int64_t D_shard,
+                         int64_t index_base, int sentinel, orb_knn2* out, int out_mem, void* stream) {
+  if (!p || !query || !out || Q <= 0 || D_shard < 0 || (D_shard > 0 && !db_shard) || sentinel < 1) return fail(ORB_E_BADARG, "bad argument");
+  if (!p->connected) return fail(ORB_E_BADARG, "orb_knn_peer_connect has not been called");
+  if (Q > p->max_q) return fail(ORB_E_CAPACITY, "Q = %d exceeds the mailbox capacity max_q = %d", Q, p->max_q);
+  if (index_base < 0 || index_base + D_shard >= (1LL << 40)) return fail(ORB_E_BADARG, "index range exceeds 2^40");
+  ORB_ON_DEVICE(p->device);
+  KnnWorkspace* ws;
+  int rc = current_device_ws(&ws);
+  if (rc != ORB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(ws->mu);
+  WsOrder order(&ws->ev_last, st);
+  const uint8_t* dq = query;
+  const uint8_t* ddb = db_shard;
+  orb_knn2* dout = out;
+  const bool any_host = q_mem != ORB_MEM_DEVICE || db_mem != ORB_MEM_DEVICE || out_mem != ORB_MEM_DEVICE;
+  if (q_mem != ORB_MEM_DEVICE || ((uintptr_t)query & 15)) {
+    if ((rc = ws->q.ensure((size_t)Q * 32)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->q.p, query, (size_t)Q * 32, q_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    dq = ws->q.as<uint8_t>();
+  }
+  if (D_shard > 0 && (db_mem != ORB_MEM_DEVICE || ((uintptr_t)db_shard & 15))) {
+    if ((rc = ws->db.ensure((size_t)D_shard * 32)) != ORB_OK) return rc;
+    CU(cudaMemcpyAsync(ws->db.p, db_shard, (size_t)D_shard * 32, db_mem == ORB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    ddb = ws->db.as<uint8_t>();
+  }
+  const size_t rec = (size_t)Q * sizeof(orb_knn2);
+  if (out_mem != ORB_MEM_DEVICE) {
+    if ((rc = ws->out.ensure(rec)) != ORB_OK) return rc;
+    dout = ws->out.as<orb_knn2>();
+  }
+  const int nchunks = orb_knn_num_chunks(Q, D_shard, ws->num_sms);
+  if ((rc = ws->partial.ensure((size_t)nchunks * Q * 2 * sizeof(unsigned long long))) != ORB_OK) return rc;
+  ++p->epoch;   // the same sequence on every rank: the calls are collective
+  uint8_t* mine = static_cast<uint8_t*>(p->box_mem);
+  orb_launch_knn_peer(dq, Q, ddb, D_shard, index_base, sentinel, ws->partial.as<unsigned long long>(), nchunks, &p->box, p->rank, p->nranks, p->max_q,
+                      p->epoch, reinterpret_cast<unsigned*>(mine + 256), (OrbKnn2*)dout, reinterpret_cast<int*>(mine + 256 + 4), st);
+  CU(cudaGetLastError());
+  if (out_mem != ORB_MEM_DEVICE) CU(cudaMemcpyAsync(out, dout, rec, cudaMemcpyDeviceToHost, st));
+  if (any_host) {
+    CU(cudaStreamSynchronize(st));
+    return peer_error(p, st);
+  }
+  return ORB_OK;
+}
+
+void orb_knn_peer_destroy(orb_knn_peer* p) {
+  if (!p) return;
+  int prev = -1;
+  cudaGetDevice(&prev);
+  cudaSetDevice(p->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < p->nranks; ++r)
+    if (r != p->rank && p->peer_mem[r]) cudaIpcCloseMemHandle(p->peer_mem[r]);
+  if (p->box_mem) cudaFree(p->box_mem);
+  if (prev >= 0) cudaSetDevice(prev);
+  cudaGetLastError();
+  delete p;
+}
+
 int orb_descriptor_distance_batch(const uint8_t* a, const uint8_t* b, int64_t n, int32_t* out, void* stream) {
   if (!a || !b || !out || n < 0) return fail(ORB_E_BADARG, "bad argument");
   if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return fail(ORB_E_BADARG, "descriptor arrays must be 16-byte aligned");

@@ -33,6 +33,9 @@ void orb_launch_stereo(const uint8_t*, const OrbKeypoint*, const uint8_t*, const
 int orb_knn_num_chunks(int Q, long long D, int num_sms);
 void orb_launch_knn(const uint8_t*, int, const uint8_t*, long long, long long, int, unsigned long long*, int, OrbKnn2*, cudaStream_t);
 void orb_launch_knn_merge_shards(const OrbKnn2*, int, int, int, OrbKnn2*, cudaStream_t);
+// box: OrbPeerBox (knn.cu) = ORB_KNN_PEER_MAX_RANKS slot pointers followed by as many flag pointers
+void orb_launch_knn_peer(const uint8_t*, int, const uint8_t*, long long, long long, int, unsigned long long*, int, const void* box, int my_rank, int nranks,
+                         int max_q, unsigned epoch, unsigned* ticket, OrbKnn2*, int* err_flag, cudaStream_t);
 void orb_launch_distance_batch(const uint8_t*, const uint8_t*, long long, int*, cudaStream_t);
 long long orb_knn_launches();
 void orb_knn_count_launches(long long n);

@@ -119,6 +119,58 @@ def hamming_knn_sharded(query, db_shard, shard_base: int, group=None, sentinel: 
     return out
 
 
+class KnnPeerGroup:
+    """The sharded scan with the exchange inside the kernel (orb_hamming_knn_peer): every rank's reduction kernel stores its two best keys per query
+    into the peers' mailboxes over NVLink and merges what the peers stored into its own - no NCCL call on the data path. One process per GPU of one
+    node; the mailbox handles (64 bytes per rank) are exchanged once, over `group` (any torch.distributed backend)."""
+
+    def __init__(self, max_q: int, group=None):
+        import torch
+        import torch.distributed as dist
+        self.rank, self.nranks = dist.get_rank(group), dist.get_world_size(group)
+        self._h = C.c_void_p()
+        check(_lib.lib().orb_knn_peer_create(self.rank, self.nranks, int(max_q), C.byref(self._h)))
+        mine = np.zeros(64, np.uint8)
+        check(_lib.lib().orb_knn_peer_export(self._h, mine.ctypes.data_as(C.c_void_p)))
+        backend = dist.get_backend(group)
+        t = torch.from_numpy(mine)
+        if backend == "nccl":
+            t = t.cuda()
+        parts = [torch.empty_like(t) for _ in range(self.nranks)]
+        dist.all_gather(parts, t, group=group)
+        handles = np.ascontiguousarray(np.stack([x.cpu().numpy() for x in parts]))
+        check(_lib.lib().orb_knn_peer_connect(self._h, handles.ctypes.data_as(C.c_void_p)))
+        dist.barrier(group=group)   # every mailbox is open everywhere before the first store
+
+    def knn(self, query, db_shard, shard_base: int, sentinel: int = 256, out=None, stream=None):
+        """Collective. query / db_shard: torch uint8 CUDA tensors; returns out [Q, 3] int64 (orb_knn2 records) as hamming_knn_sharded does."""
+        import torch
+        assert query.is_cuda and db_shard.is_cuda and query.is_contiguous() and db_shard.is_contiguous()
+        Q = query.shape[0]
+        if out is None:
+            out = torch.empty((Q, 3), dtype=torch.int64, device=query.device)
+        st = (stream or torch.cuda.current_stream(query.device)).cuda_stream
+        check(_lib.lib().orb_hamming_knn_peer(self._h, query.data_ptr(), MEM_DEVICE, Q, db_shard.data_ptr(), MEM_DEVICE, db_shard.shape[0], shard_base,
+                                              sentinel, out.data_ptr(), MEM_DEVICE, C.c_void_p(st)))
+        return out
+
+    def check(self, stream=None):
+        import torch
+        st = (stream or torch.cuda.current_stream()).cuda_stream
+        check(_lib.lib().orb_knn_peer_check(self._h, C.c_void_p(st)))
+
+    def close(self):
+        if self._h:
+            _lib.lib().orb_knn_peer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:   # noqa: BLE001
+            pass
+
+
 class ORBmatcher:
     """include/ORBmatcher.h: constructor (nnratio=0.6, checkOri=true) :54, TH_LOW/TH_HIGH/HISTO_LENGTH :223-225."""
     TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30
