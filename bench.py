@@ -593,8 +593,10 @@ def knn_parity(rank, world, out_merged, q, nsample=64):
 
 
 def bench_knn(rank, world, steps, warmup):
-    """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks, one all_gather
-    of the per-query records + device merge when world > 1. pairs/s = Q*D / time (max over ranks)."""
+    """Config C4: 2000 queries x 1M database rows, k=2; database sharded contiguously over ranks. pairs/s = Q*D / time (max over ranks).
+    world > 1: both exchange paths are timed, each behind ONE C-ABI call per rank - orb_hamming_knn_peer (the reduction kernel stores the records
+    into the peers' mailboxes over NVLink and merges: no collective launch) and orb_hamming_knn_sharded (shard scan + ncclAllGather + merge
+    kernel). The faster one with parity true is the reported value; both are listed under `variants`."""
     import torch
     from orb_slam2_detailed_comments_b200 import _lib, matcher
     rng = np.random.RandomState(7)
@@ -604,30 +606,48 @@ def bench_knn(rank, world, steps, warmup):
     gdb = torch.Generator(device="cuda").manual_seed(100 + rank)
     db = torch.randint(0, 256, (per, 32), dtype=torch.uint8, device="cuda", generator=gdb)
     out = torch.empty((KNN_Q, 3), dtype=torch.int64, device="cuda")
-    comm = matcher.nccl_comm_ptr() if world > 1 else None   # torch.distributed's ncclComm_t, handed to the C ABI
 
-    def step():
-        if world > 1:   # shard scan + ncclAllGather + device merge behind ONE C-ABI call (orb_hamming_knn_sharded)
-            matcher.hamming_knn_sharded(q, db, base, out=out, comm=comm)
-        else:
-            matcher.hamming_knn_device(q, db, out=out, index_base=base)
+    def timed(step):
+        for _ in range(max(warmup, 3)):
+            step()
+        l0 = _lib.lib().orb_matcher_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        _barrier(world)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        e1.synchronize()
+        _barrier(world)
+        ms = _max_over_ranks(e0.elapsed_time(e1), world)
+        launches = _lib.lib().orb_matcher_launch_count() - l0
+        return KNN_Q * per * world * steps / (ms * 1e-3), ms / steps, launches, knn_parity(rank, world, out, q)
 
-    for _ in range(max(warmup, 3)):
-        step()
-    l0 = _lib.lib().orb_matcher_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    _barrier(world)
-    e0.record()
-    for _ in range(steps):
-        step()
-    e1.record()
-    e1.synchronize()
-    _barrier(world)
-    ms = _max_over_ranks(e0.elapsed_time(e1), world)
-    launches = _lib.lib().orb_matcher_launch_count() - l0
-    pairs = KNN_Q * per * world * steps
-    parity = knn_parity(rank, world, out, q)
-    return pairs / (ms * 1e-3), ms / steps, launches, parity
+    if world == 1:
+        r = timed(lambda: matcher.hamming_knn_device(q, db, out=out, index_base=base))
+        return r + (None, None)
+    variants = {}
+    comm = matcher.nccl_comm_ptr()   # torch.distributed's ncclComm_t, handed to the C ABI
+    r_nccl = timed(lambda: matcher.hamming_knn_sharded(q, db, base, out=out, comm=comm))
+    variants["nccl_allgather"] = {"api": "orb_hamming_knn_sharded", "value": r_nccl[0], "ms_per_step": r_nccl[1], "gpu_launches": int(r_nccl[2]),
+                                  "parity": r_nccl[3]}
+    best, name = r_nccl, "orb_hamming_knn_sharded: shard scan + ncclAllGather + device top-2 merge in one C-ABI call"
+    try:
+        grp = matcher.KnnPeerGroup(max_q=KNN_Q)
+        out.zero_()
+        r_peer = timed(lambda: grp.knn(q, db, base, out=out))
+        grp.check()
+        variants["peer_stores"] = {"api": "orb_hamming_knn_peer", "value": r_peer[0], "ms_per_step": r_peer[1], "gpu_launches": int(r_peer[2]),
+                                   "parity": r_peer[3]}
+        ok = _max_over_ranks(0.0 if (rank != 0 or r_peer[3]) else 1.0, world) == 0.0   # rank 0 holds the parity verdict
+        if ok and r_peer[0] > r_nccl[0]:
+            best, name = r_peer, ("orb_hamming_knn_peer: shard scan, then ONE kernel that reduces, stores the records into the peers' mailboxes over "
+                                  "NVLink (CUDA IPC), waits for their flags and merges - no collective launch")
+        _barrier(world)
+        grp.close()
+    except Exception as e:   # noqa: BLE001 - no peer access between the GPUs of this box: the NCCL path stands
+        variants["peer_stores"] = {"api": "orb_hamming_knn_peer", "unavailable": str(e)[:200]}
+    return best + (name, variants)
 
 
 def run_b200(args):
@@ -653,7 +673,7 @@ def run_b200(args):
     e2e_value = B * world * e_steps / (e_ms * 1e-3)
 
     st_ms, st_matches = bench_stereo_e2e(ex, frames, e_steps, args.warmup, world)
-    knn_rate, knn_ms, knn_launches, knn_par = bench_knn(rank, world, max(args.steps, 5), args.warmup)
+    knn_rate, knn_ms, knn_launches, knn_par, knn_path, knn_variants = bench_knn(rank, world, max(args.steps, 5), args.warmup)
     g_steps = max(args.steps, 5)
     g_ms, g_matches, g_launches = bench_guided(W, H, g_steps, args.warmup, world)
     bow_voc, bow_base = _bow_inputs()
@@ -738,8 +758,8 @@ def run_b200(args):
                 "config": f"{BOW_FRAMES} frames x {BOW_N} descriptors per step per GPU, vocabulary k=10 L=6 (10^6 words), resident in HBM",
                 "words_per_frame": b_words, "gpu_launches": 2 * g_steps, "api": "orb_bow_transform (device memory)"},
         "knn": {"metric": "Hamming matches/sec (k=2 brute force)", "value": knn_rate, "unit": "pairs/s",
-                "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)"
-                          + (", orb_hamming_knn_sharded: shard scan + ncclAllGather + device top-2 merge in one C-ABI call" if world > 1 else ""),
+                "config": f"{KNN_Q} queries x {KNN_D} db rows sharded over {world} GPU(s)" + (", " + knn_path if knn_path else ""),
+                "variants": knn_variants,
                 "ms_per_step": knn_ms, "gpu_launches": int(knn_launches),
                 "parity": knn_par if world > 1 else "n/a at 1 GPU (no merge; tests/test_gpu_knn.py checks the scan)",
                 "roofline": {"bound": "popc", "achieved": knn_rate * 8 / world, "peak": popc_peak, "unit": "popc.b32/s",
