@@ -51,6 +51,7 @@ class ORBextractor {   // include/ORBextractor.h:185: the one member ComputeSter
 #include "_ref/gen_griddefs.inc"
 
 class KeyFrame;
+class Frame;
 class MapPoint;
 static MapPoint* g_cur_point = nullptr;   // the map point whose candidate scan is running (set by GetDescriptor, read by KeyFrame::GetMapPoint)
 
@@ -69,6 +70,9 @@ class MapPoint {       // include/MapPoint.h: the members the matcher loops name
   float GetMinDistanceInvariance() { return minD; }
   cv::Mat GetNormal() { return mNormal.clone(); }
   int PredictScale(const float&, KeyFrame*) { return predLevel; }
+  int PredictScale(const float&, Frame*) { return predLevel; }
+  int GetIndexInKeyFrame(KeyFrame*) { return idxInKF2; }     // SearchBySim3 asks it of the pre-matched points of keyframe 2 (:1469)
+  int idxInKF2 = -1;
   void Replace(MapPoint*) {}
   void AddObservation(KeyFrame*, size_t) {}
   bool inKF = false;
@@ -135,6 +139,9 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
   void ComputeThreeMaxima(vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);
   int SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th = 3);
   int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);
+  int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist);
+  int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, vector<MapPoint*>& vpMatched, int th);
+  int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12, const cv::Mat& t12, const float th);
   int SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches);
   int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12);
   int Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th = 3.0);
@@ -167,6 +174,9 @@ class ORBmatcher {     // include/ORBmatcher.h:54-62, 223-236
 #include "_ref/gen_fuse2.inc"
 #include "_ref/gen_epiline.inc"
 #include "_ref/gen_stri.inc"
+#include "_ref/gen_sbpk.inc"
+#include "_ref/gen_sbps.inc"
+#include "_ref/gen_sim3.inc"
 
 struct FrameDescs { cv::Mat mDescriptors; };
 
@@ -585,6 +595,147 @@ int main(int argc, char** argv) {
     std::vector<int32_t> m12(K[0].N, -1);
     for (const auto& pr : pairs) m12[pr.first] = (int32_t)pr.second;
     out.insert(out.end(), m12.begin(), m12.end());
+  } else if (mode == "sbpk" || mode == "sbps") {
+    // sbpk: SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1883-2015, relocalisation), CurrentFrame.mTcw = identity;
+    // sbps: SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:422-551, loop closing), Scw = identity, target = a KeyFrame (its own GetFeaturesInArea).
+    // float bounds[4], th, fx, fy, cx, cy; int ORBdist, checkOri, nlevels; nlevels x float scale; target: int n; n x KeyPoint; n x 32 B; n x u8 "slot
+    // holds a map point"; points: int m; m x {float X, Y, Z, angle; int level, flags (1 null [sbpk only], 2 bad, 4 already found)}; m x 32 B
+    //   -> int nmatches; n x int32 point assigned to the keypoint by this call (-1 none)
+    const bool kf_target = mode == "sbps";
+    ORB_SLAM2::Frame F;
+    ORB_SLAM2::KeyFrame KF;    // sbps: the target; sbpk: the source of the map points
+    F.mnMinX = r.get<float>(); F.mnMinY = r.get<float>(); F.mnMaxX = r.get<float>(); F.mnMaxY = r.get<float>();
+    const float th = r.get<float>();
+    F.fx = r.get<float>(); F.fy = r.get<float>(); F.cx = r.get<float>(); F.cy = r.get<float>();
+    const int orbdist = r.get<int32_t>(), ori = r.get<int32_t>(), nl = r.get<int32_t>();
+    for (int l = 0; l < nl; ++l) F.mvScaleFactors.push_back(r.get<float>());
+    F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);     // src/Frame.cc:200-202
+    F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
+    const int n = r.get<int32_t>();
+    F.N = n;
+    F.mvKeysUn.resize(n);
+    std::memcpy(F.mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+    F.mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+    ORB_SLAM2::MapPoint taken;
+    taken.nObs = 1;
+    F.mvpMapPoints.assign(n, nullptr);
+    const uint8_t* cl = r.bytes(n);
+    for (int i = 0; i < n; ++i) if (cl[i]) F.mvpMapPoints[i] = &taken;
+    F.AssignFeaturesToGrid();
+    cv::Mat I4(4, 4, CV_32F);
+    for (int y = 0; y < 4; ++y) for (int x = 0; x < 4; ++x) I4.at<float>(y, x) = y == x ? 1.f : 0.f;
+    F.mTcw = I4;
+    const int m = r.get<int32_t>();
+    std::vector<ORB_SLAM2::MapPoint> pts(m);
+    std::vector<ORB_SLAM2::MapPoint*> vp(m, nullptr);
+    std::vector<float> angle(m);
+    std::set<ORB_SLAM2::MapPoint*> found;
+    for (int i = 0; i < m; ++i) {
+      pts[i].mWorldPos = cv::Mat(3, 1, CV_32F);
+      for (int k = 0; k < 3; ++k) pts[i].mWorldPos.at<float>(k) = r.get<float>();
+      pts[i].mNormal = cv::Mat(3, 1, CV_32F);
+      pts[i].mNormal.at<float>(0) = 0.f; pts[i].mNormal.at<float>(1) = 0.f; pts[i].mNormal.at<float>(2) = 1.f;
+      angle[i] = r.get<float>();
+      pts[i].predLevel = r.get<int32_t>();
+      const int fl = r.get<int32_t>();
+      if (!(fl & 1)) vp[i] = &pts[i];
+      pts[i].bad = (fl & 2) != 0;
+      if (fl & 4) found.insert(&pts[i]);
+    }
+    for (int i = 0; i < m; ++i) pts[i].mDescriptor = mat_u8(r.bytes(32), 1, 32);
+    ORB_SLAM2::ORBmatcher matcher(0.6f, ori != 0);
+    std::vector<ORB_SLAM2::MapPoint*> result;
+    if (!kf_target) {
+      KF.mvpMapPoints = vp;
+      KF.mvKeysUn.resize(m);
+      for (int i = 0; i < m; ++i) KF.mvKeysUn[i].angle = angle[i];
+      out.push_back(matcher.SearchByProjection(F, &KF, found, th, orbdist));
+      result = F.mvpMapPoints;
+    } else {
+      KF.N = n; KF.mvKeysUn = F.mvKeysUn; KF.mDescriptors = F.mDescriptors;
+      KF.fx = F.fx; KF.fy = F.fy; KF.cx = F.cx; KF.cy = F.cy;
+      KF.mvScaleFactors = F.mvScaleFactors;
+      KF.mnMinX = F.mnMinX; KF.mnMinY = F.mnMinY; KF.mnMaxX = F.mnMaxX; KF.mnMaxY = F.mnMaxY;
+      KF.mfGridElementWidthInv = F.mfGridElementWidthInv; KF.mfGridElementHeightInv = F.mfGridElementHeightInv;
+      KF.mGrid.resize(KF.mnGridCols);
+      for (int i = 0; i < KF.mnGridCols; ++i) {
+        KF.mGrid[i].resize(KF.mnGridRows);
+        for (int j = 0; j < KF.mnGridRows; ++j) KF.mGrid[i][j] = F.mGrid[i][j];
+      }
+      result = F.mvpMapPoints;                      // vpMatched: slots that already hold a match
+      int slot = 0;
+      for (int i = 0; i < m; ++i)                   // "already found" points are the ones sitting in vpMatched (:434-435)
+        if (found.count(&pts[i])) { while (slot < n && !cl[slot]) ++slot; if (slot < n) result[slot++] = &pts[i]; }
+      out.push_back(matcher.SearchByProjection(&KF, I4, vp, result, (int)th));
+    }
+    for (int i = 0; i < n; ++i) {
+      ORB_SLAM2::MapPoint* p = result[i];
+      out.push_back(p && p != &taken && !(cl[i]) ? (int32_t)(p - pts.data()) : -1);
+    }
+  } else if (mode == "sim3") {
+    // ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1433-1684) with identity poses and s12 = 1, R12 = I, t12 = 0.
+    // float bounds[4], th, fx, fy, cx, cy; int nlevels; nlevels x float scale; twice {int n; n x KeyPoint; n x 32 B; n x {float X, Y, Z; int level,
+    // flags (1 no map point, 2 bad), prematch (keyframe 1: feature of keyframe 2 it is already matched to, -1 none; keyframe 2: unused)}}
+    //   -> int nFound; n1 x int32 feature of keyframe 2 newly matched to feature i1 (-1 none)
+    float bounds[4];
+    for (float& b : bounds) b = r.get<float>();
+    const float th = r.get<float>();
+    float cam[4];
+    for (float& c : cam) c = r.get<float>();
+    const int nl = r.get<int32_t>();
+    std::vector<float> scale(nl);
+    for (float& v : scale) v = r.get<float>();
+    ORB_SLAM2::KeyFrame K[2];
+    std::vector<ORB_SLAM2::MapPoint> pts[2];
+    std::vector<int> prematch;
+    for (int k = 0; k < 2; ++k) {
+      ORB_SLAM2::Frame F;
+      F.mnMinX = bounds[0]; F.mnMinY = bounds[1]; F.mnMaxX = bounds[2]; F.mnMaxY = bounds[3];
+      F.mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(F.mnMaxX - F.mnMinX);
+      F.mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(F.mnMaxY - F.mnMinY);
+      const int n = r.get<int32_t>();
+      F.N = n;
+      F.mvKeysUn.resize(n);
+      std::memcpy(F.mvKeysUn.data(), r.bytes((size_t)n * 28), (size_t)n * 28);
+      K[k].mDescriptors = mat_u8(r.bytes((size_t)n * 32), n, 32);
+      F.AssignFeaturesToGrid();
+      ORB_SLAM2::KeyFrame& KF = K[k];
+      KF.N = n; KF.mvKeysUn = F.mvKeysUn;
+      KF.fx = cam[0]; KF.fy = cam[1]; KF.cx = cam[2]; KF.cy = cam[3];
+      KF.mvScaleFactors = scale;
+      KF.mnMinX = F.mnMinX; KF.mnMinY = F.mnMinY; KF.mnMaxX = F.mnMaxX; KF.mnMaxY = F.mnMaxY;
+      KF.mfGridElementWidthInv = F.mfGridElementWidthInv; KF.mfGridElementHeightInv = F.mfGridElementHeightInv;
+      KF.mGrid.resize(KF.mnGridCols);
+      for (int i = 0; i < KF.mnGridCols; ++i) {
+        KF.mGrid[i].resize(KF.mnGridRows);
+        for (int j = 0; j < KF.mnGridRows; ++j) KF.mGrid[i][j] = F.mGrid[i][j];
+      }
+      KF.Rcw = cv::Mat(3, 3, CV_32F); KF.tcw = cv::Mat(3, 1, CV_32F);
+      for (int y = 0; y < 3; ++y) { for (int x = 0; x < 3; ++x) KF.Rcw.at<float>(y, x) = y == x ? 1.f : 0.f; KF.tcw.at<float>(y) = 0.f; }
+      pts[k].resize(n);
+      KF.mvpMapPoints.assign(n, nullptr);
+      for (int i = 0; i < n; ++i) {
+        pts[k][i].mWorldPos = cv::Mat(3, 1, CV_32F);
+        for (int c = 0; c < 3; ++c) pts[k][i].mWorldPos.at<float>(c) = r.get<float>();
+        pts[k][i].predLevel = r.get<int32_t>();
+        const int fl = r.get<int32_t>();
+        const int pm = r.get<int32_t>();
+        if (!(fl & 1)) KF.mvpMapPoints[i] = &pts[k][i];
+        pts[k][i].bad = (fl & 2) != 0;
+        if (k == 0) prematch.push_back(pm);
+      }
+    }
+    for (int i = 0; i < K[0].N; ++i) pts[0][i].mDescriptor = K[0].mDescriptors.row(i);   // a map point's descriptor = its feature's here
+    for (int i = 0; i < K[1].N; ++i) pts[1][i].mDescriptor = K[1].mDescriptors.row(i);
+    std::vector<ORB_SLAM2::MapPoint*> m12(K[0].N, nullptr);
+    for (int i = 0; i < K[0].N; ++i)
+      if (prematch[i] >= 0) { m12[i] = &pts[1][prematch[i]]; pts[1][prematch[i]].idxInKF2 = prematch[i]; }
+    cv::Mat R12(3, 3, CV_32F), t12(3, 1, CV_32F);
+    for (int y = 0; y < 3; ++y) { for (int x = 0; x < 3; ++x) R12.at<float>(y, x) = y == x ? 1.f : 0.f; t12.at<float>(y) = 0.f; }
+    ORB_SLAM2::ORBmatcher matcher(0.6f, true);
+    const float s12 = 1.f;
+    out.push_back(matcher.SearchBySim3(&K[0], &K[1], m12, s12, R12, t12, th));
+    for (int i = 0; i < K[0].N; ++i) out.push_back(m12[i] && prematch[i] < 0 ? (int32_t)(m12[i] - pts[1].data()) : -1);
   } else if (mode == "sinit") {
     // float bounds[4], nnratio; int checkOri, windowSize; F2: int n; n x KeyPoint (mvKeysUn); n x 32 B; F1: int m; m x KeyPoint (mvKeysUn: octave,
     // angle); m x 32 B; m x {float x, y} vbPrevMatched  ->  int nmatches; m x int32 vnMatches12

@@ -280,6 +280,41 @@ def ref_search_for_triangulation(desc1, kps1_un, has1, ur1, fv1: dict, desc2, kp
     return int(out[0]), out[1:1 + len(kps1_un)].copy()
 
 
+KFPT_DTYPE = np.dtype([("X", "<f4"), ("Y", "<f4"), ("Z", "<f4"), ("angle", "<f4"), ("level", "<i4"), ("flags", "<i4")])
+
+
+def ref_search_by_projection_keyframe(kps_un, desc, held, bounds, scale, th, cam, orbdist, check_orientation, points, qdesc, loop_form=False):
+    """loop_form=False: SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1883-2015, relocalisation; mTcw = identity);
+    loop_form=True: SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:422-551, loop closing; Scw = identity, int th, TH_LOW).
+    points: KFPT_DTYPE (world point, angle of its keypoint in the source keyframe, PredictScale result, flags 1 null, 2 bad, 4 already found).
+    Returns (nmatches, assigned [n]: point index per target keypoint, -1 none)."""
+    n, m = len(kps_un), len(points)
+    kps_un = np.ascontiguousarray(kps_un)
+    assert kps_un.dtype.itemsize == 28 and points.dtype == KFPT_DTYPE
+    payload = struct.pack("<4ff4f3i", *[float(b) for b in bounds], th, *[float(c) for c in cam], int(orbdist), int(check_orientation), len(scale))
+    payload += np.ascontiguousarray(scale, "<f4").tobytes()
+    payload += struct.pack("<i", n) + kps_un.tobytes() + np.ascontiguousarray(desc, np.uint8).tobytes()
+    payload += np.ascontiguousarray(held if held is not None else np.zeros(n, np.uint8), np.uint8).tobytes()
+    payload += struct.pack("<i", m) + np.ascontiguousarray(points).tobytes() + np.ascontiguousarray(qdesc, np.uint8).tobytes()
+    out = np.frombuffer(_run_match("sbps" if loop_form else "sbpk", payload), "<i4")
+    return int(out[0]), out[1:1 + n].copy()
+
+
+SIM3_DTYPE = np.dtype([("X", "<f4"), ("Y", "<f4"), ("Z", "<f4"), ("level", "<i4"), ("flags", "<i4"), ("prematch", "<i4")])
+
+
+def ref_search_by_sim3(bounds, th, cam, scale, kps1, desc1, pts1, kps2, desc2, pts2):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1433-1684) with identity poses, s12 = 1, R12 = I, t12 = 0. pts?: SIM3_DTYPE per feature (world point of
+    the map point it holds, PredictScale result, flags 1 = no map point, 2 = bad; prematch (keyframe 1 only) = feature of keyframe 2 already matched).
+    Returns (nFound, newly matched feature of keyframe 2 per feature of keyframe 1, -1 none)."""
+    payload = struct.pack("<4ff4fi", *[float(b) for b in bounds], th, *[float(c) for c in cam], len(scale)) + np.ascontiguousarray(scale, "<f4").tobytes()
+    for k, d, p in ((kps1, desc1, pts1), (kps2, desc2, pts2)):
+        assert p.dtype == SIM3_DTYPE and len(p) == len(k)
+        payload += struct.pack("<i", len(k)) + np.ascontiguousarray(k).tobytes() + np.ascontiguousarray(d, np.uint8).tobytes() + np.ascontiguousarray(p).tobytes()
+    out = np.frombuffer(_run_match("sim3", payload), "<i4")
+    return int(out[0]), out[1:1 + len(kps1)].copy()
+
+
 def ref_search_for_initialization(kps2_un, desc2, kps1_un, desc1, prev_matched, bounds, nnratio, check_orientation, window):
     """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:570-712) on F2's reference-built grid.
     Returns (nmatches, vnMatches12 [m])."""

@@ -464,6 +464,120 @@ def test_fuse_sim3_form_equals_reference(oracle, seed, stereo, th):
     assert np.array_equal(bi, best_ref), f"bestIdx differs at points {np.flatnonzero(bi != best_ref)[:10]}"
 
 
+def _keyframe_projection_case(seed, loop_form, n=900, m=800, th=10.0):
+    """Inputs of the two keyframe forms of SearchByProjection and the query records the host derives from them; projection exact by construction."""
+    from orb_slam2_detailed_comments_b200._lib import QUERY_DTYPE
+    c = synth.synth_guided_case(seed, n=n, m=m, stereo=False)
+    rng = np.random.default_rng(seed + 55)
+    q = c["queries"]
+    fx, fy, cx, cy = (np.float32(v) for v in CAM)
+    u = (np.round(q["u"] * 4) / 4).astype(np.float32)
+    v = (np.round(q["v"] * 4) / 4).astype(np.float32)
+    z = rng.choice(np.array([0.5, 1.0, 2.0, 4.0, -1.0], np.float32), m, p=[0.2, 0.3, 0.25, 0.2, 0.05])
+    pts = np.zeros(m, ref_binary.KFPT_DTYPE)
+    pts["X"], pts["Y"], pts["Z"] = (u - cx) / fx * z, (v - cy) / fy * z, z
+    pts["angle"] = q["angle"]
+    pts["level"] = np.clip(q["max_level"], 0, 7)
+    pts["flags"] = (rng.random(m) < 0.04) * (0 if loop_form else 1) + (rng.random(m) < 0.04) * 2 + (rng.random(m) < 0.04) * 4
+    invz = (np.float32(1.0) / z).astype(np.float32)
+    if loop_form:                                                    # x = X * invz; u = fx * x + cx (:447-451)
+        uu, vv = fx * (pts["X"] * invz) + cx, fy * (pts["Y"] * invz) + cy
+    else:                                                            # u = fx * xc * invzc + cx (:1912-1913)
+        uu, vv = fx * pts["X"] * invz + cx, fy * pts["Y"] * invz + cy
+    assert np.array_equal(uu, u) and np.array_equal(vv, v)           # exact for either sign of z
+    mnx, mny, mxx, mxy = (np.float32(b) for b in c["bounds"])
+    if loop_form:
+        skip = (pts["flags"] != 0) | (z < 0) | ~((uu >= mnx) & (uu < mxx) & (vv >= mny) & (vv < mxy))
+    else:                                                            # this form has no `invzc < 0` test
+        skip = (pts["flags"] != 0) | (uu < mnx) | (uu > mxx) | (vv < mny) | (vv > mxy)
+    q2 = np.zeros(m, QUERY_DTYPE)
+    q2["u"], q2["v"] = uu, vv
+    q2["radius"] = (np.float32(th) * SCALE[pts["level"]]).astype(np.float32)
+    q2["angle"] = pts["angle"]
+    q2["min_level"], q2["max_level"] = pts["level"] - 1, pts["level"] + (0 if loop_form else 1)
+    q2["flags"] = np.where(skip, 1, 2)                               # every accepted match blocks its keypoint for the later points
+    held = c["claimed"].copy()
+    held[:64] = 1                                                    # slots for the loop form's already-found points
+    return c, pts, q2, held
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,loop_form,ori,orbdist", [(1, False, True, 100), (2, False, False, 64), (3, True, False, 50), (4, True, False, 50)])
+def test_keyframe_projection_forms_equal_reference(oracle, seed, loop_form, ori, orbdist):
+    """The relocalisation form SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) and the loop-closing form SearchByProjection(pKF,
+    Scw, vpPoints, vpMatched, th): oracle.search_by_projection with every query claiming, no stereo check, the form's level window and threshold."""
+    th = 10.0
+    c, pts, q2, held = _keyframe_projection_case(seed, loop_form, th=th)
+    nm_ref, as_ref = ref_binary.ref_search_by_projection_keyframe(c["kps"], c["desc"], held, c["bounds"], SCALE, th, CAM, orbdist, ori, pts, c["qdesc"],
+                                                                  loop_form=loop_form)
+    assigned, qmatch, nm = oracle.search_by_projection(c["kps"], c["desc"], q2, c["qdesc"], c["bounds"], th_dist=orbdist, nn_ratio=0.0,
+                                                       check_orientation=ori and not loop_form, uright=None, claimed=held)
+    assert nm == nm_ref and nm_ref > 100, (nm, nm_ref)
+    assert np.array_equal(assigned, as_ref), f"assignment differs at keypoints {np.flatnonzero(assigned != as_ref)[:10]}"
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,th", [(1, 7.5), (2, 10.0)])
+def test_search_by_sim3_equals_reference(oracle, seed, th):
+    """SearchBySim3 == two passes of oracle.fuse_search (TH_HIGH, level window [predicted - 1, predicted], KeyFrame::GetFeaturesInArea / IsInImage) and
+    the mutual check, with the pre-matched features of both keyframes left out as the reference does through vbAlreadyMatched1 / 2."""
+    from orb_slam2_detailed_comments_b200._lib import QUERY_DTYPE, KP_DTYPE
+    c = synth.synth_guided_case(seed + 40, n=850, m=800, stereo=False)
+    rng = np.random.default_rng(seed + 5)
+    fx, fy, cx, cy = (np.float32(v) for v in CAM)
+    quant = lambda a: (np.round(a * 4) / 4).astype(np.float32)
+    k2 = c["kps"].copy()
+    k2["x"], k2["y"] = quant(k2["x"]), quant(k2["y"])
+    d2 = c["desc"]
+    q = c["queries"]
+    k1 = np.zeros(len(q), KP_DTYPE)
+    k1["x"], k1["y"], k1["octave"], k1["angle"] = quant(q["u"]), quant(q["v"]), np.clip(q["max_level"], 0, 7), q["angle"]
+    d1 = c["qdesc"]
+    mnx, mny, mxx, mxy = (np.float32(b) for b in c["bounds"])
+
+    def points(k, other_n, with_prematch):
+        n = len(k)
+        p = np.zeros(n, ref_binary.SIM3_DTYPE)
+        z = rng.choice(np.array([0.5, 1.0, 2.0, 4.0, -1.0], np.float32), n, p=[0.2, 0.3, 0.25, 0.2, 0.05])
+        p["X"], p["Y"], p["Z"] = (k["x"] - cx) / fx * z, (k["y"] - cy) / fy * z, z
+        p["level"] = k["octave"]
+        p["flags"] = (rng.random(n) < 0.05) * 1 + (rng.random(n) < 0.03) * 2
+        p["prematch"] = -1
+        invz = (np.float32(1.0) / z).astype(np.float32)
+        u, v = fx * (p["X"] * invz) + cx, fy * (p["Y"] * invz) + cy          # x = X * invz; u = fx * x + cx (:1496-1502)
+        assert np.array_equal(u, k["x"]) and np.array_equal(v, k["y"])
+        in_image = (u >= mnx) & (u < mxx) & (v >= mny) & (v < mxy)
+        return p, (p["flags"] != 0) | (z < 0) | ~in_image
+
+    p1, skip1 = points(k1, len(k2), True)
+    p2, skip2 = points(k2, len(k1), False)
+    pre = rng.choice(len(k1), 40, replace=False)
+    tgt = rng.choice(np.flatnonzero(p2["flags"] == 0), 40, replace=False)
+    pre = pre[p1["flags"][pre] == 0][:30]                                     # vpMatches12[i] != NULL only makes sense for features with a point
+    p1["prematch"][pre] = tgt[:len(pre)]
+    matched1 = p1["prematch"] >= 0
+    matched2 = np.zeros(len(k2), bool)
+    matched2[p1["prematch"][matched1]] = True
+
+    def queries(k, p, skip):
+        qq = np.zeros(len(k), QUERY_DTYPE)
+        qq["u"], qq["v"] = k["x"], k["y"]
+        qq["radius"] = (np.float32(th) * SCALE[p["level"]]).astype(np.float32)
+        qq["min_level"], qq["max_level"] = p["level"] - 1, p["level"]
+        qq["flags"] = np.where(skip, 1, 0)
+        return qq
+
+    nf_ref, m12_ref = ref_binary.ref_search_by_sim3(c["bounds"], th, CAM, SCALE, k1, d1, p1, k2, d2, p2)
+    bi1, _ = oracle.fuse_search(k2, d2, queries(k1, p1, skip1 | matched1), d1, c["bounds"], th_dist=100)
+    bi2, _ = oracle.fuse_search(k1, d1, queries(k2, p2, skip2 | matched2), d2, c["bounds"], th_dist=100)
+    m12 = np.full(len(k1), -1, np.int32)
+    for i1 in range(len(k1)):
+        if bi1[i1] >= 0 and bi2[bi1[i1]] == i1:
+            m12[i1] = bi1[i1]
+    assert int((m12 >= 0).sum()) == nf_ref and nf_ref > 100, (int((m12 >= 0).sum()), nf_ref)
+    assert np.array_equal(m12, m12_ref)
+
+
 @needs_ref
 @pytest.mark.gpu
 def test_cuda_fuse_equals_reference():
