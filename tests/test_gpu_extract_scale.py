@@ -33,7 +33,7 @@ def _check_frame(oe, frame, kps, desc, n):
 @pytest.mark.parametrize("B", [1, 17, 70, 131, 200])
 def test_ragged_multipass_batches_match_oracle(oracle, B, monkeypatch):
     """Pass size forced to 16 frames: B = 131 runs ramp-up passes of 4 and 8 frames, seven full passes and a ragged tail,
-    alternating between the two workspaces; every frame must equal the oracle."""
+    rotating through the four workspaces; every frame must equal the oracle."""
     monkeypatch.setenv("ORB_B200_CHUNK", "16")
     frames = _tiled(400, 300, B, 4000, 6)
     ex = _ex(500)
