@@ -42,16 +42,21 @@
 
 // cornerScore (OpenCV fast_score.cpp, 16-pixel ring, K = 8): S = max(max_arcs min_9(v - r), max_arcs min_9(r - v)) - 1,
 // clamped at 0. Lanes of every 32-bit value: lo = 256 + (v - r), hi = 256 + (r - v), both in [1, 511].
-__device__ __forceinline__ int fast_score(const uint8_t* __restrict__ p) {
+__device__ __forceinline__ int fast_score(unsigned p) {   // p = 32-bit shared-memory address of the candidate pixel in the window
   constexpr int wp = FAST_WP;
-  const unsigned v = p[0];
+  unsigned v, e[16];
+  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(p));
   const unsigned base = (256u + v) | ((256u - v) << 16);
-  unsigned e[16];
   // ring offsets (dx,dy), k = 0..15: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
-  e[0] = p[3 * wp];       e[1] = p[3 * wp + 1];   e[2] = p[2 * wp + 2];   e[3] = p[wp + 3];
-  e[4] = p[3];            e[5] = p[-wp + 3];      e[6] = p[-2 * wp + 2];  e[7] = p[-3 * wp + 1];
-  e[8] = p[-3 * wp];      e[9] = p[-3 * wp - 1];  e[10] = p[-2 * wp - 2]; e[11] = p[-wp - 3];
-  e[12] = p[-3];          e[13] = p[wp - 3];      e[14] = p[2 * wp - 2];  e[15] = p[3 * wp - 1];
+  asm("ld.shared.u8 %0, [%1+768];" : "=r"(e[0]) : "r"(p));   asm("ld.shared.u8 %0, [%1+769];" : "=r"(e[1]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+514];" : "=r"(e[2]) : "r"(p));   asm("ld.shared.u8 %0, [%1+259];" : "=r"(e[3]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+3];" : "=r"(e[4]) : "r"(p));     asm("ld.shared.u8 %0, [%1+-253];" : "=r"(e[5]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+-510];" : "=r"(e[6]) : "r"(p));  asm("ld.shared.u8 %0, [%1+-767];" : "=r"(e[7]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+-768];" : "=r"(e[8]) : "r"(p));  asm("ld.shared.u8 %0, [%1+-769];" : "=r"(e[9]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+-514];" : "=r"(e[10]) : "r"(p)); asm("ld.shared.u8 %0, [%1+-259];" : "=r"(e[11]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+-3];" : "=r"(e[12]) : "r"(p));   asm("ld.shared.u8 %0, [%1+253];" : "=r"(e[13]) : "r"(p));
+  asm("ld.shared.u8 %0, [%1+510];" : "=r"(e[14]) : "r"(p));  asm("ld.shared.u8 %0, [%1+767];" : "=r"(e[15]) : "r"(p));
+  static_assert(wp == 256, "the immediates above are ring offsets for a 256-byte window pitch");
 #pragma unroll
   for (int k = 0; k < 16; ++k) e[k] = base + e[k] * 0xffffu;   // (r << 16) - r: no borrow, lo >= 1
   // max over the 16 arcs of min over 9 = max over even k of min(min(e[k+1 .. k+8]), max(e[k], e[k+9])):
@@ -92,7 +97,6 @@ __device__ __forceinline__ void fast_gt2(unsigned a, unsigned ti, unsigned tm, u
 // written to the score plane at a - FAST_SC_OFF (same pitch: NMS and emission address both planes from a). Returns the number of corners appended.
 __device__ __forceinline__ int fast_score_candidates(const unsigned (&cand)[2], const uint8_t* __restrict__ win, uint8_t* __restrict__ sc,
                                                      uint16_t* __restrict__ list, int start, int warp, int qbase, int lane, int min_th) {
-  const uint32_t lt = (1u << lane) - 1u;
   int cnt;
   {
     const int c = __popc(cand[0]) + __popc(cand[1]);
@@ -114,21 +118,26 @@ __device__ __forceinline__ int fast_score_candidates(const unsigned (&cand)[2], 
       }
     }
   }
+  // pad the list to a multiple of 32 with copies of its first entry (the lists have 32 spare entries per warp): the score loop then needs no
+  // bounds branch around fast_score, only `i < cnt` in the corner predicate
+  if (cnt & 31) {
+    const int i = (cnt & ~31) + lane;
+    if (i >= cnt) list[start + i] = list[start];
+  }
   __syncwarp();
   // offset of pixel 0 of group 0 in row `warp`; row warp + 8 * ri is 8 * 256 bytes further per ri, group o 8 bytes per o
   const unsigned a0 = (unsigned)((warp + 3) * FAST_WP + 16 + qbase);
+  const unsigned win_s = orb_smem_u32(win);
+  unsigned lt;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
   int ncorner = 0;
-  for (int c0 = 0; c0 < cnt; c0 += 32) {
+  for (int c0 = 0; c0 < cnt; c0 += 32) {   // branch-free body: the compiler unrolls it by four, two chunks' loads in flight (+0.3 % over `unroll 1`)
     const int i = c0 + lane;
-    unsigned a = 0;
-    int s = 0;
-    if (i < cnt) {
-      const unsigned code = list[start + i];
-      const unsigned ri = (code >> 3) & 7u;
-      a = a0 + ri * (8u * FAST_WP) + 8u * (((code >> 6) + 5u * ri) & 31u) + (code & 7u);
-      s = fast_score(win + a);
-    }
-    const bool corner = s >= min_th;
+    const unsigned code = list[start + i];
+    const unsigned ri = (code >> 3) & 7u;
+    const unsigned a = a0 + ri * (8u * FAST_WP) + 8u * (((code >> 6) + 5u * ri) & 31u) + (code & 7u);
+    const int s = fast_score(win_s + a);
+    const bool corner = s >= min_th && i < cnt;
     __syncwarp();                                            // the reads of this chunk precede the in-place writes below
     const uint32_t b = __ballot_sync(0xffffffffu, corner);
     if (corner) {
@@ -304,7 +313,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
     }
   }
   // warp w owns max_h / 8 (+ 1 if w < max_h % 8) rows of the largest level: its list starts after the rows of the warps before it
-  uint16_t* list = lists + (warp * ((sc_rows - 2) >> 3) + min(warp, (sc_rows - 2) & 7)) * row_cap;
+  uint16_t* list = lists + (warp * ((sc_rows - 2) >> 3) + min(warp, (sc_rows - 2) & 7)) * row_cap + 32 * warp;   // + 32 spare entries per warp (padding)
   // 3. the iniTh candidates (superset of all S >= iniTh): exact scores, corners = S >= minTh
   int ncorner = fast_score_candidates(cand_i, win, sc, list, 0, warp, qbase, lane, g.min_th);
   __syncthreads();
@@ -435,7 +444,7 @@ void orb_launch_fast(const uint8_t* pyr, const void* tiles, const void* maps, in
   }
   row_cap = std::min(row_cap, 256);
   const int prow = (sc_rows - 1) & ~1;
-  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + (size_t)FAST_MAXC * prow * 8 + (size_t)max_h * row_cap * 2 +
+  const size_t smem = (size_t)win_rows * FAST_WP + (size_t)sc_rows * FAST_SP + (size_t)FAST_MAXC * prow * 8 + ((size_t)max_h * row_cap + 32 * FAST_WARPS) * 2 +
                       FAST_TAB_BYTES + 32 + FAST_MAXC + 8;   // KITTI: 38 KB
   // The opt-in shared memory size is a per-context function attribute: raise it once per device to the sm_100 maximum
   // (227 KB minus the kernel's static shared memory), so that concurrent callers with different level sizes never lower each other's limit.
