@@ -227,7 +227,7 @@ void orb_launch_knn(const uint8_t* q, int Q, const uint8_t* db, long long D, lon
                     unsigned long long* partial, int nchunks, OrbKnn2* out, cudaStream_t st) {
   const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
   long long rows = (D + nchunks - 1) / nchunks;
-  rows = (rows + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+  rows = (rows + 7) & ~7LL;   // chunks need not end on a tile: the kernel's last tile is partial. Equal chunks keep all CTAs busy on small shards
   orb_knn_kernel<<<dim3(qtiles, nchunks), KNN_THREADS, 0, st>>>((const uint4*)q, Q, (const uint4*)db, D, rows, index_base, partial);
   orb_knn_merge_partial_kernel<<<(Q + 127) / 128, 128, 0, st>>>(partial, nchunks, Q, sentinel, out);
   g_knn_launches += 2;
@@ -314,7 +314,7 @@ void orb_launch_knn_peer(const uint8_t* q, int Q, const uint8_t* db, long long D
                          int* err_flag, cudaStream_t st) {
   const int qtiles = (Q + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
   long long rows = (D + nchunks - 1) / nchunks;
-  rows = (rows + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+  rows = (rows + 7) & ~7LL;   // chunks need not end on a tile: the kernel's last tile is partial. Equal chunks keep all CTAs busy on small shards
   orb_knn_kernel<<<dim3(qtiles, nchunks), KNN_THREADS, 0, st>>>((const uint4*)q, Q, (const uint4*)db, D, rows, index_base, partial);
   orb_knn_peer_kernel<<<(Q + 127) / 128, 128, 0, st>>>(partial, nchunks, Q, sentinel, *reinterpret_cast<const OrbPeerBox*>(box), my_rank, nranks,
                                                       max_q, epoch, ticket, out, err_flag);
