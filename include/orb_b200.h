@@ -138,9 +138,9 @@ int orb_extract_stereo_batch(orb_extractor* e, const uint8_t* const* images, int
 
 /* Device-resident fast path used by the benchmark: `images` is ONE device buffer [batch][height][step];
  * outputs stay in device memory (kps/desc as above, counts_dev [batch] int32 device). Asynchronous on the
- * extractor's stream unless `sync` != 0. With sync == 0 the capacity flags (a FAST cell with more than 128 NMS survivors - the reference's
- * vector simply grows -, raw keypoints, nodes, `cap`) are NOT read by the call: truncated cells change the quadtree input silently, so an
- * asynchronous caller must poll orb_extractor_check() at a point where it synchronises anyway. */
+ * extractor's stream unless `sync` != 0. With sync == 0 the capacity flag (`cap` smaller than orb_extractor_max_keypoints(); the internal
+ * per-cell / per-level buffers are sized by geometric bounds and cannot overflow) is NOT read by the call: an asynchronous caller polls
+ * orb_extractor_check() at a point where it synchronises anyway. */
 int orb_extract_batch_device(orb_extractor* e, const uint8_t* images, int step, int width, int height, int batch,
                              orb_keypoint* kps, uint8_t* desc, int cap, int32_t* counts_dev, int sync);
 

@@ -205,7 +205,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   const int wCell = L.wCell;
   const long long cell0 = (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
   int* cnt_row = cell_cnt + cell0;
-  uint32_t* kp_row = cell_kp + cell0 * ORB_CELL_CAP;
+  uint32_t* kp_row = cell_kp + cell0 * g.cell_cap;
 
   const int iniY = ORB_MIN_BORDER + ci * L.hCell;
   const int wh = min(iniY + L.hCell + 6, L.maxBY) - iniY, dh = wh - 6;   // window rows, detection rows
@@ -363,7 +363,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       if (lane >= o) incl += yv;
     }
     const int total = __shfl_sync(0xffffffffu, incl, 31);
-    uint32_t* kp_out = kp_row + (long long)cj * ORB_CELL_CAP;
+    uint32_t* kp_out = kp_row + (long long)cj * g.cell_cap;
     int rank = incl - c0 - c1;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
@@ -373,7 +373,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
         const int bx = __ffsll((long long)m) - 1;
         m &= m - 1;
         const int x = cx0 + bx;
-        if (rank < ORB_CELL_CAP) {
+        if (rank < g.cell_cap) {
           const uint32_t s = sc[(y + 1) * FAST_SP + x];
           // cell-local FAST coordinates shifted by (j*wCell, i*hCell) (:1540-1541) == level pixel - 16
           kp_out[rank] = (uint32_t)(x + xa - ORB_MIN_BORDER) | ((uint32_t)(y + 3 + ci * L.hCell) << 12) | (s << 24);
@@ -382,8 +382,8 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       }
     }
     if (lane == 0) {
-      cnt_row[cj] = min(total, ORB_CELL_CAP);
-      if (total > ORB_CELL_CAP) atomicOr(err_flag, 1);
+      cnt_row[cj] = min(total, g.cell_cap);
+      if (total > g.cell_cap) atomicOr(err_flag, 1);
     }
   }
 }

@@ -209,7 +209,7 @@ orb_fast_band_v1_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_
   const int j0 = sg * L.fast_G, j1 = min(j0 + L.fast_G, L.nCols);
   const int wCell = L.wCell;
   int* cnt_row = cell_cnt + (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
-  uint32_t* kp_row = cell_kp + ((long long)frame * g.ncells_total + L.cell_base + ci * L.nCols) * ORB_CELL_CAP;
+  uint32_t* kp_row = cell_kp + ((long long)frame * g.ncells_total + L.cell_base + ci * L.nCols) * g.cell_cap;
 
   const int iniY = ORB_MIN_BORDER + ci * L.hCell;
   const int wh = min(iniY + L.hCell + 6, L.maxBY) - iniY, dh = wh - 6;   // window rows, detection rows
@@ -329,7 +329,7 @@ orb_fast_band_v1_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_
     }
     const int tot0 = __shfl_sync(0xffffffffu, x0, 31), tot1 = __shfl_sync(0xffffffffu, x1, 31);
     const int total = tot0 + tot1;
-    uint32_t* kp_out = kp_row + (long long)cj * ORB_CELL_CAP;
+    uint32_t* kp_out = kp_row + (long long)cj * g.cell_cap;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
       unsigned long long m = r ? m1 : m0;
@@ -339,7 +339,7 @@ orb_fast_band_v1_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_
         const int bx = __ffsll((long long)m) - 1;
         m &= m - 1;
         const int x = cx0 + bx;
-        if (rank < ORB_CELL_CAP) {
+        if (rank < g.cell_cap) {
           const uint32_t s = sc[(y + 1) * FAST_SP + x];
           // cell-local FAST coordinates shifted by (j*wCell, i*hCell) (:1540-1541) == level pixel - 16
           kp_out[rank] = (uint32_t)(x + xa - ORB_MIN_BORDER) | ((uint32_t)(y + 3 + ci * L.hCell) << 12) | (s << 24);
@@ -348,8 +348,8 @@ orb_fast_band_v1_kernel(const uint8_t* __restrict__ pyr, int* __restrict__ cell_
       }
     }
     if (lane == 0) {
-      cnt_row[cj] = min(total, ORB_CELL_CAP);
-      if (total > ORB_CELL_CAP) atomicOr(err_flag, 1);
+      cnt_row[cj] = min(total, g.cell_cap);
+      if (total > g.cell_cap) atomicOr(err_flag, 1);
     }
   }
 }

@@ -181,11 +181,6 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     if (L.nIni < 1) return fail(ORB_E_SHAPE, "aspect ratio < 0.5: the reference divides by nIni == 0 (src/ORBextractor.cc:1059)");
     L.hX = (float)(L.maxBX - ORB_MIN_BORDER) / L.nIni;
     L.quota = e->quota[l];
-    const long long by_cells = (long long)L.nCols * L.nRows * ORB_CELL_CAP;
-    // a level can never hold more raw keypoints than its cells can (cell overflow is flagged separately); dense 4K frames
-    // exceed any quota-based bound (the reference's vector simply grows, src/ORBextractor.cc:1451)
-    L.raw_cap = (int)by_cells;
-    L.raw_off = raw; raw += (int)align_up(L.raw_cap, 32);
     L.node_cap = std::max(L.quota + 3, 4 * L.nIni) + L.nIni + 8;
     L.node_off = nodes; nodes += (int)align_up(L.node_cap, 32);
     L.kept_off = L.node_off;
@@ -242,6 +237,18 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     g.blur_base[l] = l < g.nlevels ? g.lv[l].blur_tile_base : INT_MAX;
     g.fast_base[l] = l < g.nlevels ? g.lv[l].fast_tile_base : INT_MAX;
   }
+  // Capacities that cannot overflow: NMS survivors are pairwise non-adjacent (8-neighbourhood), so a cell of wCell x hCell detection pixels holds at
+  // most ceil(wCell / 2) * ceil(hCell / 2) of them, and a level at most that times its cells (the reference's vectors simply grow, :1451).
+  g.cell_cap = 4;
+  for (int l = 0; l < nl; ++l) g.cell_cap = std::max(g.cell_cap, ((g.lv[l].wCell + 1) / 2) * ((g.lv[l].hCell + 1) / 2));
+  g.cell_cap = (int)align_up(g.cell_cap, 4);
+  for (int l = 0; l < nl; ++l) {
+    OrbLevel& L = g.lv[l];
+    const long long by_cells = (long long)L.nCols * L.nRows * (((L.wCell + 1) / 2) * ((L.hCell + 1) / 2));
+    if (by_cells > (1LL << 30)) return fail(ORB_E_SHAPE, "level %d: raw keypoint capacity out of range", l);
+    L.raw_cap = (int)by_cells;
+    L.raw_off = raw; raw += (int)align_up(L.raw_cap, 32);
+  }
   g.ncells_total = cells; g.raw_total = raw; g.node_total = nodes; g.fast_tiles_total = ftiles;
   g.frame_stride = plane;
   e->geom = g;
@@ -255,12 +262,12 @@ static int default_chunk(const OrbGeom& g) {
   // passes are in flight so that the chains of small launches hide behind the other passes' large kernels. With the pyramid on the
   // high-priority stream, four workspaces of 32-frame passes are the best point on every shape (profiles/r2_stream_sweep.md: KITTI 95.4 k
   // against 92.1 k images/s host to host with two 64-frame passes, TUM 152.0 k against 146.7 k, EuRoC 123.9 k against 118.8 k), bounded by
-  // ~0.75 GB of workspace per pass (4K: 7 frames).
+  // ~0.9 GB of workspace per pass (4K: 6 frames).
   const char* env = getenv("ORB_B200_CHUNK");
   if (env && atoi(env) > 0) return atoi(env);
-  const double per_frame = 2.0 * (double)g.frame_stride + (double)g.ncells_total * (ORB_CELL_CAP + 1) * 4 +
+  const double per_frame = 2.0 * (double)g.frame_stride + (double)g.ncells_total * (g.cell_cap + 1) * 4 +
                            (double)g.raw_total * 9 + (double)g.node_total * 100;
-  int c = (int)(0.75e9 / per_frame);
+  int c = (int)(0.9e9 / per_frame);
   return std::max(1, std::min(c, 32));
 }
 
@@ -301,7 +308,7 @@ static int ensure_shape(orb_extractor* e, int W, int H, int batch, int cap) {
     ENS(pyr, B * g.frame_stride + 256);   // +256: the resize window loads may run 12 bytes past a row end
     ENS(blr, B * g.frame_stride + 256);
     ENS(cell_cnt, B * g.ncells_total * sizeof(int));
-    ENS(cell_kp, B * g.ncells_total * ORB_CELL_CAP * sizeof(uint32_t));
+    ENS(cell_kp, B * g.ncells_total * g.cell_cap * sizeof(uint32_t));
     ENS(kept, B * g.node_total * sizeof(uint32_t));
     ENS(kept_cnt, B * nl * sizeof(int));
     ENS(out_cnt, B * sizeof(int));

@@ -19,7 +19,9 @@
 #define ORB_RS_TH 32
 #define ORB_RS_BW 192
 #define ORB_RS_BH 52         // this fork resizes the PADDED level l-1 to the interior of level l: row ratio 1.32 .. 1.56 -> <= 51 source rows per 32
-#define ORB_CELL_CAP 128     // NMS survivors kept per 30-px cell (overflow -> ORB_E_CAPACITY)
+// NMS survivors per FAST cell: no two 8-neighbours both survive the strict 3x3 maximum test, so a cell of w x h detection pixels holds at most
+// ceil(w / 2) * ceil(h / 2) of them. OrbGeom::cell_cap is that bound for the largest cell of the shape (KITTI: 16 x 19 = 304): a cell can never
+// overflow, like the reference's growing std::vector (src/ORBextractor.cc:1451).
 
 struct OrbLevel {
   int cols, rows, pitch;     // padded level (mvImagePyramid[l] of this fork)
@@ -56,6 +58,7 @@ struct OrbGeom {
   int pad;                   // border stored around every level: ORB_EDGE (this fork: mvImagePyramid[l] is the padded image, F1) or 0 (ORB_FLAG_UPSTREAM_PYRAMID:
                              // raulmur's pyramid, mvImagePyramid[l] is the w_l x h_l image; its reflect-101 border lives in the apron only)
   int ncells_total;
+  int cell_cap;              // entries per cell in cell_kp (see above), multiple of 4
   int raw_total, node_total;
   int fast_tiles_total;      // FAST tiles per frame (all levels)
   unsigned long long frame_stride;   // bytes per frame in pyramid / blurred

@@ -112,7 +112,7 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
   // ---- gather this level's raw keypoints in (cell row, cell col, row-major in cell) order: vToDistributeKeys
   const int ncell = L.nRows * L.nCols;
   const int* ccount = cell_cnt + (long long)frame * g.ncells_total + L.cell_base;
-  const uint32_t* ckp = cell_kp + ((long long)frame * g.ncells_total + L.cell_base) * ORB_CELL_CAP;
+  const uint32_t* ckp = cell_kp + ((long long)frame * g.ncells_total + L.cell_base) * g.cell_cap;
   // scan cell counts in chunks, reusing `scan` storage is too small for 4K levels, so do a running carry
   int n = 0;
   for (int base = 0; base < ncell; base += NT) {
@@ -137,9 +137,9 @@ orb_quadtree_kernel(const int* __restrict__ cell_cnt, const uint32_t* __restrict
     }
     __syncthreads();
     const int off = n + (warp ? s_warp32[warp - 1] : 0) + x - v;
-    // each thread copies its own cell's entries (<= CELL_CAP, typically a handful)
+    // each thread copies its own cell's entries (<= cell_cap, typically a handful)
     if (c < ncell) {
-      const uint32_t* src = ckp + (long long)c * ORB_CELL_CAP;
+      const uint32_t* src = ckp + (long long)c * g.cell_cap;
       for (int e = 0; e < v; ++e)
         if (off + e < L.raw_cap) key[off + e] = src[e];
     }

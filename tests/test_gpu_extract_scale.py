@@ -120,42 +120,33 @@ def test_full_size_batch_properties(oracle, name, w, h, nf, B):
             assert np.array_equal(k1[i, :n].view(np.uint8), k1[j, :n].view(np.uint8)) and np.array_equal(d1[i, :n], d1[j, :n]), f"{name}: frame {i} != frame {j}"
 
 
-def test_dense_texture_cell_overflow_is_reported_in_sync_and_async_paths(oracle):
-    """ORB_CELL_CAP (128 NMS survivors per 30-px FAST cell) is a limit the reference does not have (its vector grows). Uniform noise at
-    low thresholds overflows it. The contract: a frame either matches the oracle bit for bit or the overflow is REPORTED - by the call itself
-    when it synchronises, by orb_extractor_check() for the asynchronous device path - never a silent truncation."""
+def test_dense_texture_never_overflows_a_cell(oracle):
+    """round 1 kept 128 NMS survivors per FAST cell and reported ORB_E_CAPACITY beyond (uniform noise in 45-px cells leaves 170-180). The
+    reference has no such limit (its vector grows). The cell capacity is now the geometric bound ceil(w / 2) * ceil(h / 2) - survivors of the strict 3x3
+    maximum test are pairwise non-adjacent - so the densest frames must simply equal the oracle, through the synchronous and the asynchronous path."""
     import torch
     from orb_slam2_detailed_comments_b200 import ORBextractor
-    from orb_slam2_detailed_comments_b200._lib import ORB_E_CAPACITY, OrbError
     rng = np.random.RandomState(4)
-    seen_overflow = seen_fit = False
-    # 83 x 83 and 143 x 83 images with 2 levels have 45-px FAST cells: uniform noise leaves 170-180 NMS survivors in a cell at 20/7 (overflow)
-    # and about 100 at 60/40 (fits)
-    for name, img in (("noise83", rng.randint(0, 256, (83, 83), dtype=np.uint8)), ("noise143", rng.randint(0, 256, (83, 143), dtype=np.uint8))):
+    checker = (np.indices((83, 143)).sum(axis=0) % 2 * 255).astype(np.uint8)          # every other pixel: the densest survivor pattern there is
+    dense = 0
+    for name, img in (("noise83", rng.randint(0, 256, (83, 83), dtype=np.uint8)), ("noise143", rng.randint(0, 256, (83, 143), dtype=np.uint8)),
+                      ("checker", checker), ("noise_kitti", rng.randint(0, 256, (376, 1241), dtype=np.uint8))):
+        nl = 8 if name == "noise_kitti" else 2
+        nf = 2000 if name == "noise_kitti" else 500
         for ini, mn in ((20, 7), (60, 40)):
-            okps, odesc, _ = oracle.OracleExtractor(500, 1.2, 2, ini, mn)(img)
-            ex = ORBextractor(500, 1.2, 2, ini, mn)
-            try:
-                kps, desc, counts, _ = ex.extract_batch(img[None])
-                overflow = False
-            except OrbError as e:
-                assert e.code == ORB_E_CAPACITY and "capacity" in str(e), e
-                overflow = True
-            if not overflow:
-                n = int(counts[0])
-                assert n == len(okps), (name, ini, n, len(okps))
-                assert np.array_equal(kps[0, :n].view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc[0, :n], odesc), (name, ini)
-            # the asynchronous device path must tell the same story through check()
-            ex2 = ORBextractor(500, 1.2, 2, ini, mn)
-            ex2.extract_batch_device(torch.from_numpy(img[None].copy()).cuda(), sync=False)
-            try:
-                ex2.check()
-                async_overflow = False
-            except OrbError as e:
-                assert e.code == ORB_E_CAPACITY
-                async_overflow = True
-            assert async_overflow == overflow, (name, ini, overflow, async_overflow)
-            ex2.check()                                               # flags are cleared by the check
-            seen_overflow = seen_overflow or overflow
-            seen_fit = seen_fit or not overflow
-    assert seen_overflow and seen_fit, "the test images must cover both a cell overflow and a dense frame that fits"
+            oe = oracle.OracleExtractor(nf, 1.2, nl, ini, mn)
+            okps, odesc, _ = oe(img)
+            ex = ORBextractor(nf, 1.2, nl, ini, mn)
+            kps, desc, counts, _ = ex.extract_batch(img[None])
+            n = int(counts[0])
+            assert n == len(okps), (name, ini, n, len(okps))
+            assert np.array_equal(kps[0, :n].view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc[0, :n], odesc), (name, ini)
+            for l in range(nl):
+                r_o, r_g = oe.raw_keypoints(l), ex.raw_keypoints(l)
+                assert len(r_o) == len(r_g) and np.array_equal(r_o["x"], r_g["x"]) and np.array_equal(r_o["response"], r_g["response"]), (name, ini, l)
+            dense = max(dense, len(oe.raw_keypoints(0)))
+            ex2 = ORBextractor(nf, 1.2, nl, ini, mn)
+            k2, d2, c2 = ex2.extract_batch_device(torch.from_numpy(img[None].copy()).cuda(), sync=False)
+            ex2.check()                                               # nothing to report
+            assert int(c2[0]) == n and np.array_equal(d2[0, :n].cpu().numpy(), odesc)
+    assert dense > 20000, dense                                       # the noise frame really is dense (> 1 raw keypoint per 25 pixels at level 0)
