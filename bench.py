@@ -636,7 +636,13 @@ def bench_knn(rank, world, steps, warmup):
         grp = matcher.KnnPeerGroup(max_q=KNN_Q)
         out.zero_()
         r_peer = timed(lambda: grp.knn(q, db, base, out=out))
-        grp.check()
+        bad = 0.0
+        try:
+            grp.check()
+        except Exception:   # noqa: BLE001 - a wait that timed out on this rank: every rank has to learn it (the ranks stay in step)
+            bad = 1.0
+        if _max_over_ranks(bad, world) > 0.0:
+            raise RuntimeError("a peer flag did not arrive on some rank")
         variants["peer_stores"] = {"api": "orb_hamming_knn_peer", "value": r_peer[0], "ms_per_step": r_peer[1], "gpu_launches": int(r_peer[2]),
                                    "parity": r_peer[3]}
         ok = _max_over_ranks(0.0 if (rank != 0 or r_peer[3]) else 1.0, world) == 0.0   # rank 0 holds the parity verdict

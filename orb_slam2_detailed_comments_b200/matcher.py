@@ -129,18 +129,37 @@ class KnnPeerGroup:
         import torch.distributed as dist
         self.rank, self.nranks = dist.get_rank(group), dist.get_world_size(group)
         self._h = C.c_void_p()
-        check(_lib.lib().orb_knn_peer_create(self.rank, self.nranks, int(max_q), C.byref(self._h)))
-        mine = np.zeros(64, np.uint8)
-        check(_lib.lib().orb_knn_peer_export(self._h, mine.ctypes.data_as(C.c_void_p)))
-        backend = dist.get_backend(group)
+        # Every rank walks through the same collectives whatever fails locally (a rank that raised early would leave the others hanging in the
+        # all-gather): the handle travels with a status byte, and the group only stands if every rank created AND connected.
+        err = None
+        mine = np.zeros(65, np.uint8)
+        try:
+            check(_lib.lib().orb_knn_peer_create(self.rank, self.nranks, int(max_q), C.byref(self._h)))
+            check(_lib.lib().orb_knn_peer_export(self._h, mine.ctypes.data_as(C.c_void_p)))
+            mine[64] = 1
+        except Exception as e:   # noqa: BLE001
+            err = e
+        on_gpu = dist.get_backend(group) == "nccl"
         t = torch.from_numpy(mine)
-        if backend == "nccl":
+        if on_gpu:
             t = t.cuda()
         parts = [torch.empty_like(t) for _ in range(self.nranks)]
         dist.all_gather(parts, t, group=group)
-        handles = np.ascontiguousarray(np.stack([x.cpu().numpy() for x in parts]))
-        check(_lib.lib().orb_knn_peer_connect(self._h, handles.ctypes.data_as(C.c_void_p)))
-        dist.barrier(group=group)   # every mailbox is open everywhere before the first store
+        got = np.stack([x.cpu().numpy() for x in parts])
+        ok = err is None and bool(got[:, 64].all())
+        if ok:
+            try:
+                handles = np.ascontiguousarray(got[:, :64])
+                check(_lib.lib().orb_knn_peer_connect(self._h, handles.ctypes.data_as(C.c_void_p)))
+            except Exception as e:   # noqa: BLE001
+                err, ok = e, False
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32)
+        if on_gpu:
+            flag = flag.cuda()
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)   # also: every mailbox is open everywhere before the first store
+        if int(flag.item()) == 0:
+            self.close()
+            raise RuntimeError(f"KnnPeerGroup: not every rank could set up its mailbox ({err if err is not None else 'a peer failed'})")
 
     def knn(self, query, db_shard, shard_base: int, sentinel: int = 256, out=None, stream=None):
         """Collective. query / db_shard: torch uint8 CUDA tensors; returns out [Q, 3] int64 (orb_knn2 records) as hamming_knn_sharded does."""
