@@ -35,7 +35,7 @@ struct orb_extractor {
     cudaEvent_t ev_join = nullptr;
     cudaStream_t st_side = nullptr;                       // high-priority side stream of the pass: quadtree (latency-bound) beside blur
     cudaEvent_t ev_fast = nullptr, ev_side = nullptr, ev_pyr = nullptr;   // ev_pyr: the pyramid of the pass is complete
-    cudaEvent_t ev_pfork = nullptr, ev_pjoin = nullptr;                   // pyramid on the side stream (ORB_B200_PYR_SIDE)
+    cudaEvent_t ev_pfork = nullptr, ev_pjoin = nullptr;                   // pyramid chain on the side stream (default; ORB_B200_PYR_MAIN=1 turns it off)
     int frames = 0;          // frames of the last pass run here
     // per-level TMA descriptors of `pyr` / `blr`: FAST band windows (256 B x hCell + 6), IC_Angle windows (48 B x 31), descriptor patches (64 B x 37)
     alignas(64) unsigned char fast_maps[ORB_LEVEL_MAPS_BYTES], ic_maps[ORB_LEVEL_MAPS_BYTES], pt_maps[ORB_LEVEL_MAPS_BYTES],
