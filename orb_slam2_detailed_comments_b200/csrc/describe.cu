@@ -19,14 +19,16 @@
 #define BL_RAW_W 160      // TMA box: columns x0 - 16 .. x0 + 143 (16-byte aligned start; the taps need x0 - 4 .. x0 + 131)
 #define BL_RAW_H 40       // rows y0 - 4 .. y0 + 35 (row y0 - 4 and rows past y0 + 34 only ever meet a zero tap)
 // V pass shared by both blur kernels: one thread = 4 pixels x 4 output rows from 6 staged row pairs.
-template <bool CLAMP>
+template <bool CLAMP, int TH = BL_TH>
 __device__ __forceinline__ void blur_v_pass(const uint4 (*s_p)[BL_TW / 4], uint8_t* __restrict__ out, const OrbLevel& L, int x0, int y0,
                                             const OrbGeom& g) {
   if (threadIdx.x >= 256) return;
-  const int q = threadIdx.x & 31, seg = threadIdx.x >> 5;   // output rows y0 + 4*seg .. + 3 = local rows 4*seg + 4 .. + 7
+  const int q = threadIdx.x & 31;
   const int x = x0 + 4 * q;
   if (x >= L.cols) return;
   const int pitch = L.pitch;
+#pragma unroll
+ for (int seg = threadIdx.x >> 5; seg < TH / 4; seg += 8) {   // output rows y0 + 4*seg .. + 3 = local rows 4*seg + 4 .. + 7
   uint4 P[6];                                                // pairs 2*seg .. 2*seg + 5 = local rows 4*seg .. 4*seg + 11
 #pragma unroll
   for (int i = 0; i < 6; ++i) P[i] = s_p[2 * seg + i][q];
@@ -56,24 +58,32 @@ __device__ __forceinline__ void blur_v_pass(const uint4 (*s_p)[BL_TW / 4], uint8
       *reinterpret_cast<unsigned*>(dst + r * pitch) = __byte_perm(lo, hi, 0x5410);
     }
   }
+ }
 }
 
-// Default blur kernel. Same tile, same shared layout and V pass as orb_blur_kernel below; the H pass is ONE round of 320 items:
+// Default blur kernel, tile = 128 x TH pixels with TH = 64 by default (orb_blur_kernel below: 128 x 32 only). Same shared layout and V pass; the H
+// pass runs in rounds of 320 items ((TH + 8) / 2 row pairs x 16 groups: two rounds at TH = 64, unrolled, all loads of both rounds issued up front).
+// The taller tile is worth +3.4 % on the whole step (118.8 k -> 122.8 k images/s at KITTI, 173.7 k -> 180.0 k at TUM, same box): the kernel is bound
+// by load latency, a 32-row CTA lives ~4 us and the launch / drain of such short CTAs held the achieved occupancy at 58 % of a 94 % limit.
+// H-pass item:
 //   one thread = 8 adjacent pixels of two adjacent rows: one aligned 64-bit load per row plus the 32-bit words left and right of it, i.e.
 //   6 loads per 16 pixel-rows instead of 12, and one tile / row / address computation per 16 pixel-rows instead of per 8.
-template <bool CLAMP>
+template <bool CLAMP, int TH>
 __global__ void __launch_bounds__(BL_THREADS) orb_blur8_kernel(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
                                                                const __grid_constant__ OrbGeom g) {
-  __shared__ uint4 s_p[(BL_TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
+  __shared__ uint4 s_p[(TH + 8) / 2][BL_TW / 4];   // [row pair][pixel quad]: word j = [h(2k, x+j), h(2k+1, x+j)]
   const int level = orb_level_of(g.blur_base, (int)blockIdx.x);
   const OrbLevel& L = g.lv[level];
   const unsigned t = blockIdx.x - L.blur_tile_base;
   const unsigned ty_ = (t * L.blur_inv_tx) >> 20;            // t / blur_tiles_x (host-checked range)
-  const int x0 = (int)(t - ty_ * L.blur_tiles_x) * BL_TW, y0 = (int)ty_ * BL_TH;
+  const int x0 = (int)(t - ty_ * L.blur_tiles_x) * BL_TW, y0 = (int)ty_ * TH;
   const unsigned long long off = (unsigned long long)blockIdx.y * g.frame_stride + L.plane_off;
   const unsigned tapA = g.blur_k[0], tapB = g.blur_k[1];
-  {
-    const int k = threadIdx.x >> 4, q = threadIdx.x & 15;    // row pair 0..19 (local rows 2k, 2k+1 <-> plane rows y0 - 4 + ..), 8-pixel group
+#pragma unroll
+  for (int item = threadIdx.x; item < (TH + 8) / 2 * 16; item += BL_THREADS) {   // TH = 32: exactly one round
+    const int k = item >> 4, q = item & 15;                  // row pair (local rows 2k, 2k+1 <-> plane rows y0 - 4 + ..), 8-pixel group
+    const bool need = y0 - 4 + 2 * k <= L.rows + 3;          // pairs past the last row a stored pixel reads (bottom tiles of a level) are not summed;
+                                                             // no `break`: the rounds stay unrolled with all their loads issued up front
     const int pitch = L.pitch;
     const uint8_t* src = pyr + off;                          // uniform; the per-thread part is a 32-bit offset
     const int x = x0 + 8 * q;
@@ -87,7 +97,7 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur8_kernel(const uint8_t* __
     // shuffle measured 1.3 % slower on the whole step: the shuffle can only issue once the load has landed)
     const unsigned l0 = __ldg(reinterpret_cast<const unsigned*>(src + o0) - 1), l1 = __ldg(reinterpret_cast<const unsigned*>(src + o1) - 1);
     const unsigned r0 = __ldg(reinterpret_cast<const unsigned*>(src + o0) + 2), r1 = __ldg(reinterpret_cast<const unsigned*>(src + o1) + 2);
-    if (x < L.cols) {
+    if (x < L.cols && need) {
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         unsigned h[2][4];
@@ -109,7 +119,7 @@ __global__ void __launch_bounds__(BL_THREADS) orb_blur8_kernel(const uint8_t* __
     }
   }
   __syncthreads();
-  blur_v_pass<CLAMP>(s_p, blr + off, L, x0, y0, g);
+  blur_v_pass<CLAMP, TH>(s_p, blr + off, L, x0, y0, g);
 }
 
 // TMA == true (ORB_B200_BLUR_TMA=1; measured alternative, 7 % slower: the CTA idles for the box's latency, 41 % of the stall samples on the
@@ -449,10 +459,16 @@ void orb_launch_blur(const uint8_t* pyr, uint8_t* blr, const void* maps, const O
   const dim3 grid(g.blur_tiles_total, batch);
   const bool tma = maps != nullptr && want_tma;
   const OrbLevelMaps& M = tma ? *reinterpret_cast<const OrbLevelMaps*>(maps) : no_maps;
-  static const bool v1 = getenv("ORB_B200_BLUR_V1") != nullptr;   // the 4-pixel H pass of rounds 1-2 (A/B)
-  if (!tma && !v1) {
-    if (sum > 256) orb_blur8_kernel<true><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
-    else orb_blur8_kernel<false><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+  static const bool v1 = getenv("ORB_B200_BLUR_V1") != nullptr;   // the 4-pixel H pass of rounds 1-2 (A/B; needs ORB_B200_BLUR_TH=32 as well)
+  if (g.blur_th == 128) {
+    if (sum > 256) orb_blur8_kernel<true, 128><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+    else orb_blur8_kernel<false, 128><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+  } else if (g.blur_th == 64) {   // the tile table was built for this tile height, only this kernel reads it that way
+    if (sum > 256) orb_blur8_kernel<true, 64><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+    else orb_blur8_kernel<false, 64><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+  } else if (!tma && !v1) {   // ORB_B200_BLUR_TH=32
+    if (sum > 256) orb_blur8_kernel<true, 32><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
+    else orb_blur8_kernel<false, 32><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g);
   } else if (sum > 256) {
     if (tma) orb_blur_kernel<true, true><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);
     else orb_blur_kernel<true, false><<<grid, BL_THREADS, 0, st>>>(pyr, blr, g, M);

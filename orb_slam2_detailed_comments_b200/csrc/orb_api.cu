@@ -129,6 +129,10 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
   g.nlevels = nl; g.width = W; g.height = H;
   g.ini_th = e->prm.ini_th_fast; g.min_th = e->prm.min_th_fast;
   g.pad = (e->prm.flags & ORB_FLAG_UPSTREAM_PYRAMID) ? 0 : ORB_EDGE;
+  {
+    const char* th = getenv("ORB_B200_BLUR_TH");
+    g.blur_th = (th && (atoi(th) == 32 || atoi(th) == 128)) ? atoi(th) : 64;   // 64: +3.4 % on the step against 32 (longer-lived CTAs, two rounds of loads in flight), 128: the same
+  }
   static const int taps_new[7] = {18, 34, 48, 56, 48, 34, 18}, taps_old[7] = {18, 34, 49, 55, 49, 34, 18};
   memcpy(g.blur_taps, (e->prm.flags & ORB_FLAG_LEGACY_BLUR) ? taps_old : taps_new, sizeof(g.blur_taps));
   {
@@ -176,7 +180,7 @@ static int build_geometry(orb_extractor* e, int W, int H, std::vector<ResizeTab>
     L.blur_tiles_x = (L.cols + 127) / 128;
     L.blur_tile_base = btiles;
     L.blur_inv_tx = (1u << 20) / (unsigned)L.blur_tiles_x + 1u;
-    btiles += L.blur_tiles_x * ((L.rows + 31) / 32);
+    btiles += L.blur_tiles_x * ((L.rows + g.blur_th - 1) / g.blur_th);
     L.nIni = (int)roundf((float)(L.maxBX - ORB_MIN_BORDER) / (L.maxBY - ORB_MIN_BORDER));
     if (L.nIni < 1) return fail(ORB_E_SHAPE, "aspect ratio < 0.5: the reference divides by nIni == 0 (src/ORBextractor.cc:1059)");
     L.hX = (float)(L.maxBX - ORB_MIN_BORDER) / L.nIni;

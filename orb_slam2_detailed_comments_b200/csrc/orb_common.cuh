@@ -66,6 +66,7 @@ struct OrbGeom {
   int blur_taps[7];
   unsigned blur_k[10];       // packed tap words of the blur kernel: tapA, tapB (DP4A), e0..e3, o0..o3 (DP2A)
   int blur_tiles_total;
+  int blur_th;               // rows per blur tile: 64 (default), 32 or 128 (ORB_B200_BLUR_TH)
   // first tile of every level (INT_MAX beyond nlevels): a 4-step binary search finds a CTA's level (orb_level_of)
   int blur_base[ORB_MAX_LEVELS];
   int fast_base[ORB_MAX_LEVELS];
