@@ -33,17 +33,29 @@ __global__ void __launch_bounds__(256) orb_pyr_level0_interior_kernel(const uint
   const OrbLevel& L = g.lv[0];
   const int frame = blockIdx.z;
   const int c = c_lo + blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y - (ORB_APRON - 1);
-  if (y >= L.rows + ORB_APRON - 1 || c > c_hi) return;
-  const int sy = orb_reflect101(orb_reflect101(y, L.rows) - g.pad, g.height);
+  if (c > c_hi) return;
+  // four rows per thread (y, y + 8, y + 16, y + 24), all twenty loads issued before the first store: the CTA lives long enough to amortise its launch
   const int x0 = 16 * c - 16;
-  const uint8_t* p = images + (long long)frame * image_stride + (long long)sy * step + (x0 - g.pad);
-  const unsigned sh = 8u * (unsigned)((uintptr_t)p & 3);
-  const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)p & ~(uintptr_t)3);
-  const unsigned w0 = __ldg(ap), w1 = __ldg(ap + 1), w2 = __ldg(ap + 2), w3 = __ldg(ap + 3), w4 = __ldg(ap + 4);
-  uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)y * L.pitch + x0;
-  *reinterpret_cast<uint4*>(dst) = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
-                                              __funnelshift_r(w3, w4, sh));
+  const int ylast = L.rows + ORB_APRON - 2;
+  unsigned w[4][5], sh[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int y = min((int)(blockIdx.y * 32 + threadIdx.y + 8 * r) - (ORB_APRON - 1), ylast);
+    const int sy = orb_reflect101(orb_reflect101(y, L.rows) - g.pad, g.height);
+    const uint8_t* p = images + (long long)frame * image_stride + (long long)sy * step + (x0 - g.pad);
+    sh[r] = 8u * (unsigned)((uintptr_t)p & 3);
+    const unsigned* ap = reinterpret_cast<const unsigned*>((uintptr_t)p & ~(uintptr_t)3);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) w[r][k] = __ldg(ap + k);
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int y = (int)(blockIdx.y * 32 + threadIdx.y + 8 * r) - (ORB_APRON - 1);
+    if (y > ylast) break;
+    uint8_t* dst = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)y * L.pitch + x0;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(__funnelshift_r(w[r][0], w[r][1], sh[r]), __funnelshift_r(w[r][1], w[r][2], sh[r]),
+                                                __funnelshift_r(w[r][2], w[r][3], sh[r]), __funnelshift_r(w[r][3], w[r][4], sh[r]));
+  }
 }
 
 // Border chunks: thread = (row, border chunk e, word k of the chunk); chunk index = e < n_left ? e : c_hi + 1 + (e - n_left).
@@ -288,7 +300,7 @@ void orb_launch_pyramid(const uint8_t* images, int step, long long image_stride,
     const int hi_eff = n_int > 0 ? c_hi : c_lo - 1;
     const int n_left = std::min(c_lo, c_last + 1), n_edge = n_left + (c_last - hi_eff);
     if (n_int > 0) {
-      dim3 grd((n_int + 31) / 32, (nrows + 7) / 8, batch);
+      dim3 grd((n_int + 31) / 32, (nrows + 31) / 32, batch);
       launch_chain(orb_pyr_level0_interior_kernel, grd, blk, st, false, images, step, image_stride, pyr, c_lo, c_hi, g);
       first = false;
       ++*launches;
