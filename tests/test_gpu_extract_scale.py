@@ -150,3 +150,42 @@ def test_dense_texture_never_overflows_a_cell(oracle):
             ex2.check()                                               # nothing to report
             assert int(c2[0]) == n and np.array_equal(d2[0, :n].cpu().numpy(), odesc)
     assert dense > 20000, dense                                       # the noise frame really is dense (> 1 raw keypoint per 25 pixels at level 0)
+
+
+def test_mid_size_host_call_is_cut_into_short_passes(oracle):
+    """A call with host buffers is cut into about eight passes (orb_api.cu ensure_shape: 40 KITTI frames run as passes of 2, 4 and 7 frames over four
+    workspaces) while the same frames resident in HBM run as full 32-frame passes: both must give the same bits, equal to the oracle's."""
+    import torch
+    frames = _tiled(1241, 376, 40, 321, 4)
+    ex = _ex(2000)
+    kps, desc, counts, lc = ex.extract_batch(frames)
+    dk, dd, dc = ex.extract_batch_device(torch.from_numpy(frames).cuda())
+    dk, dd, dc = dk.cpu().numpy(), dd.cpu().numpy(), dc.cpu().numpy()
+    assert np.array_equal(dc, counts)
+    oe = oracle.OracleExtractor(2000)
+    for i in range(40):
+        n = int(counts[i])
+        assert np.array_equal(dk[i, :n].view(np.uint8).reshape(-1), kps[i, :n].view(np.uint8).reshape(-1)) and np.array_equal(dd[i, :n], desc[i, :n]), i
+        if i < 4:
+            _check_frame(oe, frames[i], kps[i], desc[i], n)
+        else:
+            assert n == int(counts[i % 4]) and np.array_equal(desc[i, :n], desc[i % 4, :n]), i
+
+
+def test_mid_size_stereo_call_keeps_pairs_together():
+    """13 EuRoC-sized pairs from host buffers: passes of 10 frames with ramp-up passes of 2 and 6; odd pass sizes are evened so that a pair never
+    straddles two passes. Every pair must equal the same pair extracted alone (one pass)."""
+    from orb_slam2_detailed_comments_b200 import ORBextractor
+    P = 13
+    left = synth.synth_batch(752, 480, P, seed0=500, distinct=P)
+    right = np.ascontiguousarray(np.roll(left, -9, axis=2))
+    ex = ORBextractor(1200, 1.2, 8, 20, 7)
+    kps, desc, counts, ur, dp, matched = ex.extract_stereo_batch(left, right, 47.9, 0.11)
+    one = ORBextractor(1200, 1.2, 8, 20, 7)
+    for i in range(P):
+        k1, d1, c1, u1, p1, m1 = one.extract_stereo_batch(left[i:i + 1], right[i:i + 1], 47.9, 0.11)
+        assert np.array_equal(c1, counts[2 * i:2 * i + 2]) and int(m1[0]) == int(matched[i]), i
+        nl_, nr_ = int(c1[0]), int(c1[1])
+        assert np.array_equal(d1[0, :nl_], desc[2 * i, :nl_]) and np.array_equal(d1[1, :nr_], desc[2 * i + 1, :nr_]), i
+        assert np.array_equal(u1[0, :nl_].view(np.uint32), ur[i, :nl_].view(np.uint32)) and np.array_equal(p1[0, :nl_].view(np.uint32), dp[i, :nl_].view(np.uint32)), i
+    assert int(matched.sum()) > 100 * P

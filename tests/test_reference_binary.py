@@ -153,6 +153,65 @@ def test_oracle_equals_reference_dbow2(oracle, tmp_path, vkw, levelsup):
             assert early == 0 and fv == r[1]      # balanced tree: the whole FeatureVector is defined and equal
 
 
+# ---- seeded sweep of random configurations (sizes, scale factors, level counts, quotas, thresholds, image statistics) ----
+
+def _sweep_cases(count=24, seed=20260):
+    """Deterministic list of (w, h, nf, sf, nl, ini, mn, kind, seed). The coarsest level keeps at least 64 pixels per side: below
+    the 30-pixel FAST cell the reference's own cell arithmetic divides by zero (ORBextractor.cc:1085-1088)."""
+    rng = np.random.RandomState(seed)
+    out = []
+    while len(out) < count:
+        w, h = int(rng.randint(150, 900)), int(rng.randint(120, 560))
+        sf = float(rng.choice([1.1, 1.2, 1.25, 1.33, 1.5, 2.0]))
+        nl = int(rng.randint(1, 9))
+        if min(w, h) / sf ** (nl - 1) < 64:
+            continue
+        ini = int(rng.randint(8, 61))
+        out.append((w, h, int(rng.choice([30, 120, 500, 1000, 1500])), sf, nl, ini, int(rng.randint(1, ini + 1)),
+                    str(rng.choice(["synth", "salted", "lowcontrast"])), int(rng.randint(1, 10000))))
+    return out
+
+
+def _sweep_frame(w, h, kind, seed):
+    img = synth.synth_frame(w, h, seed)
+    rng = np.random.RandomState(seed + 1)
+    if kind == "salted":       # isolated extreme pixels: very high FAST scores, ties in the quadtree's response ordering
+        img = np.where(rng.rand(h, w) < 0.01, rng.choice([0, 255], size=(h, w)), img).astype(np.uint8)
+    elif kind == "lowcontrast":   # most cells fall through to minThFAST
+        img = (96 + (img.astype(np.int32) - 96) // 6).astype(np.uint8)
+    return np.ascontiguousarray(img)
+
+
+SWEEP = _sweep_cases()
+
+
+@needs_ref
+@pytest.mark.parametrize("case", SWEEP, ids=[f"{c[0]}x{c[1]}_s{c[3]}_l{c[4]}_{c[7]}" for c in SWEEP])
+def test_oracle_equals_reference_extractor_sweep(oracle, case):
+    w, h, nf, sf, nl, ini, mn, kind, seed = case
+    img = _sweep_frame(w, h, kind, seed)
+    tabs, ref = ref_binary.ref_extract(img[None], nf, sf, nl, ini, mn)
+    oe = oracle.OracleExtractor(nf, sf, nl, ini, mn)
+    for t in range(4):
+        assert np.array_equal(oe.table(t).view(np.uint32), tabs[t].view(np.uint32)), f"scale table {t}"
+    kps, desc, _ = oe(img)
+    _check_frame(ref[0], kps, desc, [oe.level(l) for l in range(nl)])
+
+
+@pytest.mark.gpu
+@needs_ref
+@pytest.mark.parametrize("case", SWEEP, ids=[f"{c[0]}x{c[1]}_s{c[3]}_l{c[4]}_{c[7]}" for c in SWEEP])
+def test_cuda_equals_reference_extractor_sweep(case):
+    from orb_slam2_detailed_comments_b200 import ORBextractor
+    w, h, nf, sf, nl, ini, mn, kind, seed = case
+    img = _sweep_frame(w, h, kind, seed)
+    _, ref = ref_binary.ref_extract(img[None], nf, sf, nl, ini, mn)
+    ex = ORBextractor(nf, sf, nl, ini, mn)
+    kps, desc, counts, _ = ex.extract_batch(img[None])
+    c = int(counts[0])
+    _check_frame(ref[0], kps[0, :c], desc[0, :c], [ex.pyramid_level(l) for l in range(nl)])
+
+
 # ---- the CUDA path against the reference's own code (GPU box) ----
 
 @pytest.mark.gpu

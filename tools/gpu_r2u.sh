@@ -1,22 +1,24 @@
 #!/bin/bash
-# streams x chunk on the other shapes (pyramid on the high-priority stream)
+# (1) the seeded configuration sweep against the reference's own code on the GPU; (2) 4K pass-size / blur-tile sweep on one box
 set -x
 mkdir -p gpurun_out
-: > gpurun_out/r2u_sweep.txt
-for wl in tum euroc 4k; do
-for cfg in "2 0" "4 0" "4 32" "4 48" "3 64" "4 96" "4 16" "4 8"; do
-  set -- $cfg
-  if [ $wl = 4k ] && [ $2 -gt 16 ]; then continue; fi
-  export ORB_B200_STREAMS=$1
-  if [ $2 = 0 ]; then unset ORB_B200_CHUNK; else export ORB_B200_CHUNK=$2; fi
-  timeout 300 python bench.py --workload $wl --only-headline --no-cpu > gpurun_out/r2u_tmp.json 2> gpurun_out/r2u_tmp.err
-  python - "$wl $cfg" <<'PY' >> gpurun_out/r2u_sweep.txt
-import json,sys
-try:
-    d=json.loads(open("gpurun_out/r2u_tmp.json").read().strip().splitlines()[-1])
-    print("workload streams chunk =", sys.argv[1], "->", round(d["value"]), round(d["e2e"]["value"]))
-except Exception as e: print(sys.argv[1], "failed", e)
+timeout 600 python -m pytest tests/test_reference_binary.py -m gpu -x -q > gpurun_out/r2u_tests.log 2>&1; tail -3 gpurun_out/r2u_tests.log
+run() { # name, env...
+  local name=$1; shift
+  env "$@" timeout 300 python bench.py --workload 4k --only-headline --no-cpu > gpurun_out/r2u_$name.json 2> gpurun_out/r2u_$name.err
+}
+for rep in 1 2; do
+  run def_$rep X=1
+  run c3_$rep ORB_B200_CHUNK=3
+  run c8_$rep ORB_B200_CHUNK=8
+  run c16_$rep ORB_B200_CHUNK=16
+  run b128_$rep ORB_B200_BLUR_TH=128
+done
+python - <<'PY'
+import json, glob
+for f in sorted(glob.glob("gpurun_out/r2u_*.json")):
+    try:
+        d=json.loads(open(f).read().strip().splitlines()[-1])
+        print(f, round(d["value"]), round(d["e2e"]["value"]))
+    except Exception as e: print(f, "failed", e)
 PY
-done
-done
-cat gpurun_out/r2u_sweep.txt
