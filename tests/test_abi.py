@@ -79,3 +79,23 @@ def test_bad_arguments_rejected_before_cuda():
     assert L.orb_hamming_knn(None, 0, 1, None, 0, 0, 0, 256, None, 0, None) == _lib.ORB_E_BADARG
     assert L.orb_extractor_get_levels(None) == 0
     assert L.orb_extractor_max_keypoints(None) == 0
+
+
+def test_peer_knn_bad_arguments_rejected_before_cuda():
+    """The peer-store kNN (include/orb_b200.h orb_knn_peer_*) validates ranks, capacities and pointers before it touches the device; on a box
+    without a GPU a valid create reports ORB_E_CUDA (no CPU fallback)."""
+    from orb_slam2_detailed_comments_b200 import _lib
+    L = _lib.lib()
+    h = C.c_void_p()
+    for rank, nranks, max_q in [(0, 0, 16), (0, 17, 16), (-1, 2, 16), (2, 2, 16), (0, 2, 0)]:
+        assert L.orb_knn_peer_create(rank, nranks, max_q, C.byref(h)) == _lib.ORB_E_BADARG, (rank, nranks, max_q)
+        assert not h.value
+    assert L.orb_knn_peer_create(0, 2, 16, None) == _lib.ORB_E_BADARG
+    buf = (C.c_uint8 * 64)()
+    assert L.orb_knn_peer_export(None, buf) == _lib.ORB_E_BADARG
+    assert L.orb_knn_peer_connect(None, buf) == _lib.ORB_E_BADARG
+    assert L.orb_knn_peer_check(None, None) == _lib.ORB_E_BADARG
+    assert L.orb_hamming_knn_peer(None, None, 0, 1, None, 0, 0, 0, 256, None, 0, None) == _lib.ORB_E_BADARG
+    L.orb_knn_peer_destroy(None)                       # a null handle is ignored
+    if L.orb_device_count() == 0:
+        assert L.orb_knn_peer_create(0, 2, 16, C.byref(h)) == _lib.ORB_E_CUDA and not h.value
