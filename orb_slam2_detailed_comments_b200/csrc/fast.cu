@@ -197,25 +197,24 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
   uint16_t* lists = reinterpret_cast<uint16_t*>(mbar + 1);   // [max_h][row_cap] window offsets, a warp's rows are contiguous
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int frame = blockIdx.y;
-  const int4 T = __ldg(tiles + blockIdx.x);               // level, cell row, first cell, cells
-  const int level = T.x, ci = T.y, j0 = T.z, j1 = T.z + (T.w & 255);
-  // the column tables depend on (level, first cell) only: built once per shape on the host, stored behind the band table
-  const uint8_t* tab = reinterpret_cast<const uint8_t*>(tiles + g.fast_tiles_total) + (size_t)(T.w >> 8) * FAST_TAB_BYTES;
+  // the band's geometry depends on (level, cell row, first cell) only: two int4 per band, built once per shape on the host (orb_fast_build_tiles)
+  const int4 T = __ldg(tiles + 2 * blockIdx.x), U = __ldg(tiles + 2 * blockIdx.x + 1);
+  const int level = T.x & 255, j0 = T.y, j1 = T.y + ((T.x >> 8) & 255);
+  // the column tables depend on (level, first cell) only, stored behind the band table
+  const uint8_t* tab = reinterpret_cast<const uint8_t*>(tiles + 2 * g.fast_tiles_total) + (size_t)((unsigned)T.x >> 16) * FAST_TAB_BYTES;
   const OrbLevel& L = g.lv[level];
   const int wCell = L.wCell;
-  const long long cell0 = (long long)frame * g.ncells_total + L.cell_base + ci * L.nCols;
+  const long long cell0 = (long long)frame * g.ncells_total + T.z;      // + L.cell_base + cell row * L.nCols
   int* cnt_row = cell_cnt + cell0;
   uint32_t* kp_row = cell_kp + cell0 * g.cell_cap;
 
-  const int iniY = ORB_MIN_BORDER + ci * L.hCell;
-  const int wh = min(iniY + L.hCell + 6, L.maxBY) - iniY, dh = wh - 6;   // window rows, detection rows
-  const int X0 = ORB_MIN_BORDER + j0 * wCell;                            // window [X0, X1)
-  const int X1 = min(ORB_MIN_BORDER + j1 * wCell + 6, L.maxBX);
-  if (iniY >= L.maxBY - 3 || dh <= 0 || X1 - X0 <= 6) {                  // :1479-1503 skip rules / empty domain
+  const int iniY = T.w;                                // ORB_MIN_BORDER + cell row * hCell
+  const int wh = U.z & 255, dh = wh - 6;               // window rows, detection rows
+  if (U.z >> 16) {                                     // :1479-1503 skip rules / empty domain
     for (int j = j0 + tid; j < j1; j += FAST_THREADS) cnt_row[j] = 0;
     return;
   }
-  const int xa = X0 & ~15;                         // 16-byte aligned level column of window column 16
+  const int xa = U.x;                              // 16-byte aligned level column of window column 16
   // 1. stage the window
   if (TMA) {
     if (tid == 0) {
@@ -223,13 +222,13 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
       if (orb_smem_u32(win) & 127u) atomicOr(err_flag, 16);   // TMA destination alignment
       orb_mbar_init(bar, 1);
       // the box is the level's full window height (hCell + 6 rows x 256 bytes); rows / bytes outside the plane arrive as zeros
-      orb_mbar_expect_tx(bar, (unsigned)((L.hCell + 6) * FAST_WP + FAST_TAB_BYTES));
+      orb_mbar_expect_tx(bar, (unsigned)((((U.z >> 8) & 255) + 6) * FAST_WP + FAST_TAB_BYTES));
       // tensor coordinates: byte column of the plane allocation (16-byte lead + level column xa - 16), row incl. the apron rows, frame
       orb_tma_load_3d(orb_smem_u32(win), &maps.m[level], xa, iniY + ORB_APRON_ROWS, frame, bar);
       orb_bulk_load_1d(orb_smem_u32(coltab), tab, FAST_TAB_BYTES, bar);   // column tables: same barrier, no thread instructions
     }
   } else {
-    const int nvec = (X1 - xa + 15) >> 4;
+    const int nvec = ((U.y >> 16) + 3 + 15) >> 4;   // window columns [xa, X1), X1 - xa = dx1 + 3
     const uint8_t* src = pyr + (unsigned long long)frame * g.frame_stride + L.plane_off + (long long)iniY * L.pitch + xa;
     // i / nvec == (i * inv) >> 16 for i < 65 * 18 holds for any inv in [65536 / nvec, 65536 / nvec + 2]: one MUFU.RCP instead of a division
     const unsigned inv_nvec = (unsigned)(__frcp_rn((float)nvec) * 65536.f) + 1u;
@@ -249,7 +248,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
     for (int i = tid; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     if (tid < FAST_MAXC) hasini[tid] = 0;
   }
-  const int dx0 = X0 + 3 - xa, dx1 = X1 - 3 - xa;       // detection columns in window coordinates (window column 16 + x)
+  const int dx0 = U.y & 0xffff, dx1 = U.y >> 16;        // detection columns in window coordinates (window column 16 + x)
   const int qbase = dx0 & ~7;                            // groups of 8 aligned pixels
   const int nq = (dx1 - qbase + 7) >> 3;                 // <= 29
   if (!TMA) asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -376,7 +375,7 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
         if (rank < g.cell_cap) {
           const uint32_t s = sc[(y + 1) * FAST_SP + x];
           // cell-local FAST coordinates shifted by (j*wCell, i*hCell) (:1540-1541) == level pixel - 16
-          kp_out[rank] = (uint32_t)(x + xa - ORB_MIN_BORDER) | ((uint32_t)(y + 3 + ci * L.hCell) << 12) | (s << 24);
+          kp_out[rank] = (uint32_t)(x + xa - ORB_MIN_BORDER) | ((uint32_t)(y + 3 + iniY - ORB_MIN_BORDER) << 12) | (s << 24);
         }
         ++rank;
       }
@@ -389,7 +388,8 @@ orb_fast_band_kernel(const uint8_t* __restrict__ pyr, const int4* __restrict__ t
 }
 
 // ---- host side ------------------------------------------------------------------------------------------------
-// Band table: one int4 {level, cell row, first cell, cells | table << 8} per CTA of a frame, levels in ascending order, followed by the column
+// Band table: two int4 per CTA of a frame, {level | cells << 8 | table << 16, first cell, first cell's index in the frame's cell arrays, window row iniY}
+// and {xa, dx0 | dx1 << 16, window rows | hCell << 8 | skip << 16, 0}, levels in ascending order, followed by the column
 // tables (FAST_TAB_BYTES each, one per (level, segment)): per window column cell:3 | left edge:1 | right edge:1 | column inside the cell:6
 // (0xffff outside the detection columns), then per 8-pixel group the mask of detection columns.
 void orb_fast_build_tiles(const OrbGeom& g, std::vector<int4>& tiles) {
@@ -422,7 +422,13 @@ void orb_fast_build_tiles(const OrbGeom& g, std::vector<int4>& tiles) {
     for (int ci = 0; ci < L.nRows; ++ci)
       for (int sg = 0; sg < L.fast_nseg; ++sg) {
         const int j0 = sg * L.fast_G, j1 = std::min(j0 + L.fast_G, L.nCols);
-        tiles.push_back(make_int4(l, ci, j0, std::max(j1 - j0, 0) | ((ntab + sg) << 8)));
+        const int iniY = ORB_MIN_BORDER + ci * L.hCell;
+        const int wh = std::min(iniY + L.hCell + 6, L.maxBY) - iniY;                                    // window rows; detection rows = wh - 6
+        const int X0 = ORB_MIN_BORDER + j0 * L.wCell, X1 = std::min(ORB_MIN_BORDER + j1 * L.wCell + 6, L.maxBX);   // window [X0, X1)
+        const int xa = X0 & ~15;
+        const bool skip = iniY >= L.maxBY - 3 || wh - 6 <= 0 || X1 - X0 <= 6;
+        tiles.push_back(make_int4(l | (std::max(j1 - j0, 0) << 8) | ((ntab + sg) << 16), j0, L.cell_base + ci * L.nCols, iniY));
+        tiles.push_back(make_int4(xa, skip ? 0 : (X0 + 3 - xa) | ((X1 - 3 - xa) << 16), (skip ? 0 : wh) | (L.hCell << 8) | ((skip ? 1 : 0) << 16), 0));
       }
     ntab += L.fast_nseg;
   }
