@@ -647,3 +647,25 @@ def test_search_for_initialization_equals_reference(oracle, seed, ori):
     m12, m21, nm = oracle.search_for_initialization(c["kps"], c["desc"], q, c["qdesc"], c["bounds"], 50, 0.9, ori)
     assert nm == nm_ref and nm_ref > 40, (nm, nm_ref)
     assert np.array_equal(m12, m12_ref)
+
+
+# ---- seed sweep: every pinned matcher again on further seeds with randomised switches (CPU, oracle against the reference's own code) ----
+
+@needs_ref
+@pytest.mark.parametrize("seed", range(20, 36))
+def test_matcher_pins_seed_sweep(oracle, seed):
+    rng = np.random.default_rng(1000 + seed)
+    pick = lambda *a: a[int(rng.integers(len(a)))]
+    flag = lambda: bool(rng.integers(2))
+    test_search_by_projection_equals_reference(oracle, seed, flag(), pick(1.0, 3.0, 5.0), pick(0.6, 0.8, 0.9), None)
+    mode = pick("still", "forward", "backward", "mono")
+    test_frame_to_frame_projection_equals_reference(oracle, seed, mode, mode != "mono" and flag(), flag())
+    test_search_by_bow_equals_reference(oracle, seed, flag(), pick(0.6, 0.7, 0.9))
+    test_search_by_bow_keyframes_equals_reference(oracle, seed, flag(), pick(0.6, 0.75, 0.9))
+    test_fuse_equals_reference(oracle, seed, flag(), pick(3.0, 4.0, 6.0))
+    test_fuse_sim3_form_equals_reference(oracle, seed, flag(), pick(3.0, 4.0))
+    loop_form = flag()
+    test_keyframe_projection_forms_equal_reference(oracle, seed, loop_form, flag(), pick(50, 64, 100))
+    test_search_by_sim3_equals_reference(oracle, seed, pick(7.5, 10.0))
+    test_search_for_triangulation_equals_reference(oracle, seed, flag(), False, flag(), flag())
+    test_search_for_initialization_equals_reference(oracle, seed, flag())
